@@ -279,8 +279,14 @@ typedef struct rayca_options {
     uint32_t traversal;  /* RAYCA_TRAVERSAL_* */
     uint32_t shard_index; /* this process renders image tiles t with t % shard_count == shard_index */
     uint32_t shard_count; /* 0 or 1 = whole image */
-    uint32_t tile_rows;   /* rows per shard tile (0 = default 8) */
+    uint32_t tile_rows;   /* rows per shard tile, a multiple of 8 (0 = default 8) */
+    uint32_t flags;       /* RAYCA_FLAG_* */
+    uint32_t reserved;
 } rayca_options;
+
+enum {
+    RAYCA_FLAG_COUNT_WALK = 1 /* also tally node / triangle records fetched (roofline accounting; slower) */
+};
 
 /* Optional per-pixel planes for parity checks; any pointer may be NULL.
  * For the sample index spp-1 of each pixel (i.e. the only sample at 1 spp). */
@@ -329,6 +335,11 @@ void rayca_cuda_shutdown(rayca_ctx* ctx);
 int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32_t bvh,
                             rayca_scene** out, rayca_stats* stats /*nullable*/);
 void rayca_cuda_scene_destroy(rayca_scene* scene);
+
+/* Host half only (flatten + BVH build, no device, nothing uploaded): the result can be
+ * inspected with the bvh_info / bvh_read calls below and destroyed; it cannot be rendered. */
+int rayca_cuda_scene_create_host(const rayca_scene_desc* desc, uint32_t bvh, rayca_scene** out,
+                                 rayca_stats* stats /*nullable*/);
 
 /* Replaces the pixel loop scene.rs:101-152.  `rgba8_out` is HOST memory,
  * width*height*4 bytes, row-major top-left (rayca-model/src/image.rs:29-31).

@@ -480,7 +480,8 @@ inline bool triangle_intersects_world(Point3 p0, Point3 p1, Point3 p2, const Ray
 struct Tracer {
     const Scene& s;
     bool faithful; // re-transform the three vertices on every test, as the reference does
-    Counters* cnt;
+    Counters* rays; // always valid: ray tallies
+    Counters* cnt;  // non-null only when walk records are being counted
 
     inline bool prim_intersects(const Prim& p, const Ray& ray, float& t, Point3& pt, Vec2& uv) const {
         if (faithful) {
@@ -1055,7 +1056,7 @@ struct Renderer {
                 Vec3 omega = normalized(x_to_x1);
                 Ray shadow = hit.get_next_ray(omega);
                 Hit sh;
-                if (tracer.cnt) tracer.cnt->rays_shadow++;
+                tracer.rays->rays_shadow++;
                 bool occluded = false;
                 if (tracer.intersects(shadow, sh)) {
                     if (sh.depth < dist) occluded = true;
@@ -1082,7 +1083,7 @@ struct Renderer {
         for (uint32_t ls = 0; ls < cfg.c.light_samples; ++ls) {
             Vec3 omega_i = cosine_random_dir(hit, depth, ls);
             Ray next = hit.get_next_ray(omega_i);
-            if (tracer.cnt && (cfg.c.russian_roulette || depth + 1 < cfg.c.max_depth)) tracer.cnt->rays_secondary++;
+            if (cfg.c.russian_roulette || depth + 1 < cfg.c.max_depth) tracer.rays->rays_secondary++;
             Color sample;
             if (pathtracer_trace(next, depth + 1, collect_emissive, hit.pixel, hit.sample, sample)) {
                 // sampler/cosine.rs:90-99 — PI * brdf * indirect_sample * weight
@@ -1139,7 +1140,7 @@ struct Renderer {
                 continue;
             }
             Ray shadow = make_ray(hit.get_next_ray_origin(), light_dir);
-            if (tracer.cnt) tracer.cnt->rays_shadow++;
+            tracer.rays->rays_shadow++;
             Hit sh;
             bool is_light;
             if (!tracer.intersects(shadow, sh)) {
@@ -1167,7 +1168,7 @@ struct Renderer {
         }
         Ray reflection_ray = make_ray(hit.get_next_ray_origin(), hit.get_reflection());
         Color reflection_color;
-        if (depth + 1 <= cfg.c.max_depth && tracer.cnt) tracer.cnt->rays_secondary++;
+        if (depth + 1 <= cfg.c.max_depth) tracer.rays->rays_secondary++;
         if (raytracer_trace(reflection_ray, depth + 1, reflection_color)) {
             float n_dot_r = 1.0f;
             light_contribution = light_contribution + reflection_color * hit.get_specular() * n_dot_r;
@@ -1353,7 +1354,7 @@ int rayca_oracle_render(rayca_oracle_scene* s, const rayca_config* config, const
 #else
         Counters* cnt = &counters[0];
 #endif
-        Renderer r{*s, cfg, Tracer{*s, (flags & RAYCA_ORACLE_FAITHFUL) != 0, (flags & RAYCA_ORACLE_COUNT) ? cnt : nullptr}};
+        Renderer r{*s, cfg, Tracer{*s, (flags & RAYCA_ORACLE_FAITHFUL) != 0, cnt, (flags & RAYCA_ORACLE_COUNT) ? cnt : nullptr}};
         for (uint32_t x = 0; x < width; ++x) {
             Color color = BLACK;
             Hit primary;

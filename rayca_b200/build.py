@@ -1,0 +1,59 @@
+"""Builds rayca_b200/librayca_cuda.so in-tree with nvcc for sm_100a.
+
+  --fmad=false            device code must not contract a*b+c (bit parity with the Rust reference,
+                          which never fuses; the explicit fmaf() calls still emit FFMA)
+  -Xcompiler -ffp-contract=off   same rule for the host flattening / BVH code
+  -lineinfo               so ncu's source page maps to these files
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+OUT = os.path.join(HERE, "librayca_cuda.so")
+SOURCES = ["rayca_cuda.cu", "host_scene.cpp", "bvh_build.cpp"]
+HEADERS = ["rmath.h", "gpu_types.h", "host_scene.h", "trace.cuh", "shade.cuh", "render.cuh",
+           os.path.join("..", "..", "include", "rayca_cuda.h")]
+
+
+def nvcc_path() -> str:
+    for cand in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", shutil.which("nvcc")):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found")
+
+
+def is_stale() -> bool:
+    if not os.path.exists(OUT):
+        return True
+    t = os.path.getmtime(OUT)
+    return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS) or \
+        os.path.getmtime(os.path.abspath(__file__)) > t
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    if not force and not is_stale():
+        return OUT
+    host_cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    cmd = [nvcc_path(), "-shared", "-o", OUT, "-std=c++17", "-O3", "-lineinfo",
+           "-gencode", "arch=compute_100a,code=sm_100a", "--fmad=false",
+           "-ccbin", host_cxx, "-x", "cu",
+           "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math,-fopenmp,-O2",
+           "-Xptxas", "-v" if verbose else "-O3"]
+    cmd += [os.path.join(CSRC, f) for f in SOURCES]
+    cmd += ["-lgomp"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+        raise RuntimeError("nvcc failed")
+    if verbose:
+        sys.stderr.write(res.stdout + res.stderr)
+    return OUT
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

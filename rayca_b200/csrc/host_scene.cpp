@@ -1,0 +1,443 @@
+// host_scene.cpp — scene-graph flattening, primitive emission, TLAS and HBM packing.
+// Reference behaviour restated (file:line relative to the reference checkout):
+//   SceneDrawInfo::new + traverse_*            rayca-soft/src/scene.rs:190-282
+//   BvhPrimitive::from_triangle_mesh_impl      rayca-soft/src/bvh/primitive.rs:194-237
+//   BvhModel::from_model / BvhScene::from_scene primitive.rs:355-394
+//   Tlas::new + replace_models_recursive       rayca-soft/src/bvh/tlas.rs:74-134,248-269
+// Layout decisions that differ from the reference are described in DESIGN.md.
+#include "host_scene.h"
+
+#include <algorithm>
+#include <cstring>
+#include <functional>
+
+namespace rb {
+namespace {
+
+TrsF to_trs(const rayca_trs& t) {
+    TrsF r;
+    r.t = V3{t.translation[0], t.translation[1], t.translation[2]};
+    r.q = Q4{t.rotation[0], t.rotation[1], t.rotation[2], t.rotation[3]};
+    r.s = V3{t.scale[0], t.scale[1], t.scale[2]};
+    return r;
+}
+
+// ---- 3x3 helpers (rayca-math/src/mat3.rs), row-major m[i][j]
+struct M3 {
+    float m[3][3];
+};
+M3 m3_identity() { return M3{{{1, 0, 0}, {0, 1, 0}, {0, 0, 1}}}; }
+// mat3.rs:190-216
+M3 m3_from_quat(Q4 q) {
+    float xx = q.x * q.x, xy = q.x * q.y, xz = q.x * q.z, xw = q.x * q.w;
+    float yy = q.y * q.y, yz = q.y * q.z, yw = q.y * q.w;
+    float zz = q.z * q.z, zw = q.z * q.w;
+    M3 r;
+    r.m[0][0] = 1.0f - 2.0f * (yy + zz); r.m[0][1] = 2.0f * (xy - zw);        r.m[0][2] = 2.0f * (xz + yw);
+    r.m[1][0] = 2.0f * (xy + zw);        r.m[1][1] = 1.0f - 2.0f * (xx + zz); r.m[1][2] = 2.0f * (yz - xw);
+    r.m[2][0] = 2.0f * (xz - yw);        r.m[2][1] = 2.0f * (yz + xw);        r.m[2][2] = 1.0f - 2.0f * (xx + yy);
+    return r;
+}
+// mat3.rs:160-180: e + f + g, left to right
+M3 m3_mul(const M3& a, const M3& b) {
+    M3 r;
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            float e = a.m[i][0] * b.m[0][j], f = a.m[i][1] * b.m[1][j], g = a.m[i][2] * b.m[2][j];
+            r.m[i][j] = e + f + g;
+        }
+    return r;
+}
+M3 m3_scale(V3 s) {
+    M3 r = m3_identity();
+    r.m[0][0] *= s.x; r.m[1][1] *= s.y; r.m[2][2] *= s.z;
+    return r;
+}
+M3 m3_transpose(const M3& a) {
+    M3 r;
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) r.m[i][j] = a.m[j][i];
+    return r;
+}
+// mat3.rs:218-234: ret[i] += m[i][j] * v[j] starting from 0.0
+V3 m3_apply(const M3& a, V3 v) {
+    float in[3] = {v.x, v.y, v.z}, out[3] = {0.0f, 0.0f, 0.0f};
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) out[i] += a.m[i][j] * in[j];
+    return V3{out[0], out[1], out[2]};
+}
+// Mat3::from(&Trs) (mat3.rs:126-132): from_scale then rotate => Mat3::from(q) * S
+M3 tangent_matrix_of(const TrsF& t) { return m3_mul(m3_from_quat(t.q), m3_scale(t.s)); }
+// Mat3::from(&Inversed<&Trs>).get_transpose() (mat3.rs:140-144, trs.rs:320-331)
+M3 normal_matrix_of(const TrsF& t) {
+    M3 rot = m3_mul(m3_from_quat(conj(t.q)), m3_identity()); // Mat3::from_rotation
+    return m3_transpose(m3_mul(m3_scale(reciprocal(t.s)), rot));
+}
+
+struct MeshDraw {
+    uint32_t node_local;
+    TrsF world;
+};
+
+struct Flatten {
+    const rayca_scene_desc& d;
+    HostScene& out;
+    std::vector<std::vector<MeshDraw>> mesh_draws; // per model, traversal order
+    std::string err;
+    int status = RAYCA_OK;
+
+    explicit Flatten(const rayca_scene_desc& desc, HostScene& o) : d(desc), out(o), mesh_draws(desc.model_count) {}
+
+    void model_nodes(const TrsF& parent, uint32_t node, uint32_t mi, int depth) {
+        const rayca_model& m = d.models[mi];
+        if (node >= m.node_count || depth > 4096) { status = RAYCA_E_INVALID_ARG; err = "bad node index"; return; }
+        const rayca_node& n = d.nodes[m.node_offset + node];
+        TrsF cur = trs_mul(parent, to_trs(n.trs));
+        if (n.mesh >= 0) mesh_draws[mi].push_back(MeshDraw{node, cur});
+        if (n.light >= 0) {
+            const rayca_light& l = d.lights[m.light_offset + (uint32_t)n.light];
+            GpuLight g{};
+            std::memcpy(g.color, l.color, sizeof(g.color));
+            g.intensity = l.intensity;
+            std::memcpy(g.att, l.attenuation, sizeof(g.att));
+            g.kind = l.kind;
+            TrsF local = to_trs(n.trs); // lights read the node's LOCAL trs (nee.rs:133-134, raytracer.rs:37-39)
+            V3 p = rotate(local.t, local.q); // Trs::get_translation (trs.rs:126-128)
+            g.pos[0] = p.x; g.pos[1] = p.y; g.pos[2] = p.z;
+            V3 dir = -rotate(V3{1.0f, 0.0f, 0.0f}, local.q);
+            g.dir[0] = dir.x; g.dir[1] = dir.y; g.dir[2] = dir.z;
+            out.lights.push_back(g);
+        }
+        if (n.camera >= 0 && !out.has_camera) { // camera_draw_infos[0] (scene.rs:109-112)
+            out.has_camera = true;
+            GpuCamera& c = out.camera;
+            c.t[0] = cur.t.x; c.t[1] = cur.t.y; c.t[2] = cur.t.z;
+            c.q[0] = cur.q.x; c.q[1] = cur.q.y; c.q[2] = cur.q.z; c.q[3] = cur.q.w;
+            c.s[0] = cur.s.x; c.s[1] = cur.s.y; c.s[2] = cur.s.z;
+            c.angle = tanf(d.cameras[m.camera_offset + (uint32_t)n.camera].yfov_radians * 0.5f);
+        }
+        for (uint32_t i = 0; i < n.child_count; ++i) model_nodes(cur, d.children[n.first_child + i], mi, depth + 1);
+    }
+    void scene_nodes(const TrsF& parent, uint32_t node, int depth) {
+        if (node >= d.scene_node_count || depth > 4096) { status = RAYCA_E_INVALID_ARG; err = "bad scene node"; return; }
+        const rayca_node& n = d.scene_nodes[node];
+        TrsF cur = trs_mul(parent, to_trs(n.trs));
+        if (n.model >= 0) {
+            if ((uint32_t)n.model >= d.model_count) { status = RAYCA_E_INVALID_ARG; err = "bad model index"; return; }
+            const rayca_model& m = d.models[n.model];
+            TrsF mt = trs_mul(cur, to_trs(m.root_trs));
+            for (uint32_t i = 0; i < m.root_child_count; ++i)
+                model_nodes(mt, d.children[m.root_first_child + i], (uint32_t)n.model, depth + 1);
+        }
+        for (uint32_t i = 0; i < n.child_count; ++i) scene_nodes(cur, d.children[n.first_child + i], depth + 1);
+    }
+    void run() {
+        TrsF root = to_trs(d.root_trs);
+        for (uint32_t i = 0; i < d.root_child_count; ++i) scene_nodes(root, d.children[d.root_first_child + i], 0);
+    }
+};
+
+// Resolve every (model, material handle) to one flat GPU record; index 0 is the fallback
+// Material::DEFAULT = Pbr(NONE) -> PbrMaterial::WHITE (primitive.rs:103-110, pbr.rs:73-80).
+GpuMaterial white_pbr() {
+    GpuMaterial g{};
+    g.a[0] = g.a[1] = g.a[2] = g.a[3] = 1.0f;
+    g.p0 = 0.0f;
+    g.p1 = 1.0f;
+    g.tex_albedo = g.tex_normal = g.tex_mr = -1;
+    g.kind = RAYCA_MATERIAL_PBR;
+    return g;
+}
+bool color_close_black(const float c[4]) { // Color::close (color/mod.rs:160-169) against BLACK
+    return fabsf(c[0] - 0.0f) < kF32Eps && fabsf(c[1] - 0.0f) < kF32Eps && fabsf(c[2] - 0.0f) < kF32Eps &&
+           fabsf(c[3] - 1.0f) < kF32Eps;
+}
+
+} // namespace
+
+int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::string& err) {
+    Flatten f(d, out);
+    f.run();
+    if (f.status != RAYCA_OK) { err = f.err; return f.status; }
+
+    // ---- images (texels are copied verbatim: nearest, no sRGB decode; sampler.rs:11-29)
+    out.images.resize(d.image_count);
+    for (uint32_t i = 0; i < d.image_count; ++i) {
+        const rayca_image& im = d.images[i];
+        size_t bpp = im.color_type == RAYCA_COLOR_RGB8 ? 3 : (im.color_type == RAYCA_COLOR_RGBA8 ? 4 : 16);
+        size_t bytes = (size_t)im.width * im.height * bpp;
+        size_t off = (out.texels.size() + 15) & ~size_t(15);
+        out.texels.resize(off + bytes);
+        if (bytes) std::memcpy(out.texels.data() + off, im.data, bytes);
+        out.images[i] = GpuImage{(unsigned long long)off, im.width, im.height, im.color_type, 0};
+    }
+
+    // ---- materials: [0] fallback, then per model in order
+    out.materials.push_back(white_pbr());
+    std::vector<uint32_t> model_mat_base(d.model_count, 0);
+    for (uint32_t mi = 0; mi < d.model_count; ++mi) {
+        const rayca_model& m = d.models[mi];
+        model_mat_base[mi] = (uint32_t)out.materials.size();
+        auto tex = [&](int32_t t) -> int32_t { // model.textures.get(handle) -> image
+            if (t < 0 || (uint32_t)t >= m.texture_count) return -1;
+            int32_t img = d.textures[m.texture_offset + (uint32_t)t].image;
+            if (img < 0 || (uint32_t)img >= m.image_count) return -1;
+            return (int32_t)(m.image_offset + (uint32_t)img);
+        };
+        for (uint32_t k = 0; k < m.material_count; ++k) {
+            const rayca_material& mat = d.materials[m.material_offset + k];
+            GpuMaterial g{};
+            g.tex_albedo = g.tex_normal = g.tex_mr = -1;
+            g.kind = mat.kind;
+            if (mat.kind == RAYCA_MATERIAL_PBR) {
+                if (mat.index < 0 || (uint32_t)mat.index >= m.pbr_count) {
+                    g = white_pbr();
+                } else {
+                    const rayca_pbr_material& p = d.pbr_materials[m.pbr_offset + (uint32_t)mat.index];
+                    std::memcpy(g.a, p.color, 16);
+                    g.p0 = p.metallic_factor;
+                    g.p1 = p.roughness_factor;
+                    g.tex_albedo = tex(p.albedo);
+                    g.tex_normal = tex(p.normal);
+                    g.tex_mr = tex(p.metallic_roughness);
+                }
+            } else if (mat.kind == RAYCA_MATERIAL_PHONG) {
+                rayca_phong_material p{{0, 0, 0, 1}, {0, 0, 0, 1}, {0, 0, 0, 1}, {0, 0, 0, 1}, 0.0f}; // PhongMaterial::DEFAULT
+                if (mat.index >= 0 && (uint32_t)mat.index < m.phong_count) p = d.phong_materials[m.phong_offset + (uint32_t)mat.index];
+                std::memcpy(g.a, p.ambient, 16);
+                std::memcpy(g.b, p.emission, 16);
+                std::memcpy(g.c, p.diffuse, 16);
+                std::memcpy(g.d, p.specular, 16);
+                g.p0 = p.shininess;
+                g.emissive = color_close_black(p.emission) ? 0u : 1u;
+            } else if (mat.kind == RAYCA_MATERIAL_GGX) {
+                rayca_ggx_material p{{0, 0, 0, 1}, {0, 0, 0, 1}, 0.0f};
+                if (mat.index >= 0 && (uint32_t)mat.index < m.ggx_count) p = d.ggx_materials[m.ggx_offset + (uint32_t)mat.index];
+                std::memcpy(g.a, p.diffuse, 16);
+                std::memcpy(g.d, p.specular, 16);
+                g.p0 = p.roughness;
+            } else {
+                err = "unknown material kind";
+                return RAYCA_E_INVALID_ARG;
+            }
+            out.materials.push_back(g);
+        }
+    }
+
+    // ---- BvhScene::from_scene: one BLAS per model that owns mesh nodes, ascending model handle
+    // (the reference iterates a HashMap; the order only matters for exact cross-BLAS depth ties)
+    for (uint32_t mi = 0; mi < d.model_count; ++mi) {
+        if (f.mesh_draws[mi].empty()) continue;
+        const rayca_model& m = d.models[mi];
+        HostBlas blas;
+        blas.model = mi;
+        for (const MeshDraw& md : f.mesh_draws[mi]) {
+            const rayca_node& n = d.nodes[m.node_offset + md.node_local];
+            if ((uint32_t)n.mesh >= m.mesh_count) { err = "bad mesh index"; return RAYCA_E_INVALID_ARG; }
+            const rayca_mesh& mesh = d.meshes[m.mesh_offset + (uint32_t)n.mesh];
+            M3 tangent_matrix = tangent_matrix_of(md.world);
+            M3 normal_matrix = normal_matrix_of(md.world);
+            for (uint32_t pi = 0; pi < mesh.primitive_count; ++pi) {
+                uint32_t ph = d.mesh_primitives[mesh.first_primitive + pi];
+                if (ph >= m.primitive_count) { err = "bad primitive handle"; return RAYCA_E_INVALID_ARG; }
+                const rayca_primitive& prim = d.primitives[m.primitive_offset + ph];
+                if (prim.geometry >= m.geometry_count) { err = "bad geometry handle"; return RAYCA_E_INVALID_ARG; }
+                const rayca_geometry& g = d.geometries[m.geometry_offset + prim.geometry];
+                if (g.kind != RAYCA_GEOMETRY_TRIANGLE_MESH) { err = "sphere geometry is not supported yet"; return RAYCA_E_UNSUPPORTED; }
+                uint32_t material = 0;
+                if (prim.material >= 0 && (uint32_t)prim.material < m.material_count) material = model_mat_base[mi] + (uint32_t)prim.material;
+                uint32_t ntri = g.index_count / 3;
+                size_t base = blas.tris.size();
+                blas.tris.resize(base + ntri);
+                blas.attrs.resize(base + ntri);
+                int bad = 0;
+#pragma omp parallel for schedule(static) if (ntri > 8192)
+                for (int64_t t = 0; t < (int64_t)ntri; ++t) {
+                    HostTri& ht = blas.tris[base + (size_t)t];
+                    HostAttr& ha = blas.attrs[base + (size_t)t];
+                    V3 mv[3];
+                    for (int k = 0; k < 3; ++k) {
+                        uint32_t vi = d.indices[g.first_index + (size_t)t * 3 + k];
+                        if (vi >= g.vertex_count) { bad = 1; vi = 0; }
+                        const rayca_vertex& v = d.vertices[g.first_vertex + vi];
+                        mv[k] = V3{v.pos[0], v.pos[1], v.pos[2]};
+                        std::memcpy(ha.color[k], v.color, 16);
+                        ha.normal[k] = m3_apply(normal_matrix, V3{v.normal[0], v.normal[1], v.normal[2]});
+                        ha.tangent[k] = m3_apply(tangent_matrix, V3{v.tangent[0], v.tangent[1], v.tangent[2]});
+                        ha.bitangent[k] = m3_apply(tangent_matrix, V3{v.bitangent[0], v.bitangent[1], v.bitangent[2]});
+                        ha.uv[k][0] = v.uv[0];
+                        ha.uv[k][1] = v.uv[1];
+                        ht.v[k] = trs_point(md.world, mv[k]); // Triangle::get_vertex (triangle.rs:67-69)
+                    }
+                    ha.material = material;
+                    // Triangle::new centroid quirk (triangle.rs:59-62) then `trs * Vec3` (trs.rs:253-262)
+                    V3 c = ((mv[0] + mv[1]) + mv[2]) * 0.3333f;
+                    ht.centroid = trs_vec(md.world, c);
+                    ht.bmin = V3{fminf(fminf(fminf(kF32Max, ht.v[0].x), ht.v[1].x), ht.v[2].x),
+                                 fminf(fminf(fminf(kF32Max, ht.v[0].y), ht.v[1].y), ht.v[2].y),
+                                 fminf(fminf(fminf(kF32Max, ht.v[0].z), ht.v[1].z), ht.v[2].z)};
+                    ht.bmax = V3{fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].x), ht.v[1].x), ht.v[2].x),
+                                 fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].y), ht.v[1].y), ht.v[2].y),
+                                 fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].z), ht.v[1].z), ht.v[2].z)};
+                    ht.src = (uint32_t)(base + (size_t)t);
+                }
+                if (bad) { err = "vertex index out of range"; return RAYCA_E_INVALID_ARG; }
+            }
+        }
+        build_blas(blas, bvh ? 255u : 0u); // scene.rs:95-99: !config.bvh => max_depth(0)
+        out.blas.push_back(std::move(blas));
+    }
+    if (out.blas.empty()) { // Tlas::new would assert on an empty range (tlas.rs:75)
+        err = "scene has no triangle geometry";
+        return RAYCA_E_INVALID_ARG;
+    }
+
+    // ---- TLAS (tlas.rs:74-134): median split of BLAS root boxes on the longest axis, then
+    // re-expressed as adjacent node pairs above the BLAS roots.
+    struct TNode {
+        V3 bmin, bmax;
+        int left = -1, right = -1;
+        uint32_t offset = 0, count = 0;
+    };
+    std::vector<uint32_t> order(out.blas.size());
+    for (uint32_t i = 0; i < order.size(); ++i) order[i] = i;
+    std::vector<TNode> tnodes;
+    std::function<int(uint32_t, uint32_t)> tbuild = [&](uint32_t offset, uint32_t count) -> int {
+        TNode self;
+        self.offset = offset;
+        self.count = count;
+        self.bmin = V3{kF32Max, kF32Max, kF32Max};
+        self.bmax = V3{-kF32Max, -kF32Max, -kF32Max};
+        for (uint32_t i = offset; i < offset + count; ++i) {
+            const HostNode& r = out.blas[order[i]].nodes[0];
+            self.bmin = V3{fminf(self.bmin.x, r.bmin.x), fminf(self.bmin.y, r.bmin.y), fminf(self.bmin.z, r.bmin.z)};
+            self.bmax = V3{fmaxf(self.bmax.x, r.bmax.x), fmaxf(self.bmax.y, r.bmax.y), fmaxf(self.bmax.z, r.bmax.z)};
+        }
+        V3 extent = self.bmax - self.bmin;
+        int axis = 0;
+        if (extent.y > extent.x) axis = 1;
+        float ea = axis == 0 ? extent.x : extent.y;
+        if (extent.z > ea) axis = 2;
+        auto ax = [&](const V3& v) { return axis == 0 ? v.x : (axis == 1 ? v.y : v.z); };
+        float split = ax(self.bmin) + ax(extent) * 0.5f;
+        size_t i = offset, j = (size_t)offset + count;
+        while (i < j) {
+            const HostNode& r = out.blas[order[i]].nodes[0];
+            V3 centroid = (r.bmax - r.bmin) / 2.0f; // AABB::get_centroid is the half EXTENT (aabb.rs:95-97)
+            if (ax(centroid) < split) {
+                ++i;
+            } else {
+                std::swap(order[i], order[j - 1]);
+                --j;
+            }
+        }
+        uint32_t lc = (uint32_t)i - offset, rc = count - lc;
+        if (lc > 0 && rc > 0) {
+            self.left = tbuild(offset, lc);
+            self.right = tbuild(offset + lc, rc);
+            self.count = 0;
+        }
+        tnodes.push_back(self);
+        return (int)tnodes.size() - 1;
+    };
+    int troot = tbuild(0, (uint32_t)order.size());
+    {   // apply the TLAS permutation so that blas[i] is blas_nodes[i] (Hit::blas, tlas.rs:152)
+        std::vector<HostBlas> sorted;
+        sorted.reserve(out.blas.size());
+        for (uint32_t i : order) sorted.push_back(std::move(out.blas[i]));
+        out.blas.swap(sorted);
+    }
+
+    // ---- pack BLAS nodes / triangles
+    size_t total_nodes = 0, total_tris = 0;
+    out.blas_node_offset.assign(1, 0);
+    out.blas_prim_offset.assign(1, 0);
+    for (const HostBlas& b : out.blas) {
+        total_nodes += b.nodes.size();
+        total_tris += b.tris.size();
+        out.blas_node_offset.push_back((uint32_t)total_nodes);
+        out.blas_prim_offset.push_back((uint32_t)total_tris);
+    }
+    if (total_tris >= 0xFFFFFFF0ull || total_nodes >= 0xFFFFFFF0ull) { err = "scene too large"; return RAYCA_E_UNSUPPORTED; }
+    out.nodes.resize(total_nodes);
+    out.tri_pos.resize(total_tris * 3);
+    out.tri_attr.resize(total_tris * 12);
+    uint32_t max_blas_depth = 0;
+    for (size_t bi = 0; bi < out.blas.size(); ++bi) {
+        const HostBlas& b = out.blas[bi];
+        uint32_t no = out.blas_node_offset[bi], po = out.blas_prim_offset[bi];
+        max_blas_depth = std::max(max_blas_depth, b.depth);
+        for (size_t k = 0; k < b.nodes.size(); ++k) {
+            const HostNode& n = b.nodes[k];
+            GpuNode g;
+            g.min_x = n.bmin.x; g.min_y = n.bmin.y; g.min_z = n.bmin.z;
+            g.max_x = n.bmax.x; g.max_y = n.bmax.y; g.max_z = n.bmax.z;
+            g.link0 = n.count ? po + n.offset : no + n.offset;
+            g.link1 = n.count;
+            out.nodes[no + k] = g;
+        }
+#pragma omp parallel for schedule(static) if (b.tris.size() > 8192)
+        for (int64_t k = 0; k < (int64_t)b.tris.size(); ++k) {
+            const HostTri& t = b.tris[(size_t)k];
+            const HostAttr& a = b.attrs[t.src];
+            size_t gi = (size_t)po + (size_t)k;
+            float4* p = &out.tri_pos[gi * 3];
+            p[0] = make_float4(t.v[0].x, t.v[0].y, t.v[0].z, __builtin_bit_cast(float, t.src));
+            p[1] = make_float4(t.v[1].x, t.v[1].y, t.v[1].z, __builtin_bit_cast(float, a.material));
+            p[2] = make_float4(t.v[2].x, t.v[2].y, t.v[2].z, __builtin_bit_cast(float, (uint32_t)bi));
+            float4* q = &out.tri_attr[gi * 12];
+            for (int v = 0; v < 3; ++v) {
+                q[v] = make_float4(a.color[v][0], a.color[v][1], a.color[v][2], a.color[v][3]);
+                q[3 + v] = make_float4(a.normal[v].x, a.normal[v].y, a.normal[v].z, a.uv[v][0]);
+                q[6 + v] = make_float4(a.tangent[v].x, a.tangent[v].y, a.tangent[v].z, a.uv[v][1]);
+                q[9 + v] = make_float4(a.bitangent[v].x, a.bitangent[v].y, a.bitangent[v].z,
+                                       v == 0 ? __builtin_bit_cast(float, a.material) : 0.0f);
+            }
+        }
+    }
+
+    // ---- TLAS top pairs: every record is a (box, links) copy of its child, so the walk needs
+    // only one node format.  A TLAS leaf holding k > 1 BLAS becomes a right-leaning comb whose
+    // boxes are unions of BLAS root boxes (supersets never reject what the reference accepts).
+    auto blas_root_record = [&](uint32_t bi) -> GpuNode { return out.nodes[out.blas_node_offset[bi]]; };
+    uint32_t top_depth = 0;
+    std::function<GpuNode(int, uint32_t)> emit_tnode;
+    std::function<GpuNode(uint32_t, uint32_t, uint32_t)> emit_comb = [&](uint32_t first, uint32_t count, uint32_t depth) -> GpuNode {
+        top_depth = std::max(top_depth, depth);
+        if (count == 1) return blas_root_record(first);
+        uint32_t pair = (uint32_t)out.nodes.size();
+        out.nodes.resize(out.nodes.size() + 2);
+        GpuNode l = blas_root_record(first);
+        GpuNode r = emit_comb(first + 1, count - 1, depth + 1);
+        out.nodes[pair] = l;
+        out.nodes[pair + 1] = r;
+        GpuNode self;
+        self.min_x = fminf(l.min_x, r.min_x); self.min_y = fminf(l.min_y, r.min_y); self.min_z = fminf(l.min_z, r.min_z);
+        self.max_x = fmaxf(l.max_x, r.max_x); self.max_y = fmaxf(l.max_y, r.max_y); self.max_z = fmaxf(l.max_z, r.max_z);
+        self.link0 = pair;
+        self.link1 = 0;
+        return self;
+    };
+    emit_tnode = [&](int ti, uint32_t depth) -> GpuNode {
+        top_depth = std::max(top_depth, depth);
+        const TNode tn = tnodes[(size_t)ti];
+        if (tn.left < 0 && tn.right < 0) return emit_comb(tn.offset, tn.count, depth);
+        uint32_t pair = (uint32_t)out.nodes.size();
+        out.nodes.resize(out.nodes.size() + 2);
+        GpuNode l = emit_tnode(tn.left, depth + 1);
+        GpuNode r = emit_tnode(tn.right, depth + 1);
+        out.nodes[pair] = l;
+        out.nodes[pair + 1] = r;
+        GpuNode self;
+        self.min_x = tn.bmin.x; self.min_y = tn.bmin.y; self.min_z = tn.bmin.z;
+        self.max_x = tn.bmax.x; self.max_y = tn.bmax.y; self.max_z = tn.bmax.z;
+        self.link0 = pair;
+        self.link1 = 0;
+        return self;
+    };
+    out.root = emit_tnode(troot, 0);
+    out.max_stack = top_depth + max_blas_depth + 2;
+    return RAYCA_OK;
+}
+
+} // namespace rb

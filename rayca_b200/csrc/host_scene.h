@@ -1,0 +1,72 @@
+// host_scene.h — host half of `SoftRenderer::draw` before the pixel loop
+// (rayca-soft/src/scene.rs:90-115): scene-graph flattening, per-model primitive emission,
+// BLAS/TLAS construction, and packing into the HBM layout of gpu_types.h.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/rayca_cuda.h"
+#include "gpu_types.h"
+#include "rmath.h"
+
+namespace rb {
+
+// One triangle as emitted by BvhPrimitive::from_triangle_mesh_impl (bvh/primitive.rs:194-237),
+// already moved to world space with the reference's `trs * vertex` operation order.
+struct HostTri {
+    V3 v[3];       // world space
+    V3 centroid;   // world-space `trs * ((a+b+c)*0.3333)` used by the SAH partition
+    V3 bmin, bmax; // world-space bounds of the three vertices
+    uint32_t src;  // emit order inside its model (stable id)
+};
+
+struct HostAttr {
+    float color[3][4];
+    V3 normal[3], tangent[3], bitangent[3];
+    float uv[3][2];
+    uint32_t material; // index into HostScene::materials
+};
+
+struct HostNode {
+    V3 bmin, bmax;
+    uint32_t offset, count; // count != 0: leaf over [offset, offset+count); else children offset, offset+1
+};
+
+struct HostBlas {
+    std::vector<HostTri> tris;   // reordered in place by the build
+    std::vector<HostAttr> attrs; // indexed by HostTri::src
+    std::vector<HostNode> nodes; // node 0 root, node 1 unused (blas.rs:250-256)
+    uint32_t model = 0;
+    uint32_t depth = 0;
+};
+
+struct HostScene {
+    std::vector<HostBlas> blas;          // in TLAS-reordered (blas_nodes) order after build
+    std::vector<GpuMaterial> materials;  // [0] = Material::DEFAULT -> PbrMaterial::WHITE
+    std::vector<GpuImage> images;
+    std::vector<unsigned char> texels;
+    std::vector<GpuLight> lights;
+    GpuCamera camera{};
+    bool has_camera = false;
+
+    // packed output
+    std::vector<GpuNode> nodes;          // all BLAS nodes (offset-adjusted) followed by TLAS top pairs
+    std::vector<float4> tri_pos;
+    std::vector<float4> tri_attr;
+    std::vector<uint32_t> blas_prim_offset, blas_node_offset;
+    GpuNode root{};
+    uint32_t max_stack = 0;              // deepest push chain the ordered walk can need
+};
+
+// Returns RAYCA_OK or a negative RAYCA_E_* code; `err` receives a detail string.
+int build_host_scene(const rayca_scene_desc& desc, bool bvh, HostScene& out, std::string& err);
+
+// BLAS build: top-down SAH over 63 planes x 3 axes with the reference's tie-breaking
+// (bvh/blas.rs:64-127,245-316), evaluated through per-plane bins so that one pass over the
+// node's triangles serves all 189 candidates.  `max_depth` = u8::MAX, or 0 when Config::bvh is off.
+void build_blas(HostBlas& blas, uint32_t max_depth);
+
+} // namespace rb

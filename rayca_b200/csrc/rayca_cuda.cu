@@ -1,0 +1,484 @@
+// rayca_cuda.cu — C ABI of librayca_cuda (include/rayca_cuda.h): context, scene upload, render.
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/rayca_cuda.h"
+#include "host_scene.h"
+#include "render.cuh"
+
+using namespace rb;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+#define CUDA_TRY(expr)                                                                                      \
+    do {                                                                                                    \
+        cudaError_t e__ = (expr);                                                                           \
+        if (e__ != cudaSuccess)                                                                             \
+            return fail(e__ == cudaErrorMemoryAllocation ? RAYCA_E_OOM : RAYCA_E_CUDA,                     \
+                        std::string(#expr) + ": " + cudaGetErrorString(e__));                               \
+    } while (0)
+
+double now_ms() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+} // namespace
+
+struct rayca_ctx {
+    int device = 0;
+    unsigned long long* d_counters = nullptr; // 4 x u64
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    rayca_stats last{};
+    uint64_t last_primary = 0;
+    // scratch for the host-buffer entry point
+    void* d_scratch = nullptr;
+    size_t scratch_bytes = 0;
+};
+
+struct rayca_scene {
+    rayca_ctx* ctx = nullptr;
+    HostScene host; // kept for BVH read-back; texel / attribute vectors are released after upload
+    void* d_nodes = nullptr;
+    void* d_tri_pos = nullptr;
+    void* d_tri_attr = nullptr;
+    void* d_materials = nullptr;
+    void* d_images = nullptr;
+    void* d_texels = nullptr;
+    void* d_lights = nullptr;
+    void* d_blas_prim_offset = nullptr;
+    GpuSceneView view{};
+    uint32_t max_stack = 0;
+};
+
+namespace {
+
+template <typename T>
+int upload(void** dst, const std::vector<T>& src) {
+    size_t bytes = std::max<size_t>(src.size() * sizeof(T), 16);
+    CUDA_TRY(cudaMalloc(dst, bytes));
+    if (!src.empty()) CUDA_TRY(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return RAYCA_OK;
+}
+
+int validate_config(const rayca_config& c, const rayca_scene& sc) {
+    if (c.samples_per_pixel == 0) return fail(RAYCA_E_INVALID_ARG, "samples_per_pixel must be >= 1");
+    if (!(c.gamma == c.gamma) || c.gamma == 0.0f) return fail(RAYCA_E_INVALID_ARG, "gamma must be non-zero");
+    switch (c.integrator) {
+        case RAYCA_INTEGRATOR_FLAT: break;
+        case RAYCA_INTEGRATOR_RAYTRACER:
+            if (c.max_depth + 1 > (uint32_t)kMaxDepth) return fail(RAYCA_E_UNSUPPORTED, "max_depth > 16");
+            for (const GpuLight& l : sc.host.lights) // Light::get_direction is todo!() for quad lights (light/mod.rs:79-85)
+                if (l.kind == RAYCA_LIGHT_QUAD) return fail(RAYCA_E_UNSUPPORTED, "quad lights under the raytracer");
+            break;
+        case RAYCA_INTEGRATOR_PATHTRACER: {
+            if (c.russian_roulette) return fail(RAYCA_E_UNSUPPORTED, "russian roulette");
+            if (c.direct_sampler != RAYCA_SAMPLER_NEE && c.direct_sampler != RAYCA_SAMPLER_NONE)
+                return fail(RAYCA_E_UNSUPPORTED, "direct sampler (only None / Nee)");
+            if (c.max_depth > (uint32_t)kMaxDepth) return fail(RAYCA_E_UNSUPPORTED, "max_depth > 17");
+            if (c.light_samples == 0) return fail(RAYCA_E_INVALID_ARG, "light_samples must be >= 1");
+            bool nee = c.direct_sampler == RAYCA_SAMPLER_NEE;
+            bool bounces = c.max_depth > (nee ? 1u : 0u);
+            if (bounces && c.indirect_sampler != RAYCA_SAMPLER_COSINE) return fail(RAYCA_E_UNSUPPORTED, "indirect sampler (only Cosine)");
+            if (bounces && c.light_samples != 1) return fail(RAYCA_E_UNSUPPORTED, "light_samples > 1 with indirect bounces");
+            if (nee)
+                for (const GpuLight& l : sc.host.lights) // NEE: directional is todo!() (nee.rs:177); quad is a later row
+                    if (l.kind != RAYCA_LIGHT_POINT) return fail(RAYCA_E_UNSUPPORTED, "NEE supports point lights only");
+            break;
+        }
+        default: return fail(RAYCA_E_UNSUPPORTED, "integrator (only Raytracer / Flat / Pathtracer)");
+    }
+    return RAYCA_OK;
+}
+
+template <int INTEGRATOR>
+void launch_integrator(const RenderParams& P, dim3 grid, bool cull, bool count, cudaStream_t st) {
+    if (count) {
+        if (cull) render_kernel<INTEGRATOR, true, true><<<grid, 128, 0, st>>>(P);
+        else render_kernel<INTEGRATOR, false, true><<<grid, 128, 0, st>>>(P);
+    } else {
+        if (cull) render_kernel<INTEGRATOR, true, false><<<grid, 128, 0, st>>>(P);
+        else render_kernel<INTEGRATOR, false, false><<<grid, 128, 0, st>>>(P);
+    }
+}
+
+} // namespace
+
+extern "C" {
+
+uint32_t rayca_cuda_abi_version(void) { return 1; }
+
+const char* rayca_cuda_last_error(void) { return g_last_error.c_str(); }
+
+const char* rayca_cuda_strerror(int code) {
+    switch (code) {
+        case RAYCA_OK: return "ok";
+        case RAYCA_E_INVALID_ARG: return "invalid argument";
+        case RAYCA_E_UNSUPPORTED: return "unsupported configuration";
+        case RAYCA_E_OOM: return "out of memory";
+        case RAYCA_E_CUDA: return "CUDA error";
+        case RAYCA_E_NO_CAMERA: return "scene has no camera";
+        default: return "unknown error";
+    }
+}
+
+int rayca_cuda_init(int device, rayca_ctx** out) {
+    if (!out) return fail(RAYCA_E_INVALID_ARG, "null out");
+    int n = 0;
+    CUDA_TRY(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail(RAYCA_E_INVALID_ARG, "no such CUDA device");
+    CUDA_TRY(cudaSetDevice(device));
+    rayca_ctx* c = new (std::nothrow) rayca_ctx();
+    if (!c) return fail(RAYCA_E_OOM, "host allocation");
+    c->device = device;
+    CUDA_TRY(cudaMalloc((void**)&c->d_counters, 4 * sizeof(unsigned long long)));
+    CUDA_TRY(cudaMemset(c->d_counters, 0, 4 * sizeof(unsigned long long)));
+    CUDA_TRY(cudaEventCreate(&c->ev0));
+    CUDA_TRY(cudaEventCreate(&c->ev1));
+    *out = c;
+    return RAYCA_OK;
+}
+
+void rayca_cuda_shutdown(rayca_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaFree(c->d_counters);
+    cudaFree(c->d_scratch);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    delete c;
+}
+
+void rayca_cuda_scene_destroy(rayca_scene* s) {
+    if (!s) return;
+    if (s->ctx) cudaSetDevice(s->ctx->device);
+    cudaFree(s->d_nodes);
+    cudaFree(s->d_tri_pos);
+    cudaFree(s->d_tri_attr);
+    cudaFree(s->d_materials);
+    cudaFree(s->d_images);
+    cudaFree(s->d_texels);
+    cudaFree(s->d_lights);
+    cudaFree(s->d_blas_prim_offset);
+    delete s;
+}
+
+int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32_t bvh, rayca_scene** out, rayca_stats* stats) {
+    if (!ctx || !desc || !out) return fail(RAYCA_E_INVALID_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    rayca_scene* s = new (std::nothrow) rayca_scene();
+    if (!s) return fail(RAYCA_E_OOM, "host allocation");
+    s->ctx = ctx;
+    double t0 = now_ms();
+    std::string err;
+    int rc;
+    try {
+        rc = build_host_scene(*desc, bvh != 0, s->host, err);
+    } catch (const std::bad_alloc&) {
+        delete s;
+        return fail(RAYCA_E_OOM, "host allocation while building the scene");
+    }
+    if (rc != RAYCA_OK) {
+        delete s;
+        return fail(rc, err);
+    }
+    if (s->host.max_stack > (uint32_t)kStackSize) {
+        delete s;
+        return fail(RAYCA_E_UNSUPPORTED, "BVH deeper than the traversal stack");
+    }
+    double t1 = now_ms();
+    HostScene& h = s->host;
+#define UP(dst, vec)                         \
+    do {                                     \
+        int rc__ = upload(&s->dst, h.vec);   \
+        if (rc__ != RAYCA_OK) {              \
+            rayca_cuda_scene_destroy(s);     \
+            return rc__;                     \
+        }                                    \
+    } while (0)
+    UP(d_nodes, nodes);
+    UP(d_tri_pos, tri_pos);
+    UP(d_tri_attr, tri_attr);
+    UP(d_materials, materials);
+    UP(d_images, images);
+    UP(d_texels, texels);
+    UP(d_lights, lights);
+    UP(d_blas_prim_offset, blas_prim_offset);
+#undef UP
+    GpuSceneView& v = s->view;
+    v.nodes = (const float4*)s->d_nodes;
+    v.tri_pos = (const float4*)s->d_tri_pos;
+    v.tri_attr = (const float4*)s->d_tri_attr;
+    v.materials = (const GpuMaterial*)s->d_materials;
+    v.images = (const GpuImage*)s->d_images;
+    v.texels = (const unsigned char*)s->d_texels;
+    v.lights = (const GpuLight*)s->d_lights;
+    v.blas_prim_offset = (const uint32_t*)s->d_blas_prim_offset;
+    v.blas_count = (uint32_t)h.blas.size();
+    v.light_count = (uint32_t)h.lights.size();
+    v.node_count = (uint32_t)h.nodes.size();
+    v.tri_count = (uint32_t)(h.tri_pos.size() / 3);
+    v.root_min[0] = h.root.min_x; v.root_min[1] = h.root.min_y; v.root_min[2] = h.root.min_z;
+    v.root_max[0] = h.root.max_x; v.root_max[1] = h.root.max_y; v.root_max[2] = h.root.max_z;
+    v.root_link0 = h.root.link0;
+    v.root_link1 = h.root.link1;
+    v.camera = h.camera;
+    s->max_stack = h.max_stack;
+    // host copies that are no longer needed
+    std::vector<unsigned char>().swap(h.texels);
+    std::vector<float4>().swap(h.tri_attr);
+    std::vector<float4>().swap(h.tri_pos);
+    for (HostBlas& b : h.blas) std::vector<HostAttr>().swap(b.attrs);
+    double t2 = now_ms();
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        stats->build_ms = t1 - t0;
+        stats->upload_ms = t2 - t1;
+    }
+    *out = s;
+    return RAYCA_OK;
+}
+
+int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options,
+                             uint32_t width, uint32_t height, void* d_rgba8, const rayca_aux_out* d_aux, void* cuda_stream,
+                             rayca_stats* stats) {
+    if (!ctx || !scene || !config || !d_rgba8 || width == 0 || height == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
+    if (scene->ctx != ctx) return fail(RAYCA_E_INVALID_ARG, "scene belongs to another context (or is host-only)");
+    if (!scene->host.has_camera) return fail(RAYCA_E_NO_CAMERA, "no camera node in the scene");
+    if ((uint64_t)width * height >= 0xFFFFFFFFull) return fail(RAYCA_E_UNSUPPORTED, "image too large");
+    int rc = validate_config(*config, *scene);
+    if (rc != RAYCA_OK) return rc;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+
+    RenderParams P{};
+    P.scene = scene->view;
+    P.cfg = *config;
+    P.seed = options ? options->rng_seed : 0;
+    P.width = width;
+    P.height = height;
+    P.shard_count = (options && options->shard_count > 1) ? options->shard_count : 1;
+    P.shard_index = options ? options->shard_index : 0;
+    P.tile_rows = (options && options->tile_rows) ? options->tile_rows : 8;
+    if (P.tile_rows % 8 != 0) return fail(RAYCA_E_INVALID_ARG, "tile_rows must be a multiple of 8");
+    if (P.shard_index >= P.shard_count) return fail(RAYCA_E_INVALID_ARG, "shard_index >= shard_count");
+    uint32_t rows = height;
+    if (P.shard_count > 1) {
+        uint32_t tiles = (height + P.tile_rows - 1) / P.tile_rows;
+        uint32_t per = (tiles + P.shard_count - 1) / P.shard_count; // every shard writes `per` tiles (tail tiles may be empty)
+        rows = per * P.tile_rows;
+    }
+    P.local_rows = rows;
+    float fw = (float)width, fh = (float)height;
+    P.inv_w = 1.0f / fw;
+    P.inv_h = 1.0f / fh;
+    P.aspect = fw / fh;
+    P.strate_count = sqrtf((float)config->samples_per_pixel); // scene.rs:125-127
+    P.offset = 0.5f / P.strate_count;
+    P.step = 1.0f / P.strate_count;
+    P.strate_u = (uint32_t)P.strate_count;
+    P.inv_gamma = 1.0f / config->gamma;
+    P.rgba8 = (unsigned char*)d_rgba8;
+    if (d_aux) {
+        P.hit_blas = d_aux->hit_blas;
+        P.hit_prim = d_aux->hit_prim;
+        P.hit_src = d_aux->hit_src;
+        P.depth = d_aux->depth;
+        P.uv = d_aux->uv;
+        P.rgba_f32 = d_aux->rgba_f32;
+    }
+    P.counters = ctx->d_counters;
+    const bool cull = !(options && options->traversal == RAYCA_TRAVERSAL_EXHAUSTIVE);
+    const bool count = options && (options->flags & RAYCA_FLAG_COUNT_WALK); // opt-in: walk counters cost registers
+
+    CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), st));
+    dim3 grid((width + 15) / 16, (rows + 7) / 8);
+    CUDA_TRY(cudaEventRecord(ctx->ev0, st));
+    switch (config->integrator) {
+        case RAYCA_INTEGRATOR_PATHTRACER: launch_integrator<RAYCA_INTEGRATOR_PATHTRACER>(P, grid, cull, count, st); break;
+        case RAYCA_INTEGRATOR_RAYTRACER: launch_integrator<RAYCA_INTEGRATOR_RAYTRACER>(P, grid, cull, count, st); break;
+        default: launch_integrator<RAYCA_INTEGRATOR_FLAT>(P, grid, cull, count, st); break;
+    }
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaEventRecord(ctx->ev1, st));
+    // primary rays of this shard: pixels it owns x spp
+    uint64_t own_rows = 0;
+    if (P.shard_count > 1) {
+        uint32_t tiles = (height + P.tile_rows - 1) / P.tile_rows;
+        for (uint32_t t = P.shard_index; t < tiles; t += P.shard_count) {
+            uint32_t y0 = t * P.tile_rows, y1 = std::min(height, y0 + P.tile_rows);
+            own_rows += y1 - y0;
+        }
+    } else {
+        own_rows = height;
+    }
+    ctx->last_primary = own_rows * width * (uint64_t)config->samples_per_pixel;
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        stats->kernel_launches = 1;
+        stats->rays_primary = ctx->last_primary;
+    }
+    return RAYCA_OK;
+}
+
+int rayca_cuda_last_counters(rayca_ctx* ctx, rayca_stats* stats) {
+    if (!ctx || !stats) return fail(RAYCA_E_INVALID_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    unsigned long long c[4];
+    CUDA_TRY(cudaEventSynchronize(ctx->ev1));
+    CUDA_TRY(cudaMemcpy(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
+    float ms = 0.0f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    stats->trace_ms = ms;
+    stats->rays_primary = ctx->last_primary;
+    stats->rays_shadow = c[0];
+    stats->rays_secondary = c[1];
+    stats->node_bytes = c[2] * 32ull;
+    stats->triangle_bytes = c[3] * 48ull;
+    stats->kernel_launches = 1;
+    return RAYCA_OK;
+}
+
+int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options, uint32_t width,
+                      uint32_t height, uint8_t* rgba8_out, const rayca_aux_out* aux, rayca_stats* stats) {
+    if (!ctx || !rgba8_out || width == 0 || height == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
+    if (options && options->shard_count > 1) return fail(RAYCA_E_INVALID_ARG, "sharded output is only available through render_device");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    const size_t n = (size_t)width * height;
+    // scratch layout: rgba8 | hit_blas | hit_prim | hit_src | depth | uv | rgba_f32
+    size_t need = n * 4 + (aux ? n * (4 + 4 + 4 + 4 + 8 + 16) : 0);
+    if (need > ctx->scratch_bytes) {
+        cudaFree(ctx->d_scratch);
+        ctx->d_scratch = nullptr;
+        ctx->scratch_bytes = 0;
+        CUDA_TRY(cudaMalloc(&ctx->d_scratch, need));
+        ctx->scratch_bytes = need;
+    }
+    unsigned char* base = (unsigned char*)ctx->d_scratch;
+    rayca_aux_out d{};
+    if (aux) {
+        unsigned char* p = base + n * 4;
+        if (aux->hit_blas) d.hit_blas = (uint32_t*)p;
+        p += n * 4;
+        if (aux->hit_prim) d.hit_prim = (uint32_t*)p;
+        p += n * 4;
+        if (aux->hit_src) d.hit_src = (uint32_t*)p;
+        p += n * 4;
+        if (aux->depth) d.depth = (float*)p;
+        p += n * 4;
+        if (aux->uv) d.uv = (float*)p;
+        p += n * 8;
+        if (aux->rgba_f32) d.rgba_f32 = (float*)p;
+    }
+    rayca_stats local{};
+    int rc = rayca_cuda_render_device(ctx, scene, config, options, width, height, base, aux ? &d : nullptr, nullptr, &local);
+    if (rc != RAYCA_OK) return rc;
+    double t0 = now_ms();
+    CUDA_TRY(cudaMemcpy(rgba8_out, base, n * 4, cudaMemcpyDeviceToHost));
+    if (aux) {
+        if (aux->hit_blas) CUDA_TRY(cudaMemcpy(aux->hit_blas, d.hit_blas, n * 4, cudaMemcpyDeviceToHost));
+        if (aux->hit_prim) CUDA_TRY(cudaMemcpy(aux->hit_prim, d.hit_prim, n * 4, cudaMemcpyDeviceToHost));
+        if (aux->hit_src) CUDA_TRY(cudaMemcpy(aux->hit_src, d.hit_src, n * 4, cudaMemcpyDeviceToHost));
+        if (aux->depth) CUDA_TRY(cudaMemcpy(aux->depth, d.depth, n * 4, cudaMemcpyDeviceToHost));
+        if (aux->uv) CUDA_TRY(cudaMemcpy(aux->uv, d.uv, n * 8, cudaMemcpyDeviceToHost));
+        if (aux->rgba_f32) CUDA_TRY(cudaMemcpy(aux->rgba_f32, d.rgba_f32, n * 16, cudaMemcpyDeviceToHost));
+    }
+    double t1 = now_ms();
+    if (stats) {
+        rc = rayca_cuda_last_counters(ctx, &local);
+        if (rc != RAYCA_OK) return rc;
+        local.readback_ms = t1 - t0;
+        *stats = local;
+    }
+    return RAYCA_OK;
+}
+
+int rayca_cuda_draw(const rayca_scene_desc* desc, const rayca_config* config, uint32_t width, uint32_t height, uint8_t* rgba8_out) {
+    if (!desc || !config) return fail(RAYCA_E_INVALID_ARG, "null argument");
+    rayca_ctx* ctx = nullptr;
+    int device = 0;
+    if (cudaGetDevice(&device) != cudaSuccess) device = 0;
+    int rc = rayca_cuda_init(device, &ctx);
+    if (rc != RAYCA_OK) return rc;
+    rayca_scene* scene = nullptr;
+    rc = rayca_cuda_scene_create(ctx, desc, config->bvh, &scene, nullptr);
+    if (rc == RAYCA_OK) {
+        rc = rayca_cuda_render(ctx, scene, config, nullptr, width, height, rgba8_out, nullptr, nullptr);
+        rayca_cuda_scene_destroy(scene);
+    }
+    rayca_cuda_shutdown(ctx);
+    return rc;
+}
+
+int rayca_cuda_scene_create_host(const rayca_scene_desc* desc, uint32_t bvh, rayca_scene** out, rayca_stats* stats) {
+    if (!desc || !out) return fail(RAYCA_E_INVALID_ARG, "null argument");
+    rayca_scene* s = new (std::nothrow) rayca_scene();
+    if (!s) return fail(RAYCA_E_OOM, "host allocation");
+    double t0 = now_ms();
+    std::string err;
+    int rc;
+    try {
+        rc = build_host_scene(*desc, bvh != 0, s->host, err);
+    } catch (const std::bad_alloc&) {
+        delete s;
+        return fail(RAYCA_E_OOM, "host allocation while building the scene");
+    }
+    if (rc != RAYCA_OK) {
+        delete s;
+        return fail(rc, err);
+    }
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        stats->build_ms = now_ms() - t0;
+    }
+    *out = s;
+    return RAYCA_OK;
+}
+
+int rayca_cuda_scene_bvh_info(rayca_scene* s, rayca_bvh_info* info) {
+    if (!s || !info) return fail(RAYCA_E_INVALID_ARG, "null argument");
+    info->blas_count = (uint32_t)s->host.blas.size();
+    info->node_count = s->host.blas_node_offset.back();
+    info->triangle_count = s->host.blas_prim_offset.back();
+    info->tlas_node_count = (uint32_t)s->host.nodes.size() - info->node_count;
+    return RAYCA_OK;
+}
+
+int rayca_cuda_scene_bvh_read(rayca_scene* s, float* nodes, uint32_t* blas_node_offset, uint32_t* blas_prim_offset, uint32_t* prim_src) {
+    if (!s) return fail(RAYCA_E_INVALID_ARG, "null argument");
+    const HostScene& h = s->host;
+    size_t nb = h.blas.size();
+    if (blas_node_offset) std::memcpy(blas_node_offset, h.blas_node_offset.data(), (nb + 1) * 4);
+    if (blas_prim_offset) std::memcpy(blas_prim_offset, h.blas_prim_offset.data(), (nb + 1) * 4);
+    for (size_t bi = 0; bi < nb; ++bi) {
+        const HostBlas& b = h.blas[bi];
+        if (nodes) {
+            float* o = nodes + (size_t)h.blas_node_offset[bi] * 8;
+            for (const HostNode& n : b.nodes) { // BLAS-local numbering, like the reference's Vec<BvhNode>
+                o[0] = n.bmin.x; o[1] = n.bmin.y; o[2] = n.bmin.z;
+                std::memcpy(o + 3, &n.offset, 4);
+                o[4] = n.bmax.x; o[5] = n.bmax.y; o[6] = n.bmax.z;
+                std::memcpy(o + 7, &n.count, 4);
+                o += 8;
+            }
+        }
+        if (prim_src) {
+            uint32_t* o = prim_src + h.blas_prim_offset[bi];
+            for (const HostTri& t : b.tris) *o++ = t.src;
+        }
+    }
+    return RAYCA_OK;
+}
+
+} // extern "C"

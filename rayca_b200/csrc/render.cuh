@@ -1,0 +1,343 @@
+// render.cuh — the fused per-pixel kernel: primary-ray generation, integrator, accumulation,
+// gamma, RGBA8 quantisation.  One thread owns one pixel and loops over its samples in order, so
+// the floating-point accumulation order equals the reference's (rayca-soft/src/scene.rs:117-150).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "../../include/rayca_cuda.h"
+#include "gpu_types.h"
+#include "rmath.h"
+#include "shade.cuh"
+#include "trace.cuh"
+
+namespace rb {
+
+constexpr int kMaxDepth = 17; // Config::apply maps maxdepth -1 to 16 (config.rs:59-63); raytracer visits depth 0..=max
+
+struct RenderParams {
+    GpuSceneView scene;
+    rayca_config cfg;
+    unsigned long long seed;
+    uint32_t width, height;
+    uint32_t shard_index, shard_count, tile_rows, local_rows;
+    float inv_w, inv_h, aspect;
+    float strate_count, offset, step, inv_gamma;
+    uint32_t strate_u;
+    unsigned char* rgba8;
+    uint32_t* hit_blas;
+    uint32_t* hit_prim;
+    uint32_t* hit_src;
+    float* depth;
+    float* uv;
+    float* rgba_f32;
+    unsigned long long* counters; // [0] shadow rays [1] secondary rays [2] node records [3] triangle records
+};
+
+// Philox4x32-10 keyed by the seed, counter = (pixel, sample, depth, dimension).  The reference draws
+// from thread-local unseeded fastrand (sampler/cosine.rs:66-67), which is not reproducible; both
+// this kernel and the oracle use this keyed generator instead (documented deviation).
+__device__ __forceinline__ float rng_f32(unsigned long long seed, uint32_t pixel, uint32_t sample, uint32_t depth, uint32_t dim) {
+    uint32_t c0 = pixel, c1 = sample, c2 = depth, c3 = dim;
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return (float)(c0 >> 8) * (1.0f / 16777216.0f); // 24 random bits, like fastrand::f32
+}
+
+// Vec3::close against Y_AXIS with the derived lexicographic PartialOrd (vec3.rs:26,108-111)
+__device__ __forceinline__ bool close_to_y(V3 w) {
+    float d[3] = {fabsf(w.x - 0.0f), fabsf(w.y - 1.0f), fabsf(w.z - 0.0f)};
+    for (int i = 0; i < 3; ++i) {
+        if (d[i] < kEps) return true;
+        if (d[i] > kEps) return false;
+        if (!(d[i] == kEps)) return false;
+    }
+    return false; // 4th lane: 0 < 0 is false
+}
+
+// CosineSampler::get_random_dir (sampler/cosine.rs:65-88)
+__device__ __forceinline__ V3 cosine_dir(const RenderParams& P, const Surf& sf, uint32_t pixel, uint32_t sample, uint32_t depth, uint32_t ls) {
+    float e1 = rng_f32(P.seed, pixel, sample, depth, 2 * ls);
+    float e2 = rng_f32(P.seed, pixel, sample, depth, 2 * ls + 1);
+    float theta = acosf(sqrtf(e1));
+    float omega = 2.0f * kPi * e2;
+    V3 sv{cosf(omega) * sinf(theta), sinf(omega) * sinf(theta), cosf(theta)};
+    V3 w = sf.normal;
+    V3 a = close_to_y(w) ? V3{1.0f, 0.0f, 0.0f} : V3{0.0f, 1.0f, 0.0f};
+    V3 u = normalize(cross(a, w));
+    V3 v = cross(w, u);
+    return (sv.x * u + sv.y * v) + sv.z * w;
+}
+
+struct PixelCounters {
+    uint32_t shadow = 0, secondary = 0;
+    WalkCounters walk;
+};
+
+// NextEventEstimationSampler::get_direct_lighting, point lights (sampler/nee.rs:127-216)
+template <bool CULL, bool COUNT>
+__device__ __forceinline__ Col nee_direct(const RenderParams& P, const Surf& sf, PixelCounters& pc) {
+    const GpuSceneView& s = P.scene;
+    Col ret{0.0f, 0.0f, 0.0f, 1.0f};
+    for (uint32_t li = 0; li < s.light_count; ++li) {
+        const GpuLight& L = s.lights[li];
+        for (uint32_t k = 0; k < P.cfg.light_samples; ++k) {
+            V3 x1{L.pos[0], L.pos[1], L.pos[2]};
+            V3 d = x1 - sf.point;
+            float dist = length(d);
+            V3 omega = normalize(d);
+            RayD shadow = make_ray(sf.next_origin, omega);
+            HitD sh;
+            sh.t = dist;
+            pc.shadow++;
+            bool occluded = walk<CULL, true, COUNT>(s, shadow, sh, &pc.walk);
+            Col x{0.0f, 0.0f, 0.0f, 1.0f};
+            if (!occluded) {
+                Col le = point_intensity(L, sf.point);
+                Col brdf = surf_brdf(s, sf, omega);
+                float r2 = norm2(d);
+                float d_omega = 1.0f / r2;
+                float ndo = clampf(dot(sf.normal, omega), 0.0f, 1.0f);
+                x = cscale(cscale(cmul(le, brdf), ndo), d_omega);
+            }
+            ret = cadd(ret, x);
+        }
+    }
+    return ret;
+}
+
+// Pathtracer::trace_impl (integrator/pathtracer.rs:68-106) for light_samples == 1 chains, unrolled
+// into a forward pass (trace, shade, spawn) and a backward pass that folds the radiance with the
+// reference's operator order.
+template <bool CULL, bool COUNT>
+__device__ __forceinline__ bool pathtracer(const RenderParams& P, RayD ray, uint32_t pixel, uint32_t sample, Col& out, HitD& primary,
+                                           PixelCounters& pc) {
+    const GpuSceneView& s = P.scene;
+    const bool nee = P.cfg.direct_sampler == RAYCA_SAMPLER_NEE;
+    const uint32_t max_depth = P.cfg.max_depth;
+    const uint32_t limit = nee ? max_depth - 1 : max_depth;
+    Col direct[kMaxDepth];
+    Col brdf[kMaxDepth];
+    int levels = 0;       // number of shaded (non-terminal) levels stored
+    bool have_tail = false;
+    Col tail{0.0f, 0.0f, 0.0f, 1.0f}; // value of the deepest trace_impl that returned Some without recursing
+    bool collect_emissive = true;
+    for (uint32_t depth = 0; depth < max_depth && depth < (uint32_t)kMaxDepth; ++depth) {
+        HitD h;
+        bool hit = walk<CULL, false, COUNT>(s, ray, h, &pc.walk);
+        if (depth == 0) primary = h;
+        if (!hit) break;
+        Surf sf;
+        load_surf(s, ray, h, sf);
+        if (collect_emissive && sf.mat->kind == RAYCA_MATERIAL_PHONG && sf.mat->emissive) {
+            tail = surf_color(s, sf);
+            have_tail = true;
+            break;
+        }
+        Col d{0.0f, 0.0f, 0.0f, 1.0f};
+        if (nee) d = nee_direct<CULL, COUNT>(P, sf, pc);
+        if (!(depth < limit)) { // no indirect: Some(direct + BLACK)
+            tail = cadd(d, Col{0.0f, 0.0f, 0.0f, 1.0f});
+            have_tail = true;
+            break;
+        }
+        V3 wi = cosine_dir(P, sf, pixel, sample, depth, 0);
+        direct[levels] = d;
+        brdf[levels] = surf_brdf(s, sf, wi);
+        ++levels;
+        ray = make_ray(sf.next_origin, wi);
+        if (depth + 1 < max_depth) pc.secondary++;
+        collect_emissive = !nee;
+    }
+    if (levels == 0 && !have_tail) return false;
+    // fold: value_k = direct_k + (BLACK + (BLACK + PI*brdf_k*value_{k+1}*1.0) / 1.0)
+    bool have = have_tail;
+    Col val = tail;
+    for (int k = levels - 1; k >= 0; --k) {
+        Col li{0.0f, 0.0f, 0.0f, 1.0f};
+        if (have) li = cadd(li, cscale(cmul(cscale(brdf[k], kPi), val), 1.0f));
+        li = cdiv(li, (float)P.cfg.light_samples);
+        Col indirect = cadd(Col{0.0f, 0.0f, 0.0f, 1.0f}, li);
+        val = cadd(direct[k], indirect);
+        have = true;
+    }
+    out = val;
+    return true;
+}
+
+// Raytracer::trace (integrator/raytracer.rs:16-76): mirror chain unrolled the same way.
+template <bool CULL, bool COUNT>
+__device__ __forceinline__ bool raytracer(const RenderParams& P, RayD ray, Col& out, HitD& primary, PixelCounters& pc) {
+    const GpuSceneView& s = P.scene;
+    Col ambient[kMaxDepth], light[kMaxDepth], spec[kMaxDepth];
+    int levels = 0;
+    for (uint32_t depth = 0; depth <= P.cfg.max_depth && depth < (uint32_t)kMaxDepth; ++depth) {
+        HitD h;
+        bool hit = walk<CULL, false, COUNT>(s, ray, h, &pc.walk);
+        if (depth == 0) primary = h;
+        if (!hit) break;
+        Surf sf;
+        load_surf(s, ray, h, sf);
+        Col lc{0.0f, 0.0f, 0.0f, 1.0f};
+        for (uint32_t li = 0; li < s.light_count; ++li) {
+            const GpuLight& L = s.lights[li];
+            V3 lpos{L.pos[0], L.pos[1], L.pos[2]};
+            V3 ldir;
+            if (L.kind == RAYCA_LIGHT_POINT) ldir = -normalize(sf.point - lpos); // light/point.rs:50-54
+            else ldir = V3{L.dir[0], L.dir[1], L.dir[2]};
+            RayD shadow = make_ray(sf.next_origin, ldir);
+            HitD sh;
+            pc.shadow++;
+            bool lit = true;
+            if (walk<CULL, false, COUNT>(s, shadow, sh, &pc.walk)) {
+                float ldist = length(sf.point - lpos); // light/point.rs:32-35, directional.rs:34-37
+                if (!(sh.t > ldist)) {
+                    Surf ss;
+                    load_surf(s, shadow, sh, ss);
+                    lit = surf_color(s, ss).a < 1.0f - kF32Eps; // Color::is_transparent
+                }
+            }
+            if (lit) {
+                Col intensity = (L.kind == RAYCA_LIGHT_POINT)
+                                    ? point_intensity(L, sf.point)
+                                    : cscale(Col{L.color[0], L.color[1], L.color[2], L.color[3]}, L.intensity);
+                lc = cadd(lc, surf_radiance(s, sf, intensity, ldir));
+            }
+        }
+        ambient[levels] = surf_color(s, sf);
+        light[levels] = lc;
+        spec[levels] = surf_specular(s, sf);
+        ++levels;
+        V3 refl = normalize(reflect(ray.d, sf.normal)); // hit.rs:93-101
+        ray = make_ray(sf.next_origin, refl);
+        if (depth + 1 <= P.cfg.max_depth) pc.secondary++;
+    }
+    if (levels == 0) return false;
+    Col val{0.0f, 0.0f, 0.0f, 1.0f};
+    bool have = false;
+    for (int k = levels - 1; k >= 0; --k) {
+        Col lc = light[k];
+        if (have) lc = cadd(lc, cscale(cmul(val, spec[k]), 1.0f));
+        val = cadd(ambient[k], lc);
+        have = true;
+    }
+    out = val;
+    return true;
+}
+
+// `(c * 255.0).clamp(0.0, 255.0) as u8` (color/rgba8.rs:75-84): truncation, NaN -> 0
+__device__ __forceinline__ unsigned char quantize(float c) {
+    float v = clampf(c * 255.0f, 0.0f, 255.0f);
+    return (unsigned char)__float2uint_rz(v);
+}
+
+// Block = 128 threads = 4 warps; a warp covers an 8x4 pixel tile, the block 16x8 pixels.
+template <int INTEGRATOR, bool CULL, bool COUNT>
+__global__ void __launch_bounds__(128) render_kernel(const __grid_constant__ RenderParams P) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t x = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
+    const uint32_t local_row = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+    uint32_t y = local_row;
+    if (P.shard_count > 1) {
+        uint32_t tile = local_row / P.tile_rows;
+        y = (tile * P.shard_count + P.shard_index) * P.tile_rows + (local_row % P.tile_rows);
+    }
+    const bool active = x < P.width && y < P.height;
+    PixelCounters pc;
+    if (active) {
+        const GpuCamera& cam = P.scene.camera;
+        const TrsF ctrs{V3{cam.t[0], cam.t[1], cam.t[2]}, Q4{cam.q[0], cam.q[1], cam.q[2], cam.q[3]}, V3{cam.s[0], cam.s[1], cam.s[2]}};
+        Col color{0.0f, 0.0f, 0.0f, 1.0f};
+        HitD primary;
+        primary.prim = 0xFFFFFFFFu;
+        const uint32_t pixel = y * P.width + x;
+        for (uint32_t i = 0; i < P.cfg.samples_per_pixel; ++i) {
+            float ix = (float)(i % P.strate_u);
+            float iy = (float)(i / P.strate_u);
+            float xx = (2.0f * (((float)x + ix * P.step + P.offset) * P.inv_w) - 1.0f) * cam.angle * P.aspect;
+            float yy = (1.0f - 2.0f * (((float)y + iy * P.step + P.offset) * P.inv_h)) * cam.angle;
+            V3 dir = normalize(V3{xx, yy, -1.0f});
+            // &camera_trs.trs * Ray::new(origin, dir): scale, rotate, translate (trs.rs:275-284); no re-normalise
+            V3 wd = rotate(dir * ctrs.s, ctrs.q);
+            V3 wo = rotate(scale_point(V3{0.0f, 0.0f, 0.0f}, ctrs.s), ctrs.q) + ctrs.t;
+            RayD ray = make_ray(wo, wd);
+            Col c{0.0f, 0.0f, 0.0f, 1.0f};
+            bool ok;
+            HitD ph;
+            ph.prim = 0xFFFFFFFFu;
+            ph.t = __int_as_float(0x7f800000);
+            ph.u = ph.v = 0.0f;
+            if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER) {
+                ok = pathtracer<CULL, COUNT>(P, ray, pixel, i, c, ph, pc);
+            } else if (INTEGRATOR == RAYCA_INTEGRATOR_RAYTRACER) {
+                ok = raytracer<CULL, COUNT>(P, ray, c, ph, pc);
+            } else { // Flat (integrator/flat.rs:16-28)
+                ok = walk<CULL, false, COUNT>(P.scene, ray, ph, &pc.walk);
+                if (ok) {
+                    Surf sf;
+                    load_surf(P.scene, ray, ph, sf);
+                    c = surf_color(P.scene, sf);
+                }
+            }
+            if (!ok) {
+                c = Col{0.0f, 0.0f, 0.0f, 1.0f}; // unwrap_or(Color::BLACK) (scene.rs:80-86)
+                if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER && P.cfg.max_depth == 0) ph.prim = 0xFFFFFFFFu;
+            }
+            primary = ph;
+            color = cadd(color, c);
+        }
+        color = cdiv(color, (float)P.cfg.samples_per_pixel);
+        color.r = powf(color.r, P.inv_gamma); // correct_gamma (color/mod.rs:175-180)
+        color.g = powf(color.g, P.inv_gamma);
+        color.b = powf(color.b, P.inv_gamma);
+        const size_t o = (size_t)((P.shard_count > 1) ? local_row : y) * P.width + x;
+        uchar4 q = make_uchar4(quantize(color.r), quantize(color.g), quantize(color.b), quantize(color.a));
+        reinterpret_cast<uchar4*>(P.rgba8)[o] = q;
+        const bool hit = primary.prim != 0xFFFFFFFFu;
+        if (P.hit_prim || P.hit_blas || P.hit_src) {
+            uint32_t blas = 0xFFFFFFFFu, local = 0xFFFFFFFFu, src = 0xFFFFFFFFu;
+            if (hit) {
+                blas = 0;
+                while (blas + 1 < P.scene.blas_count && primary.prim >= P.scene.blas_prim_offset[blas + 1]) ++blas;
+                local = primary.prim - P.scene.blas_prim_offset[blas];
+                src = __float_as_uint(P.scene.tri_pos[3 * (size_t)primary.prim].w);
+            }
+            if (P.hit_blas) P.hit_blas[o] = blas;
+            if (P.hit_prim) P.hit_prim[o] = local;
+            if (P.hit_src) P.hit_src[o] = src;
+        }
+        if (P.depth) P.depth[o] = hit ? primary.t : __int_as_float(0x7f800000);
+        if (P.uv) {
+            P.uv[2 * o] = hit ? primary.u : 0.0f;
+            P.uv[2 * o + 1] = hit ? primary.v : 0.0f;
+        }
+        if (P.rgba_f32) reinterpret_cast<float4*>(P.rgba_f32)[o] = make_float4(color.r, color.g, color.b, color.a);
+    }
+    // warp-aggregated counters: one atomic per warp per counter
+    uint32_t sh = __reduce_add_sync(0xFFFFFFFFu, pc.shadow);
+    uint32_t se = __reduce_add_sync(0xFFFFFFFFu, pc.secondary);
+    if (lane == 0) {
+        if (sh) atomicAdd(&P.counters[0], (unsigned long long)sh);
+        if (se) atomicAdd(&P.counters[1], (unsigned long long)se);
+    }
+    if (COUNT) {
+        unsigned long long n = pc.walk.nodes, t = pc.walk.tris;
+        for (int ofs = 16; ofs > 0; ofs >>= 1) {
+            n += __shfl_down_sync(0xFFFFFFFFu, n, ofs);
+            t += __shfl_down_sync(0xFFFFFFFFu, t, ofs);
+        }
+        if (lane == 0) {
+            atomicAdd(&P.counters[2], n);
+            atomicAdd(&P.counters[3], t);
+        }
+    }
+}
+
+} // namespace rb

@@ -133,7 +133,8 @@ class rayca_config(C.Structure):
 
 class rayca_options(C.Structure):
     _fields_ = [("rng_seed", C.c_uint64), ("traversal", C.c_uint32), ("shard_index", C.c_uint32),
-                ("shard_count", C.c_uint32), ("tile_rows", C.c_uint32)]
+                ("shard_count", C.c_uint32), ("tile_rows", C.c_uint32), ("flags", C.c_uint32),
+                ("reserved", C.c_uint32)]
 
 
 class rayca_aux_out(C.Structure):
@@ -406,15 +407,85 @@ def create_default_model() -> Model:
     return m
 
 
+_DESC_ARRAYS = [  # (pointer field, count field, element ctype or None for raw numpy)
+    ("scene_nodes", "scene_node_count", rayca_node), ("models", "model_count", rayca_model),
+    ("nodes", "node_count", rayca_node), ("children", "children_count", C.c_uint32),
+    ("meshes", "mesh_count", rayca_mesh), ("mesh_primitives", "mesh_primitive_count", C.c_uint32),
+    ("primitives", "primitive_count", rayca_primitive), ("geometries", "geometry_count", rayca_geometry),
+    ("materials", "material_count", rayca_material), ("pbr_materials", "pbr_count", rayca_pbr_material),
+    ("phong_materials", "phong_count", rayca_phong_material), ("ggx_materials", "ggx_count", rayca_ggx_material),
+    ("textures", "texture_count", rayca_texture), ("lights", "light_count", rayca_light),
+    ("cameras", "camera_count", rayca_camera),
+]
+_DESC_FORMAT = 1
+
+
 class SceneDesc:
     """Owns the ctypes arrays a `rayca_scene_desc` points into."""
 
     def __init__(self):
         self.desc = rayca_scene_desc()
         self._keep = []
+        self.triangle_count = 0
 
     def ptr(self):
         return C.byref(self.desc)
+
+    # ---- compact on-disk form used for the committed test fixtures (tests/golden/*.npz)
+    def save(self, path) -> None:
+        d = self.desc
+        out = {"format": np.array([_DESC_FORMAT], dtype=np.uint32),
+               "root": np.frombuffer(bytes(d.root_trs), dtype=np.uint8),
+               "root_children": np.array([d.root_first_child, d.root_child_count], dtype=np.uint32)}
+        for ptr, cnt, ctype in _DESC_ARRAYS:
+            n = getattr(d, cnt)
+            raw = C.string_at(getattr(d, ptr), n * C.sizeof(ctype)) if n else b""
+            out[ptr] = np.frombuffer(raw, dtype=np.uint8)
+        out["vertices"] = np.frombuffer(C.string_at(d.vertices, d.vertex_count * VERTEX_FLOATS * 4), dtype=f32) \
+            if d.vertex_count else np.zeros(0, dtype=f32)
+        out["indices"] = np.frombuffer(C.string_at(d.indices, d.index_count * 4), dtype=np.uint32) \
+            if d.index_count else np.zeros(0, dtype=np.uint32)
+        meta = []
+        for i in range(d.image_count):
+            im = d.images[i]
+            bpp = {COLOR_RGB8: 3, COLOR_RGBA8: 4, COLOR_RGBA32F: 16}[im.color_type]
+            out[f"image_{i}"] = np.frombuffer(C.string_at(im.data, im.width * im.height * bpp), dtype=np.uint8)
+            meta.append((im.width, im.height, im.color_type))
+        out["image_meta"] = np.array(meta, dtype=np.uint32).reshape(-1, 3)
+        np.savez_compressed(path, **out)
+
+    @staticmethod
+    def load(path) -> "SceneDesc":
+        z = np.load(path)
+        assert int(z["format"][0]) == _DESC_FORMAT, "fixture written by another descriptor layout"
+        sd = SceneDesc()
+        d = sd.desc
+        C.memmove(C.byref(d.root_trs), z["root"].tobytes(), C.sizeof(rayca_trs))
+        d.root_first_child, d.root_child_count = [int(x) for x in z["root_children"]]
+        for ptr, cnt, ctype in _DESC_ARRAYS:
+            raw = z[ptr].tobytes()
+            n = len(raw) // C.sizeof(ctype)
+            a = (ctype * max(n, 1))()
+            if n:
+                C.memmove(a, raw, len(raw))
+            sd._keep.append(a)
+            setattr(d, ptr, a)
+            setattr(d, cnt, n)
+        verts = np.ascontiguousarray(z["vertices"], dtype=f32)
+        idx = np.ascontiguousarray(z["indices"], dtype=np.uint32)
+        sd._keep += [verts, idx]
+        d.vertices, d.vertex_count = verts.ctypes.data, len(verts) // VERTEX_FLOATS
+        d.indices, d.index_count = idx.ctypes.data, len(idx)
+        meta = z["image_meta"]
+        imgs = (rayca_image * max(len(meta), 1))()
+        for i, (w, h, ct) in enumerate(meta):
+            data = np.ascontiguousarray(z[f"image_{i}"])
+            sd._keep.append(data)
+            imgs[i] = rayca_image(int(w), int(h), int(ct), 0, data.ctypes.data)
+        sd._keep.append(imgs)
+        d.images, d.image_count = imgs, len(meta)
+        sd.triangle_count = len(idx) // 3
+        return sd
 
 
 @dataclass

@@ -1,0 +1,274 @@
+"""Host-side mirror of rayca-soft's renderer interface over the C ABI of librayca_cuda.
+
+Reference interface mirrored here (same names, argument meaning and failure behaviour):
+    trait Draw { fn draw(&mut self, scene: &Scene, image: &mut Image) }   rayca-soft/src/draw.rs:7-9
+    SoftRenderer::default() / new_with_config(Config)                      rayca-soft/src/scene.rs:11-14,57-61
+    Config (bon builder defaults)                                          rayca-soft/src/config.rs:10-49
+    IntegratorStrategy / SamplerStrategy                                   integrator/mod.rs:32-41, sampler/mod.rs:41-50
+
+There is no CPU fallback: constructing a renderer without the built CUDA library, or without a
+CUDA device, raises.  Nothing in this module imports or calls the oracle.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import enum
+import os
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+
+from . import model as M
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librayca_cuda.so")
+
+
+class IntegratorStrategy(enum.IntEnum):
+    Scratcher = 0
+    Raytracer = 1
+    Flat = 2
+    AnalyticDirect = 3
+    Direct = 4
+    Pathtracer = 5
+
+
+class SamplerStrategy(enum.IntEnum):
+    NONE = 0
+    Nee = 1
+    Hemisphere = 2
+    Cosine = 3
+    Brdf = 4
+    Mis = 5
+
+
+TRAVERSAL_ORDERED, TRAVERSAL_EXHAUSTIVE = 0, 1
+FLAG_COUNT_WALK = 1
+
+_ERRORS = {-1: "RAYCA_E_INVALID_ARG", -2: "RAYCA_E_UNSUPPORTED", -3: "RAYCA_E_OOM", -4: "RAYCA_E_CUDA",
+           -5: "RAYCA_E_NO_CAMERA"}
+
+
+class RaycaError(RuntimeError):
+    def __init__(self, code: int, detail: str):
+        super().__init__(f"{_ERRORS.get(code, code)}: {detail}")
+        self.code = code
+
+
+@dataclass
+class Config:
+    """rayca-soft/src/config.rs:10-49 with the builder defaults."""
+    bvh: bool = True
+    light_samples: int = 1
+    light_stratify: bool = False
+    samples_per_pixel: int = 1
+    russian_roulette: bool = False
+    direct_sampler: SamplerStrategy = SamplerStrategy.Nee
+    indirect_sampler: SamplerStrategy = SamplerStrategy.Cosine
+    integrator: IntegratorStrategy = IntegratorStrategy.Pathtracer
+    max_depth: int = 5
+    gamma: float = 1.0
+
+    def apply(self, sdtf: M.SdtfConfig) -> None:
+        """Config::apply (config.rs:58-71)."""
+        self.max_depth = 16 if sdtf.max_depth == -1 else sdtf.max_depth
+        self.light_samples = sdtf.light_samples
+        self.light_stratify = sdtf.light_stratify
+        self.samples_per_pixel = sdtf.samples_per_pixel
+        self.direct_sampler = {"none": SamplerStrategy.NONE, "nee": SamplerStrategy.Nee, "mis": SamplerStrategy.Mis,
+                               "hemisphere": SamplerStrategy.Hemisphere, "cosine": SamplerStrategy.Cosine,
+                               "brdf": SamplerStrategy.Brdf}[sdtf.direct_sampler]
+        self.indirect_sampler = {"hemisphere": SamplerStrategy.Hemisphere, "cosine": SamplerStrategy.Cosine,
+                                 "brdf": SamplerStrategy.Brdf}[sdtf.indirect_sampler]
+        self.integrator = {"raytracer": IntegratorStrategy.Raytracer,
+                           "analyticdirect": IntegratorStrategy.AnalyticDirect, "direct": IntegratorStrategy.Direct,
+                           "pathtracer": IntegratorStrategy.Pathtracer}[sdtf.integrator]
+        self.gamma = sdtf.gamma
+
+    def to_c(self) -> M.rayca_config:
+        return M.rayca_config(int(self.bvh), self.light_samples, int(self.light_stratify), self.samples_per_pixel,
+                              int(self.russian_roulette), int(self.direct_sampler), int(self.indirect_sampler),
+                              int(self.integrator), self.max_depth, self.gamma)
+
+
+@dataclass
+class Image:
+    """rayca-model/src/image.rs:26-61 restricted to ColorType::RGBA8: row-major, top-left origin."""
+    width: int
+    height: int
+    buffer: Optional[np.ndarray] = None
+
+    def __post_init__(self):
+        if self.buffer is None:
+            self.buffer = np.zeros((self.height, self.width, 4), dtype=np.uint8)
+
+    def dump_png(self, path) -> None:
+        from PIL import Image as PILImage
+
+        PILImage.fromarray(self.buffer, "RGBA").save(path)
+
+
+_lib = None
+
+
+def load_library():
+    """Loads rayca_b200/librayca_cuda.so (built in-tree by rayca_b200/build.py).  Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python -m rayca_b200.build` (there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    vp, u32 = C.c_void_p, C.c_uint32
+    lib.rayca_cuda_init.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.rayca_cuda_shutdown.argtypes = [vp]
+    lib.rayca_cuda_shutdown.restype = None
+    lib.rayca_cuda_scene_create.argtypes = [vp, vp, u32, C.POINTER(vp), C.POINTER(M.rayca_stats)]
+    lib.rayca_cuda_scene_create_host.argtypes = [vp, u32, C.POINTER(vp), C.POINTER(M.rayca_stats)]
+    lib.rayca_cuda_scene_destroy.argtypes = [vp]
+    lib.rayca_cuda_scene_destroy.restype = None
+    lib.rayca_cuda_render.argtypes = [vp, vp, C.POINTER(M.rayca_config), C.POINTER(M.rayca_options), u32, u32, vp,
+                                      C.POINTER(M.rayca_aux_out), C.POINTER(M.rayca_stats)]
+    lib.rayca_cuda_render_device.argtypes = [vp, vp, C.POINTER(M.rayca_config), C.POINTER(M.rayca_options), u32, u32,
+                                             vp, C.POINTER(M.rayca_aux_out), vp, C.POINTER(M.rayca_stats)]
+    lib.rayca_cuda_last_counters.argtypes = [vp, C.POINTER(M.rayca_stats)]
+    lib.rayca_cuda_draw.argtypes = [vp, C.POINTER(M.rayca_config), u32, u32, vp]
+    lib.rayca_cuda_scene_bvh_info.argtypes = [vp, C.POINTER(M.rayca_bvh_info)]
+    lib.rayca_cuda_scene_bvh_read.argtypes = [vp, vp, vp, vp, vp]
+    lib.rayca_cuda_strerror.restype = C.c_char_p
+    lib.rayca_cuda_strerror.argtypes = [C.c_int]
+    lib.rayca_cuda_last_error.restype = C.c_char_p
+    lib.rayca_cuda_abi_version.restype = u32
+    _lib = lib
+    return lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise RaycaError(rc, load_library().rayca_cuda_last_error().decode())
+
+
+class AuxPlanes:
+    """Host planes for rayca_aux_out (parity checks)."""
+
+    def __init__(self, width: int, height: int):
+        n = width * height
+        self.hit_blas = np.full(n, 0xFFFFFFFF, dtype=np.uint32)
+        self.hit_prim = np.full(n, 0xFFFFFFFF, dtype=np.uint32)
+        self.hit_src = np.full(n, 0xFFFFFFFF, dtype=np.uint32)
+        self.depth = np.full(n, np.inf, dtype=np.float32)
+        self.uv = np.zeros(n * 2, dtype=np.float32)
+        self.rgba_f32 = np.zeros(n * 4, dtype=np.float32)
+        self.c = M.rayca_aux_out(self.hit_blas.ctypes.data, self.hit_prim.ctypes.data, self.hit_src.ctypes.data,
+                                 self.depth.ctypes.data, self.uv.ctypes.data, self.rgba_f32.ctypes.data)
+
+
+class Context:
+    """rayca_ctx: one per process and GPU."""
+
+    def __init__(self, device: int = 0):
+        self._h = C.c_void_p()
+        _check(load_library().rayca_cuda_init(device, C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if self._h:
+            load_library().rayca_cuda_shutdown(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DeviceScene:
+    """rayca_scene: the flattened scene + BVH resident in HBM (or host-only when ctx is None)."""
+
+    def __init__(self, ctx: Optional[Context], desc: M.SceneDesc, bvh: bool = True):
+        self.ctx = ctx
+        self._h = C.c_void_p()
+        self.stats = M.rayca_stats()
+        lib = load_library()
+        d = C.cast(desc.ptr(), C.c_void_p)
+        if ctx is None:
+            _check(lib.rayca_cuda_scene_create_host(d, int(bvh), C.byref(self._h), C.byref(self.stats)))
+        else:
+            _check(lib.rayca_cuda_scene_create(ctx._h, d, int(bvh), C.byref(self._h), C.byref(self.stats)))
+
+    def close(self):
+        if self._h:
+            load_library().rayca_cuda_scene_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def bvh(self):
+        lib = load_library()
+        info = M.rayca_bvh_info()
+        _check(lib.rayca_cuda_scene_bvh_info(self._h, C.byref(info)))
+        nodes = np.zeros((info.node_count, 8), dtype=np.float32)
+        no = np.zeros(info.blas_count + 1, dtype=np.uint32)
+        po = np.zeros(info.blas_count + 1, dtype=np.uint32)
+        src = np.zeros(info.triangle_count, dtype=np.uint32)
+        _check(lib.rayca_cuda_scene_bvh_read(self._h, nodes.ctypes.data, no.ctypes.data, po.ctypes.data,
+                                             src.ctypes.data))
+        return info, nodes, no, po, src
+
+    def render(self, config: Config, width: int, height: int, options: Optional[M.rayca_options] = None,
+               want_aux: bool = False):
+        """rayca_cuda_render with HOST buffers; returns (rgba8 HxWx4, aux or None, stats)."""
+        rgba8 = np.zeros((height, width, 4), dtype=np.uint8)
+        aux = AuxPlanes(width, height) if want_aux else None
+        stats = M.rayca_stats()
+        cfg = config.to_c()
+        _check(load_library().rayca_cuda_render(self.ctx._h, self._h, C.byref(cfg),
+                                                C.byref(options) if options is not None else None, width, height,
+                                                rgba8.ctypes.data, C.byref(aux.c) if aux else None, C.byref(stats)))
+        return rgba8, aux, stats
+
+    def render_device(self, config: Config, width: int, height: int, d_rgba8: int, stream: int = 0,
+                      options: Optional[M.rayca_options] = None, d_aux: Optional[M.rayca_aux_out] = None):
+        """rayca_cuda_render_device: outputs are device pointers; enqueues on `stream` without syncing."""
+        cfg = config.to_c()
+        _check(load_library().rayca_cuda_render_device(self.ctx._h, self._h, C.byref(cfg),
+                                                       C.byref(options) if options is not None else None, width,
+                                                       height, d_rgba8, C.byref(d_aux) if d_aux is not None else None,
+                                                       stream, None))
+
+    def last_counters(self) -> M.rayca_stats:
+        stats = M.rayca_stats()
+        _check(load_library().rayca_cuda_last_counters(self.ctx._h, C.byref(stats)))
+        return stats
+
+
+class CudaRenderer:
+    """Drop-in for `SoftRenderer` (rayca-soft/src/scene.rs:11-14,57-61,88-154)."""
+
+    def __init__(self, config: Optional[Config] = None, device: int = 0):
+        self.config = config if config is not None else Config()
+        self._ctx = Context(device)
+
+    @staticmethod
+    def new_with_config(config: Config) -> "CudaRenderer":
+        return CudaRenderer(config)
+
+    @staticmethod
+    def create_default_model() -> M.Model:
+        return M.create_default_model()
+
+    def draw(self, scene: M.Scene, image: Image) -> None:
+        """`Draw::draw`: rebuilds the acceleration structure on every call, like the reference."""
+        desc = scene.to_desc()
+        dev = DeviceScene(self._ctx, desc, self.config.bvh)
+        try:
+            rgba8, _, _ = dev.render(self.config, image.width, image.height)
+        finally:
+            dev.close()
+        image.buffer[...] = rgba8

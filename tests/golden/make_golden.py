@@ -1,0 +1,163 @@
+"""Regenerates tests/golden/*.npz.  Run in the authoring container only:
+
+    python tests/golden/make_golden.py [name ...]
+
+It reads the reference's own test assets from /root/reference/tests/model (glTF / SDTF files of the
+`rayca-models` submodule), builds the same scenes the reference's integration tests build
+(rayca-soft/tests/gltf.rs, rayca-soft/tests/sdtf.rs), serialises each scene as the POD descriptor of
+include/rayca_cuda.h (`<scene>.scene.npz`) and stores what the CPU oracle renders for each test case
+(`<scene>.<case>.npz`: rgba8, rgba_f32, hit_src, hit_prim, hit_blas, depth, uv, ray counts).
+
+/root/reference does not exist on the GPU box; the tests only ever read the committed .npz files.
+The reference itself cannot be executed here (Rust nightly, no toolchain), so these vectors pin the
+ORACLE's behaviour over time — they are not outputs of the reference (image-level parity unpinned).
+"""
+from __future__ import annotations
+
+import os
+import sys
+import time
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "..", ".."))
+
+from oracle import binding as O  # noqa: E402
+from rayca_b200 import model as M  # noqa: E402
+from rayca_b200.renderer import Config, IntegratorStrategy, SamplerStrategy  # noqa: E402
+
+ASSETS = "/root/reference/tests/model"
+f32 = np.float32
+
+
+def gltf_scene(rel, tweak=None, camera=None):
+    s = M.Scene()
+    h = s.push_gltf_from_path(os.path.join(ASSETS, rel))
+    if tweak:
+        tweak(s, h)
+    dm = M.create_default_model()
+    if camera is not None:
+        dm.get_mut_last_camera().trs.translation = np.array(camera, dtype=f32)
+    s.push_model(dm)
+    return s
+
+
+def unit_triangle_scene():
+    """rayca-soft/tests/gltf.rs:47-83 `triangle`: TriangleMesh::unit with RGB vertex colours under a
+    node translated (0,-1,0) and scaled (1,2,1)."""
+    m = M.Model()
+    col = np.array([[1, 0, 0, 1], [0, 1, 0, 1], [0, 0, 1, 1]], dtype=f32)
+    verts = M.make_vertices([[-1, 0, 0], [1, 0, 0], [0, 1, 0]], color=col)
+    m.geometries.append(M.TriangleMesh(verts, np.array([0, 1, 2], dtype=np.uint32)))
+    m.primitives.append(M.Primitive(0))
+    m.meshes.append(M.Mesh([0]))
+    m.nodes.append(M.Node(mesh=0, trs=M.Trs(translation=np.array([0, -1, 0], dtype=f32),
+                                            scale=np.array([1, 2, 1], dtype=f32))))
+    m.root.children.append(0)
+    s = M.Scene()
+    s.push_model(m)
+    s.push_model(M.create_default_model())
+    return s
+
+
+def cubes_over_plane_scene():
+    """rayca-soft/tests/gltf.rs:85-183 `cube_over_plane` without its sphere (spheres are a later row):
+    four box.gltf instances => four BLAS under one TLAS."""
+    s = M.Scene()
+    box = os.path.join(ASSETS, "box/box.gltf")
+    h = s.push_gltf_from_path(box)  # blue floor
+    s.nodes[h].trs.scale = np.array([16.0, 0.125, 16.0], dtype=f32)
+    s.nodes[h].trs.translation = s.nodes[h].trs.translation + np.array([0, -1, 0], dtype=f32)
+    floor = s.models[s.nodes[h].model]
+    floor.nodes[1].trs.rotation = np.array([0, 0, 0, 1], dtype=f32)
+    floor.pbr_materials[0].color = (0.1, 0.2, 0.7, 1.0)
+    floor.pbr_materials[0].metallic_factor = 1.0
+    for shift in ([1.0, 1.0, -2.0], [0.0, 0.0, -1.0], [-1.5, 0.0, -4.0]):
+        h = s.push_gltf_from_path(box)
+        s.nodes[h].trs.translation = s.nodes[h].trs.translation + np.array(shift, dtype=f32)
+    s.push_model(M.create_default_model())
+    return s
+
+
+def scale_root(f):
+    def tweak(s, h):
+        s.nodes[h].trs.scale = (s.nodes[h].trs.scale * np.array(f, dtype=f32)).astype(f32)
+    return tweak
+
+
+def sdtf_scene(rel):
+    s = M.Scene()
+    _, cfg = s.push_sdtf_from_path(os.path.join(ASSETS, rel))
+    return s, cfg
+
+
+PT1 = dict(integrator=IntegratorStrategy.Pathtracer, max_depth=1)          # deterministic NEE slice
+PT2 = dict(integrator=IntegratorStrategy.Pathtracer, max_depth=2)          # + one cosine bounce (keyed RNG)
+RT0 = dict(integrator=IntegratorStrategy.Raytracer, max_depth=0)
+RT3 = dict(integrator=IntegratorStrategy.Raytracer, max_depth=3)
+FLAT = dict(integrator=IntegratorStrategy.Flat)
+
+# scene name -> (builder, {case name -> (config kwargs, width, height)})
+SCENES = {
+    "triangle": (lambda: gltf_scene("triangle/triangle.gltf"),
+                 {"pt1": (PT1, 128, 128), "rt0": (RT0, 128, 128), "flat": (FLAT, 64, 64),
+                  "pt1_spp4": (dict(PT1, samples_per_pixel=4), 64, 64)}),
+    "unit_triangle": (unit_triangle_scene, {"pt1": (PT1, 128, 128), "pt5": (dict(integrator=IntegratorStrategy.Pathtracer), 64, 64)}),
+    "box": (lambda: gltf_scene("box/box.gltf"),
+            {"pt1": (PT1, 128, 128), "rt0": (RT0, 128, 128), "rt3": (RT3, 96, 96), "pt2": (PT2, 96, 96),
+             "pt1_nobvh": (dict(PT1, bvh=False), 64, 64), "pt1_spp2": (dict(PT1, samples_per_pixel=2), 64, 64),
+             "pt1_gamma": (dict(PT1, gamma=2.2), 64, 64), "wide": (PT1, 160, 48)}),
+    "orientation": (lambda: gltf_scene("orientation/OrientationTest.gltf", scale_root([0.2, 0.2, 0.2])),
+                    {"pt1": (PT1, 128, 128), "rt0": (RT0, 96, 96)}),
+    "cubes_over_plane": (cubes_over_plane_scene, {"pt1": (PT1, 128, 128), "rt3": (RT3, 96, 96), "pt3": (dict(integrator=IntegratorStrategy.Pathtracer, max_depth=3), 64, 64)}),
+    "suzanne": (lambda: gltf_scene("suzanne/suzanne.gltf"), {"pt1": (PT1, 128, 128), "rt0": (RT0, 96, 96), "pt2": (PT2, 64, 64)}),
+    "scene7": (None, {"sdtf": (None, 80, 60)}),
+}
+
+
+def render_case(osc, cfg: Config, w, h, seed=0x5EED):
+    opts = M.rayca_options(seed, 0, 0, 0, 0, 0, 0)
+    rgba8, aux, st = osc.render(cfg.to_c(), w, h, options=opts, flags=O.COUNT)
+    return dict(rgba8=rgba8, rgba_f32=aux.rgba_f32.reshape(h, w, 4), hit_src=aux.hit_src.reshape(h, w),
+                hit_prim=aux.hit_prim.reshape(h, w), hit_blas=aux.hit_blas.reshape(h, w),
+                depth=aux.depth.reshape(h, w), uv=aux.uv.reshape(h, w, 2),
+                rays=np.array([st.rays_primary, st.rays_shadow, st.rays_secondary], dtype=np.uint64),
+                walk=np.array([st.ord_nodes, st.ord_tris, st.exh_nodes, st.exh_tris], dtype=np.uint64),
+                config=np.array([int(cfg.bvh), cfg.light_samples, int(cfg.light_stratify), cfg.samples_per_pixel,
+                                 int(cfg.russian_roulette), int(cfg.direct_sampler), int(cfg.indirect_sampler),
+                                 int(cfg.integrator), cfg.max_depth], dtype=np.uint32),
+                gamma=np.array([cfg.gamma], dtype=f32), seed=np.array([seed], dtype=np.uint64))
+
+
+def main(names):
+    for name, (builder, cases) in SCENES.items():
+        if names and name not in names:
+            continue
+        t0 = time.time()
+        sdtf_cfg = None
+        if name == "scene7":
+            scene, sdtf_cfg = sdtf_scene("sdtf/1/scene7.sdtf")
+        else:
+            scene = builder()
+        desc = scene.to_desc()
+        desc.save(os.path.join(HERE, f"{name}.scene.npz"))
+        by_bvh = {}
+        for case, (kw, w, h) in cases.items():
+            cfg = Config()
+            if sdtf_cfg is not None:
+                cfg.apply(sdtf_cfg)
+            else:
+                for k, v in kw.items():
+                    setattr(cfg, k, v)
+            if cfg.bvh not in by_bvh:
+                by_bvh[cfg.bvh] = O.OracleScene(desc, bvh=cfg.bvh)
+            out = render_case(by_bvh[cfg.bvh], cfg, w, h)
+            np.savez_compressed(os.path.join(HERE, f"{name}.{case}.npz"), **out)
+            print(f"{name}.{case}: {w}x{h} hits={(out['hit_src'] != 0xFFFFFFFF).sum()} rays={out['rays'].tolist()} "
+                  f"mean rgb={out['rgba_f32'][..., :3].mean():.5f}")
+        print(f"{name}: {desc.triangle_count} triangles, {time.time() - t0:.1f}s")
+
+
+if __name__ == "__main__":
+    main(sys.argv[1:])
