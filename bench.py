@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s (primary + shadow) of the raytracing hot path on N B200s, beside the CPU path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload atrium|soup]
+
+One step = one frame: every pixel's primary ray, its shadow rays and shading, through the CUDA path.
+Workload (config.workload): BASELINE.json quotes its metric on 1080p Sponza; `sponza.bin` is absent
+from the reference checkout and nothing of the reference exists on the GPU box, so the default is the
+procedural Sponza-class atrium of rayca_b200/procedural.py (~262k triangles, one BLAS, textured PBR,
+the reference test's root rotation / camera / default lights), 1920x1080, 1 spp,
+Pathtracer max_depth=1 (= the deterministic primary + shadow slice of SoftRenderer::default()).
+
+Keys: `value` = device-timed whole-job throughput with the scene resident in HBM; `e2e` = the same
+metric through rayca_cuda_render with HOST output buffers (device->host copy of the frame inside the
+timed region; the per-step host->device input is the camera/config parameter block — the scene is
+uploaded once by scene_create, exactly as the reference's own timer excludes its BVH build,
+rayca-soft/src/scene.rs:101,152); `draw_e2e` = the full Draw::draw equivalent (flatten + BVH build +
+upload + render + read-back).  `cpu_baseline` = the oracle (a port of rayca-soft) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s (primary+shadow, 1080p Sponza-class scene)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="atrium", choices=["atrium", "soup"])
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--spp", type=int, default=1)
+    ap.add_argument("--triangles", type=int, default=0, help="override the workload's triangle count")
+    ap.add_argument("--traversal", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-rows", type=int, default=0, help="rows of the frame the CPU baseline renders")
+    return ap.parse_args()
+
+
+def make_scene(args):
+    from rayca_b200 import procedural as P
+
+    if args.workload == "soup":
+        n = args.triangles or 10_000_000
+        return P.soup(n), f"procedural triangle soup, {n} triangles (BASELINE.md M4 generator)"
+    n = args.triangles or 262_267
+    return P.atrium(n), ("procedural Sponza-class atrium (sponza.bin absent from the reference checkout), "
+                         "one BLAS, textured PBR, reference sponza-test camera/lights")
+
+
+def render_config(args):
+    from rayca_b200.renderer import Config
+
+    return Config(max_depth=1, samples_per_pixel=args.spp)
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index):
+        super().__init__(daemon=True)
+        self.dev = device_index
+        self.samples = []
+        self.stop = threading.Event()
+
+    def run(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.dev)], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 9:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            self.stop.wait(0.1)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(s[1]) for s in self.samples)
+        reasons = set()
+        for s in self.samples:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][2]), "reasons": sorted(reasons),
+                "samples": len(self.samples)}
+
+
+def cpu_baseline(desc, cfg, args, rows_total, faithful=True, phase=0.0):
+    """Times the oracle (a C++ port of rayca-soft's pixel loop: exhaustive unordered traversal, and with
+    `faithful` the per-test vertex re-transform the reference performs) on evenly spaced rows."""
+    from oracle import binding as O
+
+    osc = O.OracleScene(desc, bvh=True)
+    ys = ((np.arange(rows_total) + 0.5 + phase) / rows_total * args.height).astype(int) % args.height
+    rays = 0
+    ms = 0.0
+    threads = 0
+    for y in ys:
+        _, _, st = osc.render(cfg.to_c(), args.width, args.height, flags=O.FAITHFUL if faithful else 0,
+                              rows=(int(y), int(y) + 1), want_aux=False)
+        rays += st.rays_primary + st.rays_shadow + st.rays_secondary
+        ms += st.trace_ms
+        threads = st.threads
+    osc.close()
+    return rays, ms, threads
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path on the host cores.  The Rust
+    crate cannot be built here (nightly toolchain absent), so this is the oracle port in
+    reference-faithful mode, all host threads, each step a bounded sample of the same frame."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    scene, what = make_scene(args)
+    desc = scene.to_desc()
+    cfg = render_config(args)
+    rows = args.cpu_rows or 1
+    rays = 0
+    ms = 0.0
+    threads = 1
+    for k in range(args.steps):
+        r, m, threads = cpu_baseline(desc, cfg, args, rows, phase=0.37 * k)
+        rays += r
+        ms += m
+    value = rays / (ms * 1e-3) / 1e6
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / max(args.steps, 1),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": what, "width": args.width, "height": args.height, "spp": args.spp,
+                       "triangles": desc.triangle_count, "integrator": "Pathtracer max_depth=1 (NEE point lights)"},
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "port",
+                             "sample": f"{rows} evenly spaced rows of the {args.width}x{args.height} frame per step, "
+                                       "pixel loop only (BVH build excluded), reference-faithful mode"},
+            "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+
+    from rayca_b200 import build, model as M, renderer as R
+
+    build.build()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: there is no CPU fallback for the product path")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    G = world
+    W, H = args.width, args.height
+    scene, what = make_scene(args)
+    desc = scene.to_desc()
+    cfg = render_config(args)
+    ctx = R.Context(local_rank)
+    t0 = time.time()
+    dev = R.DeviceScene(ctx, desc, bvh=True)
+    build_s = time.time() - t0
+
+    tile = 8
+    tiles = (H + tile - 1) // tile
+    per = (tiles + G - 1) // G
+    local_rows = per * tile if G > 1 else H
+    local = torch.zeros((local_rows, W, 4), dtype=torch.uint8, device="cuda")
+    gathered = torch.zeros((G, local_rows, W, 4), dtype=torch.uint8, device="cuda") if G > 1 else None
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+    opts = M.rayca_options(0x5EED, args.traversal, rank, G, tile, 0, 0)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        dev.render_device(cfg, W, H, local.data_ptr(), stream=stream, options=opts)
+        if G > 1:
+            dist.all_gather_into_tensor(gathered, local)
+
+    def barrier():
+        if G > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    # ray counts of one frame (deterministic): this rank's share, summed over ranks
+    st = dev.last_counters()
+    rays_local = torch.tensor([st.rays_primary, st.rays_shadow, st.rays_secondary], dtype=torch.int64, device="cuda")
+    if G > 1:
+        dist.all_reduce(rays_local)
+    rays_frame = int(rays_local.sum().item())
+
+    # algorithmic bytes of one launch (untimed counting pass)
+    copts = M.rayca_options(0x5EED, args.traversal, rank, G, tile, R.FLAG_COUNT_WALK, 0)
+    dev.render_device(cfg, W, H, local.data_ptr(), stream=stream, options=copts)
+    torch.cuda.synchronize()
+    cst = dev.last_counters()
+    px_local = st.rays_primary // max(args.spp, 1)
+    algo_bytes = cst.node_bytes + cst.triangle_bytes + 4 * px_local  # + RGBA8 store per pixel
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    for k in range(args.steps):
+        flush.fill_(k & 0xFF)  # L2 flush between timed iterations (outside the timed events)
+        ev[k][0].record()
+        kev[k][0].record()
+        dev.render_device(cfg, W, H, local.data_ptr(), stream=stream, options=opts)
+        kev[k][1].record()
+        if G > 1:
+            dist.all_gather_into_tensor(gathered, local)
+        ev[k][1].record()
+    barrier()
+    sampler.stop.set()
+    sampler.join()
+    total_ms = sum(a.elapsed_time(b) for a, b in ev)
+    kernel_ms = sum(a.elapsed_time(b) for a, b in kev) / args.steps
+    t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+    if G > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    value = rays_frame * args.steps / (total_ms * 1e-3) / 1e6
+
+    # e2e through the host-buffer entry point (single GPU path of the C ABI; N>1: each rank its shard)
+    e2e = None
+    draw_e2e = None
+    if G == 1:
+        for _ in range(2):
+            dev.render(cfg, W, H)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        n_e2e = max(3, min(args.steps, 10))
+        for _ in range(n_e2e):
+            dev.render(cfg, W, H)
+        e2e_s = (time.perf_counter() - t1) / n_e2e
+        e2e = {"value": rays_frame / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 1024,
+               "d2h_bytes_per_step": W * H * 4, "ms_per_step": e2e_s * 1e3,
+               "what": "rayca_cuda_render: host RGBA8 out, scene resident (scene_create excluded, like the reference timer)"}
+        draw_e2e = {"ms": None}
+        img = R.Image(W, H)
+        rnd = R.CudaRenderer.__new__(R.CudaRenderer)
+        rnd.config, rnd._ctx = cfg, ctx
+        t1 = time.perf_counter()
+        rnd.draw(scene, img)
+        draw_e2e = {"ms": (time.perf_counter() - t1) * 1e3, "what": "Draw::draw: to_desc + flatten + BVH build + upload + render + read-back"}
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = algo_bytes / (kernel_ms * 1e-3) / 1e9
+        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": G, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": what, "width": W, "height": H, "spp": args.spp,
+                           "triangles": desc.triangle_count, "integrator": "Pathtracer max_depth=1 (NEE point lights)",
+                           "parallelism": f"image row-tiles of {tile} rows interleaved over {G} GPU(s), scene replicated, NCCL all_gather of RGBA8",
+                           "l2": "flushed between timed iterations (256 MiB fill)", "traversal": args.traversal},
+                "rays_per_frame": rays_frame, "kernel_ms": kernel_ms, "build_s": build_s,
+                "clocks": sampler.summary(), "gpu_launches": args.steps,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "peak_source": "measured" if peaks else "fallback",
+                             "algorithmic_bytes_per_launch": int(algo_bytes),
+                             "note": "working set is L2-resident; bytes = 32 B/node record + 48 B/triangle record fetched by the walk + 4 B/pixel"},
+                "e2e": e2e if e2e else {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 1024,
+                                        "d2h_bytes_per_step": 0, "what": "N>1: device-timed (frame stays on the GPUs)"},
+                "draw_e2e": draw_e2e}
+        if not args.no_cpu_baseline and G == 1:
+            rows = args.cpu_rows or 2
+            r, m, th = cpu_baseline(desc, cfg, args, rows)
+            line["cpu_baseline"] = {"value": r / (m * 1e-3) / 1e6, "unit": "Mrays/s", "cores": th, "kind": "port",
+                                    "sample": f"{rows} evenly spaced rows of the frame, pixel loop only, reference-faithful mode"}
+        print(json.dumps(line))
+    if G > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -268,8 +268,10 @@ typedef struct rayca_config {
 } rayca_config;
 
 enum {
-    RAYCA_TRAVERSAL_ORDERED = 0,   /* front-to-back, distance-culled (the product path) */
-    RAYCA_TRAVERSAL_EXHAUSTIVE = 1 /* reference order: every overlapped node, no cull (bvh/blas.rs:129-176) */
+    RAYCA_TRAVERSAL_ORDERED = 0,    /* product path: SAH performance tree, front-to-back, distance-culled,
+                                       every candidate re-validated against its reference leaf box */
+    RAYCA_TRAVERSAL_EXHAUSTIVE = 1, /* the reference tree walked like bvh/blas.rs:129-176: every overlapped node, no cull */
+    RAYCA_TRAVERSAL_REFERENCE_ORDERED = 2 /* the flattened reference tree, front-to-back and distance-culled */
 };
 
 /* Backend-only knobs, kept out of rayca_config so the reference `Config` stays

@@ -9,6 +9,8 @@
 #pragma once
 #include <cstdint>
 
+#include <cuda_runtime.h>
+
 namespace rb {
 
 struct alignas(16) GpuNode {
@@ -77,6 +79,15 @@ struct GpuSceneView {
     float root_max[3];
     uint32_t root_link1;
     GpuCamera camera;
+    // performance layer (fast_bvh.cpp): one binary tree over all triangles, pair layout as above;
+    // fast_tri holds 3 float4 per triangle in leaf order, w0 = reference-global triangle index,
+    // w1 = index (into `nodes`) of the reference leaf whose box must also accept the ray
+    const float4* fast_nodes;
+    const float4* fast_tri;
+    float fast_root_min[3];
+    uint32_t fast_root_link0;
+    float fast_root_max[3];
+    uint32_t fast_root_link1;
 };
 
 } // namespace rb

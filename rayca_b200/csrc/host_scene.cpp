@@ -437,6 +437,8 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
     };
     out.root = emit_tnode(troot, 0);
     out.max_stack = top_depth + max_blas_depth + 2;
+    build_fast_tree(out);
+    out.max_stack = std::max(out.max_stack, out.fast_depth + 2);
     return RAYCA_OK;
 }
 

@@ -59,6 +59,11 @@ struct HostScene {
     std::vector<uint32_t> blas_prim_offset, blas_node_offset;
     GpuNode root{};
     uint32_t max_stack = 0;              // deepest push chain the ordered walk can need
+    // performance layer
+    std::vector<GpuNode> fast_nodes;
+    std::vector<float4> fast_tri;
+    GpuNode fast_root{};
+    uint32_t fast_depth = 0;
 };
 
 // Returns RAYCA_OK or a negative RAYCA_E_* code; `err` receives a detail string.
@@ -68,5 +73,9 @@ int build_host_scene(const rayca_scene_desc& desc, bool bvh, HostScene& out, std
 // (bvh/blas.rs:64-127,245-316), evaluated through per-plane bins so that one pass over the
 // node's triangles serves all 189 candidates.  `max_depth` = u8::MAX, or 0 when Config::bvh is off.
 void build_blas(HostBlas& blas, uint32_t max_depth);
+
+// Performance layer: SAH tree over all triangles of the packed scene (fast_bvh.cpp).  Needs
+// HostScene::{blas, tri_pos, blas_prim_offset, blas_node_offset} to be final.
+void build_fast_tree(HostScene& scene);
 
 } // namespace rb

@@ -58,6 +58,8 @@ struct rayca_scene {
     void* d_texels = nullptr;
     void* d_lights = nullptr;
     void* d_blas_prim_offset = nullptr;
+    void* d_fast_nodes = nullptr;
+    void* d_fast_tri = nullptr;
     GpuSceneView view{};
     uint32_t max_stack = 0;
 };
@@ -103,14 +105,16 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
 }
 
 template <int INTEGRATOR>
-void launch_integrator(const RenderParams& P, dim3 grid, bool cull, bool count, cudaStream_t st) {
-    if (count) {
-        if (cull) render_kernel<INTEGRATOR, true, true><<<grid, 128, 0, st>>>(P);
-        else render_kernel<INTEGRATOR, false, true><<<grid, 128, 0, st>>>(P);
-    } else {
-        if (cull) render_kernel<INTEGRATOR, true, false><<<grid, 128, 0, st>>>(P);
-        else render_kernel<INTEGRATOR, false, false><<<grid, 128, 0, st>>>(P);
-    }
+void launch_integrator(const RenderParams& P, dim3 grid, uint32_t mode, bool count, cudaStream_t st) {
+#define RAYCA_LAUNCH(M)                                                             \
+    do {                                                                            \
+        if (count) render_kernel<INTEGRATOR, M, true><<<grid, 128, 0, st>>>(P);     \
+        else render_kernel<INTEGRATOR, M, false><<<grid, 128, 0, st>>>(P);          \
+    } while (0)
+    if (mode == RAYCA_TRAVERSAL_EXHAUSTIVE) RAYCA_LAUNCH(1);
+    else if (mode == RAYCA_TRAVERSAL_REFERENCE_ORDERED) RAYCA_LAUNCH(2);
+    else RAYCA_LAUNCH(0);
+#undef RAYCA_LAUNCH
 }
 
 } // namespace
@@ -171,6 +175,8 @@ void rayca_cuda_scene_destroy(rayca_scene* s) {
     cudaFree(s->d_texels);
     cudaFree(s->d_lights);
     cudaFree(s->d_blas_prim_offset);
+    cudaFree(s->d_fast_nodes);
+    cudaFree(s->d_fast_tri);
     delete s;
 }
 
@@ -215,6 +221,8 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     UP(d_texels, texels);
     UP(d_lights, lights);
     UP(d_blas_prim_offset, blas_prim_offset);
+    UP(d_fast_nodes, fast_nodes);
+    UP(d_fast_tri, fast_tri);
 #undef UP
     GpuSceneView& v = s->view;
     v.nodes = (const float4*)s->d_nodes;
@@ -234,11 +242,19 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     v.root_link0 = h.root.link0;
     v.root_link1 = h.root.link1;
     v.camera = h.camera;
+    v.fast_nodes = (const float4*)s->d_fast_nodes;
+    v.fast_tri = (const float4*)s->d_fast_tri;
+    v.fast_root_min[0] = h.fast_root.min_x; v.fast_root_min[1] = h.fast_root.min_y; v.fast_root_min[2] = h.fast_root.min_z;
+    v.fast_root_max[0] = h.fast_root.max_x; v.fast_root_max[1] = h.fast_root.max_y; v.fast_root_max[2] = h.fast_root.max_z;
+    v.fast_root_link0 = h.fast_root.link0;
+    v.fast_root_link1 = h.fast_root.link1;
     s->max_stack = h.max_stack;
     // host copies that are no longer needed
     std::vector<unsigned char>().swap(h.texels);
     std::vector<float4>().swap(h.tri_attr);
     std::vector<float4>().swap(h.tri_pos);
+    std::vector<float4>().swap(h.fast_tri);
+    std::vector<GpuNode>().swap(h.fast_nodes);
     for (HostBlas& b : h.blas) std::vector<HostAttr>().swap(b.attrs);
     double t2 = now_ms();
     if (stats) {
@@ -299,16 +315,17 @@ int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_con
         P.rgba_f32 = d_aux->rgba_f32;
     }
     P.counters = ctx->d_counters;
-    const bool cull = !(options && options->traversal == RAYCA_TRAVERSAL_EXHAUSTIVE);
+    const uint32_t mode = options ? options->traversal : (uint32_t)RAYCA_TRAVERSAL_ORDERED;
+    if (mode > RAYCA_TRAVERSAL_REFERENCE_ORDERED) return fail(RAYCA_E_INVALID_ARG, "unknown traversal mode");
     const bool count = options && (options->flags & RAYCA_FLAG_COUNT_WALK); // opt-in: walk counters cost registers
 
     CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), st));
     dim3 grid((width + 15) / 16, (rows + 7) / 8);
     CUDA_TRY(cudaEventRecord(ctx->ev0, st));
     switch (config->integrator) {
-        case RAYCA_INTEGRATOR_PATHTRACER: launch_integrator<RAYCA_INTEGRATOR_PATHTRACER>(P, grid, cull, count, st); break;
-        case RAYCA_INTEGRATOR_RAYTRACER: launch_integrator<RAYCA_INTEGRATOR_RAYTRACER>(P, grid, cull, count, st); break;
-        default: launch_integrator<RAYCA_INTEGRATOR_FLAT>(P, grid, cull, count, st); break;
+        case RAYCA_INTEGRATOR_PATHTRACER: launch_integrator<RAYCA_INTEGRATOR_PATHTRACER>(P, grid, mode, count, st); break;
+        case RAYCA_INTEGRATOR_RAYTRACER: launch_integrator<RAYCA_INTEGRATOR_RAYTRACER>(P, grid, mode, count, st); break;
+        default: launch_integrator<RAYCA_INTEGRATOR_FLAT>(P, grid, mode, count, st); break;
     }
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaEventRecord(ctx->ev1, st));
@@ -356,8 +373,9 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
     if (options && options->shard_count > 1) return fail(RAYCA_E_INVALID_ARG, "sharded output is only available through render_device");
     CUDA_TRY(cudaSetDevice(ctx->device));
     const size_t n = (size_t)width * height;
-    // scratch layout: rgba8 | hit_blas | hit_prim | hit_src | depth | uv | rgba_f32
-    size_t need = n * 4 + (aux ? n * (4 + 4 + 4 + 4 + 8 + 16) : 0);
+    // scratch layout: rgba8 | hit_blas | hit_prim | hit_src | depth | uv | rgba_f32, each plane 256 B aligned
+    auto al = [](size_t b) { return (b + 255) & ~size_t(255); };
+    size_t need = al(n * 4) + (aux ? 4 * al(n * 4) + al(n * 8) + al(n * 16) : 0);
     if (need > ctx->scratch_bytes) {
         cudaFree(ctx->d_scratch);
         ctx->d_scratch = nullptr;
@@ -368,17 +386,17 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
     unsigned char* base = (unsigned char*)ctx->d_scratch;
     rayca_aux_out d{};
     if (aux) {
-        unsigned char* p = base + n * 4;
+        unsigned char* p = base + al(n * 4);
         if (aux->hit_blas) d.hit_blas = (uint32_t*)p;
-        p += n * 4;
+        p += al(n * 4);
         if (aux->hit_prim) d.hit_prim = (uint32_t*)p;
-        p += n * 4;
+        p += al(n * 4);
         if (aux->hit_src) d.hit_src = (uint32_t*)p;
-        p += n * 4;
+        p += al(n * 4);
         if (aux->depth) d.depth = (float*)p;
-        p += n * 4;
+        p += al(n * 4);
         if (aux->uv) d.uv = (float*)p;
-        p += n * 8;
+        p += al(n * 8);
         if (aux->rgba_f32) d.rgba_f32 = (float*)p;
     }
     rayca_stats local{};

@@ -82,7 +82,7 @@ struct PixelCounters {
 };
 
 // NextEventEstimationSampler::get_direct_lighting, point lights (sampler/nee.rs:127-216)
-template <bool CULL, bool COUNT>
+template <int MODE, bool COUNT>
 __device__ __forceinline__ Col nee_direct(const RenderParams& P, const Surf& sf, PixelCounters& pc) {
     const GpuSceneView& s = P.scene;
     Col ret{0.0f, 0.0f, 0.0f, 1.0f};
@@ -97,7 +97,7 @@ __device__ __forceinline__ Col nee_direct(const RenderParams& P, const Surf& sf,
             HitD sh;
             sh.t = dist;
             pc.shadow++;
-            bool occluded = walk<CULL, true, COUNT>(s, shadow, sh, &pc.walk);
+            bool occluded = trace_ray<MODE, true, COUNT>(s, shadow, sh, &pc.walk);
             Col x{0.0f, 0.0f, 0.0f, 1.0f};
             if (!occluded) {
                 Col le = point_intensity(L, sf.point);
@@ -116,7 +116,7 @@ __device__ __forceinline__ Col nee_direct(const RenderParams& P, const Surf& sf,
 // Pathtracer::trace_impl (integrator/pathtracer.rs:68-106) for light_samples == 1 chains, unrolled
 // into a forward pass (trace, shade, spawn) and a backward pass that folds the radiance with the
 // reference's operator order.
-template <bool CULL, bool COUNT>
+template <int MODE, bool COUNT>
 __device__ __forceinline__ bool pathtracer(const RenderParams& P, RayD ray, uint32_t pixel, uint32_t sample, Col& out, HitD& primary,
                                            PixelCounters& pc) {
     const GpuSceneView& s = P.scene;
@@ -131,7 +131,7 @@ __device__ __forceinline__ bool pathtracer(const RenderParams& P, RayD ray, uint
     bool collect_emissive = true;
     for (uint32_t depth = 0; depth < max_depth && depth < (uint32_t)kMaxDepth; ++depth) {
         HitD h;
-        bool hit = walk<CULL, false, COUNT>(s, ray, h, &pc.walk);
+        bool hit = trace_ray<MODE, false, COUNT>(s, ray, h, &pc.walk);
         if (depth == 0) primary = h;
         if (!hit) break;
         Surf sf;
@@ -142,7 +142,7 @@ __device__ __forceinline__ bool pathtracer(const RenderParams& P, RayD ray, uint
             break;
         }
         Col d{0.0f, 0.0f, 0.0f, 1.0f};
-        if (nee) d = nee_direct<CULL, COUNT>(P, sf, pc);
+        if (nee) d = nee_direct<MODE, COUNT>(P, sf, pc);
         if (!(depth < limit)) { // no indirect: Some(direct + BLACK)
             tail = cadd(d, Col{0.0f, 0.0f, 0.0f, 1.0f});
             have_tail = true;
@@ -173,14 +173,14 @@ __device__ __forceinline__ bool pathtracer(const RenderParams& P, RayD ray, uint
 }
 
 // Raytracer::trace (integrator/raytracer.rs:16-76): mirror chain unrolled the same way.
-template <bool CULL, bool COUNT>
+template <int MODE, bool COUNT>
 __device__ __forceinline__ bool raytracer(const RenderParams& P, RayD ray, Col& out, HitD& primary, PixelCounters& pc) {
     const GpuSceneView& s = P.scene;
     Col ambient[kMaxDepth], light[kMaxDepth], spec[kMaxDepth];
     int levels = 0;
     for (uint32_t depth = 0; depth <= P.cfg.max_depth && depth < (uint32_t)kMaxDepth; ++depth) {
         HitD h;
-        bool hit = walk<CULL, false, COUNT>(s, ray, h, &pc.walk);
+        bool hit = trace_ray<MODE, false, COUNT>(s, ray, h, &pc.walk);
         if (depth == 0) primary = h;
         if (!hit) break;
         Surf sf;
@@ -196,7 +196,7 @@ __device__ __forceinline__ bool raytracer(const RenderParams& P, RayD ray, Col& 
             HitD sh;
             pc.shadow++;
             bool lit = true;
-            if (walk<CULL, false, COUNT>(s, shadow, sh, &pc.walk)) {
+            if (trace_ray<MODE, false, COUNT>(s, shadow, sh, &pc.walk)) {
                 float ldist = length(sf.point - lpos); // light/point.rs:32-35, directional.rs:34-37
                 if (!(sh.t > ldist)) {
                     Surf ss;
@@ -239,7 +239,7 @@ __device__ __forceinline__ unsigned char quantize(float c) {
 }
 
 // Block = 128 threads = 4 warps; a warp covers an 8x4 pixel tile, the block 16x8 pixels.
-template <int INTEGRATOR, bool CULL, bool COUNT>
+template <int INTEGRATOR, int MODE, bool COUNT>
 __global__ void __launch_bounds__(128) render_kernel(const __grid_constant__ RenderParams P) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t x = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
@@ -275,11 +275,11 @@ __global__ void __launch_bounds__(128) render_kernel(const __grid_constant__ Ren
             ph.t = __int_as_float(0x7f800000);
             ph.u = ph.v = 0.0f;
             if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER) {
-                ok = pathtracer<CULL, COUNT>(P, ray, pixel, i, c, ph, pc);
+                ok = pathtracer<MODE, COUNT>(P, ray, pixel, i, c, ph, pc);
             } else if (INTEGRATOR == RAYCA_INTEGRATOR_RAYTRACER) {
-                ok = raytracer<CULL, COUNT>(P, ray, c, ph, pc);
+                ok = raytracer<MODE, COUNT>(P, ray, c, ph, pc);
             } else { // Flat (integrator/flat.rs:16-28)
-                ok = walk<CULL, false, COUNT>(P.scene, ray, ph, &pc.walk);
+                ok = trace_ray<MODE, false, COUNT>(P.scene, ray, ph, &pc.walk);
                 if (ok) {
                     Surf sf;
                     load_surf(P.scene, ray, ph, sf);

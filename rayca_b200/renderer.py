@@ -43,7 +43,7 @@ class SamplerStrategy(enum.IntEnum):
     Mis = 5
 
 
-TRAVERSAL_ORDERED, TRAVERSAL_EXHAUSTIVE = 0, 1
+TRAVERSAL_ORDERED, TRAVERSAL_EXHAUSTIVE, TRAVERSAL_REFERENCE_ORDERED = 0, 1, 2
 FLAG_COUNT_WALK = 1
 
 _ERRORS = {-1: "RAYCA_E_INVALID_ARG", -2: "RAYCA_E_UNSUPPORTED", -3: "RAYCA_E_OOM", -4: "RAYCA_E_CUDA",

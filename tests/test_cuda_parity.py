@@ -63,7 +63,7 @@ def check_against(z, rgba8, aux, h, w, stochastic):
     assert psnr(got, want) >= 60.0
 
 
-@pytest.mark.parametrize("traversal", [R.TRAVERSAL_ORDERED, R.TRAVERSAL_EXHAUSTIVE])
+@pytest.mark.parametrize("traversal", [R.TRAVERSAL_ORDERED, R.TRAVERSAL_EXHAUSTIVE, R.TRAVERSAL_REFERENCE_ORDERED])
 @pytest.mark.parametrize("scene,case", golden_cases())
 def test_cuda_matches_golden(ctx, scene, case, traversal):
     z = load_case(scene, case)
