@@ -108,14 +108,14 @@ def test_ordered_equals_exhaustive_at_full_size(ctx):
 
 
 def test_render_is_deterministic(ctx):
-    sc = dev_scene(ctx, "box")
-    cfg = R.Config(max_depth=2)
+    sc = dev_scene(ctx, "cubes_over_plane")
+    cfg = R.Config(max_depth=3)
     opts = M.rayca_options(1234, 0, 0, 0, 0, 0, 0)
     a8, a, _ = sc.render(cfg, 128, 128, options=opts, want_aux=True)
     b8, b, _ = sc.render(cfg, 128, 128, options=opts, want_aux=True)
     assert np.array_equal(a8, b8) and np.array_equal(a.rgba_f32.view(np.uint32), b.rgba_f32.view(np.uint32))
-    c8, _, _ = sc.render(cfg, 128, 128, options=M.rayca_options(99, 0, 0, 0, 0, 0, 0))
-    assert not np.array_equal(a8, c8), "the seed must matter once a bounce is sampled"
+    _, c, _ = sc.render(cfg, 128, 128, options=M.rayca_options(99, 0, 0, 0, 0, 0, 0), want_aux=True)
+    assert not np.array_equal(a.rgba_f32, c.rgba_f32), "the seed must matter once a bounce is sampled"
 
 
 def test_draw_trait_mirror(ctx, cuda_lib):
