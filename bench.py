@@ -47,6 +47,8 @@ def parse_args():
     ap.add_argument("--spp", type=int, default=1)
     ap.add_argument("--triangles", type=int, default=0, help="override the workload's triangle count")
     ap.add_argument("--traversal", type=int, default=0)
+    ap.add_argument("--flags", type=int, default=0, help="rayca_options.flags for the timed launches")
+    ap.add_argument("--max-depth", type=int, default=1, help="Pathtracer max_depth (2 = one cosine bounce, BASELINE M5)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-rows", type=int, default=0, help="rows of the frame the CPU baseline renders")
     return ap.parse_args()
@@ -66,7 +68,7 @@ def make_scene(args):
 def render_config(args):
     from rayca_b200.renderer import Config
 
-    return Config(max_depth=1, samples_per_pixel=args.spp)
+    return Config(max_depth=args.max_depth, samples_per_pixel=args.spp)
 
 
 class ClockSampler(threading.Thread):
@@ -192,7 +194,7 @@ def run_ours(args):
     local = torch.zeros((local_rows, W, 4), dtype=torch.uint8, device="cuda")
     gathered = torch.zeros((G, local_rows, W, 4), dtype=torch.uint8, device="cuda") if G > 1 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
-    opts = M.rayca_options(0x5EED, args.traversal, rank, G, tile, 0, 0)
+    opts = M.rayca_options(0x5EED, args.traversal, rank, G, tile, args.flags, 0)
     stream = torch.cuda.current_stream().cuda_stream
 
     def step():

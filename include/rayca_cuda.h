@@ -287,7 +287,9 @@ typedef struct rayca_options {
 } rayca_options;
 
 enum {
-    RAYCA_FLAG_COUNT_WALK = 1 /* also tally node / triangle records fetched (roofline accounting; slower) */
+    RAYCA_FLAG_COUNT_WALK = 1, /* also tally node / triangle records fetched (roofline accounting; slower) */
+    RAYCA_FLAG_PERSISTENT = 2 /* persistent warps that pull 16x8 pixel groups from a global counter instead of
+                                 one thread block per group (default; faster on B200, see render.cuh) */
 };
 
 /* Optional per-pixel planes for parity checks; any pointer may be NULL.
@@ -310,7 +312,8 @@ typedef struct rayca_stats {
     uint64_t rays_shadow;
     uint64_t rays_secondary;
     uint64_t node_bytes;     /* algorithmic bytes: 64 B per node-pair record fetched */
-    uint64_t triangle_bytes; /* algorithmic bytes: 48 B per triangle tested */
+    uint64_t triangle_bytes; /* algorithmic bytes: product path 16 B per triangle plane fetched + 48 B per triangle
+                                whose vertices were fetched; reference-tree modes 48 B per triangle tested */
     uint32_t kernel_launches;
     uint32_t reserved;
 } rayca_stats;

@@ -35,15 +35,17 @@ def is_stale() -> bool:
         os.path.getmtime(os.path.abspath(__file__)) > t
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not is_stale():
+def build(force: bool = False, verbose: bool = False, out: str = OUT, defines=()) -> str:
+    """`out` / `defines` build a tuning variant next to the product library (see tools/variants.py)."""
+    if out == OUT and not force and not is_stale():
         return OUT
     host_cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
-    cmd = [nvcc_path(), "-shared", "-o", OUT, "-std=c++17", "-O3", "-lineinfo",
+    cmd = [nvcc_path(), "-shared", "-o", out, "-std=c++17", "-O3", "-lineinfo",
            "-gencode", "arch=compute_100a,code=sm_100a", "--fmad=false",
            "-ccbin", host_cxx, "-x", "cu",
            "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math,-fopenmp,-O2",
            "-Xptxas", "-v" if verbose else "-O3"]
+    cmd += [f"-D{d}" for d in defines]
     cmd += [os.path.join(CSRC, f) for f in SOURCES]
     cmd += ["-lgomp"]
     res = subprocess.run(cmd, capture_output=True, text=True)
@@ -52,7 +54,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed")
     if verbose:
         sys.stderr.write(res.stdout + res.stderr)
-    return OUT
+    return out
 
 
 if __name__ == "__main__":

@@ -208,7 +208,11 @@ void build_fast_tree(HostScene& hs) {
 #pragma omp single
         root = fb.build(0, total, 0);
     }
-    // depth-first relayout of the pairs (left subtree right after its parent pair)
+    // depth-first relayout of the pairs (left subtree right after its parent pair).  A child
+    // reference (GpuNode::link0) is either a pair index or, with kLeafRef set, a packed leaf
+    // {bits 0..27 first triangle, bits 28..30 count-1}.
+    constexpr uint32_t kLeafRef = 0x80000000u;
+    auto leaf_ref = [&](const Rec& r) { return kLeafRef | ((r.link1 - 1u) << 28) | r.link0; };
     hs.fast_nodes.clear();
     hs.fast_nodes.reserve(items.size());
     struct Todo { uint32_t slot; uint32_t dst; };
@@ -218,6 +222,8 @@ void build_fast_tree(HostScene& hs) {
         hs.fast_nodes.resize(2);
         stack.push_back({root.link0, 0});
         groot.link0 = 0;
+    } else {
+        groot.link0 = leaf_ref(root);
     }
     while (!stack.empty()) {
         Todo t = stack.back();
@@ -230,28 +236,40 @@ void build_fast_tree(HostScene& hs) {
             hs.fast_nodes.resize(hs.fast_nodes.size() + 2);
             gr.link0 = dst;
             stack.push_back({r.link0, dst});
+        } else {
+            gr.link0 = leaf_ref(r);
         }
         if (l.link1 == 0) {
             uint32_t dst = (uint32_t)hs.fast_nodes.size();
             hs.fast_nodes.resize(hs.fast_nodes.size() + 2);
             gl.link0 = dst;
             stack.push_back({l.link0, dst});
+        } else {
+            gl.link0 = leaf_ref(l);
         }
         hs.fast_nodes[t.dst] = gl;
         hs.fast_nodes[t.dst + 1] = gr;
     }
     hs.fast_root = groot;
     hs.fast_depth = fb.max_depth;
-    // triangles in leaf order: w0 = reference-global index, w1 = reference leaf node (global), w2 = 0
-    hs.fast_tri.resize((size_t)total * 3);
+    // 64-byte triangle records in leaf order: {n.xyz, d | v0, reference-global index | v1, reference
+    // leaf node | v2, dot(n,n)}.  n = (v1-v0) x (v2-v0), d = -dot(n, v0) and dot(n,n) are evaluated with
+    // the operation order of Triangle::intersects (rayca-geometry/src/triangle.rs:90-94,110,152), so the
+    // kernel reads the bits the reference would recompute for every test.
+    hs.fast_tri.resize((size_t)total * 4);
 #pragma omp parallel for schedule(static) if (total > 8192)
     for (int64_t i = 0; i < (int64_t)total; ++i) {
         uint32_t id = items[(size_t)i].id;
         const float4* src = &hs.tri_pos[(size_t)id * 3];
-        float4* dst = &hs.fast_tri[(size_t)i * 3];
-        dst[0] = make_float4(src[0].x, src[0].y, src[0].z, __builtin_bit_cast(float, id));
-        dst[1] = make_float4(src[1].x, src[1].y, src[1].z, __builtin_bit_cast(float, ref_leaf[id]));
-        dst[2] = make_float4(src[2].x, src[2].y, src[2].z, 0.0f);
+        const V3 v0{src[0].x, src[0].y, src[0].z}, v1{src[1].x, src[1].y, src[1].z}, v2{src[2].x, src[2].y, src[2].z};
+        const V3 n = cross(v1 - v0, v2 - v0);
+        const float d = -dot(n, v0);
+        const float den = dot(n, n);
+        float4* dst = &hs.fast_tri[(size_t)i * 4];
+        dst[0] = make_float4(n.x, n.y, n.z, d);
+        dst[1] = make_float4(v0.x, v0.y, v0.z, __builtin_bit_cast(float, id));
+        dst[2] = make_float4(v1.x, v1.y, v1.z, __builtin_bit_cast(float, ref_leaf[id]));
+        dst[3] = make_float4(v2.x, v2.y, v2.z, den);
     }
 }
 

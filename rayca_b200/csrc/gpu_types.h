@@ -79,15 +79,17 @@ struct GpuSceneView {
     float root_max[3];
     uint32_t root_link1;
     GpuCamera camera;
-    // performance layer (fast_bvh.cpp): one binary tree over all triangles, pair layout as above;
-    // fast_tri holds 3 float4 per triangle in leaf order, w0 = reference-global triangle index,
-    // w1 = index (into `nodes`) of the reference leaf whose box must also accept the ray
+    // performance layer (fast_bvh.cpp): one binary tree over all triangles, sibling pairs adjacent;
+    // a child reference (link0) is a pair index or, with bit 31 set, a packed leaf {first, count-1}.
+    // fast_tri holds 4 float4 (64 B) per triangle in leaf order:
+    //   {n.xyz, d | v0, reference-global triangle index | v1, reference leaf (index into `nodes`)
+    //    whose box must also accept the ray | v2, dot(n,n)}
     const float4* fast_nodes;
     const float4* fast_tri;
     float fast_root_min[3];
-    uint32_t fast_root_link0;
+    uint32_t fast_root_ref;
     float fast_root_max[3];
-    uint32_t fast_root_link1;
+    uint32_t fast_pad;
 };
 
 } // namespace rb

@@ -62,7 +62,7 @@ struct HostScene {
     // performance layer
     std::vector<GpuNode> fast_nodes;
     std::vector<float4> fast_tri;
-    GpuNode fast_root{};
+    GpuNode fast_root{};   // link0 = child reference of the root (pair index or packed leaf)
     uint32_t fast_depth = 0;
 };
 

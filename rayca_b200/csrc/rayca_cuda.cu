@@ -38,7 +38,8 @@ double now_ms() {
 
 struct rayca_ctx {
     int device = 0;
-    unsigned long long* d_counters = nullptr; // 4 x u64
+    int sm_count = 1;
+    unsigned long long* d_counters = nullptr; // kCounterSlots x u64
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     rayca_stats last{};
     uint64_t last_primary = 0;
@@ -104,17 +105,56 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
     return RAYCA_OK;
 }
 
+// Launches one instantiation.  Persistent scheduling sizes the grid to what is resident at once
+// (SM count x blocks per SM, from the occupancy API, cached per instantiation); otherwise one block
+// per 16x8 pixel group.
+template <int INTEGRATOR, int MODE, bool COUNT, bool PERSISTENT, bool BOUNCE>
+void launch_one(const RenderParams& P, dim3 groups, int sm_count, cudaStream_t st) {
+    if (PERSISTENT) {
+        static int blocks_per_sm = 0;
+        if (blocks_per_sm == 0) {
+            int n = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_kernel<INTEGRATOR, MODE, COUNT, true, BOUNCE>, 128, 0) != cudaSuccess || n < 1) n = 1;
+            blocks_per_sm = n;
+        }
+        unsigned long long want = ((unsigned long long)P.tile_count + 3) / 4; // 4 warps per block, one group each
+        unsigned long long cap = (unsigned long long)sm_count * blocks_per_sm;
+        dim3 grid((unsigned)std::max<unsigned long long>(1, std::min(want, cap)));
+        render_kernel<INTEGRATOR, MODE, COUNT, true, BOUNCE><<<grid, 128, 0, st>>>(P);
+    } else {
+        render_kernel<INTEGRATOR, MODE, COUNT, false, BOUNCE><<<groups, 128, 0, st>>>(P);
+    }
+}
+
+struct LaunchSel {
+    uint32_t mode;
+    bool count, persistent, bounce;
+    int sm_count;
+};
+
+template <int INTEGRATOR, int MODE>
+void launch_mode(const RenderParams& P, dim3 groups, const LaunchSel& k, cudaStream_t st) {
+    constexpr bool kPath = INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER; // BOUNCE only matters to the path tracer
+    if (k.count) {
+        if (kPath && k.bounce) launch_one<INTEGRATOR, MODE, true, false, kPath>(P, groups, k.sm_count, st);
+        else launch_one<INTEGRATOR, MODE, true, false, false>(P, groups, k.sm_count, st);
+    } else if (k.persistent) {
+        if (kPath && k.bounce) launch_one<INTEGRATOR, MODE, false, true, kPath>(P, groups, k.sm_count, st);
+        else launch_one<INTEGRATOR, MODE, false, true, false>(P, groups, k.sm_count, st);
+    } else {
+        if (kPath && k.bounce) launch_one<INTEGRATOR, MODE, false, false, kPath>(P, groups, k.sm_count, st);
+        else launch_one<INTEGRATOR, MODE, false, false, false>(P, groups, k.sm_count, st);
+    }
+}
+
 template <int INTEGRATOR>
-void launch_integrator(const RenderParams& P, dim3 grid, uint32_t mode, bool count, cudaStream_t st) {
-#define RAYCA_LAUNCH(M)                                                             \
-    do {                                                                            \
-        if (count) render_kernel<INTEGRATOR, M, true><<<grid, 128, 0, st>>>(P);     \
-        else render_kernel<INTEGRATOR, M, false><<<grid, 128, 0, st>>>(P);          \
-    } while (0)
-    if (mode == RAYCA_TRAVERSAL_EXHAUSTIVE) RAYCA_LAUNCH(1);
-    else if (mode == RAYCA_TRAVERSAL_REFERENCE_ORDERED) RAYCA_LAUNCH(2);
-    else RAYCA_LAUNCH(0);
-#undef RAYCA_LAUNCH
+void launch_integrator(const RenderParams& P, dim3 groups, const LaunchSel& k, cudaStream_t st) {
+#ifndef RAYCA_FAST_BUILD // tuning variants (tools/variants.py) only carry the product walk
+    if (k.mode == RAYCA_TRAVERSAL_EXHAUSTIVE) launch_mode<INTEGRATOR, 1>(P, groups, k, st);
+    else if (k.mode == RAYCA_TRAVERSAL_REFERENCE_ORDERED) launch_mode<INTEGRATOR, 2>(P, groups, k, st);
+    else
+#endif
+        launch_mode<INTEGRATOR, 0>(P, groups, k, st);
 }
 
 } // namespace
@@ -146,8 +186,9 @@ int rayca_cuda_init(int device, rayca_ctx** out) {
     rayca_ctx* c = new (std::nothrow) rayca_ctx();
     if (!c) return fail(RAYCA_E_OOM, "host allocation");
     c->device = device;
-    CUDA_TRY(cudaMalloc((void**)&c->d_counters, 4 * sizeof(unsigned long long)));
-    CUDA_TRY(cudaMemset(c->d_counters, 0, 4 * sizeof(unsigned long long)));
+    CUDA_TRY(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
+    CUDA_TRY(cudaMalloc((void**)&c->d_counters, kCounterSlots * sizeof(unsigned long long)));
+    CUDA_TRY(cudaMemset(c->d_counters, 0, kCounterSlots * sizeof(unsigned long long)));
     CUDA_TRY(cudaEventCreate(&c->ev0));
     CUDA_TRY(cudaEventCreate(&c->ev1));
     *out = c;
@@ -199,6 +240,10 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         delete s;
         return fail(rc, err);
     }
+    if (s->host.blas_prim_offset.back() >= (1u << 28)) {
+        delete s;
+        return fail(RAYCA_E_UNSUPPORTED, "more than 2^28 triangles");
+    }
     if (s->host.max_stack > (uint32_t)kStackSize) {
         delete s;
         return fail(RAYCA_E_UNSUPPORTED, "BVH deeper than the traversal stack");
@@ -246,8 +291,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     v.fast_tri = (const float4*)s->d_fast_tri;
     v.fast_root_min[0] = h.fast_root.min_x; v.fast_root_min[1] = h.fast_root.min_y; v.fast_root_min[2] = h.fast_root.min_z;
     v.fast_root_max[0] = h.fast_root.max_x; v.fast_root_max[1] = h.fast_root.max_y; v.fast_root_max[2] = h.fast_root.max_z;
-    v.fast_root_link0 = h.fast_root.link0;
-    v.fast_root_link1 = h.fast_root.link1;
+    v.fast_root_ref = h.fast_root.link0;
     s->max_stack = h.max_stack;
     // host copies that are no longer needed
     std::vector<unsigned char>().swap(h.texels);
@@ -319,13 +363,19 @@ int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_con
     if (mode > RAYCA_TRAVERSAL_REFERENCE_ORDERED) return fail(RAYCA_E_INVALID_ARG, "unknown traversal mode");
     const bool count = options && (options->flags & RAYCA_FLAG_COUNT_WALK); // opt-in: walk counters cost registers
 
-    CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), st));
+    const bool persistent = options && (options->flags & RAYCA_FLAG_PERSISTENT);
+    CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, kCounterSlots * sizeof(unsigned long long), st));
     dim3 grid((width + 15) / 16, (rows + 7) / 8);
+    P.groups_x = grid.x;
+    P.tile_count = grid.x * grid.y;
     CUDA_TRY(cudaEventRecord(ctx->ev0, st));
+    LaunchSel sel{mode, count, persistent, false, ctx->sm_count};
+    if (config->integrator == RAYCA_INTEGRATOR_PATHTRACER) // an indirect ray needs depth < limit (pathtracer.rs:94)
+        sel.bounce = config->max_depth > (config->direct_sampler == RAYCA_SAMPLER_NEE ? 1u : 0u);
     switch (config->integrator) {
-        case RAYCA_INTEGRATOR_PATHTRACER: launch_integrator<RAYCA_INTEGRATOR_PATHTRACER>(P, grid, mode, count, st); break;
-        case RAYCA_INTEGRATOR_RAYTRACER: launch_integrator<RAYCA_INTEGRATOR_RAYTRACER>(P, grid, mode, count, st); break;
-        default: launch_integrator<RAYCA_INTEGRATOR_FLAT>(P, grid, mode, count, st); break;
+        case RAYCA_INTEGRATOR_PATHTRACER: launch_integrator<RAYCA_INTEGRATOR_PATHTRACER>(P, grid, sel, st); break;
+        case RAYCA_INTEGRATOR_RAYTRACER: launch_integrator<RAYCA_INTEGRATOR_RAYTRACER>(P, grid, sel, st); break;
+        default: launch_integrator<RAYCA_INTEGRATOR_FLAT>(P, grid, sel, st); break;
     }
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaEventRecord(ctx->ev1, st));
@@ -352,7 +402,7 @@ int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_con
 int rayca_cuda_last_counters(rayca_ctx* ctx, rayca_stats* stats) {
     if (!ctx || !stats) return fail(RAYCA_E_INVALID_ARG, "null argument");
     CUDA_TRY(cudaSetDevice(ctx->device));
-    unsigned long long c[4];
+    unsigned long long c[kCounterSlots];
     CUDA_TRY(cudaEventSynchronize(ctx->ev1));
     CUDA_TRY(cudaMemcpy(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
     float ms = 0.0f;
@@ -362,7 +412,7 @@ int rayca_cuda_last_counters(rayca_ctx* ctx, rayca_stats* stats) {
     stats->rays_shadow = c[0];
     stats->rays_secondary = c[1];
     stats->node_bytes = c[2] * 32ull;
-    stats->triangle_bytes = c[3] * 48ull;
+    stats->triangle_bytes = c[3] * 48ull + c[4] * 16ull;
     stats->kernel_launches = 1;
     return RAYCA_OK;
 }

@@ -30,8 +30,12 @@ struct RenderParams {
     float* depth;
     float* uv;
     float* rgba_f32;
-    unsigned long long* counters; // [0] shadow rays [1] secondary rays [2] node records [3] triangle records
+    uint32_t tile_count, groups_x; // persistent scheduling: number of 16x8 pixel groups, groups per row
+    // [0] shadow rays [1] secondary rays [2] node records [3] triangle vertex fetches [4] plane fetches
+    // [5] next tile (persistent scheduling)
+    unsigned long long* counters;
 };
+constexpr int kCounterSlots = 8;
 
 // Philox4x32-10 keyed by the seed, counter = (pixel, sample, depth, dimension).  The reference draws
 // from thread-local unseeded fastrand (sampler/cosine.rs:66-67), which is not reproducible; both
@@ -81,25 +85,39 @@ struct PixelCounters {
     WalkCounters walk;
 };
 
-// NextEventEstimationSampler::get_direct_lighting, point lights (sampler/nee.rs:127-216)
-template <int MODE, bool COUNT>
-__device__ __forceinline__ Col nee_direct(const RenderParams& P, const Surf& sf, PixelCounters& pc) {
+// NextEventEstimationSampler::get_direct_lighting, point lights (sampler/nee.rs:127-216).
+// The shadow rays of up to 32 light samples are walked first (only the hit geometry is live), then the
+// material is evaluated once and the unoccluded samples are shaded, summed in the reference's order —
+// a reordering of independent computations, so every value is the one the reference computes.
+template <int MODE, bool COUNT, bool LAZY_MATERIAL>
+__device__ __forceinline__ Col nee_direct(const RenderParams& P, Surf& sf, PixelCounters& pc) {
     const GpuSceneView& s = P.scene;
     Col ret{0.0f, 0.0f, 0.0f, 1.0f};
-    for (uint32_t li = 0; li < s.light_count; ++li) {
-        const GpuLight& L = s.lights[li];
-        for (uint32_t k = 0; k < P.cfg.light_samples; ++k) {
-            V3 x1{L.pos[0], L.pos[1], L.pos[2]};
-            V3 d = x1 - sf.point;
-            float dist = length(d);
-            V3 omega = normalize(d);
-            RayD shadow = make_ray(sf.next_origin, omega);
+    const uint32_t ls = P.cfg.light_samples;
+    const uint32_t total = s.light_count * ls;
+    bool evaluated = !LAZY_MATERIAL;
+    for (uint32_t base = 0; base < total; base += 32u) {
+        const uint32_t n = min(32u, total - base);
+        uint32_t lit = 0;
+        for (uint32_t j = 0; j < n; ++j) {
+            const GpuLight& L = s.lights[(base + j) / ls];
+            V3 d = V3{L.pos[0], L.pos[1], L.pos[2]} - sf.point;
+            RayD shadow = make_ray(sf.next_origin, normalize(d));
             HitD sh;
-            sh.t = dist;
+            sh.t = length(d);
             pc.shadow++;
-            bool occluded = trace_ray<MODE, true, COUNT>(s, shadow, sh, &pc.walk);
+            if (!trace_ray<MODE, true, COUNT>(s, shadow, sh, &pc.walk)) lit |= 1u << j;
+        }
+        if (lit && !evaluated) {
+            eval_material(s, sf);
+            evaluated = true;
+        }
+        for (uint32_t j = 0; j < n; ++j) {
             Col x{0.0f, 0.0f, 0.0f, 1.0f};
-            if (!occluded) {
+            if ((lit >> j) & 1u) {
+                const GpuLight& L = s.lights[(base + j) / ls];
+                V3 d = V3{L.pos[0], L.pos[1], L.pos[2]} - sf.point;
+                V3 omega = normalize(d);
                 Col le = point_intensity(L, sf.point);
                 Col brdf = surf_brdf(s, sf, omega);
                 float r2 = norm2(d);
@@ -116,15 +134,17 @@ __device__ __forceinline__ Col nee_direct(const RenderParams& P, const Surf& sf,
 // Pathtracer::trace_impl (integrator/pathtracer.rs:68-106) for light_samples == 1 chains, unrolled
 // into a forward pass (trace, shade, spawn) and a backward pass that folds the radiance with the
 // reference's operator order.
-template <int MODE, bool COUNT>
+// BOUNCE = false compiles the indirect part out (the host picks it when the configuration cannot
+// spawn an indirect ray: max_depth <= 1 with NEE, 0 without) — the deterministic primary + shadow slice.
+template <int MODE, bool COUNT, bool BOUNCE>
 __device__ __forceinline__ bool pathtracer(const RenderParams& P, RayD ray, uint32_t pixel, uint32_t sample, Col& out, HitD& primary,
                                            PixelCounters& pc) {
     const GpuSceneView& s = P.scene;
     const bool nee = P.cfg.direct_sampler == RAYCA_SAMPLER_NEE;
     const uint32_t max_depth = P.cfg.max_depth;
     const uint32_t limit = nee ? max_depth - 1 : max_depth;
-    Col direct[kMaxDepth];
-    Col brdf[kMaxDepth];
+    Col direct[BOUNCE ? kMaxDepth : 1];
+    Col brdf[BOUNCE ? kMaxDepth : 1];
     int levels = 0;       // number of shaded (non-terminal) levels stored
     bool have_tail = false;
     Col tail{0.0f, 0.0f, 0.0f, 1.0f}; // value of the deepest trace_impl that returned Some without recursing
@@ -135,15 +155,15 @@ __device__ __forceinline__ bool pathtracer(const RenderParams& P, RayD ray, uint
         if (depth == 0) primary = h;
         if (!hit) break;
         Surf sf;
-        load_surf(s, ray, h, sf);
+        load_surf<BOUNCE>(s, ray, h, sf); // without bounces the material is evaluated lazily by nee_direct
         if (collect_emissive && sf.mat->kind == RAYCA_MATERIAL_PHONG && sf.mat->emissive) {
             tail = surf_color(s, sf);
             have_tail = true;
             break;
         }
         Col d{0.0f, 0.0f, 0.0f, 1.0f};
-        if (nee) d = nee_direct<MODE, COUNT>(P, sf, pc);
-        if (!(depth < limit)) { // no indirect: Some(direct + BLACK)
+        if (nee) d = nee_direct<MODE, COUNT, !BOUNCE>(P, sf, pc);
+        if (!BOUNCE || !(depth < limit)) { // no indirect: Some(direct + BLACK)
             tail = cadd(d, Col{0.0f, 0.0f, 0.0f, 1.0f});
             have_tail = true;
             break;
@@ -238,87 +258,129 @@ __device__ __forceinline__ unsigned char quantize(float c) {
     return (unsigned char)__float2uint_rz(v);
 }
 
-// Block = 128 threads = 4 warps; a warp covers an 8x4 pixel tile, the block 16x8 pixels.
-template <int INTEGRATOR, int MODE, bool COUNT>
-__global__ void __launch_bounds__(128) render_kernel(const __grid_constant__ RenderParams P) {
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t x = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
-    const uint32_t local_row = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+// One pixel: every sample's primary ray through the integrator, accumulation, gamma, RGBA8
+// (rayca-soft/src/scene.rs:123-149).
+// correct_gamma (color/mod.rs:175-180): one shared copy of powf
+__device__ __noinline__ float gamma_pow(float c, float inv_gamma) { return powf(c, inv_gamma); }
+
+template <int INTEGRATOR, int MODE, bool COUNT, bool BOUNCE>
+__device__ __forceinline__ void render_pixel(const RenderParams& P, uint32_t x, uint32_t local_row, PixelCounters& pc) {
     uint32_t y = local_row;
     if (P.shard_count > 1) {
         uint32_t tile = local_row / P.tile_rows;
         y = (tile * P.shard_count + P.shard_index) * P.tile_rows + (local_row % P.tile_rows);
     }
-    const bool active = x < P.width && y < P.height;
+    if (!(x < P.width && y < P.height)) return;
+    const GpuCamera& cam = P.scene.camera;
+    const TrsF ctrs{V3{cam.t[0], cam.t[1], cam.t[2]}, Q4{cam.q[0], cam.q[1], cam.q[2], cam.q[3]}, V3{cam.s[0], cam.s[1], cam.s[2]}};
+    Col color{0.0f, 0.0f, 0.0f, 1.0f};
+    HitD primary;
+    primary.prim = 0xFFFFFFFFu;
+    const uint32_t pixel = y * P.width + x;
+    for (uint32_t i = 0; i < P.cfg.samples_per_pixel; ++i) {
+        float ix = (float)(i % P.strate_u);
+        float iy = (float)(i / P.strate_u);
+        float xx = (2.0f * (((float)x + ix * P.step + P.offset) * P.inv_w) - 1.0f) * cam.angle * P.aspect;
+        float yy = (1.0f - 2.0f * (((float)y + iy * P.step + P.offset) * P.inv_h)) * cam.angle;
+        V3 dir = normalize(V3{xx, yy, -1.0f});
+        // &camera_trs.trs * Ray::new(origin, dir): scale, rotate, translate (trs.rs:275-284); no re-normalise
+        V3 wd = rotate(dir * ctrs.s, ctrs.q);
+        V3 wo = rotate(scale_point(V3{0.0f, 0.0f, 0.0f}, ctrs.s), ctrs.q) + ctrs.t;
+        RayD ray = make_ray(wo, wd);
+        Col c{0.0f, 0.0f, 0.0f, 1.0f};
+        bool ok;
+        HitD ph;
+        ph.prim = 0xFFFFFFFFu;
+        ph.t = __int_as_float(0x7f800000);
+        ph.u = ph.v = 0.0f;
+        if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER) {
+            ok = pathtracer<MODE, COUNT, BOUNCE>(P, ray, pixel, i, c, ph, pc);
+        } else if (INTEGRATOR == RAYCA_INTEGRATOR_RAYTRACER) {
+            ok = raytracer<MODE, COUNT>(P, ray, c, ph, pc);
+        } else { // Flat (integrator/flat.rs:16-28)
+            ok = trace_ray<MODE, false, COUNT>(P.scene, ray, ph, &pc.walk);
+            if (ok) {
+                Surf sf;
+                load_surf(P.scene, ray, ph, sf);
+                c = surf_color(P.scene, sf);
+            }
+        }
+        if (!ok) {
+            c = Col{0.0f, 0.0f, 0.0f, 1.0f}; // unwrap_or(Color::BLACK) (scene.rs:80-86)
+            if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER && P.cfg.max_depth == 0) ph.prim = 0xFFFFFFFFu;
+        }
+        primary = ph;
+        color = cadd(color, c);
+    }
+    color = cdiv(color, (float)P.cfg.samples_per_pixel);
+    if (P.inv_gamma != 1.0f) { // powf(c, 1.0) == c in the reference's libm; skipping it keeps the bits
+        color.r = gamma_pow(color.r, P.inv_gamma);
+        color.g = gamma_pow(color.g, P.inv_gamma);
+        color.b = gamma_pow(color.b, P.inv_gamma);
+    }
+    const size_t o = (size_t)((P.shard_count > 1) ? local_row : y) * P.width + x;
+    uchar4 q = make_uchar4(quantize(color.r), quantize(color.g), quantize(color.b), quantize(color.a));
+    reinterpret_cast<uchar4*>(P.rgba8)[o] = q;
+    const bool hit = primary.prim != 0xFFFFFFFFu;
+    if (P.hit_prim || P.hit_blas || P.hit_src) {
+        uint32_t blas = 0xFFFFFFFFu, local = 0xFFFFFFFFu, src = 0xFFFFFFFFu;
+        if (hit) {
+            blas = 0;
+            while (blas + 1 < P.scene.blas_count && primary.prim >= P.scene.blas_prim_offset[blas + 1]) ++blas;
+            local = primary.prim - P.scene.blas_prim_offset[blas];
+            src = __float_as_uint(P.scene.tri_pos[3 * (size_t)primary.prim].w);
+        }
+        if (P.hit_blas) P.hit_blas[o] = blas;
+        if (P.hit_prim) P.hit_prim[o] = local;
+        if (P.hit_src) P.hit_src[o] = src;
+    }
+    if (P.depth) P.depth[o] = hit ? primary.t : __int_as_float(0x7f800000);
+    if (P.uv) {
+        P.uv[2 * o] = hit ? primary.u : 0.0f;
+        P.uv[2 * o + 1] = hit ? primary.v : 0.0f;
+    }
+    if (P.rgba_f32) reinterpret_cast<float4*>(P.rgba_f32)[o] = make_float4(color.r, color.g, color.b, color.a);
+}
+
+// 8 blocks x 4 warps per SM = 64 registers per thread: the walk is latency- and issue-bound, and half
+// occupancy with a few spilled shading temporaries beats 25 % occupancy without (profiles/: 1.28 ms at
+// 146 registers, 0.98 at 80, 0.92 at 64 for the 1080p atrium frame).
+#ifndef RAYCA_MIN_BLOCKS
+#define RAYCA_MIN_BLOCKS 8
+#endif
+
+// Block = 128 threads = 4 warps; a warp owns an 8x4 pixel tile (coherent rays share node fetches
+// through L1), four consecutive tiles form a 16x8 pixel group.
+//   default: one block per pixel group, scheduled by the hardware's block dispatcher.
+//   PERSISTENT (RAYCA_FLAG_PERSISTENT): the grid is sized to the resident capacity of the GPU and every
+//     warp pulls its next group (4 tiles, walked one after the other) from a global counter — one
+//     atomicAdd per warp, broadcast by shuffle.  Measured 15-20 % SLOWER than the static grid on B200 for
+//     the 1080p frames (profiles/r01_ab_*): the block dispatcher already is a dynamic queue with 16k
+//     entries per frame, and the persistent form adds the fetch latency to every group.
+template <int INTEGRATOR, int MODE, bool COUNT, bool PERSISTENT, bool BOUNCE>
+__global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) render_kernel(const __grid_constant__ RenderParams P) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     PixelCounters pc;
-    if (active) {
-        const GpuCamera& cam = P.scene.camera;
-        const TrsF ctrs{V3{cam.t[0], cam.t[1], cam.t[2]}, Q4{cam.q[0], cam.q[1], cam.q[2], cam.q[3]}, V3{cam.s[0], cam.s[1], cam.s[2]}};
-        Col color{0.0f, 0.0f, 0.0f, 1.0f};
-        HitD primary;
-        primary.prim = 0xFFFFFFFFu;
-        const uint32_t pixel = y * P.width + x;
-        for (uint32_t i = 0; i < P.cfg.samples_per_pixel; ++i) {
-            float ix = (float)(i % P.strate_u);
-            float iy = (float)(i / P.strate_u);
-            float xx = (2.0f * (((float)x + ix * P.step + P.offset) * P.inv_w) - 1.0f) * cam.angle * P.aspect;
-            float yy = (1.0f - 2.0f * (((float)y + iy * P.step + P.offset) * P.inv_h)) * cam.angle;
-            V3 dir = normalize(V3{xx, yy, -1.0f});
-            // &camera_trs.trs * Ray::new(origin, dir): scale, rotate, translate (trs.rs:275-284); no re-normalise
-            V3 wd = rotate(dir * ctrs.s, ctrs.q);
-            V3 wo = rotate(scale_point(V3{0.0f, 0.0f, 0.0f}, ctrs.s), ctrs.q) + ctrs.t;
-            RayD ray = make_ray(wo, wd);
-            Col c{0.0f, 0.0f, 0.0f, 1.0f};
-            bool ok;
-            HitD ph;
-            ph.prim = 0xFFFFFFFFu;
-            ph.t = __int_as_float(0x7f800000);
-            ph.u = ph.v = 0.0f;
-            if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER) {
-                ok = pathtracer<MODE, COUNT>(P, ray, pixel, i, c, ph, pc);
-            } else if (INTEGRATOR == RAYCA_INTEGRATOR_RAYTRACER) {
-                ok = raytracer<MODE, COUNT>(P, ray, c, ph, pc);
-            } else { // Flat (integrator/flat.rs:16-28)
-                ok = trace_ray<MODE, false, COUNT>(P.scene, ray, ph, &pc.walk);
-                if (ok) {
-                    Surf sf;
-                    load_surf(P.scene, ray, ph, sf);
-                    c = surf_color(P.scene, sf);
-                }
+    if (PERSISTENT) {
+        // one atomic per warp per GROUP (4 tiles): same-address atomics retire at about one per L2 clock,
+        // so per-tile fetches (260k per 1080p frame) would cost more than the imbalance they remove
+        for (;;) {
+            unsigned long long t = 0;
+            if (lane == 0) t = atomicAdd(&P.counters[5], 1ull);
+            const uint32_t group = (uint32_t)__shfl_sync(0xFFFFFFFFu, t, 0);
+            if (group >= P.tile_count) break;
+            const uint32_t gx = group % P.groups_x, gy = group / P.groups_x;
+#pragma unroll 1
+            for (uint32_t sub = 0; sub < 4u; ++sub) {
+                const uint32_t x = gx * 16u + (sub & 1u) * 8u + (lane & 7u);
+                const uint32_t local_row = gy * 8u + (sub >> 1) * 4u + (lane >> 3);
+                render_pixel<INTEGRATOR, MODE, COUNT, BOUNCE>(P, x, local_row, pc);
             }
-            if (!ok) {
-                c = Col{0.0f, 0.0f, 0.0f, 1.0f}; // unwrap_or(Color::BLACK) (scene.rs:80-86)
-                if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER && P.cfg.max_depth == 0) ph.prim = 0xFFFFFFFFu;
-            }
-            primary = ph;
-            color = cadd(color, c);
         }
-        color = cdiv(color, (float)P.cfg.samples_per_pixel);
-        color.r = powf(color.r, P.inv_gamma); // correct_gamma (color/mod.rs:175-180)
-        color.g = powf(color.g, P.inv_gamma);
-        color.b = powf(color.b, P.inv_gamma);
-        const size_t o = (size_t)((P.shard_count > 1) ? local_row : y) * P.width + x;
-        uchar4 q = make_uchar4(quantize(color.r), quantize(color.g), quantize(color.b), quantize(color.a));
-        reinterpret_cast<uchar4*>(P.rgba8)[o] = q;
-        const bool hit = primary.prim != 0xFFFFFFFFu;
-        if (P.hit_prim || P.hit_blas || P.hit_src) {
-            uint32_t blas = 0xFFFFFFFFu, local = 0xFFFFFFFFu, src = 0xFFFFFFFFu;
-            if (hit) {
-                blas = 0;
-                while (blas + 1 < P.scene.blas_count && primary.prim >= P.scene.blas_prim_offset[blas + 1]) ++blas;
-                local = primary.prim - P.scene.blas_prim_offset[blas];
-                src = __float_as_uint(P.scene.tri_pos[3 * (size_t)primary.prim].w);
-            }
-            if (P.hit_blas) P.hit_blas[o] = blas;
-            if (P.hit_prim) P.hit_prim[o] = local;
-            if (P.hit_src) P.hit_src[o] = src;
-        }
-        if (P.depth) P.depth[o] = hit ? primary.t : __int_as_float(0x7f800000);
-        if (P.uv) {
-            P.uv[2 * o] = hit ? primary.u : 0.0f;
-            P.uv[2 * o + 1] = hit ? primary.v : 0.0f;
-        }
-        if (P.rgba_f32) reinterpret_cast<float4*>(P.rgba_f32)[o] = make_float4(color.r, color.g, color.b, color.a);
+    } else {
+        const uint32_t x = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
+        const uint32_t local_row = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+        render_pixel<INTEGRATOR, MODE, COUNT, BOUNCE>(P, x, local_row, pc);
     }
     // warp-aggregated counters: one atomic per warp per counter
     uint32_t sh = __reduce_add_sync(0xFFFFFFFFu, pc.shadow);
@@ -328,14 +390,16 @@ __global__ void __launch_bounds__(128) render_kernel(const __grid_constant__ Ren
         if (se) atomicAdd(&P.counters[1], (unsigned long long)se);
     }
     if (COUNT) {
-        unsigned long long n = pc.walk.nodes, t = pc.walk.tris;
+        unsigned long long n = pc.walk.nodes, t = pc.walk.tris, pl = pc.walk.planes;
         for (int ofs = 16; ofs > 0; ofs >>= 1) {
             n += __shfl_down_sync(0xFFFFFFFFu, n, ofs);
             t += __shfl_down_sync(0xFFFFFFFFu, t, ofs);
+            pl += __shfl_down_sync(0xFFFFFFFFu, pl, ofs);
         }
         if (lane == 0) {
             atomicAdd(&P.counters[2], n);
             atomicAdd(&P.counters[3], t);
+            atomicAdd(&P.counters[4], pl);
         }
     }
 }

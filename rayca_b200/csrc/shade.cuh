@@ -52,6 +52,10 @@ struct Surf {
     float uvx, uvy;
     Col geom_color;
     const GpuMaterial* mat;
+    // textured PBR lookups, evaluated once per hit by eval_material (the reference re-samples the same
+    // texels on every Material::get_* call; the values are identical)
+    Col pbr;                    // PbrMaterial::get_color
+    float metallic, roughness;  // PbrMaterial::get_metallic_roughness
 };
 
 __device__ __forceinline__ V3 interp3(float4 a0, float4 a1, float4 a2, float w, float u, float v) {
@@ -65,6 +69,22 @@ __device__ __forceinline__ Col pbr_color(const GpuSceneView& s, const GpuMateria
     return c;
 }
 
+// PbrMaterial::get_metallic_roughness (pbr.rs:125-136): metallic = B, roughness = R
+__device__ __forceinline__ void eval_material(const GpuSceneView& s, Surf& sf) {
+    const GpuMaterial* m = sf.mat;
+    if (m->kind != RAYCA_MATERIAL_PBR) return;
+    sf.pbr = pbr_color(s, m, sf.uvx, sf.uvy);
+    if (m->tex_mr >= 0) {
+        Col c = sample_image(s, m->tex_mr, sf.uvx, sf.uvy);
+        sf.metallic = c.b;
+        sf.roughness = c.r;
+    } else {
+        sf.metallic = m->p0;
+        sf.roughness = m->p1;
+    }
+}
+
+template <bool MATERIAL = true>
 __device__ __forceinline__ void load_surf(const GpuSceneView& s, const RayD& ray, const HitD& h, Surf& sf) {
     const float4* q = s.tri_attr + 12 * (size_t)h.prim;
     float u = h.u, v = h.v;
@@ -100,13 +120,14 @@ __device__ __forceinline__ void load_surf(const GpuSceneView& s, const RayD& ray
     }
     sf.normal = n;
     sf.next_origin = sf.point + n * kRayBias; // hit.rs:164-171
+    if (MATERIAL) eval_material(s, sf);
 }
 
 // Material::get_color (material/mod.rs:107-114) x geometry colour (primitive.rs:142-148)
 __device__ __forceinline__ Col surf_color(const GpuSceneView& s, const Surf& sf) {
     const GpuMaterial* m = sf.mat;
     Col mc;
-    if (m->kind == RAYCA_MATERIAL_PBR) mc = pbr_color(s, m, sf.uvx, sf.uvy);
+    if (m->kind == RAYCA_MATERIAL_PBR) mc = sf.pbr;
     else if (m->kind == RAYCA_MATERIAL_PHONG) mc = cadd(ld_col(m->a), ld_col(m->b)); // ambient + emission
     else mc = ld_col(m->a);
     return cmul(sf.geom_color, mc);
@@ -115,22 +136,14 @@ __device__ __forceinline__ Col surf_color(const GpuSceneView& s, const Surf& sf)
 __device__ __forceinline__ Col surf_diffuse(const GpuSceneView& s, const Surf& sf) {
     const GpuMaterial* m = sf.mat;
     Col mc;
-    if (m->kind == RAYCA_MATERIAL_PBR) mc = pbr_color(s, m, sf.uvx, sf.uvy);
+    if (m->kind == RAYCA_MATERIAL_PBR) mc = sf.pbr;
     else if (m->kind == RAYCA_MATERIAL_PHONG) mc = ld_col(m->c);
     else mc = ld_col(m->a);
     return cmul(sf.geom_color, mc);
 }
-// PbrMaterial::get_metallic_roughness (pbr.rs:125-136): metallic = B, roughness = R
 __device__ __forceinline__ void surf_metal_rough(const GpuSceneView& s, const Surf& sf, float& metallic, float& roughness) {
-    const GpuMaterial* m = sf.mat;
-    if (m->tex_mr >= 0) {
-        Col c = sample_image(s, m->tex_mr, sf.uvx, sf.uvy);
-        metallic = c.b;
-        roughness = c.r;
-    } else {
-        metallic = m->p0;
-        roughness = m->p1;
-    }
+    metallic = sf.metallic;
+    roughness = sf.roughness;
 }
 // Material::get_specular (material/mod.rs:143-152)
 __device__ __forceinline__ Col surf_specular(const GpuSceneView& s, const Surf& sf) {
@@ -138,7 +151,7 @@ __device__ __forceinline__ Col surf_specular(const GpuSceneView& s, const Surf& 
     if (m->kind == RAYCA_MATERIAL_PBR) {
         float metallic, roughness;
         surf_metal_rough(s, sf, metallic, roughness);
-        return cscale(pbr_color(s, m, sf.uvx, sf.uvy), metallic);
+        return cscale(sf.pbr, metallic);
     }
     return ld_col(m->d);
 }
@@ -154,12 +167,20 @@ __device__ __forceinline__ float surf_roughness(const GpuSceneView& s, const Sur
     return m->p0;
 }
 
+// powf(x, 2.0 / 4.0 / 5.0) of the reference (f32::powf -> libm) written as products: correctly rounded
+// squares, at most an ulp or two away from libm for the 4th / 5th power, i.e. inside the spread
+// libdevice's own powf has against glibc, and far inside the 1e-3 RGB tolerance.  Keeps ~1k instructions
+// of inlined powf out of the kernel (the i-cache is what this kernel starves on, see profiles/).
+__device__ __forceinline__ float pow2(float x) { return x * x; }
+__device__ __forceinline__ float pow4(float x) { float x2 = x * x; return x2 * x2; }
+__device__ __forceinline__ float pow5(float x) { float x2 = x * x; return (x2 * x2) * x; }
+
 // ---- brdf/ggx.rs:58-127 (path-tracer form)
 __device__ __forceinline__ float ggx_d(float a, V3 h, V3 n) {
     float a2 = a * a;
     float ct = clampf(dot(h, n), 0.0f, 1.0f);
     float theta = acosf(ct);
-    float den = powf(ct, 4.0f) * powf(a2 + powf(tanf(theta), 2.0f), 2.0f);
+    float den = pow4(ct) * pow2(a2 + pow2(tanf(theta)));
     if (den == 0.0f) return 0.0f;
     return a2 * kFrac1Pi / den;
 }
@@ -167,7 +188,7 @@ __device__ __forceinline__ float ggx_g1(float a, V3 omega, V3 n) {
     float ct = dot(omega, n);
     if (ct <= 0.0f) return 0.0f;
     float theta = acosf(ct);
-    float den = 1.0f + sqrtf(1.0f + a * a * powf(tanf(theta), 2.0f));
+    float den = 1.0f + sqrtf(1.0f + a * a * pow2(tanf(theta)));
     return 2.0f / den;
 }
 __device__ __forceinline__ Col ggx_bsdf(const GpuSceneView& s, const Surf& sf, V3 wi) {
@@ -182,7 +203,7 @@ __device__ __forceinline__ Col ggx_bsdf(const GpuSceneView& s, const Surf& sf, V
     V3 h = normalize(wi + wo);
     // get_f: ks + (WHITE - ks) * (1 - |wi.h|)^5
     float idh = fabsf(dot(wi, h));
-    Col f = cadd(ks, cscale(csub(Col{1.0f, 1.0f, 1.0f, 1.0f}, ks), powf(1.0f - idh, 5.0f)));
+    Col f = cadd(ks, cscale(csub(Col{1.0f, 1.0f, 1.0f, 1.0f}, ks), pow5(1.0f - idh)));
     float g = ggx_g1(a, wi, n) * ggx_g1(a, wo, n);
     float d = ggx_d(a, h, n);
     float den = 4.0f * idn * odn;
@@ -228,7 +249,7 @@ __device__ __forceinline__ Col surf_radiance(const GpuSceneView& s, const Surf& 
     float d = k * k * kFrac1Pi;
     Col albedo = surf_color(s, sf);
     V3 f0 = V3{0.04f, 0.04f, 0.04f} * (1.0f - metallic) + col_to_v3(albedo) * metallic;
-    float fp = powf(1.0f - ldh, 5.0f);
+    float fp = pow5(1.0f - ldh);
     V3 f = f0 + (V3{1.0f, 1.0f, 1.0f} - f0) * fp;
     V3 kd = (V3{1.0f, 1.0f, 1.0f} - f) * (1.0f - metallic);
     float ggxv = ndl * (ndv * (1.0f - roughness) + roughness);

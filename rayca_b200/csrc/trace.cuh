@@ -36,8 +36,9 @@ struct HitD {
 };
 
 struct WalkCounters {
-    unsigned long long nodes = 0; // 32 B node records fetched
-    unsigned long long tris = 0;  // 48 B triangle records fetched
+    unsigned long long nodes = 0;  // 32 B node records fetched
+    unsigned long long tris = 0;   // 48 B: three vertex quads of a triangle record fetched
+    unsigned long long planes = 0; // 16 B: plane quad of a performance-layer triangle record fetched
 };
 
 // AABB::intersects (bvh/aabb.rs:74-93); returns tmin or f32::MAX
@@ -101,7 +102,7 @@ __device__ __forceinline__ bool walk(const GpuSceneView& s, const RayD& ray, Hit
             if (tri_test(a, b, c, ray, t, u, v, p)) {
                 if (ANY) {
                     if (t < best_t) return true;
-                } else if (t < best_t || (t == best_t && i < best)) {
+                } else if (t < best_t || (t == best_t && i < best && best != 0xFFFFFFFFu)) {
                     best_t = t;
                     best = i;
                     bu = u;
@@ -191,141 +192,211 @@ __device__ __forceinline__ bool walk(const GpuSceneView& s, const RayD& ray, Hit
 
 // ---------------------------------------------------------------------------------------------
 // Performance-layer walk (fast_bvh.cpp).  Same result as walk<> by construction:
-//   * the slab test here is CONSERVATIVE: it accepts whenever the exact test would, plus a relative
-//     tolerance in t, so rounding can never hide a triangle the reference would reach;
-//   * a candidate hit only counts if the exact slab test of its REFERENCE leaf box (nodes[w1]) accepts
-//     the ray — that is precisely the condition under which the reference tests the triangle;
-//   * ties on depth resolve to the lowest reference-global index (w0), like depth-first order does.
+//   * the slab test here is CONSERVATIVE (see FastRay), so rounding cannot hide a triangle the
+//     reference would reach;
+//   * a candidate hit only counts if the exact slab test of its REFERENCE leaf box (nodes[leaf])
+//     accepts the ray — that is precisely the condition under which the reference tests the triangle;
+//   * ties on depth resolve to the lowest reference-global index, like depth-first order does;
+//   * the triangle test performs the reference's operations on the reference's operands: the plane
+//     (n, d) and dot(n,n) of the 64-byte record are precomputed on the host with the very same f32
+//     operation order (rmath.h), so every accepted (t, u, v) is bit-identical.  The test is only
+//     REORDERED: plane distance first (16 bytes), then `t > best` rejects before the edge functions
+//     — a hit with t > best would be discarded anyway.
+//
+// Instruction budget (this loop is issue-bound, profiles/): per box 6 SEL + 6 FFMA + 2 FMNMX3 + 2 FFMA.
+//   exact      t  = RN(RN(p - o) * rd)                         (aabb.rs:76-80)
+//   here       t' = RN(fma(p, rd, a)),  a = RN(-o*rd) -/+ e,   e = 2^-22 |o*rd| per axis
+//   |t - t'| <= u|o*rd| + 3u|t| with u = 2^-24; e = 4u|o*rd| covers the first term (and the rounding of
+//   a itself), folded into the addend of the near (-e) and far (+e) plane; the second term and the
+//   triangle-test-vs-box rounding for grazing rays are covered by widening the resulting interval by
+//   1e-5 relative (fma(|t|, -/+1e-5, t)).  Near/far planes are picked per axis by the sign of rd, so no
+//   min/max per axis is needed.  NaNs (0 * inf for a denormal direction lane) are dropped by
+//   fminf/fmaxf, which only ever widens the interval.
 constexpr float kSlabTol = 1.0e-5f;
+constexpr uint32_t kLeafFlag = 0x80000000u; // child reference: bit31 leaf, bits 28..30 count-1, bits 0..27 first
 
-__device__ __forceinline__ bool slab_conservative(const float4 lo, const float4 hi, const RayD& r, float& entry) {
-    float t1x = (lo.x - r.o.x) * r.rd.x, t2x = (hi.x - r.o.x) * r.rd.x;
-    float t1y = (lo.y - r.o.y) * r.rd.y, t2y = (hi.y - r.o.y) * r.rd.y;
-    float t1z = (lo.z - r.o.z) * r.rd.z, t2z = (hi.z - r.o.z) * r.rd.z;
-    float tmax = fminf(fminf(fmaxf(t1x, t2x), fmaxf(t1y, t2y)), fmaxf(t1z, t2z));
-    float tmin = fmaxf(fmaxf(fminf(t1x, t2x), fminf(t1y, t2y)), fminf(t1z, t2z));
-    float tol = kSlabTol * fmaxf(fabsf(tmin), fabsf(tmax));
-    entry = tmin - tol;
-    return (tmax + tol >= tmin) && (tmax + tol >= 0.0f);
+struct FastRay {
+    float rdx, rdy, rdz;
+    float anx, any, anz; // near-plane addend  RN(-o*rd) - e
+    float afx, afy, afz; // far-plane addend   RN(-o*rd) + e
+    bool sx, sy, sz;     // rd < 0: the near plane is the box maximum
+};
+
+__device__ __forceinline__ FastRay make_fast_ray(const RayD& r) {
+    FastRay f;
+    f.rdx = r.rd.x; f.rdy = r.rd.y; f.rdz = r.rd.z;
+    const float nx = -(r.o.x * r.rd.x), ny = -(r.o.y * r.rd.y), nz = -(r.o.z * r.rd.z);
+    const float ex = fabsf(nx) * 2.384185791015625e-07f, ey = fabsf(ny) * 2.384185791015625e-07f,
+                ez = fabsf(nz) * 2.384185791015625e-07f; // 2^-22
+    f.anx = nx - ex; f.any = ny - ey; f.anz = nz - ez;
+    f.afx = nx + ex; f.afy = ny + ey; f.afz = nz + ez;
+    f.sx = r.rd.x < 0.0f; f.sy = r.rd.y < 0.0f; f.sz = r.rd.z < 0.0f;
+    return f;
 }
 
-template <bool ANY, bool COUNT>
-__device__ __forceinline__ bool walk_fast(const GpuSceneView& s, const RayD& ray, HitD& hit, WalkCounters* wc) {
+// returns "may intersect"; entry <= the exact slab entry distance of the same box
+__device__ __forceinline__ bool slab_fast(const float4 lo, const float4 hi, const FastRay& f, float& entry) {
+    const float tn = fmaxf(fmaxf(__fmaf_rn(f.sx ? hi.x : lo.x, f.rdx, f.anx), __fmaf_rn(f.sy ? hi.y : lo.y, f.rdy, f.any)),
+                           __fmaf_rn(f.sz ? hi.z : lo.z, f.rdz, f.anz));
+    const float tf = fminf(fminf(__fmaf_rn(f.sx ? lo.x : hi.x, f.rdx, f.afx), __fmaf_rn(f.sy ? lo.y : hi.y, f.rdy, f.afy)),
+                           __fmaf_rn(f.sz ? lo.z : hi.z, f.rdz, f.afz));
+    entry = __fmaf_rn(fabsf(tn), -kSlabTol, tn);
+    const float ext = __fmaf_rn(fabsf(tf), kSlabTol, tf);
+    return ext >= entry && ext >= 0.0f;
+}
+
+template <bool COUNT>
+__device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD& ray, HitD& hit, WalkCounters* wc, const bool ANY) {
+    const V3 o = ray.o, d = ray.d;
     float best_t = ANY ? hit.t : __int_as_float(0x7f800000);
     uint32_t best = 0xFFFFFFFFu;
-    float bu = 0.0f, bv = 0.0f;
-    V3 bp{0.0f, 0.0f, 0.0f};
+    float bu = 0.0f, bv = 0.0f, bden = 1.0f;
     uint32_t ok_leaf = 0xFFFFFFFFu; // last reference leaf whose exact slab test accepted this ray
+
+    auto finish = [&]() -> bool {
+        if (ANY) return false;
+        hit.t = best_t;
+        hit.prim = best;
+        hit.u = bu / bden; // uv = (u / |n|^2, v / |n|^2) (triangle.rs:152-153)
+        hit.v = bv / bden;
+        hit.p = o + d * best_t; // Hit::point, the `p` of the winning test (triangle.rs:121)
+        return best != 0xFFFFFFFFu;
+    };
+    // A ray with an exactly-zero direction lane has rdir = 0 there (vec3.rs:195-216): both slab
+    // distances of that axis are 0, tmax <= 0, and `tmax > 0.0` (aabb.rs:88) rejects EVERY box, the
+    // TLAS root included — the reference returns a miss for such rays (SURVEY A-3).
+    if (ray.rd.x == 0.0f || ray.rd.y == 0.0f || ray.rd.z == 0.0f) return finish();
+
+    const float4* __restrict__ fast_nodes = s.fast_nodes;
+    const float4* __restrict__ fast_tri = s.fast_tri;
+    const float4* __restrict__ ref_nodes = s.nodes;
+    const FastRay fr = make_fast_ray(ray);
 
     auto ref_leaf_accepts = [&](uint32_t leaf) -> bool {
         if (leaf == ok_leaf) return true;
-        const float4 lo = __ldg(&s.nodes[2 * (size_t)leaf]);
-        const float4 hi = __ldg(&s.nodes[2 * (size_t)leaf + 1]);
+        const float4 lo = __ldg(&ref_nodes[2 * (size_t)leaf]);
+        const float4 hi = __ldg(&ref_nodes[2 * (size_t)leaf + 1]);
         if (COUNT) wc->nodes += 1;
         if (slab(lo, hi, ray) == kF32Max) return false;
         ok_leaf = leaf;
         return true;
     };
-    auto leaf = [&](uint32_t first, uint32_t count) -> bool {
-        if (COUNT) wc->tris += count;
-        for (uint32_t i = first; i < first + count; ++i) {
-            const float4 a = __ldg(&s.fast_tri[3 * (size_t)i + 0]);
-            const float4 b = __ldg(&s.fast_tri[3 * (size_t)i + 1]);
-            const float4 c = __ldg(&s.fast_tri[3 * (size_t)i + 2]);
-            float t, u, v;
-            V3 p;
-            if (tri_test(a, b, c, ray, t, u, v, p)) {
-                const uint32_t ref = __float_as_uint(a.w);
-                if (ANY) {
-                    if (t < best_t && ref_leaf_accepts(__float_as_uint(b.w))) return true;
-                } else if (t < best_t || (t == best_t && ref < best)) {
-                    if (ref_leaf_accepts(__float_as_uint(b.w))) {
-                        best_t = t;
-                        best = ref;
-                        bu = u;
-                        bv = v;
-                        bp = p;
-                    }
-                }
-            }
-        }
-        return false;
-    };
-    auto finish = [&]() -> bool {
-        if (ANY) return false;
-        hit.t = best_t;
-        hit.prim = best;
-        hit.u = bu;
-        hit.v = bv;
-        hit.p = bp;
-        return best != 0xFFFFFFFFu;
-    };
-
     {
         if (COUNT) wc->nodes += 1;
         float4 lo = make_float4(s.fast_root_min[0], s.fast_root_min[1], s.fast_root_min[2], 0.0f);
         float4 hi = make_float4(s.fast_root_max[0], s.fast_root_max[1], s.fast_root_max[2], 0.0f);
         float e;
-        if (!slab_conservative(lo, hi, ray, e)) return finish();
-        if (s.fast_root_link1 != 0) {
-            if (leaf(s.fast_root_link0, s.fast_root_link1)) return true;
-            return finish();
-        }
+        if (!slab_fast(lo, hi, fr, e)) return finish();
     }
-    uint32_t stack_i[kStackSize];
-    float stack_d[kStackSize];
+    uint2 stack[kStackSize]; // {child reference, entry distance}
     int sp = 0;
-    uint32_t cur = s.fast_root_link0;
+    uint32_t cur = s.fast_root_ref;
     for (;;) {
-        const float4* np = s.fast_nodes + 2 * (size_t)cur;
-        float4 a0 = __ldg(np + 0), a1 = __ldg(np + 1), b0 = __ldg(np + 2), b1 = __ldg(np + 3);
-        if (COUNT) wc->nodes += 2;
-        float d0, d1;
-        bool h0 = slab_conservative(a0, a1, ray, d0);
-        bool h1 = slab_conservative(b0, b1, ray, d1);
-        h0 = h0 && !(d0 > best_t);
-        h1 = h1 && !(d1 > best_t);
-        uint32_t l0 = __float_as_uint(a0.w), c0 = __float_as_uint(a1.w);
-        uint32_t l1 = __float_as_uint(b0.w), c1 = __float_as_uint(b1.w);
-        if (h0 && h1 && d1 < d0) {
-            float td = d0; d0 = d1; d1 = td;
-            uint32_t tl = l0; l0 = l1; l1 = tl;
-            uint32_t tc = c0; c0 = c1; c1 = tc;
-        }
-        if (h0 && c0 != 0) {
-            if (leaf(l0, c0)) return true;
-            h0 = false;
-            if (h1 && d1 > best_t) h1 = false;
-        }
-        if (h1 && c1 != 0) {
-            if (leaf(l1, c1)) return true;
-            h1 = false;
-        }
-        if (h0) {
-            cur = l0;
-            if (h1 && sp < kStackSize) {
-                stack_i[sp] = l1;
-                stack_d[sp] = d1;
-                ++sp;
+        // inner nodes: descend to the nearer accepted child, push the farther one
+        while (!(cur & kLeafFlag)) {
+            const float4* np = fast_nodes + 2 * (size_t)cur;
+            const float4 a0 = __ldg(np + 0), a1 = __ldg(np + 1), b0 = __ldg(np + 2), b1 = __ldg(np + 3);
+            if (COUNT) wc->nodes += 2;
+            float d0, d1;
+            bool h0 = slab_fast(a0, a1, fr, d0);
+            bool h1 = slab_fast(b0, b1, fr, d1);
+            h0 = h0 && !(d0 > best_t);
+            h1 = h1 && !(d1 > best_t);
+            uint32_t c0 = __float_as_uint(a0.w), c1 = __float_as_uint(b0.w);
+            if (h0 && h1) {
+                if (d1 < d0) {
+                    float td = d0; d0 = d1; d1 = td;
+                    uint32_t tc = c0; c0 = c1; c1 = tc;
+                }
+                cur = c0;
+                if (sp < kStackSize) stack[sp++] = make_uint2(c1, __float_as_uint(d1));
+            } else if (h0) {
+                cur = c0;
+            } else if (h1) {
+                cur = c1;
+            } else {
+                bool popped = false;
+                while (sp > 0) {
+                    const uint2 e = stack[--sp];
+                    if (__uint_as_float(e.y) > best_t) continue;
+                    cur = e.x;
+                    popped = true;
+                    break;
+                }
+                if (!popped) return finish();
             }
-            continue;
         }
-        if (h1) {
-            cur = l1;
-            continue;
+        // leaf: Triangle::intersects (rayca-geometry/src/triangle.rs:84-159) on the 64-byte records
+        // {n.xyz, d | v0, ref index | v1, ref leaf | v2, dot(n,n)}
+        {
+            const uint32_t first = cur & 0x0FFFFFFFu, count = ((cur >> 28) & 7u) + 1u;
+            for (uint32_t i = first; i < first + count; ++i) {
+                const float4* q = fast_tri + 4 * (size_t)i;
+                const float4 q0 = __ldg(q);
+                if (COUNT) wc->planes += 1;
+                const V3 n{q0.x, q0.y, q0.z};
+                const float ndd = dot(d, n);
+                if (ndd > 0.0f) continue;             // back face (:96)
+                if (fabsf(ndd) < kF32Eps) continue;   // parallel (:106)
+                const float t = -(dot(n, o) + q0.w) / ndd;
+                if (t < 0.0f) continue;               // behind (:117)
+                if (ANY ? !(t < best_t) : (t > best_t)) continue; // cannot win: skip the edge functions
+                const float4 q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+                if (COUNT) wc->tris += 1;
+                const V3 v0{q1.x, q1.y, q1.z}, v1{q2.x, q2.y, q2.z}, v2{q3.x, q3.y, q3.z};
+                const V3 p = o + d * t;
+                V3 cc = cross(v1 - v0, p - v0);
+                if (dot(n, cc) < 0.0f) continue;
+                cc = cross(v2 - v1, p - v1);
+                const float u = dot(n, cc);
+                if (u < 0.0f) continue;
+                cc = cross(v0 - v2, p - v2);
+                const float v = dot(n, cc);
+                if (v < 0.0f) continue;
+                const uint32_t id = __float_as_uint(q1.w);
+                if (ANY) {
+                    if (ref_leaf_accepts(__float_as_uint(q2.w))) return true;
+                } else if (t < best_t || (id < best && best != 0xFFFFFFFFu)) { // here t <= best_t
+                    if (ref_leaf_accepts(__float_as_uint(q2.w))) {
+                        best_t = t;
+                        best = id;
+                        bu = u;
+                        bv = v;
+                        bden = q3.w;
+                    }
+                }
+            }
         }
         bool popped = false;
         while (sp > 0) {
-            --sp;
-            if (stack_d[sp] > best_t) continue;
-            cur = stack_i[sp];
+            const uint2 e = stack[--sp];
+            if (__uint_as_float(e.y) > best_t) continue;
+            cur = e.x;
             popped = true;
             break;
         }
-        if (!popped) break;
+        if (!popped) return finish();
     }
-    return finish();
 }
+
+// One shared copy of the walk serves closest-hit and any-hit queries of every call site: the kernel
+// starves on instruction fetch when the walk is inlined two or three times (measured 1.9 ms -> 1.25 ms
+// for the 1080p atrium frame, profiles/).  RAYCA_INLINE_WALK restores the inlined form for A/B runs.
+#ifndef RAYCA_INLINE_WALK
+template <bool COUNT>
+__device__ __noinline__ bool walk_fast_shared(const GpuSceneView& s, const RayD& ray, HitD& hit, WalkCounters* wc, bool any) {
+    return walk_fast_body<COUNT>(s, ray, hit, wc, any);
+}
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool walk_fast(const GpuSceneView& s, const RayD& ray, HitD& hit, WalkCounters* wc) {
+    return walk_fast_shared<COUNT>(s, ray, hit, wc, ANY);
+}
+#else
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool walk_fast(const GpuSceneView& s, const RayD& ray, HitD& hit, WalkCounters* wc) {
+    return walk_fast_body<COUNT>(s, ray, hit, wc, ANY);
+}
+#endif
 
 // MODE 0: performance layer (product path); 1: reference tree, exhaustive, reference visiting rule;
 // 2: reference tree, ordered + distance-culled ("flattened reference BVH").

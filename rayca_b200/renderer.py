@@ -22,7 +22,8 @@ import numpy as np
 from . import model as M
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librayca_cuda.so")
+# RAYCA_CUDA_LIB selects a tuning variant of the same library (kernel experiments); never a fallback
+LIB_PATH = os.environ.get("RAYCA_CUDA_LIB") or os.path.join(_HERE, "librayca_cuda.so")
 
 
 class IntegratorStrategy(enum.IntEnum):
@@ -45,6 +46,7 @@ class SamplerStrategy(enum.IntEnum):
 
 TRAVERSAL_ORDERED, TRAVERSAL_EXHAUSTIVE, TRAVERSAL_REFERENCE_ORDERED = 0, 1, 2
 FLAG_COUNT_WALK = 1
+FLAG_PERSISTENT = 2
 
 _ERRORS = {-1: "RAYCA_E_INVALID_ARG", -2: "RAYCA_E_UNSUPPORTED", -3: "RAYCA_E_OOM", -4: "RAYCA_E_CUDA",
            -5: "RAYCA_E_NO_CAMERA"}
