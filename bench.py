@@ -152,7 +152,7 @@ def run_reference(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / max(args.steps, 1),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": what, "width": args.width, "height": args.height, "spp": args.spp,
-                       "triangles": desc.triangle_count, "integrator": "Pathtracer max_depth=1 (NEE point lights)"},
+                       "triangles": desc.triangle_count, "integrator": f"Pathtracer max_depth={args.max_depth} (NEE point lights" + (", cosine bounce, Philox keyed RNG)" if args.max_depth > 1 else ")")},
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "port",
                              "sample": f"{rows} evenly spaced rows of the {args.width}x{args.height} frame per step, "
                                        "pixel loop only (BVH build excluded), reference-faithful mode"},
@@ -213,6 +213,7 @@ def run_ours(args):
     # ray counts of one frame (deterministic): this rank's share, summed over ranks
     st = dev.last_counters()
     rays_local = torch.tensor([st.rays_primary, st.rays_shadow, st.rays_secondary], dtype=torch.int64, device="cuda")
+    rays_local_n = st.rays_primary + st.rays_shadow + st.rays_secondary
     if G > 1:
         dist.all_reduce(rays_local)
     rays_frame = int(rays_local.sum().item())
@@ -250,22 +251,52 @@ def run_ours(args):
     total_ms = float(t.item())
     value = rays_frame * args.steps / (total_ms * 1e-3) / 1e6
 
-    # e2e through the host-buffer entry point (single GPU path of the C ABI; N>1: each rank its shard)
-    e2e = None
+    # e2e: the frame lands in (pinned) HOST memory inside the timed region, every step.
+    #   N == 1: rayca_cuda_render, the reference-facing entry point (row bands traced on one stream and
+    #           read back on another);
+    #   N  > 1: each rank traces its tiles, NCCL all_gather, rank 0 copies the gathered frame to the host.
+    # Wall clock between barriers, max over ranks.  Per-step host->device input = the kernel parameter
+    # block (camera, config, pointers); the scene was uploaded once by scene_create, which the
+    # reference's own timer excludes too (scene.rs:101,152).
+    param_bytes = 1024
+    n_e2e = max(3, args.steps)
     draw_e2e = None
     if G == 1:
-        for _ in range(2):
-            dev.render(cfg, W, H)
+        img = R.Image(W, H, pinned=True)
+        for _ in range(3):
+            dev.render(cfg, W, H, out=img.buffer, options=opts)
         torch.cuda.synchronize()
         t1 = time.perf_counter()
-        n_e2e = max(3, min(args.steps, 10))
         for _ in range(n_e2e):
-            dev.render(cfg, W, H)
+            dev.render(cfg, W, H, out=img.buffer, options=opts)
         e2e_s = (time.perf_counter() - t1) / n_e2e
-        e2e = {"value": rays_frame / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 1024,
-               "d2h_bytes_per_step": W * H * 4, "ms_per_step": e2e_s * 1e3,
-               "what": "rayca_cuda_render: host RGBA8 out, scene resident (scene_create excluded, like the reference timer)"}
-        draw_e2e = {"ms": None}
+        d2h = W * H * 4
+        e2e_what = "rayca_cuda_render: pinned host RGBA8 out, scene resident (scene_create excluded, like the reference timer)"
+    else:
+        host = torch.empty((G, local_rows, W, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
+
+        def e2e_step():
+            dev.render_device(cfg, W, H, local.data_ptr(), stream=stream, options=opts)
+            dist.all_gather_into_tensor(gathered, local)
+            if rank == 0:
+                host.copy_(gathered, non_blocking=True)
+
+        for _ in range(3):
+            e2e_step()
+        barrier()
+        t1 = time.perf_counter()
+        for _ in range(n_e2e):
+            e2e_step()
+            torch.cuda.synchronize()  # the frame must be on the host before the next one starts
+        barrier()
+        e2e_t = torch.tensor([(time.perf_counter() - t1) / n_e2e], dtype=torch.float64, device="cuda")
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+        e2e_s = float(e2e_t.item())
+        d2h = G * local_rows * W * 4
+        e2e_what = "render_device on every rank + NCCL all_gather + rank-0 copy of the frame to pinned host memory"
+    e2e = {"value": rays_frame / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": param_bytes,
+           "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "what": e2e_what}
+    if G == 1:
         img = R.Image(W, H)
         rnd = R.CudaRenderer.__new__(R.CudaRenderer)
         rnd.config, rnd._ctx = cfg, ctx
@@ -285,7 +316,7 @@ def run_ours(args):
                 "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": what, "width": W, "height": H, "spp": args.spp,
-                           "triangles": desc.triangle_count, "integrator": "Pathtracer max_depth=1 (NEE point lights)",
+                           "triangles": desc.triangle_count, "integrator": f"Pathtracer max_depth={args.max_depth} (NEE point lights" + (", cosine bounce, Philox keyed RNG)" if args.max_depth > 1 else ")"),
                            "parallelism": f"image row-tiles of {tile} rows interleaved over {G} GPU(s), scene replicated, NCCL all_gather of RGBA8",
                            "l2": "flushed between timed iterations (256 MiB fill)", "traversal": args.traversal},
                 "rays_per_frame": rays_frame, "kernel_ms": kernel_ms, "build_s": build_s,
@@ -293,10 +324,14 @@ def run_ours(args):
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": None, "peak_source": "measured" if peaks else "fallback",
                              "algorithmic_bytes_per_launch": int(algo_bytes),
-                             "note": "working set is L2-resident; bytes = 32 B/node record + 48 B/triangle record fetched by the walk + 4 B/pixel"},
-                "e2e": e2e if e2e else {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 1024,
-                                        "d2h_bytes_per_step": 0, "what": "N>1: device-timed (frame stays on the GPUs)"},
-                "draw_e2e": draw_e2e}
+                             "note": "algorithmic bytes = 32 B per node record + 16 B per triangle plane + 48 B per triangle whose "
+                                     "vertices are fetched (counted by the kernel in a COUNT launch) + 4 B per pixel; the "
+                                     "262k-triangle scene is L2/L1-resident, so this can exceed the HBM peak: the kernel is "
+                                     "issue-bound, see profiles/"},
+                "e2e": e2e, "draw_e2e": draw_e2e,
+                "walk": {"node_records_per_ray": cst.node_bytes / 32 / max(rays_local_n, 1),
+                         "triangle_bytes_per_ray": cst.triangle_bytes / max(rays_local_n, 1),
+                         "algorithmic_bytes_per_ray": algo_bytes / max(rays_local_n, 1)}}
         if not args.no_cpu_baseline and G == 1:
             rows = args.cpu_rows or 2
             r, m, th = cpu_baseline(desc, cfg, args, rows)

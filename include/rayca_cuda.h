@@ -331,6 +331,12 @@ typedef struct rayca_scene rayca_scene;
 
 /* ------------------------------------------------------------- entry points */
 
+/* Pinned (page-locked) host memory for `rgba8_out`: with it rayca_cuda_render overlaps the read-back of
+ * finished row bands with the tracing of the next ones.  The Rust shim allocates Image buffers that it
+ * owns through this pair; any other host pointer works too, only without the overlap. */
+int rayca_cuda_host_alloc(size_t bytes, void** out);
+void rayca_cuda_host_free(void* p);
+
 /* Binds a context to one CUDA device (one process per GPU). */
 int rayca_cuda_init(int device, rayca_ctx** out);
 void rayca_cuda_shutdown(rayca_ctx* ctx);

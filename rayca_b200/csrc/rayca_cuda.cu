@@ -43,9 +43,12 @@ struct rayca_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     rayca_stats last{};
     uint64_t last_primary = 0;
-    // scratch for the host-buffer entry point
+    // scratch for the host-buffer entry point: device planes, a side stream for the read-back, and
+    // one event per row band (kernel done -> copy may start)
     void* d_scratch = nullptr;
     size_t scratch_bytes = 0;
+    cudaStream_t render_stream = nullptr, copy_stream = nullptr;
+    cudaEvent_t band_done[8] = {};
 };
 
 struct rayca_scene {
@@ -191,6 +194,9 @@ int rayca_cuda_init(int device, rayca_ctx** out) {
     CUDA_TRY(cudaMemset(c->d_counters, 0, kCounterSlots * sizeof(unsigned long long)));
     CUDA_TRY(cudaEventCreate(&c->ev0));
     CUDA_TRY(cudaEventCreate(&c->ev1));
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->render_stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    for (cudaEvent_t& e : c->band_done) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     *out = c;
     return RAYCA_OK;
 }
@@ -202,6 +208,10 @@ void rayca_cuda_shutdown(rayca_ctx* c) {
     cudaFree(c->d_scratch);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->render_stream) cudaStreamDestroy(c->render_stream);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    for (cudaEvent_t e : c->band_done)
+        if (e) cudaEventDestroy(e);
     delete c;
 }
 
@@ -310,9 +320,33 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     return RAYCA_OK;
 }
 
+} // extern "C"
+
+namespace {
+// One launch over image rows [row_begin, row_end) (unsharded) or over this shard's tiles.  `first`
+// resets the counters and records the start event, `last` records the end event, so that a frame
+// rendered as several row bands still reports one kernel time and one set of ray counts.
+struct Band {
+    uint32_t row_begin, row_end;
+    bool first, last;
+};
+int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options, uint32_t width,
+                   uint32_t height, void* d_rgba8, const rayca_aux_out* d_aux, cudaStream_t st, const Band* band, rayca_stats* stats);
+} // namespace
+
+extern "C" {
+
 int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options,
                              uint32_t width, uint32_t height, void* d_rgba8, const rayca_aux_out* d_aux, void* cuda_stream,
                              rayca_stats* stats) {
+    return enqueue_render(ctx, scene, config, options, width, height, d_rgba8, d_aux, (cudaStream_t)cuda_stream, nullptr, stats);
+}
+
+} // extern "C"
+
+namespace {
+int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options, uint32_t width,
+                   uint32_t height, void* d_rgba8, const rayca_aux_out* d_aux, cudaStream_t st, const Band* band, rayca_stats* stats) {
     if (!ctx || !scene || !config || !d_rgba8 || width == 0 || height == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
     if (scene->ctx != ctx) return fail(RAYCA_E_INVALID_ARG, "scene belongs to another context (or is host-only)");
     if (!scene->host.has_camera) return fail(RAYCA_E_NO_CAMERA, "no camera node in the scene");
@@ -320,7 +354,6 @@ int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_con
     int rc = validate_config(*config, *scene);
     if (rc != RAYCA_OK) return rc;
     CUDA_TRY(cudaSetDevice(ctx->device));
-    cudaStream_t st = (cudaStream_t)cuda_stream;
 
     RenderParams P{};
     P.scene = scene->view;
@@ -340,6 +373,16 @@ int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_con
         rows = per * P.tile_rows;
     }
     P.local_rows = rows;
+    P.row_begin = 0;
+    P.row_end = height;
+    if (band) {
+        if (P.shard_count > 1 || band->row_begin % 8 != 0 || band->row_begin >= band->row_end || band->row_end > height)
+            return fail(RAYCA_E_INVALID_ARG, "bad row band");
+        P.row_begin = band->row_begin;
+        P.row_end = band->row_end;
+        rows = band->row_end - band->row_begin;
+    }
+    const bool first = !band || band->first, last = !band || band->last;
     float fw = (float)width, fh = (float)height;
     P.inv_w = 1.0f / fw;
     P.inv_h = 1.0f / fh;
@@ -362,13 +405,14 @@ int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_con
     const uint32_t mode = options ? options->traversal : (uint32_t)RAYCA_TRAVERSAL_ORDERED;
     if (mode > RAYCA_TRAVERSAL_REFERENCE_ORDERED) return fail(RAYCA_E_INVALID_ARG, "unknown traversal mode");
     const bool count = options && (options->flags & RAYCA_FLAG_COUNT_WALK); // opt-in: walk counters cost registers
-
     const bool persistent = options && (options->flags & RAYCA_FLAG_PERSISTENT);
-    CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, kCounterSlots * sizeof(unsigned long long), st));
+
+    if (first) CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, kCounterSlots * sizeof(unsigned long long), st));
+    else if (persistent) CUDA_TRY(cudaMemsetAsync(ctx->d_counters + 5, 0, sizeof(unsigned long long), st)); // next-group counter
     dim3 grid((width + 15) / 16, (rows + 7) / 8);
     P.groups_x = grid.x;
     P.tile_count = grid.x * grid.y;
-    CUDA_TRY(cudaEventRecord(ctx->ev0, st));
+    if (first) CUDA_TRY(cudaEventRecord(ctx->ev0, st));
     LaunchSel sel{mode, count, persistent, false, ctx->sm_count};
     if (config->integrator == RAYCA_INTEGRATOR_PATHTRACER) // an indirect ray needs depth < limit (pathtracer.rs:94)
         sel.bounce = config->max_depth > (config->direct_sampler == RAYCA_SAMPLER_NEE ? 1u : 0u);
@@ -378,7 +422,7 @@ int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_con
         default: launch_integrator<RAYCA_INTEGRATOR_FLAT>(P, grid, sel, st); break;
     }
     CUDA_TRY(cudaGetLastError());
-    CUDA_TRY(cudaEventRecord(ctx->ev1, st));
+    if (last) CUDA_TRY(cudaEventRecord(ctx->ev1, st));
     // primary rays of this shard: pixels it owns x spp
     uint64_t own_rows = 0;
     if (P.shard_count > 1) {
@@ -397,6 +441,19 @@ int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_con
         stats->rays_primary = ctx->last_primary;
     }
     return RAYCA_OK;
+}
+} // namespace
+
+extern "C" {
+
+int rayca_cuda_host_alloc(size_t bytes, void** out) {
+    if (!out || bytes == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
+    CUDA_TRY(cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+    return RAYCA_OK;
+}
+
+void rayca_cuda_host_free(void* p) {
+    if (p) cudaFreeHost(p);
 }
 
 int rayca_cuda_last_counters(rayca_ctx* ctx, rayca_stats* stats) {
@@ -449,11 +506,35 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
         p += al(n * 8);
         if (aux->rgba_f32) d.rgba_f32 = (float*)p;
     }
+    // Row bands: the kernel of band k+1 runs while band k is copied to the host on the side stream, so
+    // the PCIe read-back of the frame hides behind the trace instead of following it.  A caller buffer
+    // from rayca_cuda_host_alloc (pinned) makes the copies truly asynchronous; pageable memory still
+    // works (the runtime stages it) but serialises the copies on the calling thread.
     rayca_stats local{};
-    int rc = rayca_cuda_render_device(ctx, scene, config, options, width, height, base, aux ? &d : nullptr, nullptr, &local);
-    if (rc != RAYCA_OK) return rc;
+    const uint32_t nb_max = (uint32_t)(sizeof(ctx->band_done) / sizeof(ctx->band_done[0]));
+    uint32_t nb = height >= 512 ? 4 : (height >= 128 ? 2 : 1);
+    if (nb > nb_max) nb = nb_max;
+    const uint32_t band_rows = (((height + nb - 1) / nb) + 7) & ~7u;
     double t0 = now_ms();
-    CUDA_TRY(cudaMemcpy(rgba8_out, base, n * 4, cudaMemcpyDeviceToHost));
+    int rc = RAYCA_OK;
+    uint32_t launched = 0;
+    for (uint32_t k = 0; k < nb; ++k) {
+        Band bd{k * band_rows, std::min(height, (k + 1) * band_rows), k == 0, false};
+        if (bd.row_begin >= height) break;
+        bd.last = bd.row_end == height;
+        rc = enqueue_render(ctx, scene, config, options, width, height, base, aux ? &d : nullptr, ctx->render_stream, &bd, &local);
+        if (rc != RAYCA_OK) return rc;
+        CUDA_TRY(cudaEventRecord(ctx->band_done[k], ctx->render_stream));
+        ++launched;
+    }
+    for (uint32_t k = 0; k < launched; ++k) {
+        const size_t y0 = (size_t)k * band_rows, y1 = std::min<size_t>(height, (size_t)(k + 1) * band_rows);
+        CUDA_TRY(cudaStreamWaitEvent(ctx->copy_stream, ctx->band_done[k], 0));
+        CUDA_TRY(cudaMemcpyAsync(rgba8_out + y0 * width * 4, base + y0 * width * 4, (y1 - y0) * width * 4, cudaMemcpyDeviceToHost,
+                                 ctx->copy_stream));
+    }
+    CUDA_TRY(cudaStreamSynchronize(ctx->copy_stream));
+    local.kernel_launches = launched;
     if (aux) {
         if (aux->hit_blas) CUDA_TRY(cudaMemcpy(aux->hit_blas, d.hit_blas, n * 4, cudaMemcpyDeviceToHost));
         if (aux->hit_prim) CUDA_TRY(cudaMemcpy(aux->hit_prim, d.hit_prim, n * 4, cudaMemcpyDeviceToHost));
@@ -464,9 +545,12 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
     }
     double t1 = now_ms();
     if (stats) {
+        const uint32_t launches = local.kernel_launches;
         rc = rayca_cuda_last_counters(ctx, &local);
         if (rc != RAYCA_OK) return rc;
-        local.readback_ms = t1 - t0;
+        local.kernel_launches = launches;
+        local.readback_ms = (t1 - t0) - local.trace_ms; // what the read-back added beyond the kernels
+        if (local.readback_ms < 0.0) local.readback_ms = 0.0;
         *stats = local;
     }
     return RAYCA_OK;

@@ -20,6 +20,7 @@ struct RenderParams {
     unsigned long long seed;
     uint32_t width, height;
     uint32_t shard_index, shard_count, tile_rows, local_rows;
+    uint32_t row_begin, row_end; // unsharded: this launch covers image rows [row_begin, row_end)
     float inv_w, inv_h, aspect;
     float strate_count, offset, step, inv_gamma;
     uint32_t strate_u;
@@ -265,12 +266,12 @@ __device__ __noinline__ float gamma_pow(float c, float inv_gamma) { return powf(
 
 template <int INTEGRATOR, int MODE, bool COUNT, bool BOUNCE>
 __device__ __forceinline__ void render_pixel(const RenderParams& P, uint32_t x, uint32_t local_row, PixelCounters& pc) {
-    uint32_t y = local_row;
+    uint32_t y = local_row + P.row_begin;
     if (P.shard_count > 1) {
         uint32_t tile = local_row / P.tile_rows;
         y = (tile * P.shard_count + P.shard_index) * P.tile_rows + (local_row % P.tile_rows);
     }
-    if (!(x < P.width && y < P.height)) return;
+    if (!(x < P.width && y < P.row_end)) return;
     const GpuCamera& cam = P.scene.camera;
     const TrsF ctrs{V3{cam.t[0], cam.t[1], cam.t[2]}, Q4{cam.q[0], cam.q[1], cam.q[2], cam.q[3]}, V3{cam.s[0], cam.s[1], cam.s[2]}};
     Col color{0.0f, 0.0f, 0.0f, 1.0f};

@@ -94,16 +94,45 @@ class Config:
                               int(self.integrator), self.max_depth, self.gamma)
 
 
+class PinnedBuffer:
+    """Page-locked host memory from rayca_cuda_host_alloc, viewed as a numpy array."""
+
+    def __init__(self, shape, dtype=np.uint8):
+        self._p = C.c_void_p()
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        _check(load_library().rayca_cuda_host_alloc(n, C.byref(self._p)))
+        self.array = np.ctypeslib.as_array(C.cast(self._p, C.POINTER(C.c_uint8)), shape=(n,)).view(dtype).reshape(shape)
+
+    def close(self):
+        if self._p:
+            self.array = None
+            load_library().rayca_cuda_host_free(self._p)
+            self._p = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 @dataclass
 class Image:
-    """rayca-model/src/image.rs:26-61 restricted to ColorType::RGBA8: row-major, top-left origin."""
+    """rayca-model/src/image.rs:26-61 restricted to ColorType::RGBA8: row-major, top-left origin.
+    `pinned=True` takes the pixel buffer from rayca_cuda_host_alloc (overlapped read-back)."""
     width: int
     height: int
     buffer: Optional[np.ndarray] = None
+    pinned: bool = False
 
     def __post_init__(self):
         if self.buffer is None:
-            self.buffer = np.zeros((self.height, self.width, 4), dtype=np.uint8)
+            if self.pinned:
+                self._pin = PinnedBuffer((self.height, self.width, 4))
+                self.buffer = self._pin.array
+                self.buffer[...] = 0
+            else:
+                self.buffer = np.zeros((self.height, self.width, 4), dtype=np.uint8)
 
     def dump_png(self, path) -> None:
         from PIL import Image as PILImage
@@ -123,6 +152,9 @@ def load_library():
         raise RuntimeError(f"{LIB_PATH} is missing: run `python -m rayca_b200.build` (there is no CPU fallback)")
     lib = C.CDLL(LIB_PATH)
     vp, u32 = C.c_void_p, C.c_uint32
+    lib.rayca_cuda_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
+    lib.rayca_cuda_host_free.argtypes = [vp]
+    lib.rayca_cuda_host_free.restype = None
     lib.rayca_cuda_init.argtypes = [C.c_int, C.POINTER(vp)]
     lib.rayca_cuda_shutdown.argtypes = [vp]
     lib.rayca_cuda_shutdown.restype = None
@@ -224,9 +256,12 @@ class DeviceScene:
         return info, nodes, no, po, src
 
     def render(self, config: Config, width: int, height: int, options: Optional[M.rayca_options] = None,
-               want_aux: bool = False):
-        """rayca_cuda_render with HOST buffers; returns (rgba8 HxWx4, aux or None, stats)."""
-        rgba8 = np.zeros((height, width, 4), dtype=np.uint8)
+               want_aux: bool = False, out: Optional[np.ndarray] = None):
+        """rayca_cuda_render with HOST buffers; returns (rgba8 HxWx4, aux or None, stats).
+        `out`: caller-owned HxWx4 uint8 buffer (e.g. Image.buffer), written in place."""
+        if out is not None:
+            assert out.shape == (height, width, 4) and out.dtype == np.uint8 and out.flags["C_CONTIGUOUS"]
+        rgba8 = out if out is not None else np.zeros((height, width, 4), dtype=np.uint8)
         aux = AuxPlanes(width, height) if want_aux else None
         stats = M.rayca_stats()
         cfg = config.to_c()
@@ -270,7 +305,6 @@ class CudaRenderer:
         desc = scene.to_desc()
         dev = DeviceScene(self._ctx, desc, self.config.bvh)
         try:
-            rgba8, _, _ = dev.render(self.config, image.width, image.height)
+            dev.render(self.config, image.width, image.height, out=image.buffer)
         finally:
             dev.close()
-        image.buffer[...] = rgba8

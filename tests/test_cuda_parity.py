@@ -183,3 +183,73 @@ def test_sharded_rows_reassemble(ctx):
             t = k * G + g
             out[t * tile:(t + 1) * tile] = local[k]
     assert np.array_equal(out[:h], full)
+
+
+@pytest.fixture(scope="module")
+def atrium(ctx):
+    """BASELINE M3 stand-in at full size: the procedural Sponza-class atrium bench.py times."""
+    from rayca_b200 import procedural as P
+
+    sc = R.DeviceScene(ctx, P.atrium(262_267).to_desc())
+    yield sc
+    sc.close()
+
+
+def _bits(aux):
+    return aux.hit_src, aux.hit_prim, aux.hit_blas, aux.depth.view(np.uint32), aux.uv.view(np.uint32), aux.rgba_f32.view(np.uint32)
+
+
+@pytest.mark.parametrize("other", [R.TRAVERSAL_EXHAUSTIVE, R.TRAVERSAL_REFERENCE_ORDERED])
+def test_product_walk_equals_reference_walks_on_the_bench_frame(ctx, atrium, other):
+    """1920x1080, 262k triangles, primary + shadow rays: the performance-layer walk returns bit for bit what
+    the reference tree walked with the reference's visiting rule (exhaustive, depth-first, first hit wins
+    ties) returns — ids, depth, barycentrics, float colour and RGBA8."""
+    cfg = R.Config(max_depth=1)
+    a8, a, sa = atrium.render(cfg, 1920, 1080, options=M.rayca_options(0, R.TRAVERSAL_ORDERED, 0, 0, 0, 0, 0), want_aux=True)
+    b8, b, sb = atrium.render(cfg, 1920, 1080, options=M.rayca_options(0, other, 0, 0, 0, 0, 0), want_aux=True)
+    for x, y in zip(_bits(a), _bits(b)):
+        assert np.array_equal(x, y)
+    assert np.array_equal(a8, b8)
+    assert (sa.rays_primary, sa.rays_shadow) == (sb.rays_primary, sb.rays_shadow)
+    assert (a.hit_src != 0xFFFFFFFF).mean() > 0.9, "the camera sits inside the atrium: nearly every pixel hits"
+
+
+def test_bounce_frame_equals_reference_walk(ctx, atrium):
+    """BASELINE M5 (one cosine bounce, incoherent secondary + shadow rays) at 960x540: same keyed RNG, so the
+    product walk and the reference-tree ordered walk must agree bit for bit."""
+    cfg = R.Config(max_depth=2)
+    a8, a, _ = atrium.render(cfg, 960, 540, options=M.rayca_options(0x5EED, R.TRAVERSAL_ORDERED, 0, 0, 0, 0, 0), want_aux=True)
+    b8, b, _ = atrium.render(cfg, 960, 540, options=M.rayca_options(0x5EED, R.TRAVERSAL_REFERENCE_ORDERED, 0, 0, 0, 0, 0), want_aux=True)
+    for x, y in zip(_bits(a), _bits(b)):
+        assert np.array_equal(x, y)
+    assert np.array_equal(a8, b8)
+
+
+def test_persistent_scheduling_equals_static_grid(ctx, atrium):
+    cfg = R.Config(max_depth=1, samples_per_pixel=4)
+    a8, a, sa = atrium.render(cfg, 1001, 563, options=M.rayca_options(0, 0, 0, 0, 0, 0, 0), want_aux=True)
+    b8, b, sb = atrium.render(cfg, 1001, 563, options=M.rayca_options(0, 0, 0, 0, 0, R.FLAG_PERSISTENT, 0), want_aux=True)
+    for x, y in zip(_bits(a), _bits(b)):
+        assert np.array_equal(x, y)
+    assert np.array_equal(a8, b8)
+    assert (sa.rays_primary, sa.rays_shadow) == (sb.rays_primary, sb.rays_shadow)
+
+
+def test_host_render_bands_equal_single_launch(ctx, atrium):
+    """rayca_cuda_render traces the frame in row bands and reads each band back on a side stream (into pinned
+    or pageable memory); the result must equal one render_device launch over the whole frame."""
+    import torch
+
+    cfg = R.Config(max_depth=1)
+    w, h = 1283, 721
+    img = R.Image(w, h, pinned=True)
+    _, _, st = atrium.render(cfg, w, h, out=img.buffer)
+    pageable, _, _ = atrium.render(cfg, w, h)
+    buf = torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda:0")
+    atrium.render_device(cfg, w, h, buf.data_ptr())
+    torch.cuda.synchronize()
+    one = buf.cpu().numpy()
+    assert np.array_equal(img.buffer, one) and np.array_equal(pageable, one)
+    assert st.rays_primary == w * h and st.kernel_launches == 4
+    c = atrium.last_counters()
+    assert c.rays_primary == w * h and c.rays_shadow == st.rays_shadow
