@@ -11,12 +11,13 @@
 // made conservative by a relative tolerance, every candidate hit is re-validated against the exact
 // reference leaf box, and every triangle carries its reference index for the tie-break.
 //
-// Build: top-down binned SAH (16 bins, 3 axes) over bounding-box centroids, leaves of <= 4 triangles,
+// Build: top-down binned SAH (32 bins, 3 axes) over bounding-box centroids, leaves of <= 4 triangles,
 // OpenMP tasks for independent subtrees; children are stored as adjacent 32-byte records (one 64-byte
 // fetch per visited inner node) and the array is laid out in depth-first order.
 #include "host_scene.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #ifdef _OPENMP
@@ -26,9 +27,18 @@
 namespace rb {
 namespace {
 
-constexpr int kBins = 16;
-constexpr uint32_t kLeafMax = 4;
-constexpr float kTraversalCost = 1.0f; // relative to one triangle test
+constexpr int kMaxBins = 64;
+// Tunables (defaults picked by measurement on B200, profiles/; the RAYCA_FAST_* environment variables
+// exist for such A/B runs only).
+int kBins = 32;
+uint32_t kLeafMax = 4;            // <= 8: a packed leaf reference holds count-1 in 3 bits
+float kTraversalCost = 1.0f;      // cost of visiting one node relative to one triangle test
+
+void read_tunables() {
+    if (const char* e = std::getenv("RAYCA_FAST_BINS")) kBins = std::max(4, std::min(kMaxBins, std::atoi(e)));
+    if (const char* e = std::getenv("RAYCA_FAST_LEAF_MAX")) kLeafMax = (uint32_t)std::max(1, std::min(8, std::atoi(e)));
+    if (const char* e = std::getenv("RAYCA_FAST_TRAV_COST")) kTraversalCost = (float)std::atof(e);
+}
 
 struct Item {
     float mn[3], mx[3];
@@ -93,8 +103,8 @@ struct FastBuilder {
             float lo = cb.mn[a], hi = cb.mx[a];
             if (!(hi > lo)) continue;
             float scale = (float)kBins / (hi - lo);
-            Bx bbox[kBins];
-            uint32_t bcnt[kBins];
+            Bx bbox[kMaxBins];
+            uint32_t bcnt[kMaxBins];
             for (int k = 0; k < kBins; ++k) { bbox[k].reset(); bcnt[k] = 0; }
             for (uint32_t i = b; i < e; ++i) {
                 int k = (int)((items[i].c[a] - lo) * scale);
@@ -102,8 +112,8 @@ struct FastBuilder {
                 bbox[k].grow(items[i].mn, items[i].mx);
                 bcnt[k]++;
             }
-            float rarea[kBins];
-            uint32_t rcnt[kBins];
+            float rarea[kMaxBins];
+            uint32_t rcnt[kMaxBins];
             Bx acc;
             acc.reset();
             uint32_t cnt = 0;
@@ -175,6 +185,7 @@ GpuNode to_gpu(const Rec& r) {
 } // namespace
 
 void build_fast_tree(HostScene& hs) {
+    read_tunables();
     // gather triangles in reference-global order with their reference leaf
     const size_t nb = hs.blas.size();
     const uint32_t total = hs.blas_prim_offset[nb];

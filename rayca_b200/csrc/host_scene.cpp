@@ -7,6 +7,10 @@
 // Layout decisions that differ from the reference are described in DESIGN.md.
 #include "host_scene.h"
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+
 #include <algorithm>
 #include <cstring>
 #include <functional>
@@ -155,7 +159,21 @@ bool color_close_black(const float c[4]) { // Color::close (color/mod.rs:160-169
 
 } // namespace
 
+namespace {
+struct PhaseTimer { // RAYCA_TIMING=1 prints the host phases of scene_create to stderr
+    bool on = std::getenv("RAYCA_TIMING") != nullptr;
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    void lap(const char* what) {
+        if (!on) return;
+        auto n = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[rayca] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
+        t = n;
+    }
+};
+} // namespace
+
 int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::string& err) {
+    PhaseTimer phase;
     Flatten f(d, out);
     f.run();
     if (f.status != RAYCA_OK) { err = f.err; return f.status; }
@@ -172,6 +190,7 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
         out.images[i] = GpuImage{(unsigned long long)off, im.width, im.height, im.color_type, 0};
     }
 
+    phase.lap("images");
     // ---- materials: [0] fallback, then per model in order
     out.materials.push_back(white_pbr());
     std::vector<uint32_t> model_mat_base(d.model_count, 0);
@@ -224,6 +243,7 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
         }
     }
 
+    phase.lap("materials/lights/camera");
     // ---- BvhScene::from_scene: one BLAS per model that owns mesh nodes, ascending model handle
     // (the reference iterates a HashMap; the order only matters for exact cross-BLAS depth ties)
     for (uint32_t mi = 0; mi < d.model_count; ++mi) {
@@ -284,7 +304,9 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
                 if (bad) { err = "vertex index out of range"; return RAYCA_E_INVALID_ARG; }
             }
         }
+        phase.lap("emit triangles");
         build_blas(blas, bvh ? 255u : 0u); // scene.rs:95-99: !config.bvh => max_depth(0)
+        phase.lap("reference BLAS build");
         out.blas.push_back(std::move(blas));
     }
     if (out.blas.empty()) { // Tlas::new would assert on an empty range (tlas.rs:75)
@@ -348,6 +370,7 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
         out.blas.swap(sorted);
     }
 
+    phase.lap("TLAS");
     // ---- pack BLAS nodes / triangles
     size_t total_nodes = 0, total_tris = 0;
     out.blas_node_offset.assign(1, 0);
@@ -396,6 +419,7 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
         }
     }
 
+    phase.lap("pack nodes/triangles/attrs");
     // ---- TLAS top pairs: every record is a (box, links) copy of its child, so the walk needs
     // only one node format.  A TLAS leaf holding k > 1 BLAS becomes a right-leaning comb whose
     // boxes are unions of BLAS root boxes (supersets never reject what the reference accepts).
@@ -437,7 +461,9 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
     };
     out.root = emit_tnode(troot, 0);
     out.max_stack = top_depth + max_blas_depth + 2;
+    phase.lap("TLAS top pairs");
     build_fast_tree(out);
+    phase.lap("performance tree");
     out.max_stack = std::max(out.max_stack, out.fast_depth + 2);
     return RAYCA_OK;
 }
