@@ -264,55 +264,62 @@ __device__ __forceinline__ unsigned char quantize(float c) {
 // correct_gamma (color/mod.rs:175-180): one shared copy of powf
 __device__ __noinline__ float gamma_pow(float c, float inv_gamma) { return powf(c, inv_gamma); }
 
-template <int INTEGRATOR, int MODE, bool COUNT, bool BOUNCE>
-__device__ __forceinline__ void render_pixel(const RenderParams& P, uint32_t x, uint32_t local_row, PixelCounters& pc) {
-    uint32_t y = local_row + P.row_begin;
+// image row of a launch-local row (row bands of the host path, interleaved tiles of a shard)
+__device__ __forceinline__ uint32_t image_row(const RenderParams& P, uint32_t local_row) {
     if (P.shard_count > 1) {
         uint32_t tile = local_row / P.tile_rows;
-        y = (tile * P.shard_count + P.shard_index) * P.tile_rows + (local_row % P.tile_rows);
+        return (tile * P.shard_count + P.shard_index) * P.tile_rows + (local_row % P.tile_rows);
     }
-    if (!(x < P.width && y < P.row_end)) return;
+    return local_row + P.row_begin;
+}
+
+__device__ __forceinline__ HitD no_hit() {
+    HitD h;
+    h.prim = 0xFFFFFFFFu;
+    h.t = __int_as_float(0x7f800000);
+    h.u = h.v = 0.0f;
+    h.p = V3{0.0f, 0.0f, 0.0f};
+    return h;
+}
+
+// One sample of one pixel: primary ray (scene.rs:129-141) through the integrator (scene.rs:80-86).
+template <int INTEGRATOR, int MODE, bool COUNT, bool BOUNCE>
+__device__ __forceinline__ void trace_sample(const RenderParams& P, uint32_t x, uint32_t y, uint32_t i, Col& c, HitD& ph, PixelCounters& pc) {
     const GpuCamera& cam = P.scene.camera;
     const TrsF ctrs{V3{cam.t[0], cam.t[1], cam.t[2]}, Q4{cam.q[0], cam.q[1], cam.q[2], cam.q[3]}, V3{cam.s[0], cam.s[1], cam.s[2]}};
-    Col color{0.0f, 0.0f, 0.0f, 1.0f};
-    HitD primary;
-    primary.prim = 0xFFFFFFFFu;
     const uint32_t pixel = y * P.width + x;
-    for (uint32_t i = 0; i < P.cfg.samples_per_pixel; ++i) {
-        float ix = (float)(i % P.strate_u);
-        float iy = (float)(i / P.strate_u);
-        float xx = (2.0f * (((float)x + ix * P.step + P.offset) * P.inv_w) - 1.0f) * cam.angle * P.aspect;
-        float yy = (1.0f - 2.0f * (((float)y + iy * P.step + P.offset) * P.inv_h)) * cam.angle;
-        V3 dir = normalize(V3{xx, yy, -1.0f});
-        // &camera_trs.trs * Ray::new(origin, dir): scale, rotate, translate (trs.rs:275-284); no re-normalise
-        V3 wd = rotate(dir * ctrs.s, ctrs.q);
-        V3 wo = rotate(scale_point(V3{0.0f, 0.0f, 0.0f}, ctrs.s), ctrs.q) + ctrs.t;
-        RayD ray = make_ray(wo, wd);
-        Col c{0.0f, 0.0f, 0.0f, 1.0f};
-        bool ok;
-        HitD ph;
-        ph.prim = 0xFFFFFFFFu;
-        ph.t = __int_as_float(0x7f800000);
-        ph.u = ph.v = 0.0f;
-        if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER) {
-            ok = pathtracer<MODE, COUNT, BOUNCE>(P, ray, pixel, i, c, ph, pc);
-        } else if (INTEGRATOR == RAYCA_INTEGRATOR_RAYTRACER) {
-            ok = raytracer<MODE, COUNT>(P, ray, c, ph, pc);
-        } else { // Flat (integrator/flat.rs:16-28)
-            ok = trace_ray<MODE, false, COUNT>(P.scene, ray, ph, &pc.walk);
-            if (ok) {
-                Surf sf;
-                load_surf(P.scene, ray, ph, sf);
-                c = surf_color(P.scene, sf);
-            }
+    float ix = (float)(i % P.strate_u);
+    float iy = (float)(i / P.strate_u);
+    float xx = (2.0f * (((float)x + ix * P.step + P.offset) * P.inv_w) - 1.0f) * cam.angle * P.aspect;
+    float yy = (1.0f - 2.0f * (((float)y + iy * P.step + P.offset) * P.inv_h)) * cam.angle;
+    V3 dir = normalize(V3{xx, yy, -1.0f});
+    // &camera_trs.trs * Ray::new(origin, dir): scale, rotate, translate (trs.rs:275-284); no re-normalise
+    V3 wd = rotate(dir * ctrs.s, ctrs.q);
+    V3 wo = rotate(scale_point(V3{0.0f, 0.0f, 0.0f}, ctrs.s), ctrs.q) + ctrs.t;
+    RayD ray = make_ray(wo, wd);
+    c = Col{0.0f, 0.0f, 0.0f, 1.0f};
+    bool ok;
+    ph = no_hit();
+    if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER) {
+        ok = pathtracer<MODE, COUNT, BOUNCE>(P, ray, pixel, i, c, ph, pc);
+    } else if (INTEGRATOR == RAYCA_INTEGRATOR_RAYTRACER) {
+        ok = raytracer<MODE, COUNT>(P, ray, c, ph, pc);
+    } else { // Flat (integrator/flat.rs:16-28)
+        ok = trace_ray<MODE, false, COUNT>(P.scene, ray, ph, &pc.walk);
+        if (ok) {
+            Surf sf;
+            load_surf(P.scene, ray, ph, sf);
+            c = surf_color(P.scene, sf);
         }
-        if (!ok) {
-            c = Col{0.0f, 0.0f, 0.0f, 1.0f}; // unwrap_or(Color::BLACK) (scene.rs:80-86)
-            if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER && P.cfg.max_depth == 0) ph.prim = 0xFFFFFFFFu;
-        }
-        primary = ph;
-        color = cadd(color, c);
     }
+    if (!ok) {
+        c = Col{0.0f, 0.0f, 0.0f, 1.0f}; // unwrap_or(Color::BLACK) (scene.rs:80-86)
+        if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER && P.cfg.max_depth == 0) ph.prim = 0xFFFFFFFFu;
+    }
+}
+
+// `color /= spp; correct_gamma; *pixel = color.into()` (scene.rs:145-149) plus the optional parity planes.
+__device__ __forceinline__ void write_pixel(const RenderParams& P, uint32_t x, uint32_t y, uint32_t local_row, Col color, const HitD& primary) {
     color = cdiv(color, (float)P.cfg.samples_per_pixel);
     if (P.inv_gamma != 1.0f) { // powf(c, 1.0) == c in the reference's libm; skipping it keeps the bits
         color.r = gamma_pow(color.r, P.inv_gamma);
@@ -341,6 +348,56 @@ __device__ __forceinline__ void render_pixel(const RenderParams& P, uint32_t x, 
         P.uv[2 * o + 1] = hit ? primary.v : 0.0f;
     }
     if (P.rgba_f32) reinterpret_cast<float4*>(P.rgba_f32)[o] = make_float4(color.r, color.g, color.b, color.a);
+}
+
+// One warp, one 8x4 pixel tile.
+//   1 spp: lane = pixel.
+//   n spp: the tile's 32*n (pixel, sample) pairs are traced 32 at a time in pixel-major order, so the rays
+//     a warp walks together are the samples of ONE or two pixels — far more coherent than 32 different
+//     pixels (the 10M-triangle soup at 16 spp ran at 7 of 32 lanes active with lane = pixel).  Lane p owns
+//     pixel p of the tile and adds that pixel's sample colours in sample order (shuffles), which is the
+//     reference's `color += sample` order (scene.rs:129-144), so the f32 sum has the same bits.
+template <int INTEGRATOR, int MODE, bool COUNT, bool BOUNCE>
+__device__ __forceinline__ void render_tile(const RenderParams& P, uint32_t x0, uint32_t row0, uint32_t lane, PixelCounters& pc) {
+    const uint32_t spp = P.cfg.samples_per_pixel;
+    const uint32_t x = x0 + (lane & 7u), local_row = row0 + (lane >> 3);
+    const uint32_t y = image_row(P, local_row);
+    const bool mine = x < P.width && y < P.row_end;
+    Col color{0.0f, 0.0f, 0.0f, 1.0f};
+    HitD primary = no_hit();
+    const bool want_aux = P.hit_prim || P.hit_blas || P.hit_src || P.depth || P.uv;
+#pragma unroll 1
+    for (uint32_t k0 = 0; k0 < 32u * spp; k0 += 32u) {
+        const uint32_t k = k0 + lane, pl = k / spp, i = k - pl * spp;
+        const uint32_t sx = x0 + (pl & 7u), srow = row0 + (pl >> 3), sy = image_row(P, srow);
+        Col c{0.0f, 0.0f, 0.0f, 1.0f};
+        HitD ph = no_hit();
+        if (sx < P.width && sy < P.row_end) trace_sample<INTEGRATOR, MODE, COUNT, BOUNCE>(P, sx, sy, i, c, ph, pc);
+        if (spp == 1) { // lane = pixel: nothing to exchange
+            color = cadd(color, c);
+            primary = ph;
+            break;
+        }
+#pragma unroll 1
+        for (uint32_t src = 0; src < 32u; ++src) {
+            const uint32_t ks = k0 + src, ps = ks / spp; // warp-uniform
+            Col cs{__shfl_sync(0xFFFFFFFFu, c.r, src), __shfl_sync(0xFFFFFFFFu, c.g, src), __shfl_sync(0xFFFFFFFFu, c.b, src),
+                   __shfl_sync(0xFFFFFFFFu, c.a, src)};
+            if (ps == lane) color = cadd(color, cs);
+            if (want_aux && ks - ps * spp == spp - 1u) { // the parity planes describe sample spp-1
+                const uint32_t hp = __shfl_sync(0xFFFFFFFFu, ph.prim, src);
+                const float ht = __shfl_sync(0xFFFFFFFFu, ph.t, src), hu = __shfl_sync(0xFFFFFFFFu, ph.u, src),
+                            hv = __shfl_sync(0xFFFFFFFFu, ph.v, src);
+                if (ps == lane) {
+                    primary.prim = hp;
+                    primary.t = ht;
+                    primary.u = hu;
+                    primary.v = hv;
+                }
+            }
+        }
+    }
+    if (mine) write_pixel(P, x, y, local_row, color, primary);
 }
 
 // 8 blocks x 4 warps per SM = 64 registers per thread: the walk is latency- and issue-bound, and half
@@ -373,15 +430,11 @@ __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) render_kernel(const __g
             const uint32_t gx = group % P.groups_x, gy = group / P.groups_x;
 #pragma unroll 1
             for (uint32_t sub = 0; sub < 4u; ++sub) {
-                const uint32_t x = gx * 16u + (sub & 1u) * 8u + (lane & 7u);
-                const uint32_t local_row = gy * 8u + (sub >> 1) * 4u + (lane >> 3);
-                render_pixel<INTEGRATOR, MODE, COUNT, BOUNCE>(P, x, local_row, pc);
+                render_tile<INTEGRATOR, MODE, COUNT, BOUNCE>(P, gx * 16u + (sub & 1u) * 8u, gy * 8u + (sub >> 1) * 4u, lane, pc);
             }
         }
     } else {
-        const uint32_t x = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
-        const uint32_t local_row = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
-        render_pixel<INTEGRATOR, MODE, COUNT, BOUNCE>(P, x, local_row, pc);
+        render_tile<INTEGRATOR, MODE, COUNT, BOUNCE>(P, blockIdx.x * 16u + (warp & 1u) * 8u, blockIdx.y * 8u + (warp >> 1) * 4u, lane, pc);
     }
     // warp-aggregated counters: one atomic per warp per counter
     uint32_t sh = __reduce_add_sync(0xFFFFFFFFu, pc.shadow);
