@@ -317,4 +317,73 @@ static inline Ray transform_ray(const Trs& t, Ray r) {
     return r;
 }
 
+// ---- Mat4 (rayca-math/src/mat4.rs), only what the sphere path needs
+struct Mat4 {
+    float m[4][4];
+};
+static inline Mat4 mat4_identity() {
+    Mat4 r{};
+    for (int i = 0; i < 4; ++i) r.m[i][i] = 1.0f;
+    return r;
+}
+// mat4.rs:160-189 — row * column over 16 lanes of which 12 are masked to zero; ordered reduce_sum
+static inline Mat4 operator*(const Mat4& a, const Mat4& b) {
+    Mat4 r;
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) {
+            float acc = ((a.m[i][0] * b.m[0][j] + a.m[i][1] * b.m[1][j]) + a.m[i][2] * b.m[2][j]) + a.m[i][3] * b.m[3][j];
+            for (int z = 0; z < 12; ++z) acc += 0.0f; // the masked lanes
+            r.m[i][j] = acc;
+        }
+    return r;
+}
+// mat4.rs:207-235
+static inline Mat4 mat4_from_quat(Quat q) {
+    Mat3 r3 = mat3_from_quat(q);
+    Mat4 r = mat4_identity();
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) r.m[i][j] = r3.m[i][j];
+    return r;
+}
+// mat4.rs:63-79,104-118: from_translation / from_rotation (= Mat4::from(q) * identity) / from_scale
+static inline Mat4 mat4_from_translation(Vec3 t) {
+    Mat4 r = mat4_identity();
+    r.m[0][3] += t.x;
+    r.m[1][3] += t.y;
+    r.m[2][3] += t.z;
+    return r;
+}
+static inline Mat4 mat4_from_rotation(Quat q) { return mat4_from_quat(q) * mat4_identity(); }
+static inline Mat4 mat4_from_scale(Vec3 s) {
+    Mat4 r = mat4_identity();
+    r.m[0][0] *= s.x;
+    r.m[1][1] *= s.y;
+    r.m[2][2] *= s.z;
+    return r;
+}
+// mat4.rs:276-283 — From<&Inversed<Trs>>: S^-1 * (R^-1 * T^-1)
+static inline Mat4 mat4_from_inversed_trs(const Trs& t) {
+    return mat4_from_scale(reciprocal(t.scale)) * (mat4_from_rotation(conjugate(t.rotation)) * mat4_from_translation(t.translation * -1.0f));
+}
+// mat4.rs:290-313 (impl_mul3!): rows dot [x, y, z, 1], divide by the 4th unless it is zero
+static inline Point3 operator*(const Mat4& a, Point3 p) {
+    float ret[4];
+    for (int i = 0; i < 4; ++i) ret[i] = ((a.m[i][0] * p.x + a.m[i][1] * p.y) + a.m[i][2] * p.z) + a.m[i][3] * 1.0f;
+    float den = ret[3] != 0.0f ? ret[3] : 1.0f;
+    return {ret[0] / den, ret[1] / den, ret[2] / den};
+}
+// trs.rs:405-414 with ray.rs:74-91: translate, rotate, scale by the inverse parts
+static inline Ray inverse_transform_ray(const Trs& t, Ray r) {
+    r.origin = r.origin + (t.translation * -1.0f);
+    Quat qi = conjugate(t.rotation);
+    r.dir = rotate(r.dir, qi);
+    r.rdir = reciprocal(r.dir);
+    r.origin = to_point3(rotate(to_vec3(r.origin), qi));
+    Vec3 si = reciprocal(t.scale);
+    r.dir = r.dir * si;
+    r.rdir = reciprocal(r.dir);
+    r.origin = scale_point(r.origin, si);
+    return r;
+}
+
 } // namespace orc

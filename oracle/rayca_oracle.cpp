@@ -63,6 +63,10 @@ struct Prim {
     uint32_t model;    // owning model
     int32_t material;  // model-local material handle or -1
     uint32_t src;      // stable id: emit order within the model
+    // BvhGeometry::Sphere (primitive.rs:10-13, 270-282): model-space sphere, the node TRS is applied per query
+    bool sphere = false;
+    Point3 center{0, 0, 0};
+    float radius = 0, radius2 = 0;
     // cache of the values the reference recomputes on every query (bit-identical, same ops)
     Point3 wv[3];
     Vec3 wcentroid;
@@ -238,7 +242,26 @@ void emit_mesh_prims(Scene& s, const rayca_scene_desc& d, uint32_t model_index, 
     for (uint32_t pi = 0; pi < mesh.primitive_count; ++pi) {
         const rayca_primitive& prim = d.primitives[m.primitive_offset + d.mesh_primitives[mesh.first_primitive + pi]];
         const rayca_geometry& g = d.geometries[m.geometry_offset + prim.geometry];
-        if (g.kind != RAYCA_GEOMETRY_TRIANGLE_MESH) continue; // spheres: SURVEY 8(f) rank 2
+        if (g.kind == RAYCA_GEOMETRY_SPHERE) { // BvhPrimitive::from_sphere (primitive.rs:270-282)
+            Prim p{};
+            p.sphere = true;
+            p.center = {g.center[0], g.center[1], g.center[2]};
+            p.radius = g.radius;
+            p.radius2 = g.radius * g.radius; // Sphere::new (sphere.rs:51-62)
+            p.trs = trs_key;
+            p.model = model_index;
+            p.material = prim.material;
+            p.src = (uint32_t)out.size();
+            // Sphere::{get_center,get_radius,min,max} (sphere.rs:72-93,169-181)
+            Point3 c = transform_point(trs, p.center);
+            float r = p.radius * maxf(maxf(maxf(trs.scale.x, trs.scale.y), trs.scale.z), 0.0f); // reduce_max over 4 lanes, w = 0
+            p.wcentroid = to_vec3(c);
+            p.wmin = c - Vec3{r, r, r};
+            p.wmax = c + Vec3{r, r, r};
+            out.push_back(p);
+            continue;
+        }
+        if (g.kind != RAYCA_GEOMETRY_TRIANGLE_MESH) continue;
         for (uint32_t t = 0; t < g.index_count / 3; ++t) {
             Prim p;
             for (int k = 0; k < 3; ++k) {
@@ -296,6 +319,17 @@ BvhNode make_node(const Blas& blas, uint32_t offset, uint32_t count) {
     n.count = count;
     return n;
 }
+// AABB::grow_primitive (aabb.rs:61-72): triangle = its three world vertices, sphere = its min / max points
+inline void grow_prim(AABB& box, const Prim& p) {
+    if (p.sphere) {
+        grow(box, p.wmin);
+        grow(box, p.wmax);
+        return;
+    }
+    grow(box, p.wv[0]);
+    grow(box, p.wv[1]);
+    grow(box, p.wv[2]);
+}
 // blas.rs:64-89 — candidate boxes start at AABB::default() = two points at the ORIGIN (A-21)
 float evaluate_sah(const Blas& blas, const BvhNode& node, int axis, float pos) {
     AABB left_box{{0, 0, 0}, {0, 0, 0}}, right_box{{0, 0, 0}, {0, 0, 0}};
@@ -304,14 +338,10 @@ float evaluate_sah(const Blas& blas, const BvhNode& node, int axis, float pos) {
         const Prim& p = blas.prims[i];
         if (p.wcentroid[axis] < pos) {
             left_count++;
-            grow(left_box, p.wv[0]);
-            grow(left_box, p.wv[1]);
-            grow(left_box, p.wv[2]);
+            grow_prim(left_box, p);
         } else {
             right_count++;
-            grow(right_box, p.wv[0]);
-            grow(right_box, p.wv[1]);
-            grow(right_box, p.wv[2]);
+            grow_prim(right_box, p);
         }
     }
     float cost = (float)left_count * area(left_box) + (float)right_count * area(right_box);
@@ -483,7 +513,33 @@ struct Tracer {
     Counters* rays; // always valid: ray tallies
     Counters* cnt;  // non-null only when walk records are being counted
 
+    // Sphere::intersects + intersects_impl (rayca-geometry/src/sphere.rs:101-163)
+    inline bool sphere_intersects(const Prim& p, const Ray& ray, float& t_out, Point3& pt, Vec2& uv) const {
+        const Trs& trs = s.world_trs[p.trs];
+        Ray r = inverse_transform_ray(trs, ray);
+        float a = dot(r.dir, r.dir);
+        Vec3 c_to_r = r.origin - p.center;
+        float b = dot(c_to_r, r.dir);
+        float c = dot(c_to_r, c_to_r) - p.radius2;
+        float det = b * b - a * c;
+        if (det < 0.0f) return false;
+        float det_sqrt = std::sqrt(det);
+        float t0 = (-b + det_sqrt) / a;
+        float t1 = (-b - det_sqrt) / a;
+        if (t0 < 0.0f && t1 < 0.0f) return false;
+        float t;
+        if (t0 >= 0.0f && t1 >= 0.0f) t = minf(t0, t1);
+        else if (t0 >= 0.0f) t = t0;
+        else t = t1;
+        Point3 point = r.origin + r.dir * t;
+        t_out = t;
+        pt = transform_point(trs, point);
+        uv = {0.0f, 0.0f};
+        return true;
+    }
+
     inline bool prim_intersects(const Prim& p, const Ray& ray, float& t, Point3& pt, Vec2& uv) const {
+        if (p.sphere) return sphere_intersects(p, ray, t, pt, uv);
         if (faithful) {
             const Trs& trs = s.world_trs[p.trs]; // get_world_trs (primitive.rs:96)
             return triangle_intersects_world(transform_point(trs, p.v[0]), transform_point(trs, p.v[1]),
@@ -755,10 +811,12 @@ struct HitInfo {
 
     // bvh/triangle.rs:34-71 — v2*(1-u-v) + v0*u + v1*v
     Color geometry_color() const {
+        if (prim->sphere) return WHITE; // primitive.rs:19
         float u = hit.uv.x, v = hit.uv.y;
         return prim->ext[2].color * (1.0f - u - v) + prim->ext[0].color * u + prim->ext[1].color * v;
     }
     Vec2 get_uv() const {
+        if (prim->sphere) return {0.0f, 0.0f}; // primitive.rs:26-27
         float u = hit.uv.x, v = hit.uv.y;
         return prim->ext[2].uv * (1.0f - u - v) + prim->ext[0].uv * u + prim->ext[1].uv * v;
     }
@@ -857,6 +915,13 @@ struct HitInfo {
     float get_shininess() const { return phong(material()).shininess; } // material/mod.rs:154-160 (Phong only)
     // hit.rs:77-83 / primitive.rs:171-181 / pbr.rs:104-123
     Vec3 get_normal() {
+        if (!has_normal && prim->sphere) { // primitive.rs:183-190
+            const Trs& trs = s.world_trs[prim->trs];
+            Point3 hit_point = mat4_from_inversed_trs(trs) * hit.point;
+            Vec3 n = normalized(hit_point - prim->center); // Sphere::get_model_normal (sphere.rs:95-97)
+            normal = normalized(transpose(mat3_from_inversed_trs(trs)) * n);
+            has_normal = true;
+        }
         if (!has_normal) {
             Vec3 n = interp(&VertexExt::normal);
             rayca_material m = material();

@@ -44,6 +44,7 @@ struct Item {
     float mn[3], mx[3];
     float c[3];
     uint32_t id; // reference-global triangle index
+    uint32_t sphere; // 0: triangle, else 1 (a leaf never mixes the two kinds)
 };
 
 struct Bx {
@@ -95,6 +96,8 @@ struct FastBuilder {
             return self;
         };
         if (n <= 1) return make_leaf();
+        bool mixed = false; // triangles and spheres have different 64-byte records: keep leaves pure
+        for (uint32_t i = b + 1; i < e && !mixed; ++i) mixed = items[i].sphere != items[b].sphere;
 
         // binned SAH
         float best_cost = kF32Max;
@@ -137,7 +140,7 @@ struct FastBuilder {
         if (n <= kLeafMax) {
             float leaf_cost = (float)n * parent_area;
             float split_cost = kTraversalCost * parent_area + best_cost;
-            if (best_axis < 0 || leaf_cost <= split_cost) return make_leaf();
+            if (!mixed && (best_axis < 0 || leaf_cost <= split_cost)) return make_leaf();
         }
         uint32_t mid;
         if (best_axis < 0) {
@@ -210,6 +213,7 @@ void build_fast_tree(HostScene& hs) {
             it.mx[0] = t.bmax.x; it.mx[1] = t.bmax.y; it.mx[2] = t.bmax.z;
             for (int a = 0; a < 3; ++a) it.c[a] = 0.5f * (it.mn[a] + it.mx[a]);
             it.id = po + (uint32_t)k;
+            it.sphere = t.sphere ? 1u : 0u;
         }
     }
     FastBuilder fb(items);
@@ -222,8 +226,10 @@ void build_fast_tree(HostScene& hs) {
     // depth-first relayout of the pairs (left subtree right after its parent pair).  A child
     // reference (GpuNode::link0) is either a pair index or, with kLeafRef set, a packed leaf
     // {bits 0..27 first triangle, bits 28..30 count-1}.
-    constexpr uint32_t kLeafRef = 0x80000000u;
-    auto leaf_ref = [&](const Rec& r) { return kLeafRef | ((r.link1 - 1u) << 28) | r.link0; };
+    constexpr uint32_t kLeafRef = 0x80000000u, kSphereRef = 0x08000000u; // first index: 27 bits
+    auto leaf_ref = [&](const Rec& r) {
+        return kLeafRef | ((r.link1 - 1u) << 28) | (items[r.link0].sphere ? kSphereRef : 0u) | r.link0;
+    };
     hs.fast_nodes.clear();
     hs.fast_nodes.reserve(items.size());
     struct Todo { uint32_t slot; uint32_t dst; };
@@ -271,6 +277,22 @@ void build_fast_tree(HostScene& hs) {
 #pragma omp parallel for schedule(static) if (total > 8192)
     for (int64_t i = 0; i < (int64_t)total; ++i) {
         uint32_t id = items[(size_t)i].id;
+        if (items[(size_t)i].sphere) {
+            // sphere record: what `&Inversed(trs) * ray` applies (translate by -t, rotate by q^-1, scale by 1/s;
+            // trs.rs:301-312,405-414) | {centre, radius^2} of the model-space sphere
+            size_t bi = 0;
+            while (bi + 1 < nb && id >= hs.blas_prim_offset[bi + 1]) ++bi;
+            const HostBlas& hb = hs.blas[bi];
+            const HostSphere& sp = hb.spheres[hb.tris[id - hs.blas_prim_offset[bi]].sphere - 1];
+            const V3 rs = reciprocal(sp.world.s);
+            const Q4 qi = conj(sp.world.q);
+            float4* dst = &hs.fast_tri[(size_t)i * 4];
+            dst[0] = make_float4(-sp.world.t.x, -sp.world.t.y, -sp.world.t.z, sp.radius2);
+            dst[1] = make_float4(qi.x, qi.y, qi.z, qi.w);
+            dst[2] = make_float4(rs.x, rs.y, rs.z, __builtin_bit_cast(float, id));
+            dst[3] = make_float4(sp.center.x, sp.center.y, sp.center.z, __builtin_bit_cast(float, ref_leaf[id]));
+            continue;
+        }
         const float4* src = &hs.tri_pos[(size_t)id * 3];
         const V3 v0{src[0].x, src[0].y, src[0].z}, v1{src[1].x, src[1].y, src[1].z}, v2{src[2].x, src[2].y, src[2].z};
         const V3 n = cross(v1 - v0, v2 - v0);

@@ -78,6 +78,41 @@ M3 normal_matrix_of(const TrsF& t) {
     return m3_transpose(m3_mul(m3_scale(reciprocal(t.s)), rot));
 }
 
+// ---- Mat4 (rayca-math/src/mat4.rs) for the sphere path: Mat4::from(&Inversed<Trs>) =
+// from_scale(1/s) * (from_rotation(q^-1) * from_translation(-t)) (mat4.rs:276-283).  The product sums
+// row * column over 16 SIMD lanes of which 12 are masked to zero, in lane order (mat4.rs:160-189).
+struct M4 {
+    float m[4][4];
+};
+M4 m4_identity() {
+    M4 r{};
+    for (int i = 0; i < 4; ++i) r.m[i][i] = 1.0f;
+    return r;
+}
+M4 m4_mul(const M4& a, const M4& b) {
+    M4 r;
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) {
+            float acc = ((a.m[i][0] * b.m[0][j] + a.m[i][1] * b.m[1][j]) + a.m[i][2] * b.m[2][j]) + a.m[i][3] * b.m[3][j];
+            for (int z = 0; z < 12; ++z) acc += 0.0f;
+            r.m[i][j] = acc;
+        }
+    return r;
+}
+M4 m4_from_inversed(const TrsF& t) {
+    M4 sc = m4_identity();
+    V3 rs = reciprocal(t.s);
+    sc.m[0][0] *= rs.x; sc.m[1][1] *= rs.y; sc.m[2][2] *= rs.z;
+    M3 r3 = m3_from_quat(conj(t.q));
+    M4 rq = m4_identity();
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) rq.m[i][j] = r3.m[i][j];
+    M4 rot = m4_mul(rq, m4_identity()); // Mat4::rotate: Mat4::from(q) * self (mat4.rs:110-112)
+    M4 tr = m4_identity();
+    tr.m[0][3] += -t.t.x; tr.m[1][3] += -t.t.y; tr.m[2][3] += -t.t.z;
+    return m4_mul(sc, m4_mul(rot, tr));
+}
+
 struct MeshDraw {
     uint32_t node_local;
     TrsF world;
@@ -263,9 +298,31 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
                 const rayca_primitive& prim = d.primitives[m.primitive_offset + ph];
                 if (prim.geometry >= m.geometry_count) { err = "bad geometry handle"; return RAYCA_E_INVALID_ARG; }
                 const rayca_geometry& g = d.geometries[m.geometry_offset + prim.geometry];
-                if (g.kind != RAYCA_GEOMETRY_TRIANGLE_MESH) { err = "sphere geometry is not supported yet"; return RAYCA_E_UNSUPPORTED; }
                 uint32_t material = 0;
                 if (prim.material >= 0 && (uint32_t)prim.material < m.material_count) material = model_mat_base[mi] + (uint32_t)prim.material;
+                if (g.kind == RAYCA_GEOMETRY_SPHERE) { // BvhPrimitive::from_sphere (primitive.rs:270-282)
+                    HostSphere sp;
+                    sp.center = V3{g.center[0], g.center[1], g.center[2]};
+                    sp.radius2 = g.radius * g.radius;
+                    sp.world = md.world;
+                    sp.material = material;
+                    blas.spheres.push_back(sp);
+                    HostTri ht{};
+                    // Sphere::{get_center,get_radius,min,max} (sphere.rs:72-93,169-181); reduce_max runs over 4 lanes, w = 0
+                    V3 c = trs_point(md.world, sp.center);
+                    float r = g.radius * fmaxf(fmaxf(fmaxf(md.world.s.x, md.world.s.y), md.world.s.z), 0.0f);
+                    ht.centroid = c;
+                    ht.bmin = c - V3{r, r, r};
+                    ht.bmax = c + V3{r, r, r};
+                    ht.src = (uint32_t)blas.tris.size();
+                    ht.sphere = (uint32_t)blas.spheres.size();
+                    blas.tris.push_back(ht);
+                    blas.attrs.push_back(HostAttr{});
+                    blas.attrs.back().material = material;
+                    out.has_spheres = true;
+                    continue;
+                }
+                if (g.kind != RAYCA_GEOMETRY_TRIANGLE_MESH) { err = "unknown geometry kind"; return RAYCA_E_INVALID_ARG; }
                 uint32_t ntri = g.index_count / 3;
                 size_t base = blas.tris.size();
                 blas.tris.resize(base + ntri);
@@ -405,6 +462,28 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
             const HostAttr& a = b.attrs[t.src];
             size_t gi = (size_t)po + (size_t)k;
             float4* p = &out.tri_pos[gi * 3];
+            if (t.sphere) {
+                // sphere prim: attr record = {inverse Mat4 rows 0..2 | normal matrix rows (w: centre) | world t, q, s |
+                // material}; what primitive.rs:183-190 derives from the node TRS on every shaded hit
+                const HostSphere& sp = b.spheres[t.sphere - 1];
+                p[0] = make_float4(sp.center.x, sp.center.y, sp.center.z, __builtin_bit_cast(float, t.src));
+                p[1] = make_float4(sp.radius2, 0.0f, 0.0f, __builtin_bit_cast(float, a.material));
+                p[2] = make_float4(0.0f, 0.0f, 0.0f, __builtin_bit_cast(float, (uint32_t)bi));
+                float4* q = &out.tri_attr[gi * 12];
+                M4 inv = m4_from_inversed(sp.world);
+                M3 nm = normal_matrix_of(sp.world);
+                const float cc[3] = {sp.center.x, sp.center.y, sp.center.z};
+                for (int r = 0; r < 3; ++r) {
+                    q[r] = make_float4(inv.m[r][0], inv.m[r][1], inv.m[r][2], inv.m[r][3]);
+                    q[3 + r] = make_float4(nm.m[r][0], nm.m[r][1], nm.m[r][2], cc[r]);
+                }
+                q[6] = make_float4(sp.world.t.x, sp.world.t.y, sp.world.t.z, 0.0f);
+                q[7] = make_float4(sp.world.q.x, sp.world.q.y, sp.world.q.z, sp.world.q.w);
+                q[8] = make_float4(sp.world.s.x, sp.world.s.y, sp.world.s.z, 0.0f);
+                q[9] = make_float4(0.0f, 0.0f, 0.0f, __builtin_bit_cast(float, a.material));
+                q[10] = q[11] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                continue;
+            }
             p[0] = make_float4(t.v[0].x, t.v[0].y, t.v[0].z, __builtin_bit_cast(float, t.src));
             p[1] = make_float4(t.v[1].x, t.v[1].y, t.v[1].z, __builtin_bit_cast(float, a.material));
             p[2] = make_float4(t.v[2].x, t.v[2].y, t.v[2].z, __builtin_bit_cast(float, (uint32_t)bi));

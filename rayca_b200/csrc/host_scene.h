@@ -21,6 +21,16 @@ struct HostTri {
     V3 centroid;   // world-space `trs * ((a+b+c)*0.3333)` used by the SAH partition
     V3 bmin, bmax; // world-space bounds of the three vertices
     uint32_t src;  // emit order inside its model (stable id)
+    uint32_t sphere = 0; // 0: triangle; k > 0: HostBlas::spheres[k - 1] (v[] unused, bounds / centroid are the sphere's)
+};
+
+// BvhGeometry::Sphere (bvh/primitive.rs:10-13,270-282): the sphere stays in MODEL space, the node's
+// world TRS is applied to the ray and to the hit point on every query (rayca-geometry/src/sphere.rs:155-163).
+struct HostSphere {
+    V3 center;      // model space
+    float radius2;  // Sphere::new: radius * radius
+    TrsF world;     // world TRS of the owning node
+    uint32_t material;
 };
 
 struct HostAttr {
@@ -38,6 +48,7 @@ struct HostNode {
 struct HostBlas {
     std::vector<HostTri> tris;   // reordered in place by the build
     std::vector<HostAttr> attrs; // indexed by HostTri::src
+    std::vector<HostSphere> spheres;
     std::vector<HostNode> nodes; // node 0 root, node 1 unused (blas.rs:250-256)
     uint32_t model = 0;
     uint32_t depth = 0;
@@ -51,6 +62,7 @@ struct HostScene {
     std::vector<GpuLight> lights;
     GpuCamera camera{};
     bool has_camera = false;
+    bool has_spheres = false; // the reference-tree walks (traversal modes 1 / 2) handle triangles only
 
     // packed output
     std::vector<GpuNode> nodes;          // all BLAS nodes (offset-adjusted) followed by TLAS top pairs

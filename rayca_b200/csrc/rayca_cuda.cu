@@ -131,7 +131,7 @@ void launch_one(const RenderParams& P, dim3 groups, int sm_count, cudaStream_t s
 
 struct LaunchSel {
     uint32_t mode;
-    bool count, persistent, bounce;
+    bool count, persistent, bounce, spheres;
     int sm_count;
 };
 
@@ -155,6 +155,7 @@ void launch_integrator(const RenderParams& P, dim3 groups, const LaunchSel& k, c
 #ifndef RAYCA_FAST_BUILD // tuning variants (tools/variants.py) only carry the product walk
     if (k.mode == RAYCA_TRAVERSAL_EXHAUSTIVE) launch_mode<INTEGRATOR, 1>(P, groups, k, st);
     else if (k.mode == RAYCA_TRAVERSAL_REFERENCE_ORDERED) launch_mode<INTEGRATOR, 2>(P, groups, k, st);
+    else if (k.spheres) launch_mode<INTEGRATOR, 3>(P, groups, k, st);
     else
 #endif
         launch_mode<INTEGRATOR, 0>(P, groups, k, st);
@@ -250,9 +251,9 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         delete s;
         return fail(rc, err);
     }
-    if (s->host.blas_prim_offset.back() >= (1u << 28)) {
+    if (s->host.blas_prim_offset.back() >= (1u << 27)) {
         delete s;
-        return fail(RAYCA_E_UNSUPPORTED, "more than 2^28 triangles");
+        return fail(RAYCA_E_UNSUPPORTED, "more than 2^27 primitives");
     }
     if (s->host.max_stack > (uint32_t)kStackSize) {
         delete s;
@@ -404,6 +405,8 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     P.counters = ctx->d_counters;
     const uint32_t mode = options ? options->traversal : (uint32_t)RAYCA_TRAVERSAL_ORDERED;
     if (mode > RAYCA_TRAVERSAL_REFERENCE_ORDERED) return fail(RAYCA_E_INVALID_ARG, "unknown traversal mode");
+    if (mode != RAYCA_TRAVERSAL_ORDERED && scene->host.has_spheres)
+        return fail(RAYCA_E_UNSUPPORTED, "the reference-tree walks (traversal 1 / 2) handle triangle scenes only");
     const bool count = options && (options->flags & RAYCA_FLAG_COUNT_WALK); // opt-in: walk counters cost registers
     const bool persistent = options && (options->flags & RAYCA_FLAG_PERSISTENT);
 
@@ -413,7 +416,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     P.groups_x = grid.x;
     P.tile_count = grid.x * grid.y;
     if (first) CUDA_TRY(cudaEventRecord(ctx->ev0, st));
-    LaunchSel sel{mode, count, persistent, false, ctx->sm_count};
+    LaunchSel sel{mode, count, persistent, false, scene->host.has_spheres, ctx->sm_count};
     if (config->integrator == RAYCA_INTEGRATOR_PATHTRACER) // an indirect ray needs depth < limit (pathtracer.rs:94)
         sel.bounce = config->max_depth > (config->direct_sampler == RAYCA_SAMPLER_NEE ? 1u : 0u);
     switch (config->integrator) {

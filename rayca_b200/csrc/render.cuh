@@ -156,7 +156,7 @@ __device__ __forceinline__ bool pathtracer(const RenderParams& P, RayD ray, uint
         if (depth == 0) primary = h;
         if (!hit) break;
         Surf sf;
-        load_surf<BOUNCE>(s, ray, h, sf); // without bounces the material is evaluated lazily by nee_direct
+        load_surf<BOUNCE, MODE == 3>(s, ray, h, sf); // without bounces the material is evaluated lazily by nee_direct
         if (collect_emissive && sf.mat->kind == RAYCA_MATERIAL_PHONG && sf.mat->emissive) {
             tail = surf_color(s, sf);
             have_tail = true;
@@ -205,7 +205,7 @@ __device__ __forceinline__ bool raytracer(const RenderParams& P, RayD ray, Col& 
         if (depth == 0) primary = h;
         if (!hit) break;
         Surf sf;
-        load_surf(s, ray, h, sf);
+        load_surf<true, MODE == 3>(s, ray, h, sf);
         Col lc{0.0f, 0.0f, 0.0f, 1.0f};
         for (uint32_t li = 0; li < s.light_count; ++li) {
             const GpuLight& L = s.lights[li];
@@ -221,7 +221,7 @@ __device__ __forceinline__ bool raytracer(const RenderParams& P, RayD ray, Col& 
                 float ldist = length(sf.point - lpos); // light/point.rs:32-35, directional.rs:34-37
                 if (!(sh.t > ldist)) {
                     Surf ss;
-                    load_surf(s, shadow, sh, ss);
+                    load_surf<true, MODE == 3>(s, shadow, sh, ss);
                     lit = surf_color(s, ss).a < 1.0f - kF32Eps; // Color::is_transparent
                 }
             }
@@ -279,6 +279,7 @@ __device__ __forceinline__ HitD no_hit() {
     h.t = __int_as_float(0x7f800000);
     h.u = h.v = 0.0f;
     h.p = V3{0.0f, 0.0f, 0.0f};
+    h.sphere = 0;
     return h;
 }
 
@@ -308,7 +309,7 @@ __device__ __forceinline__ void trace_sample(const RenderParams& P, uint32_t x, 
         ok = trace_ray<MODE, false, COUNT>(P.scene, ray, ph, &pc.walk);
         if (ok) {
             Surf sf;
-            load_surf(P.scene, ray, ph, sf);
+            load_surf<true, MODE == 3>(P.scene, ray, ph, sf);
             c = surf_color(P.scene, sf);
         }
     }

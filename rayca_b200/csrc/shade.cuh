@@ -84,9 +84,33 @@ __device__ __forceinline__ void eval_material(const GpuSceneView& s, Surf& sf) {
     }
 }
 
-template <bool MATERIAL = true>
+template <bool MATERIAL = true, bool SPHERES = true>
 __device__ __forceinline__ void load_surf(const GpuSceneView& s, const RayD& ray, const HitD& h, Surf& sf) {
     const float4* q = s.tri_attr + 12 * (size_t)h.prim;
+    if (SPHERES && h.sphere) {
+        // BvhGeometry::Sphere: colour WHITE, uv (0,0) (primitive.rs:16-29); normal = normalize(N * normalize(
+        // inv * hit.point - centre)) with inv = Mat4::from(&Inversed(trs)), N = Mat3::from(&inv)^T (primitive.rs:183-190);
+        // the attr record carries inv rows 0..2 and N's rows (host_scene.cpp), the 4th row of inv is (0,0,0,1)
+        const float4 r0 = __ldg(q + 0), r1 = __ldg(q + 1), r2 = __ldg(q + 2);
+        const float4 n0 = __ldg(q + 3), n1 = __ldg(q + 4), n2 = __ldg(q + 5);
+        const V3 hp{((r0.x * h.p.x + r0.y * h.p.y) + r0.z * h.p.z) + r0.w * 1.0f, ((r1.x * h.p.x + r1.y * h.p.y) + r1.z * h.p.z) + r1.w * 1.0f,
+                    ((r2.x * h.p.x + r2.y * h.p.y) + r2.z * h.p.z) + r2.w * 1.0f};
+        const V3 mn = normalize(hp - V3{n0.w, n1.w, n2.w});
+        V3 wn; // Mat3 * Vec3 accumulates from 0.0 (mat3.rs:218-234)
+        wn.x = ((0.0f + n0.x * mn.x) + n0.y * mn.y) + n0.z * mn.z;
+        wn.y = ((0.0f + n1.x * mn.x) + n1.y * mn.y) + n1.z * mn.z;
+        wn.z = ((0.0f + n2.x * mn.x) + n2.y * mn.y) + n2.z * mn.z;
+        sf.geom_color = Col{1.0f, 1.0f, 1.0f, 1.0f};
+        sf.uvx = sf.uvy = 0.0f;
+        sf.mat = s.materials + __float_as_uint(__ldg(q + 9).w);
+        sf.point = h.p;
+        sf.ray_dir = ray.d;
+        sf.view_dir = -ray.d;
+        sf.normal = normalize(wn);
+        sf.next_origin = sf.point + sf.normal * kRayBias; // hit.rs:164-171
+        if (MATERIAL) eval_material(s, sf);
+        return;
+    }
     float u = h.u, v = h.v;
     float w = 1.0f - u - v;
     // bvh/triangle.rs:34-48 — v2*(1-u-v) + v0*u + v1*v with Color / Vec2 operators

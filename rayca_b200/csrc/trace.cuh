@@ -33,6 +33,7 @@ struct HitD {
     uint32_t prim; // global triangle index, ~0u = miss
     float u, v;
     V3 p;
+    uint32_t sphere; // the hit primitive is a sphere (BvhGeometry::Sphere): uv = 0, see load_surf
 };
 
 struct WalkCounters {
@@ -120,6 +121,7 @@ __device__ __forceinline__ bool walk(const GpuSceneView& s, const RayD& ray, Hit
         hit.u = bu;
         hit.v = bv;
         hit.p = bp;
+        hit.sphere = 0; // the reference-tree walks handle triangles only (scene_create refuses otherwise)
         return best != 0xFFFFFFFFu;
     };
 
@@ -213,7 +215,8 @@ __device__ __forceinline__ bool walk(const GpuSceneView& s, const RayD& ray, Hit
 //   min/max per axis is needed.  NaNs (0 * inf for a denormal direction lane) are dropped by
 //   fminf/fmaxf, which only ever widens the interval.
 constexpr float kSlabTol = 1.0e-5f;
-constexpr uint32_t kLeafFlag = 0x80000000u; // child reference: bit31 leaf, bits 28..30 count-1, bits 0..27 first
+// child reference: bit31 leaf, bits 28..30 count-1, bit 27 the leaf holds spheres, bits 0..26 first record
+constexpr uint32_t kLeafFlag = 0x80000000u, kSphereFlag = 0x08000000u;
 
 struct FastRay {
     float rdx, rdy, rdz;
@@ -245,12 +248,15 @@ __device__ __forceinline__ bool slab_fast(const float4 lo, const float4 hi, cons
     return ext >= entry && ext >= 0.0f;
 }
 
-template <bool COUNT>
+// SPHERES: the scene holds sphere primitives (kernel instantiation MODE 3); triangle-only scenes run the
+// instantiation without the sphere leaf code (it costs 6 % on the atrium frame when compiled in).
+template <bool COUNT, bool SPHERES>
 __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD& ray, HitD& hit, WalkCounters* wc, const bool ANY) {
     const V3 o = ray.o, d = ray.d;
     float best_t = ANY ? hit.t : __int_as_float(0x7f800000);
     uint32_t best = 0xFFFFFFFFu;
     float bu = 0.0f, bv = 0.0f, bden = 1.0f;
+    uint32_t bsphere = 0;
     uint32_t ok_leaf = 0xFFFFFFFFu; // last reference leaf whose exact slab test accepted this ray
 
     auto finish = [&]() -> bool {
@@ -259,7 +265,19 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
         hit.prim = best;
         hit.u = bu / bden; // uv = (u / |n|^2, v / |n|^2) (triangle.rs:152-153)
         hit.v = bv / bden;
-        hit.p = o + d * best_t; // Hit::point, the `p` of the winning test (triangle.rs:121)
+        hit.sphere = SPHERES ? bsphere : 0u;
+        if (SPHERES && bsphere) { // hit.point = trs * (inverse ray origin + dir * t) (sphere.rs:141,160-161)
+            const float4* a = s.tri_attr + 12 * (size_t)best;
+            const float4 wt = __ldg(a + 6), wq = __ldg(a + 7), ws = __ldg(a + 8);
+            const TrsF w{V3{wt.x, wt.y, wt.z}, Q4{wq.x, wq.y, wq.z, wq.w}, V3{ws.x, ws.y, ws.z}};
+            const Q4 qi = conj(w.q);
+            const V3 si = reciprocal(w.s);
+            const V3 lo = scale_point(rotate(o + (-w.t), qi), si);
+            const V3 ld = rotate(d, qi) * si;
+            hit.p = trs_point(w, lo + ld * best_t);
+        } else {
+            hit.p = o + d * best_t; // Hit::point, the `p` of the winning test (triangle.rs:121)
+        }
         return best != 0xFFFFFFFFu;
     };
     // A ray with an exactly-zero direction lane has rdir = 0 there (vec3.rs:195-216): both slab
@@ -328,8 +346,49 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
         }
         // leaf: Triangle::intersects (rayca-geometry/src/triangle.rs:84-159) on the 64-byte records
         // {n.xyz, d | v0, ref index | v1, ref leaf | v2, dot(n,n)}
-        {
-            const uint32_t first = cur & 0x0FFFFFFFu, count = ((cur >> 28) & 7u) + 1u;
+        if (SPHERES && (cur & kSphereFlag)) {
+            // Sphere::intersects (rayca-geometry/src/sphere.rs:101-163) on the 64-byte records
+            // {-t, r^2 | q^-1 | 1/s, ref index | centre, ref leaf}: the ray goes to model space by translate,
+            // rotate, scale (trs.rs:405-414 with ray.rs:74-91), then the geometric quadratic
+            const uint32_t first = cur & 0x07FFFFFFu, count = ((cur >> 28) & 7u) + 1u;
+            for (uint32_t i = first; i < first + count; ++i) {
+                const float4* q = fast_tri + 4 * (size_t)i;
+                const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+                if (COUNT) { wc->planes += 1; wc->tris += 1; }
+                const Q4 qi{q1.x, q1.y, q1.z, q1.w};
+                const V3 si{q2.x, q2.y, q2.z};
+                const V3 lo = scale_point(rotate(o + V3{q0.x, q0.y, q0.z}, qi), si);
+                const V3 ld = rotate(d, qi) * si;
+                const float a = dot(ld, ld);
+                const V3 c_to_r = lo - V3{q3.x, q3.y, q3.z};
+                const float b = dot(c_to_r, ld);
+                const float c = dot(c_to_r, c_to_r) - q0.w;
+                const float det = b * b - a * c;
+                if (det < 0.0f) continue;
+                const float det_sqrt = sqrtf(det);
+                const float t0 = (-b + det_sqrt) / a;
+                const float t1 = (-b - det_sqrt) / a;
+                if (t0 < 0.0f && t1 < 0.0f) continue;
+                float t;
+                if (t0 >= 0.0f && t1 >= 0.0f) t = fminf(t0, t1);
+                else if (t0 >= 0.0f) t = t0;
+                else t = t1;
+                const uint32_t id = __float_as_uint(q2.w);
+                if (ANY) {
+                    if (t < best_t && ref_leaf_accepts(__float_as_uint(q3.w))) return true;
+                } else if (t < best_t || (t == best_t && id < best && best != 0xFFFFFFFFu)) {
+                    if (ref_leaf_accepts(__float_as_uint(q3.w))) {
+                        best_t = t;
+                        best = id;
+                        bu = 0.0f;
+                        bv = 0.0f;
+                        bden = 1.0f;
+                        bsphere = 1;
+                    }
+                }
+            }
+        } else {
+            const uint32_t first = cur & 0x07FFFFFFu, count = ((cur >> 28) & 7u) + 1u;
             for (uint32_t i = first; i < first + count; ++i) {
                 const float4* q = fast_tri + 4 * (size_t)i;
                 const float4 q0 = __ldg(q);
@@ -363,6 +422,7 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
                         bu = u;
                         bv = v;
                         bden = q3.w;
+                        bsphere = 0;
                     }
                 }
             }
@@ -383,26 +443,27 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
 // starves on instruction fetch when the walk is inlined two or three times (measured 1.9 ms -> 1.25 ms
 // for the 1080p atrium frame, profiles/).  RAYCA_INLINE_WALK restores the inlined form for A/B runs.
 #ifndef RAYCA_INLINE_WALK
-template <bool COUNT>
+template <bool COUNT, bool SPHERES>
 __device__ __noinline__ bool walk_fast_shared(const GpuSceneView& s, const RayD& ray, HitD& hit, WalkCounters* wc, bool any) {
-    return walk_fast_body<COUNT>(s, ray, hit, wc, any);
+    return walk_fast_body<COUNT, SPHERES>(s, ray, hit, wc, any);
 }
-template <bool ANY, bool COUNT>
+template <bool ANY, bool COUNT, bool SPHERES>
 __device__ __forceinline__ bool walk_fast(const GpuSceneView& s, const RayD& ray, HitD& hit, WalkCounters* wc) {
-    return walk_fast_shared<COUNT>(s, ray, hit, wc, ANY);
+    return walk_fast_shared<COUNT, SPHERES>(s, ray, hit, wc, ANY);
 }
 #else
-template <bool ANY, bool COUNT>
+template <bool ANY, bool COUNT, bool SPHERES>
 __device__ __forceinline__ bool walk_fast(const GpuSceneView& s, const RayD& ray, HitD& hit, WalkCounters* wc) {
-    return walk_fast_body<COUNT>(s, ray, hit, wc, ANY);
+    return walk_fast_body<COUNT, SPHERES>(s, ray, hit, wc, ANY);
 }
 #endif
 
-// MODE 0: performance layer (product path); 1: reference tree, exhaustive, reference visiting rule;
+// MODE 0: performance layer (product path), 3: the same for scenes with spheres; 1: reference tree, exhaustive, reference visiting rule;
 // 2: reference tree, ordered + distance-culled ("flattened reference BVH").
 template <int MODE, bool ANY, bool COUNT>
 __device__ __forceinline__ bool trace_ray(const GpuSceneView& s, const RayD& ray, HitD& hit, WalkCounters* wc) {
-    if (MODE == 0) return walk_fast<ANY, COUNT>(s, ray, hit, wc);
+    if (MODE == 0) return walk_fast<ANY, COUNT, false>(s, ray, hit, wc);
+    if (MODE == 3) return walk_fast<ANY, COUNT, true>(s, ray, hit, wc);
     if (MODE == 1) return walk<false, ANY, COUNT>(s, ray, hit, wc);
     return walk<true, ANY, COUNT>(s, ray, hit, wc);
 }

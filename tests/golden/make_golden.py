@@ -112,7 +112,13 @@ SCENES = {
                     {"pt1": (PT1, 128, 128), "rt0": (RT0, 96, 96)}),
     "cubes_over_plane": (cubes_over_plane_scene, {"pt1": (PT1, 128, 128), "rt3": (RT3, 96, 96), "pt3": (dict(integrator=IntegratorStrategy.Pathtracer, max_depth=3), 64, 64)}),
     "suzanne": (lambda: gltf_scene("suzanne/suzanne.gltf"), {"pt1": (PT1, 128, 128), "rt0": (RT0, 96, 96), "pt2": (PT2, 64, 64)}),
-    "scene7": (None, {"sdtf": (None, 80, 60)}),
+    "scene7": ("sdtf/1/scene7.sdtf", {"sdtf": (None, 80, 60)}),
+    # spheres (BvhGeometry::Sphere) under the Raytracer with the files' own cameras, lights and Phong materials
+    # (rayca-soft/tests/sdtf.rs scene2..scene6); `nobvh` = the Config::bvh(false) those tests use
+    "dice": ("sdtf/1/scene2.sdtf", {"sdtf": (None, 160, 120), "nobvh": (dict(bvh=False), 96, 72)}),
+    "scene4": ("sdtf/1/scene4-specular.sdtf", {"sdtf": (None, 160, 120)}),
+    "scene5": ("sdtf/1/scene5.sdtf", {"sdtf": (None, 160, 120)}),
+    "scene6": ("sdtf/1/scene6.sdtf", {"sdtf": (None, 160, 120), "spp4": (dict(samples_per_pixel=4), 64, 48)}),
 }
 
 
@@ -136,8 +142,8 @@ def main(names):
             continue
         t0 = time.time()
         sdtf_cfg = None
-        if name == "scene7":
-            scene, sdtf_cfg = sdtf_scene("sdtf/1/scene7.sdtf")
+        if isinstance(builder, str):
+            scene, sdtf_cfg = sdtf_scene(builder)
         else:
             scene = builder()
         desc = scene.to_desc()
@@ -147,9 +153,8 @@ def main(names):
             cfg = Config()
             if sdtf_cfg is not None:
                 cfg.apply(sdtf_cfg)
-            else:
-                for k, v in kw.items():
-                    setattr(cfg, k, v)
+            for k, v in (kw or {}).items():
+                setattr(cfg, k, v)
             if cfg.bvh not in by_bvh:
                 by_bvh[cfg.bvh] = O.OracleScene(desc, bvh=cfg.bvh)
             out = render_case(by_bvh[cfg.bvh], cfg, w, h)

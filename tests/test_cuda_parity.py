@@ -71,7 +71,12 @@ def test_cuda_matches_golden(ctx, scene, case, traversal):
     h, w = z["hit_src"].shape
     sc = dev_scene(ctx, scene, cfg.bvh)
     opts = M.rayca_options(int(z["seed"][0]), traversal, 0, 0, 0, 0, 0)
-    rgba8, aux, st = sc.render(cfg, w, h, options=opts, want_aux=True)
+    try:
+        rgba8, aux, st = sc.render(cfg, w, h, options=opts, want_aux=True)
+    except R.RaycaError as e:
+        if traversal != R.TRAVERSAL_ORDERED and e.code == -2 and "triangle scenes only" in str(e):
+            pytest.skip("the reference-tree walks are triangle-only; sphere scenes run on the product walk")
+        raise
     stochastic = cfg.integrator == R.IntegratorStrategy.Pathtracer and cfg.max_depth > 1
     check_against(z, rgba8, aux, h, w, stochastic)
     rays = [int(x) for x in z["rays"]]
