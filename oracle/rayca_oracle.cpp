@@ -170,6 +170,8 @@ Color to_color(const float c[4]) { return {c[0], c[1], c[2], c[3]}; }
 struct ModelDrawInfo {
     std::vector<uint32_t> mesh_nodes;      // world_trs indices, traversal order
     std::vector<uint32_t> mesh_node_local; // model-local node index
+    std::vector<uint32_t> quad_nodes;      // world_trs indices of quad-light nodes (scene.rs:265-272)
+    std::vector<uint32_t> quad_lights;     // their global light indices
     bool used = false;
 };
 
@@ -199,6 +201,11 @@ struct Flattener {
             ld.light = m.light_offset + (uint32_t)n.light;
             ld.node_trs = to_trs(n.trs);
             s.light_draws.push_back(ld);
+            if (d.lights[ld.light].kind == RAYCA_LIGHT_QUAD) { // the quad becomes two emissive triangles of this model
+                mdi[model_index].quad_nodes.push_back(key);
+                mdi[model_index].quad_lights.push_back(ld.light);
+                mdi[model_index].used = true;
+            }
         }
         if (n.camera >= 0 && !s.has_camera) { // camera_draw_infos[0] (scene.rs:110)
             s.has_camera = true;
@@ -291,6 +298,46 @@ void emit_mesh_prims(Scene& s, const rayca_scene_desc& d, uint32_t model_index, 
             p.wmax = mx;
             out.push_back(p);
         }
+    }
+}
+
+// BvhPrimitive::from_quad_light (bvh/primitive.rs:310-346): triangles [a, d, b] and [a, c, d] with a = origin,
+// b = ab, d = ab + ac, c = ac in the light node's space; vertex normal = the quad normal, untransformed;
+// colour WHITE, uv / tangents zero (VertexExtBuilder defaults); material = the light's emissive material
+void emit_quad_prims(Scene& s, const rayca_scene_desc& d, uint32_t model_index, uint32_t light_index, uint32_t trs_key,
+                     std::vector<Prim>& out) {
+    const rayca_light& l = d.lights[light_index];
+    const Trs& trs = s.world_trs[trs_key];
+    Vec3 ab{l.ab[0], l.ab[1], l.ab[2]}, ac{l.ac[0], l.ac[1], l.ac[2]};
+    Vec3 normal = normalized(cross(ab, ac)); // QuadLight::get_normal (quad.rs:36-38)
+    Point3 a{0, 0, 0};
+    Point3 b = a + ab, dd = (a + ab) + ac, c = a + ac;
+    Point3 tri[2][3] = {{a, dd, b}, {a, c, dd}};
+    for (int t = 0; t < 2; ++t) {
+        Prim p{};
+        for (int k = 0; k < 3; ++k) {
+            p.v[k] = tri[t][k];
+            p.ext[k].color = WHITE;
+            p.ext[k].normal = normal;
+            p.ext[k].tangent = {0, 0, 0};
+            p.ext[k].bitangent = {0, 0, 0};
+            p.ext[k].uv = {0, 0};
+        }
+        p.centroid = ((to_vec3(p.v[0]) + to_vec3(p.v[1])) + to_vec3(p.v[2])) * 0.3333f;
+        p.trs = trs_key;
+        p.model = model_index;
+        p.material = l.material;
+        p.src = (uint32_t)out.size();
+        for (int k = 0; k < 3; ++k) p.wv[k] = transform_point(trs, p.v[k]);
+        p.wcentroid = transform_vec(trs, p.centroid);
+        Point3 mn{F32_MAX, F32_MAX, F32_MAX}, mx{F32_MIN, F32_MIN, F32_MIN};
+        for (int k = 0; k < 3; ++k) {
+            mn = {minf(mn.x, p.wv[k].x), minf(mn.y, p.wv[k].y), minf(mn.z, p.wv[k].z)};
+            mx = {maxf(mx.x, p.wv[k].x), maxf(mx.y, p.wv[k].y), maxf(mx.z, p.wv[k].z)};
+        }
+        p.wmin = mn;
+        p.wmax = mx;
+        out.push_back(p);
     }
 }
 
@@ -1242,6 +1289,126 @@ struct Renderer {
         return true;
     }
 
+    // ---- QuadLight (rayca-model/src/light/quad.rs); `trs` is the light node's LOCAL trs
+    static Point3 quad_corner(const rayca_light& l, const Trs& trs, int k) { // get_a (quad.rs:48-57)
+        Point3 a = to_point3(trs_get_translation(trs));
+        Vec3 ab{l.ab[0], l.ab[1], l.ab[2]}, ac{l.ac[0], l.ac[1], l.ac[2]};
+        switch (k & 3) {
+            case 0: return a;
+            case 1: return a + ab;
+            case 2: return (a + ab) + ac;
+            default: return a + ac;
+        }
+    }
+    static Vec3 quad_normal(const rayca_light& l) { // quad.rs:36-38
+        return normalized(cross(Vec3{l.ab[0], l.ab[1], l.ab[2]}, Vec3{l.ac[0], l.ac[1], l.ac[2]}));
+    }
+    static float quad_area(const rayca_light& l) { // quad.rs:40-46 (sin_theta = 1 - cos_theta, as written)
+        Vec3 ab{l.ab[0], l.ab[1], l.ab[2]}, ac{l.ac[0], l.ac[1], l.ac[2]};
+        float ab_len = len(ab), ac_len = len(ac);
+        float cos_theta = dot(ab, ac) / (ab_len * ac_len);
+        float sin_theta = 1.0f - cos_theta;
+        return sin_theta * ab_len * ac_len;
+    }
+    // get_radiance / theta / gamma / get_intensity (quad.rs:72-104): edge i runs from corner i to corner i+1
+    static Color quad_intensity(const rayca_light& l, const Trs& trs, Point3 frag, Vec3 n) {
+        Vec3 ret{0, 0, 0};
+        for (int e = 0; e < 4; ++e) {
+            Point3 pa = quad_corner(l, trs, e), pb = quad_corner(l, trs, e + 1);
+            float theta = std::acos(dot(normalized(pa - frag), normalized(pb - frag)));
+            Vec3 gamma = normalized(cross(pa - frag, pb - frag));
+            ret = ret + theta * gamma;
+        }
+        ret = ret / 2.0f;
+        float irradiance = dot(ret, n);
+        return l.intensity * to_color(l.color) * irradiance;
+    }
+    // Light::get_intensity (light/mod.rs:54-60)
+    Color light_intensity(const rayca_light& l, const Trs& trs, Point3 frag, Vec3 n) {
+        if (l.kind == RAYCA_LIGHT_DIRECTIONAL) return l.intensity * to_color(l.color);
+        if (l.kind == RAYCA_LIGHT_POINT) return point_intensity(l, trs, frag);
+        return quad_intensity(l, trs, frag, n);
+    }
+
+    // integrator/analyticdirect.rs:16-49
+    bool analytic_trace(const Ray& ray, uint32_t depth, Color& out, Hit* primary) {
+        if (depth >= cfg.c.max_depth) return false;
+        Hit h;
+        if (!tracer.intersects(ray, h)) return false;
+        if (primary) *primary = h;
+        HitInfo hit(s, h);
+        Color ambient_and_emission = hit.get_color();
+        if (hit.is_emissive()) {
+            out = ambient_and_emission;
+            return true;
+        }
+        Vec3 n = hit.get_normal();
+        Color light_contribution = BLACK;
+        for (const LightDraw& ld : s.light_draws)
+            light_contribution = light_contribution + light_intensity(s.lights[ld.light], ld.node_trs, hit.hit.point, n);
+        Color f = hit.get_diffuse() * FRAC_1_PI;
+        out = f * light_contribution;
+        return true;
+    }
+
+    // integrator/direct.rs:16-88; QuadLight::get_random_point (quad.rs:117-137) draws from the keyed RNG:
+    // counter (pixel, sample, depth 0, 2 * (light * light_samples + i) + {0, 1})
+    bool direct_trace(const Ray& ray, uint32_t depth, uint32_t pixel, uint32_t sample, Color& out, Hit* primary) {
+        if (depth >= cfg.c.max_depth) return false;
+        Hit h;
+        if (!tracer.intersects(ray, h)) return false;
+        if (primary) *primary = h;
+        HitInfo hit(s, h);
+        hit.pixel = pixel;
+        hit.sample = sample;
+        Color ambient_and_emissive = hit.get_color();
+        if (hit.is_emissive()) {
+            out = ambient_and_emissive;
+            return true;
+        }
+        Color light_contribution = BLACK;
+        const uint32_t ls = cfg.c.light_samples;
+        const uint32_t strate_count = cfg.c.light_stratify ? (uint32_t)std::sqrt((float)ls) : 1u; // config.rs:73-79
+        uint32_t li = 0;
+        for (const LightDraw& ld : s.light_draws) {
+            const rayca_light& l = s.lights[ld.light];
+            const uint32_t light_slot = li++;
+            if (l.kind != RAYCA_LIGHT_QUAD) continue;
+            Vec3 ab{l.ab[0], l.ab[1], l.ab[2]}, ac{l.ac[0], l.ac[1], l.ac[2]};
+            Color ldc = BLACK;
+            for (uint32_t i = 0; i < ls; ++i) {
+                Vec3 step1 = ab / (float)strate_count, step2 = ac / (float)strate_count;
+                float u1 = rng_f32(cfg.seed, pixel, sample, 0, 2 * (light_slot * ls + i)) / (float)strate_count;
+                float u2 = rng_f32(cfg.seed, pixel, sample, 0, 2 * (light_slot * ls + i) + 1) / (float)strate_count;
+                Point3 x1 = (quad_corner(l, ld.node_trs, 0) + (u1 * ab)) + (u2 * ac);
+                if (cfg.c.light_stratify) {
+                    float i1 = (float)(i % strate_count), i2 = (float)(i / strate_count);
+                    x1 = x1 + ((step1 * i1) + (step2 * i2));
+                }
+                Vec3 x1_to_hit = x1 - hit.hit.point;
+                Vec3 omega_i = normalized(x1_to_hit);
+                Ray shadow = make_ray(hit.get_next_ray_origin(), omega_i);
+                tracer.rays->rays_shadow++;
+                Hit sh;
+                if (tracer.intersects(shadow, sh)) {
+                    HitInfo shi(s, sh);
+                    if (!shi.is_emissive()) continue;
+                }
+                Color brdf = get_brdf(hit, omega_i);
+                float r = len(x1_to_hit);
+                float r_squared = r * r; // len().powf(2.0)
+                float d_omega_i = dot(quad_normal(l), omega_i) / r_squared;
+                ldc = ldc + (brdf * dot(hit.get_normal(), omega_i)) * d_omega_i;
+            }
+            Color lic = l.intensity * to_color(l.color);
+            float area = quad_area(l);
+            ldc = ((lic * area) * ldc) / (float)ls;
+            light_contribution = light_contribution + ldc;
+        }
+        out = light_contribution;
+        return true;
+    }
+
     // integrator/flat.rs:16-28
     bool flat_trace(const Ray& ray, Color& out, Hit* primary) {
         Hit h;
@@ -1260,6 +1427,8 @@ struct Renderer {
             case RAYCA_INTEGRATOR_PATHTRACER: ok = pathtracer_trace(ray, 0, true, pixel, sample, c, primary); break;
             case RAYCA_INTEGRATOR_RAYTRACER: ok = raytracer_trace(ray, 0, c, primary); break;
             case RAYCA_INTEGRATOR_FLAT: ok = flat_trace(ray, c, primary); break;
+            case RAYCA_INTEGRATOR_ANALYTIC_DIRECT: ok = analytic_trace(ray, 0, c, primary); break;
+            case RAYCA_INTEGRATOR_DIRECT: ok = direct_trace(ray, 0, pixel, sample, c, primary); break;
             default: status = RAYCA_E_UNSUPPORTED; break;
         }
         hit_any = ok && primary && primary->blas != ~0u;
@@ -1315,6 +1484,8 @@ int rayca_oracle_scene_create(const rayca_scene_desc* desc, uint32_t bvh, rayca_
         blas.max_depth = bvh ? 255 : 0; // scene.rs:95-99
         for (size_t k = 0; k < f.mdi[m].mesh_nodes.size(); ++k)
             emit_mesh_prims(*s, d, m, f.mdi[m].mesh_node_local[k], f.mdi[m].mesh_nodes[k], blas.prims);
+        for (size_t k = 0; k < f.mdi[m].quad_nodes.size(); ++k) // primitive.rs:363-367: area lights after the meshes
+            emit_quad_prims(*s, d, m, f.mdi[m].quad_lights[k], f.mdi[m].quad_nodes[k], blas.prims);
         build_blas(blas);
         s->blas_nodes.push_back({(uint32_t)s->blass.size()});
         s->blass.push_back(std::move(blas));
@@ -1388,7 +1559,10 @@ int rayca_oracle_render(rayca_oracle_scene* s, const rayca_config* config, const
         bool needs_indirect = cfg.c.russian_roulette || cfg.c.max_depth > (cfg.c.direct_sampler != RAYCA_SAMPLER_NONE ? 1u : 0u);
         if (needs_indirect && cfg.c.indirect_sampler != RAYCA_SAMPLER_COSINE) return RAYCA_E_UNSUPPORTED;
         if (cfg.c.russian_roulette) return RAYCA_E_UNSUPPORTED;
-    } else if (cfg.c.integrator != RAYCA_INTEGRATOR_RAYTRACER && cfg.c.integrator != RAYCA_INTEGRATOR_FLAT) {
+    } else if (cfg.c.integrator == RAYCA_INTEGRATOR_DIRECT) {
+        if (cfg.c.light_samples == 0) return RAYCA_E_INVALID_ARG;
+    } else if (cfg.c.integrator != RAYCA_INTEGRATOR_RAYTRACER && cfg.c.integrator != RAYCA_INTEGRATOR_FLAT &&
+               cfg.c.integrator != RAYCA_INTEGRATOR_ANALYTIC_DIRECT) {
         return RAYCA_E_UNSUPPORTED;
     }
     uint32_t row_begin = rows ? rows[0] : 0, row_end = rows ? std::min(rows[1], height) : height;
