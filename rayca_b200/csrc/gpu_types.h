@@ -50,6 +50,13 @@ struct alignas(16) GpuLight {
     uint32_t kind;
     float dir[3];   // directional: -rotate(X_AXIS, node rotation) (light/directional.rs:47-51)
     uint32_t pad;
+    // quad (rayca-model/src/light/quad.rs): corner a = pos, edges ab / ac, normalize(ab x ac), get_area()
+    float ab[3];
+    float area;
+    float ac[3];
+    uint32_t pad2;
+    float normal[3];
+    uint32_t pad3;
 };
 
 struct GpuCamera {

@@ -117,15 +117,20 @@ struct MeshDraw {
     uint32_t node_local;
     TrsF world;
 };
+struct QuadDraw { // a quad-light node: becomes two emissive triangles of its model (scene.rs:265-272)
+    uint32_t light; // global light index
+    TrsF world;
+};
 
 struct Flatten {
     const rayca_scene_desc& d;
     HostScene& out;
     std::vector<std::vector<MeshDraw>> mesh_draws; // per model, traversal order
+    std::vector<std::vector<QuadDraw>> quad_draws;
     std::string err;
     int status = RAYCA_OK;
 
-    explicit Flatten(const rayca_scene_desc& desc, HostScene& o) : d(desc), out(o), mesh_draws(desc.model_count) {}
+    explicit Flatten(const rayca_scene_desc& desc, HostScene& o) : d(desc), out(o), mesh_draws(desc.model_count), quad_draws(desc.model_count) {}
 
     void model_nodes(const TrsF& parent, uint32_t node, uint32_t mi, int depth) {
         const rayca_model& m = d.models[mi];
@@ -145,6 +150,18 @@ struct Flatten {
             g.pos[0] = p.x; g.pos[1] = p.y; g.pos[2] = p.z;
             V3 dir = -rotate(V3{1.0f, 0.0f, 0.0f}, local.q);
             g.dir[0] = dir.x; g.dir[1] = dir.y; g.dir[2] = dir.z;
+            if (l.kind == RAYCA_LIGHT_QUAD) {
+                V3 ab{l.ab[0], l.ab[1], l.ab[2]}, ac{l.ac[0], l.ac[1], l.ac[2]};
+                V3 nq = normalize(cross(ab, ac)); // QuadLight::get_normal (quad.rs:36-38)
+                float ab_len = length(ab), ac_len = length(ac);
+                float cos_theta = dot(ab, ac) / (ab_len * ac_len); // get_area (quad.rs:40-46), sin = 1 - cos as written
+                float sin_theta = 1.0f - cos_theta;
+                std::memcpy(g.ab, l.ab, sizeof(g.ab));
+                std::memcpy(g.ac, l.ac, sizeof(g.ac));
+                g.normal[0] = nq.x; g.normal[1] = nq.y; g.normal[2] = nq.z;
+                g.area = sin_theta * ab_len * ac_len;
+                quad_draws[mi].push_back(QuadDraw{m.light_offset + (uint32_t)n.light, cur});
+            }
             out.lights.push_back(g);
         }
         if (n.camera >= 0 && !out.has_camera) { // camera_draw_infos[0] (scene.rs:109-112)
@@ -282,7 +299,7 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
     // ---- BvhScene::from_scene: one BLAS per model that owns mesh nodes, ascending model handle
     // (the reference iterates a HashMap; the order only matters for exact cross-BLAS depth ties)
     for (uint32_t mi = 0; mi < d.model_count; ++mi) {
-        if (f.mesh_draws[mi].empty()) continue;
+        if (f.mesh_draws[mi].empty() && f.quad_draws[mi].empty()) continue;
         const rayca_model& m = d.models[mi];
         HostBlas blas;
         blas.model = mi;
@@ -359,6 +376,40 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
                     ht.src = (uint32_t)(base + (size_t)t);
                 }
                 if (bad) { err = "vertex index out of range"; return RAYCA_E_INVALID_ARG; }
+            }
+        }
+        // BvhPrimitive::from_quad_light (primitive.rs:310-346), after the meshes (primitive.rs:363-367): triangles
+        // [a, d, b] and [a, c, d], a = origin of the light node; vertex normal = quad normal (not transformed),
+        // colour WHITE, uv / tangents zero; material = the light's emissive Phong material
+        for (const QuadDraw& qd : f.quad_draws[mi]) {
+            const rayca_light& l = d.lights[qd.light];
+            V3 ab{l.ab[0], l.ab[1], l.ab[2]}, ac{l.ac[0], l.ac[1], l.ac[2]};
+            V3 nq = normalize(cross(ab, ac));
+            V3 a{0.0f, 0.0f, 0.0f};
+            V3 b = a + ab, dd = (a + ab) + ac, c = a + ac;
+            V3 tri[2][3] = {{a, dd, b}, {a, c, dd}};
+            uint32_t material = 0;
+            if (l.material >= 0 && (uint32_t)l.material < m.material_count) material = model_mat_base[mi] + (uint32_t)l.material;
+            for (int t = 0; t < 2; ++t) {
+                HostTri ht{};
+                HostAttr ha{};
+                for (int k = 0; k < 3; ++k) {
+                    ht.v[k] = trs_point(qd.world, tri[t][k]);
+                    for (int ch = 0; ch < 4; ++ch) ha.color[k][ch] = 1.0f;
+                    ha.normal[k] = nq;
+                }
+                ha.material = material;
+                V3 cen = ((tri[t][0] + tri[t][1]) + tri[t][2]) * 0.3333f;
+                ht.centroid = trs_vec(qd.world, cen);
+                ht.bmin = V3{fminf(fminf(fminf(kF32Max, ht.v[0].x), ht.v[1].x), ht.v[2].x),
+                             fminf(fminf(fminf(kF32Max, ht.v[0].y), ht.v[1].y), ht.v[2].y),
+                             fminf(fminf(fminf(kF32Max, ht.v[0].z), ht.v[1].z), ht.v[2].z)};
+                ht.bmax = V3{fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].x), ht.v[1].x), ht.v[2].x),
+                             fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].y), ht.v[1].y), ht.v[2].y),
+                             fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].z), ht.v[1].z), ht.v[2].z)};
+                ht.src = (uint32_t)blas.tris.size();
+                blas.tris.push_back(ht);
+                blas.attrs.push_back(ha);
             }
         }
         phase.lap("emit triangles");

@@ -253,6 +253,105 @@ __device__ __forceinline__ bool raytracer(const RenderParams& P, RayD ray, Col& 
     return true;
 }
 
+// ---- QuadLight (rayca-model/src/light/quad.rs): corner k of a, a+ab, (a+ab)+ac, a+ac (get_a / get_b :48-70)
+__device__ __forceinline__ V3 quad_corner(const GpuLight& L, int k) {
+    const V3 a{L.pos[0], L.pos[1], L.pos[2]}, ab{L.ab[0], L.ab[1], L.ab[2]}, ac{L.ac[0], L.ac[1], L.ac[2]};
+    switch (k & 3) {
+        case 0: return a;
+        case 1: return a + ab;
+        case 2: return (a + ab) + ac;
+        default: return a + ac;
+    }
+}
+// Light::get_intensity (light/mod.rs:54-60); quad: theta / gamma / get_radiance / get_intensity (quad.rs:72-104)
+__device__ __forceinline__ Col light_intensity_at(const GpuLight& L, V3 frag, V3 n) {
+    const Col lc = cscale(Col{L.color[0], L.color[1], L.color[2], L.color[3]}, L.intensity);
+    if (L.kind == RAYCA_LIGHT_DIRECTIONAL) return lc;
+    if (L.kind == RAYCA_LIGHT_POINT) return point_intensity(L, frag);
+    V3 ret{0.0f, 0.0f, 0.0f};
+#pragma unroll 1
+    for (int e = 0; e < 4; ++e) {
+        const V3 ra = quad_corner(L, e) - frag, rb = quad_corner(L, e + 1) - frag;
+        const float theta = acosf(dot(normalize(ra), normalize(rb)));
+        ret = ret + theta * normalize(cross(ra, rb));
+    }
+    ret = ret / 2.0f;
+    return cscale(lc, dot(ret, n));
+}
+__device__ __forceinline__ bool surf_emissive(const Surf& sf) { // primitive.rs:122-130 / phong.rs:50-52
+    return sf.mat->kind == RAYCA_MATERIAL_PHONG && sf.mat->emissive;
+}
+
+// AnalyticDirect::trace (integrator/analyticdirect.rs:16-49)
+template <int MODE, bool COUNT>
+__device__ __forceinline__ bool analytic_direct(const RenderParams& P, const RayD& ray, Col& out, HitD& primary, PixelCounters& pc) {
+    const GpuSceneView& s = P.scene;
+    if (0u >= P.cfg.max_depth) return false;
+    if (!trace_ray<MODE, false, COUNT>(s, ray, primary, &pc.walk)) return false;
+    Surf sf;
+    load_surf<true, MODE == 3>(s, ray, primary, sf);
+    if (surf_emissive(sf)) {
+        out = surf_color(s, sf);
+        return true;
+    }
+    Col lc{0.0f, 0.0f, 0.0f, 1.0f};
+    for (uint32_t li = 0; li < s.light_count; ++li) lc = cadd(lc, light_intensity_at(s.lights[li], sf.point, sf.normal));
+    out = cmul(cscale(surf_diffuse(s, sf), kFrac1Pi), lc);
+    return true;
+}
+
+// Direct::trace (integrator/direct.rs:16-88) with QuadLight::get_random_point (quad.rs:117-137); the two uniform
+// numbers of light sample i of light l come from the keyed RNG at (pixel, sample, depth 0, 2*(l*light_samples+i)+{0,1})
+template <int MODE, bool COUNT>
+__device__ __forceinline__ bool direct_lighting(const RenderParams& P, const RayD& ray, uint32_t pixel, uint32_t sample, Col& out,
+                                                HitD& primary, PixelCounters& pc) {
+    const GpuSceneView& s = P.scene;
+    if (0u >= P.cfg.max_depth) return false;
+    if (!trace_ray<MODE, false, COUNT>(s, ray, primary, &pc.walk)) return false;
+    Surf sf;
+    load_surf<true, MODE == 3>(s, ray, primary, sf);
+    if (surf_emissive(sf)) {
+        out = surf_color(s, sf);
+        return true;
+    }
+    const uint32_t ls = P.cfg.light_samples;
+    const uint32_t strate = P.cfg.light_stratify ? __float2uint_rz(sqrtf((float)ls)) : 1u; // config.rs:73-79
+    const float fstrate = (float)strate;
+    Col lc{0.0f, 0.0f, 0.0f, 1.0f};
+    for (uint32_t li = 0; li < s.light_count; ++li) {
+        const GpuLight& L = s.lights[li];
+        if (L.kind != RAYCA_LIGHT_QUAD) continue;
+        const V3 ab{L.ab[0], L.ab[1], L.ab[2]}, ac{L.ac[0], L.ac[1], L.ac[2]}, qn{L.normal[0], L.normal[1], L.normal[2]};
+        const V3 step1 = ab / fstrate, step2 = ac / fstrate;
+        Col ld{0.0f, 0.0f, 0.0f, 1.0f};
+#pragma unroll 1
+        for (uint32_t i = 0; i < ls; ++i) {
+            const float u1 = rng_f32(P.seed, pixel, sample, 0, 2u * (li * ls + i)) / fstrate;
+            const float u2 = rng_f32(P.seed, pixel, sample, 0, 2u * (li * ls + i) + 1u) / fstrate;
+            V3 x1 = (quad_corner(L, 0) + u1 * ab) + u2 * ac;
+            if (P.cfg.light_stratify) x1 = x1 + (step1 * (float)(i % strate) + step2 * (float)(i / strate));
+            const V3 to_hit = x1 - sf.point;
+            const V3 omega = normalize(to_hit);
+            const RayD shadow = make_ray(sf.next_origin, omega);
+            HitD sh;
+            pc.shadow++;
+            if (trace_ray<MODE, false, COUNT>(s, shadow, sh, &pc.walk)) { // seen unless the closest hit is not a light
+                const GpuMaterial* sm = s.materials + __float_as_uint(__ldg(s.tri_attr + 12 * (size_t)sh.prim + 9).w);
+                if (!(sm->kind == RAYCA_MATERIAL_PHONG && sm->emissive)) continue;
+            }
+            const Col brdf = surf_brdf(s, sf, omega);
+            const float r = length(to_hit);
+            const float d_omega = dot(qn, omega) / (r * r); // len().powf(2.0)
+            ld = cadd(ld, cscale(cscale(brdf, dot(sf.normal, omega)), d_omega));
+        }
+        const Col li_c = cscale(Col{L.color[0], L.color[1], L.color[2], L.color[3]}, L.intensity);
+        ld = cdiv(cmul(cscale(li_c, L.area), ld), (float)ls);
+        lc = cadd(lc, ld);
+    }
+    out = lc;
+    return true;
+}
+
 // `(c * 255.0).clamp(0.0, 255.0) as u8` (color/rgba8.rs:75-84): truncation, NaN -> 0
 __device__ __forceinline__ unsigned char quantize(float c) {
     float v = clampf(c * 255.0f, 0.0f, 255.0f);
@@ -305,6 +404,10 @@ __device__ __forceinline__ void trace_sample(const RenderParams& P, uint32_t x, 
         ok = pathtracer<MODE, COUNT, BOUNCE>(P, ray, pixel, i, c, ph, pc);
     } else if (INTEGRATOR == RAYCA_INTEGRATOR_RAYTRACER) {
         ok = raytracer<MODE, COUNT>(P, ray, c, ph, pc);
+    } else if (INTEGRATOR == RAYCA_INTEGRATOR_ANALYTIC_DIRECT) {
+        ok = analytic_direct<MODE, COUNT>(P, ray, c, ph, pc);
+    } else if (INTEGRATOR == RAYCA_INTEGRATOR_DIRECT) {
+        ok = direct_lighting<MODE, COUNT>(P, ray, pixel, i, c, ph, pc);
     } else { // Flat (integrator/flat.rs:16-28)
         ok = trace_ray<MODE, false, COUNT>(P.scene, ray, ph, &pc.walk);
         if (ok) {

@@ -119,6 +119,12 @@ SCENES = {
     "scene4": ("sdtf/1/scene4-specular.sdtf", {"sdtf": (None, 160, 120)}),
     "scene5": ("sdtf/1/scene5.sdtf", {"sdtf": (None, 160, 120)}),
     "scene6": ("sdtf/1/scene6.sdtf", {"sdtf": (None, 160, 120), "spp4": (dict(samples_per_pixel=4), 64, 48)}),
+    # quad lights (two emissive triangles each) under AnalyticDirect / Direct (rayca-soft/tests/sdtf.rs, sdtf/2)
+    "analytic": ("sdtf/2/analytic.sdtf", {"sdtf": (None, 160, 120)}),
+    "direct9": ("sdtf/2/direct9.sdtf", {"sdtf": (None, 120, 90)}),
+    "direct3x3": ("sdtf/2/direct3x3.sdtf", {"sdtf": (None, 120, 90)}),
+    "cornell": ("sdtf/2/cornell.sdtf", {"sdtf": (None, 120, 120), "analytic": (dict(integrator=IntegratorStrategy.AnalyticDirect), 96, 96)}),
+    "quadsphere": ("sdtf/2/sphere.sdtf", {"sdtf": (None, 120, 90)}),
 }
 
 
