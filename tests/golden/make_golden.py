@@ -125,6 +125,7 @@ SCENES = {
     "direct3x3": ("sdtf/2/direct3x3.sdtf", {"sdtf": (None, 120, 90)}),
     "cornell": ("sdtf/2/cornell.sdtf", {"sdtf": (None, 120, 120), "analytic": (dict(integrator=IntegratorStrategy.AnalyticDirect), 96, 96)}),
     "quadsphere": ("sdtf/2/sphere.sdtf", {"sdtf": (None, 120, 90)}),
+    "dragon": ("sdtf/2/dragon.sdtf", {"ls4": (dict(light_samples=4), 48, 36)}),  # 100,002 triangles + 2 quad lights
 }
 
 

@@ -258,3 +258,32 @@ def test_host_render_bands_equal_single_launch(ctx, atrium):
     assert st.rays_primary == w * h and st.kernel_launches == 4
     c = atrium.last_counters()
     assert c.rays_primary == w * h and c.rays_shadow == st.rays_shadow
+
+
+def test_dragon_direct_lighting_at_full_size(ctx):
+    """The reference's sdtf/2/dragon.sdtf at its own 640x480 with its own settings (Direct integrator, two quad
+    lights, 25 stratified light samples: 0.3 M primary + 15 M closest-hit shadow rays over 100,002 triangles): the
+    product walk and the reference-tree ordered walk agree bit for bit."""
+    sc = dev_scene(ctx, "dragon")
+    cfg = R.Config(integrator=R.IntegratorStrategy.Direct, light_samples=25, light_stratify=True, max_depth=5)
+    a8, a, sa = sc.render(cfg, 640, 480, options=M.rayca_options(0x5EED, R.TRAVERSAL_ORDERED, 0, 0, 0, 0, 0), want_aux=True)
+    b8, b, sb = sc.render(cfg, 640, 480, options=M.rayca_options(0x5EED, R.TRAVERSAL_REFERENCE_ORDERED, 0, 0, 0, 0, 0), want_aux=True)
+    for x, y in zip(_bits(a), _bits(b)):
+        assert np.array_equal(x, y)
+    assert np.array_equal(a8, b8)
+    assert sa.rays_shadow == sb.rays_shadow and sa.rays_shadow > 10_000_000
+
+
+def test_thousand_spheres_at_full_size(ctx):
+    """sdtf/1/scene5.sdtf (1000 spheres, Raytracer depth 5) at 1280x960: deterministic, every hit is a sphere hit,
+    and the static and persistent schedules agree."""
+    sc = dev_scene(ctx, "scene5")
+    cfg = R.Config(integrator=R.IntegratorStrategy.Raytracer, max_depth=5)
+    a8, a, sa = sc.render(cfg, 1280, 960, want_aux=True)
+    b8, b, sb = sc.render(cfg, 1280, 960, options=M.rayca_options(0, 0, 0, 0, 0, R.FLAG_PERSISTENT, 0), want_aux=True)
+    for x, y in zip(_bits(a), _bits(b)):
+        assert np.array_equal(x, y)
+    assert np.array_equal(a8, b8)
+    hit = a.hit_src != 0xFFFFFFFF
+    assert 0.2 < hit.mean() < 0.9 and np.all(a.uv.reshape(-1, 2)[hit] == 0.0)
+    assert sa.rays_secondary > 0 and sa.rays_shadow == sb.rays_shadow
