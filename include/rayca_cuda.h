@@ -337,6 +337,11 @@ typedef struct rayca_scene rayca_scene;
 int rayca_cuda_host_alloc(size_t bytes, void** out);
 void rayca_cuda_host_free(void* p);
 
+/* Measurement aid (bench.py): best-of-5 streaming read bandwidth over a `bytes` buffer read `reps` times with
+ * 128-bit loads from all SMs.  A buffer well inside the 126 MB L2 gives the L2 -> SM read peak that bounds the
+ * walk on L2-resident scenes; a buffer of several GB gives the HBM read peak. */
+int rayca_cuda_probe_read_bandwidth(rayca_ctx* ctx, size_t bytes, uint32_t reps, double* gb_per_s);
+
 /* Binds a context to one CUDA device (one process per GPU). */
 int rayca_cuda_init(int device, rayca_ctx** out);
 void rayca_cuda_shutdown(rayca_ctx* ctx);

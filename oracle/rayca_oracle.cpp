@@ -88,6 +88,7 @@ struct Blas {
     std::vector<Prim> prims;
     uint32_t model = 0;
     uint8_t max_depth = 255;
+    bool has_spheres = false; // lets triangle-only BLAS keep the branch-free leaf loop (it is the timed CPU baseline)
 };
 
 struct TlasNode {
@@ -561,7 +562,7 @@ struct Tracer {
     Counters* cnt;  // non-null only when walk records are being counted
 
     // Sphere::intersects + intersects_impl (rayca-geometry/src/sphere.rs:101-163)
-    inline bool sphere_intersects(const Prim& p, const Ray& ray, float& t_out, Point3& pt, Vec2& uv) const {
+    __attribute__((noinline)) bool sphere_intersects(const Prim& p, const Ray& ray, float& t_out, Point3& pt, Vec2& uv) const {
         const Trs& trs = s.world_trs[p.trs];
         Ray r = inverse_transform_ray(trs, ray);
         float a = dot(r.dir, r.dir);
@@ -585,8 +586,18 @@ struct Tracer {
         return true;
     }
 
+    template <bool MAY_BE_SPHERE>
     inline bool prim_intersects(const Prim& p, const Ray& ray, float& t, Point3& pt, Vec2& uv) const {
-        if (p.sphere) return sphere_intersects(p, ray, t, pt, uv);
+        if (MAY_BE_SPHERE && p.sphere) { // own temporaries: the triangle path keeps its results in registers
+            float st;
+            Point3 spt;
+            Vec2 suv;
+            if (!sphere_intersects(p, ray, st, spt, suv)) return false;
+            t = st;
+            pt = spt;
+            uv = suv;
+            return true;
+        }
         if (faithful) {
             const Trs& trs = s.world_trs[p.trs]; // get_world_trs (primitive.rs:96)
             return triangle_intersects_world(transform_point(trs, p.v[0]), transform_point(trs, p.v[1]),
@@ -596,6 +607,9 @@ struct Tracer {
     }
 
     // blas.rs:129-176 (recursive, both children always visited, strict '<')
+    // SPH: the BLAS holds spheres; triangle-only BLAS get an instantiation without any sphere code, which is
+    // what the timed CPU baseline runs (with the branch compiled in, gcc produced a 1.8x slower triangle loop)
+    template <bool SPH>
     bool node_intersects(const Blas& blas, const BvhNode& node, const Ray& ray, Hit& out) const {
         if (cnt) cnt->exh_nodes++;
         float d = aabb_intersects(node.bounds, ray);
@@ -608,7 +622,7 @@ struct Tracer {
                 float t;
                 Point3 pt;
                 Vec2 uv;
-                if (prim_intersects(blas.prims[i], ray, t, pt, uv)) {
+                if (prim_intersects<SPH>(blas.prims[i], ray, t, pt, uv)) {
                     if (t < depth) {
                         depth = t;
                         out.depth = t;
@@ -621,7 +635,7 @@ struct Tracer {
             }
         } else {
             Hit h;
-            if (node_intersects(blas, blas.nodes[node.offset], ray, h)) {
+            if (node_intersects<SPH>(blas, blas.nodes[node.offset], ray, h)) {
                 if (h.depth < depth) {
                     depth = h.depth;
                     out = h;
@@ -629,7 +643,7 @@ struct Tracer {
                 }
             }
             Hit h2;
-            if (node_intersects(blas, blas.nodes[node.offset + 1], ray, h2)) {
+            if (node_intersects<SPH>(blas, blas.nodes[node.offset + 1], ray, h2)) {
                 if (h2.depth < depth) {
                     out = h2;
                     found = true;
@@ -648,7 +662,8 @@ struct Tracer {
             for (uint32_t i = node.offset; i < node.offset + node.count; ++i) {
                 const Blas& blas = s.blass[s.blas_nodes[i].blas];
                 Hit h;
-                if (node_intersects(blas, blas.nodes[0], ray, h)) {
+                if (blas.has_spheres ? node_intersects<true>(blas, blas.nodes[0], ray, h)
+                                     : node_intersects<false>(blas, blas.nodes[0], ray, h)) {
                     if (h.depth < depth) {
                         depth = h.depth;
                         h.blas = i;
@@ -698,7 +713,8 @@ struct Tracer {
                     float t;
                     Point3 pt;
                     Vec2 uv;
-                    if (prim_intersects(blas.prims[i], ray, t, pt, uv)) {
+                    if (blas.has_spheres ? prim_intersects<true>(blas.prims[i], ray, t, pt, uv)
+                                     : prim_intersects<false>(blas.prims[i], ray, t, pt, uv)) {
                         uint64_t key = ((uint64_t)blas_index << 32) | i;
                         if (t < best_t || (t == best_t && key < best_key)) {
                             best_t = t;
@@ -1486,6 +1502,7 @@ int rayca_oracle_scene_create(const rayca_scene_desc* desc, uint32_t bvh, rayca_
             emit_mesh_prims(*s, d, m, f.mdi[m].mesh_node_local[k], f.mdi[m].mesh_nodes[k], blas.prims);
         for (size_t k = 0; k < f.mdi[m].quad_nodes.size(); ++k) // primitive.rs:363-367: area lights after the meshes
             emit_quad_prims(*s, d, m, f.mdi[m].quad_lights[k], f.mdi[m].quad_nodes[k], blas.prims);
+        for (const Prim& p : blas.prims) blas.has_spheres = blas.has_spheres || p.sphere;
         build_blas(blas);
         s->blas_nodes.push_back({(uint32_t)s->blass.size()});
         s->blass.push_back(std::move(blas));

@@ -455,6 +455,56 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
 
 extern "C" {
 
+} // extern "C"
+
+namespace {
+// streaming 128-bit reads over a buffer, grid-stride, every load kept alive through a XOR fold
+__global__ void __launch_bounds__(256) probe_read_kernel(const uint4* __restrict__ p, size_t n, uint32_t reps, uint32_t* sink) {
+    uint32_t acc = 0;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (uint32_t r = 0; r < reps; ++r)
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+            const uint4 v = __ldg(p + i);
+            acc ^= v.x ^ v.y ^ v.z ^ v.w;
+        }
+    if (acc == 0x9E3779B9u) *sink = acc; // practically never: keeps the loads observable
+}
+} // namespace
+
+extern "C" {
+
+int rayca_cuda_probe_read_bandwidth(rayca_ctx* ctx, size_t bytes, uint32_t reps, double* gb_per_s) {
+    if (!ctx || !gb_per_s || bytes < 4096 || reps == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    void* buf = nullptr;
+    uint32_t* sink = nullptr;
+    CUDA_TRY(cudaMalloc(&buf, bytes));
+    CUDA_TRY(cudaMalloc((void**)&sink, 4));
+    CUDA_TRY(cudaMemset(buf, 1, bytes));
+    const size_t n = bytes / sizeof(uint4);
+    const int grid = ctx->sm_count * 8;
+    probe_read_kernel<<<grid, 256>>>((const uint4*)buf, n, 2, sink); // warm-up: pulls the buffer into L2 if it fits
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int k = 0; k < 5; ++k) {
+        CUDA_TRY(cudaEventRecord(e0));
+        probe_read_kernel<<<grid, 256>>>((const uint4*)buf, n, reps, sink);
+        CUDA_TRY(cudaEventRecord(e1));
+        CUDA_TRY(cudaEventSynchronize(e1));
+        float ms = 0.0f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+        best = ms < best ? ms : best;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(buf);
+    cudaFree(sink);
+    *gb_per_s = (double)n * sizeof(uint4) * reps / (best * 1e-3) / 1e9;
+    return RAYCA_OK;
+}
+
 int rayca_cuda_host_alloc(size_t bytes, void** out) {
     if (!out || bytes == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
     CUDA_TRY(cudaHostAlloc(out, bytes, cudaHostAllocDefault));

@@ -155,6 +155,7 @@ def load_library():
     lib.rayca_cuda_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
     lib.rayca_cuda_host_free.argtypes = [vp]
     lib.rayca_cuda_host_free.restype = None
+    lib.rayca_cuda_probe_read_bandwidth.argtypes = [vp, C.c_size_t, u32, C.POINTER(C.c_double)]
     lib.rayca_cuda_init.argtypes = [C.c_int, C.POINTER(vp)]
     lib.rayca_cuda_shutdown.argtypes = [vp]
     lib.rayca_cuda_shutdown.restype = None
@@ -205,6 +206,12 @@ class Context:
         self._h = C.c_void_p()
         _check(load_library().rayca_cuda_init(device, C.byref(self._h)))
         self.device = device
+
+    def probe_read_bandwidth(self, nbytes: int, reps: int) -> float:
+        """GB/s of a streaming read over an nbytes buffer (L2-resident when small): bench.py's L2 roofline."""
+        out = C.c_double()
+        _check(load_library().rayca_cuda_probe_read_bandwidth(self._h, nbytes, reps, C.byref(out)))
+        return out.value
 
     def close(self):
         if self._h:
