@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--traversal", type=int, default=0)
     ap.add_argument("--flags", type=int, default=0, help="rayca_options.flags for the timed launches")
     ap.add_argument("--max-depth", type=int, default=1, help="Pathtracer max_depth (2 = one cosine bounce, BASELINE M5)")
+    ap.add_argument("--gather", choices=["peer", "nccl"], default="peer",
+                    help="N>1: peer = kernels store tiles into rank 0's frame over NVLink; nccl = all_gather_into_tensor")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-rows", type=int, default=0, help="rows of the frame the CPU baseline renders")
     return ap.parse_args()
@@ -197,10 +199,40 @@ def run_ours(args):
     opts = M.rayca_options(0x5EED, args.traversal, rank, G, tile, args.flags, 0)
     stream = torch.cuda.current_stream().cuda_stream
 
-    def step():
-        dev.render_device(cfg, W, H, local.data_ptr(), stream=stream, options=opts)
-        if G > 1:
+    # N > 1, --gather peer (default): rank 0 owns the frame; every rank's trace kernel stores its tiles
+    # straight into it over NVLink (CUDA IPC mapping) and publishes a per-rank completion flag, rank 0
+    # waits on the flags on its stream.  --gather nccl: local tiles + all_gather_into_tensor.
+    frame, frame_id = None, [0]
+    peer = G > 1 and args.gather == "peer"
+    frames = []
+    if peer:
+        for _ in range(2):  # two frames: the e2e loop traces frame k+1 while rank 0 still reads frame k back
+            handle = [None]
+            if rank == 0:
+                frames.append(R.SharedFrame(ctx, W, H))
+                handle[0] = frames[-1].export()
+            dist.broadcast_object_list(handle, src=0)
+            if rank != 0:
+                frames.append(R.SharedFrame(ctx, W, H, handle=handle[0]))
+        frame = frames[0]
+
+    def trace():
+        if peer:
+            frame_id[0] += 1
+            dev.render_to_frame(cfg, frame, frame_id[0], stream=stream, options=opts)
+        else:
+            dev.render_device(cfg, W, H, local.data_ptr(), stream=stream, options=opts)
+
+    def gather():
+        if peer:
+            if rank == 0:
+                frame.wait(G, frame_id[0], stream=stream)
+        elif G > 1:
             dist.all_gather_into_tensor(gathered, local)
+
+    def step():
+        trace()
+        gather()
 
     def barrier():
         if G > 1:
@@ -210,6 +242,24 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
+    if peer:
+        # The shared frame must equal the NCCL-gathered tiles, byte for byte, at the moment the flag wait
+        # returns: rank 0 clears the frame before every round, so a flag that overtook its pixels shows up
+        # as black tiles.
+        dev.render_device(cfg, W, H, local.data_ptr(), stream=stream, options=opts)
+        dist.all_gather_into_tensor(gathered, local)
+        expect = gathered.view(G, per, tile, W, 4).permute(1, 0, 2, 3, 4).reshape(per * G * tile, W, 4)[:H].contiguous()
+        shared = torch.as_tensor(frame, device="cuda") if rank == 0 else None
+        for _ in range(16):
+            if rank == 0:
+                shared.zero_()
+            barrier()
+            step()
+            if rank == 0 and not torch.equal(shared, expect):  # same stream as the wait: ordered after it
+                raise RuntimeError("shared frame differs from the NCCL-gathered frame")
+            barrier()
+        if rank == 0 and frame.timed_out():
+            raise RuntimeError("shared frame: a rank's completion flag never arrived")
     # ray counts of one frame (deterministic): this rank's share, summed over ranks
     st = dev.last_counters()
     rays_local = torch.tensor([st.rays_primary, st.rays_shadow, st.rays_secondary], dtype=torch.int64, device="cuda")
@@ -235,10 +285,9 @@ def run_ours(args):
         flush.fill_(k & 0xFF)  # L2 flush between timed iterations (outside the timed events)
         ev[k][0].record()
         kev[k][0].record()
-        dev.render_device(cfg, W, H, local.data_ptr(), stream=stream, options=opts)
+        trace()
         kev[k][1].record()
-        if G > 1:
-            dist.all_gather_into_tensor(gathered, local)
+        gather()
         ev[k][1].record()
     barrier()
     sampler.stop.set()
@@ -273,27 +322,50 @@ def run_ours(args):
         d2h = W * H * 4
         e2e_what = "rayca_cuda_render: pinned host RGBA8 out, scene resident (scene_create excluded, like the reference timer)"
     else:
-        host = torch.empty((G, local_rows, W, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
+        srcs = [torch.as_tensor(f, device="cuda") for f in frames] if (peer and rank == 0) else [gathered]
+        host = torch.empty(tuple(srcs[0].shape), dtype=torch.uint8).pin_memory() if rank == 0 else None
+        ids = [frame_id[0], 0]
+        if peer and rank == 0:
+            frames[0].release(ids[0], stream=stream)  # the timed loop above consumed nothing: catch up
+        e2e_k = [0]
 
         def e2e_step():
-            dev.render_device(cfg, W, H, local.data_ptr(), stream=stream, options=opts)
-            dist.all_gather_into_tensor(gathered, local)
-            if rank == 0:
-                host.copy_(gathered, non_blocking=True)
+            if peer:
+                # frames used alternately; a rank overwrites a frame only after rank 0 released its last use
+                b = e2e_k[0] & 1
+                e2e_k[0] += 1
+                f = frames[b]
+                f.acquire(ids[b], stream=stream)
+                ids[b] += 1
+                dev.render_to_frame(cfg, f, ids[b], stream=stream, options=opts)
+                if rank == 0:
+                    f.wait(G, ids[b], stream=stream)
+                    host.copy_(srcs[b], non_blocking=True)
+                    f.release(ids[b], stream=stream)
+            else:
+                step()
+                if rank == 0:
+                    host.copy_(srcs[0], non_blocking=True)
+            torch.cuda.synchronize()  # rank 0: the frame is on the host before the next one starts
 
-        for _ in range(3):
+        for _ in range(4):
             e2e_step()
+        torch.cuda.synchronize()
+        if rank == 0 and not torch.equal(host, srcs[0].cpu()):
+            raise RuntimeError("e2e: host frame differs from the device frame")
         barrier()
         t1 = time.perf_counter()
         for _ in range(n_e2e):
             e2e_step()
-            torch.cuda.synchronize()  # the frame must be on the host before the next one starts
         barrier()
+        if peer and any(f.timed_out() for f in frames):
+            raise RuntimeError("shared frame: a flag wait timed out during the e2e loop")
         e2e_t = torch.tensor([(time.perf_counter() - t1) / n_e2e], dtype=torch.float64, device="cuda")
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
         e2e_s = float(e2e_t.item())
-        d2h = G * local_rows * W * 4
-        e2e_what = "render_device on every rank + NCCL all_gather + rank-0 copy of the frame to pinned host memory"
+        d2h = int(host.numel()) if rank == 0 else 0
+        e2e_what = ("render_to_frame on every rank (peer stores into rank 0's frame, two frames alternating with acquire / release flags) + flag wait + rank-0 copy to pinned host memory"
+                    if peer else "render_device on every rank + NCCL all_gather + rank-0 copy of the frame to pinned host memory")
     e2e = {"value": rays_frame / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": param_bytes,
            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "what": e2e_what}
     if G == 1:
@@ -327,10 +399,10 @@ def run_ours(args):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": what, "width": W, "height": H, "spp": args.spp,
                            "triangles": desc.triangle_count, "integrator": f"Pathtracer max_depth={args.max_depth} (NEE point lights" + (", cosine bounce, Philox keyed RNG)" if args.max_depth > 1 else ")"),
-                           "parallelism": f"image row-tiles of {tile} rows interleaved over {G} GPU(s), scene replicated, NCCL all_gather of RGBA8",
+                           "parallelism": f"image row-tiles of {tile} rows interleaved over {G} GPU(s), scene replicated, " + ("tiles stored into rank 0's frame by the trace kernel over NVLink (CUDA IPC), per-rank completion flags" if peer else "NCCL all_gather of RGBA8"),
                            "l2": "flushed between timed iterations (256 MiB fill)", "traversal": args.traversal},
                 "rays_per_frame": rays_frame, "kernel_ms": kernel_ms, "build_s": build_s,
-                "clocks": sampler.summary(), "gpu_launches": args.steps,
+                "clocks": sampler.summary(), "gpu_launches": args.steps * (3 if peer else 1),  # peer: trace + flag signal + flag wait (rank 0)
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "peak_source": "measured" if peaks else "fallback",
                              "l2": {"peak": l2_peak, "frac": achieved / l2_peak, "unit": "GB/s",

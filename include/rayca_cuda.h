@@ -342,6 +342,41 @@ void rayca_cuda_host_free(void* p);
  * walk on L2-resident scenes; a buffer of several GB gives the HBM read peak. */
 int rayca_cuda_probe_read_bandwidth(rayca_ctx* ctx, size_t bytes, uint32_t reps, double* gb_per_s);
 
+/* ---- Shared frame: the multi-GPU gather folded into the trace kernel's own stores ------------------------
+ * One process per GPU.  The OWNER (the rank that wants the image) creates a frame in its HBM and exports a
+ * 64-byte CUDA IPC handle; every other rank imports it, which maps the owner's memory over NVLink / NVSwitch.
+ * rayca_cuda_render_to_frame then makes each rank's trace kernel store its tiles' pixels straight into their
+ * final row-major place in the owner's frame, followed on the same stream by a one-thread kernel that
+ * publishes `frame_id` in that rank's flag slot.  The owner enqueues rayca_cuda_frame_wait (a one-warp kernel
+ * spinning on the flags, with a ~2 s time-out) and may then read the frame on the same stream: no collective,
+ * no local staging buffer, no pack / unpack kernel.
+ * Back-pressure for a pipeline of frames: the owner calls rayca_cuda_frame_release(frame_id) once it has
+ * consumed a frame (e.g. after its device-to-host copy, in stream order); a rank that is about to overwrite the
+ * frame first calls rayca_cuda_frame_acquire(previous frame_id), which waits for that release.  Two frames used
+ * alternately let the ranks trace frame k+1 while the owner still reads frame k.
+ * Layout of the allocation: 64 x u64 flags (512 B: slot r = rank r stored, slot 32 = owner consumed) |
+ * width*height*4 bytes RGBA8. */
+typedef struct rayca_frame rayca_frame;
+#define RAYCA_IPC_HANDLE_BYTES 64
+int rayca_cuda_frame_create(rayca_ctx* ctx, uint32_t width, uint32_t height, rayca_frame** out);
+int rayca_cuda_frame_export(rayca_frame* frame, uint8_t handle[RAYCA_IPC_HANDLE_BYTES]);
+int rayca_cuda_frame_import(rayca_ctx* ctx, const uint8_t handle[RAYCA_IPC_HANDLE_BYTES], uint32_t width, uint32_t height,
+                            rayca_frame** out);
+void* rayca_cuda_frame_pixels(rayca_frame* frame); /* device pointer (owner: local; importer: peer mapping) */
+void rayca_cuda_frame_destroy(rayca_frame* frame);
+/* options->shard_index / shard_count / tile_rows select this rank's tiles as in rayca_cuda_render_device
+ * (at most 32 ranks per frame). */
+int rayca_cuda_render_to_frame(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options,
+                               rayca_frame* frame, uint64_t frame_id, void* cuda_stream);
+/* Owner only: returns once (in stream order) ranks 0..rank_count-1 have published a frame id >= frame_id.
+ * A time-out sets a flag (device-visible host memory inside the frame object) read by rayca_cuda_frame_timed_out. */
+int rayca_cuda_frame_wait(rayca_ctx* ctx, rayca_frame* frame, uint32_t rank_count, uint64_t frame_id, void* cuda_stream);
+/* Owner only: in stream order, marks every frame id <= frame_id as consumed. */
+int rayca_cuda_frame_release(rayca_ctx* ctx, rayca_frame* frame, uint64_t frame_id, void* cuda_stream);
+/* Any rank: in stream order, waits until the owner has released a frame id >= frame_id (0 returns at once). */
+int rayca_cuda_frame_acquire(rayca_ctx* ctx, rayca_frame* frame, uint64_t frame_id, void* cuda_stream);
+int rayca_cuda_frame_timed_out(rayca_frame* frame);
+
 /* Binds a context to one CUDA device (one process per GPU). */
 int rayca_cuda_init(int device, rayca_ctx** out);
 void rayca_cuda_shutdown(rayca_ctx* ctx);

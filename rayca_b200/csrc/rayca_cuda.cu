@@ -335,8 +335,10 @@ struct Band {
     uint32_t row_begin, row_end;
     bool first, last;
 };
+struct FrameTarget {}; // shared-frame launch (rayca_cuda_render_to_frame): pixels at their image row
 int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options, uint32_t width,
-                   uint32_t height, void* d_rgba8, const rayca_aux_out* d_aux, cudaStream_t st, const Band* band, rayca_stats* stats);
+                   uint32_t height, void* d_rgba8, const rayca_aux_out* d_aux, cudaStream_t st, const Band* band, rayca_stats* stats,
+                   const FrameTarget* target = nullptr);
 } // namespace
 
 extern "C" {
@@ -351,7 +353,8 @@ int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_con
 
 namespace {
 int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options, uint32_t width,
-                   uint32_t height, void* d_rgba8, const rayca_aux_out* d_aux, cudaStream_t st, const Band* band, rayca_stats* stats) {
+                   uint32_t height, void* d_rgba8, const rayca_aux_out* d_aux, cudaStream_t st, const Band* band, rayca_stats* stats,
+                   const FrameTarget* target) {
     if (!ctx || !scene || !config || !d_rgba8 || width == 0 || height == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
     if (scene->ctx != ctx) return fail(RAYCA_E_INVALID_ARG, "scene belongs to another context (or is host-only)");
     if (!scene->host.has_camera) return fail(RAYCA_E_NO_CAMERA, "no camera node in the scene");
@@ -407,6 +410,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
         P.rgba_f32 = d_aux->rgba_f32;
     }
     P.counters = ctx->d_counters;
+    if (target) P.direct_rows = 1;
     const uint32_t mode = options ? options->traversal : (uint32_t)RAYCA_TRAVERSAL_ORDERED;
     if (mode > RAYCA_TRAVERSAL_REFERENCE_ORDERED) return fail(RAYCA_E_INVALID_ARG, "unknown traversal mode");
     if (mode != RAYCA_TRAVERSAL_ORDERED && scene->host.has_spheres)
@@ -504,6 +508,154 @@ int rayca_cuda_probe_read_bandwidth(rayca_ctx* ctx, size_t bytes, uint32_t reps,
     *gb_per_s = (double)n * sizeof(uint4) * reps / (best * 1e-3) / 1e9;
     return RAYCA_OK;
 }
+
+} // extern "C"
+
+struct rayca_frame {
+    rayca_ctx* ctx = nullptr;
+    unsigned char* base = nullptr; // flags | pixels
+    uint32_t width = 0, height = 0;
+    bool imported = false;
+    int* timed_out = nullptr; // pinned, device-visible
+};
+
+namespace {
+constexpr size_t kFrameFlagBytes = 64 * sizeof(unsigned long long);
+constexpr uint32_t kConsumedSlot = 32; // slots 0..31: "rank r has stored frame id"; slot 32: "owner has consumed frame id"
+// Publishes `value` in one flag slot (local or peer memory).  Launched on the stream right after the trace
+// kernel: a kernel's stores, peer stores included, are performed before the next kernel of the stream starts,
+// and the system fence orders this thread's flag store after them for an observer on another GPU.
+__global__ void frame_signal_kernel(volatile unsigned long long* slot, unsigned long long value) {
+    __threadfence_system();
+    *slot = value;
+}
+// one warp: lane r polls slot first+r; gives up after ~2 s so that a dead peer cannot hang the GPU
+__global__ void frame_wait_kernel(const volatile unsigned long long* flags, uint32_t ranks, unsigned long long frame_id, int* timed_out) {
+    const uint32_t r = threadIdx.x;
+    if (r < ranks) {
+        const long long t0 = clock64();
+        while (flags[r] < frame_id) {
+            if (clock64() - t0 > 4000000000ll) {
+                *timed_out = 1;
+                break;
+            }
+            __nanosleep(200);
+        }
+    }
+    __threadfence_system();
+}
+} // namespace
+
+extern "C" {
+
+int rayca_cuda_frame_create(rayca_ctx* ctx, uint32_t width, uint32_t height, rayca_frame** out) {
+    if (!ctx || !out || width == 0 || height == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    rayca_frame* f = new (std::nothrow) rayca_frame();
+    if (!f) return fail(RAYCA_E_OOM, "host allocation");
+    f->ctx = ctx;
+    f->width = width;
+    f->height = height;
+    const size_t bytes = kFrameFlagBytes + (size_t)width * height * 4;
+    CUDA_TRY(cudaMalloc((void**)&f->base, bytes)); // a plain cudaMalloc block: IPC handles cover whole allocations
+    CUDA_TRY(cudaMemset(f->base, 0, bytes));
+    CUDA_TRY(cudaHostAlloc((void**)&f->timed_out, sizeof(int), cudaHostAllocMapped));
+    *f->timed_out = 0;
+    *out = f;
+    return RAYCA_OK;
+}
+
+int rayca_cuda_frame_export(rayca_frame* f, uint8_t handle[RAYCA_IPC_HANDLE_BYTES]) {
+    if (!f || !handle || f->imported) return fail(RAYCA_E_INVALID_ARG, "export needs the owner's frame");
+    static_assert(sizeof(cudaIpcMemHandle_t) == RAYCA_IPC_HANDLE_BYTES, "CUDA IPC handle size");
+    CUDA_TRY(cudaSetDevice(f->ctx->device));
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, f->base));
+    std::memcpy(handle, &h, sizeof(h));
+    return RAYCA_OK;
+}
+
+int rayca_cuda_frame_import(rayca_ctx* ctx, const uint8_t handle[RAYCA_IPC_HANDLE_BYTES], uint32_t width, uint32_t height,
+                            rayca_frame** out) {
+    if (!ctx || !handle || !out || width == 0 || height == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    rayca_frame* f = new (std::nothrow) rayca_frame();
+    if (!f) return fail(RAYCA_E_OOM, "host allocation");
+    f->ctx = ctx;
+    f->width = width;
+    f->height = height;
+    f->imported = true;
+    CUDA_TRY(cudaHostAlloc((void**)&f->timed_out, sizeof(int), cudaHostAllocMapped));
+    *f->timed_out = 0;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof(h));
+    cudaError_t e = cudaIpcOpenMemHandle((void**)&f->base, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        cudaFreeHost(f->timed_out);
+        delete f;
+        return fail(RAYCA_E_CUDA, std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e));
+    }
+    *out = f;
+    return RAYCA_OK;
+}
+
+void* rayca_cuda_frame_pixels(rayca_frame* f) { return f ? f->base + kFrameFlagBytes : nullptr; }
+
+void rayca_cuda_frame_destroy(rayca_frame* f) {
+    if (!f) return;
+    cudaSetDevice(f->ctx->device);
+    if (f->imported) cudaIpcCloseMemHandle(f->base);
+    else cudaFree(f->base);
+    if (f->timed_out) cudaFreeHost(f->timed_out);
+    delete f;
+}
+
+int rayca_cuda_render_to_frame(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options,
+                               rayca_frame* frame, uint64_t frame_id, void* cuda_stream) {
+    if (!frame || frame->ctx != ctx) return fail(RAYCA_E_INVALID_ARG, "frame belongs to another context");
+    const uint32_t rank = (options && options->shard_count > 1) ? options->shard_index : 0;
+    if (rank >= kConsumedSlot) return fail(RAYCA_E_INVALID_ARG, "at most 32 ranks share a frame");
+    FrameTarget t{};
+    int rc = enqueue_render(ctx, scene, config, options, frame->width, frame->height, frame->base + kFrameFlagBytes, nullptr,
+                            (cudaStream_t)cuda_stream, nullptr, nullptr, &t);
+    if (rc != RAYCA_OK) return rc;
+    frame_signal_kernel<<<1, 1, 0, (cudaStream_t)cuda_stream>>>(reinterpret_cast<volatile unsigned long long*>(frame->base) + rank, frame_id);
+    CUDA_TRY(cudaGetLastError());
+    return RAYCA_OK;
+}
+
+int rayca_cuda_frame_release(rayca_ctx* ctx, rayca_frame* frame, uint64_t frame_id, void* cuda_stream) {
+    if (!ctx || !frame || frame->imported) return fail(RAYCA_E_INVALID_ARG, "release needs the owner's frame");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    frame_signal_kernel<<<1, 1, 0, (cudaStream_t)cuda_stream>>>(reinterpret_cast<volatile unsigned long long*>(frame->base) + kConsumedSlot, frame_id);
+    CUDA_TRY(cudaGetLastError());
+    return RAYCA_OK;
+}
+
+int rayca_cuda_frame_acquire(rayca_ctx* ctx, rayca_frame* frame, uint64_t frame_id, void* cuda_stream) {
+    if (!ctx || !frame) return fail(RAYCA_E_INVALID_ARG, "null argument");
+    if (frame_id == 0) return RAYCA_OK; // nothing has been stored yet
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    int* d_flag = nullptr;
+    CUDA_TRY(cudaHostGetDevicePointer((void**)&d_flag, frame->timed_out, 0));
+    frame_wait_kernel<<<1, 32, 0, (cudaStream_t)cuda_stream>>>(
+        reinterpret_cast<const volatile unsigned long long*>(frame->base) + kConsumedSlot, 1, frame_id, d_flag);
+    CUDA_TRY(cudaGetLastError());
+    return RAYCA_OK;
+}
+
+int rayca_cuda_frame_wait(rayca_ctx* ctx, rayca_frame* frame, uint32_t rank_count, uint64_t frame_id, void* cuda_stream) {
+    if (!ctx || !frame || frame->imported || rank_count == 0 || rank_count > 32) return fail(RAYCA_E_INVALID_ARG, "wait needs the owner's frame and 1..32 ranks");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    int* d_flag = nullptr;
+    CUDA_TRY(cudaHostGetDevicePointer((void**)&d_flag, frame->timed_out, 0));
+    frame_wait_kernel<<<1, 32, 0, (cudaStream_t)cuda_stream>>>(reinterpret_cast<const volatile unsigned long long*>(frame->base), rank_count,
+                                                              frame_id, d_flag);
+    CUDA_TRY(cudaGetLastError());
+    return RAYCA_OK;
+}
+
+int rayca_cuda_frame_timed_out(rayca_frame* f) { return (f && f->timed_out) ? *f->timed_out : 0; }
 
 int rayca_cuda_host_alloc(size_t bytes, void** out) {
     if (!out || bytes == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");

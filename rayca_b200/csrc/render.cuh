@@ -35,6 +35,9 @@ struct RenderParams {
     // [0] shadow rays [1] secondary rays [2] node records [3] triangle vertex fetches [4] plane fetches
     // [5] next tile (persistent scheduling)
     unsigned long long* counters;
+    // shared frame (multi-GPU, rayca_cuda_render_to_frame): rgba8 points into the OWNER GPU's frame (peer memory
+    // over NVLink) and pixels go to their final row-major position
+    uint32_t direct_rows; // 1: write at the image row even when sharded
 };
 constexpr int kCounterSlots = 8;
 
@@ -430,7 +433,7 @@ __device__ __forceinline__ void write_pixel(const RenderParams& P, uint32_t x, u
         color.g = gamma_pow(color.g, P.inv_gamma);
         color.b = gamma_pow(color.b, P.inv_gamma);
     }
-    const size_t o = (size_t)((P.shard_count > 1) ? local_row : y) * P.width + x;
+    const size_t o = (size_t)((P.shard_count > 1 && !P.direct_rows) ? local_row : y) * P.width + x;
     uchar4 q = make_uchar4(quantize(color.r), quantize(color.g), quantize(color.b), quantize(color.a));
     reinterpret_cast<uchar4*>(P.rgba8)[o] = q;
     const bool hit = primary.prim != 0xFFFFFFFFu;

@@ -156,6 +156,18 @@ def load_library():
     lib.rayca_cuda_host_free.argtypes = [vp]
     lib.rayca_cuda_host_free.restype = None
     lib.rayca_cuda_probe_read_bandwidth.argtypes = [vp, C.c_size_t, u32, C.POINTER(C.c_double)]
+    lib.rayca_cuda_frame_create.argtypes = [vp, u32, u32, C.POINTER(vp)]
+    lib.rayca_cuda_frame_export.argtypes = [vp, C.c_char_p]
+    lib.rayca_cuda_frame_import.argtypes = [vp, C.c_char_p, u32, u32, C.POINTER(vp)]
+    lib.rayca_cuda_frame_pixels.argtypes = [vp]
+    lib.rayca_cuda_frame_pixels.restype = vp
+    lib.rayca_cuda_frame_destroy.argtypes = [vp]
+    lib.rayca_cuda_frame_destroy.restype = None
+    lib.rayca_cuda_render_to_frame.argtypes = [vp, vp, C.POINTER(M.rayca_config), C.POINTER(M.rayca_options), vp, C.c_uint64, vp]
+    lib.rayca_cuda_frame_wait.argtypes = [vp, vp, u32, C.c_uint64, vp]
+    lib.rayca_cuda_frame_release.argtypes = [vp, vp, C.c_uint64, vp]
+    lib.rayca_cuda_frame_acquire.argtypes = [vp, vp, C.c_uint64, vp]
+    lib.rayca_cuda_frame_timed_out.argtypes = [vp]
     lib.rayca_cuda_init.argtypes = [C.c_int, C.POINTER(vp)]
     lib.rayca_cuda_shutdown.argtypes = [vp]
     lib.rayca_cuda_shutdown.restype = None
@@ -225,6 +237,59 @@ class Context:
             pass
 
 
+class SharedFrame:
+    """rayca_frame: an RGBA8 frame in the owner GPU's HBM that every rank's kernel writes into over NVLink
+    (CUDA IPC mapping), with one completion flag per rank.  `SharedFrame(ctx, w, h)` creates (owner),
+    `SharedFrame(ctx, w, h, handle=...)` imports the owner's `export()`ed handle."""
+
+    def __init__(self, ctx: Context, width: int, height: int, handle: Optional[bytes] = None):
+        self.ctx, self.width, self.height, self.owner = ctx, width, height, handle is None
+        self._h = C.c_void_p()
+        lib = load_library()
+        if handle is None:
+            _check(lib.rayca_cuda_frame_create(ctx._h, width, height, C.byref(self._h)))
+        else:
+            _check(lib.rayca_cuda_frame_import(ctx._h, handle, width, height, C.byref(self._h)))
+
+    def export(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        _check(load_library().rayca_cuda_frame_export(self._h, buf))
+        return buf.raw
+
+    @property
+    def pixels_ptr(self) -> int:
+        return load_library().rayca_cuda_frame_pixels(self._h)
+
+    @property
+    def __cuda_array_interface__(self):
+        return {"shape": (self.height, self.width, 4), "typestr": "|u1", "data": (self.pixels_ptr, False), "version": 3}
+
+    def wait(self, rank_count: int, frame_id: int, stream: int = 0) -> None:
+        _check(load_library().rayca_cuda_frame_wait(self.ctx._h, self._h, rank_count, frame_id, stream))
+
+    def release(self, frame_id: int, stream: int = 0) -> None:
+        """Owner: frames up to frame_id have been consumed (stream order)."""
+        _check(load_library().rayca_cuda_frame_release(self.ctx._h, self._h, frame_id, stream))
+
+    def acquire(self, frame_id: int, stream: int = 0) -> None:
+        """Any rank: wait (stream order) until the owner released frame_id before overwriting the frame."""
+        _check(load_library().rayca_cuda_frame_acquire(self.ctx._h, self._h, frame_id, stream))
+
+    def timed_out(self) -> bool:
+        return bool(load_library().rayca_cuda_frame_timed_out(self._h))
+
+    def close(self):
+        if self._h:
+            load_library().rayca_cuda_frame_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class DeviceScene:
     """rayca_scene: the flattened scene + BVH resident in HBM (or host-only when ctx is None)."""
 
@@ -285,6 +350,14 @@ class DeviceScene:
                                                        C.byref(options) if options is not None else None, width,
                                                        height, d_rgba8, C.byref(d_aux) if d_aux is not None else None,
                                                        stream, None))
+
+    def render_to_frame(self, config: Config, frame: SharedFrame, frame_id: int, stream: int = 0,
+                        options: Optional[M.rayca_options] = None):
+        """rayca_cuda_render_to_frame: this rank's tiles go straight into the (possibly remote) shared frame."""
+        cfg = config.to_c()
+        _check(load_library().rayca_cuda_render_to_frame(self.ctx._h, self._h, C.byref(cfg),
+                                                         C.byref(options) if options is not None else None, frame._h,
+                                                         frame_id, stream))
 
     def last_counters(self) -> M.rayca_stats:
         stats = M.rayca_stats()

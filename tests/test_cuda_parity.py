@@ -260,6 +260,43 @@ def test_host_render_bands_equal_single_launch(ctx, atrium):
     assert c.rays_primary == w * h and c.rays_shadow == st.rays_shadow
 
 
+def test_shared_frame_of_three_shards_equals_single_launch(ctx, atrium):
+    """rayca_cuda_render_to_frame: three shards (here three launches of one process; on N GPUs one per rank,
+    through the CUDA IPC mapping) store their interleaved 8-row tiles straight into ONE frame and publish their
+    completion flags; frame_wait sees all three and the frame equals a single full launch, ragged last tile
+    included."""
+    import torch
+
+    cfg = R.Config(max_depth=1)
+    w, h = 1283, 717
+    frame = R.SharedFrame(ctx, w, h)
+    assert len(frame.export()) == 64
+    for frame_id in (1, 2):
+        for r in (2, 0, 1):
+            atrium.render_to_frame(cfg, frame, frame_id, options=M.rayca_options(0x5EED, 0, r, 3, 8, 0, 0))
+        frame.wait(3, frame_id)
+        torch.cuda.synchronize()
+        assert not frame.timed_out()
+    buf = torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda:0")
+    atrium.render_device(cfg, w, h, buf.data_ptr())
+    torch.cuda.synchronize()
+    assert torch.equal(torch.as_tensor(frame, device="cuda:0"), buf)
+    frame.close()
+
+
+def test_shared_frame_wait_times_out_instead_of_hanging(ctx, atrium):
+    """A rank that never publishes its flag must not hang the owner: the wait kernel gives up after ~2 s and
+    frame_timed_out reports it."""
+    import torch
+
+    frame = R.SharedFrame(ctx, 64, 64)
+    atrium.render_to_frame(R.Config(max_depth=1), frame, 7, options=M.rayca_options(0x5EED, 0, 0, 2, 8, 0, 0))
+    frame.wait(2, 7)
+    torch.cuda.synchronize()
+    assert frame.timed_out()
+    frame.close()
+
+
 def test_dragon_direct_lighting_at_full_size(ctx):
     """The reference's sdtf/2/dragon.sdtf at its own 640x480 with its own settings (Direct integrator, two quad
     lights, 25 stratified light samples: 0.3 M primary + 15 M closest-hit shadow rays over 100,002 triangles): the
