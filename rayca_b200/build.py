@@ -15,8 +15,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "librayca_cuda.so")
-SOURCES = ["rayca_cuda.cu", "host_scene.cpp", "bvh_build.cpp", "fast_bvh.cpp"]
-HEADERS = ["rmath.h", "gpu_types.h", "host_scene.h", "trace.cuh", "shade.cuh", "render.cuh",
+SOURCES = ["rayca_cuda.cu", "host_scene.cpp", "bvh_build.cpp", "fast_bvh.cpp", "gpu_fast_build.cu"]
+HEADERS = ["rmath.h", "gpu_types.h", "host_scene.h", "gpu_fast_build.h", "trace.cuh", "shade.cuh", "render.cuh",
            os.path.join("..", "..", "include", "rayca_cuda.h")]
 
 

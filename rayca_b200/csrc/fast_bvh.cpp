@@ -187,6 +187,13 @@ GpuNode to_gpu(const Rec& r) {
 
 } // namespace
 
+void fast_tree_tunables(int& bins, uint32_t& leaf_max, float& traversal_cost) {
+    read_tunables();
+    bins = kBins;
+    leaf_max = kLeafMax;
+    traversal_cost = kTraversalCost;
+}
+
 void build_fast_tree(HostScene& hs) {
     read_tunables();
     // gather triangles in reference-global order with their reference leaf

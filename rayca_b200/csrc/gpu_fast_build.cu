@@ -1,0 +1,825 @@
+// gpu_fast_build.cu — the performance tree (fast_bvh.cpp) built on the GPU, emitted directly in the
+// 32-byte record layout the walk reads.  SURVEY 8(f) rank 1: `draw` rebuilds its BVH on every call
+// (rayca-soft/src/scene.rs:92-99), so once tracing takes a millisecond the build is the frame time.
+//
+// Same algorithm as the host builder: top-down binned SAH, 32 bins x 3 axes over bounding-box centroids,
+// leaves of <= kLeafMax primitives, triangles and spheres never share a leaf.  Two tiers:
+//   * BIG nodes (> 32 primitives) are processed level by level, all nodes of a level at once: one thread per
+//     primitive adds its box to the (node, axis, bin) accumulators with ordered-integer atomicMin / atomicMax,
+//     one thread per (node, axis) sweeps the 31 planes, a scan over the left/right flags gives every primitive
+//     its place in a stable partition, and the scatter pass accumulates the boxes of the big children.
+//   * a node of <= 32 primitives is finished by ONE WARP: the primitives live in shared memory, lane k
+//     evaluates plane k of each axis, the subtree is built depth-first with a small stack, and its pairs go into
+//     a block of pair slots reserved for it (n - 1 pairs at most).
+// Pair numbering is deterministic (level base + node slot, scanned reservations): no atomics decide layout.
+// The tree may differ from the host builder's in the order of primitives inside a leaf (stable partition here,
+// std::partition there); the walk's result does not depend on it (every hit is validated against its reference
+// leaf box and ties go to the lowest reference index, trace.cuh).
+#include "gpu_fast_build.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+
+namespace rb {
+namespace {
+
+constexpr uint32_t kSmall = 32;   // nodes of <= kSmall primitives are finished by one warp
+constexpr int kGpuBins = 32;
+constexpr uint32_t kNone = 0xFFFFFFFFu;
+constexpr uint32_t kRootRec = 0xFFFFFFFEu;
+constexpr uint32_t kLeafRef = 0x80000000u, kSphereRef = 0x08000000u;
+constexpr float kMaxF = 3.402823466e+38f;
+
+// float <-> unsigned with the same order (so that integer atomicMin / atomicMax order floats)
+__device__ __forceinline__ uint32_t f2o(float f) {
+    uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float o2f(uint32_t o) {
+    return __uint_as_float((o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o);
+}
+constexpr uint32_t kOrdMaxInit = 0u;          // below every float
+constexpr uint32_t kOrdMinInit = 0xFFFFFFFFu; // above every float
+
+__device__ __forceinline__ void atomic_box(uint32_t* b, const float mn[3], const float mx[3]) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        if (mn[k] == mn[k]) atomicMin(b + k, f2o(mn[k])); // fminf / fmaxf ignore NaN operands
+        if (mx[k] == mx[k]) atomicMax(b + 3 + k, f2o(mx[k]));
+    }
+}
+
+struct BoxF {
+    float mn[3], mx[3];
+};
+__device__ __forceinline__ void box_reset(BoxF& b) {
+    for (int k = 0; k < 3; ++k) { b.mn[k] = kMaxF; b.mx[k] = -kMaxF; }
+}
+__device__ __forceinline__ void box_grow(BoxF& b, const float* lo, const float* hi) {
+    for (int k = 0; k < 3; ++k) { b.mn[k] = fminf(b.mn[k], lo[k]); b.mx[k] = fmaxf(b.mx[k], hi[k]); }
+}
+__device__ __forceinline__ float box_area(const BoxF& b) { // Bx::area of fast_bvh.cpp
+    float ex = b.mx[0] - b.mn[0], ey = b.mx[1] - b.mn[1], ez = b.mx[2] - b.mn[2];
+    if (ex < 0.0f) return 0.0f;
+    return ex * ey + ey * ez + ez * ex;
+}
+__device__ __forceinline__ int bin_of(float c, float lo, float scale) {
+    int k = (int)((c - lo) * scale);
+    return k < 0 ? 0 : (k >= kGpuBins ? kGpuBins - 1 : k);
+}
+
+// ---- exclusive scan of u32 (out has n + 1 entries), three kernels ---------------------------------------
+constexpr int kScanBlock = 1024;
+__device__ __forceinline__ uint32_t block_exclusive(uint32_t v, uint32_t* total) {
+    __shared__ uint32_t warp_sums[32];
+    const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= (uint32_t)o) inc += t;
+    }
+    if (lane == 31) warp_sums[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        uint32_t s = warp_sums[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xFFFFFFFFu, s, o);
+            if (lane >= (uint32_t)o) s += t;
+        }
+        warp_sums[lane] = s;
+    }
+    __syncthreads();
+    const uint32_t base = w ? warp_sums[w - 1] : 0u;
+    if (total) *total = warp_sums[31];
+    __syncthreads();
+    return base + inc - v;
+}
+__global__ void __launch_bounds__(kScanBlock) scan_partials(const uint32_t* in, uint32_t n, uint32_t* partial) {
+    const uint32_t i = blockIdx.x * kScanBlock + threadIdx.x;
+    uint32_t total;
+    block_exclusive(i < n ? in[i] : 0u, &total);
+    if (threadIdx.x == 0) partial[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(kScanBlock) scan_partials_scan(uint32_t* partial, uint32_t blocks) {
+    // one block walks the partial sums in chunks of 1024
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < blocks; base += kScanBlock) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i < blocks ? partial[i] : 0u;
+        uint32_t total;
+        const uint32_t ex = block_exclusive(v, &total);
+        if (i < blocks) partial[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) partial[blocks] = carry;
+}
+__global__ void __launch_bounds__(kScanBlock) scan_final(const uint32_t* in, uint32_t n, const uint32_t* partial, uint32_t* out) {
+    const uint32_t i = blockIdx.x * kScanBlock + threadIdx.x;
+    const uint32_t ex = block_exclusive(i < n ? in[i] : 0u, nullptr);
+    if (i < n) out[i] = partial[blockIdx.x] + ex;
+    if (i == 0) out[n] = partial[gridDim.x];
+}
+void exclusive_scan(const uint32_t* in, uint32_t n, uint32_t* out, uint32_t* partial, cudaStream_t st) {
+    const uint32_t blocks = (n + kScanBlock - 1) / kScanBlock;
+    scan_partials<<<blocks, kScanBlock, 0, st>>>(in, n, partial);
+    scan_partials_scan<<<1, kScanBlock, 0, st>>>(partial, blocks);
+    scan_final<<<blocks, kScanBlock, 0, st>>>(in, n, partial, out);
+}
+
+// ---- tier 1: big nodes, level by level -------------------------------------------------------------------
+struct WorkNode {
+    uint32_t start, n, rec, depth; // rec: index of this node's 32-byte record (kRootRec: the root record)
+};
+struct NodeInfo { // decoded once per node per level
+    float box_mn[3], box_mx[3];
+    float lo[3], scale[3];
+    uint32_t active; // bit a: the centroids spread along axis a
+};
+struct Decision {
+    uint32_t axis, bin;  // primitive goes left iff bin_of(axis) < bin
+    float lo, scale;
+    uint32_t nl;         // primitives on the left
+    uint32_t positional; // 1: centroids coincide (or the plane separates nothing): split by position at n / 2
+    uint32_t pair;       // pair slot of the two children
+    uint32_t child_slot[2]; // slot in the next level's big list, or kNone
+};
+constexpr int kAcc = 12;                 // box min, box max, centroid min, centroid max
+constexpr int kBinWords = 7;             // box min, box max, count
+constexpr int kNodeBinWords = 3 * kGpuBins * kBinWords;
+
+__global__ void init_acc(uint32_t* acc, uint32_t nodes) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nodes * kAcc) return;
+    const uint32_t k = i % kAcc;
+    acc[i] = (k % 6) < 3 ? kOrdMinInit : kOrdMaxInit;
+}
+__global__ void init_bins(uint32_t* bins, uint32_t nodes) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)nodes * kNodeBinWords) return;
+    const uint32_t k = (uint32_t)(i % kBinWords);
+    bins[i] = k < 3 ? kOrdMinInit : (k < 6 ? kOrdMaxInit : 0u);
+}
+// Box and centroid box of every big node: positions of a node are contiguous, so a warp first reduces each run of
+// equal slots with shuffles and only the first lane of a run touches memory (same-address atomics from different
+// warps serialise at ~15 ns each: 2 ms per level for the top levels without this).
+__device__ __forceinline__ uint32_t run_min(uint32_t v, uint32_t key, uint32_t lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t ov = __shfl_down_sync(0xFFFFFFFFu, v, o), ok = __shfl_down_sync(0xFFFFFFFFu, key, o);
+        if (lane + o < 32 && ok == key) v = min(v, ov);
+    }
+    return v;
+}
+__device__ __forceinline__ uint32_t run_max(uint32_t v, uint32_t key, uint32_t lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t ov = __shfl_down_sync(0xFFFFFFFFu, v, o), ok = __shfl_down_sync(0xFFFFFFFFu, key, o);
+        if (lane + o < 32 && ok == key) v = max(v, ov);
+    }
+    return v;
+}
+__global__ void accumulate_boxes(const float4* __restrict__ bmn, const float4* __restrict__ bmx, const uint32_t* __restrict__ order,
+                                 const uint32_t* __restrict__ node_of, uint32_t n, uint32_t* acc) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u;
+    const uint32_t s = p < n ? node_of[p] : kNone;
+    uint32_t lo[6], hi[6]; // ordered-integer images; NaN bounds are skipped like fminf / fmaxf skip them
+#pragma unroll
+    for (int k = 0; k < 6; ++k) { lo[k] = kOrdMinInit; hi[k] = kOrdMaxInit; }
+    if (s != kNone) {
+        const uint32_t id = order[p];
+        const float4 a = bmn[id], b = bmx[id];
+        const float mn[3] = {a.x, a.y, a.z}, mx[3] = {b.x, b.y, b.z};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float c = 0.5f * (mn[k] + mx[k]);
+            if (mn[k] == mn[k]) lo[k] = f2o(mn[k]);
+            if (mx[k] == mx[k]) hi[k] = f2o(mx[k]);
+            if (c == c) { lo[3 + k] = f2o(c); hi[3 + k] = f2o(c); }
+        }
+    }
+    const uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, s, 1);
+    const bool head = lane == 0 || prev != s;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        lo[k] = run_min(lo[k], s, lane);
+        hi[k] = run_max(hi[k], s, lane);
+    }
+    if (s == kNone || !head) return;
+    uint32_t* a = acc + (size_t)s * kAcc;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        atomicMin(a + k, lo[k]);
+        atomicMax(a + 3 + k, hi[k]);
+        atomicMin(a + 6 + k, lo[3 + k]);
+        atomicMax(a + 9 + k, hi[3 + k]);
+    }
+}
+__global__ void prepare_nodes(const uint32_t* __restrict__ acc, uint32_t nodes, NodeInfo* info) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= nodes) return;
+    const uint32_t* a = acc + (size_t)s * kAcc;
+    NodeInfo ni;
+    ni.active = 0;
+    for (int k = 0; k < 3; ++k) {
+        ni.box_mn[k] = o2f(a[k]);
+        ni.box_mx[k] = o2f(a[3 + k]);
+        const float lo = o2f(a[6 + k]), hi = o2f(a[9 + k]);
+        ni.lo[k] = lo;
+        ni.scale[k] = 0.0f;
+        if (hi > lo) {
+            ni.active |= 1u << k;
+            ni.scale[k] = (float)kGpuBins / (hi - lo);
+        }
+    }
+    info[s] = ni;
+}
+// One thread per primitive.  A block whose 256 positions all belong to ONE node (every block of the top levels)
+// bins into shared memory and flushes its non-empty bins once; other blocks go to the global bins directly.
+constexpr uint32_t kBinThreads = 256;
+__global__ void __launch_bounds__(kBinThreads) bin_prims(const float4* __restrict__ bmn, const float4* __restrict__ bmx,
+                                                       const uint32_t* __restrict__ order, const uint32_t* __restrict__ node_of, uint32_t n,
+                                                       const NodeInfo* __restrict__ info, uint32_t* bins) {
+    __shared__ uint32_t local[kNodeBinWords];
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t s = p < n ? node_of[p] : kNone;
+    const uint32_t s0 = node_of[blockIdx.x * blockDim.x];
+    const bool uniform = __syncthreads_and(s == s0 || p >= n) && s0 != kNone;
+    if (uniform) {
+        for (uint32_t i = threadIdx.x; i < (uint32_t)kNodeBinWords; i += kBinThreads) {
+            const uint32_t k = i % kBinWords;
+            local[i] = k < 3 ? kOrdMinInit : (k < 6 ? kOrdMaxInit : 0u);
+        }
+        __syncthreads();
+    }
+    if (s != kNone) {
+        const uint32_t id = order[p];
+        const float4 a = bmn[id], b = bmx[id];
+        const float mn[3] = {a.x, a.y, a.z}, mx[3] = {b.x, b.y, b.z};
+        const NodeInfo& ni = info[s];
+        const uint32_t active = ni.active;
+#pragma unroll
+        for (int ax = 0; ax < 3; ++ax) {
+            if (!(active >> ax & 1u)) continue;
+            const int k = bin_of(0.5f * (mn[ax] + mx[ax]), ni.lo[ax], ni.scale[ax]);
+            uint32_t* w = (uniform ? local : bins + (size_t)s * kNodeBinWords) + ((size_t)ax * kGpuBins + k) * kBinWords;
+            atomic_box(w, mn, mx);
+            atomicAdd(w + 6, 1u);
+        }
+    }
+    if (!uniform) return;
+    __syncthreads();
+    uint32_t* g = bins + (size_t)s0 * kNodeBinWords;
+    for (uint32_t i = threadIdx.x; i < (uint32_t)kNodeBinWords; i += kBinThreads) {
+        const uint32_t bin = i / kBinWords, k = i % kBinWords;
+        if (local[bin * kBinWords + 6] == 0) continue;
+        if (k < 3) atomicMin(g + i, local[i]);
+        else if (k < 6) atomicMax(g + i, local[i]);
+        else atomicAdd(g + i, local[i]);
+    }
+}
+// 32 nodes x 3 axes per block: thread (node, axis) sweeps the 31 planes of its axis, thread (node, 0) decides
+__global__ void __launch_bounds__(96) decide_splits(const WorkNode* __restrict__ work, uint32_t nodes, const NodeInfo* __restrict__ info,
+                                                    const uint32_t* __restrict__ bins, uint32_t pair_base, Decision* dec,
+                                                    GpuNode* records, GpuNode* root_record, uint32_t* child_big, uint32_t* child_small) {
+    __shared__ float s_cost[96];
+    __shared__ uint32_t s_bin[96], s_nl[96];
+    const uint32_t local = threadIdx.x / 3, ax = threadIdx.x % 3;
+    const uint32_t s = blockIdx.x * 32 + local;
+    float best_cost = kMaxF;
+    uint32_t best_bin = 0, best_nl = 0;
+    if (s < nodes && (info[s].active >> ax & 1u)) {
+        const uint32_t* w = bins + ((size_t)s * 3 + ax) * kGpuBins * kBinWords;
+        float rarea[kGpuBins];
+        uint32_t rcnt[kGpuBins];
+        BoxF acc;
+        box_reset(acc);
+        uint32_t cnt = 0;
+        for (int k = kGpuBins - 1; k >= 1; --k) {
+            const uint32_t* b = w + k * kBinWords;
+            if (b[6]) {
+                const float lo[3] = {o2f(b[0]), o2f(b[1]), o2f(b[2])}, hi[3] = {o2f(b[3]), o2f(b[4]), o2f(b[5])};
+                box_grow(acc, lo, hi);
+            }
+            cnt += b[6];
+            rarea[k] = box_area(acc);
+            rcnt[k] = cnt;
+        }
+        box_reset(acc);
+        cnt = 0;
+        for (int k = 1; k < kGpuBins; ++k) { // plane between bin k-1 and bin k
+            const uint32_t* b = w + (k - 1) * kBinWords;
+            if (b[6]) {
+                const float lo[3] = {o2f(b[0]), o2f(b[1]), o2f(b[2])}, hi[3] = {o2f(b[3]), o2f(b[4]), o2f(b[5])};
+                box_grow(acc, lo, hi);
+            }
+            cnt += b[6];
+            if (cnt == 0 || rcnt[k] == 0) continue;
+            const float cost = box_area(acc) * (float)cnt + rarea[k] * (float)rcnt[k];
+            if (cost < best_cost) { best_cost = cost; best_bin = (uint32_t)k; best_nl = cnt; }
+        }
+    }
+    s_cost[threadIdx.x] = best_cost;
+    s_bin[threadIdx.x] = best_bin;
+    s_nl[threadIdx.x] = best_nl;
+    __syncthreads();
+    if (ax != 0 || s >= nodes) return;
+    int axis = -1;
+    float cost = kMaxF;
+    for (int a = 0; a < 3; ++a)
+        if (s_cost[local * 3 + a] < cost) { cost = s_cost[local * 3 + a]; axis = a; }
+    const WorkNode wn = work[s];
+    const NodeInfo& ni = info[s];
+    Decision d;
+    d.positional = 0;
+    d.axis = 0;
+    d.bin = 0;
+    d.lo = 0.0f;
+    d.scale = 0.0f;
+    d.nl = wn.n / 2;
+    if (axis < 0) {
+        d.positional = 1;
+    } else {
+        d.axis = (uint32_t)axis;
+        d.bin = s_bin[local * 3 + axis];
+        d.lo = ni.lo[axis];
+        d.scale = ni.scale[axis];
+        d.nl = s_nl[local * 3 + axis];
+        if (d.nl == 0 || d.nl == wn.n) { // cannot happen (both sides counted), kept like the host builder
+            d.positional = 1;
+            d.nl = wn.n / 2;
+        }
+    }
+    d.pair = pair_base + s;
+    d.child_slot[0] = d.child_slot[1] = kNone;
+    dec[s] = d;
+    GpuNode g;
+    g.min_x = ni.box_mn[0]; g.min_y = ni.box_mn[1]; g.min_z = ni.box_mn[2];
+    g.max_x = ni.box_mx[0]; g.max_y = ni.box_mx[1]; g.max_z = ni.box_mx[2];
+    g.link0 = 2 * d.pair; // record index of the left child; the right child follows it
+    g.link1 = 0;
+    *(wn.rec == kRootRec ? root_record : records + wn.rec) = g;
+    const uint32_t nc[2] = {d.nl, wn.n - d.nl};
+    for (int c = 0; c < 2; ++c) {
+        child_big[2 * s + c] = nc[c] > kSmall ? 1u : 0u;
+        child_small[2 * s + c] = nc[c] > kSmall ? 0u : 1u;
+    }
+}
+// one thread per child: append it to the next level's big list or to the list of small subtrees
+__global__ void make_children(const WorkNode* __restrict__ work, uint32_t nodes, Decision* dec, const uint32_t* __restrict__ big_index,
+                              const uint32_t* __restrict__ small_index, WorkNode* next, WorkNode* small, uint32_t small_base) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nodes * 2) return;
+    const uint32_t s = i >> 1, c = i & 1u;
+    const WorkNode wn = work[s];
+    Decision& d = dec[s];
+    WorkNode child;
+    child.start = c ? wn.start + d.nl : wn.start;
+    child.n = c ? wn.n - d.nl : d.nl;
+    child.rec = 2 * d.pair + c;
+    child.depth = wn.depth + 1;
+    if (child.n > kSmall) {
+        const uint32_t slot = big_index[i];
+        next[slot] = child;
+        d.child_slot[c] = slot;
+    } else {
+        small[small_base + small_index[i]] = child;
+    }
+}
+__global__ void left_flags(const float4* __restrict__ bmn, const float4* __restrict__ bmx, const uint32_t* __restrict__ order,
+                           const uint32_t* __restrict__ node_of, uint32_t n, const WorkNode* __restrict__ work,
+                           const Decision* __restrict__ dec, uint32_t* flags) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const uint32_t s = node_of[p];
+    uint32_t f = 0;
+    if (s != kNone) {
+        const Decision& d = dec[s];
+        if (d.positional) {
+            f = (p - work[s].start) < d.nl;
+        } else {
+            const uint32_t id = order[p];
+            const float4 a = bmn[id], b = bmx[id];
+            const float mn = d.axis == 0 ? a.x : (d.axis == 1 ? a.y : a.z), mx = d.axis == 0 ? b.x : (d.axis == 1 ? b.y : b.z);
+            f = (uint32_t)bin_of(0.5f * (mn + mx), d.lo, d.scale) < d.bin;
+        }
+    }
+    flags[p] = f;
+}
+// stable partition of every big node's range + next level's node_of
+__global__ void scatter_prims(const uint32_t* __restrict__ order, const uint32_t* __restrict__ node_of, uint32_t n,
+                              const WorkNode* __restrict__ work, const Decision* __restrict__ dec, const uint32_t* __restrict__ flags,
+                              const uint32_t* __restrict__ scan, uint32_t* order_out, uint32_t* node_of_out) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const uint32_t s = node_of[p];
+    const uint32_t id = order[p];
+    if (s == kNone) {
+        order_out[p] = id;
+        node_of_out[p] = kNone;
+        return;
+    }
+    const WorkNode wn = work[s];
+    const Decision& d = dec[s];
+    const uint32_t lefts_before = scan[p] - scan[wn.start];
+    const uint32_t q = p - wn.start;
+    const uint32_t left = flags[p];
+    const uint32_t dst = wn.start + (left ? lefts_before : d.nl + (q - lefts_before));
+    const uint32_t slot = d.child_slot[left ? 0 : 1];
+    order_out[dst] = id;
+    node_of_out[dst] = slot;
+}
+
+// ---- tier 2: one warp finishes a subtree of <= 32 primitives ------------------------------------------------
+struct SmallShared {
+    float mn[3][32], mx[3][32], c[3][32];
+    uint32_t id[32]; // bit 31: sphere
+    uint32_t st_range[34], st_rec[34], st_depth[34]; // range = b | e << 8
+};
+__device__ __forceinline__ float warp_min_f(float v) { return o2f(__reduce_min_sync(0xFFFFFFFFu, f2o(v))); }
+__device__ __forceinline__ float warp_max_f(float v) { return o2f(__reduce_max_sync(0xFFFFFFFFu, f2o(v))); }
+
+constexpr int kSmallWarps = 4;
+__global__ void __launch_bounds__(32 * kSmallWarps) build_small(const float4* __restrict__ bmn, const float4* __restrict__ bmx,
+                                                                uint32_t* order, const WorkNode* __restrict__ small, uint32_t count,
+                                                                const uint32_t* __restrict__ pair_offset, uint32_t pair_base,
+                                                                GpuNode* records, GpuNode* root_record, uint32_t leaf_max, float trav_cost,
+                                                                uint32_t* max_depth) {
+    __shared__ SmallShared shared[kSmallWarps];
+    const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+    const uint32_t item = blockIdx.x * kSmallWarps + w;
+    if (item >= count) return;
+    SmallShared& S = shared[w];
+    const WorkNode wn = small[item];
+    if (lane < wn.n) {
+        const uint32_t id = order[wn.start + lane];
+        const float4 a = bmn[id], b = bmx[id];
+        S.mn[0][lane] = a.x; S.mn[1][lane] = a.y; S.mn[2][lane] = a.z;
+        S.mx[0][lane] = b.x; S.mx[1][lane] = b.y; S.mx[2][lane] = b.z;
+        S.c[0][lane] = 0.5f * (a.x + b.x); S.c[1][lane] = 0.5f * (a.y + b.y); S.c[2][lane] = 0.5f * (a.z + b.z);
+        S.id[lane] = id | (__float_as_uint(b.w) ? 0x80000000u : 0u);
+    }
+    uint32_t next_pair = pair_base + pair_offset[item];
+    uint32_t deepest = 0;
+    int sp = 0;
+    if (lane == 0) { S.st_range[0] = 0u | (wn.n << 8); S.st_rec[0] = wn.rec; S.st_depth[0] = wn.depth; }
+    sp = 1;
+    __syncwarp();
+    while (sp > 0) {
+        --sp;
+        const uint32_t range = S.st_range[sp], rec = S.st_rec[sp], depth = S.st_depth[sp];
+        const uint32_t b = range & 0xFFu, e = range >> 8, m = e - b;
+        const bool in = lane >= b && lane < e;
+        // node box and centroid box
+        float bx_mn[3], bx_mx[3], cb_mn[3], cb_mx[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            // NaN bounds are skipped like fminf / fmaxf skip them
+            const float lo = in ? S.mn[k][lane] : kMaxF, hi = in ? S.mx[k][lane] : -kMaxF, cc = in ? S.c[k][lane] : kMaxF;
+            bx_mn[k] = warp_min_f(lo == lo ? lo : kMaxF);
+            bx_mx[k] = warp_max_f(hi == hi ? hi : -kMaxF);
+            cb_mn[k] = warp_min_f(cc == cc ? cc : kMaxF);
+            const float c2 = in ? S.c[k][lane] : -kMaxF;
+            cb_mx[k] = warp_max_f(c2 == c2 ? c2 : -kMaxF);
+        }
+        GpuNode g;
+        g.min_x = bx_mn[0]; g.min_y = bx_mn[1]; g.min_z = bx_mn[2];
+        g.max_x = bx_mx[0]; g.max_y = bx_mx[1]; g.max_z = bx_mx[2];
+        const uint32_t first_kind = S.id[b] >> 31;
+        const bool mixed = __any_sync(0xFFFFFFFFu, in && (S.id[lane] >> 31) != first_kind);
+        bool leaf = m <= 1;
+        int best_axis = -1;
+        uint32_t best_bin = 0;
+        float best_cost = kMaxF;
+        if (!leaf) {
+            // lane k (1..31) evaluates the plane between bin k-1 and bin k on each axis
+#pragma unroll 1
+            for (int ax = 0; ax < 3; ++ax) {
+                const float lo = cb_mn[ax], hi = cb_mx[ax];
+                if (!(hi > lo)) continue;
+                const float scale = (float)kGpuBins / (hi - lo);
+                BoxF L, R;
+                box_reset(L);
+                box_reset(R);
+                uint32_t nl = 0, nr = 0;
+                for (uint32_t j = b; j < e; ++j) {
+                    const int k = bin_of(S.c[ax][j], lo, scale);
+                    const float pmn[3] = {S.mn[0][j], S.mn[1][j], S.mn[2][j]}, pmx[3] = {S.mx[0][j], S.mx[1][j], S.mx[2][j]};
+                    if (k < (int)lane) { box_grow(L, pmn, pmx); ++nl; } else { box_grow(R, pmn, pmx); ++nr; }
+                }
+                float cost = kMaxF;
+                if (lane >= 1 && nl != 0 && nr != 0) cost = box_area(L) * (float)nl + box_area(R) * (float)nr;
+                // lowest cost, ties to the lowest plane (the host sweep keeps the first minimum)
+                const uint32_t key = f2o(cost);
+                const uint32_t mk = __reduce_min_sync(0xFFFFFFFFu, key);
+                const uint32_t who = __ffs(__ballot_sync(0xFFFFFFFFu, key == mk)) - 1u;
+                const float c = o2f(mk);
+                if (c < best_cost) { best_cost = c; best_axis = ax; best_bin = who; }
+            }
+            if (m <= leaf_max) {
+                BoxF pb;
+                for (int k = 0; k < 3; ++k) { pb.mn[k] = bx_mn[k]; pb.mx[k] = bx_mx[k]; }
+                const float parent_area = box_area(pb);
+                const float leaf_cost = (float)m * parent_area;
+                const float split_cost = trav_cost * parent_area + best_cost;
+                if (!mixed && (best_axis < 0 || leaf_cost <= split_cost)) leaf = true;
+            }
+        }
+        if (leaf) {
+            g.link0 = kLeafRef | ((m - 1u) << 28) | (first_kind ? kSphereRef : 0u) | (wn.start + b);
+            g.link1 = m;
+            deepest = max(deepest, depth);
+        } else {
+            // stable partition of [b, e) inside the warp
+            uint32_t mid = b + m / 2;
+            if (best_axis >= 0) {
+                const float lo = cb_mn[best_axis], scale = (float)kGpuBins / (cb_mx[best_axis] - lo);
+                const bool left = in && (uint32_t)bin_of(S.c[best_axis][lane], lo, scale) < best_bin;
+                const uint32_t lmask = __ballot_sync(0xFFFFFFFFu, left), imask = __ballot_sync(0xFFFFFFFFu, in);
+                const uint32_t nl = __popc(lmask);
+                if (nl != 0 && nl != m) {
+                    const uint32_t below = (1u << lane) - 1u;
+                    const uint32_t dst = left ? b + __popc(lmask & below) : b + nl + __popc(imask & ~lmask & below);
+                    float v[9];
+                    uint32_t vid = 0;
+                    if (in) {
+                        for (int k = 0; k < 3; ++k) { v[k] = S.mn[k][lane]; v[3 + k] = S.mx[k][lane]; v[6 + k] = S.c[k][lane]; }
+                        vid = S.id[lane];
+                    }
+                    __syncwarp();
+                    if (in) {
+                        for (int k = 0; k < 3; ++k) { S.mn[k][dst] = v[k]; S.mx[k][dst] = v[3 + k]; S.c[k][dst] = v[6 + k]; }
+                        S.id[dst] = vid;
+                    }
+                    mid = b + nl;
+                }
+            }
+            const uint32_t pair = next_pair++;
+            g.link0 = 2 * pair;
+            g.link1 = 0;
+            if (lane == 0) { // right below left: the left child is popped first (depth-first)
+                S.st_range[sp] = mid | (e << 8); S.st_rec[sp] = 2 * pair + 1; S.st_depth[sp] = depth + 1;
+                S.st_range[sp + 1] = b | (mid << 8); S.st_rec[sp + 1] = 2 * pair; S.st_depth[sp + 1] = depth + 1;
+            }
+            sp += 2;
+        }
+        if (lane == 0) *(rec == kRootRec ? root_record : records + rec) = g;
+        __syncwarp();
+    }
+    if (lane < wn.n) order[wn.start + lane] = S.id[lane] & 0x7FFFFFFFu;
+    if (lane == 0) atomicMax(max_depth, deepest);
+}
+
+// 64-byte records in leaf order (see fast_bvh.cpp): triangles {n, d | v0, id | v1, reference leaf | v2, n.n} with the
+// operation order of Triangle::intersects (rayca-geometry/src/triangle.rs:90-94,110,152); spheres are copied
+// from the host-made records.
+__global__ void emit_records(const uint32_t* __restrict__ order, uint32_t n, const float4* __restrict__ tri_pos,
+                             const uint32_t* __restrict__ ref_leaf, const float4* __restrict__ bmx,
+                             const float4* __restrict__ sphere_records, float4* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t id = order[i];
+    float4* dst = out + (size_t)i * 4;
+    if (__float_as_uint(bmx[id].w)) {
+        const uint32_t k = __float_as_uint(bmx[id].w) - 1u;
+        for (int j = 0; j < 4; ++j) dst[j] = sphere_records[(size_t)k * 4 + j];
+        return;
+    }
+    const float4 p0 = tri_pos[(size_t)id * 3], p1 = tri_pos[(size_t)id * 3 + 1], p2 = tri_pos[(size_t)id * 3 + 2];
+    const V3 v0{p0.x, p0.y, p0.z}, v1{p1.x, p1.y, p1.z}, v2{p2.x, p2.y, p2.z};
+    const V3 nn = cross(v1 - v0, v2 - v0); // rmath.h: the reference's operation order
+    const float d = -dot(nn, v0);
+    const float den = dot(nn, nn);
+    const float nx = nn.x, ny = nn.y, nz = nn.z;
+    dst[0] = make_float4(nx, ny, nz, d);
+    dst[1] = make_float4(p0.x, p0.y, p0.z, __uint_as_float(id));
+    dst[2] = make_float4(p1.x, p1.y, p1.z, __uint_as_float(ref_leaf[id]));
+    dst[3] = make_float4(p2.x, p2.y, p2.z, den);
+}
+__global__ void small_sizes(const WorkNode* __restrict__ small, uint32_t count, uint32_t* sizes) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) sizes[i] = small[i].n - 1u; // pairs a subtree over n primitives can need
+}
+
+struct DeviceBuffers { // one cudaMalloc for all temporaries (35 separate allocations cost more than the build)
+    struct Want { void** p; size_t offset; };
+    std::vector<Want> wants;
+    size_t bytes = 0;
+    void* base = nullptr;
+    std::vector<void*> kept; // separately allocated outputs, freed unless released
+    ~DeviceBuffers() {
+        cudaFree(base);
+        for (void* p : kept) cudaFree(p);
+    }
+    template <class T> cudaError_t alloc(T** out, size_t count) { // temporaries: address assigned by commit()
+        wants.push_back({(void**)out, bytes});
+        bytes += (std::max<size_t>(count, 1) * sizeof(T) + 255) & ~size_t(255);
+        return cudaSuccess;
+    }
+    cudaError_t commit() {
+        cudaError_t e = cudaMalloc(&base, bytes);
+        if (e != cudaSuccess) return e;
+        for (const Want& w : wants) *w.p = (char*)base + w.offset;
+        return cudaSuccess;
+    }
+    template <class T> cudaError_t alloc_output(T** out, size_t count) {
+        void* p = nullptr;
+        cudaError_t e = cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T));
+        if (e == cudaSuccess) kept.push_back(p);
+        *out = (T*)p;
+        return e;
+    }
+    void release(void* p) { kept.erase(std::remove(kept.begin(), kept.end(), p), kept.end()); }
+};
+
+inline uint32_t blocks_for(size_t n, uint32_t threads) { return (uint32_t)((n + threads - 1) / threads); }
+
+} // namespace
+
+#define FB_TRY(expr)                                                                 \
+    do {                                                                             \
+        cudaError_t e__ = (expr);                                                    \
+        if (e__ != cudaSuccess) {                                                    \
+            err = std::string("device tree build: ") + cudaGetErrorString(e__);     \
+            return e__ == cudaErrorMemoryAllocation ? RAYCA_E_OOM : RAYCA_E_CUDA;    \
+        }                                                                            \
+    } while (0)
+
+int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStream_t st, FastTreeDevice& out, std::string& err) {
+    int bins_unused;
+    uint32_t leaf_max;
+    float trav_cost;
+    fast_tree_tunables(bins_unused, leaf_max, trav_cost);
+    const size_t nb = hs.blas.size();
+    const uint32_t N = hs.blas_prim_offset[nb];
+    if (N == 0) { err = "no primitives"; return RAYCA_E_INVALID_ARG; }
+
+    // ---- host side: bounds in reference-global order, reference leaf of every primitive, sphere records
+    std::vector<float4> hmn(N), hmx(N);
+    std::vector<uint32_t> ref_leaf(N, 0);
+    std::vector<float4> sphere_records;
+    std::vector<uint32_t> sphere_base(nb + 1, 0);
+    for (size_t bi = 0; bi < nb; ++bi) sphere_base[bi + 1] = sphere_base[bi] + (uint32_t)hs.blas[bi].spheres.size();
+    sphere_records.resize((size_t)sphere_base[nb] * 4);
+    for (size_t bi = 0; bi < nb; ++bi) {
+        const HostBlas& b = hs.blas[bi];
+        const uint32_t po = hs.blas_prim_offset[bi];
+        for (size_t k = 0; k < b.nodes.size(); ++k) {
+            const HostNode& n = b.nodes[k];
+            if (k == 1 || n.count == 0) continue;
+            const uint32_t leaf = hs.blas_node_offset[bi] + (uint32_t)k;
+#pragma omp parallel for schedule(static) if (n.count > 8192)
+            for (int64_t i = 0; i < (int64_t)n.count; ++i) ref_leaf[po + n.offset + (size_t)i] = leaf;
+        }
+#pragma omp parallel for schedule(static) if (b.tris.size() > 8192)
+        for (int64_t k = 0; k < (int64_t)b.tris.size(); ++k) {
+            const HostTri& t = b.tris[(size_t)k];
+            const uint32_t id = po + (uint32_t)k;
+            uint32_t sphere = 0;
+            if (t.sphere) {
+                sphere = sphere_base[bi] + t.sphere; // 1-based, scene-global
+                const HostSphere& sp = b.spheres[t.sphere - 1];
+                const V3 rs = reciprocal(sp.world.s);
+                const Q4 qi = conj(sp.world.q);
+                float4* dst = &sphere_records[(size_t)(sphere - 1) * 4];
+                dst[0] = make_float4(-sp.world.t.x, -sp.world.t.y, -sp.world.t.z, sp.radius2);
+                dst[1] = make_float4(qi.x, qi.y, qi.z, qi.w);
+                dst[2] = make_float4(rs.x, rs.y, rs.z, __builtin_bit_cast(float, id));
+                dst[3] = make_float4(sp.center.x, sp.center.y, sp.center.z, 0.0f); // w: reference leaf, below
+            }
+            hmn[id] = make_float4(t.bmin.x, t.bmin.y, t.bmin.z, 0.0f);
+            hmx[id] = make_float4(t.bmax.x, t.bmax.y, t.bmax.z, __builtin_bit_cast(float, sphere));
+        }
+        for (size_t k = 0; k < b.tris.size(); ++k)
+            if (b.tris[k].sphere) {
+                const uint32_t sphere = sphere_base[bi] + b.tris[k].sphere;
+                sphere_records[(size_t)(sphere - 1) * 4 + 3].w = __builtin_bit_cast(float, ref_leaf[po + k]);
+            }
+    }
+
+    // ---- device buffers
+    DeviceBuffers buf;
+    const uint32_t cap_big = N / (kSmall + 1) + 1;
+    float4 *d_mn, *d_mx, *d_sphere, *d_tri;
+    uint32_t *d_order[2], *d_node_of[2], *d_flags, *d_scan, *d_partial, *d_ref_leaf, *d_acc[2], *d_bins, *d_child_big, *d_child_small,
+        *d_big_index, *d_small_index, *d_sizes, *d_pair_offset, *d_depth;
+    WorkNode *d_work[2], *d_small;
+    NodeInfo* d_info;
+    Decision* d_dec;
+    GpuNode *d_records, *d_root;
+    FB_TRY(buf.alloc(&d_mn, N));
+    FB_TRY(buf.alloc(&d_mx, N));
+    FB_TRY(buf.alloc(&d_sphere, sphere_records.size()));
+    FB_TRY(buf.alloc_output(&d_tri, (size_t)N * 4));
+    for (int k = 0; k < 2; ++k) {
+        FB_TRY(buf.alloc(&d_order[k], N));
+        FB_TRY(buf.alloc(&d_node_of[k], N));
+        FB_TRY(buf.alloc(&d_acc[k], (size_t)cap_big * kAcc));
+        FB_TRY(buf.alloc(&d_work[k], cap_big));
+    }
+    FB_TRY(buf.alloc(&d_flags, N));
+    FB_TRY(buf.alloc(&d_scan, (size_t)N + 1));
+    FB_TRY(buf.alloc(&d_partial, (size_t)N / kScanBlock + 4));
+    FB_TRY(buf.alloc(&d_ref_leaf, N));
+    FB_TRY(buf.alloc(&d_bins, (size_t)cap_big * kNodeBinWords));
+    FB_TRY(buf.alloc(&d_child_big, (size_t)cap_big * 2));
+    FB_TRY(buf.alloc(&d_child_small, (size_t)cap_big * 2));
+    FB_TRY(buf.alloc(&d_big_index, (size_t)cap_big * 2 + 1));
+    FB_TRY(buf.alloc(&d_small_index, (size_t)cap_big * 2 + 1));
+    FB_TRY(buf.alloc(&d_small, N));
+    FB_TRY(buf.alloc(&d_sizes, N));
+    FB_TRY(buf.alloc(&d_pair_offset, (size_t)N + 1));
+    FB_TRY(buf.alloc(&d_depth, 1));
+    FB_TRY(buf.alloc(&d_info, cap_big));
+    FB_TRY(buf.alloc(&d_dec, cap_big));
+    FB_TRY(buf.alloc_output(&d_records, (size_t)N * 2 + 2));
+    FB_TRY(buf.alloc(&d_root, 1));
+    FB_TRY(buf.commit());
+
+    cudaEvent_t e0, e1;
+    FB_TRY(cudaEventCreate(&e0));
+    FB_TRY(cudaEventCreate(&e1));
+    FB_TRY(cudaMemcpyAsync(d_mn, hmn.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
+    FB_TRY(cudaMemcpyAsync(d_mx, hmx.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
+    FB_TRY(cudaMemcpyAsync(d_ref_leaf, ref_leaf.data(), (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    if (!sphere_records.empty())
+        FB_TRY(cudaMemcpyAsync(d_sphere, sphere_records.data(), sphere_records.size() * sizeof(float4), cudaMemcpyHostToDevice, st));
+    FB_TRY(cudaEventRecord(e0, st));
+    FB_TRY(cudaMemsetAsync(d_depth, 0, 4, st));
+    FB_TRY(cudaMemsetAsync(d_records, 0, ((size_t)N * 2 + 2) * sizeof(GpuNode), st));
+    {   // order = identity
+        std::vector<uint32_t> iota(N);
+        for (uint32_t i = 0; i < N; ++i) iota[i] = i;
+        FB_TRY(cudaMemcpyAsync(d_order[0], iota.data(), (size_t)N * 4, cudaMemcpyHostToDevice, st));
+        FB_TRY(cudaStreamSynchronize(st)); // iota goes out of scope
+    }
+    const uint32_t T = 256;
+    uint32_t nbig = 0, nsmall = 0, pair_base = 0, levels = 0;
+    int cur = 0;
+    WorkNode root_work{0u, N, kRootRec, 0u};
+    if (N > kSmall) {
+        nbig = 1;
+        FB_TRY(cudaMemcpyAsync(d_work[0], &root_work, sizeof(root_work), cudaMemcpyHostToDevice, st));
+        FB_TRY(cudaMemsetAsync(d_node_of[0], 0, (size_t)N * 4, st));
+        init_acc<<<1, 32, 0, st>>>(d_acc[0], 1);
+        accumulate_boxes<<<blocks_for(N, T), T, 0, st>>>(d_mn, d_mx, d_order[0], d_node_of[0], N, d_acc[0]);
+    } else {
+        nsmall = 1;
+        FB_TRY(cudaMemcpyAsync(d_small, &root_work, sizeof(root_work), cudaMemcpyHostToDevice, st));
+    }
+    while (nbig > 0) {
+        const int nxt = cur ^ 1;
+        prepare_nodes<<<blocks_for(nbig, T), T, 0, st>>>(d_acc[cur], nbig, d_info);
+        init_bins<<<blocks_for((size_t)nbig * kNodeBinWords, T), T, 0, st>>>(d_bins, nbig);
+        bin_prims<<<blocks_for(N, kBinThreads), kBinThreads, 0, st>>>(d_mn, d_mx, d_order[cur], d_node_of[cur], N, d_info, d_bins);
+        decide_splits<<<blocks_for(nbig, 32), 96, 0, st>>>(d_work[cur], nbig, d_info, d_bins, pair_base, d_dec, d_records, d_root,
+                                                           d_child_big, d_child_small);
+        exclusive_scan(d_child_big, nbig * 2, d_big_index, d_partial, st);
+        exclusive_scan(d_child_small, nbig * 2, d_small_index, d_partial, st);
+        uint32_t counts[2];
+        FB_TRY(cudaMemcpyAsync(&counts[0], d_big_index + nbig * 2, 4, cudaMemcpyDeviceToHost, st));
+        FB_TRY(cudaMemcpyAsync(&counts[1], d_small_index + nbig * 2, 4, cudaMemcpyDeviceToHost, st));
+        FB_TRY(cudaStreamSynchronize(st));
+        if (counts[0] > cap_big || (size_t)nsmall + counts[1] > N) { err = "device tree build: work list overflow"; return RAYCA_E_CUDA; }
+        make_children<<<blocks_for((size_t)nbig * 2, T), T, 0, st>>>(d_work[cur], nbig, d_dec, d_big_index, d_small_index, d_work[nxt],
+                                                                  d_small, nsmall);
+        if (counts[0]) init_acc<<<blocks_for((size_t)counts[0] * kAcc, T), T, 0, st>>>(d_acc[nxt], counts[0]);
+        left_flags<<<blocks_for(N, T), T, 0, st>>>(d_mn, d_mx, d_order[cur], d_node_of[cur], N, d_work[cur], d_dec, d_flags);
+        exclusive_scan(d_flags, N, d_scan, d_partial, st);
+        scatter_prims<<<blocks_for(N, T), T, 0, st>>>(d_order[cur], d_node_of[cur], N, d_work[cur], d_dec, d_flags, d_scan, d_order[nxt],
+                                                      d_node_of[nxt]);
+        if (counts[0]) accumulate_boxes<<<blocks_for(N, T), T, 0, st>>>(d_mn, d_mx, d_order[nxt], d_node_of[nxt], N, d_acc[nxt]);
+        pair_base += nbig;
+        nsmall += counts[1];
+        nbig = counts[0];
+        cur = nxt;
+        ++levels;
+        if (levels > 4096) { err = "device tree build: runaway depth"; return RAYCA_E_CUDA; }
+    }
+    if (nsmall) {
+        small_sizes<<<blocks_for(nsmall, T), T, 0, st>>>(d_small, nsmall, d_sizes);
+        exclusive_scan(d_sizes, nsmall, d_pair_offset, d_partial, st);
+        build_small<<<blocks_for(nsmall, kSmallWarps), 32 * kSmallWarps, 0, st>>>(d_mn, d_mx, d_order[cur], d_small, nsmall, d_pair_offset,
+                                                                              pair_base, d_records, d_root, leaf_max, trav_cost, d_depth);
+    }
+    emit_records<<<blocks_for(N, T), T, 0, st>>>(d_order[cur], N, d_tri_pos, d_ref_leaf, d_mx, d_sphere, d_tri);
+    FB_TRY(cudaEventRecord(e1, st));
+    FB_TRY(cudaMemcpyAsync(&out.root, d_root, sizeof(GpuNode), cudaMemcpyDeviceToHost, st));
+    FB_TRY(cudaMemcpyAsync(&out.depth, d_depth, 4, cudaMemcpyDeviceToHost, st));
+    FB_TRY(cudaStreamSynchronize(st));
+    FB_TRY(cudaGetLastError());
+    cudaEventElapsedTime(&out.build_ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    out.levels = levels;
+    out.small_subtrees = nsmall;
+    out.nodes = d_records;
+    out.tri = d_tri;
+    buf.release(d_records);
+    buf.release(d_tri);
+    return RAYCA_OK;
+}
+
+} // namespace rb

@@ -1,0 +1,26 @@
+// gpu_fast_build.h — performance tree built on the device (gpu_fast_build.cu); same records as fast_bvh.cpp.
+#pragma once
+#include <string>
+
+#include "host_scene.h"
+
+namespace rb {
+
+struct FastTreeDevice {
+    void* nodes = nullptr;  // GpuNode pairs (cudaMalloc); owned by the caller after a successful build
+    void* tri = nullptr;    // 4 x float4 per primitive in leaf order
+    GpuNode root{};         // link0: pair index 0 or a packed leaf
+    uint32_t depth = 0;     // deepest leaf
+    uint32_t levels = 0;    // level-synchronous passes over big nodes
+    uint32_t small_subtrees = 0;
+    float build_ms = 0.0f;  // device time, CUDA events
+};
+
+// Inputs: the packed host scene WITHOUT its performance tree (HostScene::{blas, blas_prim_offset,
+// blas_node_offset} final) and the device copy of HostScene::tri_pos.  Returns RAYCA_OK or an error code.
+int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStream_t stream, FastTreeDevice& out, std::string& err);
+
+// tunables shared with the host builder (fast_bvh.cpp)
+void fast_tree_tunables(int& bins, uint32_t& leaf_max, float& traversal_cost);
+
+} // namespace rb

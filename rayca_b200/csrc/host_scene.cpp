@@ -224,7 +224,7 @@ struct PhaseTimer { // RAYCA_TIMING=1 prints the host phases of scene_create to 
 };
 } // namespace
 
-int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::string& err) {
+int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::string& err, bool fast_tree) {
     PhaseTimer phase;
     Flatten f(d, out);
     f.run();
@@ -592,9 +592,11 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
     out.root = emit_tnode(troot, 0);
     out.max_stack = top_depth + max_blas_depth + 2;
     phase.lap("TLAS top pairs");
-    build_fast_tree(out);
-    phase.lap("performance tree");
-    out.max_stack = std::max(out.max_stack, out.fast_depth + 2);
+    if (fast_tree) {
+        build_fast_tree(out);
+        phase.lap("performance tree (host)");
+        out.max_stack = std::max(out.max_stack, out.fast_depth + 2);
+    }
     return RAYCA_OK;
 }
 

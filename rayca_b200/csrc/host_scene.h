@@ -79,7 +79,8 @@ struct HostScene {
 };
 
 // Returns RAYCA_OK or a negative RAYCA_E_* code; `err` receives a detail string.
-int build_host_scene(const rayca_scene_desc& desc, bool bvh, HostScene& out, std::string& err);
+// `fast_tree` = false leaves the performance tree to the device builder (gpu_fast_build.cu).
+int build_host_scene(const rayca_scene_desc& desc, bool bvh, HostScene& out, std::string& err, bool fast_tree = true);
 
 // BLAS build: top-down SAH over 63 planes x 3 axes with the reference's tie-breaking
 // (bvh/blas.rs:64-127,245-316), evaluated through per-plane bins so that one pass over the

@@ -1,6 +1,7 @@
 // rayca_cuda.cu — C ABI of librayca_cuda (include/rayca_cuda.h): context, scene upload, render.
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -9,6 +10,7 @@
 #include <cuda_runtime.h>
 
 #include "../../include/rayca_cuda.h"
+#include "gpu_fast_build.h"
 #include "host_scene.h"
 #include "render.cuh"
 
@@ -245,8 +247,11 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     double t0 = now_ms();
     std::string err;
     int rc;
+    // the performance tree is built on the device; RAYCA_HOST_FAST_TREE=1 (or a non-default bin count) keeps the
+    // host builder for A/B runs
+    const bool host_fast_tree = std::getenv("RAYCA_HOST_FAST_TREE") != nullptr || std::getenv("RAYCA_FAST_BINS") != nullptr;
     try {
-        rc = build_host_scene(*desc, bvh != 0, s->host, err);
+        rc = build_host_scene(*desc, bvh != 0, s->host, err, host_fast_tree);
     } catch (const std::bad_alloc&) {
         delete s;
         return fail(RAYCA_E_OOM, "host allocation while building the scene");
@@ -281,8 +286,29 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     UP(d_texels, texels);
     UP(d_lights, lights);
     UP(d_blas_prim_offset, blas_prim_offset);
-    UP(d_fast_nodes, fast_nodes);
-    UP(d_fast_tri, fast_tri);
+    if (host_fast_tree) {
+        UP(d_fast_nodes, fast_nodes);
+        UP(d_fast_tri, fast_tri);
+    } else {
+        FastTreeDevice ft;
+        rc = build_fast_tree_device(h, (const float4*)s->d_tri_pos, ctx->render_stream, ft, err);
+        if (rc != RAYCA_OK) {
+            rayca_cuda_scene_destroy(s);
+            return fail(rc, err);
+        }
+        s->d_fast_nodes = ft.nodes;
+        s->d_fast_tri = ft.tri;
+        h.fast_root = ft.root;
+        h.fast_depth = ft.depth;
+        h.max_stack = std::max(h.max_stack, ft.depth + 2);
+        if (std::getenv("RAYCA_TIMING"))
+            std::fprintf(stderr, "[rayca] %-28s %8.2f ms (%u levels, %u warp subtrees, depth %u)\n", "performance tree (device)",
+                         ft.build_ms, ft.levels, ft.small_subtrees, ft.depth);
+        if (h.max_stack > (uint32_t)kStackSize) {
+            rayca_cuda_scene_destroy(s);
+            return fail(RAYCA_E_UNSUPPORTED, "BVH deeper than the traversal stack");
+        }
+    }
 #undef UP
     GpuSceneView& v = s->view;
     v.nodes = (const float4*)s->d_nodes;
