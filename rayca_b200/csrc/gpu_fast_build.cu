@@ -598,6 +598,282 @@ __global__ void emit_records(const uint32_t* __restrict__ order, uint32_t n, con
     dst[2] = make_float4(p1.x, p1.y, p1.z, __uint_as_float(ref_leaf[id]));
     dst[3] = make_float4(p2.x, p2.y, p2.z, den);
 }
+// =====================================================================================================
+// Reference BLAS on the device: the tree of rayca-soft/src/bvh/blas.rs:64-127,245-316, node for node and
+// primitive order for primitive order (see bvh_build.cpp for the host version and why binning by candidate
+// index is exact).  The reference builder stops early (its candidate boxes start at the origin, A-21), so
+// its trees have a few hundred nodes over very large ranges: every level is a handful of passes over all
+// primitives, which is what the host spends 110 ms on for 262k triangles.
+//   * 63 planes x 3 axes: a primitive is LEFT of plane i iff centroid < lo + i * scale; k = first such i (binary
+//     search with the same comparisons), bins k in [1, 64]; prefix / suffix unions give every candidate's boxes.
+//   * the in-place swap partition (blas.rs:283-291) is a fixed permutation of the range given the left/right
+//     flags: lefts below nL stay, the k-th right at or below nL (ascending) goes to t(k-1) - 1, the k-th left
+//     above nL (descending, positions t1 > t2 > ...) goes into the k-th hole, every other right moves down by
+//     one (t0 = n).  Checked against the sequential loop in tests/test_partition_permutation.py.
+//   * nodes get temporary ids level by level; the host renumbers them in the reference's depth-first push order.
+constexpr int kRefPlanes = 64;
+constexpr int kRefBins = kRefPlanes + 1;                  // k in [1, 64]; entry 0 unused
+constexpr int kRefNodeBinWords = 3 * kRefBins * kBinWords;
+struct RefNode {
+    float mn[3], mx[3];
+    uint32_t start, n, left, level; // left: temporary id of the left child (right = left + 1), kNone for a leaf
+};
+struct RefInfo {
+    float lo[3], scale[3];
+    uint32_t active;
+};
+struct RefDecision {
+    uint32_t axis;
+    float pos;
+    uint32_t nl;
+    uint32_t partition; // the swap loop runs (cost <= no-split cost)
+    uint32_t split;     // both sides non-empty: two children
+    uint32_t child_slot[2];
+};
+__device__ __forceinline__ int ref_bin_of(float c, float lo, float scale) {
+    int a = 1, b = kRefPlanes;
+    while (a < b) {
+        const int mid = (a + b) >> 1;
+        if (c < lo + (float)mid * scale) b = mid; else a = mid + 1;
+    }
+    return a;
+}
+__global__ void ref_prepare(const uint32_t* __restrict__ acc, const uint32_t* __restrict__ active_ids, uint32_t count, RefNode* nodes,
+                            RefInfo* info) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= count) return;
+    const uint32_t* a = acc + (size_t)s * kAcc;
+    RefNode& nd = nodes[active_ids[s]];
+    RefInfo ri;
+    ri.active = 0;
+    for (int k = 0; k < 3; ++k) {
+        const float lo = o2f(a[k]), hi = o2f(a[3 + k]);
+        nd.mn[k] = lo;
+        nd.mx[k] = hi;
+        ri.lo[k] = lo;
+        ri.scale[k] = 0.0f;
+        if (!(lo == hi)) {
+            ri.active |= 1u << k;
+            ri.scale[k] = (hi - lo) / (float)kRefPlanes;
+        }
+    }
+    info[s] = ri;
+}
+__global__ void ref_init_bins(uint32_t* bins, uint32_t nodes) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)nodes * kRefNodeBinWords) return;
+    const uint32_t k = (uint32_t)(i % kBinWords);
+    bins[i] = k < 3 ? kOrdMinInit : (k < 6 ? kOrdMaxInit : 0u);
+}
+__global__ void __launch_bounds__(kBinThreads) ref_bin_prims(const float4* __restrict__ bmn, const float4* __restrict__ bmx,
+                                                           const float4* __restrict__ cen, const uint32_t* __restrict__ order,
+                                                           const uint32_t* __restrict__ node_of, uint32_t n,
+                                                           const RefInfo* __restrict__ info, uint32_t* bins) {
+    __shared__ uint32_t local[kRefNodeBinWords];
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t s = p < n ? node_of[p] : kNone;
+    const uint32_t s0 = node_of[blockIdx.x * blockDim.x];
+    const bool uniform = __syncthreads_and(s == s0 || p >= n) && s0 != kNone;
+    if (uniform) {
+        for (uint32_t i = threadIdx.x; i < (uint32_t)kRefNodeBinWords; i += kBinThreads) {
+            const uint32_t k = i % kBinWords;
+            local[i] = k < 3 ? kOrdMinInit : (k < 6 ? kOrdMaxInit : 0u);
+        }
+        __syncthreads();
+    }
+    if (s != kNone) {
+        const uint32_t id = order[p];
+        const float4 a = bmn[id], b = bmx[id], c4 = cen[id];
+        const float mn[3] = {a.x, a.y, a.z}, mx[3] = {b.x, b.y, b.z}, c[3] = {c4.x, c4.y, c4.z};
+        const RefInfo& ri = info[s];
+        const uint32_t active = ri.active;
+#pragma unroll
+        for (int ax = 0; ax < 3; ++ax) {
+            if (!(active >> ax & 1u)) continue;
+            const int k = ref_bin_of(c[ax], ri.lo[ax], ri.scale[ax]);
+            uint32_t* w = (uniform ? local : bins + (size_t)s * kRefNodeBinWords) + ((size_t)ax * kRefBins + k) * kBinWords;
+            atomic_box(w, mn, mx);
+            atomicAdd(w + 6, 1u);
+        }
+    }
+    if (!uniform) return;
+    __syncthreads();
+    uint32_t* g = bins + (size_t)s0 * kRefNodeBinWords;
+    for (uint32_t i = threadIdx.x; i < (uint32_t)kRefNodeBinWords; i += kBinThreads) {
+        const uint32_t bin = i / kBinWords, k = i % kBinWords;
+        if (local[bin * kBinWords + 6] == 0) continue;
+        if (k < 3) atomicMin(g + i, local[i]);
+        else if (k < 6) atomicMax(g + i, local[i]);
+        else atomicAdd(g + i, local[i]);
+    }
+}
+__device__ __forceinline__ float ref_area(const BoxF& b) { // aabb.rs:20-23
+    const float ex = b.mx[0] - b.mn[0], ey = b.mx[1] - b.mn[1], ez = b.mx[2] - b.mn[2];
+    return ex * ey + ey * ez + ez * ex;
+}
+__device__ __forceinline__ void ref_origin(BoxF& b) { // AABB::default(): both corners at the origin (blas.rs:66-67)
+    for (int k = 0; k < 3; ++k) b.mn[k] = b.mx[k] = 0.0f;
+}
+__device__ __forceinline__ void ref_merge_bin(BoxF& acc, const uint32_t* b) {
+    const float lo[3] = {o2f(b[0]), o2f(b[1]), o2f(b[2])}, hi[3] = {o2f(b[3]), o2f(b[4]), o2f(b[5])};
+    box_grow(acc, lo, hi);
+}
+// find_best_split_plane + the no-split test (blas.rs:93-127,270-276): thread (node, axis) sweeps its 63 planes
+__global__ void __launch_bounds__(96) ref_decide(const uint32_t* __restrict__ active_ids, uint32_t count, const RefNode* __restrict__ nodes,
+                                                 const RefInfo* __restrict__ info, const uint32_t* __restrict__ bins, RefDecision* dec,
+                                                 uint32_t* split_flags) {
+    __shared__ float s_cost[96];
+    __shared__ uint32_t s_plane[96], s_nl[96];
+    const uint32_t local = threadIdx.x / 3, ax = threadIdx.x % 3;
+    const uint32_t s = blockIdx.x * 32 + local;
+    float best_cost = kMaxF;
+    uint32_t best_plane = 0, best_nl = 0;
+    if (s < count && (info[s].active >> ax & 1u)) {
+        const uint32_t* w = bins + ((size_t)s * 3 + ax) * kRefBins * kBinWords;
+        float rarea[kRefPlanes];
+        uint32_t rcount[kRefPlanes];
+        BoxF acc;
+        ref_origin(acc);
+        uint32_t cnt = 0;
+        for (int i = kRefPlanes - 1; i >= 1; --i) { // right(i) = origin U bins k > i
+            const uint32_t* b = w + (i + 1) * kBinWords;
+            if (b[6]) ref_merge_bin(acc, b);
+            cnt += b[6];
+            rarea[i] = ref_area(acc);
+            rcount[i] = cnt;
+        }
+        ref_origin(acc);
+        cnt = 0;
+        for (int i = 1; i < kRefPlanes; ++i) {
+            const uint32_t* b = w + i * kBinWords;
+            if (b[6]) ref_merge_bin(acc, b);
+            cnt += b[6];
+            float cost = (float)(int)cnt * ref_area(acc) + (float)(int)rcount[i] * rarea[i]; // evaluate_sah (blas.rs:83-88)
+            if (!(cost > 0.0f)) cost = kMaxF;
+            if (cost < best_cost) { best_cost = cost; best_plane = (uint32_t)i; best_nl = cnt; }
+        }
+    }
+    s_cost[threadIdx.x] = best_cost;
+    s_plane[threadIdx.x] = best_plane;
+    s_nl[threadIdx.x] = best_nl;
+    __syncthreads();
+    if (ax != 0 || s >= count) return;
+    float cost = kMaxF;
+    int axis = 0;
+    uint32_t plane = 0, nl = 0;
+    bool any = false;
+    for (int a = 0; a < 3; ++a)
+        if (s_cost[local * 3 + a] < cost) { cost = s_cost[local * 3 + a]; axis = a; plane = s_plane[local * 3 + a]; nl = s_nl[local * 3 + a]; any = true; }
+    const RefNode& nd = nodes[active_ids[s]];
+    const RefInfo& ri = info[s];
+    BoxF nb;
+    for (int k = 0; k < 3; ++k) { nb.mn[k] = nd.mn[k]; nb.mx[k] = nd.mx[k]; }
+    const float no_split = (float)nd.n * ref_area(nb); // calculate_cost (blas.rs:125-127)
+    RefDecision d;
+    d.axis = (uint32_t)axis;
+    d.pos = any ? ri.lo[axis] + (float)plane * ri.scale[axis] : 0.0f;
+    d.partition = cost > no_split ? 0u : 1u;
+    // without a winning plane every centroid compares `< 0.0` (split_pos stays 0.0 on axis 0): count the lefts later
+    d.nl = any ? nl : kNone;
+    d.split = 0;
+    d.child_slot[0] = d.child_slot[1] = kNone;
+    dec[s] = d;
+    split_flags[s] = 0;
+}
+// left / right flag of every primitive of a partitioned node: centroid[axis] < pos (blas.rs:284)
+__global__ void ref_flags(const float4* __restrict__ cen, const uint32_t* __restrict__ order, const uint32_t* __restrict__ node_of,
+                          uint32_t n, const RefDecision* __restrict__ dec, uint32_t* flags) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const uint32_t s = node_of[p];
+    uint32_t f = 0;
+    if (s != kNone && dec[s].partition) {
+        const float4 c = cen[order[p]];
+        const uint32_t ax = dec[s].axis;
+        f = (ax == 0 ? c.x : (ax == 1 ? c.y : c.z)) < dec[s].pos;
+    }
+    flags[p] = f;
+}
+// after the scan: left counts, which nodes really split
+__global__ void ref_counts(const uint32_t* __restrict__ active_ids, uint32_t count, const RefNode* __restrict__ nodes,
+                           const uint32_t* __restrict__ scan, RefDecision* dec, uint32_t* split_flags) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= count) return;
+    const RefNode& nd = nodes[active_ids[s]];
+    RefDecision& d = dec[s];
+    if (!d.partition) { split_flags[s] = 0; return; }
+    d.nl = scan[nd.start + nd.n] - scan[nd.start];
+    d.split = d.nl > 0 && d.nl < nd.n;
+    split_flags[s] = d.split;
+}
+__global__ void ref_children(const uint32_t* __restrict__ active_ids, uint32_t count, RefNode* nodes, RefDecision* dec,
+                             const uint32_t* __restrict__ split_index, uint32_t next_id, uint32_t level, uint32_t* next_active) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= count) return;
+    RefDecision& d = dec[s];
+    RefNode& nd = nodes[active_ids[s]];
+    if (!d.split) return;
+    const uint32_t k = split_index[s];
+    const uint32_t left = next_id + 2 * k;
+    nd.left = left;
+    for (uint32_t c = 0; c < 2; ++c) {
+        RefNode ch;
+        for (int j = 0; j < 3; ++j) { ch.mn[j] = kMaxF; ch.mx[j] = -kMaxF; }
+        ch.start = c ? nd.start + d.nl : nd.start;
+        ch.n = c ? nd.n - d.nl : d.nl;
+        ch.left = kNone;
+        ch.level = level + 1;
+        nodes[left + c] = ch;
+        next_active[2 * k + c] = left + c;
+        d.child_slot[c] = 2 * k + c;
+    }
+}
+// the permutation of the swap loop, part 1: where the holes and the tail lefts are
+__global__ void ref_tables(const uint32_t* __restrict__ node_of, uint32_t n, const uint32_t* __restrict__ active_ids,
+                           const RefNode* __restrict__ nodes, const RefDecision* __restrict__ dec, const uint32_t* __restrict__ flags,
+                           const uint32_t* __restrict__ scan, uint32_t* hole_pos, uint32_t* tail_pos) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const uint32_t s = node_of[p];
+    if (s == kNone || !dec[s].partition) return;
+    const RefNode& nd = nodes[active_ids[s]];
+    const uint32_t nl = dec[s].nl, q = p - nd.start, lb = scan[p] - scan[nd.start];
+    if (flags[p]) {
+        if (q >= nl) tail_pos[nd.start + (nl - lb) - 1] = q; // k-th left above nL, counted from the end
+    } else if (q <= nl) {
+        hole_pos[nd.start + (q - lb)] = q; // k-th right at or below nL, k - 1 = rights before it
+    }
+}
+__global__ void ref_scatter(const uint32_t* __restrict__ order, const uint32_t* __restrict__ node_of, uint32_t n,
+                            const uint32_t* __restrict__ active_ids, const RefNode* __restrict__ nodes,
+                            const RefDecision* __restrict__ dec, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ scan,
+                            const uint32_t* __restrict__ hole_pos, const uint32_t* __restrict__ tail_pos, uint32_t* order_out,
+                            uint32_t* node_of_out) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const uint32_t s = node_of[p];
+    const uint32_t id = order[p];
+    if (s == kNone || !dec[s].partition) {
+        order_out[p] = id;
+        node_of_out[p] = kNone;
+        return;
+    }
+    const RefNode& nd = nodes[active_ids[s]];
+    const RefDecision& d = dec[s];
+    const uint32_t nl = d.nl, q = p - nd.start, lb = scan[p] - scan[nd.start];
+    uint32_t dst;
+    if (flags[p]) {
+        dst = q < nl ? q : hole_pos[nd.start + (nl - lb) - 1];
+    } else if (q <= nl) {
+        const uint32_t k = q - lb; // rights before this one
+        dst = (k == 0 ? nd.n : tail_pos[nd.start + k - 1]) - 1u;
+    } else {
+        dst = q - 1u;
+    }
+    order_out[nd.start + dst] = id;
+    node_of_out[nd.start + dst] = d.split ? d.child_slot[dst < nl ? 0 : 1] : kNone;
+}
+
 __global__ void small_sizes(const WorkNode* __restrict__ small, uint32_t count, uint32_t* sizes) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) sizes[i] = small[i].n - 1u; // pairs a subtree over n primitives can need
@@ -819,6 +1095,161 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
     out.tri = d_tri;
     buf.release(d_records);
     buf.release(d_tri);
+    return RAYCA_OK;
+}
+
+
+int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::string& err, float* device_ms) {
+    const uint32_t N = (uint32_t)blas.tris.size();
+    if (N == 0) { err = "no primitives"; return RAYCA_E_INVALID_ARG; }
+    std::vector<float4> hmn(N), hmx(N), hcen(N);
+#pragma omp parallel for schedule(static) if (N > 8192)
+    for (int64_t i = 0; i < (int64_t)N; ++i) {
+        const HostTri& t = blas.tris[(size_t)i];
+        hmn[(size_t)i] = make_float4(t.bmin.x, t.bmin.y, t.bmin.z, 0.0f);
+        hmx[(size_t)i] = make_float4(t.bmax.x, t.bmax.y, t.bmax.z, 0.0f);
+        hcen[(size_t)i] = make_float4(t.centroid.x, t.centroid.y, t.centroid.z, 0.0f);
+    }
+    DeviceBuffers buf;
+    const uint32_t cap = std::min<uint32_t>(N, 16384u); // nodes of one level; broader levels fall back to the host builder
+    float4 *d_mn, *d_mx, *d_cen;
+    uint32_t *d_order[2], *d_node_of[2], *d_flags, *d_scan, *d_partial, *d_hole, *d_tail, *d_acc[2], *d_bins, *d_split, *d_split_index,
+        *d_active[2];
+    RefNode* d_nodes;
+    RefInfo* d_info;
+    RefDecision* d_dec;
+    const size_t node_cap = (size_t)N * 2 + 2;
+    FB_TRY(buf.alloc(&d_mn, N));
+    FB_TRY(buf.alloc(&d_mx, N));
+    FB_TRY(buf.alloc(&d_cen, N));
+    for (int k = 0; k < 2; ++k) {
+        FB_TRY(buf.alloc(&d_order[k], N));
+        FB_TRY(buf.alloc(&d_node_of[k], N));
+        FB_TRY(buf.alloc(&d_acc[k], (size_t)cap * 2 * kAcc));
+        FB_TRY(buf.alloc(&d_active[k], (size_t)cap * 2));
+    }
+    FB_TRY(buf.alloc(&d_flags, N));
+    FB_TRY(buf.alloc(&d_scan, (size_t)N + 1));
+    FB_TRY(buf.alloc(&d_partial, (size_t)N / kScanBlock + 4));
+    FB_TRY(buf.alloc(&d_hole, N));
+    FB_TRY(buf.alloc(&d_tail, N));
+    FB_TRY(buf.alloc(&d_bins, (size_t)cap * kRefNodeBinWords));
+    FB_TRY(buf.alloc(&d_split, cap));
+    FB_TRY(buf.alloc(&d_split_index, (size_t)cap + 1));
+    FB_TRY(buf.alloc(&d_nodes, node_cap));
+    FB_TRY(buf.alloc(&d_info, cap));
+    FB_TRY(buf.alloc(&d_dec, cap));
+    FB_TRY(buf.commit());
+
+    cudaEvent_t e0, e1;
+    FB_TRY(cudaEventCreate(&e0));
+    FB_TRY(cudaEventCreate(&e1));
+    std::vector<uint32_t> order(N);
+    for (uint32_t i = 0; i < N; ++i) order[i] = i;
+    FB_TRY(cudaMemcpyAsync(d_mn, hmn.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
+    FB_TRY(cudaMemcpyAsync(d_mx, hmx.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
+    FB_TRY(cudaMemcpyAsync(d_cen, hcen.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
+    FB_TRY(cudaMemcpyAsync(d_order[0], order.data(), (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    FB_TRY(cudaEventRecord(e0, st));
+    RefNode init[2];
+    std::memset(init, 0, sizeof(init));
+    init[0].start = 0;
+    init[0].n = N;
+    init[0].left = kNone;
+    init[0].level = 0;
+    init[1].left = kNone;
+    FB_TRY(cudaMemcpyAsync(d_nodes, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    const uint32_t zero = 0;
+    FB_TRY(cudaMemcpyAsync(d_active[0], &zero, 4, cudaMemcpyHostToDevice, st));
+    FB_TRY(cudaMemsetAsync(d_node_of[0], 0, (size_t)N * 4, st));
+    const uint32_t T = 256;
+    init_acc<<<1, 32, 0, st>>>(d_acc[0], 1);
+    accumulate_boxes<<<blocks_for(N, T), T, 0, st>>>(d_mn, d_mx, d_order[0], d_node_of[0], N, d_acc[0]);
+    uint32_t count = 1, next_id = 2, level = 0;
+    int cur = 0;
+    for (;;) {
+        ref_prepare<<<blocks_for(count, T), T, 0, st>>>(d_acc[cur], d_active[cur], count, d_nodes, d_info);
+        if (level >= max_depth) break;
+        const int nxt = cur ^ 1;
+        ref_init_bins<<<blocks_for((size_t)count * kRefNodeBinWords, T), T, 0, st>>>(d_bins, count);
+        ref_bin_prims<<<blocks_for(N, kBinThreads), kBinThreads, 0, st>>>(d_mn, d_mx, d_cen, d_order[cur], d_node_of[cur], N, d_info, d_bins);
+        ref_decide<<<blocks_for(count, 32), 96, 0, st>>>(d_active[cur], count, d_nodes, d_info, d_bins, d_dec, d_split);
+        ref_flags<<<blocks_for(N, T), T, 0, st>>>(d_cen, d_order[cur], d_node_of[cur], N, d_dec, d_flags);
+        exclusive_scan(d_flags, N, d_scan, d_partial, st);
+        ref_counts<<<blocks_for(count, T), T, 0, st>>>(d_active[cur], count, d_nodes, d_scan, d_dec, d_split);
+        exclusive_scan(d_split, count, d_split_index, d_partial, st);
+        uint32_t splits = 0;
+        FB_TRY(cudaMemcpyAsync(&splits, d_split_index + count, 4, cudaMemcpyDeviceToHost, st));
+        FB_TRY(cudaStreamSynchronize(st));
+        if (splits * 2 > cap || (size_t)next_id + 2 * (size_t)splits > node_cap) {
+            err = "device BLAS build: level too broad";
+            return RAYCA_E_UNSUPPORTED;
+        }
+        ref_children<<<blocks_for(count, T), T, 0, st>>>(d_active[cur], count, d_nodes, d_dec, d_split_index, next_id, level, d_active[nxt]);
+        ref_tables<<<blocks_for(N, T), T, 0, st>>>(d_node_of[cur], N, d_active[cur], d_nodes, d_dec, d_flags, d_scan, d_hole, d_tail);
+        ref_scatter<<<blocks_for(N, T), T, 0, st>>>(d_order[cur], d_node_of[cur], N, d_active[cur], d_nodes, d_dec, d_flags, d_scan, d_hole,
+                                                    d_tail, d_order[nxt], d_node_of[nxt]);
+        cur = nxt; // the partition may have reordered ranges even when nothing split
+        if (splits == 0) break;
+        init_acc<<<blocks_for((size_t)splits * 2 * kAcc, T), T, 0, st>>>(d_acc[cur], splits * 2);
+        accumulate_boxes<<<blocks_for(N, T), T, 0, st>>>(d_mn, d_mx, d_order[cur], d_node_of[cur], N, d_acc[cur]);
+        next_id += 2 * splits;
+        count = 2 * splits;
+        ++level;
+    }
+    FB_TRY(cudaEventRecord(e1, st));
+    std::vector<RefNode> tmp(next_id);
+    FB_TRY(cudaMemcpyAsync(tmp.data(), d_nodes, (size_t)next_id * sizeof(RefNode), cudaMemcpyDeviceToHost, st));
+    FB_TRY(cudaMemcpyAsync(order.data(), d_order[cur], (size_t)N * 4, cudaMemcpyDeviceToHost, st));
+    FB_TRY(cudaStreamSynchronize(st));
+    FB_TRY(cudaGetLastError());
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (device_ms) *device_ms = ms;
+
+    // renumber in the reference's push order (blas.rs:296-311): a node's children are appended when the node is
+    // processed, then the left subtree is processed completely before the right one
+    blas.nodes.clear();
+    blas.nodes.reserve(next_id);
+    auto to_host = [](const RefNode& r) {
+        HostNode h;
+        h.bmin = V3{r.mn[0], r.mn[1], r.mn[2]};
+        h.bmax = V3{r.mx[0], r.mx[1], r.mx[2]};
+        h.offset = r.start;
+        h.count = r.n;
+        return h;
+    };
+    blas.nodes.push_back(to_host(tmp[0]));
+    HostNode dummy{};
+    dummy.bmin = dummy.bmax = V3{0, 0, 0};
+    dummy.offset = dummy.count = 0;
+    blas.nodes.push_back(dummy);
+    uint32_t deepest = 0;
+    struct Todo { uint32_t tmp_id, out_index; };
+    std::vector<Todo> stack{{0u, 0u}};
+    while (!stack.empty()) {
+        const Todo t = stack.back();
+        stack.pop_back();
+        const RefNode& r = tmp[t.tmp_id];
+        deepest = std::max(deepest, r.level);
+        HostNode h = to_host(r);
+        if (r.left != kNone) {
+            const uint32_t li = (uint32_t)blas.nodes.size();
+            blas.nodes.resize(blas.nodes.size() + 2);
+            h.offset = li;
+            h.count = 0;
+            stack.push_back({r.left + 1, li + 1}); // popped after the whole left subtree
+            stack.push_back({r.left, li});
+        }
+        blas.nodes[t.out_index] = h;
+    }
+    blas.depth = deepest;
+    std::vector<HostTri> sorted(N);
+#pragma omp parallel for schedule(static) if (N > 8192)
+    for (int64_t i = 0; i < (int64_t)N; ++i) sorted[(size_t)i] = blas.tris[order[(size_t)i]];
+    blas.tris.swap(sorted);
     return RAYCA_OK;
 }
 

@@ -20,6 +20,10 @@ struct FastTreeDevice {
 // blas_node_offset} final) and the device copy of HostScene::tri_pos.  Returns RAYCA_OK or an error code.
 int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStream_t stream, FastTreeDevice& out, std::string& err);
 
+// Reference BLAS (bvh_build.cpp's build_blas) on the device: same nodes, same primitive order.  RAYCA_E_UNSUPPORTED
+// asks the caller to use the host builder (a level broader than the device work lists).
+int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t stream, std::string& err, float* device_ms);
+
 // tunables shared with the host builder (fast_bvh.cpp)
 void fast_tree_tunables(int& bins, uint32_t& leaf_max, float& traversal_cost);
 

@@ -224,7 +224,8 @@ struct PhaseTimer { // RAYCA_TIMING=1 prints the host phases of scene_create to 
 };
 } // namespace
 
-int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::string& err, bool fast_tree) {
+int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::string& err, bool fast_tree,
+                     const BlasBuilder* blas_builder) {
     PhaseTimer phase;
     Flatten f(d, out);
     f.run();
@@ -413,8 +414,13 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
             }
         }
         phase.lap("emit triangles");
-        build_blas(blas, bvh ? 255u : 0u); // scene.rs:95-99: !config.bvh => max_depth(0)
-        phase.lap("reference BLAS build");
+        const uint32_t max_depth = bvh ? 255u : 0u; // scene.rs:95-99: !config.bvh => max_depth(0)
+        if (blas_builder && (*blas_builder)(blas, max_depth)) {
+            phase.lap("reference BLAS build (device)");
+        } else {
+            build_blas(blas, max_depth);
+            phase.lap("reference BLAS build (host)");
+        }
         out.blas.push_back(std::move(blas));
     }
     if (out.blas.empty()) { // Tlas::new would assert on an empty range (tlas.rs:75)

@@ -3,6 +3,7 @@
 // BLAS/TLAS construction, and packing into the HBM layout of gpu_types.h.
 #pragma once
 #include <cstdint>
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -80,7 +81,11 @@ struct HostScene {
 
 // Returns RAYCA_OK or a negative RAYCA_E_* code; `err` receives a detail string.
 // `fast_tree` = false leaves the performance tree to the device builder (gpu_fast_build.cu).
-int build_host_scene(const rayca_scene_desc& desc, bool bvh, HostScene& out, std::string& err, bool fast_tree = true);
+// `blas_builder`, when given, replaces build_blas (the device builder of gpu_fast_build.cu): it returns true when
+// it built the BLAS and false to leave it to the host builder.
+using BlasBuilder = std::function<bool(HostBlas&, uint32_t max_depth)>;
+int build_host_scene(const rayca_scene_desc& desc, bool bvh, HostScene& out, std::string& err, bool fast_tree = true,
+                     const BlasBuilder* blas_builder = nullptr);
 
 // BLAS build: top-down SAH over 63 planes x 3 axes with the reference's tie-breaking
 // (bvh/blas.rs:64-127,245-316), evaluated through per-plane bins so that one pass over the

@@ -250,8 +250,20 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     // the performance tree is built on the device; RAYCA_HOST_FAST_TREE=1 (or a non-default bin count) keeps the
     // host builder for A/B runs
     const bool host_fast_tree = std::getenv("RAYCA_HOST_FAST_TREE") != nullptr || std::getenv("RAYCA_FAST_BINS") != nullptr;
+    // so is the reference BLAS of every model with enough primitives to pay for the launches (RAYCA_HOST_REF_TREE=1:
+    // host builder everywhere)
+    const bool host_ref_tree = std::getenv("RAYCA_HOST_REF_TREE") != nullptr;
+    const BlasBuilder device_blas = [&](HostBlas& blas, uint32_t max_depth) -> bool {
+        if (host_ref_tree || blas.tris.size() < 16384) return false;
+        std::string build_err;
+        float ms = 0.0f;
+        const int brc = build_blas_device(blas, max_depth, ctx->render_stream, build_err, &ms);
+        if (brc == RAYCA_OK && std::getenv("RAYCA_TIMING")) std::fprintf(stderr, "[rayca] %-28s %8.2f ms\n", "  BLAS kernels", ms);
+        if (brc != RAYCA_OK) cudaGetLastError();
+        return brc == RAYCA_OK;
+    };
     try {
-        rc = build_host_scene(*desc, bvh != 0, s->host, err, host_fast_tree);
+        rc = build_host_scene(*desc, bvh != 0, s->host, err, host_fast_tree, &device_blas);
     } catch (const std::bad_alloc&) {
         delete s;
         return fail(RAYCA_E_OOM, "host allocation while building the scene");

@@ -377,3 +377,39 @@ def test_device_built_tree_on_the_bench_scene(ctx, atrium):
     assert np.array_equal(a8, b8) and np.array_equal(a8, c8)
     host.close()
     again.close()
+
+
+def _host_ref_scene(ctx, desc):
+    import os
+
+    os.environ["RAYCA_HOST_REF_TREE"] = "1"
+    try:
+        return R.DeviceScene(ctx, desc)
+    finally:
+        del os.environ["RAYCA_HOST_REF_TREE"]
+
+
+def _big_scene_descs():
+    from rayca_b200 import procedural as P
+
+    yield "atrium", P.atrium(262_267).to_desc()
+    yield "soup", P.soup(200_000).to_desc()
+    for name in ("dragon", "scene7"):
+        yield name, load_desc(name)
+
+
+def test_device_built_reference_blas_equals_host_built(ctx):
+    """The reference BLAS (blas.rs:64-127,245-316) of models with >= 16384 primitives is built on the GPU: node
+    boxes, child links, leaf ranges and the primitive order left by the reference's swap partition must equal the
+    host builder's (which the CPU tests pin against the oracle) bit for bit."""
+    for name, desc in _big_scene_descs():
+        a = R.DeviceScene(ctx, desc)
+        b = _host_ref_scene(ctx, desc)
+        ia, na, noa, poa, sa = a.bvh()
+        ib, nb, nob, pob, sb = b.bvh()
+        assert (ia.blas_count, ia.node_count, ia.triangle_count, ia.tlas_node_count) == \
+            (ib.blas_count, ib.node_count, ib.triangle_count, ib.tlas_node_count), name
+        assert np.array_equal(na.view(np.uint32), nb.view(np.uint32)), name
+        assert np.array_equal(noa, nob) and np.array_equal(poa, pob) and np.array_equal(sa, sb), name
+        a.close()
+        b.close()
