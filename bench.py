@@ -372,9 +372,14 @@ def run_ours(args):
         img = R.Image(W, H)
         rnd = R.CudaRenderer.__new__(R.CudaRenderer)
         rnd.config, rnd._ctx = cfg, ctx
-        t1 = time.perf_counter()
-        rnd.draw(scene, img)
-        draw_e2e = {"ms": (time.perf_counter() - t1) * 1e3, "what": "Draw::draw: to_desc + flatten + BVH build + upload + render + read-back"}
+        draws = []
+        for _ in range(4):  # the first call pays one-time allocations; report the median of the next three
+            t1 = time.perf_counter()
+            rnd.draw(scene, img)
+            draws.append((time.perf_counter() - t1) * 1e3)
+        draw_e2e = {"ms": sorted(draws[1:])[1], "first_ms": draws[0],
+                    "what": "Draw::draw, median of 3 after one warm-up call: to_desc + flatten + reference BLAS and performance tree "
+                            "(both built on the GPU) + upload + render + read-back"}
 
     if rank == 0:
         peaks = {}

@@ -1246,7 +1246,7 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
         blas.nodes[t.out_index] = h;
     }
     blas.depth = deepest;
-    std::vector<HostTri> sorted(N);
+    PodVector<HostTri> sorted(N);
 #pragma omp parallel for schedule(static) if (N > 8192)
     for (int64_t i = 0; i < (int64_t)N; ++i) sorted[(size_t)i] = blas.tris[order[(size_t)i]];
     blas.tris.swap(sorted);

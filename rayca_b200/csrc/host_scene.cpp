@@ -304,6 +304,23 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
         const rayca_model& m = d.models[mi];
         HostBlas blas;
         blas.model = mi;
+        // Emit order is the reference's (primitive.rs:349-367): nodes in draw order, primitives in mesh order.  Pass 1
+        // validates, places every primitive (a sphere takes one slot, a mesh its triangle count) and fills the
+        // spheres; pass 2 fills the triangles, all meshes of the model in ONE parallel loop over 4096-triangle
+        // chunks (a model made of many small meshes would otherwise be emitted by a single thread).
+        struct MeshJob {
+            const MeshDraw* md;
+            const rayca_geometry* g;
+            uint32_t material;
+            size_t base;
+            M3 tangent_matrix, normal_matrix;
+        };
+        struct Chunk { uint32_t job, first, count; };
+        std::vector<MeshJob> jobs;
+        std::vector<Chunk> chunks;
+        struct SphereSlot { size_t slot; uint32_t sphere; uint32_t material; float radius; };
+        std::vector<SphereSlot> sphere_slots;
+        size_t total_prims = 0;
         for (const MeshDraw& md : f.mesh_draws[mi]) {
             const rayca_node& n = d.nodes[m.node_offset + md.node_local];
             if ((uint32_t)n.mesh >= m.mesh_count) { err = "bad mesh index"; return RAYCA_E_INVALID_ARG; }
@@ -325,60 +342,76 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
                     sp.world = md.world;
                     sp.material = material;
                     blas.spheres.push_back(sp);
-                    HostTri ht{};
-                    // Sphere::{get_center,get_radius,min,max} (sphere.rs:72-93,169-181); reduce_max runs over 4 lanes, w = 0
-                    V3 c = trs_point(md.world, sp.center);
-                    float r = g.radius * fmaxf(fmaxf(fmaxf(md.world.s.x, md.world.s.y), md.world.s.z), 0.0f);
-                    ht.centroid = c;
-                    ht.bmin = c - V3{r, r, r};
-                    ht.bmax = c + V3{r, r, r};
-                    ht.src = (uint32_t)blas.tris.size();
-                    ht.sphere = (uint32_t)blas.spheres.size();
-                    blas.tris.push_back(ht);
-                    blas.attrs.push_back(HostAttr{});
-                    blas.attrs.back().material = material;
+                    sphere_slots.push_back({total_prims, (uint32_t)blas.spheres.size(), material, g.radius});
+                    total_prims += 1;
                     out.has_spheres = true;
                     continue;
                 }
                 if (g.kind != RAYCA_GEOMETRY_TRIANGLE_MESH) { err = "unknown geometry kind"; return RAYCA_E_INVALID_ARG; }
-                uint32_t ntri = g.index_count / 3;
-                size_t base = blas.tris.size();
-                blas.tris.resize(base + ntri);
-                blas.attrs.resize(base + ntri);
-                int bad = 0;
-#pragma omp parallel for schedule(static) if (ntri > 8192)
-                for (int64_t t = 0; t < (int64_t)ntri; ++t) {
-                    HostTri& ht = blas.tris[base + (size_t)t];
-                    HostAttr& ha = blas.attrs[base + (size_t)t];
-                    V3 mv[3];
-                    for (int k = 0; k < 3; ++k) {
-                        uint32_t vi = d.indices[g.first_index + (size_t)t * 3 + k];
-                        if (vi >= g.vertex_count) { bad = 1; vi = 0; }
-                        const rayca_vertex& v = d.vertices[g.first_vertex + vi];
-                        mv[k] = V3{v.pos[0], v.pos[1], v.pos[2]};
-                        std::memcpy(ha.color[k], v.color, 16);
-                        ha.normal[k] = m3_apply(normal_matrix, V3{v.normal[0], v.normal[1], v.normal[2]});
-                        ha.tangent[k] = m3_apply(tangent_matrix, V3{v.tangent[0], v.tangent[1], v.tangent[2]});
-                        ha.bitangent[k] = m3_apply(tangent_matrix, V3{v.bitangent[0], v.bitangent[1], v.bitangent[2]});
-                        ha.uv[k][0] = v.uv[0];
-                        ha.uv[k][1] = v.uv[1];
-                        ht.v[k] = trs_point(md.world, mv[k]); // Triangle::get_vertex (triangle.rs:67-69)
-                    }
-                    ha.material = material;
-                    // Triangle::new centroid quirk (triangle.rs:59-62) then `trs * Vec3` (trs.rs:253-262)
-                    V3 c = ((mv[0] + mv[1]) + mv[2]) * 0.3333f;
-                    ht.centroid = trs_vec(md.world, c);
-                    ht.bmin = V3{fminf(fminf(fminf(kF32Max, ht.v[0].x), ht.v[1].x), ht.v[2].x),
-                                 fminf(fminf(fminf(kF32Max, ht.v[0].y), ht.v[1].y), ht.v[2].y),
-                                 fminf(fminf(fminf(kF32Max, ht.v[0].z), ht.v[1].z), ht.v[2].z)};
-                    ht.bmax = V3{fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].x), ht.v[1].x), ht.v[2].x),
-                                 fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].y), ht.v[1].y), ht.v[2].y),
-                                 fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].z), ht.v[1].z), ht.v[2].z)};
-                    ht.src = (uint32_t)(base + (size_t)t);
-                }
-                if (bad) { err = "vertex index out of range"; return RAYCA_E_INVALID_ARG; }
+                const uint32_t ntri = g.index_count / 3;
+                const uint32_t job = (uint32_t)jobs.size();
+                jobs.push_back({&md, &g, material, total_prims, tangent_matrix, normal_matrix});
+                for (uint32_t first = 0; first < ntri; first += 4096) chunks.push_back({job, first, std::min(4096u, ntri - first)});
+                total_prims += ntri;
             }
         }
+        blas.tris.resize(total_prims);
+        blas.attrs.resize(total_prims);
+        for (const SphereSlot& ss : sphere_slots) {
+            const HostSphere& sp = blas.spheres[ss.sphere - 1];
+            HostTri ht{};
+            // Sphere::{get_center,get_radius,min,max} (sphere.rs:72-93,169-181); reduce_max runs over 4 lanes, w = 0
+            V3 c = trs_point(sp.world, sp.center);
+            float r = ss.radius * fmaxf(fmaxf(fmaxf(sp.world.s.x, sp.world.s.y), sp.world.s.z), 0.0f);
+            ht.centroid = c;
+            ht.bmin = c - V3{r, r, r};
+            ht.bmax = c + V3{r, r, r};
+            ht.src = (uint32_t)ss.slot;
+            ht.sphere = ss.sphere;
+            blas.tris[ss.slot] = ht;
+            HostAttr ha{};
+            ha.material = ss.material;
+            blas.attrs[ss.slot] = ha;
+        }
+        int bad = 0;
+#pragma omp parallel for schedule(dynamic, 1) if (total_prims > 8192)
+        for (int64_t ci = 0; ci < (int64_t)chunks.size(); ++ci) {
+            const Chunk ch = chunks[(size_t)ci];
+            const MeshJob& job = jobs[ch.job];
+            const rayca_geometry& g = *job.g;
+            const MeshDraw& md = *job.md;
+            for (uint32_t t = ch.first; t < ch.first + ch.count; ++t) {
+                HostTri& ht = blas.tris[job.base + t];
+                HostAttr& ha = blas.attrs[job.base + t];
+                V3 mv[3];
+                for (int k = 0; k < 3; ++k) {
+                    uint32_t vi = d.indices[g.first_index + (size_t)t * 3 + k];
+                    if (vi >= g.vertex_count) { bad = 1; vi = 0; }
+                    const rayca_vertex& v = d.vertices[g.first_vertex + vi];
+                    mv[k] = V3{v.pos[0], v.pos[1], v.pos[2]};
+                    std::memcpy(ha.color[k], v.color, 16);
+                    ha.normal[k] = m3_apply(job.normal_matrix, V3{v.normal[0], v.normal[1], v.normal[2]});
+                    ha.tangent[k] = m3_apply(job.tangent_matrix, V3{v.tangent[0], v.tangent[1], v.tangent[2]});
+                    ha.bitangent[k] = m3_apply(job.tangent_matrix, V3{v.bitangent[0], v.bitangent[1], v.bitangent[2]});
+                    ha.uv[k][0] = v.uv[0];
+                    ha.uv[k][1] = v.uv[1];
+                    ht.v[k] = trs_point(md.world, mv[k]); // Triangle::get_vertex (triangle.rs:67-69)
+                }
+                ha.material = job.material;
+                // Triangle::new centroid quirk (triangle.rs:59-62) then `trs * Vec3` (trs.rs:253-262)
+                V3 c = ((mv[0] + mv[1]) + mv[2]) * 0.3333f;
+                ht.centroid = trs_vec(md.world, c);
+                ht.bmin = V3{fminf(fminf(fminf(kF32Max, ht.v[0].x), ht.v[1].x), ht.v[2].x),
+                             fminf(fminf(fminf(kF32Max, ht.v[0].y), ht.v[1].y), ht.v[2].y),
+                             fminf(fminf(fminf(kF32Max, ht.v[0].z), ht.v[1].z), ht.v[2].z)};
+                ht.bmax = V3{fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].x), ht.v[1].x), ht.v[2].x),
+                             fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].y), ht.v[1].y), ht.v[2].y),
+                             fmaxf(fmaxf(fmaxf(-kF32Max, ht.v[0].z), ht.v[1].z), ht.v[2].z)};
+                ht.src = (uint32_t)(job.base + t);
+                ht.sphere = 0;
+            }
+        }
+        if (bad) { err = "vertex index out of range"; return RAYCA_E_INVALID_ARG; }
         // BvhPrimitive::from_quad_light (primitive.rs:310-346), after the meshes (primitive.rs:363-367): triangles
         // [a, d, b] and [a, c, d], a = origin of the light node; vertex normal = quad normal (not transformed),
         // colour WHITE, uv / tangents zero; material = the light's emissive Phong material

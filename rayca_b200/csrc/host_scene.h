@@ -4,6 +4,9 @@
 #pragma once
 #include <cstdint>
 #include <functional>
+#include <memory>
+#include <type_traits>
+#include <utility>
 #include <string>
 #include <vector>
 
@@ -15,6 +18,18 @@
 
 namespace rb {
 
+// std::vector whose resize() leaves trivially-constructible elements uninitialised: the big per-triangle arrays
+// (tens of MB) are written once by a parallel loop right after being sized, and value-initialising them first
+// costs a sequential pass of page faults (30 of the 42 ms "emit triangles" took for 262k triangles).
+template <class T>
+struct DefaultInitAllocator : std::allocator<T> {
+    template <class U> struct rebind { using other = DefaultInitAllocator<U>; };
+    using std::allocator<T>::allocator;
+    template <class U> void construct(U* p) noexcept(std::is_nothrow_default_constructible<U>::value) { ::new ((void*)p) U; }
+    template <class U, class... A> void construct(U* p, A&&... a) { ::new ((void*)p) U(std::forward<A>(a)...); }
+};
+template <class T> using PodVector = std::vector<T, DefaultInitAllocator<T>>;
+
 // One triangle as emitted by BvhPrimitive::from_triangle_mesh_impl (bvh/primitive.rs:194-237),
 // already moved to world space with the reference's `trs * vertex` operation order.
 struct HostTri {
@@ -22,7 +37,7 @@ struct HostTri {
     V3 centroid;   // world-space `trs * ((a+b+c)*0.3333)` used by the SAH partition
     V3 bmin, bmax; // world-space bounds of the three vertices
     uint32_t src;  // emit order inside its model (stable id)
-    uint32_t sphere = 0; // 0: triangle; k > 0: HostBlas::spheres[k - 1] (v[] unused, bounds / centroid are the sphere's)
+    uint32_t sphere; // 0: triangle; k > 0: HostBlas::spheres[k - 1] (v[] unused, bounds / centroid are the sphere's)
 };
 
 // BvhGeometry::Sphere (bvh/primitive.rs:10-13,270-282): the sphere stays in MODEL space, the node's
@@ -47,8 +62,8 @@ struct HostNode {
 };
 
 struct HostBlas {
-    std::vector<HostTri> tris;   // reordered in place by the build
-    std::vector<HostAttr> attrs; // indexed by HostTri::src
+    PodVector<HostTri> tris;     // reordered in place by the build
+    PodVector<HostAttr> attrs;   // indexed by HostTri::src
     std::vector<HostSphere> spheres;
     std::vector<HostNode> nodes; // node 0 root, node 1 unused (blas.rs:250-256)
     uint32_t model = 0;
@@ -67,8 +82,8 @@ struct HostScene {
 
     // packed output
     std::vector<GpuNode> nodes;          // all BLAS nodes (offset-adjusted) followed by TLAS top pairs
-    std::vector<float4> tri_pos;
-    std::vector<float4> tri_attr;
+    PodVector<float4> tri_pos;
+    PodVector<float4> tri_attr;
     std::vector<uint32_t> blas_prim_offset, blas_node_offset;
     GpuNode root{};
     uint32_t max_stack = 0;              // deepest push chain the ordered walk can need

@@ -72,8 +72,9 @@ struct rayca_scene {
 
 namespace {
 
-template <typename T>
-int upload(void** dst, const std::vector<T>& src) {
+template <typename V>
+int upload(void** dst, const V& src) {
+    using T = typename V::value_type;
     size_t bytes = std::max<size_t>(src.size() * sizeof(T), 16);
     CUDA_TRY(cudaMalloc(dst, bytes));
     if (!src.empty()) CUDA_TRY(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
@@ -348,11 +349,11 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     s->max_stack = h.max_stack;
     // host copies that are no longer needed
     std::vector<unsigned char>().swap(h.texels);
-    std::vector<float4>().swap(h.tri_attr);
-    std::vector<float4>().swap(h.tri_pos);
+    PodVector<float4>().swap(h.tri_attr);
+    PodVector<float4>().swap(h.tri_pos);
     std::vector<float4>().swap(h.fast_tri);
     std::vector<GpuNode>().swap(h.fast_nodes);
-    for (HostBlas& b : h.blas) std::vector<HostAttr>().swap(b.attrs);
+    for (HostBlas& b : h.blas) PodVector<HostAttr>().swap(b.attrs);
     double t2 = now_ms();
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
