@@ -1305,6 +1305,80 @@ struct Renderer {
         return true;
     }
 
+    // integrator/scratcher.rs:16-89: transmission through transparent surfaces (Color::over), direct light with the
+    // raytracer's shadow rule, reflection weighted by the material's radiance function
+    bool scratcher_trace(const Ray& ray, uint32_t depth, Color& out, Hit* primary = nullptr) {
+        if (depth > cfg.c.max_depth) return false;
+        Hit h;
+        if (!tracer.intersects(ray, h)) return false;
+        if (primary) *primary = h;
+        HitInfo hit(s, h);
+        Color pixel_color = BLACK;
+        if (is_transparent(hit.get_color())) {
+            // hit.rs:178-187: origin pushed BELOW the surface, same direction
+            Point3 transmit_origin = hit.hit.point + (-hit.get_normal()) * RAY_BIAS;
+            Ray transmit_ray = make_ray(transmit_origin, ray.dir);
+            if (depth + 1 <= cfg.c.max_depth) tracer.rays->rays_secondary++;
+            Color transmit_color;
+            if (scratcher_trace(transmit_ray, depth + 1, transmit_color)) {
+                Color top = hit.get_color(); // Color::over (color/mod.rs:149-154)
+                transmit_color.r = top.r * top.a + transmit_color.r * (1.0f - top.a);
+                transmit_color.g = top.g * top.a + transmit_color.g * (1.0f - top.a);
+                transmit_color.b = top.b * top.a + transmit_color.b * (1.0f - top.a);
+                transmit_color.a = 1.0f;
+                pixel_color = pixel_color + transmit_color;
+            }
+        }
+        for (const LightDraw& ld : s.light_draws) {
+            const rayca_light& light = s.lights[ld.light];
+            Vec3 light_dir;
+            if (light.kind == RAYCA_LIGHT_POINT) { // light/point.rs:50-54
+                Vec3 dist = normalized(to_vec3(hit.hit.point) - trs_get_translation(ld.node_trs));
+                light_dir = -dist;
+            } else if (light.kind == RAYCA_LIGHT_DIRECTIONAL) { // light/directional.rs:47-51
+                light_dir = -rotate(Vec3{1.0f, 0.0f, 0.0f}, ld.node_trs.rotation);
+            } else {
+                status = RAYCA_E_UNSUPPORTED; // Light::get_direction todo!() for quad
+                continue;
+            }
+            Ray shadow = make_ray(hit.get_next_ray_origin(), light_dir);
+            tracer.rays->rays_shadow++;
+            Hit sh;
+            bool is_light;
+            if (!tracer.intersects(shadow, sh)) {
+                is_light = true;
+            } else {
+                float light_distance;
+                if (light.kind == RAYCA_LIGHT_POINT)
+                    light_distance = len(to_vec3(hit.hit.point - trs_get_translation(ld.node_trs)));
+                else
+                    light_distance = len(to_vec3(hit.hit.point) - trs_get_translation(ld.node_trs));
+                if (sh.depth > light_distance) {
+                    is_light = true;
+                } else {
+                    HitInfo shi(s, sh);
+                    is_light = is_transparent(shi.get_color());
+                }
+            }
+            if (is_light) {
+                Color intensity = (light.kind == RAYCA_LIGHT_POINT) ? point_intensity(light, ld.node_trs, hit.hit.point)
+                                                                    : light.intensity * to_color(light.color);
+                Irradiance ir = make_irradiance(intensity, hit, light_dir);
+                pixel_color = pixel_color + get_radiance(hit, ir);
+            }
+        }
+        Vec3 reflection = hit.get_reflection();
+        Ray reflection_ray = make_ray(hit.get_next_ray_origin(), reflection);
+        if (depth + 1 <= cfg.c.max_depth) tracer.rays->rays_secondary++;
+        Color reflection_intensity;
+        if (scratcher_trace(reflection_ray, depth + 1, reflection_intensity)) {
+            Irradiance ir = make_irradiance(reflection_intensity, hit, reflection);
+            pixel_color = pixel_color + get_radiance(hit, ir);
+        }
+        out = pixel_color;
+        return true;
+    }
+
     // ---- QuadLight (rayca-model/src/light/quad.rs); `trs` is the light node's LOCAL trs
     static Point3 quad_corner(const rayca_light& l, const Trs& trs, int k) { // get_a (quad.rs:48-57)
         Point3 a = to_point3(trs_get_translation(trs));
@@ -1442,6 +1516,7 @@ struct Renderer {
         switch (cfg.c.integrator) {
             case RAYCA_INTEGRATOR_PATHTRACER: ok = pathtracer_trace(ray, 0, true, pixel, sample, c, primary); break;
             case RAYCA_INTEGRATOR_RAYTRACER: ok = raytracer_trace(ray, 0, c, primary); break;
+            case RAYCA_INTEGRATOR_SCRATCHER: ok = scratcher_trace(ray, 0, c, primary); break;
             case RAYCA_INTEGRATOR_FLAT: ok = flat_trace(ray, c, primary); break;
             case RAYCA_INTEGRATOR_ANALYTIC_DIRECT: ok = analytic_trace(ray, 0, c, primary); break;
             case RAYCA_INTEGRATOR_DIRECT: ok = direct_trace(ray, 0, pixel, sample, c, primary); break;
@@ -1578,7 +1653,8 @@ int rayca_oracle_render(rayca_oracle_scene* s, const rayca_config* config, const
         if (cfg.c.russian_roulette) return RAYCA_E_UNSUPPORTED;
     } else if (cfg.c.integrator == RAYCA_INTEGRATOR_DIRECT) {
         if (cfg.c.light_samples == 0) return RAYCA_E_INVALID_ARG;
-    } else if (cfg.c.integrator != RAYCA_INTEGRATOR_RAYTRACER && cfg.c.integrator != RAYCA_INTEGRATOR_FLAT &&
+    } else if (cfg.c.integrator != RAYCA_INTEGRATOR_RAYTRACER && cfg.c.integrator != RAYCA_INTEGRATOR_SCRATCHER &&
+               cfg.c.integrator != RAYCA_INTEGRATOR_FLAT &&
                cfg.c.integrator != RAYCA_INTEGRATOR_ANALYTIC_DIRECT) {
         return RAYCA_E_UNSUPPORTED;
     }

@@ -91,9 +91,10 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
             if (c.light_samples == 0) return fail(RAYCA_E_INVALID_ARG, "light_samples must be >= 1");
             break;
         case RAYCA_INTEGRATOR_RAYTRACER:
+        case RAYCA_INTEGRATOR_SCRATCHER:
             if (c.max_depth + 1 > (uint32_t)kMaxDepth) return fail(RAYCA_E_UNSUPPORTED, "max_depth > 16");
             for (const GpuLight& l : sc.host.lights) // Light::get_direction is todo!() for quad lights (light/mod.rs:79-85)
-                if (l.kind == RAYCA_LIGHT_QUAD) return fail(RAYCA_E_UNSUPPORTED, "quad lights under the raytracer");
+                if (l.kind == RAYCA_LIGHT_QUAD) return fail(RAYCA_E_UNSUPPORTED, "quad lights under the raytracer / scratcher");
             break;
         case RAYCA_INTEGRATOR_PATHTRACER: {
             if (c.russian_roulette) return fail(RAYCA_E_UNSUPPORTED, "russian roulette");
@@ -110,7 +111,7 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
                     if (l.kind != RAYCA_LIGHT_POINT) return fail(RAYCA_E_UNSUPPORTED, "NEE supports point lights only");
             break;
         }
-        default: return fail(RAYCA_E_UNSUPPORTED, "integrator (Scratcher is not built)");
+        default: return fail(RAYCA_E_INVALID_ARG, "unknown integrator");
     }
     return RAYCA_OK;
 }
@@ -469,6 +470,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     switch (config->integrator) {
         case RAYCA_INTEGRATOR_PATHTRACER: launch_integrator<RAYCA_INTEGRATOR_PATHTRACER>(P, grid, sel, st); break;
         case RAYCA_INTEGRATOR_RAYTRACER: launch_integrator<RAYCA_INTEGRATOR_RAYTRACER>(P, grid, sel, st); break;
+        case RAYCA_INTEGRATOR_SCRATCHER: launch_integrator<RAYCA_INTEGRATOR_SCRATCHER>(P, grid, sel, st); break;
         case RAYCA_INTEGRATOR_ANALYTIC_DIRECT: launch_integrator<RAYCA_INTEGRATOR_ANALYTIC_DIRECT>(P, grid, sel, st); break;
         case RAYCA_INTEGRATOR_DIRECT: launch_integrator<RAYCA_INTEGRATOR_DIRECT>(P, grid, sel, st); break;
         default: launch_integrator<RAYCA_INTEGRATOR_FLAT>(P, grid, sel, st); break;

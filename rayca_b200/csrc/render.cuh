@@ -197,6 +197,114 @@ __device__ __forceinline__ bool pathtracer(const RenderParams& P, RayD ray, uint
 }
 
 // Raytracer::trace (integrator/raytracer.rs:16-76): mirror chain unrolled the same way.
+// The light loop the Raytracer and the Scratcher share (raytracer.rs:34-67, scratcher.rs:45-76): a light
+// contributes unless an OPAQUE surface lies between the point and the light (closest hit only).
+template <int MODE, bool COUNT>
+__device__ __forceinline__ void whitted_lights(const RenderParams& P, const Surf& sf, Col& acc, PixelCounters& pc) {
+    const GpuSceneView& s = P.scene;
+    for (uint32_t li = 0; li < s.light_count; ++li) {
+        const GpuLight& L = s.lights[li];
+        V3 lpos{L.pos[0], L.pos[1], L.pos[2]};
+        V3 ldir;
+        if (L.kind == RAYCA_LIGHT_POINT) ldir = -normalize(sf.point - lpos); // light/point.rs:50-54
+        else ldir = V3{L.dir[0], L.dir[1], L.dir[2]};
+        RayD shadow = make_ray(sf.next_origin, ldir);
+        HitD sh;
+        pc.shadow++;
+        bool lit = true;
+        if (trace_ray<MODE, false, COUNT>(s, shadow, sh, &pc.walk)) {
+            float ldist = length(sf.point - lpos); // light/point.rs:32-35, directional.rs:34-37
+            if (!(sh.t > ldist)) {
+                Surf ss;
+                load_surf<true, MODE == 3>(s, shadow, sh, ss);
+                lit = surf_color(s, ss).a < 1.0f - kF32Eps; // Color::is_transparent
+            }
+        }
+        if (lit) {
+            Col intensity = (L.kind == RAYCA_LIGHT_POINT)
+                                ? point_intensity(L, sf.point)
+                                : cscale(Col{L.color[0], L.color[1], L.color[2], L.color[3]}, L.intensity);
+            acc = cadd(acc, surf_radiance(s, sf, intensity, ldir));
+        }
+    }
+}
+
+// integrator/scratcher.rs:16-89.  The reference recurses twice per hit (transmission through a transparent surface,
+// then reflection) and combines the results with functions of the hit (Color::over, Hit::get_radiance), so the
+// recursion is run here with an explicit stack of frames: stage 1 waits for the transmitted colour, stage 3 for the
+// reflected one; additions happen in the reference's order (transmission, lights, reflection).
+template <int MODE, bool COUNT>
+__device__ __noinline__ bool scratcher(const RenderParams& P, RayD ray, Col& out, HitD& primary, PixelCounters& pc) {
+    const GpuSceneView& s = P.scene;
+    struct Frame {
+        Surf sf;
+        Col acc;
+        V3 refl;
+        int stage;
+    };
+    Frame st[kMaxDepth];
+    int sp = 0; // frames on the stack = depth of the call being entered
+    bool calling = true, ret_ok = false;
+    Col ret{0.0f, 0.0f, 0.0f, 1.0f};
+    for (;;) {
+        if (calling) { // trace(ray, depth = sp)
+            HitD h;
+            bool ok = (uint32_t)sp <= P.cfg.max_depth && sp < kMaxDepth;
+            if (ok) {
+                ok = trace_ray<MODE, false, COUNT>(s, ray, h, &pc.walk);
+                if (sp == 0) primary = h;
+            }
+            if (!ok) { // None
+                ret_ok = false;
+                calling = false;
+                if (sp == 0) break;
+                continue;
+            }
+            Frame& f = st[sp++];
+            load_surf<true, MODE == 3>(s, ray, h, f.sf);
+            f.acc = Col{0.0f, 0.0f, 0.0f, 1.0f};
+            f.stage = 2;
+            if (surf_color(s, f.sf).a < 1.0f - kF32Eps) { // hit.is_transparent(): continue below the surface (hit.rs:178-187)
+                ray = make_ray(f.sf.point + (-f.sf.normal) * kRayBias, f.sf.ray_dir);
+                if ((uint32_t)sp <= P.cfg.max_depth) pc.secondary++;
+                f.stage = 1;
+                continue;
+            }
+        } else { // a child returned into the top frame
+            Frame& f = st[sp - 1];
+            if (f.stage == 1) {
+                if (ret_ok) { // transmit_color.over(hit.get_color()); pixel_color += transmit_color (color/mod.rs:149-154)
+                    const Col top = surf_color(s, f.sf);
+                    Col t;
+                    t.r = top.r * top.a + ret.r * (1.0f - top.a);
+                    t.g = top.g * top.a + ret.g * (1.0f - top.a);
+                    t.b = top.b * top.a + ret.b * (1.0f - top.a);
+                    t.a = 1.0f;
+                    f.acc = cadd(f.acc, t);
+                }
+                f.stage = 2;
+            } else { // stage 3: reflection
+                if (ret_ok) f.acc = cadd(f.acc, surf_radiance(s, f.sf, ret, f.refl));
+                ret = f.acc;
+                ret_ok = true;
+                --sp;
+                if (sp == 0) break;
+                continue;
+            }
+        }
+        // stage 2: direct light, then the reflection call
+        Frame& f = st[sp - 1];
+        whitted_lights<MODE, COUNT>(P, f.sf, f.acc, pc);
+        f.refl = normalize(reflect(f.sf.ray_dir, f.sf.normal)); // hit.rs:93-101
+        ray = make_ray(f.sf.next_origin, f.refl);
+        if ((uint32_t)sp <= P.cfg.max_depth) pc.secondary++;
+        f.stage = 3;
+        calling = true;
+    }
+    out = ret;
+    return ret_ok;
+}
+
 template <int MODE, bool COUNT>
 __device__ __forceinline__ bool raytracer(const RenderParams& P, RayD ray, Col& out, HitD& primary, PixelCounters& pc) {
     const GpuSceneView& s = P.scene;
@@ -210,31 +318,7 @@ __device__ __forceinline__ bool raytracer(const RenderParams& P, RayD ray, Col& 
         Surf sf;
         load_surf<true, MODE == 3>(s, ray, h, sf);
         Col lc{0.0f, 0.0f, 0.0f, 1.0f};
-        for (uint32_t li = 0; li < s.light_count; ++li) {
-            const GpuLight& L = s.lights[li];
-            V3 lpos{L.pos[0], L.pos[1], L.pos[2]};
-            V3 ldir;
-            if (L.kind == RAYCA_LIGHT_POINT) ldir = -normalize(sf.point - lpos); // light/point.rs:50-54
-            else ldir = V3{L.dir[0], L.dir[1], L.dir[2]};
-            RayD shadow = make_ray(sf.next_origin, ldir);
-            HitD sh;
-            pc.shadow++;
-            bool lit = true;
-            if (trace_ray<MODE, false, COUNT>(s, shadow, sh, &pc.walk)) {
-                float ldist = length(sf.point - lpos); // light/point.rs:32-35, directional.rs:34-37
-                if (!(sh.t > ldist)) {
-                    Surf ss;
-                    load_surf<true, MODE == 3>(s, shadow, sh, ss);
-                    lit = surf_color(s, ss).a < 1.0f - kF32Eps; // Color::is_transparent
-                }
-            }
-            if (lit) {
-                Col intensity = (L.kind == RAYCA_LIGHT_POINT)
-                                    ? point_intensity(L, sf.point)
-                                    : cscale(Col{L.color[0], L.color[1], L.color[2], L.color[3]}, L.intensity);
-                lc = cadd(lc, surf_radiance(s, sf, intensity, ldir));
-            }
-        }
+        whitted_lights<MODE, COUNT>(P, sf, lc, pc);
         ambient[levels] = surf_color(s, sf);
         light[levels] = lc;
         spec[levels] = surf_specular(s, sf);
@@ -407,6 +491,8 @@ __device__ __forceinline__ void trace_sample(const RenderParams& P, uint32_t x, 
         ok = pathtracer<MODE, COUNT, BOUNCE>(P, ray, pixel, i, c, ph, pc);
     } else if (INTEGRATOR == RAYCA_INTEGRATOR_RAYTRACER) {
         ok = raytracer<MODE, COUNT>(P, ray, c, ph, pc);
+    } else if (INTEGRATOR == RAYCA_INTEGRATOR_SCRATCHER) {
+        ok = scratcher<MODE, COUNT>(P, ray, c, ph, pc);
     } else if (INTEGRATOR == RAYCA_INTEGRATOR_ANALYTIC_DIRECT) {
         ok = analytic_direct<MODE, COUNT>(P, ray, c, ph, pc);
     } else if (INTEGRATOR == RAYCA_INTEGRATOR_DIRECT) {

@@ -80,6 +80,45 @@ def cubes_over_plane_scene():
     return s
 
 
+def scratcher_sphere_scene():
+    """rayca-soft/tests/gltf.rs:9-45 `sphere`: Sphere::unit under a node translated (0,0,-1) and scaled (1,2,1),
+    drawn by the Scratcher integrator with Config::bvh(false)."""
+    m = M.Model()
+    m.geometries.append(M.Sphere(np.array([0, 0, 0], dtype=f32), 1.0))
+    m.primitives.append(M.Primitive(0))
+    m.meshes.append(M.Mesh([0]))
+    m.nodes.append(M.Node(mesh=0, trs=M.Trs(translation=np.array([0, 0, -1], dtype=f32),
+                                            scale=np.array([1, 2, 1], dtype=f32))))
+    m.root.children.append(0)
+    s = M.Scene()
+    s.push_model(m)
+    s.push_model(M.create_default_model())
+    return s
+
+
+def glass_scene():
+    """Transmission branch of the Scratcher (scratcher.rs:34-43, Color::over): two half-transparent triangles
+    (vertex alpha 0.35 / 0.6) one behind the other in front of an opaque checker of four triangles."""
+    m = M.Model()
+    back = M.make_vertices([[-3, -3, 0], [3, -3, 0], [3, 3, 0], [-3, 3, 0], [0, 0, 0]],
+                           color=[[0.9, 0.2, 0.2, 1], [0.2, 0.9, 0.2, 1], [0.2, 0.2, 0.9, 1], [0.9, 0.9, 0.2, 1], [1, 1, 1, 1]])
+    m.geometries.append(M.TriangleMesh(back, np.array([0, 1, 4, 1, 2, 4, 2, 3, 4, 3, 0, 4], dtype=np.uint32)))
+    near = M.make_vertices([[-1, -0.8, 0], [1, -0.8, 0], [0, 1, 0]], color=[[0.1, 0.6, 0.9, 0.35]] * 3)
+    m.geometries.append(M.TriangleMesh(near, np.array([0, 1, 2], dtype=np.uint32)))
+    mid = M.make_vertices([[-1.2, 0.9, 0], [0.2, -1.1, 0], [1.4, 0.7, 0]], color=[[0.9, 0.5, 0.1, 0.6]] * 3)
+    m.geometries.append(M.TriangleMesh(mid, np.array([0, 1, 2], dtype=np.uint32)))
+    for g in range(3):
+        m.primitives.append(M.Primitive(g))
+        m.meshes.append(M.Mesh([g]))
+    for mesh, z in ((0, -3.0), (1, -1.0), (2, -2.0)):
+        m.nodes.append(M.Node(mesh=mesh, trs=M.Trs(translation=np.array([0, 0, z], dtype=f32))))
+        m.root.children.append(len(m.nodes) - 1)
+    s = M.Scene()
+    s.push_model(m)
+    s.push_model(M.create_default_model())
+    return s
+
+
 def scale_root(f):
     def tweak(s, h):
         s.nodes[h].trs.scale = (s.nodes[h].trs.scale * np.array(f, dtype=f32)).astype(f32)
@@ -97,6 +136,7 @@ PT2 = dict(integrator=IntegratorStrategy.Pathtracer, max_depth=2)          # + o
 RT0 = dict(integrator=IntegratorStrategy.Raytracer, max_depth=0)
 RT3 = dict(integrator=IntegratorStrategy.Raytracer, max_depth=3)
 FLAT = dict(integrator=IntegratorStrategy.Flat)
+SC3 = dict(integrator=IntegratorStrategy.Scratcher, max_depth=3)
 
 # scene name -> (builder, {case name -> (config kwargs, width, height)})
 SCENES = {
@@ -110,8 +150,13 @@ SCENES = {
              "pt1_gamma": (dict(PT1, gamma=2.2), 64, 64), "wide": (PT1, 160, 48)}),
     "orientation": (lambda: gltf_scene("orientation/OrientationTest.gltf", scale_root([0.2, 0.2, 0.2])),
                     {"pt1": (PT1, 128, 128), "rt0": (RT0, 96, 96)}),
-    "cubes_over_plane": (cubes_over_plane_scene, {"pt1": (PT1, 128, 128), "rt3": (RT3, 96, 96), "pt3": (dict(integrator=IntegratorStrategy.Pathtracer, max_depth=3), 64, 64)}),
+    "cubes_over_plane": (cubes_over_plane_scene, {"pt1": (PT1, 128, 128), "rt3": (RT3, 96, 96), "sc3": (SC3, 96, 96), "pt3": (dict(integrator=IntegratorStrategy.Pathtracer, max_depth=3), 64, 64)}),
     "suzanne": (lambda: gltf_scene("suzanne/suzanne.gltf"), {"pt1": (PT1, 128, 128), "rt0": (RT0, 96, 96), "pt2": (PT2, 64, 64)}),
+    # Scratcher (integrator/scratcher.rs): the reference's own fixture, the transmission branch, reflections
+    "scratcher_sphere": (scratcher_sphere_scene, {"nobvh": (dict(integrator=IntegratorStrategy.Scratcher, bvh=False), 128, 128),
+                                                  "sc3": (SC3, 64, 64)}),
+    "glass": (glass_scene, {"sc3": (SC3, 128, 128), "sc0": (dict(integrator=IntegratorStrategy.Scratcher, max_depth=0), 64, 64),
+                            "sc5_spp4": (dict(integrator=IntegratorStrategy.Scratcher, max_depth=5, samples_per_pixel=4), 48, 48)}),
     "scene7": ("sdtf/1/scene7.sdtf", {"sdtf": (None, 80, 60)}),
     # spheres (BvhGeometry::Sphere) under the Raytracer with the files' own cameras, lights and Phong materials
     # (rayca-soft/tests/sdtf.rs scene2..scene6); `nobvh` = the Config::bvh(false) those tests use

@@ -150,7 +150,7 @@ def test_draw_trait_mirror(ctx, cuda_lib):
 
 def test_unsupported_and_error_paths(ctx):
     sc = dev_scene(ctx, "box")
-    for cfg in (R.Config(integrator=R.IntegratorStrategy.Scratcher), R.Config(direct_sampler=R.SamplerStrategy.Mis),
+    for cfg in (R.Config(direct_sampler=R.SamplerStrategy.Mis),
                 R.Config(russian_roulette=True), R.Config(indirect_sampler=R.SamplerStrategy.Brdf)):
         with pytest.raises(R.RaycaError) as e:
             sc.render(cfg, 16, 16)
