@@ -1147,6 +1147,10 @@ Color point_intensity(const rayca_light& l, const Trs& trs, Point3 frag) {
     return (l.intensity * to_color(l.color)) / point_fallof(l, trs, frag);
 }
 
+// Russian-roulette paths have no depth limit in the reference (pathtracer.rs:76); with the keyed RNG both this
+// oracle and the kernel stop a path that is still alive after this many bounces.
+constexpr uint32_t kRouletteDepthCap = 64;
+
 struct Renderer {
     const Scene& s;
     Config cfg;
@@ -1167,12 +1171,72 @@ struct Renderer {
         return (sv.x * u + sv.y * v) + sv.z * w;
     }
 
-    // sampler/nee.rs:127-216 (point lights; quad = 8(f), directional = todo!())
-    Color nee_direct(HitInfo& hit) {
+    // sampler/hemisphere.rs:17-40 with the keyed RNG in place of fastrand
+    Vec3 hemisphere_random_dir(HitInfo& hit, uint32_t depth, uint32_t light_sample) {
+        float e1 = rng_f32(cfg.seed, hit.pixel, hit.sample, depth, 2 * light_sample);
+        float e2 = rng_f32(cfg.seed, hit.pixel, hit.sample, depth, 2 * light_sample + 1);
+        float theta = std::acos(e1);
+        float omega = 2.0f * PI * e2;
+        Vec3 sv{std::cos(omega) * std::sin(theta), std::sin(omega) * std::sin(theta), std::cos(theta)};
+        Vec3 w = hit.get_normal();
+        Vec3 a = vec3_close(w, Vec3{0, 1, 0}) ? Vec3{1, 0, 0} : Vec3{0, 1, 0};
+        Vec3 u = normalized(cross(a, w));
+        Vec3 v = normalized(cross(w, u));
+        return (sv.x * u + sv.y * v) + sv.z * w;
+    }
+
+    // Keyed-RNG dimensions at one (pixel, sample, depth): [0, 2 LS) indirect directions, [2 LS, 3 LS) russian
+    // roulette, then two per (light, light sample) for the quad-light points.
+    uint32_t dim_roulette(uint32_t ls) const { return 2 * cfg.c.light_samples + ls; }
+    uint32_t dim_quad(uint32_t light_slot, uint32_t ls) const { return 3 * cfg.c.light_samples + 2 * (light_slot * cfg.c.light_samples + ls); }
+
+    // NextEventEstimationSampler::get_quad_light_sample (sampler/nee.rs:46-93); QuadLight::get_random_point
+    // (quad.rs:112-133).  The sample counts only when the CLOSEST hit along omega is emissive.
+    Color nee_quad_sample(HitInfo& hit, const LightDraw& ld, const rayca_light& l, uint32_t light_slot, uint32_t i, uint32_t depth) {
+        Color ldc = BLACK;
+        const uint32_t ls = cfg.c.light_samples;
+        const uint32_t strate_count = cfg.c.light_stratify ? (uint32_t)std::sqrt((float)ls) : 1u; // config.rs:73-79
+        Vec3 ab{l.ab[0], l.ab[1], l.ab[2]}, ac{l.ac[0], l.ac[1], l.ac[2]};
+        float area = quad_area(l);
+        Vec3 step1 = ab / (float)strate_count, step2 = ac / (float)strate_count;
+        float u1 = rng_f32(cfg.seed, hit.pixel, hit.sample, depth, dim_quad(light_slot, i)) / (float)strate_count;
+        float u2 = rng_f32(cfg.seed, hit.pixel, hit.sample, depth, dim_quad(light_slot, i) + 1) / (float)strate_count;
+        Point3 x1 = (quad_corner(l, ld.node_trs, 0) + (u1 * ab)) + (u2 * ac);
+        if (cfg.c.light_stratify) {
+            float i1 = (float)(i % strate_count), i2 = (float)(i / strate_count);
+            x1 = x1 + ((step1 * i1) + (step2 * i2));
+        }
+        Vec3 x_to_x1 = x1 - hit.hit.point;
+        Vec3 omega = normalized(x_to_x1);
+        Ray shadow = hit.get_next_ray(omega);
+        tracer.rays->rays_shadow++;
+        Hit sh;
+        if (tracer.intersects(shadow, sh)) {
+            HitInfo shi(s, sh);
+            if (shi.is_emissive()) {
+                Color le = l.intensity * to_color(l.color);
+                Color brdf = get_brdf(hit, omega);
+                float r_squared = norm(x_to_x1);
+                float d_omega = dot(quad_normal(l), omega) / r_squared;
+                float n_dot_omega = clampf(dot(hit.get_normal(), omega), 0.0f, 1.0f);
+                ldc = le * area * brdf * n_dot_omega * d_omega;
+            }
+        }
+        return ldc;
+    }
+
+    // sampler/nee.rs:127-216 (directional = todo!())
+    Color nee_direct(HitInfo& hit, uint32_t depth = 0) {
         Color ret = BLACK;
+        uint32_t light_slot_next = 0;
         for (const LightDraw& ld : s.light_draws) {
             const rayca_light& light = s.lights[ld.light];
+            const uint32_t light_slot = light_slot_next++;
             for (uint32_t ls = 0; ls < cfg.c.light_samples; ++ls) {
+                if (light.kind == RAYCA_LIGHT_QUAD) {
+                    ret = ret + nee_quad_sample(hit, ld, light, light_slot, ls, depth);
+                    continue;
+                }
                 if (light.kind != RAYCA_LIGHT_POINT) {
                     status = RAYCA_E_UNSUPPORTED;
                     continue;
@@ -1208,15 +1272,33 @@ struct Renderer {
     Color indirect_lighting(HitInfo& hit, uint32_t depth) {
         Color li = BLACK;
         bool collect_emissive = cfg.c.direct_sampler == RAYCA_SAMPLER_NONE;
+        const bool hemisphere = cfg.c.indirect_sampler == RAYCA_SAMPLER_HEMISPHERE;
         for (uint32_t ls = 0; ls < cfg.c.light_samples; ++ls) {
-            Vec3 omega_i = cosine_random_dir(hit, depth, ls);
+            Vec3 omega_i = hemisphere ? hemisphere_random_dir(hit, depth, ls) : cosine_random_dir(hit, depth, ls);
+            Color brdf_i = get_brdf(hit, omega_i);
             Ray next = hit.get_next_ray(omega_i);
+            float weight = 1.0f;
+            if (cfg.c.russian_roulette) { // pathtracer.rs:37-50, ray.rs:95-105
+                Color next_throughput = 2.0f * PI * hit.hit.ray.throughput * brdf_i * clampf(dot(hit.get_normal(), omega_i), 0.0f, 1.0f);
+                float mx = std::max(std::max(next_throughput.r, next_throughput.g), next_throughput.b);
+                float q = 1.0f - std::min(mx, 1.0f);
+                float e = clampf(rng_f32(cfg.seed, hit.pixel, hit.sample, depth, dim_roulette(ls)), 0.0f, 1.0f - F32_EPSILON);
+                if (!(q < e)) continue; // the path has not survived
+                weight = 1.0f / (1.0f - q);
+                next.throughput = next_throughput * weight;
+                if (depth + 1 >= kRouletteDepthCap) continue; // keyed-RNG paths are cut at the cap on both sides (documented)
+            }
             if (cfg.c.russian_roulette || depth + 1 < cfg.c.max_depth) tracer.rays->rays_secondary++;
             Color sample;
             if (pathtracer_trace(next, depth + 1, collect_emissive, hit.pixel, hit.sample, sample)) {
-                // sampler/cosine.rs:90-99 — PI * brdf * indirect_sample * weight
-                Color brdf = get_brdf(hit, omega_i);
-                li = li + PI * brdf * sample * 1.0f;
+                if (hemisphere) { // sampler/hemisphere.rs:42-52 — 2 PI * brdf * cosine_law * indirect_sample * weight
+                    Color brdf = get_brdf(hit, omega_i);
+                    float cosine_law = clampf(dot(hit.get_normal(), omega_i), 0.0f, 1.0f);
+                    li = li + 2.0f * PI * brdf * cosine_law * sample * weight;
+                } else { // sampler/cosine.rs:90-99 — PI * brdf * indirect_sample * weight
+                    Color brdf = get_brdf(hit, omega_i);
+                    li = li + PI * brdf * sample * weight;
+                }
             }
         }
         return li / (float)cfg.c.light_samples;
@@ -1238,7 +1320,7 @@ struct Renderer {
             return true;
         }
         Color direct = BLACK;
-        if (cfg.c.direct_sampler == RAYCA_SAMPLER_NEE) direct = nee_direct(hit);
+        if (cfg.c.direct_sampler == RAYCA_SAMPLER_NEE) direct = nee_direct(hit, depth);
         uint32_t limit = (cfg.c.direct_sampler != RAYCA_SAMPLER_NONE) ? cfg.c.max_depth - 1 : cfg.c.max_depth;
         Color indirect = BLACK;
         if (cfg.c.russian_roulette || depth < limit) indirect = indirect + indirect_lighting(hit, depth);
@@ -1649,8 +1731,8 @@ int rayca_oracle_render(rayca_oracle_scene* s, const rayca_config* config, const
     if (cfg.c.integrator == RAYCA_INTEGRATOR_PATHTRACER) {
         if (cfg.c.direct_sampler != RAYCA_SAMPLER_NEE && cfg.c.direct_sampler != RAYCA_SAMPLER_NONE) return RAYCA_E_UNSUPPORTED;
         bool needs_indirect = cfg.c.russian_roulette || cfg.c.max_depth > (cfg.c.direct_sampler != RAYCA_SAMPLER_NONE ? 1u : 0u);
-        if (needs_indirect && cfg.c.indirect_sampler != RAYCA_SAMPLER_COSINE) return RAYCA_E_UNSUPPORTED;
-        if (cfg.c.russian_roulette) return RAYCA_E_UNSUPPORTED;
+        if (needs_indirect && cfg.c.indirect_sampler != RAYCA_SAMPLER_COSINE && cfg.c.indirect_sampler != RAYCA_SAMPLER_HEMISPHERE)
+            return RAYCA_E_UNSUPPORTED; // Brdf sampler: a later row
     } else if (cfg.c.integrator == RAYCA_INTEGRATOR_DIRECT) {
         if (cfg.c.light_samples == 0) return RAYCA_E_INVALID_ARG;
     } else if (cfg.c.integrator != RAYCA_INTEGRATOR_RAYTRACER && cfg.c.integrator != RAYCA_INTEGRATOR_SCRATCHER &&

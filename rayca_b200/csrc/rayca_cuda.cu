@@ -97,18 +97,18 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
                 if (l.kind == RAYCA_LIGHT_QUAD) return fail(RAYCA_E_UNSUPPORTED, "quad lights under the raytracer / scratcher");
             break;
         case RAYCA_INTEGRATOR_PATHTRACER: {
-            if (c.russian_roulette) return fail(RAYCA_E_UNSUPPORTED, "russian roulette");
             if (c.direct_sampler != RAYCA_SAMPLER_NEE && c.direct_sampler != RAYCA_SAMPLER_NONE)
-                return fail(RAYCA_E_UNSUPPORTED, "direct sampler (only None / Nee)");
+                return fail(RAYCA_E_UNSUPPORTED, "direct sampler (only None / Nee; Mis is a later row)");
             if (c.max_depth > (uint32_t)kMaxDepth) return fail(RAYCA_E_UNSUPPORTED, "max_depth > 17");
             if (c.light_samples == 0) return fail(RAYCA_E_INVALID_ARG, "light_samples must be >= 1");
             bool nee = c.direct_sampler == RAYCA_SAMPLER_NEE;
-            bool bounces = c.max_depth > (nee ? 1u : 0u);
-            if (bounces && c.indirect_sampler != RAYCA_SAMPLER_COSINE) return fail(RAYCA_E_UNSUPPORTED, "indirect sampler (only Cosine)");
+            bool bounces = c.russian_roulette || c.max_depth > (nee ? 1u : 0u);
+            if (bounces && c.indirect_sampler != RAYCA_SAMPLER_COSINE && c.indirect_sampler != RAYCA_SAMPLER_HEMISPHERE)
+                return fail(RAYCA_E_UNSUPPORTED, "indirect sampler (only Cosine / Hemisphere; Brdf is a later row)");
             if (bounces && c.light_samples != 1) return fail(RAYCA_E_UNSUPPORTED, "light_samples > 1 with indirect bounces");
             if (nee)
-                for (const GpuLight& l : sc.host.lights) // NEE: directional is todo!() (nee.rs:177); quad is a later row
-                    if (l.kind != RAYCA_LIGHT_POINT) return fail(RAYCA_E_UNSUPPORTED, "NEE supports point lights only");
+                for (const GpuLight& l : sc.host.lights) // NEE: directional is todo!() (nee.rs:177)
+                    if (l.kind == RAYCA_LIGHT_DIRECTIONAL) return fail(RAYCA_E_UNSUPPORTED, "NEE with a directional light");
             break;
         }
         default: return fail(RAYCA_E_INVALID_ARG, "unknown integrator");
@@ -465,9 +465,18 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     P.tile_count = grid.x * grid.y;
     if (first) CUDA_TRY(cudaEventRecord(ctx->ev0, st));
     LaunchSel sel{mode, count, persistent, false, scene->host.has_spheres, ctx->sm_count};
-    if (config->integrator == RAYCA_INTEGRATOR_PATHTRACER) // an indirect ray needs depth < limit (pathtracer.rs:94)
-        sel.bounce = config->max_depth > (config->direct_sampler == RAYCA_SAMPLER_NEE ? 1u : 0u);
-    switch (config->integrator) {
+    uint32_t integrator = config->integrator;
+    if (integrator == RAYCA_INTEGRATOR_PATHTRACER) { // an indirect ray needs depth < limit (pathtracer.rs:94)
+        const bool nee = config->direct_sampler == RAYCA_SAMPLER_NEE;
+        sel.bounce = config->max_depth > (nee ? 1u : 0u);
+        // hemisphere bounces, roulette and quad lights under NEE run in the general path tracer (render.cuh)
+        bool general = config->russian_roulette != 0 || (sel.bounce && config->indirect_sampler == RAYCA_SAMPLER_HEMISPHERE);
+        if (nee)
+            for (const GpuLight& l : scene->host.lights) general = general || l.kind == RAYCA_LIGHT_QUAD;
+        if (general) integrator = kInternalPathGeneral;
+    }
+    switch (integrator) {
+        case kInternalPathGeneral: launch_integrator<(int)kInternalPathGeneral>(P, grid, sel, st); break;
         case RAYCA_INTEGRATOR_PATHTRACER: launch_integrator<RAYCA_INTEGRATOR_PATHTRACER>(P, grid, sel, st); break;
         case RAYCA_INTEGRATOR_RAYTRACER: launch_integrator<RAYCA_INTEGRATOR_RAYTRACER>(P, grid, sel, st); break;
         case RAYCA_INTEGRATOR_SCRATCHER: launch_integrator<RAYCA_INTEGRATOR_SCRATCHER>(P, grid, sel, st); break;

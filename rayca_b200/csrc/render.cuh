@@ -369,6 +369,140 @@ __device__ __forceinline__ bool surf_emissive(const Surf& sf) { // primitive.rs:
     return sf.mat->kind == RAYCA_MATERIAL_PHONG && sf.mat->emissive;
 }
 
+// ---- the general path tracer: everything pathtracer<> above leaves out so that the bench path stays small —
+// hemisphere bounces (sampler/hemisphere.rs), quad lights under next event estimation (sampler/nee.rs:46-93) and
+// russian roulette (pathtracer.rs:37-50, ray.rs:95-105).  One path per sample (light_samples = 1 whenever there are
+// bounces), so radiance = sum over depths of (product of the bounce factors so far) x (direct light at that depth):
+// accumulated forwards, which lets roulette paths run without a depth array.  The reference nests the same terms
+// from the tail; the two differ by rounding only, inside the tolerance the stochastic cases are compared with.
+constexpr uint32_t kInternalPathGeneral = 6u;  // launch-time selector next to the RAYCA_INTEGRATOR_* values
+constexpr uint32_t kRouletteDepthCap = 64u;    // a path still alive after this many bounces stops (oracle: same cap)
+
+__device__ __forceinline__ V3 hemisphere_dir(const RenderParams& P, const Surf& sf, uint32_t pixel, uint32_t sample, uint32_t depth) {
+    float e1 = rng_f32(P.seed, pixel, sample, depth, 0);
+    float e2 = rng_f32(P.seed, pixel, sample, depth, 1);
+    float theta = acosf(e1);
+    float omega = 2.0f * kPi * e2;
+    V3 sv{cosf(omega) * sinf(theta), sinf(omega) * sinf(theta), cosf(theta)};
+    V3 w = sf.normal;
+    V3 a = close_to_y(w) ? V3{1.0f, 0.0f, 0.0f} : V3{0.0f, 1.0f, 0.0f};
+    V3 u = normalize(cross(a, w));
+    V3 v = normalize(cross(w, u));
+    return (sv.x * u + sv.y * v) + sv.z * w;
+}
+
+// NextEventEstimationSampler::get_direct_lighting with point AND quad lights; dimensions as in the oracle:
+// [0, 2 LS) bounce direction, [2 LS, 3 LS) roulette, then two per (light, light sample)
+template <int MODE, bool COUNT>
+__device__ __forceinline__ Col nee_general(const RenderParams& P, const Surf& sf, uint32_t pixel, uint32_t sample, uint32_t depth,
+                                           PixelCounters& pc) {
+    const GpuSceneView& s = P.scene;
+    const uint32_t ls = P.cfg.light_samples;
+    const uint32_t strate = P.cfg.light_stratify ? __float2uint_rz(sqrtf((float)ls)) : 1u; // config.rs:73-79
+    const float fstrate = (float)strate;
+    Col ret{0.0f, 0.0f, 0.0f, 1.0f};
+    for (uint32_t li = 0; li < s.light_count; ++li) {
+        const GpuLight& L = s.lights[li];
+#pragma unroll 1
+        for (uint32_t i = 0; i < ls; ++i) {
+            Col xs{0.0f, 0.0f, 0.0f, 1.0f};
+            if (L.kind == RAYCA_LIGHT_QUAD) {
+                const V3 ab{L.ab[0], L.ab[1], L.ab[2]}, ac{L.ac[0], L.ac[1], L.ac[2]}, qn{L.normal[0], L.normal[1], L.normal[2]};
+                const uint32_t dim = 3u * ls + 2u * (li * ls + i);
+                const float u1 = rng_f32(P.seed, pixel, sample, depth, dim) / fstrate;
+                const float u2 = rng_f32(P.seed, pixel, sample, depth, dim + 1u) / fstrate;
+                V3 x1 = (quad_corner(L, 0) + u1 * ab) + u2 * ac;
+                if (P.cfg.light_stratify) x1 = x1 + ((ab / fstrate) * (float)(i % strate) + (ac / fstrate) * (float)(i / strate));
+                const V3 to_x1 = x1 - sf.point;
+                const V3 omega = normalize(to_x1);
+                const RayD shadow = make_ray(sf.next_origin, omega);
+                HitD sh;
+                pc.shadow++;
+                if (trace_ray<MODE, false, COUNT>(s, shadow, sh, &pc.walk)) { // counts only when the closest hit is a light
+                    const GpuMaterial* sm = s.materials + __float_as_uint(__ldg(s.tri_attr + 12 * (size_t)sh.prim + 9).w);
+                    if (sm->kind == RAYCA_MATERIAL_PHONG && sm->emissive) {
+                        const Col le = cscale(Col{L.color[0], L.color[1], L.color[2], L.color[3]}, L.intensity);
+                        const Col brdf = surf_brdf(s, sf, omega);
+                        const float d_omega = dot(qn, omega) / norm2(to_x1);
+                        const float n_dot = fminf(fmaxf(dot(sf.normal, omega), 0.0f), 1.0f);
+                        xs = cscale(cscale(cmul(cscale(le, L.area), brdf), n_dot), d_omega);
+                    }
+                }
+            } else { // point light (nee.rs:95-137)
+                const V3 to_x1 = V3{L.pos[0], L.pos[1], L.pos[2]} - sf.point;
+                const float dist = length(to_x1);
+                const V3 omega = normalize(to_x1);
+                const RayD shadow = make_ray(sf.next_origin, omega);
+                HitD sh;
+                pc.shadow++;
+                bool occluded = false;
+                if (trace_ray<MODE, false, COUNT>(s, shadow, sh, &pc.walk)) occluded = sh.t < dist;
+                if (!occluded) {
+                    const Col le = point_intensity(L, sf.point);
+                    const Col brdf = surf_brdf(s, sf, omega);
+                    const float d_omega = 1.0f / norm2(to_x1);
+                    const float n_dot = fminf(fmaxf(dot(sf.normal, omega), 0.0f), 1.0f);
+                    xs = cscale(cscale(cmul(le, brdf), n_dot), d_omega);
+                }
+            }
+            ret = cadd(ret, xs);
+        }
+    }
+    return ret;
+}
+
+template <int MODE, bool COUNT>
+__device__ __noinline__ bool pathtracer_general(const RenderParams& P, RayD ray, uint32_t pixel, uint32_t sample, Col& out,
+                                                HitD& primary, PixelCounters& pc) {
+    const GpuSceneView& s = P.scene;
+    const bool nee = P.cfg.direct_sampler == RAYCA_SAMPLER_NEE;
+    const bool rr = P.cfg.russian_roulette != 0;
+    const bool hemisphere = P.cfg.indirect_sampler == RAYCA_SAMPLER_HEMISPHERE;
+    const uint32_t max_depth = P.cfg.max_depth;
+    const uint32_t limit = nee ? max_depth - 1u : max_depth;
+    Col sum{0.0f, 0.0f, 0.0f, 1.0f};
+    Col factor{1.0f, 1.0f, 1.0f, 1.0f};      // product of the samplers' get_radiance factors down to this depth
+    Col throughput{1.0f, 1.0f, 1.0f, 1.0f};  // Ray::throughput, only used by the roulette
+    bool collect_emissive = true, any = false;
+    for (uint32_t depth = 0;; ++depth) {
+        if (!rr && depth >= max_depth) break;
+        if (rr && depth >= kRouletteDepthCap) break;
+        HitD h;
+        const bool hit = trace_ray<MODE, false, COUNT>(s, ray, h, &pc.walk);
+        if (depth == 0) primary = h;
+        if (!hit) break;
+        any = true;
+        Surf sf;
+        load_surf<true, MODE == 3>(s, ray, h, sf);
+        if (collect_emissive && surf_emissive(sf)) {
+            sum = cadd(sum, cmul(factor, surf_color(s, sf)));
+            break;
+        }
+        if (nee) sum = cadd(sum, cmul(factor, nee_general<MODE, COUNT>(P, sf, pixel, sample, depth, pc)));
+        if (!(rr || depth < limit)) break;
+        const V3 wi = hemisphere ? hemisphere_dir(P, sf, pixel, sample, depth) : cosine_dir(P, sf, pixel, sample, depth, 0);
+        const Col brdf = surf_brdf(s, sf, wi);
+        const float cosine_law = fminf(fmaxf(dot(sf.normal, wi), 0.0f), 1.0f);
+        float weight = 1.0f;
+        if (rr) {
+            const Col next_tp = cscale(cmul(cscale(throughput, 2.0f * kPi), brdf), cosine_law);
+            const float q = 1.0f - fminf(fmaxf(fmaxf(next_tp.r, next_tp.g), next_tp.b), 1.0f);
+            const float e = fminf(fmaxf(rng_f32(P.seed, pixel, sample, depth, 2u * P.cfg.light_samples), 0.0f), 1.0f - kF32Eps);
+            if (!(q < e)) break; // the path has not survived
+            weight = 1.0f / (1.0f - q);
+            throughput = cscale(next_tp, weight);
+        }
+        // hemisphere.rs:42-52: 2 PI * brdf * cosine_law * sample * weight; cosine.rs:90-99: PI * brdf * sample * weight
+        const Col f = hemisphere ? cscale(cscale(cscale(brdf, 2.0f * kPi), cosine_law), weight) : cscale(cscale(brdf, kPi), weight);
+        factor = cmul(factor, f);
+        ray = make_ray(sf.next_origin, wi);
+        if (rr || depth + 1u < max_depth) pc.secondary++;
+        collect_emissive = !nee;
+    }
+    out = sum;
+    return any;
+}
+
 // AnalyticDirect::trace (integrator/analyticdirect.rs:16-49)
 template <int MODE, bool COUNT>
 __device__ __forceinline__ bool analytic_direct(const RenderParams& P, const RayD& ray, Col& out, HitD& primary, PixelCounters& pc) {
@@ -487,7 +621,9 @@ __device__ __forceinline__ void trace_sample(const RenderParams& P, uint32_t x, 
     c = Col{0.0f, 0.0f, 0.0f, 1.0f};
     bool ok;
     ph = no_hit();
-    if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER) {
+    if (INTEGRATOR == (int)kInternalPathGeneral) {
+        ok = pathtracer_general<MODE, COUNT>(P, ray, pixel, i, c, ph, pc);
+    } else if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER) {
         ok = pathtracer<MODE, COUNT, BOUNCE>(P, ray, pixel, i, c, ph, pc);
     } else if (INTEGRATOR == RAYCA_INTEGRATOR_RAYTRACER) {
         ok = raytracer<MODE, COUNT>(P, ray, c, ph, pc);

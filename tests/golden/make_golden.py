@@ -136,6 +136,8 @@ PT2 = dict(integrator=IntegratorStrategy.Pathtracer, max_depth=2)          # + o
 RT0 = dict(integrator=IntegratorStrategy.Raytracer, max_depth=0)
 RT3 = dict(integrator=IntegratorStrategy.Raytracer, max_depth=3)
 FLAT = dict(integrator=IntegratorStrategy.Flat)
+PTC = dict(integrator=IntegratorStrategy.Pathtracer, indirect_sampler=SamplerStrategy.Hemisphere, max_depth=5, samples_per_pixel=4,
+           light_samples=1, light_stratify=False)
 SC3 = dict(integrator=IntegratorStrategy.Scratcher, max_depth=3)
 
 # scene name -> (builder, {case name -> (config kwargs, width, height)})
@@ -168,7 +170,14 @@ SCENES = {
     "analytic": ("sdtf/2/analytic.sdtf", {"sdtf": (None, 160, 120)}),
     "direct9": ("sdtf/2/direct9.sdtf", {"sdtf": (None, 120, 90)}),
     "direct3x3": ("sdtf/2/direct3x3.sdtf", {"sdtf": (None, 120, 90)}),
-    "cornell": ("sdtf/2/cornell.sdtf", {"sdtf": (None, 120, 120), "analytic": (dict(integrator=IntegratorStrategy.AnalyticDirect), 96, 96)}),
+    "cornell": ("sdtf/2/cornell.sdtf", {"sdtf": (None, 120, 120), "analytic": (dict(integrator=IntegratorStrategy.AnalyticDirect), 96, 96),
+                                        # the path-tracing settings of sdtf/3 and sdtf/4 on the same box (cornellSimple, cornellNEE,
+                                        # cornellRR, cornellCosine) at 4 spp: hemisphere / cosine bounces, quad-light NEE, roulette
+                                        "pt_simple": (dict(PTC, direct_sampler=SamplerStrategy.NONE), 48, 48),
+                                        "pt_nee": (dict(PTC, direct_sampler=SamplerStrategy.Nee), 48, 48),
+                                        "pt_rr": (dict(PTC, direct_sampler=SamplerStrategy.Nee, russian_roulette=True, max_depth=16), 48, 48),
+                                        "pt_cosine_rr": (dict(PTC, direct_sampler=SamplerStrategy.Nee, indirect_sampler=SamplerStrategy.Cosine,
+                                                              russian_roulette=True, max_depth=16), 40, 40)}),
     "quadsphere": ("sdtf/2/sphere.sdtf", {"sdtf": (None, 120, 90)}),
     "dragon": ("sdtf/2/dragon.sdtf", {"ls4": (dict(light_samples=4), 48, 36)}),  # 100,002 triangles + 2 quad lights
 }

@@ -150,8 +150,8 @@ def test_draw_trait_mirror(ctx, cuda_lib):
 
 def test_unsupported_and_error_paths(ctx):
     sc = dev_scene(ctx, "box")
-    for cfg in (R.Config(direct_sampler=R.SamplerStrategy.Mis),
-                R.Config(russian_roulette=True), R.Config(indirect_sampler=R.SamplerStrategy.Brdf)):
+    for cfg in (R.Config(direct_sampler=R.SamplerStrategy.Mis), R.Config(indirect_sampler=R.SamplerStrategy.Brdf),
+                R.Config(light_samples=4)):  # Mis / Brdf samplers and branching bounces are later rows
         with pytest.raises(R.RaycaError) as e:
             sc.render(cfg, 16, 16)
         assert e.value.code == -2
@@ -413,3 +413,25 @@ def test_device_built_reference_blas_equals_host_built(ctx):
         assert np.array_equal(noa, nob) and np.array_equal(poa, pob) and np.array_equal(sa, sb), name
         a.close()
         b.close()
+
+
+def test_cornell_estimators_agree_in_the_mean(ctx):
+    """sdtf/3 + sdtf/4 settings at the files' own 480x480: hemisphere and cosine bounces, with and without next event
+    estimation on the quad light, with and without russian roulette are estimators of the same image, so their
+    mean radiance must agree (64 spp: within 3 %)."""
+    sc = dev_scene(ctx, "cornell")
+    P, S = R.IntegratorStrategy.Pathtracer, R.SamplerStrategy
+    base = dict(integrator=P, max_depth=16, samples_per_pixel=64, light_samples=1, light_stratify=False)
+    means = {}
+    for name, kw in {"hemisphere": dict(direct_sampler=S.NONE, indirect_sampler=S.Hemisphere),
+                     "cosine": dict(direct_sampler=S.NONE, indirect_sampler=S.Cosine),
+                     "nee": dict(direct_sampler=S.Nee, indirect_sampler=S.Hemisphere),
+                     "nee+rr": dict(direct_sampler=S.Nee, indirect_sampler=S.Cosine, russian_roulette=True)}.items():
+        _, aux, st = sc.render(R.Config(**base, **kw), 480, 480, want_aux=True)
+        rgb = aux.rgba_f32.reshape(480, 480, 4)[..., :3]
+        assert np.isfinite(rgb).all()
+        means[name] = float(rgb.mean())
+        assert st.rays_primary == 480 * 480 * 64
+    ref = means["nee"]
+    for name, m in means.items():
+        assert abs(m - ref) <= 0.03 * ref, means
