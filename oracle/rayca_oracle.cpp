@@ -976,6 +976,26 @@ struct HitInfo {
         }
     }
     float get_shininess() const { return phong(material()).shininess; } // material/mod.rs:154-160 (Phong only)
+    // specular weight: phong.rs:64-71, ggx.rs:54-61 (Vec3::reduce_avg = ordered 4-lane sum / 3); todo!() for PBR
+    bool t_unsupported = false;
+    float get_t() {
+        rayca_material m = material();
+        float kd[3], ks[3];
+        if (m.kind == RAYCA_MATERIAL_PHONG) {
+            const rayca_phong_material pm = phong(m);
+            for (int k = 0; k < 3; ++k) { kd[k] = pm.diffuse[k]; ks[k] = pm.specular[k]; }
+        } else if (m.kind == RAYCA_MATERIAL_GGX) {
+            const rayca_ggx_material gm = ggx(m);
+            for (int k = 0; k < 3; ++k) { kd[k] = gm.diffuse[k]; ks[k] = gm.specular[k]; }
+        } else {
+            t_unsupported = true;
+            return 0.0f;
+        }
+        float kd_avg = (((kd[0] + kd[1]) + kd[2]) + 0.0f) / 3.0f, ks_avg = (((ks[0] + ks[1]) + ks[2]) + 0.0f) / 3.0f;
+        if (ks_avg == 0.0f && kd_avg == 0.0f) return 1.0f;
+        float t = ks_avg / (ks_avg + kd_avg);
+        return m.kind == RAYCA_MATERIAL_GGX ? std::max(t, 0.25f) : t;
+    }
     // hit.rs:77-83 / primitive.rs:171-181 / pbr.rs:104-123
     Vec3 get_normal() {
         if (!has_normal && prim->sphere) { // primitive.rs:183-190
@@ -1075,6 +1095,48 @@ Color lambertian_get_brdf(HitInfo& hit, Vec3 omega_i) {
     float s = hit.get_shininess();
     Color specular = (hit.get_specular() * (s + 2.0f) * std::pow(dot(hit.get_reflection(), omega_i), s) * FRAC_1_PI) / 2.0f;
     return lambertian + specular;
+}
+// brdf/lambertian.rs:70-76, brdf/ggx.rs:188-203; hit.rs:238-245
+Color get_specular_component(HitInfo& hit, Vec3 omega) {
+    if (hit.material().kind == RAYCA_MATERIAL_PHONG) {
+        float sh = hit.get_shininess();
+        float n_dot_omega = clampf(dot(hit.get_normal(), omega), 0.0f, 1.0f);
+        return hit.get_specular() * n_dot_omega * (sh + 2.0f) / (sh + 1.0f);
+    }
+    Vec3 omega_o = hit.get_view();
+    Vec3 n = hit.get_normal();
+    float o_dot_n = clampf(dot(omega_o, n), 0.0f, 1.0f);
+    Vec3 h = normalized(omega + omega_o);
+    float n_dot_h = clampf(dot(n, h), 0.0f, 1.0f);
+    if (o_dot_n == 0.0f || n_dot_h == 0.0f) return BLACK;
+    Color ks = hit.get_specular();
+    float a = hit.get_roughness();
+    float h_dot_omega = clampf(dot(h, omega), 0.0f, 1.0f);
+    return ggx_get_f(ks, omega, h) * (ggx_get_g1(a, omega, n) * ggx_get_g1(a, omega_o, n)) * h_dot_omega / (o_dot_n * n_dot_h);
+}
+// lambertian::get_random_dir (lambertian.rs:31-68) / ggx::get_random_dir (ggx.rs:146-186) with e0, e1, e2 supplied
+Vec3 material_random_dir(HitInfo& hit, float e0, float e1, float e2) {
+    const bool is_phong = hit.material().kind == RAYCA_MATERIAL_PHONG;
+    float t = hit.get_t();
+    float theta;
+    if (e0 <= t) {
+        if (is_phong) theta = std::acos(clampf(std::pow(e1, 1.0f / (hit.get_shininess() + 1.0f)), -1.0f, 1.0f));
+        else theta = std::atan((hit.get_roughness() * std::sqrt(e1)) / std::sqrt(1.0f - e1));
+    } else {
+        theta = std::acos(clampf(std::sqrt(e1), -1.0f, 1.0f));
+    }
+    float omega = 2.0f * PI * e2;
+    Vec3 sv{std::cos(omega) * std::sin(theta), std::sin(omega) * std::sin(theta), std::cos(theta)};
+    Vec3 w = (is_phong && e0 <= t) ? hit.get_reflection() : hit.get_normal();
+    Vec3 a = vec3_close(w, Vec3{0, 1, 0}) ? Vec3{1, 0, 0} : Vec3{0, 1, 0};
+    Vec3 u = normalized(cross(a, w));
+    Vec3 v = cross(w, u);
+    Vec3 dir = (sv.x * u + sv.y * v) + sv.z * w;
+    if (!is_phong && e0 <= t) { // the sampled vector is the half vector: reflect -omega_o about it (vec3.rs:219-221)
+        Vec3 mo = -hit.get_view();
+        return mo - (2.0f * dot(mo, dir)) * dir;
+    }
+    return dir;
 }
 // hit.rs:220-227
 Color get_brdf(HitInfo& hit, Vec3 omega_i) {
@@ -1188,6 +1250,7 @@ struct Renderer {
     // Keyed-RNG dimensions at one (pixel, sample, depth): [0, 2 LS) indirect directions, [2 LS, 3 LS) russian
     // roulette, then two per (light, light sample) for the quad-light points.
     uint32_t dim_roulette(uint32_t ls) const { return 2 * cfg.c.light_samples + ls; }
+    uint32_t dim_lobe(uint32_t ls) const { return 0x10000u + ls; } // specular / diffuse lobe choice of the Brdf sampler
     uint32_t dim_quad(uint32_t light_slot, uint32_t ls) const { return 3 * cfg.c.light_samples + 2 * (light_slot * cfg.c.light_samples + ls); }
 
     // NextEventEstimationSampler::get_quad_light_sample (sampler/nee.rs:46-93); QuadLight::get_random_point
@@ -1273,8 +1336,18 @@ struct Renderer {
         Color li = BLACK;
         bool collect_emissive = cfg.c.direct_sampler == RAYCA_SAMPLER_NONE;
         const bool hemisphere = cfg.c.indirect_sampler == RAYCA_SAMPLER_HEMISPHERE;
+        const bool brdf_sampler = cfg.c.indirect_sampler == RAYCA_SAMPLER_BRDF;
         for (uint32_t ls = 0; ls < cfg.c.light_samples; ++ls) {
-            Vec3 omega_i = hemisphere ? hemisphere_random_dir(hit, depth, ls) : cosine_random_dir(hit, depth, ls);
+            Vec3 omega_i;
+            if (brdf_sampler) { // sampler/brdf.rs:70-73: the material's own importance sampling; lobe choice at dim_lobe
+                float e0 = rng_f32(cfg.seed, hit.pixel, hit.sample, depth, dim_lobe(ls));
+                float e1 = rng_f32(cfg.seed, hit.pixel, hit.sample, depth, 2 * ls);
+                float e2 = rng_f32(cfg.seed, hit.pixel, hit.sample, depth, 2 * ls + 1);
+                omega_i = material_random_dir(hit, e0, e1, e2);
+                if (hit.t_unsupported) { status = RAYCA_E_UNSUPPORTED; return BLACK; } // Material::get_t is todo!() for PBR
+            } else {
+                omega_i = hemisphere ? hemisphere_random_dir(hit, depth, ls) : cosine_random_dir(hit, depth, ls);
+            }
             Color brdf_i = get_brdf(hit, omega_i);
             Ray next = hit.get_next_ray(omega_i);
             float weight = 1.0f;
@@ -1291,7 +1364,11 @@ struct Renderer {
             if (cfg.c.russian_roulette || depth + 1 < cfg.c.max_depth) tracer.rays->rays_secondary++;
             Color sample;
             if (pathtracer_trace(next, depth + 1, collect_emissive, hit.pixel, hit.sample, sample)) {
-                if (hemisphere) { // sampler/hemisphere.rs:42-52 — 2 PI * brdf * cosine_law * indirect_sample * weight
+                if (brdf_sampler) { // sampler/brdf.rs:80-90 — indirect_sample * (cd + cs) * weight
+                    Color cd = hit.get_diffuse();
+                    Color cs = get_specular_component(hit, omega_i);
+                    li = li + sample * (cd + cs) * weight;
+                } else if (hemisphere) { // sampler/hemisphere.rs:42-52 — 2 PI * brdf * cosine_law * indirect_sample * weight
                     Color brdf = get_brdf(hit, omega_i);
                     float cosine_law = clampf(dot(hit.get_normal(), omega_i), 0.0f, 1.0f);
                     li = li + 2.0f * PI * brdf * cosine_law * sample * weight;
@@ -1731,8 +1808,9 @@ int rayca_oracle_render(rayca_oracle_scene* s, const rayca_config* config, const
     if (cfg.c.integrator == RAYCA_INTEGRATOR_PATHTRACER) {
         if (cfg.c.direct_sampler != RAYCA_SAMPLER_NEE && cfg.c.direct_sampler != RAYCA_SAMPLER_NONE) return RAYCA_E_UNSUPPORTED;
         bool needs_indirect = cfg.c.russian_roulette || cfg.c.max_depth > (cfg.c.direct_sampler != RAYCA_SAMPLER_NONE ? 1u : 0u);
-        if (needs_indirect && cfg.c.indirect_sampler != RAYCA_SAMPLER_COSINE && cfg.c.indirect_sampler != RAYCA_SAMPLER_HEMISPHERE)
-            return RAYCA_E_UNSUPPORTED; // Brdf sampler: a later row
+        if (needs_indirect && cfg.c.indirect_sampler != RAYCA_SAMPLER_COSINE && cfg.c.indirect_sampler != RAYCA_SAMPLER_HEMISPHERE &&
+            cfg.c.indirect_sampler != RAYCA_SAMPLER_BRDF)
+            return RAYCA_E_UNSUPPORTED;
     } else if (cfg.c.integrator == RAYCA_INTEGRATOR_DIRECT) {
         if (cfg.c.light_samples == 0) return RAYCA_E_INVALID_ARG;
     } else if (cfg.c.integrator != RAYCA_INTEGRATOR_RAYTRACER && cfg.c.integrator != RAYCA_INTEGRATOR_SCRATCHER &&

@@ -103,8 +103,14 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
             if (c.light_samples == 0) return fail(RAYCA_E_INVALID_ARG, "light_samples must be >= 1");
             bool nee = c.direct_sampler == RAYCA_SAMPLER_NEE;
             bool bounces = c.russian_roulette || c.max_depth > (nee ? 1u : 0u);
-            if (bounces && c.indirect_sampler != RAYCA_SAMPLER_COSINE && c.indirect_sampler != RAYCA_SAMPLER_HEMISPHERE)
-                return fail(RAYCA_E_UNSUPPORTED, "indirect sampler (only Cosine / Hemisphere; Brdf is a later row)");
+            if (bounces && c.indirect_sampler != RAYCA_SAMPLER_COSINE && c.indirect_sampler != RAYCA_SAMPLER_HEMISPHERE &&
+                c.indirect_sampler != RAYCA_SAMPLER_BRDF)
+                return fail(RAYCA_E_UNSUPPORTED, "indirect sampler");
+            if (bounces && c.indirect_sampler == RAYCA_SAMPLER_BRDF) { // Material::get_t is todo!() for PBR (material/mod.rs:163-169)
+                bool pbr = sc.host.materials.size() <= 1;
+                for (size_t k = 1; k < sc.host.materials.size(); ++k) pbr = pbr || sc.host.materials[k].kind == RAYCA_MATERIAL_PBR;
+                if (pbr) return fail(RAYCA_E_UNSUPPORTED, "the Brdf sampler needs Phong / GGX materials");
+            }
             if (bounces && c.light_samples != 1) return fail(RAYCA_E_UNSUPPORTED, "light_samples > 1 with indirect bounces");
             if (nee)
                 for (const GpuLight& l : sc.host.lights) // NEE: directional is todo!() (nee.rs:177)
@@ -470,7 +476,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
         const bool nee = config->direct_sampler == RAYCA_SAMPLER_NEE;
         sel.bounce = config->max_depth > (nee ? 1u : 0u);
         // hemisphere bounces, roulette and quad lights under NEE run in the general path tracer (render.cuh)
-        bool general = config->russian_roulette != 0 || (sel.bounce && config->indirect_sampler == RAYCA_SAMPLER_HEMISPHERE);
+        bool general = config->russian_roulette != 0 || (sel.bounce && config->indirect_sampler != RAYCA_SAMPLER_COSINE);
         if (nee)
             for (const GpuLight& l : scene->host.lights) general = general || l.kind == RAYCA_LIGHT_QUAD;
         if (general) integrator = kInternalPathGeneral;

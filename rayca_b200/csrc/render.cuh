@@ -391,6 +391,59 @@ __device__ __forceinline__ V3 hemisphere_dir(const RenderParams& P, const Surf& 
     return (sv.x * u + sv.y * v) + sv.z * w;
 }
 
+// Material::get_t: the specular weight (phong.rs:64-71, ggx.rs:54-61; todo!() for PBR, refused at launch)
+__device__ __forceinline__ float surf_t(const Surf& sf) {
+    const GpuMaterial* m = sf.mat;
+    const float* kd = m->kind == RAYCA_MATERIAL_PHONG ? m->c : m->a;
+    const float* ks = m->d;
+    const float kd_avg = (((kd[0] + kd[1]) + kd[2]) + 0.0f) / 3.0f, ks_avg = (((ks[0] + ks[1]) + ks[2]) + 0.0f) / 3.0f;
+    if (ks_avg == 0.0f && kd_avg == 0.0f) return 1.0f;
+    const float t = ks_avg / (ks_avg + kd_avg);
+    return m->kind == RAYCA_MATERIAL_GGX ? fmaxf(t, 0.25f) : t;
+}
+// lambertian::get_random_dir (lambertian.rs:31-68) / ggx::get_random_dir (ggx.rs:146-186)
+__device__ __forceinline__ V3 material_dir(const GpuSceneView& s, const Surf& sf, float e0, float e1, float e2) {
+    const bool is_phong = sf.mat->kind == RAYCA_MATERIAL_PHONG;
+    const float t = surf_t(sf);
+    float theta;
+    if (e0 <= t) {
+        if (is_phong) theta = acosf(clampf(powf(e1, 1.0f / (sf.mat->p0 + 1.0f)), -1.0f, 1.0f));
+        else theta = atanf((surf_roughness(s, sf) * sqrtf(e1)) / sqrtf(1.0f - e1));
+    } else {
+        theta = acosf(clampf(sqrtf(e1), -1.0f, 1.0f));
+    }
+    const float omega = 2.0f * kPi * e2;
+    const V3 sv{cosf(omega) * sinf(theta), sinf(omega) * sinf(theta), cosf(theta)};
+    const V3 w = (is_phong && e0 <= t) ? normalize(reflect(sf.ray_dir, sf.normal)) : sf.normal;
+    const V3 a = close_to_y(w) ? V3{1.0f, 0.0f, 0.0f} : V3{0.0f, 1.0f, 0.0f};
+    const V3 u = normalize(cross(a, w));
+    const V3 v = cross(w, u);
+    const V3 dir = (sv.x * u + sv.y * v) + sv.z * w;
+    if (!is_phong && e0 <= t) { // the sampled vector is the half vector: reflect -omega_o about it
+        const V3 mo = -sf.view_dir;
+        return mo - (2.0f * dot(mo, dir)) * dir;
+    }
+    return dir;
+}
+// lambertian::get_specular_component (lambertian.rs:70-76) / ggx::get_specular_component (ggx.rs:188-203)
+__device__ __forceinline__ Col surf_specular_component(const GpuSceneView& s, const Surf& sf, V3 wi) {
+    if (sf.mat->kind == RAYCA_MATERIAL_PHONG) {
+        const float sh = sf.mat->p0;
+        const float ndw = clampf(dot(sf.normal, wi), 0.0f, 1.0f);
+        return cdiv(cscale(cscale(ld_col(sf.mat->d), ndw), sh + 2.0f), sh + 1.0f);
+    }
+    const V3 wo = sf.view_dir, n = sf.normal;
+    const float odn = clampf(dot(wo, n), 0.0f, 1.0f);
+    const V3 h = normalize(wi + wo);
+    const float ndh = clampf(dot(n, h), 0.0f, 1.0f);
+    if (odn == 0.0f || ndh == 0.0f) return Col{0.0f, 0.0f, 0.0f, 1.0f};
+    const Col ks = surf_specular(s, sf);
+    const float a = surf_roughness(s, sf);
+    const float hdw = clampf(dot(h, wi), 0.0f, 1.0f);
+    const Col f = cadd(ks, cscale(csub(Col{1.0f, 1.0f, 1.0f, 1.0f}, ks), pow5(1.0f - fabsf(dot(wi, h)))));
+    return cdiv(cscale(cscale(f, ggx_g1(a, wi, n) * ggx_g1(a, wo, n)), hdw), odn * ndh);
+}
+
 // NextEventEstimationSampler::get_direct_lighting with point AND quad lights; dimensions as in the oracle:
 // [0, 2 LS) bounce direction, [2 LS, 3 LS) roulette, then two per (light, light sample)
 template <int MODE, bool COUNT>
@@ -458,6 +511,7 @@ __device__ __noinline__ bool pathtracer_general(const RenderParams& P, RayD ray,
     const bool nee = P.cfg.direct_sampler == RAYCA_SAMPLER_NEE;
     const bool rr = P.cfg.russian_roulette != 0;
     const bool hemisphere = P.cfg.indirect_sampler == RAYCA_SAMPLER_HEMISPHERE;
+    const bool brdf_sampler = P.cfg.indirect_sampler == RAYCA_SAMPLER_BRDF;
     const uint32_t max_depth = P.cfg.max_depth;
     const uint32_t limit = nee ? max_depth - 1u : max_depth;
     Col sum{0.0f, 0.0f, 0.0f, 1.0f};
@@ -480,7 +534,12 @@ __device__ __noinline__ bool pathtracer_general(const RenderParams& P, RayD ray,
         }
         if (nee) sum = cadd(sum, cmul(factor, nee_general<MODE, COUNT>(P, sf, pixel, sample, depth, pc)));
         if (!(rr || depth < limit)) break;
-        const V3 wi = hemisphere ? hemisphere_dir(P, sf, pixel, sample, depth) : cosine_dir(P, sf, pixel, sample, depth, 0);
+        V3 wi;
+        if (brdf_sampler) // sampler/brdf.rs:70-73; lobe choice at dimension 0x10000 (oracle: dim_lobe)
+            wi = material_dir(s, sf, rng_f32(P.seed, pixel, sample, depth, 0x10000u), rng_f32(P.seed, pixel, sample, depth, 0),
+                              rng_f32(P.seed, pixel, sample, depth, 1));
+        else
+            wi = hemisphere ? hemisphere_dir(P, sf, pixel, sample, depth) : cosine_dir(P, sf, pixel, sample, depth, 0);
         const Col brdf = surf_brdf(s, sf, wi);
         const float cosine_law = fminf(fmaxf(dot(sf.normal, wi), 0.0f), 1.0f);
         float weight = 1.0f;
@@ -493,7 +552,10 @@ __device__ __noinline__ bool pathtracer_general(const RenderParams& P, RayD ray,
             throughput = cscale(next_tp, weight);
         }
         // hemisphere.rs:42-52: 2 PI * brdf * cosine_law * sample * weight; cosine.rs:90-99: PI * brdf * sample * weight
-        const Col f = hemisphere ? cscale(cscale(cscale(brdf, 2.0f * kPi), cosine_law), weight) : cscale(cscale(brdf, kPi), weight);
+        // brdf.rs:80-90: sample * (cd + cs) * weight
+        const Col f = brdf_sampler ? cscale(cadd(surf_diffuse(s, sf), surf_specular_component(s, sf, wi)), weight)
+                      : hemisphere ? cscale(cscale(cscale(brdf, 2.0f * kPi), cosine_law), weight)
+                                   : cscale(cscale(brdf, kPi), weight);
         factor = cmul(factor, f);
         ray = make_ray(sf.next_origin, wi);
         if (rr || depth + 1u < max_depth) pc.secondary++;
