@@ -1043,6 +1043,12 @@ struct HitInfo {
     }
     Ray get_next_ray(Vec3 dir) { return make_ray(get_next_ray_origin(), dir); }
     // primitive.rs:122-130
+    // primitive.rs:132-140: Phong emission, BLACK for PBR / GGX
+    Color get_emission() const {
+        rayca_material m = material();
+        if (m.kind == RAYCA_MATERIAL_PHONG) return to_color(phong(m).emission);
+        return BLACK;
+    }
     bool is_emissive() const {
         rayca_material m = material();
         if (m.kind == RAYCA_MATERIAL_PHONG) return !color_close(to_color(phong(m).emission), BLACK);
@@ -1137,6 +1143,28 @@ Vec3 material_random_dir(HitInfo& hit, float e0, float e1, float e2) {
         return mo - (2.0f * dot(mo, dir)) * dir;
     }
     return dir;
+}
+// lambertian::get_pdf (lambertian.rs:17-26) / ggx::get_pdf (ggx.rs:129-144); hit.rs:229-236
+float material_pdf(HitInfo& hit, Vec3 omega) {
+    constexpr float FRAC_2_PI = 0.636619772367581343075535053490057448f;
+    if (hit.material().kind == RAYCA_MATERIAL_PHONG) {
+        float r_dot_omega = clampf(dot(hit.get_reflection(), omega), 0.0f, 1.0f);
+        float sh = hit.get_shininess();
+        float spec = (sh + 1.0f) * FRAC_2_PI * std::pow(r_dot_omega, sh);
+        float diff = clampf(dot(hit.get_normal(), omega), 0.0f, 1.0f) * FRAC_1_PI;
+        float t = hit.get_t();
+        return (1.0f - t) * diff + t * spec;
+    }
+    Vec3 omega_o = hit.get_view();
+    Vec3 h = normalized(omega_o + omega);
+    float h_dot_omega = clampf(dot(h, omega), 0.0f, 1.0f);
+    if (h_dot_omega == 0.0f) return 0.0f;
+    Vec3 n = hit.get_normal();
+    float n_dot_h = clampf(dot(n, h), 0.0f, 1.0f);
+    float spec = ggx_get_d(hit.get_roughness(), h, n) * n_dot_h / (4.0f * h_dot_omega);
+    float dif = clampf(dot(n, omega), 0.0f, 1.0f) * FRAC_1_PI;
+    float t = hit.get_t();
+    return (1.0f - t) * dif + t * spec;
 }
 // hit.rs:220-227
 Color get_brdf(HitInfo& hit, Vec3 omega_i) {
@@ -1255,7 +1283,8 @@ struct Renderer {
 
     // NextEventEstimationSampler::get_quad_light_sample (sampler/nee.rs:46-93); QuadLight::get_random_point
     // (quad.rs:112-133).  The sample counts only when the CLOSEST hit along omega is emissive.
-    Color nee_quad_sample(HitInfo& hit, const LightDraw& ld, const rayca_light& l, uint32_t light_slot, uint32_t i, uint32_t depth) {
+    Color nee_quad_sample(HitInfo& hit, const LightDraw& ld, const rayca_light& l, uint32_t light_slot, uint32_t i, uint32_t depth,
+                          Vec3* omega_out = nullptr) {
         Color ldc = BLACK;
         const uint32_t ls = cfg.c.light_samples;
         const uint32_t strate_count = cfg.c.light_stratify ? (uint32_t)std::sqrt((float)ls) : 1u; // config.rs:73-79
@@ -1271,6 +1300,7 @@ struct Renderer {
         }
         Vec3 x_to_x1 = x1 - hit.hit.point;
         Vec3 omega = normalized(x_to_x1);
+        if (omega_out) *omega_out = omega;
         Ray shadow = hit.get_next_ray(omega);
         tracer.rays->rays_shadow++;
         Hit sh;
@@ -1286,6 +1316,26 @@ struct Renderer {
             }
         }
         return ldc;
+    }
+
+    // NextEventEstimationSampler::get_point_light_sample (sampler/nee.rs:95-137)
+    Color nee_point_sample(HitInfo& hit, const LightDraw& ld, const rayca_light& light, Vec3* omega_out = nullptr) {
+        Point3 x1 = to_point3(trs_get_translation(ld.node_trs));
+        Point3 x = hit.hit.point;
+        Vec3 x_to_x1 = x1 - x;
+        float dist = len(x_to_x1);
+        Vec3 omega = normalized(x_to_x1);
+        if (omega_out) *omega_out = omega;
+        Ray shadow = hit.get_next_ray(omega);
+        Hit sh;
+        tracer.rays->rays_shadow++;
+        if (tracer.intersects(shadow, sh) && sh.depth < dist) return BLACK;
+        Color le = point_intensity(light, ld.node_trs, x);
+        Color brdf = get_brdf(hit, omega);
+        float r2 = norm(x_to_x1);
+        float d_omega = 1.0f / r2;
+        float n_dot_omega = clampf(dot(hit.get_normal(), omega), 0.0f, 1.0f);
+        return le * brdf * n_dot_omega * d_omega;
     }
 
     // sampler/nee.rs:127-216 (directional = todo!())
@@ -1304,29 +1354,109 @@ struct Renderer {
                     status = RAYCA_E_UNSUPPORTED;
                     continue;
                 }
-                Point3 x1 = to_point3(trs_get_translation(ld.node_trs));
-                Point3 x = hit.hit.point;
-                Vec3 x_to_x1 = x1 - x;
-                float dist = len(x_to_x1);
-                Vec3 omega = normalized(x_to_x1);
-                Ray shadow = hit.get_next_ray(omega);
-                Hit sh;
-                tracer.rays->rays_shadow++;
-                bool occluded = false;
-                if (tracer.intersects(shadow, sh)) {
-                    if (sh.depth < dist) occluded = true;
-                }
-                Color xs = BLACK;
-                if (!occluded) {
-                    Color le = point_intensity(light, ld.node_trs, x);
-                    Color brdf = get_brdf(hit, omega);
-                    float r2 = norm(x_to_x1);
-                    float d_omega = 1.0f / r2;
-                    float n_dot_omega = clampf(dot(hit.get_normal(), omega), 0.0f, 1.0f);
-                    xs = le * brdf * n_dot_omega * d_omega;
-                }
-                ret = ret + xs;
+                ret = ret + nee_point_sample(hit, ld, light);
             }
+        }
+        return ret;
+    }
+
+    // QuadLight::intersects over its two "wide" triangles (quad.rs:135-158; the `ab + ab` of corner c is the
+    // reference's); first hit in list order, single-sided like every triangle test
+    bool quad_light_intersects(const rayca_light& l, const Trs& trs, const Ray& ray, Point3& point) {
+        const float SMALL_BIAS = 1e-2f;
+        Vec3 ab{l.ab[0], l.ab[1], l.ab[2]}, ac{l.ac[0], l.ac[1], l.ac[2]};
+        Point3 a = to_point3(-normalized(ab + ac) * SMALL_BIAS);
+        Point3 b = to_point3(ab + normalized(ab - ac) * SMALL_BIAS);
+        Point3 c = to_point3((ab + ac) + normalized(ab + ab) * SMALL_BIAS);
+        Point3 d = to_point3(ac + normalized(ac - ab) * SMALL_BIAS);
+        Point3 tri[2][3] = {{a, c, b}, {a, d, c}};
+        for (int k = 0; k < 2; ++k) {
+            float t;
+            Vec2 uv;
+            if (triangle_intersects_world(transform_point(trs, tri[k][0]), transform_point(trs, tri[k][1]), transform_point(trs, tri[k][2]),
+                                          ray, t, point, uv))
+                return true;
+        }
+        return false;
+    }
+    // NextEventEstimationSample::get_pdf (sampler/nee.rs:44-65)
+    float nee_pdf(const LightDraw& ld, HitInfo& hit, Vec3 omega) {
+        const rayca_light& l = s.lights[ld.light];
+        if (l.kind != RAYCA_LIGHT_QUAD) return 0.0f; // Light::intersects is None for point / directional lights
+        Ray ray = hit.get_next_ray(omega);
+        Point3 light_point;
+        if (!quad_light_intersects(l, ld.node_trs, ray, light_point)) return 0.0f;
+        float area = quad_area(l);
+        if (area == 0.0f) return 0.0f;
+        float nl_dot_omega = clampf(dot(quad_normal(l), omega), 0.0f, 1.0f);
+        if (nl_dot_omega == 0.0f) return 0.0f;
+        float r_squared = norm(light_point - hit.hit.point);
+        return r_squared / (area * nl_dot_omega);
+    }
+    // MultipleImportanceSampling::get_direct_lighting (sampler/mis.rs:41-72) with BrdfSampler::sample_direct
+    // (sampler/brdf.rs:48-66); the Brdf sample draws its three numbers at dimensions 0x20000..0x20002
+    Color mis_direct(HitInfo& hit, uint32_t depth) {
+        struct LightSample { Vec3 omega; Color x; };
+        std::vector<LightSample> samples;
+        uint32_t light_slot_next = 0;
+        for (const LightDraw& ld : s.light_draws) {
+            const rayca_light& light = s.lights[ld.light];
+            const uint32_t light_slot = light_slot_next++;
+            for (uint32_t ls = 0; ls < cfg.c.light_samples; ++ls) {
+                LightSample smp;
+                if (light.kind == RAYCA_LIGHT_QUAD) {
+                    smp.x = nee_quad_sample(hit, ld, light, light_slot, ls, depth, &smp.omega);
+                } else if (light.kind == RAYCA_LIGHT_POINT) {
+                    smp.x = nee_point_sample(hit, ld, light, &smp.omega);
+                } else {
+                    status = RAYCA_E_UNSUPPORTED;
+                    continue;
+                }
+                samples.push_back(smp);
+            }
+        }
+        // Brdf sample
+        float e0 = rng_f32(cfg.seed, hit.pixel, hit.sample, depth, 0x20000u);
+        float e1 = rng_f32(cfg.seed, hit.pixel, hit.sample, depth, 0x20001u);
+        float e2 = rng_f32(cfg.seed, hit.pixel, hit.sample, depth, 0x20002u);
+        Vec3 omega_b = material_random_dir(hit, e0, e1, e2);
+        if (hit.t_unsupported) { status = RAYCA_E_UNSUPPORTED; return BLACK; }
+        float pdf_b = material_pdf(hit, omega_b);
+        Color x_b = BLACK;
+        {
+            Ray shadow = hit.get_next_ray(omega_b);
+            tracer.rays->rays_shadow++;
+            Hit sh;
+            if (tracer.intersects(shadow, sh)) {
+                HitInfo shi(s, sh);
+                if (shi.is_emissive()) {
+                    Color li = shi.get_emission();
+                    Color cd = hit.get_diffuse();
+                    Color cs = get_specular_component(hit, omega_b);
+                    x_b = li * (cd + cs);
+                }
+            }
+        }
+        auto pdf_nee_of = [&](Vec3 omega) {
+            float ret = 0.0f;
+            uint32_t k = 0;
+            for (const LightDraw& ld : s.light_draws) // one term per light SAMPLE (get_pdf_nee sums over the sample list)
+                for (uint32_t ls = 0; ls < cfg.c.light_samples; ++ls, ++k) ret += nee_pdf(ld, hit, omega);
+            return ret / (float)samples.size();
+        };
+        Color ret = BLACK;
+        for (const LightSample& smp : samples) {
+            float pdf_nee = pdf_nee_of(smp.omega);
+            float pdf_brdf = material_pdf(hit, smp.omega);
+            float pdf_den = pdf_nee * pdf_nee + pdf_brdf * pdf_brdf;
+            float w = pdf_den == 0.0f ? 0.0f : (pdf_nee * pdf_nee) / pdf_den;
+            ret = ret + w * smp.x;
+        }
+        {
+            float pdf_nee = pdf_nee_of(omega_b);
+            float pdf_den = pdf_nee * pdf_nee + pdf_b * pdf_b;
+            float w = pdf_den == 0.0f ? 0.0f : (pdf_b * pdf_b) / pdf_den;
+            ret = ret + w * x_b;
         }
         return ret;
     }
@@ -1398,6 +1528,7 @@ struct Renderer {
         }
         Color direct = BLACK;
         if (cfg.c.direct_sampler == RAYCA_SAMPLER_NEE) direct = nee_direct(hit, depth);
+        else if (cfg.c.direct_sampler == RAYCA_SAMPLER_MIS) direct = mis_direct(hit, depth);
         uint32_t limit = (cfg.c.direct_sampler != RAYCA_SAMPLER_NONE) ? cfg.c.max_depth - 1 : cfg.c.max_depth;
         Color indirect = BLACK;
         if (cfg.c.russian_roulette || depth < limit) indirect = indirect + indirect_lighting(hit, depth);
@@ -1806,7 +1937,9 @@ int rayca_oracle_render(rayca_oracle_scene* s, const rayca_config* config, const
     if (config->samples_per_pixel == 0) return RAYCA_E_INVALID_ARG;
     Config cfg{*config, options ? options->rng_seed : 0};
     if (cfg.c.integrator == RAYCA_INTEGRATOR_PATHTRACER) {
-        if (cfg.c.direct_sampler != RAYCA_SAMPLER_NEE && cfg.c.direct_sampler != RAYCA_SAMPLER_NONE) return RAYCA_E_UNSUPPORTED;
+        if (cfg.c.direct_sampler != RAYCA_SAMPLER_NEE && cfg.c.direct_sampler != RAYCA_SAMPLER_NONE &&
+            cfg.c.direct_sampler != RAYCA_SAMPLER_MIS)
+            return RAYCA_E_UNSUPPORTED;
         bool needs_indirect = cfg.c.russian_roulette || cfg.c.max_depth > (cfg.c.direct_sampler != RAYCA_SAMPLER_NONE ? 1u : 0u);
         if (needs_indirect && cfg.c.indirect_sampler != RAYCA_SAMPLER_COSINE && cfg.c.indirect_sampler != RAYCA_SAMPLER_HEMISPHERE &&
             cfg.c.indirect_sampler != RAYCA_SAMPLER_BRDF)

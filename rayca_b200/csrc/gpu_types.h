@@ -57,6 +57,9 @@ struct alignas(16) GpuLight {
     uint32_t pad2;
     float normal[3];
     uint32_t pad3;
+    // the two "wide" triangles QuadLight::intersects tests (quad.rs:135-158), corners a, b, c, d moved to world space
+    // with the light node's LOCAL trs: triangles (a, c, b) and (a, d, c); read by the MIS light pdf only
+    float wide[4][4];
 };
 
 struct GpuCamera {

@@ -160,6 +160,15 @@ struct Flatten {
                 std::memcpy(g.ac, l.ac, sizeof(g.ac));
                 g.normal[0] = nq.x; g.normal[1] = nq.y; g.normal[2] = nq.z;
                 g.area = sin_theta * ab_len * ac_len;
+                {   // get_wide_triangles (quad.rs:147-158; `ab + ab` for corner c is the reference's), then `trs * vertex`
+                    const float small_bias = 1e-2f;
+                    V3 wide[4] = {-normalize(ab + ac) * small_bias, ab + normalize(ab - ac) * small_bias,
+                                  (ab + ac) + normalize(ab + ab) * small_bias, ac + normalize(ac - ab) * small_bias};
+                    for (int k = 0; k < 4; ++k) {
+                        V3 w = trs_point(local, wide[k]);
+                        g.wide[k][0] = w.x; g.wide[k][1] = w.y; g.wide[k][2] = w.z; g.wide[k][3] = 0.0f;
+                    }
+                }
                 quad_draws[mi].push_back(QuadDraw{m.light_offset + (uint32_t)n.light, cur});
             }
             out.lights.push_back(g);

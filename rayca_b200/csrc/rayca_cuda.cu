@@ -97,19 +97,23 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
                 if (l.kind == RAYCA_LIGHT_QUAD) return fail(RAYCA_E_UNSUPPORTED, "quad lights under the raytracer / scratcher");
             break;
         case RAYCA_INTEGRATOR_PATHTRACER: {
-            if (c.direct_sampler != RAYCA_SAMPLER_NEE && c.direct_sampler != RAYCA_SAMPLER_NONE)
-                return fail(RAYCA_E_UNSUPPORTED, "direct sampler (only None / Nee; Mis is a later row)");
+            if (c.direct_sampler != RAYCA_SAMPLER_NEE && c.direct_sampler != RAYCA_SAMPLER_NONE && c.direct_sampler != RAYCA_SAMPLER_MIS)
+                return fail(RAYCA_E_UNSUPPORTED, "direct sampler (None / Nee / Mis)");
             if (c.max_depth > (uint32_t)kMaxDepth) return fail(RAYCA_E_UNSUPPORTED, "max_depth > 17");
             if (c.light_samples == 0) return fail(RAYCA_E_INVALID_ARG, "light_samples must be >= 1");
-            bool nee = c.direct_sampler == RAYCA_SAMPLER_NEE;
+            bool mis = c.direct_sampler == RAYCA_SAMPLER_MIS;
+            bool nee = c.direct_sampler == RAYCA_SAMPLER_NEE || mis;
             bool bounces = c.russian_roulette || c.max_depth > (nee ? 1u : 0u);
+            bool material_sampling = mis || (bounces && c.indirect_sampler == RAYCA_SAMPLER_BRDF);
+            if (mis && sc.host.lights.size() * (size_t)c.light_samples > kMaxMisSamples)
+                return fail(RAYCA_E_UNSUPPORTED, "Mis keeps at most 16 light samples per hit");
             if (bounces && c.indirect_sampler != RAYCA_SAMPLER_COSINE && c.indirect_sampler != RAYCA_SAMPLER_HEMISPHERE &&
                 c.indirect_sampler != RAYCA_SAMPLER_BRDF)
                 return fail(RAYCA_E_UNSUPPORTED, "indirect sampler");
-            if (bounces && c.indirect_sampler == RAYCA_SAMPLER_BRDF) { // Material::get_t is todo!() for PBR (material/mod.rs:163-169)
+            if (material_sampling) { // Material::get_t is todo!() for PBR (material/mod.rs:163-169)
                 bool pbr = sc.host.materials.size() <= 1;
                 for (size_t k = 1; k < sc.host.materials.size(); ++k) pbr = pbr || sc.host.materials[k].kind == RAYCA_MATERIAL_PBR;
-                if (pbr) return fail(RAYCA_E_UNSUPPORTED, "the Brdf sampler needs Phong / GGX materials");
+                if (pbr) return fail(RAYCA_E_UNSUPPORTED, "the Brdf / Mis samplers need Phong / GGX materials");
             }
             if (bounces && c.light_samples != 1) return fail(RAYCA_E_UNSUPPORTED, "light_samples > 1 with indirect bounces");
             if (nee)
@@ -473,10 +477,11 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     LaunchSel sel{mode, count, persistent, false, scene->host.has_spheres, ctx->sm_count};
     uint32_t integrator = config->integrator;
     if (integrator == RAYCA_INTEGRATOR_PATHTRACER) { // an indirect ray needs depth < limit (pathtracer.rs:94)
-        const bool nee = config->direct_sampler == RAYCA_SAMPLER_NEE;
+        const bool mis = config->direct_sampler == RAYCA_SAMPLER_MIS;
+        const bool nee = config->direct_sampler == RAYCA_SAMPLER_NEE || mis;
         sel.bounce = config->max_depth > (nee ? 1u : 0u);
         // hemisphere bounces, roulette and quad lights under NEE run in the general path tracer (render.cuh)
-        bool general = config->russian_roulette != 0 || (sel.bounce && config->indirect_sampler != RAYCA_SAMPLER_COSINE);
+        bool general = mis || config->russian_roulette != 0 || (sel.bounce && config->indirect_sampler != RAYCA_SAMPLER_COSINE);
         if (nee)
             for (const GpuLight& l : scene->host.lights) general = general || l.kind == RAYCA_LIGHT_QUAD;
         if (general) integrator = kInternalPathGeneral;

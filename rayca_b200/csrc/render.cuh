@@ -446,60 +446,149 @@ __device__ __forceinline__ Col surf_specular_component(const GpuSceneView& s, co
 
 // NextEventEstimationSampler::get_direct_lighting with point AND quad lights; dimensions as in the oracle:
 // [0, 2 LS) bounce direction, [2 LS, 3 LS) roulette, then two per (light, light sample)
+// One next-event-estimation sample of light `li` (sampler/nee.rs:46-137): its direction and its value
+template <int MODE, bool COUNT>
+__device__ __forceinline__ Col nee_sample(const RenderParams& P, const Surf& sf, uint32_t li, uint32_t i, uint32_t pixel, uint32_t sample,
+                                          uint32_t depth, PixelCounters& pc, V3& omega) {
+    const GpuSceneView& s = P.scene;
+    const GpuLight& L = s.lights[li];
+    const uint32_t ls = P.cfg.light_samples;
+    Col xs{0.0f, 0.0f, 0.0f, 1.0f};
+    if (L.kind == RAYCA_LIGHT_QUAD) {
+        const uint32_t strate = P.cfg.light_stratify ? __float2uint_rz(sqrtf((float)ls)) : 1u; // config.rs:73-79
+        const float fstrate = (float)strate;
+        const V3 ab{L.ab[0], L.ab[1], L.ab[2]}, ac{L.ac[0], L.ac[1], L.ac[2]}, qn{L.normal[0], L.normal[1], L.normal[2]};
+        const uint32_t dim = 3u * ls + 2u * (li * ls + i);
+        const float u1 = rng_f32(P.seed, pixel, sample, depth, dim) / fstrate;
+        const float u2 = rng_f32(P.seed, pixel, sample, depth, dim + 1u) / fstrate;
+        V3 x1 = (quad_corner(L, 0) + u1 * ab) + u2 * ac;
+        if (P.cfg.light_stratify) x1 = x1 + ((ab / fstrate) * (float)(i % strate) + (ac / fstrate) * (float)(i / strate));
+        const V3 to_x1 = x1 - sf.point;
+        omega = normalize(to_x1);
+        const RayD shadow = make_ray(sf.next_origin, omega);
+        HitD sh;
+        pc.shadow++;
+        if (trace_ray<MODE, false, COUNT>(s, shadow, sh, &pc.walk)) { // counts only when the closest hit is a light
+            const GpuMaterial* sm = s.materials + __float_as_uint(__ldg(s.tri_attr + 12 * (size_t)sh.prim + 9).w);
+            if (sm->kind == RAYCA_MATERIAL_PHONG && sm->emissive) {
+                const Col le = cscale(Col{L.color[0], L.color[1], L.color[2], L.color[3]}, L.intensity);
+                const Col brdf = surf_brdf(s, sf, omega);
+                const float d_omega = dot(qn, omega) / norm2(to_x1);
+                const float n_dot = fminf(fmaxf(dot(sf.normal, omega), 0.0f), 1.0f);
+                xs = cscale(cscale(cmul(cscale(le, L.area), brdf), n_dot), d_omega);
+            }
+        }
+    } else { // point light (nee.rs:95-137)
+        const V3 to_x1 = V3{L.pos[0], L.pos[1], L.pos[2]} - sf.point;
+        const float dist = length(to_x1);
+        omega = normalize(to_x1);
+        const RayD shadow = make_ray(sf.next_origin, omega);
+        HitD sh;
+        pc.shadow++;
+        bool occluded = false;
+        if (trace_ray<MODE, false, COUNT>(s, shadow, sh, &pc.walk)) occluded = sh.t < dist;
+        if (!occluded) {
+            const Col le = point_intensity(L, sf.point);
+            const Col brdf = surf_brdf(s, sf, omega);
+            const float d_omega = 1.0f / norm2(to_x1);
+            const float n_dot = fminf(fmaxf(dot(sf.normal, omega), 0.0f), 1.0f);
+            xs = cscale(cscale(cmul(le, brdf), n_dot), d_omega);
+        }
+    }
+    return xs;
+}
+// NextEventEstimationSampler::get_direct_lighting with point AND quad lights; dimensions as in the oracle:
+// [0, 2 LS) bounce direction, [2 LS, 3 LS) roulette, then two per (light, light sample)
 template <int MODE, bool COUNT>
 __device__ __forceinline__ Col nee_general(const RenderParams& P, const Surf& sf, uint32_t pixel, uint32_t sample, uint32_t depth,
                                            PixelCounters& pc) {
+    Col ret{0.0f, 0.0f, 0.0f, 1.0f};
+    for (uint32_t li = 0; li < P.scene.light_count; ++li)
+#pragma unroll 1
+        for (uint32_t i = 0; i < P.cfg.light_samples; ++i) {
+            V3 omega;
+            ret = cadd(ret, nee_sample<MODE, COUNT>(P, sf, li, i, pixel, sample, depth, pc, omega));
+        }
+    return ret;
+}
+
+// lambertian::get_pdf (lambertian.rs:17-26) / ggx::get_pdf (ggx.rs:129-144)
+__device__ __forceinline__ float material_pdf(const GpuSceneView& s, const Surf& sf, V3 omega) {
+    const float kFrac2Pi = 0.636619772367581343075535053490057448f;
+    if (sf.mat->kind == RAYCA_MATERIAL_PHONG) {
+        const V3 refl = normalize(reflect(sf.ray_dir, sf.normal));
+        const float rdw = clampf(dot(refl, omega), 0.0f, 1.0f);
+        const float sh = sf.mat->p0;
+        const float spec = (sh + 1.0f) * kFrac2Pi * powf(rdw, sh);
+        const float diff = clampf(dot(sf.normal, omega), 0.0f, 1.0f) * kFrac1Pi;
+        const float t = surf_t(sf);
+        return (1.0f - t) * diff + t * spec;
+    }
+    const V3 h = normalize(sf.view_dir + omega);
+    const float hdw = clampf(dot(h, omega), 0.0f, 1.0f);
+    if (hdw == 0.0f) return 0.0f;
+    const float ndh = clampf(dot(sf.normal, h), 0.0f, 1.0f);
+    const float spec = ggx_d(surf_roughness(s, sf), h, sf.normal) * ndh / (4.0f * hdw);
+    const float dif = clampf(dot(sf.normal, omega), 0.0f, 1.0f) * kFrac1Pi;
+    const float t = surf_t(sf);
+    return (1.0f - t) * dif + t * spec;
+}
+// NextEventEstimationSample::get_pdf (nee.rs:44-65): QuadLight::intersects over its wide triangles, first hit in order
+__device__ __forceinline__ float nee_pdf(const GpuLight& L, const Surf& sf, V3 omega) {
+    if (L.kind != RAYCA_LIGHT_QUAD) return 0.0f;
+    const RayD ray = make_ray(sf.next_origin, omega);
+    const float4 a = make_float4(L.wide[0][0], L.wide[0][1], L.wide[0][2], 0.0f), b = make_float4(L.wide[1][0], L.wide[1][1], L.wide[1][2], 0.0f),
+                 c = make_float4(L.wide[2][0], L.wide[2][1], L.wide[2][2], 0.0f), d = make_float4(L.wide[3][0], L.wide[3][1], L.wide[3][2], 0.0f);
+    float t, u, v;
+    V3 p;
+    if (!tri_test(a, c, b, ray, t, u, v, p) && !tri_test(a, d, c, ray, t, u, v, p)) return 0.0f;
+    if (L.area == 0.0f) return 0.0f;
+    const float nl = clampf(dot(V3{L.normal[0], L.normal[1], L.normal[2]}, omega), 0.0f, 1.0f);
+    if (nl == 0.0f) return 0.0f;
+    return norm2(p - sf.point) / (L.area * nl);
+}
+constexpr uint32_t kMaxMisSamples = 16; // lights x light_samples the MIS estimator keeps per hit (refused beyond)
+// MultipleImportanceSampling::get_direct_lighting (sampler/mis.rs:41-72) + BrdfSampler::sample_direct (brdf.rs:48-66)
+template <int MODE, bool COUNT>
+__device__ __noinline__ Col mis_general(const RenderParams& P, const Surf& sf, uint32_t pixel, uint32_t sample, uint32_t depth,
+                                        PixelCounters& pc) {
     const GpuSceneView& s = P.scene;
     const uint32_t ls = P.cfg.light_samples;
-    const uint32_t strate = P.cfg.light_stratify ? __float2uint_rz(sqrtf((float)ls)) : 1u; // config.rs:73-79
-    const float fstrate = (float)strate;
-    Col ret{0.0f, 0.0f, 0.0f, 1.0f};
-    for (uint32_t li = 0; li < s.light_count; ++li) {
-        const GpuLight& L = s.lights[li];
+    V3 omegas[kMaxMisSamples];
+    Col xs[kMaxMisSamples];
+    uint32_t n = 0;
+    for (uint32_t li = 0; li < s.light_count; ++li)
 #pragma unroll 1
-        for (uint32_t i = 0; i < ls; ++i) {
-            Col xs{0.0f, 0.0f, 0.0f, 1.0f};
-            if (L.kind == RAYCA_LIGHT_QUAD) {
-                const V3 ab{L.ab[0], L.ab[1], L.ab[2]}, ac{L.ac[0], L.ac[1], L.ac[2]}, qn{L.normal[0], L.normal[1], L.normal[2]};
-                const uint32_t dim = 3u * ls + 2u * (li * ls + i);
-                const float u1 = rng_f32(P.seed, pixel, sample, depth, dim) / fstrate;
-                const float u2 = rng_f32(P.seed, pixel, sample, depth, dim + 1u) / fstrate;
-                V3 x1 = (quad_corner(L, 0) + u1 * ab) + u2 * ac;
-                if (P.cfg.light_stratify) x1 = x1 + ((ab / fstrate) * (float)(i % strate) + (ac / fstrate) * (float)(i / strate));
-                const V3 to_x1 = x1 - sf.point;
-                const V3 omega = normalize(to_x1);
-                const RayD shadow = make_ray(sf.next_origin, omega);
-                HitD sh;
-                pc.shadow++;
-                if (trace_ray<MODE, false, COUNT>(s, shadow, sh, &pc.walk)) { // counts only when the closest hit is a light
-                    const GpuMaterial* sm = s.materials + __float_as_uint(__ldg(s.tri_attr + 12 * (size_t)sh.prim + 9).w);
-                    if (sm->kind == RAYCA_MATERIAL_PHONG && sm->emissive) {
-                        const Col le = cscale(Col{L.color[0], L.color[1], L.color[2], L.color[3]}, L.intensity);
-                        const Col brdf = surf_brdf(s, sf, omega);
-                        const float d_omega = dot(qn, omega) / norm2(to_x1);
-                        const float n_dot = fminf(fmaxf(dot(sf.normal, omega), 0.0f), 1.0f);
-                        xs = cscale(cscale(cmul(cscale(le, L.area), brdf), n_dot), d_omega);
-                    }
-                }
-            } else { // point light (nee.rs:95-137)
-                const V3 to_x1 = V3{L.pos[0], L.pos[1], L.pos[2]} - sf.point;
-                const float dist = length(to_x1);
-                const V3 omega = normalize(to_x1);
-                const RayD shadow = make_ray(sf.next_origin, omega);
-                HitD sh;
-                pc.shadow++;
-                bool occluded = false;
-                if (trace_ray<MODE, false, COUNT>(s, shadow, sh, &pc.walk)) occluded = sh.t < dist;
-                if (!occluded) {
-                    const Col le = point_intensity(L, sf.point);
-                    const Col brdf = surf_brdf(s, sf, omega);
-                    const float d_omega = 1.0f / norm2(to_x1);
-                    const float n_dot = fminf(fmaxf(dot(sf.normal, omega), 0.0f), 1.0f);
-                    xs = cscale(cscale(cmul(le, brdf), n_dot), d_omega);
-                }
-            }
-            ret = cadd(ret, xs);
+        for (uint32_t i = 0; i < ls && n < kMaxMisSamples; ++i, ++n) xs[n] = nee_sample<MODE, COUNT>(P, sf, li, i, pixel, sample, depth, pc, omegas[n]);
+    const V3 omega_b = material_dir(s, sf, rng_f32(P.seed, pixel, sample, depth, 0x20000u), rng_f32(P.seed, pixel, sample, depth, 0x20001u),
+                                    rng_f32(P.seed, pixel, sample, depth, 0x20002u));
+    const float pdf_b = material_pdf(s, sf, omega_b);
+    Col x_b{0.0f, 0.0f, 0.0f, 1.0f};
+    {
+        const RayD shadow = make_ray(sf.next_origin, omega_b);
+        HitD sh;
+        pc.shadow++;
+        if (trace_ray<MODE, false, COUNT>(s, shadow, sh, &pc.walk)) {
+            const GpuMaterial* sm = s.materials + __float_as_uint(__ldg(s.tri_attr + 12 * (size_t)sh.prim + 9).w);
+            if (sm->kind == RAYCA_MATERIAL_PHONG && sm->emissive)
+                x_b = cmul(ld_col(sm->b), cadd(surf_diffuse(s, sf), surf_specular_component(s, sf, omega_b)));
         }
+    }
+    Col ret{0.0f, 0.0f, 0.0f, 1.0f};
+#pragma unroll 1
+    for (uint32_t k = 0; k <= n; ++k) { // k == n: the Brdf sample
+        const V3 omega = k < n ? omegas[k] : omega_b;
+        float pdf_nee = 0.0f;
+        for (uint32_t li = 0; li < s.light_count; ++li) {
+            const float pl = nee_pdf(s.lights[li], sf, omega);
+            for (uint32_t i = 0; i < ls; ++i) pdf_nee += pl; // get_pdf_nee sums one term per light SAMPLE
+        }
+        pdf_nee = pdf_nee / (float)n;
+        const float pdf_brdf = k < n ? material_pdf(s, sf, omega) : pdf_b;
+        const float den = pdf_nee * pdf_nee + pdf_brdf * pdf_brdf;
+        const float num = k < n ? pdf_nee * pdf_nee : pdf_brdf * pdf_brdf;
+        const float w = den == 0.0f ? 0.0f : num / den;
+        ret = cadd(ret, cscale(k < n ? xs[k] : x_b, w));
     }
     return ret;
 }
@@ -508,7 +597,8 @@ template <int MODE, bool COUNT>
 __device__ __noinline__ bool pathtracer_general(const RenderParams& P, RayD ray, uint32_t pixel, uint32_t sample, Col& out,
                                                 HitD& primary, PixelCounters& pc) {
     const GpuSceneView& s = P.scene;
-    const bool nee = P.cfg.direct_sampler == RAYCA_SAMPLER_NEE;
+    const bool mis = P.cfg.direct_sampler == RAYCA_SAMPLER_MIS;
+    const bool nee = P.cfg.direct_sampler == RAYCA_SAMPLER_NEE || mis; // "a direct sampler is set" (pathtracer.rs:86-90)
     const bool rr = P.cfg.russian_roulette != 0;
     const bool hemisphere = P.cfg.indirect_sampler == RAYCA_SAMPLER_HEMISPHERE;
     const bool brdf_sampler = P.cfg.indirect_sampler == RAYCA_SAMPLER_BRDF;
@@ -532,7 +622,8 @@ __device__ __noinline__ bool pathtracer_general(const RenderParams& P, RayD ray,
             sum = cadd(sum, cmul(factor, surf_color(s, sf)));
             break;
         }
-        if (nee) sum = cadd(sum, cmul(factor, nee_general<MODE, COUNT>(P, sf, pixel, sample, depth, pc)));
+        if (mis) sum = cadd(sum, cmul(factor, mis_general<MODE, COUNT>(P, sf, pixel, sample, depth, pc)));
+        else if (nee) sum = cadd(sum, cmul(factor, nee_general<MODE, COUNT>(P, sf, pixel, sample, depth, pc)));
         if (!(rr || depth < limit)) break;
         V3 wi;
         if (brdf_sampler) // sampler/brdf.rs:70-73; lobe choice at dimension 0x10000 (oracle: dim_lobe)

@@ -178,12 +178,16 @@ SCENES = {
                                         "pt_rr": (dict(PTC, direct_sampler=SamplerStrategy.Nee, russian_roulette=True, max_depth=16), 48, 48),
                                         "pt_brdf_rr": (dict(PTC, direct_sampler=SamplerStrategy.Nee, indirect_sampler=SamplerStrategy.Brdf,
                                                             russian_roulette=True, max_depth=16), 40, 40),
+                                        "pt_mis_rr": (dict(PTC, direct_sampler=SamplerStrategy.Mis, indirect_sampler=SamplerStrategy.Brdf,
+                                                           russian_roulette=True, max_depth=16), 40, 40),
                                         "pt_cosine_rr": (dict(PTC, direct_sampler=SamplerStrategy.Nee, indirect_sampler=SamplerStrategy.Cosine,
                                                               russian_roulette=True, max_depth=16), 40, 40)}),
     # sdtf/4/ggx.sdtf: spheres with Phong and GGX materials of growing roughness under the Brdf sampler (its own settings,
     # 2 spp instead of 64; russian roulette as the file asks, which Config::apply drops: both variants)
     "ggx": ("sdtf/4/ggx.sdtf", {"brdf": (dict(samples_per_pixel=2), 160, 35),
                                 "brdf_rr": (dict(samples_per_pixel=2, russian_roulette=True), 160, 35)}),
+    # sdtf/4/mis.sdtf: glossy plates under four quad lights, multiple importance sampling, its own settings at 2 spp
+    "mis": ("sdtf/4/mis.sdtf", {"sdtf": (dict(samples_per_pixel=2), 96, 64)}),
     "quadsphere": ("sdtf/2/sphere.sdtf", {"sdtf": (None, 120, 90)}),
     "dragon": ("sdtf/2/dragon.sdtf", {"ls4": (dict(light_samples=4), 48, 36)}),  # 100,002 triangles + 2 quad lights
 }

@@ -77,7 +77,9 @@ def test_cuda_matches_golden(ctx, scene, case, traversal):
         if traversal != R.TRAVERSAL_ORDERED and e.code == -2 and "triangle scenes only" in str(e):
             pytest.skip("the reference-tree walks are triangle-only; sphere scenes run on the product walk")
         raise
-    stochastic = cfg.integrator == R.IntegratorStrategy.Pathtracer and cfg.max_depth > 1
+    # directions built with acosf / cosf / sinf (bounces, the Brdf sample of Mis) differ from glibc's by ulps
+    stochastic = cfg.integrator == R.IntegratorStrategy.Pathtracer and (
+        cfg.max_depth > 1 or cfg.russian_roulette or cfg.direct_sampler == R.SamplerStrategy.Mis)
     check_against(z, rgba8, aux, h, w, stochastic)
     rays = [int(x) for x in z["rays"]]
     assert st.rays_primary == rays[0]
@@ -151,7 +153,7 @@ def test_draw_trait_mirror(ctx, cuda_lib):
 def test_unsupported_and_error_paths(ctx):
     sc = dev_scene(ctx, "box")
     for cfg in (R.Config(direct_sampler=R.SamplerStrategy.Mis), R.Config(indirect_sampler=R.SamplerStrategy.Brdf),
-                R.Config(light_samples=4)):  # Mis / Brdf samplers and branching bounces are later rows
+                R.Config(light_samples=4)):  # Mis / Brdf need Phong or GGX materials (box.gltf is PBR); branching bounces
         with pytest.raises(R.RaycaError) as e:
             sc.render(cfg, 16, 16)
         assert e.value.code == -2
@@ -417,8 +419,8 @@ def test_device_built_reference_blas_equals_host_built(ctx):
 
 def test_cornell_estimators_agree_in_the_mean(ctx):
     """sdtf/3 + sdtf/4 settings at the files' own 480x480: hemisphere and cosine bounces, with and without next event
-    estimation on the quad light, with and without russian roulette are estimators of the same image, so their
-    mean radiance must agree (64 spp: within 3 %)."""
+    estimation on the quad light, with and without russian roulette, the Brdf sampler and multiple importance
+    sampling are estimators of the same image, so their mean radiance must agree (64 spp: within 3 %)."""
     sc = dev_scene(ctx, "cornell")
     P, S = R.IntegratorStrategy.Pathtracer, R.SamplerStrategy
     base = dict(integrator=P, max_depth=16, samples_per_pixel=64, light_samples=1, light_stratify=False)
@@ -426,7 +428,9 @@ def test_cornell_estimators_agree_in_the_mean(ctx):
     for name, kw in {"hemisphere": dict(direct_sampler=S.NONE, indirect_sampler=S.Hemisphere),
                      "cosine": dict(direct_sampler=S.NONE, indirect_sampler=S.Cosine),
                      "nee": dict(direct_sampler=S.Nee, indirect_sampler=S.Hemisphere),
-                     "nee+rr": dict(direct_sampler=S.Nee, indirect_sampler=S.Cosine, russian_roulette=True)}.items():
+                     "nee+rr": dict(direct_sampler=S.Nee, indirect_sampler=S.Cosine, russian_roulette=True),
+                     "nee+brdf+rr": dict(direct_sampler=S.Nee, indirect_sampler=S.Brdf, russian_roulette=True),
+                     "mis+brdf+rr": dict(direct_sampler=S.Mis, indirect_sampler=S.Brdf, russian_roulette=True)}.items():
         _, aux, st = sc.render(R.Config(**base, **kw), 480, 480, want_aux=True)
         rgb = aux.rgba_f32.reshape(480, 480, 4)[..., :3]
         assert np.isfinite(rgb).all()
