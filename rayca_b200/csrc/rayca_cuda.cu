@@ -779,29 +779,48 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
         if (aux->rgba_f32) d.rgba_f32 = (float*)p;
     }
     // Row bands: the kernel of band k+1 runs while band k is copied to the host on the side stream, so
-    // the PCIe read-back of the frame hides behind the trace instead of following it.  A caller buffer
+    // the PCIe read-back of the frame hides behind the trace instead of following it.  Bands shrink towards the
+    // end of the frame: only the last copy is exposed.  A caller buffer
     // from rayca_cuda_host_alloc (pinned) makes the copies truly asynchronous; pageable memory still
     // works (the runtime stages it) but serialises the copies on the calling thread.
     rayca_stats local{};
     const uint32_t nb_max = (uint32_t)(sizeof(ctx->band_done) / sizeof(ctx->band_done[0]));
-    uint32_t nb = height >= 512 ? 4 : (height >= 128 ? 2 : 1);
+    // measured on B200, 1080p atrium, pinned output (tools/band_ab.py): 1 band 1.086 ms, 4 equal bands 1.095 (every
+    // launch adds its own tail), 3 tapered bands 1.010, 4 tapered 1.028, 8 tapered 1.165
+    uint32_t nb = height >= 512 ? 3 : (height >= 128 ? 2 : 1);
+    bool taper = true;
+    if (const char* e = std::getenv("RAYCA_BANDS")) nb = (uint32_t)std::max(1, std::atoi(e)); // A/B runs
+    if (const char* e = std::getenv("RAYCA_BAND_TAPER")) taper = std::atoi(e) != 0;
     if (nb > nb_max) nb = nb_max;
-    const uint32_t band_rows = (((height + nb - 1) / nb) + 7) & ~7u;
+    // band k covers rows [edge[k], edge[k+1]), multiples of 8; tapered: heights proportional to nb - k, so that the
+    // last copy (the only one nothing hides) is short
+    uint32_t edge[9] = {0};
+    {
+        const uint32_t total_w = taper ? nb * (nb + 1) / 2 : nb;
+        uint32_t acc_w = 0;
+        for (uint32_t k = 0; k < nb; ++k) {
+            acc_w += taper ? nb - k : 1;
+            uint32_t y = (uint32_t)(((uint64_t)height * acc_w + total_w - 1) / total_w);
+            y = (y + 7) & ~7u;
+            edge[k + 1] = std::min(height, std::max(y, edge[k]));
+        }
+        edge[nb] = height;
+    }
     double t0 = now_ms();
     int rc = RAYCA_OK;
     uint32_t launched = 0;
+    uint32_t band_of[8] = {0};
     for (uint32_t k = 0; k < nb; ++k) {
-        Band bd{k * band_rows, std::min(height, (k + 1) * band_rows), k == 0, false};
-        if (bd.row_begin >= height) break;
-        bd.last = bd.row_end == height;
+        if (edge[k] >= edge[k + 1]) continue;
+        Band bd{edge[k], edge[k + 1], launched == 0, edge[k + 1] == height};
         rc = enqueue_render(ctx, scene, config, options, width, height, base, aux ? &d : nullptr, ctx->render_stream, &bd, &local);
         if (rc != RAYCA_OK) return rc;
-        CUDA_TRY(cudaEventRecord(ctx->band_done[k], ctx->render_stream));
-        ++launched;
+        CUDA_TRY(cudaEventRecord(ctx->band_done[launched], ctx->render_stream));
+        band_of[launched++] = k;
     }
-    for (uint32_t k = 0; k < launched; ++k) {
-        const size_t y0 = (size_t)k * band_rows, y1 = std::min<size_t>(height, (size_t)(k + 1) * band_rows);
-        CUDA_TRY(cudaStreamWaitEvent(ctx->copy_stream, ctx->band_done[k], 0));
+    for (uint32_t j = 0; j < launched; ++j) {
+        const size_t y0 = edge[band_of[j]], y1 = edge[band_of[j] + 1];
+        CUDA_TRY(cudaStreamWaitEvent(ctx->copy_stream, ctx->band_done[j], 0));
         CUDA_TRY(cudaMemcpyAsync(rgba8_out + y0 * width * 4, base + y0 * width * 4, (y1 - y0) * width * 4, cudaMemcpyDeviceToHost,
                                  ctx->copy_stream));
     }

@@ -257,7 +257,7 @@ def test_host_render_bands_equal_single_launch(ctx, atrium):
     torch.cuda.synchronize()
     one = buf.cpu().numpy()
     assert np.array_equal(img.buffer, one) and np.array_equal(pageable, one)
-    assert st.rays_primary == w * h and st.kernel_launches == 4
+    assert st.rays_primary == w * h and st.kernel_launches == 3
     c = atrium.last_counters()
     assert c.rays_primary == w * h and c.rays_shadow == st.rays_shadow
 
