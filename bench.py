@@ -86,7 +86,30 @@ class ClockSampler(threading.Thread):
         self.samples = []
         self.stop = threading.Event()
 
+    def run_nvml(self):
+        """In-process NVML polling (every 2 ms): a 20-step timed region lasts tens of milliseconds, which one
+        nvidia-smi process per sample cannot resolve."""
+        import pynvml as N
+
+        N.nvmlInit()
+        h = N.nvmlDeviceGetHandleByIndex(self.dev)
+        mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
+        get_reasons = getattr(N, "nvmlDeviceGetCurrentClocksEventReasons", None) or N.nvmlDeviceGetCurrentClocksThrottleReasons
+        bits = ((0x8, 5), (0x40, 6), (0x20, 7), (0x4, 8))  # hw_slowdown, hw_thermal, sw_thermal, sw_power_cap
+        while not self.stop.is_set():
+            r = int(get_reasons(h))
+            f = [str(self.dev), str(N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)), str(mx), "", hex(r), "", "", "", ""]
+            for bit, slot in bits:
+                f[slot] = "Active" if r & bit else "Not Active"
+            self.samples.append(f)
+            self.stop.wait(0.002)
+
     def run(self):
+        try:
+            self.run_nvml()
+            return
+        except Exception:
+            pass
         while not self.stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
@@ -308,6 +331,7 @@ def run_ours(args):
     # block (camera, config, pointers); the scene was uploaded once by scene_create, which the
     # reference's own timer excludes too (scene.rs:101,152).
     param_bytes = 1024
+    frame_crc = None
     n_e2e = max(3, args.steps)
     draw_e2e = None
     if G == 1:
@@ -320,6 +344,16 @@ def run_ours(args):
             dev.render(cfg, W, H, out=img.buffer, options=opts)
         e2e_s = (time.perf_counter() - t1) / n_e2e
         d2h = W * H * 4
+        import zlib
+
+        frame_crc = zlib.crc32(np.ascontiguousarray(img.buffer).tobytes())  # A/B runs: same pixels, byte for byte
+        ab_ref = os.environ.get("RAYCA_AB_FRAME")  # tools/ab2.sh: the first variant saves its frame, the others diff against it
+        if ab_ref:
+            if os.path.exists(ab_ref):
+                dq = np.abs(np.load(ab_ref).astype(np.int16) - img.buffer.astype(np.int16))
+                frame_crc = f"{frame_crc} maxdiff_u8={int(dq.max())} differing_bytes={int((dq > 0).sum())}"
+            else:
+                np.save(ab_ref, np.ascontiguousarray(img.buffer))
         e2e_what = "rayca_cuda_render: pinned host RGBA8 out, scene resident (scene_create excluded, like the reference timer)"
     else:
         srcs = [torch.as_tensor(f, device="cuda") for f in frames] if (peer and rank == 0) else [gathered]
@@ -394,7 +428,7 @@ def run_ours(args):
         # DRAM bytes of one launch from the committed `ncu --set full` capture of this command (None for other workloads)
         traffic = None
         try:
-            prof = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_render_kernel_v3.json")))
+            prof = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_render_kernel_v4.json")))
             if args.workload == "atrium" and (W, H, args.spp, args.max_depth, G) == (1920, 1080, 1, 1, 1):
                 traffic = prof["dram_bytes_per_launch"]
         except Exception:
@@ -417,7 +451,7 @@ def run_ours(args):
                                      "vertices are fetched (counted by the kernel in a COUNT launch) + 4 B per pixel; the "
                                      "262k-triangle scene is L2/L1-resident, so this can exceed the HBM peak: the kernel is "
                                      "issue-bound, see profiles/"},
-                "e2e": e2e, "draw_e2e": draw_e2e,
+                "e2e": e2e, "draw_e2e": draw_e2e, "frame_crc32": frame_crc,
                 "walk": {"node_records_per_ray": cst.node_bytes / 32 / max(rays_local_n, 1),
                          "triangle_bytes_per_ray": cst.triangle_bytes / max(rays_local_n, 1),
                          "algorithmic_bytes_per_ray": algo_bytes / max(rays_local_n, 1)}}

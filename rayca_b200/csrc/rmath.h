@@ -62,7 +62,13 @@ RHD V3 cross(V3 a, V3 b) {
 RHD float norm2(V3 a) { return dot(a, a); }
 RHD float length(V3 a) { return sqrtf(dot(a, a)); }
 // vec3.rs:183-188 — no-op when len <= EPS
+#if defined(__CUDACC__)
+// one out-of-line copy: three IEEE divisions and a square root are ~50 SASS instructions, and the kernel
+// inlines some twenty normalisations into straight-line shading code that already starves on instruction fetch
+__host__ __device__ __noinline__ inline V3 normalize(V3 a) {
+#else
 RHD V3 normalize(V3 a) {
+#endif
     float l = length(a);
     if (l > kEps) return V3{a.x / l, a.y / l, a.z / l};
     return a;

@@ -205,7 +205,7 @@ __device__ __forceinline__ bool walk(const GpuSceneView& s, const RayD& ray, Hit
 //     REORDERED: plane distance first (16 bytes), then `t > best` rejects before the edge functions
 //     — a hit with t > best would be discarded anyway.
 //
-// Instruction budget (this loop is issue-bound, profiles/): per box 6 SEL + 6 FFMA + 2 FMNMX3 + 2 FFMA.
+// Instruction budget (this loop is issue-bound, profiles/): per box 6 LOP3 + 6 FFMA + 2 FMNMX3 + 2 FFMA.
 //   exact      t  = RN(RN(p - o) * rd)                         (aabb.rs:76-80)
 //   here       t' = RN(fma(p, rd, a)),  a = RN(-o*rd) -/+ e,   e = 2^-22 |o*rd| per axis
 //   |t - t'| <= u|o*rd| + 3u|t| with u = 2^-24; e = 4u|o*rd| covers the first term (and the rounding of
@@ -222,8 +222,12 @@ struct FastRay {
     float rdx, rdy, rdz;
     float anx, any, anz; // near-plane addend  RN(-o*rd) - e
     float afx, afy, afz; // far-plane addend   RN(-o*rd) + e
-    bool sx, sy, sz;     // rd < 0: the near plane is the box maximum
+    uint32_t sx, sy, sz; // rd < 0 ? ~0 : 0 — near/far planes are picked with one LOP3 each (FSEL would need the
+                         // three sign predicates, which the compiler re-derives with 3 FSETP on every visit)
 };
+__device__ __forceinline__ float pick(uint32_t m, float a, float b) { // m ? a : b on the bit patterns
+    return __uint_as_float((__float_as_uint(a) & m) | (__float_as_uint(b) & ~m));
+}
 
 __device__ __forceinline__ FastRay make_fast_ray(const RayD& r) {
     FastRay f;
@@ -233,16 +237,20 @@ __device__ __forceinline__ FastRay make_fast_ray(const RayD& r) {
                 ez = fabsf(nz) * 2.384185791015625e-07f; // 2^-22
     f.anx = nx - ex; f.any = ny - ey; f.anz = nz - ez;
     f.afx = nx + ex; f.afy = ny + ey; f.afz = nz + ez;
-    f.sx = r.rd.x < 0.0f; f.sy = r.rd.y < 0.0f; f.sz = r.rd.z < 0.0f;
+    // sign bit smeared over the word; asm keeps the compiler from turning the masks back into predicates + FSEL
+    // (rd is never +-0 in the walk: zero-direction rays skip it, see walk_fast_body)
+    asm("shr.s32 %0, %1, 31;" : "=r"(f.sx) : "r"(__float_as_int(r.rd.x)));
+    asm("shr.s32 %0, %1, 31;" : "=r"(f.sy) : "r"(__float_as_int(r.rd.y)));
+    asm("shr.s32 %0, %1, 31;" : "=r"(f.sz) : "r"(__float_as_int(r.rd.z)));
     return f;
 }
 
 // returns "may intersect"; entry <= the exact slab entry distance of the same box
 __device__ __forceinline__ bool slab_fast(const float4 lo, const float4 hi, const FastRay& f, float& entry) {
-    const float tn = fmaxf(fmaxf(__fmaf_rn(f.sx ? hi.x : lo.x, f.rdx, f.anx), __fmaf_rn(f.sy ? hi.y : lo.y, f.rdy, f.any)),
-                           __fmaf_rn(f.sz ? hi.z : lo.z, f.rdz, f.anz));
-    const float tf = fminf(fminf(__fmaf_rn(f.sx ? lo.x : hi.x, f.rdx, f.afx), __fmaf_rn(f.sy ? lo.y : hi.y, f.rdy, f.afy)),
-                           __fmaf_rn(f.sz ? lo.z : hi.z, f.rdz, f.afz));
+    const float tn = fmaxf(fmaxf(__fmaf_rn(pick(f.sx, hi.x, lo.x), f.rdx, f.anx), __fmaf_rn(pick(f.sy, hi.y, lo.y), f.rdy, f.any)),
+                           __fmaf_rn(pick(f.sz, hi.z, lo.z), f.rdz, f.anz));
+    const float tf = fminf(fminf(__fmaf_rn(pick(f.sx, lo.x, hi.x), f.rdx, f.afx), __fmaf_rn(pick(f.sy, lo.y, hi.y), f.rdy, f.afy)),
+                           __fmaf_rn(pick(f.sz, lo.z, hi.z), f.rdz, f.afz));
     entry = __fmaf_rn(fabsf(tn), -kSlabTol, tn);
     const float ext = __fmaf_rn(fabsf(tf), kSlabTol, tf);
     return ext >= entry && ext >= 0.0f;
@@ -283,7 +291,14 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
     // A ray with an exactly-zero direction lane has rdir = 0 there (vec3.rs:195-216): both slab
     // distances of that axis are 0, tmax <= 0, and `tmax > 0.0` (aabb.rs:88) rejects EVERY box, the
     // TLAS root included — the reference returns a miss for such rays (SURVEY A-3).
-    if (ray.rd.x == 0.0f || ray.rd.y == 0.0f || ray.rd.z == 0.0f) return finish();
+    //
+    // Control flow is kept STRUCTURED — no return from inside the loops, one break target per loop, an
+    // empty stack shows up as the sentinel reference kDone popped from slot 0 — so that, inlined into
+    // a caller's loop, the compiler still brackets the inner node loop and the leaf loop with convergence
+    // barriers (a first inlined version with early returns lost them: lanes that left the node loop for
+    // a leaf never rejoined the others, 0.90 -> 1.43 ms on the 1080p atrium frame).
+    bool found = false; // ANY: an accepted hit below hit.t exists
+    bool go = !(ray.rd.x == 0.0f || ray.rd.y == 0.0f || ray.rd.z == 0.0f);
 
     const float4* __restrict__ fast_nodes = s.fast_nodes;
     const float4* __restrict__ fast_tri = s.fast_tri;
@@ -299,20 +314,35 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
         ok_leaf = leaf;
         return true;
     };
-    {
+    if (go) {
         if (COUNT) wc->nodes += 1;
         float4 lo = make_float4(s.fast_root_min[0], s.fast_root_min[1], s.fast_root_min[2], 0.0f);
         float4 hi = make_float4(s.fast_root_max[0], s.fast_root_max[1], s.fast_root_max[2], 0.0f);
         float e;
-        if (!slab_fast(lo, hi, fr, e)) return finish();
+        go = slab_fast(lo, hi, fr, e);
     }
-    uint2 stack[kStackSize]; // {child reference, entry distance}
-    int sp = 0;
-    uint32_t cur = s.fast_root_ref;
+    constexpr uint32_t kDone = 0xFFFFFFFFu; // leaf flag set: leaves the node loop like any leaf reference
+    // {child reference, entry distance}; slot 0 holds the sentinel (distance -inf is never culled), the last
+    // slot absorbs pushes beyond kStackSize entries (the count saturates, as before those are dropped)
+    uint2 stack[kStackSize + 2];
+    stack[0] = make_uint2(kDone, 0xff800000u);
+    int sp = 1;
+    uint32_t cur = go ? s.fast_root_ref : kDone;
+    auto push = [&](uint32_t ref, float dist) {
+        stack[sp] = make_uint2(ref, __float_as_uint(dist)); // unguarded store, saturating count
+        sp = min(sp + 1, kStackSize + 1);
+    };
+    auto pop = [&]() -> uint32_t { // next entry whose entry distance does not exceed the best depth
+        uint2 e;
+        do {
+            e = stack[--sp];
+        } while (__uint_as_float(e.y) > best_t);
+        return e.x;
+    };
     for (;;) {
         // inner nodes: descend to the nearer accepted child, push the farther one
         while (!(cur & kLeafFlag)) {
-            const float4* np = fast_nodes + 2 * (size_t)cur;
+            const float4* np = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(fast_nodes) + (unsigned long long)cur * 32ull);
             const float4 a0 = __ldg(np + 0), a1 = __ldg(np + 1), b0 = __ldg(np + 2), b1 = __ldg(np + 3);
             if (COUNT) wc->nodes += 2;
             float d0, d1;
@@ -327,31 +357,24 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
                     uint32_t tc = c0; c0 = c1; c1 = tc;
                 }
                 cur = c0;
-                if (sp < kStackSize) stack[sp++] = make_uint2(c1, __float_as_uint(d1));
+                push(c1, d1);
             } else if (h0) {
                 cur = c0;
             } else if (h1) {
                 cur = c1;
             } else {
-                bool popped = false;
-                while (sp > 0) {
-                    const uint2 e = stack[--sp];
-                    if (__uint_as_float(e.y) > best_t) continue;
-                    cur = e.x;
-                    popped = true;
-                    break;
-                }
-                if (!popped) return finish();
+                cur = pop();
             }
         }
+        if (cur == kDone) break;
         // leaf: Triangle::intersects (rayca-geometry/src/triangle.rs:84-159) on the 64-byte records
         // {n.xyz, d | v0, ref index | v1, ref leaf | v2, dot(n,n)}
+        const uint32_t first = cur & 0x07FFFFFFu, count = ((cur >> 28) & 7u) + 1u;
         if (SPHERES && (cur & kSphereFlag)) {
             // Sphere::intersects (rayca-geometry/src/sphere.rs:101-163) on the 64-byte records
             // {-t, r^2 | q^-1 | 1/s, ref index | centre, ref leaf}: the ray goes to model space by translate,
             // rotate, scale (trs.rs:405-414 with ray.rs:74-91), then the geometric quadratic
-            const uint32_t first = cur & 0x07FFFFFFu, count = ((cur >> 28) & 7u) + 1u;
-            for (uint32_t i = first; i < first + count; ++i) {
+            for (uint32_t i = first; i < first + count && !found; ++i) {
                 const float4* q = fast_tri + 4 * (size_t)i;
                 const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
                 if (COUNT) { wc->planes += 1; wc->tris += 1; }
@@ -375,7 +398,7 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
                 else t = t1;
                 const uint32_t id = __float_as_uint(q2.w);
                 if (ANY) {
-                    if (t < best_t && ref_leaf_accepts(__float_as_uint(q3.w))) return true;
+                    if (t < best_t && ref_leaf_accepts(__float_as_uint(q3.w))) found = true;
                 } else if (t < best_t || (t == best_t && id < best && best != 0xFFFFFFFFu)) {
                     if (ref_leaf_accepts(__float_as_uint(q3.w))) {
                         best_t = t;
@@ -388,8 +411,7 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
                 }
             }
         } else {
-            const uint32_t first = cur & 0x07FFFFFFu, count = ((cur >> 28) & 7u) + 1u;
-            for (uint32_t i = first; i < first + count; ++i) {
+            for (uint32_t i = first; i < first + count && !found; ++i) {
                 const float4* q = fast_tri + 4 * (size_t)i;
                 const float4 q0 = __ldg(q);
                 if (COUNT) wc->planes += 1;
@@ -414,7 +436,7 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
                 if (v < 0.0f) continue;
                 const uint32_t id = __float_as_uint(q1.w);
                 if (ANY) {
-                    if (ref_leaf_accepts(__float_as_uint(q2.w))) return true;
+                    if (ref_leaf_accepts(__float_as_uint(q2.w))) found = true;
                 } else if (t < best_t || (id < best && best != 0xFFFFFFFFu)) { // here t <= best_t
                     if (ref_leaf_accepts(__float_as_uint(q2.w))) {
                         best_t = t;
@@ -427,16 +449,11 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
                 }
             }
         }
-        bool popped = false;
-        while (sp > 0) {
-            const uint2 e = stack[--sp];
-            if (__uint_as_float(e.y) > best_t) continue;
-            cur = e.x;
-            popped = true;
-            break;
-        }
-        if (!popped) return finish();
+        if (found) break;
+        cur = pop();
     }
+    if (found) return true;
+    return finish();
 }
 
 // One shared copy of the walk serves closest-hit and any-hit queries of every call site: the kernel

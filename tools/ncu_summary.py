@@ -36,6 +36,13 @@ def main():
                 d[h] = f"{vals[i]} {units[i]}".strip()
         res.append(d)
     doc = {"report": rep.split("/")[-1], "note": sys.argv[3] if len(sys.argv) > 3 else "", "launches": res}
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    try:  # dram__bytes_read.sum + dram__bytes_write.sum of the first launch: bench.py's roofline.traffic
+        first = res[0]
+        doc["dram_bytes_per_launch"] = int(sum(float(first[k].split()[0]) * scale[first[k].split()[1]]
+                                               for k in ("dram__bytes_read.sum", "dram__bytes_write.sum")))
+    except Exception:
+        pass
     print(json.dumps(doc, indent=1))
     if len(sys.argv) > 2 and sys.argv[2] != "-":
         json.dump(doc, open(sys.argv[2], "w"), indent=1)

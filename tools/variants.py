@@ -22,6 +22,6 @@ def one(spec):
 
 
 if __name__ == "__main__":
-    with ThreadPoolExecutor(max_workers=4) as ex:
+    with ThreadPoolExecutor(max_workers=6) as ex:
         for o in ex.map(one, sys.argv[1:]):
             print(o)
