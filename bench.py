@@ -85,9 +85,10 @@ class ClockSampler(threading.Thread):
         self.dev = device_index
         self.samples = []
         self.stop = threading.Event()
+        self.ready = threading.Event()  # set once the first sample is in: the caller starts timing after that
 
     def run_nvml(self):
-        """In-process NVML polling (every 2 ms): a 20-step timed region lasts tens of milliseconds, which one
+        """In-process NVML polling (every 0.5 ms): a 20-step timed region lasts tens of milliseconds, which one
         nvidia-smi process per sample cannot resolve."""
         import pynvml as N
 
@@ -96,13 +97,16 @@ class ClockSampler(threading.Thread):
         mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
         get_reasons = getattr(N, "nvmlDeviceGetCurrentClocksEventReasons", None) or N.nvmlDeviceGetCurrentClocksThrottleReasons
         bits = ((0x8, 5), (0x40, 6), (0x20, 7), (0x4, 8))  # hw_slowdown, hw_thermal, sw_thermal, sw_power_cap
-        while not self.stop.is_set():
+        last = False
+        while not last:  # one more sample after stop: a timed region of a few milliseconds still gets its closing sample
+            last = self.stop.is_set()
             r = int(get_reasons(h))
             f = [str(self.dev), str(N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)), str(mx), "", hex(r), "", "", "", ""]
             for bit, slot in bits:
                 f[slot] = "Active" if r & bit else "Not Active"
             self.samples.append(f)
-            self.stop.wait(0.002)
+            self.ready.set()
+            self.stop.wait(0.0005)
 
     def run(self):
         try:
@@ -117,6 +121,7 @@ class ClockSampler(threading.Thread):
                 f = [x.strip() for x in out.strip().split(",")]
                 if len(f) >= 9:
                     self.samples.append(f)
+                    self.ready.set()
             except Exception:
                 pass
             self.stop.wait(0.1)
@@ -301,9 +306,11 @@ def run_ours(args):
 
     sampler = ClockSampler(local_rank)
     sampler.start()
+    sampler.ready.wait(5.0)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
+    del sampler.samples[:]  # keep the samples taken from here on: under load
     for k in range(args.steps):
         flush.fill_(k & 0xFF)  # L2 flush between timed iterations (outside the timed events)
         ev[k][0].record()

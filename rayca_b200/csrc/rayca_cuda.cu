@@ -115,7 +115,10 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
                 for (size_t k = 1; k < sc.host.materials.size(); ++k) pbr = pbr || sc.host.materials[k].kind == RAYCA_MATERIAL_PBR;
                 if (pbr) return fail(RAYCA_E_UNSUPPORTED, "the Brdf / Mis samplers need Phong / GGX materials");
             }
-            if (bounces && c.light_samples != 1) return fail(RAYCA_E_UNSUPPORTED, "light_samples > 1 with indirect bounces");
+            if (bounces && c.light_samples != 1) { // a tree of light_samples^depth paths per sample (pathtracer_branching)
+                if (c.russian_roulette) return fail(RAYCA_E_UNSUPPORTED, "light_samples > 1 with russian roulette");
+                if (c.max_depth > (uint32_t)kMaxBranchDepth) return fail(RAYCA_E_UNSUPPORTED, "light_samples > 1 with max_depth > 8");
+            }
             if (nee)
                 for (const GpuLight& l : sc.host.lights) // NEE: directional is todo!() (nee.rs:177)
                     if (l.kind == RAYCA_LIGHT_DIRECTIONAL) return fail(RAYCA_E_UNSUPPORTED, "NEE with a directional light");
@@ -481,7 +484,8 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
         const bool nee = config->direct_sampler == RAYCA_SAMPLER_NEE || mis;
         sel.bounce = config->max_depth > (nee ? 1u : 0u);
         // hemisphere bounces, roulette and quad lights under NEE run in the general path tracer (render.cuh)
-        bool general = mis || config->russian_roulette != 0 || (sel.bounce && config->indirect_sampler != RAYCA_SAMPLER_COSINE);
+        bool general = mis || config->russian_roulette != 0 || (sel.bounce && config->indirect_sampler != RAYCA_SAMPLER_COSINE) ||
+                       (sel.bounce && config->light_samples > 1);
         if (nee)
             for (const GpuLight& l : scene->host.lights) general = general || l.kind == RAYCA_LIGHT_QUAD;
         if (general) integrator = kInternalPathGeneral;

@@ -378,9 +378,10 @@ __device__ __forceinline__ bool surf_emissive(const Surf& sf) { // primitive.rs:
 constexpr uint32_t kInternalPathGeneral = 6u;  // launch-time selector next to the RAYCA_INTEGRATOR_* values
 constexpr uint32_t kRouletteDepthCap = 64u;    // a path still alive after this many bounces stops (oracle: same cap)
 
-__device__ __forceinline__ V3 hemisphere_dir(const RenderParams& P, const Surf& sf, uint32_t pixel, uint32_t sample, uint32_t depth) {
-    float e1 = rng_f32(P.seed, pixel, sample, depth, 0);
-    float e2 = rng_f32(P.seed, pixel, sample, depth, 1);
+__device__ __forceinline__ V3 hemisphere_dir(const RenderParams& P, const Surf& sf, uint32_t pixel, uint32_t sample, uint32_t depth,
+                                             uint32_t ls = 0) {
+    float e1 = rng_f32(P.seed, pixel, sample, depth, 2 * ls);
+    float e2 = rng_f32(P.seed, pixel, sample, depth, 2 * ls + 1);
     float theta = acosf(e1);
     float omega = 2.0f * kPi * e2;
     V3 sv{cosf(omega) * sinf(theta), sinf(omega) * sinf(theta), cosf(theta)};
@@ -656,6 +657,100 @@ __device__ __noinline__ bool pathtracer_general(const RenderParams& P, RayD ray,
     return any;
 }
 
+// Pathtracer::get_indirect_lighting with light_samples > 1 (integrator/pathtracer.rs:23-66): EVERY hit below the
+// indirect depth limit spawns light_samples indirect rays and each of them recurses, so a pixel sample is a tree of
+// up to LS^depth paths.  Walked depth-first on an explicit stack of levels {surface, path factor, next sample};
+// radiance is accumulated forwards like pathtracer_general: sum += (product of f_k / LS down the path) * direct, where
+// f_k is the indirect sampler's get_radiance factor.  The keyed RNG dimensions of sample `ls` at one (pixel, sample,
+// depth) are the oracle's: 2 ls, 2 ls + 1 (+ 0x10000 + ls for the Brdf sampler's lobe choice) — sibling subtrees at
+// the same depth draw the same numbers, on both sides.  Without russian roulette only (refused at launch), at most
+// kMaxBranchDepth levels.
+constexpr int kMaxBranchDepth = 8;
+struct BranchLevel {
+    Surf sf;
+    Col factor;
+    uint32_t next_ls;
+};
+
+template <int MODE, bool COUNT>
+__device__ __noinline__ bool pathtracer_branching(const RenderParams& P, RayD ray, uint32_t pixel, uint32_t sample, Col& out,
+                                                  HitD& primary, PixelCounters& pc) {
+    const GpuSceneView& s = P.scene;
+    const bool mis = P.cfg.direct_sampler == RAYCA_SAMPLER_MIS;
+    const bool nee = P.cfg.direct_sampler == RAYCA_SAMPLER_NEE || mis;
+    const bool hemisphere = P.cfg.indirect_sampler == RAYCA_SAMPLER_HEMISPHERE;
+    const bool brdf_sampler = P.cfg.indirect_sampler == RAYCA_SAMPLER_BRDF;
+    const uint32_t max_depth = P.cfg.max_depth;
+    const uint32_t limit = nee ? max_depth - 1u : max_depth;
+    const uint32_t LS = P.cfg.light_samples;
+    Col sum{0.0f, 0.0f, 0.0f, 1.0f};
+    out = sum;
+    if (max_depth == 0) return false;
+    BranchLevel stack[kMaxBranchDepth];
+    int top = -1; // stack[top] is the hit at depth == top whose indirect rays are being spawned
+    Col factor{1.0f, 1.0f, 1.0f, 1.0f};
+    uint32_t depth = 0; // depth of `ray`
+    bool collect_emissive = true, any = false;
+    for (;;) {
+        HitD h;
+        const bool hit = trace_ray<MODE, false, COUNT>(s, ray, h, &pc.walk);
+        if (depth == 0) {
+            primary = h;
+            any = hit;
+        }
+        if (hit) {
+            Surf sf;
+            load_surf<true, MODE == 3>(s, ray, h, sf);
+            if (collect_emissive && surf_emissive(sf)) {
+                sum = cadd(sum, cmul(factor, surf_color(s, sf)));
+            } else {
+                if (mis) sum = cadd(sum, cmul(factor, mis_general<MODE, COUNT>(P, sf, pixel, sample, depth, pc)));
+                else if (nee) sum = cadd(sum, cmul(factor, nee_general<MODE, COUNT>(P, sf, pixel, sample, depth, pc)));
+                if (depth < limit && top + 1 < kMaxBranchDepth) {
+                    ++top; // == depth: levels are pushed in depth order
+                    stack[top].sf = sf;
+                    stack[top].factor = factor;
+                    stack[top].next_ls = 0;
+                }
+            }
+        }
+        // the next indirect ray: the deepest level that still has samples to spawn
+        bool found = false;
+        while (top >= 0 && !found) {
+            BranchLevel& L = stack[top];
+            if (L.next_ls == LS) {
+                --top;
+            } else {
+                const uint32_t ls = L.next_ls++;
+                const uint32_t d = (uint32_t)top;
+                // trace_impl(depth + 1) returns None before tracing anything once depth + 1 reaches max_depth
+                if (d + 1u < max_depth) {
+                    V3 wi;
+                    if (brdf_sampler)
+                        wi = material_dir(s, L.sf, rng_f32(P.seed, pixel, sample, d, 0x10000u + ls), rng_f32(P.seed, pixel, sample, d, 2u * ls),
+                                          rng_f32(P.seed, pixel, sample, d, 2u * ls + 1u));
+                    else
+                        wi = hemisphere ? hemisphere_dir(P, L.sf, pixel, sample, d, ls) : cosine_dir(P, L.sf, pixel, sample, d, ls);
+                    const Col brdf = surf_brdf(s, L.sf, wi);
+                    const float cosine_law = fminf(fmaxf(dot(L.sf.normal, wi), 0.0f), 1.0f);
+                    const Col f = brdf_sampler ? cscale(cadd(surf_diffuse(s, L.sf), surf_specular_component(s, L.sf, wi)), 1.0f)
+                                  : hemisphere ? cscale(cscale(cscale(brdf, 2.0f * kPi), cosine_law), 1.0f)
+                                               : cscale(cscale(brdf, kPi), 1.0f);
+                    factor = cmul(L.factor, cdiv(f, (float)LS));
+                    ray = make_ray(L.sf.next_origin, wi);
+                    depth = d + 1u;
+                    collect_emissive = !nee;
+                    pc.secondary++;
+                    found = true;
+                }
+            }
+        }
+        if (!found) break;
+    }
+    out = sum;
+    return any;
+}
+
 // AnalyticDirect::trace (integrator/analyticdirect.rs:16-49)
 template <int MODE, bool COUNT>
 __device__ __forceinline__ bool analytic_direct(const RenderParams& P, const RayD& ray, Col& out, HitD& primary, PixelCounters& pc) {
@@ -775,7 +870,10 @@ __device__ __forceinline__ void trace_sample(const RenderParams& P, uint32_t x, 
     bool ok;
     ph = no_hit();
     if (INTEGRATOR == (int)kInternalPathGeneral) {
-        ok = pathtracer_general<MODE, COUNT>(P, ray, pixel, i, c, ph, pc);
+        if (P.cfg.light_samples > 1 && !P.cfg.russian_roulette && P.cfg.max_depth > (P.cfg.direct_sampler == RAYCA_SAMPLER_NONE ? 0u : 1u))
+            ok = pathtracer_branching<MODE, COUNT>(P, ray, pixel, i, c, ph, pc); // light_samples indirect rays per hit
+        else
+            ok = pathtracer_general<MODE, COUNT>(P, ray, pixel, i, c, ph, pc);
     } else if (INTEGRATOR == RAYCA_INTEGRATOR_PATHTRACER) {
         ok = pathtracer<MODE, COUNT, BOUNCE>(P, ray, pixel, i, c, ph, pc);
     } else if (INTEGRATOR == RAYCA_INTEGRATOR_RAYTRACER) {

@@ -152,7 +152,9 @@ SCENES = {
              "pt1_gamma": (dict(PT1, gamma=2.2), 64, 64), "wide": (PT1, 160, 48)}),
     "orientation": (lambda: gltf_scene("orientation/OrientationTest.gltf", scale_root([0.2, 0.2, 0.2])),
                     {"pt1": (PT1, 128, 128), "rt0": (RT0, 96, 96)}),
-    "cubes_over_plane": (cubes_over_plane_scene, {"pt1": (PT1, 128, 128), "rt3": (RT3, 96, 96), "sc3": (SC3, 96, 96), "pt3": (dict(integrator=IntegratorStrategy.Pathtracer, max_depth=3), 64, 64)}),
+    "cubes_over_plane": (cubes_over_plane_scene, {"pt1": (PT1, 128, 128), "rt3": (RT3, 96, 96), "sc3": (SC3, 96, 96), "pt3": (dict(integrator=IntegratorStrategy.Pathtracer, max_depth=3), 64, 64),
+                                                  # branching bounces under point-light NEE (PBR materials, cosine sampler)
+                                                  "pt3_ls2": (dict(integrator=IntegratorStrategy.Pathtracer, max_depth=3, light_samples=2), 64, 64)}),
     "suzanne": (lambda: gltf_scene("suzanne/suzanne.gltf"), {"pt1": (PT1, 128, 128), "rt0": (RT0, 96, 96), "pt2": (PT2, 64, 64)}),
     # Scratcher (integrator/scratcher.rs): the reference's own fixture, the transmission branch, reflections
     "scratcher_sphere": (scratcher_sphere_scene, {"nobvh": (dict(integrator=IntegratorStrategy.Scratcher, bvh=False), 128, 128),
@@ -181,7 +183,13 @@ SCENES = {
                                         "pt_mis_rr": (dict(PTC, direct_sampler=SamplerStrategy.Mis, indirect_sampler=SamplerStrategy.Brdf,
                                                            russian_roulette=True, max_depth=16), 40, 40),
                                         "pt_cosine_rr": (dict(PTC, direct_sampler=SamplerStrategy.Nee, indirect_sampler=SamplerStrategy.Cosine,
-                                                              russian_roulette=True, max_depth=16), 40, 40)}),
+                                                              russian_roulette=True, max_depth=16), 40, 40),
+                                        # light_samples > 1 WITH bounces: every hit spawns light_samples indirect rays
+                                        # (pathtracer.rs:23-66), a tree of paths per pixel sample
+                                        "pt_branch_nee": (dict(PTC, samples_per_pixel=2, direct_sampler=SamplerStrategy.Nee,
+                                                               indirect_sampler=SamplerStrategy.Cosine, light_samples=3, max_depth=3), 40, 40),
+                                        "pt_branch_simple": (dict(PTC, samples_per_pixel=2, direct_sampler=SamplerStrategy.NONE,
+                                                                  light_samples=2, max_depth=3), 40, 40)}),
     # sdtf/4/ggx.sdtf: spheres with Phong and GGX materials of growing roughness under the Brdf sampler (its own settings,
     # 2 spp instead of 64; russian roulette as the file asks, which Config::apply drops: both variants)
     "ggx": ("sdtf/4/ggx.sdtf", {"brdf": (dict(samples_per_pixel=2), 160, 35),
@@ -208,9 +216,16 @@ def render_case(osc, cfg: Config, w, h, seed=0x5EED):
 
 
 def main(names):
+    """`names`: scene names (all their cases) and / or `scene.case` entries (only those cases are rewritten)."""
+    only = {n for n in names if "." in n}
+    names = [n.split(".")[0] for n in names]
     for name, (builder, cases) in SCENES.items():
         if names and name not in names:
             continue
+        if only and not any(o.startswith(name + ".") for o in only) :
+            pass
+        elif only:
+            cases = {c: v for c, v in cases.items() if f"{name}.{c}" in only}
         t0 = time.time()
         sdtf_cfg = None
         if isinstance(builder, str):

@@ -153,7 +153,8 @@ def test_draw_trait_mirror(ctx, cuda_lib):
 def test_unsupported_and_error_paths(ctx):
     sc = dev_scene(ctx, "box")
     for cfg in (R.Config(direct_sampler=R.SamplerStrategy.Mis), R.Config(indirect_sampler=R.SamplerStrategy.Brdf),
-                R.Config(light_samples=4)):  # Mis / Brdf need Phong or GGX materials (box.gltf is PBR); branching bounces
+                R.Config(light_samples=4, russian_roulette=True), R.Config(light_samples=2, max_depth=9)):
+        # Mis / Brdf need Phong or GGX materials (box.gltf is PBR); branching bounces run without roulette, 8 levels deep
         with pytest.raises(R.RaycaError) as e:
             sc.render(cfg, 16, 16)
         assert e.value.code == -2
@@ -415,6 +416,30 @@ def test_device_built_reference_blas_equals_host_built(ctx):
         assert np.array_equal(noa, nob) and np.array_equal(poa, pob) and np.array_equal(sa, sb), name
         a.close()
         b.close()
+
+
+def test_branching_bounces_estimate_the_same_image(ctx):
+    """light_samples > 1 with bounces (pathtracer.rs:23-66: every hit spawns light_samples indirect rays): the tree of
+    paths is an estimator of the same depth-truncated image as the single chain, so the means agree (within 4 %),
+    and the secondary-ray count is bounded by the full tree.  Without a direct sampler: the reference's NEE sums its
+    light samples without dividing by their number (the oracle and the golden cases keep that), so only the
+    indirect estimator, which does divide (pathtracer.rs:65), is independent of light_samples."""
+    sc = dev_scene(ctx, "cornell")
+    P, S = R.IntegratorStrategy.Pathtracer, R.SamplerStrategy
+    base = dict(integrator=P, max_depth=4, light_stratify=False, direct_sampler=S.NONE)
+    means = {}
+    for name, kw in {"chain": dict(indirect_sampler=S.Cosine, light_samples=1, samples_per_pixel=64),
+                     "tree2 cosine": dict(indirect_sampler=S.Cosine, light_samples=2, samples_per_pixel=32),
+                     "tree3 hemisphere": dict(indirect_sampler=S.Hemisphere, light_samples=3, samples_per_pixel=16)}.items():
+        _, aux, st = sc.render(R.Config(**base, **kw), 240, 240, want_aux=True)
+        rgb = aux.rgba_f32.reshape(240, 240, 4)[..., :3]
+        assert np.isfinite(rgb).all()
+        means[name] = float(rgb.mean())
+        ls, spp = kw["light_samples"], kw["samples_per_pixel"]
+        assert st.rays_primary == 240 * 240 * spp
+        assert 0 < st.rays_secondary <= st.rays_primary * (ls + ls ** 2 + ls ** 3)  # max_depth 4: traced indirect rays leave depths 0, 1, 2
+    for name, m in means.items():
+        assert abs(m - means["chain"]) <= 0.04 * means["chain"], means
 
 
 def test_cornell_estimators_agree_in_the_mean(ctx):
