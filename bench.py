@@ -361,7 +361,7 @@ def run_ours(args):
                 frame_crc = f"{frame_crc} maxdiff_u8={int(dq.max())} differing_bytes={int((dq > 0).sum())}"
             else:
                 np.save(ab_ref, np.ascontiguousarray(img.buffer))
-        e2e_what = "rayca_cuda_render: pinned host RGBA8 out, scene resident (scene_create excluded, like the reference timer)"
+        e2e_what = "rayca_cuda_render: RGBA8 frame stored by the kernel straight into the caller's pinned host buffer (zero copy over PCIe), scene resident (scene_create excluded, like the reference timer)"
     else:
         srcs = [torch.as_tensor(f, device="cuda") for f in frames] if (peer and rank == 0) else [gathered]
         host = torch.empty(tuple(srcs[0].shape), dtype=torch.uint8).pin_memory() if rank == 0 else None

@@ -331,9 +331,9 @@ typedef struct rayca_scene rayca_scene;
 
 /* ------------------------------------------------------------- entry points */
 
-/* Pinned (page-locked) host memory for `rgba8_out`: with it rayca_cuda_render overlaps the read-back of
- * finished row bands with the tracing of the next ones.  The Rust shim allocates Image buffers that it
- * owns through this pair; any other host pointer works too, only without the overlap. */
+/* Pinned (page-locked) host memory for `rgba8_out`: rayca_cuda_render lets the kernel store the frame straight
+ * into it (zero copy, one launch).  The Rust shim allocates Image buffers that it owns through this pair; any
+ * other host pointer works too — pageable memory is filled by overlapped copies of row bands instead. */
 int rayca_cuda_host_alloc(size_t bytes, void** out);
 void rayca_cuda_host_free(void* p);
 

@@ -814,6 +814,25 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
     int rc = RAYCA_OK;
     uint32_t launched = 0;
     uint32_t band_of[8] = {0};
+    // Zero copy: when the caller's buffer is pinned host memory (rayca_cuda_host_alloc, or any cudaHostAlloc /
+    // cudaHostRegister'ed range) the device can address it, so ONE launch stores the RGBA8 pixels straight into it
+    // over PCIe — posted writes that drain while the rest of the frame is traced: no device staging plane, no
+    // copy, no band tails.  RAYCA_ZERO_COPY=0 restores the banded copy for A/B runs.
+    void* host_view = nullptr;
+    {
+        const char* e = std::getenv("RAYCA_ZERO_COPY");
+        cudaPointerAttributes at{};
+        if (!(e && std::atoi(e) == 0) && cudaPointerGetAttributes(&at, rgba8_out) == cudaSuccess && at.type == cudaMemoryTypeHost)
+            host_view = at.devicePointer;
+        cudaGetLastError(); // a pageable pointer is reported as an error by older runtimes: not ours to keep
+    }
+    if (host_view) nb = 0;
+    if (host_view) {
+        rc = enqueue_render(ctx, scene, config, options, width, height, host_view, aux ? &d : nullptr, ctx->render_stream, nullptr, &local);
+        if (rc != RAYCA_OK) return rc;
+        launched = 1;
+        CUDA_TRY(cudaStreamSynchronize(ctx->render_stream));
+    }
     for (uint32_t k = 0; k < nb; ++k) {
         if (edge[k] >= edge[k + 1]) continue;
         Band bd{edge[k], edge[k + 1], launched == 0, edge[k + 1] == height};
@@ -822,13 +841,13 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
         CUDA_TRY(cudaEventRecord(ctx->band_done[launched], ctx->render_stream));
         band_of[launched++] = k;
     }
-    for (uint32_t j = 0; j < launched; ++j) {
+    for (uint32_t j = 0; j < launched && !host_view; ++j) {
         const size_t y0 = edge[band_of[j]], y1 = edge[band_of[j] + 1];
         CUDA_TRY(cudaStreamWaitEvent(ctx->copy_stream, ctx->band_done[j], 0));
         CUDA_TRY(cudaMemcpyAsync(rgba8_out + y0 * width * 4, base + y0 * width * 4, (y1 - y0) * width * 4, cudaMemcpyDeviceToHost,
                                  ctx->copy_stream));
     }
-    CUDA_TRY(cudaStreamSynchronize(ctx->copy_stream));
+    if (!host_view) CUDA_TRY(cudaStreamSynchronize(ctx->copy_stream));
     local.kernel_launches = launched;
     if (aux) {
         if (aux->hit_blas) CUDA_TRY(cudaMemcpy(aux->hit_blas, d.hit_blas, n * 4, cudaMemcpyDeviceToHost));

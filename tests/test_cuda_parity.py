@@ -244,15 +244,18 @@ def test_persistent_scheduling_equals_static_grid(ctx, atrium):
 
 
 def test_host_render_bands_equal_single_launch(ctx, atrium):
-    """rayca_cuda_render traces the frame in row bands and reads each band back on a side stream (into pinned
-    or pageable memory); the result must equal one render_device launch over the whole frame."""
+    """rayca_cuda_render stores the frame straight into a pinned caller buffer from one launch (zero copy), and for
+    pageable memory traces it in row bands, each read back on a side stream; both must equal one render_device
+    launch over the whole frame."""
     import torch
 
     cfg = R.Config(max_depth=1)
     w, h = 1283, 721
     img = R.Image(w, h, pinned=True)
-    _, _, st = atrium.render(cfg, w, h, out=img.buffer)
-    pageable, _, _ = atrium.render(cfg, w, h)
+    img.buffer[...] = 7
+    _, _, zc = atrium.render(cfg, w, h, out=img.buffer)
+    assert zc.rays_primary == w * h and zc.kernel_launches == 1
+    pageable, _, st = atrium.render(cfg, w, h)
     buf = torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda:0")
     atrium.render_device(cfg, w, h, buf.data_ptr())
     torch.cuda.synchronize()
