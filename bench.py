@@ -49,7 +49,7 @@ def parse_args():
     ap.add_argument("--traversal", type=int, default=0)
     ap.add_argument("--flags", type=int, default=0, help="rayca_options.flags for the timed launches")
     ap.add_argument("--max-depth", type=int, default=1, help="Pathtracer max_depth (2 = one cosine bounce, BASELINE M5)")
-    ap.add_argument("--gather", choices=["peer", "nccl"], default="peer",
+    ap.add_argument("--gather", choices=["peer", "nccl", "host"], default="peer",
                     help="N>1: peer = kernels store tiles into rank 0's frame over NVLink; nccl = all_gather_into_tensor")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-rows", type=int, default=0, help="rows of the frame the CPU baseline renders")
@@ -244,15 +244,34 @@ def run_ours(args):
                 frames.append(R.SharedFrame(ctx, W, H, handle=handle[0]))
         frame = frames[0]
 
+    # N > 1, --gather host: the frame lives in POSIX shared memory that every rank page-locks; each rank's kernel stores
+    # its tiles straight into it over its own PCIe link (zero copy): no gather and no device-to-host copy at all.
+    host_mode = G > 1 and args.gather == "host"
+    hframes = []
+    if host_mode:
+        for _ in range(2):
+            nm = [None]
+            if rank == 0:
+                hframes.append(R.HostFrame(W, H))
+                nm[0] = hframes[-1].name
+            dist.broadcast_object_list(nm, src=0)
+            if rank != 0:
+                hframes.append(R.HostFrame(W, H, name=nm[0]))
+    hopts = M.rayca_options(0x5EED, args.traversal, rank, G, tile, args.flags | R.FLAG_DIRECT_ROWS, 0)
+
     def trace():
-        if peer:
+        if host_mode:
+            dev.render_device(cfg, W, H, hframes[0].device_ptr, stream=stream, options=hopts)
+        elif peer:
             frame_id[0] += 1
             dev.render_to_frame(cfg, frame, frame_id[0], stream=stream, options=opts)
         else:
             dev.render_device(cfg, W, H, local.data_ptr(), stream=stream, options=opts)
 
     def gather():
-        if peer:
+        if host_mode:
+            pass  # nothing to collect: the pixels are already at their place in host memory when the launches are done
+        elif peer:
             if rank == 0:
                 frame.wait(G, frame_id[0], stream=stream)
         elif G > 1:
@@ -270,6 +289,20 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
+    if host_mode:
+        # the host frame must equal the NCCL-gathered tiles byte for byte once every rank's launch is complete
+        dev.render_device(cfg, W, H, local.data_ptr(), stream=stream, options=opts)
+        dist.all_gather_into_tensor(gathered, local)
+        expect = gathered.view(G, per, tile, W, 4).permute(1, 0, 2, 3, 4).reshape(per * G * tile, W, 4)[:H].cpu().numpy()
+        for _ in range(4):
+            if rank == 0:
+                hframes[0].pixels[...] = 0
+            barrier()
+            step()
+            barrier()
+            if rank == 0 and not np.array_equal(hframes[0].pixels, expect):
+                raise RuntimeError("host frame differs from the NCCL-gathered frame")
+            barrier()
     if peer:
         # The shared frame must equal the NCCL-gathered tiles, byte for byte, at the moment the flag wait
         # returns: rank 0 clears the frame before every round, so a flag that overtook its pixels shows up
@@ -370,7 +403,26 @@ def run_ours(args):
             frames[0].release(ids[0], stream=stream)  # the timed loop above consumed nothing: catch up
         e2e_k = [0]
 
+        uses = [0, 0]  # host mode: how often each of the two host frames has been filled (same on every rank)
+
         def e2e_step():
+            if host_mode:
+                # every rank: wait until rank 0 consumed the frame's previous content, store this rank's tiles through
+                # rayca_cuda_render (synchronous: returns when the pixels are in host memory), publish a host flag;
+                # rank 0: spin on the G flags — then the whole frame is in host memory — and mark it consumed
+                b = e2e_k[0] & 1
+                e2e_k[0] += 1
+                f = hframes[b]
+                while f.flags[R.HostFrame.SLOTS - 1] < uses[b]:
+                    pass
+                dev.render(cfg, W, H, out=f.pixels, options=hopts)
+                uses[b] += 1
+                f.flags[rank] = uses[b]
+                if rank == 0:
+                    while (f.flags[:G] < uses[b]).any():
+                        pass
+                    f.flags[R.HostFrame.SLOTS - 1] = uses[b]
+                return
             if peer:
                 # frames used alternately; a rank overwrites a frame only after rank 0 released its last use
                 b = e2e_k[0] & 1
@@ -392,7 +444,11 @@ def run_ours(args):
         for _ in range(4):
             e2e_step()
         torch.cuda.synchronize()
-        if rank == 0 and not torch.equal(host, srcs[0].cpu()):
+        if host_mode:
+            barrier()
+            if rank == 0 and not (np.array_equal(hframes[0].pixels, expect) and np.array_equal(hframes[1].pixels, expect)):
+                raise RuntimeError("e2e: host frame differs from the NCCL-gathered frame")
+        elif rank == 0 and not torch.equal(host, srcs[0].cpu()):
             raise RuntimeError("e2e: host frame differs from the device frame")
         barrier()
         t1 = time.perf_counter()
@@ -405,7 +461,10 @@ def run_ours(args):
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
         e2e_s = float(e2e_t.item())
         d2h = int(host.numel()) if rank == 0 else 0
-        e2e_what = ("render_to_frame on every rank (peer stores into rank 0's frame, two frames alternating with acquire / release flags) + flag wait + rank-0 copy to pinned host memory"
+        if host_mode:
+            d2h = W * H * 4 // G  # each rank stores its own tiles into the host frame
+        e2e_what = ("rayca_cuda_render on every rank with RAYCA_FLAG_DIRECT_ROWS: each rank's kernel stores its tiles straight into a shared, page-locked host frame over its own PCIe link (zero copy, two frames alternating, host-side completion / consumed flags); no gather, no device-to-host copy"
+                    if host_mode else "render_to_frame on every rank (peer stores into rank 0's frame, two frames alternating with acquire / release flags) + flag wait + rank-0 copy to pinned host memory"
                     if peer else "render_device on every rank + NCCL all_gather + rank-0 copy of the frame to pinned host memory")
     e2e = {"value": rays_frame / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": param_bytes,
            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "what": e2e_what}
@@ -445,7 +504,7 @@ def run_ours(args):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": what, "width": W, "height": H, "spp": args.spp,
                            "triangles": desc.triangle_count, "integrator": f"Pathtracer max_depth={args.max_depth} (NEE point lights" + (", cosine bounce, Philox keyed RNG)" if args.max_depth > 1 else ")"),
-                           "parallelism": f"image row-tiles of {tile} rows interleaved over {G} GPU(s), scene replicated, " + ("tiles stored into rank 0's frame by the trace kernel over NVLink (CUDA IPC), per-rank completion flags" if peer else "NCCL all_gather of RGBA8"),
+                           "parallelism": f"image row-tiles of {tile} rows interleaved over {G} GPU(s), scene replicated, " + ("tiles stored by the trace kernel straight into a shared page-locked HOST frame (POSIX shm registered by every rank), no gather" if host_mode else "tiles stored into rank 0's frame by the trace kernel over NVLink (CUDA IPC), per-rank completion flags" if peer else "NCCL all_gather of RGBA8"),
                            "l2": "flushed between timed iterations (256 MiB fill)", "traversal": args.traversal},
                 "rays_per_frame": rays_frame, "kernel_ms": kernel_ms, "build_s": build_s,
                 "clocks": sampler.summary(), "gpu_launches": args.steps * (3 if peer else 1),  # peer: trace + flag signal + flag wait (rank 0)
@@ -468,6 +527,8 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": r / (m * 1e-3) / 1e6, "unit": "Mrays/s", "cores": th, "kind": "port",
                                     "sample": f"{rows} evenly spaced rows of the frame, pixel loop only, reference-faithful mode"}
         print(json.dumps(line))
+    for f in hframes:
+        f.close()
     if G > 1:
         dist.destroy_process_group()
 

@@ -288,8 +288,13 @@ typedef struct rayca_options {
 
 enum {
     RAYCA_FLAG_COUNT_WALK = 1, /* also tally node / triangle records fetched (roofline accounting; slower) */
-    RAYCA_FLAG_PERSISTENT = 2 /* persistent warps that pull 16x8 pixel groups from a global counter instead of
-                                 one thread block per group (default; faster on B200, see render.cuh) */
+    RAYCA_FLAG_PERSISTENT = 2, /* persistent warps that pull 16x8 pixel groups from a global counter instead of
+                                  one thread block per group (default; faster on B200, see render.cuh) */
+    RAYCA_FLAG_DIRECT_ROWS = 4 /* sharded launches (shard_count > 1): the output pointer addresses the FULL width x height
+                                  frame and every owned pixel is stored at its final row-major position, instead of the
+                                  shard's tiles packed one after the other — a frame all ranks can address (pinned host
+                                  memory registered in every process, rayca_cuda_host_register) is then complete once
+                                  every rank's launch is, with no gather and no device-to-host copy */
 };
 
 /* Optional per-pixel planes for parity checks; any pointer may be NULL.
@@ -336,6 +341,14 @@ typedef struct rayca_scene rayca_scene;
  * other host pointer works too — pageable memory is filled by overlapped copies of row bands instead. */
 int rayca_cuda_host_alloc(size_t bytes, void** out);
 void rayca_cuda_host_free(void* p);
+
+/* Page-locks and maps host memory the caller already owns (cudaHostRegister, portable + mapped): an Image's Vec<u8>
+ * that lives across frames, or a POSIX shared-memory frame that the one-process-per-GPU ranks of a node all mmap —
+ * each rank registers its own mapping and its kernel stores its tiles straight into the shared frame over its own
+ * PCIe link (RAYCA_FLAG_DIRECT_ROWS).  `device_view` receives the address the device uses for `p` (pass it to
+ * rayca_cuda_render_device); rayca_cuda_render accepts `p` itself. */
+int rayca_cuda_host_register(void* p, size_t bytes, void** device_view);
+int rayca_cuda_host_unregister(void* p);
 
 /* Measurement aid (bench.py): best-of-5 streaming read bandwidth over a `bytes` buffer read `reps` times with
  * 128-bit loads from all SMs.  A buffer well inside the 126 MB L2 gives the L2 -> SM read peak that bounds the

@@ -463,7 +463,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
         P.rgba_f32 = d_aux->rgba_f32;
     }
     P.counters = ctx->d_counters;
-    if (target) P.direct_rows = 1;
+    if (target || (options && (options->flags & RAYCA_FLAG_DIRECT_ROWS))) P.direct_rows = 1;
     const uint32_t mode = options ? options->traversal : (uint32_t)RAYCA_TRAVERSAL_ORDERED;
     if (mode > RAYCA_TRAVERSAL_REFERENCE_ORDERED) return fail(RAYCA_E_INVALID_ARG, "unknown traversal mode");
     if (mode != RAYCA_TRAVERSAL_ORDERED && scene->host.has_spheres)
@@ -732,6 +732,25 @@ void rayca_cuda_host_free(void* p) {
     if (p) cudaFreeHost(p);
 }
 
+int rayca_cuda_host_register(void* p, size_t bytes, void** device_view) {
+    if (!p || bytes == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
+    CUDA_TRY(cudaHostRegister(p, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped));
+    if (device_view) {
+        cudaError_t e = cudaHostGetDevicePointer(device_view, p, 0);
+        if (e != cudaSuccess) {
+            cudaHostUnregister(p);
+            return fail(RAYCA_E_CUDA, cudaGetErrorString(e));
+        }
+    }
+    return RAYCA_OK;
+}
+
+int rayca_cuda_host_unregister(void* p) {
+    if (!p) return fail(RAYCA_E_INVALID_ARG, "null argument");
+    CUDA_TRY(cudaHostUnregister(p));
+    return RAYCA_OK;
+}
+
 int rayca_cuda_last_counters(rayca_ctx* ctx, rayca_stats* stats) {
     if (!ctx || !stats) return fail(RAYCA_E_INVALID_ARG, "null argument");
     CUDA_TRY(cudaSetDevice(ctx->device));
@@ -753,8 +772,15 @@ int rayca_cuda_last_counters(rayca_ctx* ctx, rayca_stats* stats) {
 int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options, uint32_t width,
                       uint32_t height, uint8_t* rgba8_out, const rayca_aux_out* aux, rayca_stats* stats) {
     if (!ctx || !rgba8_out || width == 0 || height == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
-    if (options && options->shard_count > 1) return fail(RAYCA_E_INVALID_ARG, "sharded output is only available through render_device");
     CUDA_TRY(cudaSetDevice(ctx->device));
+    const bool sharded = options && options->shard_count > 1;
+    if (sharded) { // one rank's tiles of a frame that several ranks fill: only straight into pinned memory, at the final rows
+        cudaPointerAttributes at{};
+        const bool pinned = cudaPointerGetAttributes(&at, rgba8_out) == cudaSuccess && at.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+        if (!pinned || aux || !(options->flags & RAYCA_FLAG_DIRECT_ROWS))
+            return fail(RAYCA_E_INVALID_ARG, "a sharded render to host memory needs a pinned frame, RAYCA_FLAG_DIRECT_ROWS and no aux planes");
+    }
     const size_t n = (size_t)width * height;
     // scratch layout: rgba8 | hit_blas | hit_prim | hit_src | depth | uv | rgba_f32, each plane 256 B aligned
     auto al = [](size_t b) { return (b + 255) & ~size_t(255); };
@@ -822,7 +848,7 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
     {
         const char* e = std::getenv("RAYCA_ZERO_COPY");
         cudaPointerAttributes at{};
-        if (!(e && std::atoi(e) == 0) && cudaPointerGetAttributes(&at, rgba8_out) == cudaSuccess && at.type == cudaMemoryTypeHost)
+        if ((sharded || !(e && std::atoi(e) == 0)) && cudaPointerGetAttributes(&at, rgba8_out) == cudaSuccess && at.type == cudaMemoryTypeHost)
             host_view = at.devicePointer;
         cudaGetLastError(); // a pageable pointer is reported as an error by older runtimes: not ours to keep
     }

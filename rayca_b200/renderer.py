@@ -47,6 +47,7 @@ class SamplerStrategy(enum.IntEnum):
 TRAVERSAL_ORDERED, TRAVERSAL_EXHAUSTIVE, TRAVERSAL_REFERENCE_ORDERED = 0, 1, 2
 FLAG_COUNT_WALK = 1
 FLAG_PERSISTENT = 2
+FLAG_DIRECT_ROWS = 4
 
 _ERRORS = {-1: "RAYCA_E_INVALID_ARG", -2: "RAYCA_E_UNSUPPORTED", -3: "RAYCA_E_OOM", -4: "RAYCA_E_CUDA",
            -5: "RAYCA_E_NO_CAMERA"}
@@ -155,6 +156,8 @@ def load_library():
     lib.rayca_cuda_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
     lib.rayca_cuda_host_free.argtypes = [vp]
     lib.rayca_cuda_host_free.restype = None
+    lib.rayca_cuda_host_register.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
+    lib.rayca_cuda_host_unregister.argtypes = [vp]
     lib.rayca_cuda_probe_read_bandwidth.argtypes = [vp, C.c_size_t, u32, C.POINTER(C.c_double)]
     lib.rayca_cuda_frame_create.argtypes = [vp, u32, u32, C.POINTER(vp)]
     lib.rayca_cuda_frame_export.argtypes = [vp, C.c_char_p]
@@ -229,6 +232,59 @@ class Context:
         if self._h:
             load_library().rayca_cuda_shutdown(self._h)
             self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class HostFrame:
+    """An RGBA8 frame in POSIX shared memory that every one-process-per-GPU rank of a node maps and page-locks
+    (rayca_cuda_host_register): with FLAG_DIRECT_ROWS each rank's kernel stores its tiles straight into the frame
+    over its own PCIe link, so the frame is complete in HOST memory once every rank's launch is — no gather, no
+    device-to-host copy.  Behind the pixels sit 64 int64 slots for host-side flags (per-rank "frame k stored",
+    slot 63 = "consumed up to k").  `HostFrame(w, h)` creates (owner), `HostFrame(w, h, name=...)` attaches."""
+
+    SLOTS = 64
+
+    def __init__(self, width: int, height: int, name: Optional[str] = None):
+        from multiprocessing import shared_memory
+
+        self.width, self.height, self.owner = width, height, name is None
+        nbytes = width * height * 4 + 8 * self.SLOTS
+        self._shm = shared_memory.SharedMemory(create=True, size=nbytes) if name is None else shared_memory.SharedMemory(name=name)
+        self.name = self._shm.name
+        if name is not None:  # the owner unlinks; keep this process's resource tracker from doing it again at exit
+            try:
+                from multiprocessing import resource_tracker
+
+                resource_tracker.unregister(self._shm._name, "shared_memory")
+            except Exception:
+                pass
+        raw = np.frombuffer(self._shm.buf, dtype=np.uint8, count=nbytes)
+        self.pixels = raw[: width * height * 4].reshape(height, width, 4)
+        self.flags = raw[width * height * 4:].view(np.int64)
+        if self.owner:
+            raw[...] = 0
+        self._addr = raw.ctypes.data
+        dv = C.c_void_p()
+        _check(load_library().rayca_cuda_host_register(self._addr, nbytes, C.byref(dv)))
+        self.device_ptr = dv.value
+        self._registered = True
+
+    def close(self):
+        if getattr(self, "_registered", False):
+            load_library().rayca_cuda_host_unregister(self._addr)
+            self._registered = False
+            self.pixels = self.flags = None
+            try:
+                self._shm.close()
+                if self.owner:
+                    self._shm.unlink()
+            except Exception:
+                pass
 
     def __del__(self):
         try:

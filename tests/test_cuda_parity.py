@@ -290,6 +290,35 @@ def test_shared_frame_of_three_shards_equals_single_launch(ctx, atrium):
     frame.close()
 
 
+def test_host_frame_of_three_shards_equals_single_launch(ctx, atrium):
+    """Multi-GPU host path on one device: three shards stored with RAYCA_FLAG_DIRECT_ROWS straight into one
+    page-locked shared-memory frame (rayca_cuda_host_register) — through rayca_cuda_render and through
+    render_device with the frame's device view — give the frame of a single launch; a sharded render into pageable
+    memory or without the flag is refused."""
+    import torch
+
+    cfg = R.Config(max_depth=1)
+    w, h, G = 1283, 721, 3
+    full, _, _ = atrium.render(cfg, w, h)
+    f = R.HostFrame(w, h)
+    try:
+        for g in range(G):
+            _, _, st = atrium.render(cfg, w, h, out=f.pixels, options=M.rayca_options(0, 0, g, G, 8, R.FLAG_DIRECT_ROWS, 0))
+            assert st.kernel_launches == 1
+        assert np.array_equal(f.pixels, full)
+        f.pixels[...] = 0
+        for g in range(G):
+            atrium.render_device(cfg, w, h, f.device_ptr, options=M.rayca_options(0, 0, g, G, 8, R.FLAG_DIRECT_ROWS, 0))
+        torch.cuda.synchronize()
+        assert np.array_equal(f.pixels, full)
+        for out, flags in ((f.pixels, 0), (np.zeros((h, w, 4), dtype=np.uint8), R.FLAG_DIRECT_ROWS)):
+            with pytest.raises(R.RaycaError) as e:
+                atrium.render(cfg, w, h, out=out, options=M.rayca_options(0, 0, 0, G, 8, flags, 0))
+            assert e.value.code == -1
+    finally:
+        f.close()
+
+
 def test_shared_frame_wait_times_out_instead_of_hanging(ctx, atrium):
     """A rank that never publishes its flag must not hang the owner: the wait kernel gives up after ~2 s and
     frame_timed_out reports it."""
