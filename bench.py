@@ -49,8 +49,9 @@ def parse_args():
     ap.add_argument("--traversal", type=int, default=0)
     ap.add_argument("--flags", type=int, default=0, help="rayca_options.flags for the timed launches")
     ap.add_argument("--max-depth", type=int, default=1, help="Pathtracer max_depth (2 = one cosine bounce, BASELINE M5)")
-    ap.add_argument("--gather", choices=["peer", "nccl", "host"], default="peer",
-                    help="N>1: peer = kernels store tiles into rank 0's frame over NVLink; nccl = all_gather_into_tensor")
+    ap.add_argument("--gather", choices=["peer", "nccl", "host"], default="host",
+                    help="N>1: host = kernels store tiles straight into a shared page-locked host frame (zero copy, default); "
+                         "peer = kernels store tiles into rank 0's device frame over NVLink; nccl = all_gather_into_tensor")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-rows", type=int, default=0, help="rows of the frame the CPU baseline renders")
     return ap.parse_args()
