@@ -32,7 +32,12 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-METRIC = "Mrays/s (primary+shadow, 1080p Sponza-class scene)"
+def metric_name(args):
+    """BASELINE.json's metric on the workload actually run (the default is the 1080p Sponza-class frame)."""
+    rays = "primary+shadow" if args.max_depth <= 1 else "primary+shadow+bounce"
+    scene = "Sponza-class scene" if args.workload == "atrium" else f"{args.workload} scene"
+    res = "1080p" if (args.width, args.height) == (1920, 1080) else f"{args.width}x{args.height}"
+    return f"Mrays/s ({rays}, {res} {scene}" + (f", {args.spp} spp" if args.spp > 1 else "") + ")"
 
 
 def parse_args():
@@ -140,55 +145,189 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.samples)}
 
 
-def cpu_baseline(desc, cfg, args, rows_total, faithful=True, phase=0.0):
-    """Times the oracle (a C++ port of rayca-soft's pixel loop: exhaustive unordered traversal, and with
-    `faithful` the per-test vertex re-transform the reference performs) on evenly spaced rows."""
-    from oracle import binding as O
+def sample_rows(args, rows_total):
+    """The fixed, evenly spaced image rows every CPU leg renders (the same rows in every step and every arm)."""
+    return [int(y) for y in ((np.arange(rows_total) + 0.5) / rows_total * args.height).astype(int) % args.height]
 
-    osc = O.OracleScene(desc, bvh=True)
-    ys = ((np.arange(rows_total) + 0.5 + phase) / rows_total * args.height).astype(int) % args.height
-    rays = 0
-    ms = 0.0
-    threads = 0
+
+def cpu_leg(osc, cfg, args, ys, flags, threads=0, keep=False):
+    """Times the oracle's pixel loop on image rows `ys` (one call per row; the oracle hands out pixels, not rows, to
+    its threads — rayca-soft/src/scene.rs:117-122 — so one row of 1920 pixels keeps every core busy).
+    Returns (rays, ms, threads that rendered pixels, {row: (rgba8 row, aux planes)} when keep)."""
+    from oracle import binding as O  # noqa: F401
+
+    rays, ms, th, kept = 0, 0.0, 0, {}
     for y in ys:
-        _, _, st = osc.render(cfg.to_c(), args.width, args.height, flags=O.FAITHFUL if faithful else 0,
-                              rows=(int(y), int(y) + 1), want_aux=False)
+        rgba8, aux, st = osc.render(cfg.to_c(), args.width, args.height, flags=flags, threads=threads,
+                                    rows=(int(y), int(y) + 1), want_aux=keep)
         rays += st.rays_primary + st.rays_shadow + st.rays_secondary
         ms += st.trace_ms
-        threads = st.threads
+        th = max(th, st.threads)
+        if keep:
+            W = args.width
+            sl = slice(y * W, (y + 1) * W)
+            kept[y] = {"rgba8": rgba8[y].copy(), "hit_src": aux.hit_src[sl].copy(), "hit_prim": aux.hit_prim[sl].copy(),
+                       "hit_blas": aux.hit_blas[sl].copy(), "depth": aux.depth[sl].copy(),
+                       "uv": aux.uv[2 * y * W:2 * (y + 1) * W].copy(), "rgba_f32": aux.rgba_f32[4 * y * W:4 * (y + 1) * W].copy()}
+    return rays, ms, th, kept
+
+
+def host_threads():
+    """Host cores this process may use (torchrun exports OMP_NUM_THREADS=1: the oracle gets an explicit count)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_legs(desc, cfg, args, rows, gpu=None):
+    """Every CPU figure of the bench line, all on the same fixed rows of the same frame:
+      faithful   = the reference's algorithm (exhaustive unordered walk of the reference BVH, vertices re-transformed
+                   per test) on all host threads — "rayca-soft on the host cores";
+      1 thread   = the same on one thread, one row;
+      optimised  = ordered, distance-culled walk over a binned-SAH tree of pre-transformed triangles (oracle OptTree),
+                   whole frame, all host threads — what a tuned CPU renderer would do, so the speed-up is not inflated.
+    With `gpu` = (rgba8 frame, aux planes) of the CUDA path the oracle rows are compared with it (parity_rows)."""
+    from oracle import binding as O
+
+    W, H = args.width, args.height
+    nthr = host_threads()
+    osc = O.OracleScene(desc, bvh=True)
+    ys = sample_rows(args, rows)
+    out = {}
+    r, m, th, kept = cpu_leg(osc, cfg, args, ys, O.FAITHFUL, threads=nthr, keep=gpu is not None)
+    faithful = r / (m * 1e-3) / 1e6
+    out["cpu_baseline"] = {"value": faithful, "unit": "Mrays/s", "cores": th, "kind": "port",
+                           "sample": f"image rows {ys} of the {W}x{H} frame (pixels of a row spread over the threads), pixel loop only "
+                                     "(BVH build excluded), reference-faithful mode: exhaustive walk of the reference BVH, vertices "
+                                     "re-transformed per test", "host_threads_available": nthr}
+    r1, m1, th1, _ = cpu_leg(osc, cfg, args, ys[len(ys) // 2:len(ys) // 2 + 1], O.FAITHFUL, threads=1)
+    out["cpu_1thread"] = {"value": r1 / (m1 * 1e-3) / 1e6, "unit": "Mrays/s", "cores": th1, "kind": "port",
+                          "sample": f"image row {ys[len(ys) // 2]}, reference-faithful mode, one thread"}
+    out["cpu_baseline"]["scaling_vs_1thread"] = faithful / max(out["cpu_1thread"]["value"], 1e-30)
+    opt_frame = None
+    try:
+        rgba8, aux, st = osc.render(cfg.to_c(), W, H, flags=O.OPTIMISED, threads=nthr, want_aux=gpu is not None)
+        rays = st.rays_primary + st.rays_shadow + st.rays_secondary
+        out["cpu_optimised"] = {"value": rays / (st.trace_ms * 1e-3) / 1e6, "unit": "Mrays/s", "cores": st.threads, "kind": "port",
+                                "tree_build_ms": st.opt_build_ms,
+                                "sample": f"the whole {W}x{H} frame, ordered + distance-culled walk over a binned-SAH tree of "
+                                          "pre-transformed triangles (oracle/rayca_oracle.cpp OptTree); same pixels as the faithful mode"}
+        opt_frame = (rgba8, aux)
+    except RuntimeError as e:  # sphere scenes: the optimised arm covers triangle scenes
+        out["cpu_optimised"] = {"unavailable": str(e)}
+    if gpu is not None:
+        g8, gaux = gpu
+        stochastic = args.max_depth > 1  # bounce directions go through cosf / sinf / acosf: ulp differences, rare different hits
+
+        def rgb_err(a, b):  # per pixel, absolute (relative above 1.0 for the unclamped HDR values of stochastic frames)
+            e = np.abs(a.reshape(-1, 4) - b.reshape(-1, 4))
+            if stochastic:
+                e = e / np.maximum(np.abs(b.reshape(-1, 4)), 1.0)
+            return np.nan_to_num(e, nan=0.0).max(axis=1) if len(e) else np.zeros(0)
+
+        idm, derr, u8, errs = 0, 0, 0, []
+        for y, k in kept.items():
+            sl = slice(y * W, (y + 1) * W)
+            idm += int((gaux.hit_src[sl] != k["hit_src"]).sum() + (gaux.hit_prim[sl] != k["hit_prim"]).sum() +
+                       (gaux.hit_blas[sl] != k["hit_blas"]).sum())
+            derr += int((gaux.depth[sl].view(np.uint32) != k["depth"].view(np.uint32)).sum() +
+                        (gaux.uv[2 * y * W:2 * (y + 1) * W].view(np.uint32) != k["uv"].view(np.uint32)).sum())
+            errs.append(rgb_err(gaux.rgba_f32[4 * y * W:4 * (y + 1) * W], k["rgba_f32"]))
+            u8 = max(u8, int(np.abs(g8[y].astype(np.int16) - k["rgba8"].astype(np.int16)).max()))
+        errs = np.concatenate(errs)
+        out["parity_rows"] = {"rows": ys, "against": "oracle, reference-faithful exhaustive walk", "pixels": len(ys) * W,
+                              "id_mismatch": idm, "depth_uv_bit_mismatch": derr, "max_rgb_err": float(errs.max()),
+                              "pixels_beyond_1e-3": int((errs > 1e-3).sum()), "max_rgba8_diff": u8}
+        if opt_frame is not None:
+            o8, oaux = opt_frame
+            ferr = rgb_err(gaux.rgba_f32, oaux.rgba_f32)
+            out["parity_frame"] = {
+                "against": "oracle, optimised arm (checked against the exhaustive walk on the sampled rows), whole frame",
+                "pixels": W * H,
+                "id_mismatch": int((gaux.hit_src != oaux.hit_src).sum() + (gaux.hit_prim != oaux.hit_prim).sum()),
+                "depth_uv_bit_mismatch": int((gaux.depth.view(np.uint32) != oaux.depth.view(np.uint32)).sum() +
+                                             (gaux.uv.view(np.uint32) != oaux.uv.view(np.uint32)).sum()),
+                "max_rgb_err": float(ferr.max()), "pixels_beyond_1e-3": int((ferr > 1e-3).sum()),
+                "max_rgba8_diff": int(np.abs(g8.astype(np.int16) - o8.astype(np.int16)).max()),
+                "rgba8_bytes_differing": int((g8 != o8).sum()),
+                "optimised_equals_exhaustive_on_rows": all(
+                    np.array_equal(oaux.hit_src[y * W:(y + 1) * W], k["hit_src"]) and
+                    np.array_equal(oaux.depth[y * W:(y + 1) * W].view(np.uint32), k["depth"].view(np.uint32)) and
+                    np.array_equal(oaux.rgba_f32[4 * y * W:4 * (y + 1) * W].view(np.uint32), k["rgba_f32"].view(np.uint32))
+                    for y, k in kept.items())}
+        # verdict: ids / depth / uv bit-exact everywhere; RGB within 1e-3 (stochastic frames: on >= 99 % of the pixels)
+        bad = idm + derr
+        allowed = 0.01 if stochastic else 0.0
+        bad += int(out["parity_rows"]["pixels_beyond_1e-3"] > allowed * len(errs))
+        if "parity_frame" in out:
+            pf = out["parity_frame"]
+            bad += pf["id_mismatch"] + pf["depth_uv_bit_mismatch"] + int(pf["pixels_beyond_1e-3"] > allowed * W * H)
+            bad += int(not pf["optimised_equals_exhaustive_on_rows"])
+        out["parity_ok"] = bad == 0
     osc.close()
-    return rays, ms, threads
+    return out
 
 
 def run_reference(args):
     """--impl reference: the reference's CPU implementation of the path on the host cores.  The Rust
     crate cannot be built here (nightly toolchain absent), so this is the oracle port in
-    reference-faithful mode, all host threads, each step a bounded sample of the same frame."""
+    reference-faithful mode on all host threads; every step renders the SAME fixed rows of the frame."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    from oracle import binding as O
+
     scene, what = make_scene(args)
     desc = scene.to_desc()
     cfg = render_config(args)
-    rows = args.cpu_rows or 1
-    rays = 0
-    ms = 0.0
-    threads = 1
+    rows = args.cpu_rows or 4
+    ys = sample_rows(args, rows)
+    nthr = host_threads()
+    osc = O.OracleScene(desc, bvh=True)
+    for _ in range(min(args.warmup, 1)):
+        cpu_leg(osc, cfg, args, ys[:1], O.FAITHFUL, threads=nthr)
+    rays, ms, threads = 0, 0.0, 1
     for k in range(args.steps):
-        r, m, threads = cpu_baseline(desc, cfg, args, rows, phase=0.37 * k)
+        r, m, threads, _ = cpu_leg(osc, cfg, args, ys, O.FAITHFUL, threads=nthr)
         rays += r
         ms += m
+    osc.close()
     value = rays / (ms * 1e-3) / 1e6
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+    line = {"impl": "reference", "metric": metric_name(args), "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / max(args.steps, 1),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": what, "width": args.width, "height": args.height, "spp": args.spp,
-                       "triangles": desc.triangle_count, "integrator": f"Pathtracer max_depth={args.max_depth} (NEE point lights" + (", cosine bounce, Philox keyed RNG)" if args.max_depth > 1 else ")")},
+            "config": bench_config(args, what, desc),
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "port",
-                             "sample": f"{rows} evenly spaced rows of the {args.width}x{args.height} frame per step, "
-                                       "pixel loop only (BVH build excluded), reference-faithful mode"},
+                             "sample": f"image rows {ys} of the {args.width}x{args.height} frame in every step (pixels of a row spread "
+                                       "over the threads), pixel loop only (BVH build excluded), reference-faithful mode",
+                             "host_threads_available": nthr},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+def bench_config(args, what, desc):
+    """`config` of the JSON line: derived from the arguments only, so both arms print the same object (the reference arm
+    renders a bounded sample of this workload; the sample is described under cpu_baseline.sample)."""
+    G, tile = args.gpus, 8
+    gather = {"host": "tiles stored by the trace kernel straight into a shared page-locked HOST frame (POSIX shm registered by every rank), no gather",
+              "peer": "tiles stored into rank 0's device frame by the trace kernel over NVLink (CUDA IPC), per-rank completion flags",
+              "nccl": "NCCL all_gather of RGBA8 tiles"}[args.gather]
+    return {"workload": what, "width": args.width, "height": args.height, "spp": args.spp, "triangles": desc.triangle_count,
+            "integrator": f"Pathtracer max_depth={args.max_depth} (NEE point lights" +
+                          (", cosine bounce, Philox keyed RNG)" if args.max_depth > 1 else ")"),
+            "parallelism": (f"image row-tiles of {tile} rows interleaved over {G} GPUs, scene replicated, " + gather) if G > 1
+                           else "one GPU, whole frame in one launch",
+            "l2": "GPU arm: flushed between timed iterations (256 MiB fill)", "traversal": args.traversal}
+
+
+def ncu_profile_name(args, G):
+    """profiles/ file that holds the `ncu --set full` summary of this exact bench command (tools/ncu_summary.py)."""
+    if G != 1:
+        return "r02_ncu_none.json"
+    if args.workload == "soup":
+        return "r02_ncu_soup.json"
+    return "r02_ncu_bounce.json" if args.max_depth > 1 else "r02_ncu_atrium.json"
 
 
 def run_ours(args):
@@ -228,7 +367,7 @@ def run_ours(args):
     opts = M.rayca_options(0x5EED, args.traversal, rank, G, tile, args.flags, 0)
     stream = torch.cuda.current_stream().cuda_stream
 
-    # N > 1, --gather peer (default): rank 0 owns the frame; every rank's trace kernel stores its tiles
+    # N > 1, --gather peer: rank 0 owns the frame; every rank's trace kernel stores its tiles
     # straight into it over NVLink (CUDA IPC mapping) and publishes a per-rank completion flag, rank 0
     # waits on the flags on its stream.  --gather nccl: local tiles + all_gather_into_tensor.
     frame, frame_id = None, [0]
@@ -488,46 +627,75 @@ def run_ours(args):
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
         achieved = algo_bytes / (kernel_ms * 1e-3) / 1e9
-        # the scene is L2-resident, so also report against the measured L2 -> SM read bandwidth
-        l2_peak = ctx.probe_read_bandwidth(24 << 20, 64)
-        # DRAM bytes of one launch from the committed `ncu --set full` capture of this command (None for other workloads)
-        traffic = None
+        # the hot set is L2 / L1 resident, so the governing memory bound is the L2 -> SM read path.
+        # Probe: 128-bit ld.global.cg (L1 bypassed) over a 64 MiB L2-resident buffer from all SMs; the physical
+        # ceiling is 148 SMs x 64 B/clk x f_SM, which the answer must not exceed.
+        l2_peak = ctx.probe_read_bandwidth(64 << 20, 32)
+        clk = sampler.summary()
+        l2_ceiling = 148 * 64 * float(clk.get("sm_max_mhz") or 1965.0) * 1e6 / 1e9
+        # what physically moved per launch: the committed `ncu --set full` summary of this exact command, if any
+        prof_name = ncu_profile_name(args, G)
+        phys, traffic, issue_pct, simt = None, None, None, None
         try:
-            prof = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_render_kernel_v4.json")))
-            if args.workload == "atrium" and (W, H, args.spp, args.max_depth, G) == (1920, 1080, 1, 1, 1):
-                traffic = prof["dram_bytes_per_launch"]
+            prof = json.load(open(os.path.join(ROOT, "profiles", prof_name)))
+            k0 = prof["launches"][0]
+
+            def num(key):
+                v, u = (k0[key].split() + [""])[:2]
+                return float(v) * {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1.0)
+
+            dur = num("gpu__time_duration.sum") * {"us": 1e-6, "ms": 1e-3, "ns": 1e-9}.get(k0["gpu__time_duration.sum"].split()[1], 1e-6)
+            l2_read = num("lts__t_sectors_srcunit_tex_op_read.sum") * 32.0
+            l1_read = num("l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum") * 32.0
+            dram = num("dram__bytes_read.sum") + num("dram__bytes_write.sum")
+            traffic = int(dram)
+            issue_pct = num("smsp__issue_active.avg.pct_of_peak_sustained_active")
+            simt = num("smsp__thread_inst_executed_per_inst_executed.ratio")
+            phys = {"source": "profiles/" + prof_name, "kernel_us_under_ncu": dur * 1e6,
+                    "l1_read_bytes": int(l1_read), "l2_to_l1_read_bytes": int(l2_read),
+                    "dram_read_bytes": int(num("dram__bytes_read.sum")), "dram_write_bytes": int(num("dram__bytes_write.sum")),
+                    "l2_gbs": l2_read / dur / 1e9, "l2_frac": l2_read / dur / 1e9 / l2_peak,
+                    "dram_gbs": dram / dur / 1e9, "dram_frac": dram / dur / 1e9 / hbm_peak,
+                    "logical_over_l2_bytes": algo_bytes / max(l2_read, 1.0)}
         except Exception:
             pass
-        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": G, "steps": args.steps,
+        line = {"metric": metric_name(args), "value": value, "unit": "Mrays/s", "n_gpus": G, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": what, "width": W, "height": H, "spp": args.spp,
-                           "triangles": desc.triangle_count, "integrator": f"Pathtracer max_depth={args.max_depth} (NEE point lights" + (", cosine bounce, Philox keyed RNG)" if args.max_depth > 1 else ")"),
-                           "parallelism": f"image row-tiles of {tile} rows interleaved over {G} GPU(s), scene replicated, " + ("tiles stored by the trace kernel straight into a shared page-locked HOST frame (POSIX shm registered by every rank), no gather" if host_mode else "tiles stored into rank 0's frame by the trace kernel over NVLink (CUDA IPC), per-rank completion flags" if peer else "NCCL all_gather of RGBA8"),
-                           "l2": "flushed between timed iterations (256 MiB fill)", "traversal": args.traversal},
+                "config": bench_config(args, what, desc),
                 "rays_per_frame": rays_frame, "kernel_ms": kernel_ms, "build_s": build_s,
-                "clocks": sampler.summary(), "gpu_launches": args.steps * (3 if peer else 1),  # peer: trace + flag signal + flag wait (rank 0)
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": traffic, "peak_source": "measured" if peaks else "fallback",
-                             "l2": {"peak": l2_peak, "frac": achieved / l2_peak, "unit": "GB/s",
-                                    "how": "streaming 128-bit reads over a 24 MiB (L2-resident) buffer, best of 5"},
+                "clocks": clk, "gpu_launches": args.steps * ((3 if rank == 0 else 2) if peer else 1),  # peer: trace + flag signal (+ flag wait on rank 0)
+                "roofline": {"bound": "l2", "achieved": achieved, "peak": l2_peak, "unit": "GB/s", "frac": achieved / l2_peak,
+                             "traffic": traffic, "peak_source": "measured in this run (rayca_cuda_probe_read_bandwidth: ld.global.cg "
+                                                                "over a 64 MiB L2-resident buffer, best of 5)",
+                             "peak_ceiling_148sm_x_64B_per_clk": l2_ceiling,
+                             "hbm": {"peak": hbm_peak, "frac_logical": achieved / hbm_peak,
+                                     "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+                                     "note": "logical bytes against HBM: not a roofline fraction (the bytes are served by L1 / L2), kept for continuity with round 1"},
                              "algorithmic_bytes_per_launch": int(algo_bytes),
-                             "note": "algorithmic bytes = 32 B per node record + 16 B per triangle plane + 48 B per triangle whose "
-                                     "vertices are fetched (counted by the kernel in a COUNT launch) + 4 B per pixel; the "
-                                     "262k-triangle scene is L2/L1-resident, so this can exceed the HBM peak: the kernel is "
-                                     "issue-bound, see profiles/"},
+                             "physical": phys, "issue_active_pct": issue_pct, "simt_lanes_per_instruction": simt,
+                             "governing": "issue slots (see issue_active_pct and profiles/): neither L2 nor HBM is near its peak in physical bytes",
+                             "note": "achieved = LOGICAL bytes per launch (32 B per node record + 16 B per triangle plane + 48 B per "
+                                     "triangle whose vertices are fetched, counted per lane by the kernel in a COUNT launch, + 4 B per "
+                                     "pixel) / kernel time; lanes of a warp that read the same record count it 32 times, L1 serves "
+                                     "most of them - `physical` holds the bytes ncu saw move (per launch, committed capture)"},
                 "e2e": e2e, "draw_e2e": draw_e2e, "frame_crc32": frame_crc,
                 "walk": {"node_records_per_ray": cst.node_bytes / 32 / max(rays_local_n, 1),
                          "triangle_bytes_per_ray": cst.triangle_bytes / max(rays_local_n, 1),
                          "algorithmic_bytes_per_ray": algo_bytes / max(rays_local_n, 1)}}
         if not args.no_cpu_baseline and G == 1:
-            rows = args.cpu_rows or 2
-            r, m, th = cpu_baseline(desc, cfg, args, rows)
-            line["cpu_baseline"] = {"value": r / (m * 1e-3) / 1e6, "unit": "Mrays/s", "cores": th, "kind": "port",
-                                    "sample": f"{rows} evenly spaced rows of the frame, pixel loop only, reference-faithful mode"}
-        print(json.dumps(line))
+            # the CUDA frame with its parity planes, through the reference-facing entry point, for the oracle comparison
+            g8, gaux, _ = dev.render(cfg, W, H, options=opts, want_aux=True)
+            line.update(cpu_legs(desc, cfg, args, args.cpu_rows or 8, gpu=(g8, gaux)))
+            bad = not line["parity_ok"]
+            print(json.dumps(line))
+            if bad:
+                sys.stderr.write("bench.py: the CUDA frame differs from the oracle (see parity_rows / parity_frame)\n")
+                sys.exit(3)
+        else:
+            print(json.dumps(line))
     for f in hframes:
         f.close()
     if G > 1:

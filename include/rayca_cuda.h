@@ -289,7 +289,8 @@ typedef struct rayca_options {
 enum {
     RAYCA_FLAG_COUNT_WALK = 1, /* also tally node / triangle records fetched (roofline accounting; slower) */
     RAYCA_FLAG_PERSISTENT = 2, /* persistent warps that pull 16x8 pixel groups from a global counter instead of
-                                  one thread block per group (default; faster on B200, see render.cuh) */
+                                  one thread block per group.  NOT the default: measured 15-20 % slower than the
+                                  static grid on B200 for the 1080p frames (render.cuh, profiles/r01_ab_registers_*) */
     RAYCA_FLAG_DIRECT_ROWS = 4 /* sharded launches (shard_count > 1): the output pointer addresses the FULL width x height
                                   frame and every owned pixel is stored at its final row-major position, instead of the
                                   shard's tiles packed one after the other — a frame all ranks can address (pinned host
@@ -351,8 +352,8 @@ int rayca_cuda_host_register(void* p, size_t bytes, void** device_view);
 int rayca_cuda_host_unregister(void* p);
 
 /* Measurement aid (bench.py): best-of-5 streaming read bandwidth over a `bytes` buffer read `reps` times with
- * 128-bit loads from all SMs.  A buffer well inside the 126 MB L2 gives the L2 -> SM read peak that bounds the
- * walk on L2-resident scenes; a buffer of several GB gives the HBM read peak. */
+ * 128-bit ld.global.cg loads (L1 bypassed) from all SMs.  A buffer well inside the 126 MB L2 gives the L2 -> SM
+ * read peak that bounds the walk on L2-resident scenes; a buffer of several GB gives the HBM read peak. */
 int rayca_cuda_probe_read_bandwidth(rayca_ctx* ctx, size_t bytes, uint32_t reps, double* gb_per_s);
 
 /* ---- Shared frame: the multi-GPU gather folded into the trace kernel's own stores ------------------------

@@ -18,13 +18,14 @@ _SO = os.path.join(_HERE, "_build", "librayca_oracle.so")
 
 FAITHFUL = 1
 COUNT = 2
+OPTIMISED = 4  # ordered, culled walk over a binned-SAH tree of pre-transformed triangles ("optimised CPU" arm)
 
 
 class rayca_oracle_stats(C.Structure):
     _fields_ = [("build_ms", C.c_double), ("trace_ms", C.c_double), ("rays_primary", C.c_uint64),
                 ("rays_shadow", C.c_uint64), ("rays_secondary", C.c_uint64), ("ord_nodes", C.c_uint64),
                 ("ord_tris", C.c_uint64), ("exh_nodes", C.c_uint64), ("exh_tris", C.c_uint64),
-                ("threads", C.c_uint32), ("reserved", C.c_uint32)]
+                ("threads", C.c_uint32), ("reserved", C.c_uint32), ("opt_build_ms", C.c_double)]
 
 
 def build(force: bool = False) -> str:

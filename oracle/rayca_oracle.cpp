@@ -116,6 +116,30 @@ struct Hit {
     Vec2 uv;
 };
 
+// "Optimised CPU" arm: what a tuned CPU renderer would run on the same scene —
+// ONE binned-SAH tree over the pre-transformed world-space triangles of every BLAS, walked front to back with
+// distance culling.  It is NOT the reference's algorithm (that is the exhaustive walk above); it exists so that the
+// GPU number can be read against a fair CPU implementation, and as a fast full-frame checker.  It returns the
+// reference's result by the same argument the CUDA product walk uses: a candidate counts only
+// if the exact slab test of its reference LEAF accepts the ray, ties go to the lowest (blas, primitive) index,
+// and the box test is conservative (1e-5 relative slack).
+struct OptNode {
+    float lo[3], hi[3];
+    uint32_t first, count; // count != 0: leaf over opt.prims[first, first+count); else children first, first+1
+};
+struct OptPrim {
+    Point3 v[3];
+    uint32_t blas;  // index into blas_nodes (TLAS order) = Hit::blas
+    uint32_t prim;  // Hit::primitive
+    const AABB* leaf; // bounds of the reference leaf that holds the primitive
+};
+struct OptTree {
+    std::vector<OptNode> nodes;
+    std::vector<OptPrim> prims;
+    double build_ms = 0;
+    uint32_t depth = 0;
+};
+
 struct Counters {
     uint64_t rays_primary = 0, rays_shadow = 0, rays_secondary = 0;
     uint64_t ord_nodes = 0, ord_tris = 0; // ordered, distance-culled traversal (algorithmic bytes model)
@@ -150,6 +174,8 @@ struct rayca_oracle_scene {
     TlasNode root;
     double build_ms = 0;
     std::string error;
+    OptTree* opt = nullptr; // built on the first RAYCA_ORACLE_OPTIMISED render
+    ~rayca_oracle_scene() { delete opt; }
 };
 
 namespace {
@@ -560,6 +586,7 @@ struct Tracer {
     bool faithful; // re-transform the three vertices on every test, as the reference does
     Counters* rays; // always valid: ray tallies
     Counters* cnt;  // non-null only when walk records are being counted
+    const OptTree* opt = nullptr; // non-null: the optimised arm answers the query
 
     // Sphere::intersects + intersects_impl (rayca-geometry/src/sphere.rs:101-163)
     __attribute__((noinline)) bool sphere_intersects(const Prim& p, const Ray& ray, float& t_out, Point3& pt, Vec2& uv) const {
@@ -747,8 +774,92 @@ struct Tracer {
         }
     }
 
+    // conservative slab on an optimised-tree box: [entry, exit] widened by 1e-5 relative, like the CUDA walk
+    static inline bool opt_slab(const OptNode& n, const Ray& ray, float& entry) {
+        const float ox = ray.origin.x, oy = ray.origin.y, oz = ray.origin.z;
+        const float t1x = (n.lo[0] - ox) * ray.rdir.x, t2x = (n.hi[0] - ox) * ray.rdir.x;
+        const float t1y = (n.lo[1] - oy) * ray.rdir.y, t2y = (n.hi[1] - oy) * ray.rdir.y;
+        const float t1z = (n.lo[2] - oz) * ray.rdir.z, t2z = (n.hi[2] - oz) * ray.rdir.z;
+        const float tmax = minf(minf(maxf(t1x, t2x), maxf(t1y, t2y)), maxf(t1z, t2z));
+        const float tmin = maxf(maxf(minf(t1x, t2x), minf(t1y, t2y)), minf(t1z, t2z));
+        entry = tmin - std::fabs(tmin) * 1.0e-5f;
+        const float ext = tmax + std::fabs(tmax) * 1.0e-5f;
+        return ext >= entry && ext >= 0.0f;
+    }
+
+    // Ordered, distance-culled closest hit over the optimised tree (see OptTree).
+    bool opt_intersects(const Ray& ray, Hit& out) const {
+        // a zero direction lane has rdir = 0 there: every reference box rejects the ray (SURVEY A-3)
+        if (ray.rdir.x == 0.0f || ray.rdir.y == 0.0f || ray.rdir.z == 0.0f) return false;
+        const OptTree& t = *opt;
+        float best_t = INFINITY;
+        uint64_t best_key = ~0ull;
+        const AABB* ok_leaf = nullptr;
+        struct Entry { uint32_t node; float d; };
+        Entry stack[128];
+        int sp = 0;
+        float e0;
+        if (t.nodes.empty() || !opt_slab(t.nodes[0], ray, e0)) return false;
+        uint32_t cur = 0;
+        for (;;) {
+            const OptNode& n = t.nodes[cur];
+            if (n.count) {
+                for (uint32_t i = n.first; i < n.first + n.count; ++i) {
+                    const OptPrim& p = t.prims[i];
+                    float tt;
+                    Point3 pt;
+                    Vec2 uv;
+                    if (!triangle_intersects_world(p.v[0], p.v[1], p.v[2], ray, tt, pt, uv)) continue;
+                    const uint64_t key = ((uint64_t)p.blas << 32) | p.prim;
+                    if (!(tt < best_t || (tt == best_t && key < best_key))) continue;
+                    if (p.leaf != ok_leaf) { // the reference tests the triangle iff its leaf box accepts the ray
+                        if (aabb_intersects(*p.leaf, ray) == F32_MAX) continue;
+                        ok_leaf = p.leaf;
+                    }
+                    best_t = tt;
+                    best_key = key;
+                    out.depth = tt;
+                    out.point = pt;
+                    out.uv = uv;
+                    out.blas = p.blas;
+                    out.primitive = p.prim;
+                }
+            } else {
+                float dl, dr;
+                uint32_t l = n.first, r = n.first + 1;
+                bool hl = opt_slab(t.nodes[l], ray, dl) && !(dl > best_t);
+                bool hr = opt_slab(t.nodes[r], ray, dr) && !(dr > best_t);
+                if (hl && hr) {
+                    if (dr < dl) { std::swap(l, r); std::swap(dl, dr); }
+                    if (sp < 128) stack[sp++] = {r, dr};
+                    cur = l;
+                    continue;
+                } else if (hl) {
+                    cur = l;
+                    continue;
+                } else if (hr) {
+                    cur = r;
+                    continue;
+                }
+            }
+            bool popped = false;
+            while (sp > 0) {
+                --sp;
+                if (stack[sp].d > best_t) continue;
+                cur = stack[sp].node;
+                popped = true;
+                break;
+            }
+            if (!popped) break;
+        }
+        if (best_key == ~0ull) return false;
+        out.ray = ray;
+        return true;
+    }
+
     // Tlas::intersects (tlas.rs:271-275)
     bool intersects(const Ray& ray, Hit& out) const {
+        if (opt) return opt_intersects(ray, out);
         bool found = tlas_node_intersects(s.root, ray, out);
         if (cnt) {
             float best_t = INFINITY;
@@ -760,6 +871,142 @@ struct Tracer {
         return found;
     }
 };
+
+
+// ------------------------------------------------------------- optimised-arm tree (see OptTree)
+// Binned SAH (16 bins on the centroid bounds, leaves of at most 4 triangles); a split that does not separate
+// anything, or a node deeper than 48 levels, falls back to the positional median, which bounds the depth.
+struct OptBuilder {
+    OptTree& t;
+    std::vector<Point3> cen;
+    std::vector<uint32_t> order; // permutation of t.prims being partitioned
+    std::vector<OptPrim> src;
+
+    static void grow3(float lo[3], float hi[3], const Point3& p) {
+        lo[0] = minf(lo[0], p.x); lo[1] = minf(lo[1], p.y); lo[2] = minf(lo[2], p.z);
+        hi[0] = maxf(hi[0], p.x); hi[1] = maxf(hi[1], p.y); hi[2] = maxf(hi[2], p.z);
+    }
+    void bounds(uint32_t first, uint32_t count, float lo[3], float hi[3]) const {
+        for (int k = 0; k < 3; ++k) { lo[k] = INFINITY; hi[k] = -INFINITY; }
+        for (uint32_t i = first; i < first + count; ++i)
+            for (int v = 0; v < 3; ++v) grow3(lo, hi, src[order[i]].v[v]);
+    }
+    static float half_area(const float lo[3], const float hi[3]) {
+        const float ex = hi[0] - lo[0], ey = hi[1] - lo[1], ez = hi[2] - lo[2];
+        return ex * ey + ey * ez + ez * ex;
+    }
+    void build(uint32_t node, uint32_t first, uint32_t count, uint32_t depth) {
+        OptNode& n0 = t.nodes[node];
+        bounds(first, count, n0.lo, n0.hi);
+        t.depth = std::max(t.depth, depth);
+        if (count <= 4) {
+            n0.first = first;
+            n0.count = count;
+            return;
+        }
+        float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (uint32_t i = first; i < first + count; ++i) grow3(clo, chi, cen[order[i]]);
+        constexpr int B = 16;
+        int best_axis = -1, best_plane = 0;
+        float best_cost = INFINITY;
+        if (depth < 48) {
+            for (int a = 0; a < 3; ++a) {
+                const float ext = chi[a] - clo[a];
+                if (!(ext > 0.0f)) continue;
+                uint32_t cnt[B] = {0};
+                float blo[B][3], bhi[B][3];
+                for (int b = 0; b < B; ++b)
+                    for (int k = 0; k < 3; ++k) { blo[b][k] = INFINITY; bhi[b][k] = -INFINITY; }
+                const float scale = (float)B / ext;
+                for (uint32_t i = first; i < first + count; ++i) {
+                    const Point3& c = cen[order[i]];
+                    const float cv = a == 0 ? c.x : (a == 1 ? c.y : c.z);
+                    int b = std::min(B - 1, std::max(0, (int)((cv - clo[a]) * scale)));
+                    cnt[b]++;
+                    for (int v = 0; v < 3; ++v) grow3(blo[b], bhi[b], src[order[i]].v[v]);
+                }
+                float ra[B];
+                uint32_t rc[B];
+                float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+                uint32_t c = 0;
+                for (int b = B - 1; b > 0; --b) {
+                    for (int k = 0; k < 3; ++k) { lo[k] = minf(lo[k], blo[b][k]); hi[k] = maxf(hi[k], bhi[b][k]); }
+                    c += cnt[b];
+                    ra[b] = c ? half_area(lo, hi) : 0.0f;
+                    rc[b] = c;
+                }
+                for (int k = 0; k < 3; ++k) { lo[k] = INFINITY; hi[k] = -INFINITY; }
+                c = 0;
+                for (int b = 0; b < B - 1; ++b) {
+                    for (int k = 0; k < 3; ++k) { lo[k] = minf(lo[k], blo[b][k]); hi[k] = maxf(hi[k], bhi[b][k]); }
+                    c += cnt[b];
+                    if (c == 0 || rc[b + 1] == 0) continue;
+                    const float cost = half_area(lo, hi) * (float)c + ra[b + 1] * (float)rc[b + 1];
+                    if (cost < best_cost) { best_cost = cost; best_axis = a; best_plane = b; }
+                }
+            }
+        }
+        uint32_t mid = first + count / 2;
+        if (best_axis >= 0) {
+            const int a = best_axis;
+            const float scale = (float)B / (chi[a] - clo[a]);
+            auto left = [&](uint32_t id) {
+                const Point3& c = cen[id];
+                const float cv = a == 0 ? c.x : (a == 1 ? c.y : c.z);
+                return std::min(B - 1, std::max(0, (int)((cv - clo[a]) * scale))) <= best_plane;
+            };
+            mid = (uint32_t)(std::partition(order.begin() + first, order.begin() + first + count, left) - order.begin());
+            if (mid == first || mid == first + count) mid = first + count / 2;
+        }
+        const uint32_t child = (uint32_t)t.nodes.size();
+        t.nodes.emplace_back();
+        t.nodes.emplace_back();
+        t.nodes[node].first = child;
+        t.nodes[node].count = 0;
+        build(child, first, mid - first, depth + 1);
+        build(child + 1, mid, first + count - mid, depth + 1);
+    }
+};
+
+// returns false when the scene holds spheres (the optimised arm covers triangle scenes)
+bool build_opt_tree(Scene& s) {
+    if (s.opt) return true;
+    auto t0 = std::chrono::steady_clock::now();
+    OptTree* t = new OptTree();
+    OptBuilder b{*t, {}, {}, {}};
+    for (uint32_t i = 0; i < s.blas_nodes.size(); ++i) {
+        const Blas& blas = s.blass[s.blas_nodes[i].blas];
+        if (blas.has_spheres) {
+            delete t;
+            return false;
+        }
+        for (const BvhNode& n : blas.nodes) {
+            if (!n.is_leaf()) continue;
+            for (uint32_t k = n.offset; k < n.offset + n.count; ++k) {
+                const Prim& p = blas.prims[k];
+                b.src.push_back(OptPrim{{p.wv[0], p.wv[1], p.wv[2]}, i, k, &n.bounds});
+            }
+        }
+    }
+    const uint32_t n = (uint32_t)b.src.size();
+    b.cen.resize(n);
+    b.order.resize(n);
+    for (uint32_t i = 0; i < n; ++i) {
+        const OptPrim& p = b.src[i];
+        b.cen[i] = Point3{(p.v[0].x + p.v[1].x + p.v[2].x) * (1.0f / 3.0f), (p.v[0].y + p.v[1].y + p.v[2].y) * (1.0f / 3.0f),
+                          (p.v[0].z + p.v[1].z + p.v[2].z) * (1.0f / 3.0f)};
+        b.order[i] = i;
+    }
+    t->nodes.reserve(n ? 2 * (size_t)n : 1);
+    t->nodes.emplace_back();
+    if (n) b.build(0, 0, n, 0);
+    else t->nodes.clear();
+    t->prims.resize(n);
+    for (uint32_t i = 0; i < n; ++i) t->prims[i] = b.src[b.order[i]];
+    t->build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    s.opt = t;
+    return true;
+}
 
 // ---------------------------------------------------------------------- shading
 
@@ -1828,10 +2075,13 @@ typedef struct rayca_oracle_stats {
     uint64_t rays_primary, rays_shadow, rays_secondary;
     uint64_t ord_nodes, ord_tris; // ordered + culled traversal record counts (algorithmic bytes model)
     uint64_t exh_nodes, exh_tris; // exhaustive (reference) traversal record counts
-    uint32_t threads, reserved;
+    uint32_t threads, reserved; // threads = host threads that actually rendered pixels in this call
+    double opt_build_ms;        // RAYCA_ORACLE_OPTIMISED: build time of the optimised-arm tree (once per scene)
 } rayca_oracle_stats;
 
-enum { RAYCA_ORACLE_FAITHFUL = 1, RAYCA_ORACLE_COUNT = 2 };
+// FAITHFUL: re-transform the vertices on every test like the reference; COUNT: tally walk records;
+// OPTIMISED: answer closest-hit queries with the ordered, culled walk over the optimised-arm tree (OptTree)
+enum { RAYCA_ORACLE_FAITHFUL = 1, RAYCA_ORACLE_COUNT = 2, RAYCA_ORACLE_OPTIMISED = 4 };
 
 int rayca_oracle_scene_create(const rayca_scene_desc* desc, uint32_t bvh, rayca_oracle_scene** out) {
     if (!desc || !out) return RAYCA_E_INVALID_ARG;
@@ -1968,19 +2218,31 @@ int rayca_oracle_render(rayca_oracle_scene* s, const rayca_config* config, const
 #else
     int nthreads = 1;
 #endif
+    const OptTree* opt = nullptr;
+    if (flags & RAYCA_ORACLE_OPTIMISED) {
+        if (!build_opt_tree(*s)) return RAYCA_E_UNSUPPORTED;
+        opt = s->opt;
+    }
     std::vector<Counters> counters((size_t)nthreads);
+    std::vector<uint32_t> worked((size_t)nthreads, 0u);
     int status = 0;
     auto t0 = std::chrono::steady_clock::now();
-#pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads)
-    for (int64_t yy_ = row_begin; yy_ < (int64_t)row_end; ++yy_) {
-        uint32_t y = (uint32_t)yy_;
+    // The reference fans out over rows AND pixels (`par_iter_mut` on both, rayca-soft/src/scene.rs:117-122): one task
+    // per pixel.  Here: one flat pixel index, handed out in chunks of 16 pixels.
+    const int64_t px_begin = (int64_t)row_begin * width, px_end = (int64_t)row_end * width;
+#pragma omp parallel num_threads(nthreads)
+    {
 #ifdef _OPENMP
-        Counters* cnt = &counters[(size_t)omp_get_thread_num()];
+        const size_t tid = (size_t)omp_get_thread_num();
 #else
-        Counters* cnt = &counters[0];
+        const size_t tid = 0;
 #endif
-        Renderer r{*s, cfg, Tracer{*s, (flags & RAYCA_ORACLE_FAITHFUL) != 0, cnt, (flags & RAYCA_ORACLE_COUNT) ? cnt : nullptr}};
-        for (uint32_t x = 0; x < width; ++x) {
+        Counters* cnt = &counters[tid];
+        Renderer r{*s, cfg, Tracer{*s, (flags & RAYCA_ORACLE_FAITHFUL) != 0, cnt, (flags & RAYCA_ORACLE_COUNT) ? cnt : nullptr, opt}};
+#pragma omp for schedule(dynamic, 16) nowait
+        for (int64_t p_ = px_begin; p_ < px_end; ++p_) {
+            worked[tid] = 1;
+            const uint32_t y = (uint32_t)(p_ / width), x = (uint32_t)(p_ % width);
             Color color = BLACK;
             Hit primary;
             bool hit_any = false;
@@ -2037,7 +2299,9 @@ int rayca_oracle_render(rayca_oracle_scene* s, const rayca_config* config, const
         std::memset(stats, 0, sizeof(*stats));
         stats->build_ms = s->build_ms;
         stats->trace_ms = ms;
-        stats->threads = (uint32_t)nthreads;
+        stats->threads = 0; // threads that actually rendered pixels (not the size of the pool)
+        for (uint32_t w : worked) stats->threads += w;
+        stats->opt_build_ms = opt ? opt->build_ms : 0.0;
         for (const Counters& c : counters) {
             stats->rays_primary += c.rays_primary;
             stats->rays_shadow += c.rays_shadow;

@@ -17,6 +17,10 @@
 #define RHD inline
 #endif
 
+#ifndef RAYCA_SHADE_OPT
+#define RAYCA_SHADE_OPT 0
+#endif
+
 namespace rb {
 
 constexpr float kF32Eps = 1.1920929e-07f;          // f32::EPSILON
@@ -74,7 +78,13 @@ RHD V3 normalize(V3 a) {
     return a;
 }
 // vec3.rs:195-216 — zero lanes give a ZERO reciprocal, never an infinity
+#if defined(__CUDA_ARCH__) && RAYCA_SHADE_OPT
+// rcp.rn.f32 is the correctly rounded reciprocal, i.e. the very value of the IEEE division 1.0f / d, without the
+// general division's quotient refinement (make_ray runs three of these per ray)
+RHD float recip_lane(float d) { return d == 0.0f ? 0.0f : __frcp_rn(d); }
+#else
 RHD float recip_lane(float d) { return d == 0.0f ? 0.0f : 1.0f / d; }
+#endif
 RHD V3 reciprocal(V3 a) { return V3{recip_lane(a.x), recip_lane(a.y), recip_lane(a.z)}; }
 // vec3.rs:219-221
 RHD V3 reflect(V3 v, V3 n) {

@@ -21,21 +21,38 @@ __device__ __forceinline__ Col ld_col(const float* p) { return Col{p[0], p[1], p
 // Rust `as u32`: saturating, NaN -> 0
 __device__ __forceinline__ uint32_t f32_as_u32(float f) { return __float2uint_rz(f); }
 
+#if RAYCA_SHADE_OPT
+// (float)t / 255.0f for a byte t, in three instructions: q = t * r with r = RN(1/255), one residual step
+// q' = fma(fma(-q, 255, t), r, q).  Equal to the IEEE quotient for ALL 256 inputs (checked exhaustively with exact
+// rational arithmetic in tests/test_oracle_kat.py::test_byte_over_255_identity); the general division is ~10
+// instructions plus a slow path, and a shaded pixel converts twelve texel channels.
+__device__ __forceinline__ float byte_to_unit(unsigned char t) {
+    const float ft = (float)t, r = 0x1.010102p-8f;
+    const float q = ft * r;
+    return __fmaf_rn(__fmaf_rn(-q, 255.0f, ft), r, q);
+}
+// x % n: a mask when n is a power of two (every glTF texture of the fixtures is), the general remainder otherwise
+__device__ __forceinline__ uint32_t wrap_index(uint32_t x, uint32_t n) { return (n & (n - 1u)) == 0u ? (x & (n - 1u)) : (x % n); }
+#else
+__device__ __forceinline__ float byte_to_unit(unsigned char t) { return (float)t / 255.0f; }
+__device__ __forceinline__ uint32_t wrap_index(uint32_t x, uint32_t n) { return x % n; }
+#endif
+
 // Sampler::sample — nearest, repeat, no filtering, no sRGB decode
 __device__ __forceinline__ Col sample_image(const GpuSceneView& s, int image, float uvx, float uvy) {
     const GpuImage im = s.images[image];
     float x = (uvx - floorf(uvx) + 1.0f) * (float)im.width;
     float y = (uvy - floorf(uvy) + 1.0f) * (float)im.height;
-    uint32_t xi = f32_as_u32(x) % im.width;
-    uint32_t yi = f32_as_u32(y) % im.height;
+    uint32_t xi = wrap_index(f32_as_u32(x), im.width);
+    uint32_t yi = wrap_index(f32_as_u32(y), im.height);
     size_t idx = (size_t)yi * im.width + xi;
     const unsigned char* base = s.texels + im.offset;
     if (im.color_type == RAYCA_COLOR_RGBA8) {
         uchar4 t = __ldg(reinterpret_cast<const uchar4*>(base) + idx);
-        return Col{(float)t.x / 255.0f, (float)t.y / 255.0f, (float)t.z / 255.0f, (float)t.w / 255.0f};
+        return Col{byte_to_unit(t.x), byte_to_unit(t.y), byte_to_unit(t.z), byte_to_unit(t.w)};
     } else if (im.color_type == RAYCA_COLOR_RGB8) {
         const unsigned char* p = base + idx * 3;
-        return Col{(float)__ldg(p) / 255.0f, (float)__ldg(p + 1) / 255.0f, (float)__ldg(p + 2) / 255.0f, 255.0f / 255.0f};
+        return Col{byte_to_unit(__ldg(p)), byte_to_unit(__ldg(p + 1)), byte_to_unit(__ldg(p + 2)), 255.0f / 255.0f};
     } else {
         float4 t = __ldg(reinterpret_cast<const float4*>(base) + idx);
         return Col{t.x / 255.0f, t.y / 255.0f, t.z / 255.0f, t.w / 255.0f}; // color/mod.rs:222-231

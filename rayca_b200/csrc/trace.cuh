@@ -22,6 +22,9 @@
 namespace rb {
 
 constexpr int kStackSize = 96;
+#ifndef RAYCA_SMEM_STACK
+#define RAYCA_SMEM_STACK 0
+#endif
 
 struct RayD {
     V3 o, d, rd;
@@ -218,6 +221,55 @@ constexpr float kSlabTol = 1.0e-5f;
 // child reference: bit31 leaf, bits 28..30 count-1, bit 27 the leaf holds spheres, bits 0..26 first record
 constexpr uint32_t kLeafFlag = 0x80000000u, kSphereFlag = 0x08000000u;
 
+#ifndef RAYCA_FOLD_TOL
+#define RAYCA_FOLD_TOL 0
+#endif
+#if RAYCA_FOLD_TOL
+// The relative widening of the interval is FOLDED into the per-ray constants: the near planes use rd (1 - tol') and
+// a_near (1 - tol'), the far planes rd (1 + tol') and a_far (1 + tol'), so a box costs 6 LOP3 + 6 FFMA + 2 FMNMX3 and
+// nothing else.  Why this accepts everything the explicit form `fma(|t|, -/+tol, t)` accepted:
+//   * tn = max_i v_i.  If tn > 0 the maximum is attained by a positive lane and scaling every lane by (1 - tol')
+//     scales the maximum; negative lanes move towards zero but stay negative, and a negative entry distance is never
+//     compared with anything but `exit >= entry` (true whenever exit >= 0) and `entry > best` (false).
+//   * tf = min_i f_i.  If every far lane is >= 0 the minimum scales by (1 + tol'); if one is negative the box is
+//     behind the origin and both forms reject.
+//   * the products rd (1 -/+ tol') and a (1 -/+ tol') are rounded (2^-24 relative, and p*rd, a can each be as large as
+//     |o*rd| while their sum is small), so the per-axis bound e doubles to 2^-21 |o*rd| and tol' = 1.1e-5 > 1e-5.
+struct FastRay {
+    float rnx, rny, rnz; // rd (1 - tol')
+    float rfx, rfy, rfz; // rd (1 + tol')
+    float anx, any, anz; // near-plane addend  (RN(-o*rd) - e)(1 - tol')
+    float afx, afy, afz; // far-plane addend   (RN(-o*rd) + e)(1 + tol')
+    uint32_t sx, sy, sz; // rd < 0 ? ~0 : 0
+};
+__device__ __forceinline__ float pick(uint32_t m, float a, float b) { // m ? a : b on the bit patterns
+    return __uint_as_float((__float_as_uint(a) & m) | (__float_as_uint(b) & ~m));
+}
+__device__ __forceinline__ FastRay make_fast_ray(const RayD& r) {
+    FastRay f;
+    constexpr float kLo = 1.0f - 1.1e-5f, kHi = 1.0f + 1.1e-5f;
+    f.rnx = r.rd.x * kLo; f.rny = r.rd.y * kLo; f.rnz = r.rd.z * kLo;
+    f.rfx = r.rd.x * kHi; f.rfy = r.rd.y * kHi; f.rfz = r.rd.z * kHi;
+    const float nx = -(r.o.x * r.rd.x), ny = -(r.o.y * r.rd.y), nz = -(r.o.z * r.rd.z);
+    const float ex = fabsf(nx) * 4.76837158203125e-07f, ey = fabsf(ny) * 4.76837158203125e-07f,
+                ez = fabsf(nz) * 4.76837158203125e-07f; // 2^-21
+    f.anx = (nx - ex) * kLo; f.any = (ny - ey) * kLo; f.anz = (nz - ez) * kLo;
+    f.afx = (nx + ex) * kHi; f.afy = (ny + ey) * kHi; f.afz = (nz + ez) * kHi;
+    asm("shr.s32 %0, %1, 31;" : "=r"(f.sx) : "r"(__float_as_int(r.rd.x)));
+    asm("shr.s32 %0, %1, 31;" : "=r"(f.sy) : "r"(__float_as_int(r.rd.y)));
+    asm("shr.s32 %0, %1, 31;" : "=r"(f.sz) : "r"(__float_as_int(r.rd.z)));
+    return f;
+}
+// returns "may intersect"; entry <= the exact slab entry distance of the same box whenever that is positive
+__device__ __forceinline__ bool slab_fast(const float4 lo, const float4 hi, const FastRay& f, float& entry) {
+    const float tn = fmaxf(fmaxf(__fmaf_rn(pick(f.sx, hi.x, lo.x), f.rnx, f.anx), __fmaf_rn(pick(f.sy, hi.y, lo.y), f.rny, f.any)),
+                           __fmaf_rn(pick(f.sz, hi.z, lo.z), f.rnz, f.anz));
+    const float tf = fminf(fminf(__fmaf_rn(pick(f.sx, lo.x, hi.x), f.rfx, f.afx), __fmaf_rn(pick(f.sy, lo.y, hi.y), f.rfy, f.afy)),
+                           __fmaf_rn(pick(f.sz, lo.z, hi.z), f.rfz, f.afz));
+    entry = tn;
+    return tf >= tn && tf >= 0.0f;
+}
+#else
 struct FastRay {
     float rdx, rdy, rdz;
     float anx, any, anz; // near-plane addend  RN(-o*rd) - e
@@ -255,6 +307,8 @@ __device__ __forceinline__ bool slab_fast(const float4 lo, const float4 hi, cons
     const float ext = __fmaf_rn(fabsf(tf), kSlabTol, tf);
     return ext >= entry && ext >= 0.0f;
 }
+
+#endif // RAYCA_FOLD_TOL
 
 // SPHERES: the scene holds sphere primitives (kernel instantiation MODE 3); triangle-only scenes run the
 // instantiation without the sphere leaf code (it costs 6 % on the atrium frame when compiled in).
@@ -323,7 +377,35 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
     }
     constexpr uint32_t kDone = 0xFFFFFFFFu; // leaf flag set: leaves the node loop like any leaf reference
     // {child reference, entry distance}; slot 0 holds the sentinel (distance -inf is never culled), the last
-    // slot absorbs pushes beyond kStackSize entries (the count saturates, as before those are dropped)
+    // slot absorbs pushes beyond kStackSize entries (the count saturates; scene_create refuses trees that deep)
+#if RAYCA_SMEM_STACK > 0
+    // The first RAYCA_SMEM_STACK slots of every thread live in SHARED memory, [slot][thread] so that a warp's
+    // accesses to one slot are 256 contiguous bytes (no bank conflicts); deeper slots spill to the local array,
+    // which a well-built tree touches rarely.  With the whole stack in local memory every resident thread owned
+    // 784 B of it, 119 MB per GPU — more than L2 keeps next to the scene — and the evictions showed up as 334 MB
+    // of DRAM writes per 1080p frame (profiles/r01_ncu_render_kernel_v4.json).
+    constexpr int kSm = RAYCA_SMEM_STACK;
+    __shared__ uint2 s_stack[kSm][128];
+    uint2 stack[kStackSize + 2 - kSm];
+    const uint32_t tid = threadIdx.x;
+    s_stack[0][tid] = make_uint2(kDone, 0xff800000u);
+    int sp = 1;
+    uint32_t cur = go ? s.fast_root_ref : kDone;
+    auto push = [&](uint32_t ref, float dist) {
+        const uint2 e = make_uint2(ref, __float_as_uint(dist));
+        if (sp < kSm) s_stack[sp][tid] = e;
+        else stack[sp - kSm] = e;
+        sp = min(sp + 1, kStackSize + 1);
+    };
+    auto pop = [&]() -> uint32_t { // next entry whose entry distance does not exceed the best depth
+        uint2 e;
+        do {
+            --sp;
+            e = sp < kSm ? s_stack[sp][tid] : stack[sp - kSm];
+        } while (__uint_as_float(e.y) > best_t);
+        return e.x;
+    };
+#else
     uint2 stack[kStackSize + 2];
     stack[0] = make_uint2(kDone, 0xff800000u);
     int sp = 1;
@@ -339,6 +421,7 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
         } while (__uint_as_float(e.y) > best_t);
         return e.x;
     };
+#endif
     for (;;) {
         // inner nodes: descend to the nearer accepted child, push the farther one
         while (!(cur & kLeafFlag)) {
@@ -437,7 +520,7 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
                 const uint32_t id = __float_as_uint(q1.w);
                 if (ANY) {
                     if (ref_leaf_accepts(__float_as_uint(q2.w))) found = true;
-                } else if (t < best_t || (id < best && best != 0xFFFFFFFFu)) { // here t <= best_t
+                } else if (t < best_t || (t == best_t && id < best && best != 0xFFFFFFFFu)) { // a NaN t never replaces a hit (strict `<`, blas.rs:150)
                     if (ref_leaf_accepts(__float_as_uint(q2.w))) {
                         best_t = t;
                         best = id;
