@@ -502,8 +502,8 @@ class Scene:
         self.root.children.append(len(self.nodes) - 1)
         return len(self.nodes) - 1
 
-    def push_gltf_from_path(self, path) -> int:
-        return self.push_model(load_gltf_path(path))
+    def push_gltf_from_path(self, path, image_hook=None) -> int:
+        return self.push_model(load_gltf_path(path, image_hook=image_hook))
 
     def push_sdtf_from_path(self, path):
         model, config = load_sdtf_path(path)
@@ -752,23 +752,79 @@ def _decompose(mat16):
     return translation.astype(f32), np.array(q, dtype=f32), np.array([sx, sy, sz], dtype=f32)
 
 
-def load_gltf_path(path) -> Model:
-    """Model::load_gltf_path (rayca-model/src/loader/gltf.rs:256-299)."""
+def _read_glb(data: bytes):
+    """Binary glTF container (glTF 2.0 spec 4.4): 12-byte header `glTF`, version 2, total length; then chunks
+    {u32 length, u32 type, payload} — the first is JSON (0x4E4F534A), the optional second BIN (0x004E4942).
+    Returns (json dict, bin chunk or None).  The reference leaves this case `unimplemented!()`
+    (rayca-model/src/loader/gltf.rs:239-241, buffer `Source::Bin`); SURVEY 8(f) rank 4 asks for it."""
+    import struct
+
+    if len(data) < 20 or data[:4] != b"glTF":
+        raise ValueError("not a GLB container")
+    version, total = struct.unpack_from("<II", data, 4)
+    if version != 2 or total > len(data):
+        raise ValueError(f"unsupported GLB (version {version}, length {total} of {len(data)})")
+    off, doc, blob = 12, None, None
+    while off + 8 <= total:
+        n, kind = struct.unpack_from("<II", data, off)
+        payload = data[off + 8: off + 8 + n]
+        if len(payload) != n:
+            raise ValueError("truncated GLB chunk")
+        if kind == 0x4E4F534A and doc is None:
+            doc = json.loads(payload.decode("utf-8"))
+        elif kind == 0x004E4942 and blob is None:
+            blob = payload
+        off += 8 + n  # chunk lengths are multiples of 4 (spec 4.4.3)
+    if doc is None:
+        raise ValueError("GLB without a JSON chunk")
+    return doc, blob
+
+
+def load_gltf_path(path, image_hook=None) -> Model:
+    """Model::load_gltf_path (rayca-model/src/loader/gltf.rs:256-299).  Also reads `.glb` containers, buffers without
+    a `uri` (the GLB BIN chunk) and images stored in a bufferView — the `Source::Bin` / `Source::View` cases the
+    reference leaves unimplemented (gltf.rs:239-241,318-324).
+    `image_hook(uri_or_None, load)` (fixtures only) may replace an image: `load()` decodes the original."""
     path = os.fspath(path)
     parent = os.path.dirname(path)
     with open(path, "rb") as f:
-        g = json.load(f)
+        raw = f.read()
+    glb_bin = None
+    if raw[:4] == b"glTF":
+        g, glb_bin = _read_glb(raw)
+    else:
+        g = json.loads(raw.decode("utf-8"))
 
     def load_uri(uri, prefix):
-        if uri.startswith(prefix):
-            return base64.b64decode(uri[len(prefix):])
+        if uri.startswith("data:"):
+            head, _, payload = uri.partition(",")
+            if not head.endswith(";base64"):
+                raise ValueError("only base64 data URIs are supported")
+            return base64.b64decode(payload)
         with open(os.path.join(parent, uri), "rb") as fh:
             return fh.read()
+
+    def load_buffer(b):
+        if "uri" in b:
+            return load_uri(b["uri"], "data:application/octet-stream;base64,")
+        if glb_bin is None:
+            raise ValueError("buffer without a uri outside a GLB container")
+        return glb_bin  # Source::Bin
+
+    buffers = [load_buffer(b) for b in g.get("buffers", [])]
+
+    def view_bytes(index):
+        view = g["bufferViews"][index]
+        o = view.get("byteOffset", 0)
+        return bytes(buffers[view["buffer"]][o:o + view["byteLength"]])
 
     m = Model()
     # load_images (gltf.rs:306-350)
     for gi in g.get("images", []):
-        m.images.append(_decode_image(load_uri(gi["uri"], "data:image/png;base64,")))
+        def load(gi=gi):
+            data = load_uri(gi["uri"], "data:image/png;base64,") if "uri" in gi else view_bytes(gi["bufferView"])
+            return _decode_image(data)
+        m.images.append(image_hook(gi.get("uri"), load) if image_hook else load())
     # load_textures (gltf.rs:352-362)
     for gt in g.get("textures", []):
         m.textures.append(Texture(gt["source"]))
@@ -786,8 +842,6 @@ def load_gltf_path(path) -> Model:
             p.metallic_roughness = pbr["metallicRoughnessTexture"]["index"]
         m.pbr_materials.append(p)
         m.materials.append(Material(MATERIAL_PBR, len(m.pbr_materials) - 1))
-
-    buffers = [load_uri(b["uri"], "data:application/octet-stream;base64,") for b in g.get("buffers", [])]
 
     def read_accessor(index):
         acc = g["accessors"][index]
