@@ -119,6 +119,83 @@ def glass_scene():
     return s
 
 
+def normalquad_scene():
+    """Row a12 (normal mapping): a 2 x 2 quad with tangents, bitangents and three textures — albedo, metallic /
+    roughness, and a procedural NORMAL map of overlapping ripples — under a rotated, non-uniformly scaled node, so
+    that PbrMaterial::get_normal (rayca-model/src/material/pbr.rs:94-123), Mat3::tbn (rayca-math/src/mat3.rs:57-65)
+    and the tangent / bitangent transforms of BvhPrimitive (rayca-soft/src/bvh/primitive.rs:209-226) all take part.
+    The uv range (0..1.5) wraps the sampler."""
+    n = 64
+    yy, xx = np.mgrid[0:n, 0:n].astype(np.float64)
+    hx = 0.45 * np.cos(2 * np.pi * xx / 16.0) + 0.25 * np.sin(2 * np.pi * (xx + 2 * yy) / 21.0)
+    hy = 0.45 * np.sin(2 * np.pi * yy / 12.0) + 0.25 * np.cos(2 * np.pi * (xx - yy) / 17.0)
+    nz = np.sqrt(np.maximum(1.0 - np.minimum(hx * hx + hy * hy, 0.95), 0.05))
+    nrm = np.stack([hx, hy, nz], axis=-1)
+    normal_tex = np.concatenate([np.clip((nrm * 0.5 + 0.5) * 255.0 + 0.5, 0, 255), np.full((n, n, 1), 255.0)], axis=-1).astype(np.uint8)
+    albedo = np.zeros((32, 32, 3), dtype=np.uint8)
+    cy, cx = np.mgrid[0:32, 0:32]
+    albedo[..., 0] = 120 + 100 * (((cx // 4) + (cy // 4)) % 2)
+    albedo[..., 1] = 90 + 5 * cx
+    albedo[..., 2] = 200 - 4 * cy
+    mr = np.zeros((16, 16, 4), dtype=np.uint8)
+    my, mx = np.mgrid[0:16, 0:16]
+    mr[..., 0] = 60 + 12 * mx      # roughness = R
+    mr[..., 2] = 16 * ((my // 4) % 2) * 8  # metallic = B
+    mr[..., 3] = 255
+    m = M.Model()
+    m.images = [M.Image(32, 32, M.COLOR_RGB8, np.ascontiguousarray(albedo)), M.Image(n, n, M.COLOR_RGBA8, np.ascontiguousarray(normal_tex)),
+                M.Image(16, 16, M.COLOR_RGBA8, np.ascontiguousarray(mr))]
+    m.textures = [M.Texture(0), M.Texture(1), M.Texture(2)]
+    m.pbr_materials.append(M.PbrMaterial(color=(0.9, 0.85, 0.8, 1.0), albedo=0, normal=1, metallic_factor=1.0, roughness_factor=1.0,
+                                         metallic_roughness=2))
+    m.materials.append(M.Material(M.MATERIAL_PBR, 0))
+    pos = [[-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0]]
+    uv = [[0, 1.5], [1.5, 1.5], [1.5, 0], [0, 0]]
+    # a slightly tilted tangent frame per vertex (not orthonormal on purpose: the reference does not re-orthogonalise)
+    nor = [[0, 0, 1], [0.1, 0, 0.995], [0, 0.1, 0.995], [-0.1, -0.1, 0.99]]
+    tan = [[1, 0, 0], [0.995, 0, -0.1], [1, 0.05, 0], [0.99, 0, 0.1]]
+    bit = [[0, 1, 0], [0, 1, 0.02], [0, 0.995, -0.1], [0.03, 0.99, 0.1]]
+    verts = M.make_vertices(pos, normal=nor, uv=uv, tangent=tan, bitangent=bit)
+    m.geometries.append(M.TriangleMesh(verts, np.array([0, 1, 2, 0, 2, 3], dtype=np.uint32)))
+    m.primitives.append(M.Primitive(0, 0))
+    m.meshes.append(M.Mesh([0]))
+    q = np.array([0.18, -0.25, 0.07, 0.0], dtype=f32)
+    q[3] = np.sqrt(f32(1.0) - (q[:3] * q[:3]).sum())
+    m.nodes.append(M.Node(mesh=0, trs=M.Trs(translation=np.array([0.1, -0.2, 0.5], dtype=f32), rotation=q,
+                                            scale=np.array([1.4, 0.9, 1.0], dtype=f32))))
+    m.root.children.append(0)
+    s = M.Scene()
+    s.push_model(m)
+    s.push_model(M.create_default_model())
+    return s
+
+
+def flighthelmet_scene():
+    """rayca-soft/tests/gltf.rs:296-317 `flight`: FlightHelmet.gltf (94,722 triangles with the asset's own tangents, six
+    PBR materials with albedo + NORMAL + metallic/roughness maps) and the default model with its camera moved to
+    (0, 0.32, 1).  Two reductions keep the fixture committable: every texture is point-subsampled to 256 x 256
+    (stride 8 / 4, no filtering), and the three leather textures missing from the reference checkout
+    (.MISSING_LARGE_BLOBS) are replaced by flat 4 x 4 textures (albedo grey-brown, normal (0,0,1),
+    occlusion/rough/metal (255, 160, 0))."""
+    def hook(uri, load):
+        try:
+            im = load()
+        except FileNotFoundError:
+            flat = {"BaseColor": (150, 110, 80, 255), "Normal": (128, 128, 255, 255)}
+            c = next((v for k, v in flat.items() if k in (uri or "")), (255, 160, 0, 255))
+            return M.Image(4, 4, M.COLOR_RGBA8, np.ascontiguousarray(np.tile(np.array(c, dtype=np.uint8), (4, 4, 1))))
+        st = max(1, im.width // 256)
+        d = np.ascontiguousarray(im.data[::st, ::st])
+        return M.Image(d.shape[1], d.shape[0], im.color_type, d)
+
+    s = M.Scene()
+    s.push_gltf_from_path(os.path.join(ASSETS, "flight-helmet/FlightHelmet.gltf"), image_hook=hook)
+    dm = M.create_default_model()
+    dm.get_mut_last_camera().trs.translation = np.array([0.0, 0.32, 1.0], dtype=f32)
+    s.push_model(dm)
+    return s
+
+
 def scale_root(f):
     def tweak(s, h):
         s.nodes[h].trs.scale = (s.nodes[h].trs.scale * np.array(f, dtype=f32)).astype(f32)
@@ -155,6 +232,11 @@ SCENES = {
     "cubes_over_plane": (cubes_over_plane_scene, {"pt1": (PT1, 128, 128), "rt3": (RT3, 96, 96), "sc3": (SC3, 96, 96), "pt3": (dict(integrator=IntegratorStrategy.Pathtracer, max_depth=3), 64, 64),
                                                   # branching bounces under point-light NEE (PBR materials, cosine sampler)
                                                   "pt3_ls2": (dict(integrator=IntegratorStrategy.Pathtracer, max_depth=3, light_samples=2), 64, 64)}),
+    # normal-mapped shading (row a12 had no oracle evidence): a synthetic quad with a tilted tangent frame
+    # under a rotated / scaled node, and the reference's own `flight` test scene
+    "normalquad": (normalquad_scene, {"pt1": (PT1, 128, 128), "rt0": (RT0, 96, 96), "pt2": (PT2, 64, 64),
+                                      "pt1_spp4": (dict(PT1, samples_per_pixel=4), 64, 64)}),
+    "flighthelmet": (flighthelmet_scene, {"pt1": (PT1, 128, 128), "rt2": (dict(integrator=IntegratorStrategy.Raytracer, max_depth=2), 64, 64)}),
     "suzanne": (lambda: gltf_scene("suzanne/suzanne.gltf"), {"pt1": (PT1, 128, 128), "rt0": (RT0, 96, 96), "pt2": (PT2, 64, 64)}),
     # Scratcher (integrator/scratcher.rs): the reference's own fixture, the transmission branch, reflections
     "scratcher_sphere": (scratcher_sphere_scene, {"nobvh": (dict(integrator=IntegratorStrategy.Scratcher, bvh=False), 128, 128),
