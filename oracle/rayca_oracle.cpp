@@ -264,6 +264,30 @@ struct Flattener {
     }
 };
 
+// Sphere::{get_center,get_radius,min,max,get_centroid} (rayca-geometry/src/sphere.rs:72-93,165-181)
+void sphere_world_bounds(Prim& p, const Trs& trs) {
+    Point3 c = transform_point(trs, p.center);
+    float r = p.radius * maxf(maxf(maxf(trs.scale.x, trs.scale.y), trs.scale.z), 0.0f); // reduce_max over 4 lanes, w = 0
+    p.wcentroid = to_vec3(c);
+    p.wmin = c - Vec3{r, r, r};
+    p.wmax = c + Vec3{r, r, r};
+}
+
+// Triangle::{get_vertex,get_centroid,min,max} (rayca-geometry/src/triangle.rs:59-82,161-181): the cache of what the
+// reference recomputes per query
+void triangle_world_bounds(Prim& p, const Trs& trs) {
+    for (int k = 0; k < 3; ++k) p.wv[k] = transform_point(trs, p.v[k]);
+    p.wcentroid = transform_vec(trs, p.centroid);
+    Point3 mn{F32_MAX, F32_MAX, F32_MAX}, mx{F32_MIN, F32_MIN, F32_MIN};
+    for (int k = 0; k < 3; ++k) {
+        mn = {minf(mn.x, p.wv[k].x), minf(mn.y, p.wv[k].y), minf(mn.z, p.wv[k].z)};
+        mx = {maxf(mx.x, p.wv[k].x), maxf(mx.y, p.wv[k].y), maxf(mx.z, p.wv[k].z)};
+    }
+    p.wmin = mn;
+    p.wmax = mx;
+}
+
+
 // bvh/primitive.rs:194-237 for one mesh node
 void emit_mesh_prims(Scene& s, const rayca_scene_desc& d, uint32_t model_index, uint32_t node_local, uint32_t trs_key,
                      std::vector<Prim>& out) {
@@ -286,12 +310,7 @@ void emit_mesh_prims(Scene& s, const rayca_scene_desc& d, uint32_t model_index, 
             p.model = model_index;
             p.material = prim.material;
             p.src = (uint32_t)out.size();
-            // Sphere::{get_center,get_radius,min,max} (sphere.rs:72-93,169-181)
-            Point3 c = transform_point(trs, p.center);
-            float r = p.radius * maxf(maxf(maxf(trs.scale.x, trs.scale.y), trs.scale.z), 0.0f); // reduce_max over 4 lanes, w = 0
-            p.wcentroid = to_vec3(c);
-            p.wmin = c - Vec3{r, r, r};
-            p.wmax = c + Vec3{r, r, r};
+            sphere_world_bounds(p, trs);
             out.push_back(p);
             continue;
         }
@@ -313,16 +332,7 @@ void emit_mesh_prims(Scene& s, const rayca_scene_desc& d, uint32_t model_index, 
             p.model = model_index;
             p.material = prim.material;
             p.src = (uint32_t)out.size();
-            // cache of per-query recomputation
-            for (int k = 0; k < 3; ++k) p.wv[k] = transform_point(trs, p.v[k]);
-            p.wcentroid = transform_vec(trs, p.centroid);
-            Point3 mn{F32_MAX, F32_MAX, F32_MAX}, mx{F32_MIN, F32_MIN, F32_MIN};
-            for (int k = 0; k < 3; ++k) {
-                mn = {minf(mn.x, p.wv[k].x), minf(mn.y, p.wv[k].y), minf(mn.z, p.wv[k].z)};
-                mx = {maxf(mx.x, p.wv[k].x), maxf(mx.y, p.wv[k].y), maxf(mx.z, p.wv[k].z)};
-            }
-            p.wmin = mn;
-            p.wmax = mx;
+            triangle_world_bounds(p, trs);
             out.push_back(p);
         }
     }
@@ -2360,6 +2370,64 @@ int rayca_oracle_kat_triangle(const float verts[9], const rayca_trs* trs, const 
         out[0] = tt; out[1] = uv.x; out[2] = uv.y; out[3] = p.x; out[4] = p.y; out[5] = p.z;
     }
     return hit ? 1 : 0;
+}
+// returns 1 on hit; out = {t, px, py, pz} (Sphere::intersects, rayca-geometry/src/sphere.rs:101-163)
+int rayca_oracle_kat_sphere(const float center[3], float radius, const rayca_trs* trs, const float o[3], const float d[3], float out[4]) {
+    Scene s;
+    s.world_trs.push_back(to_trs(*trs));
+    Prim p{};
+    p.sphere = true;
+    p.center = {center[0], center[1], center[2]};
+    p.radius = radius;
+    p.radius2 = radius * radius;
+    p.trs = 0;
+    Counters c;
+    Tracer tr{s, false, &c, nullptr};
+    float t;
+    Point3 pt;
+    Vec2 uv;
+    bool hit = tr.sphere_intersects(p, make_ray(Point3{o[0], o[1], o[2]}, Vec3{d[0], d[1], d[2]}), t, pt, uv);
+    if (hit) {
+        out[0] = t; out[1] = pt.x; out[2] = pt.y; out[3] = pt.z;
+    }
+    return hit ? 1 : 0;
+}
+// out = {min.xyz, max.xyz, centroid.xyz}
+void rayca_oracle_kat_sphere_bounds(const float center[3], float radius, const rayca_trs* trs, float out[9]) {
+    Prim p{};
+    p.sphere = true;
+    p.center = {center[0], center[1], center[2]};
+    p.radius = radius;
+    sphere_world_bounds(p, to_trs(*trs));
+    out[0] = p.wmin.x; out[1] = p.wmin.y; out[2] = p.wmin.z; out[3] = p.wmax.x; out[4] = p.wmax.y; out[5] = p.wmax.z;
+    out[6] = p.wcentroid.x; out[7] = p.wcentroid.y; out[8] = p.wcentroid.z;
+}
+// Sphere::get_model_normal (sphere.rs:95-97) as the shading path evaluates it
+void rayca_oracle_kat_sphere_normal(const float center[3], const float point[3], float out[3]) {
+    Vec3 n = normalized(Point3{point[0], point[1], point[2]} - Point3{center[0], center[1], center[2]});
+    out[0] = n.x; out[1] = n.y; out[2] = n.z;
+}
+// out = {min.xyz, max.xyz, centroid.xyz} of a triangle under `trs`
+void rayca_oracle_kat_triangle_bounds(const float verts[9], const rayca_trs* trs, float out[9]) {
+    Prim p{};
+    for (int k = 0; k < 3; ++k) p.v[k] = {verts[3 * k], verts[3 * k + 1], verts[3 * k + 2]};
+    p.centroid = ((to_vec3(p.v[0]) + to_vec3(p.v[1])) + to_vec3(p.v[2])) * 0.3333f; // Triangle::new (triangle.rs:59-62)
+    triangle_world_bounds(p, to_trs(*trs));
+    out[0] = p.wmin.x; out[1] = p.wmin.y; out[2] = p.wmin.z; out[3] = p.wmax.x; out[4] = p.wmax.y; out[5] = p.wmax.z;
+    out[6] = p.wcentroid.x; out[7] = p.wcentroid.y; out[8] = p.wcentroid.z;
+}
+// &Inversed<Trs> * Vec3 (rayca-math/src/trs.rs:383-403): translate by -t, rotate by q^-1, scale by 1/s — the operation
+// sequence inverse_transform_ray applies to a ray's origin and direction
+void rayca_oracle_kat_trs_inverse_vec(const rayca_trs* t, const float v[3], float out[3]) {
+    Trs trs = to_trs(*t);
+    Vec3 r = Vec3{v[0], v[1], v[2]} + (trs.translation * -1.0f);
+    r = rotate(r, conjugate(trs.rotation));
+    r = r * reciprocal(trs.scale);
+    out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+void rayca_oracle_kat_trs_vec(const rayca_trs* t, const float v[3], float out[3]) {
+    Vec3 r = transform_vec(to_trs(*t), Vec3{v[0], v[1], v[2]});
+    out[0] = r.x; out[1] = r.y; out[2] = r.z;
 }
 float rayca_oracle_kat_aabb(const float a[3], const float b[3], const float o[3], const float d[3]) {
     AABB box{{a[0], a[1], a[2]}, {b[0], b[1], b[2]}};

@@ -173,3 +173,88 @@ def test_keyed_rng_is_deterministic_and_uniform(oracle):
     assert a == b and all(0.0 <= x < 1.0 for x in a)
     assert abs(np.mean(a) - 0.5) < 0.03
     assert lib.rayca_oracle_kat_rng(0x5EED, 1, 0, 0, 0) != lib.rayca_oracle_kat_rng(0x5EED, 1, 0, 0, 1)
+
+
+def f9(*v):
+    return (C.c_float * 9)(*v)
+
+
+def test_sphere_intersects(oracle):
+    """rayca-geometry/src/sphere.rs:186-203 `intersect`: unit sphere at the origin is hit from inside along +x, missed
+    from (2,0,0) along +x; a sphere at (4,0,0) is missed by a ray along -z."""
+    lib = oracle.lib()
+    out = f4()
+    ident = trs()
+    assert lib.rayca_oracle_kat_sphere(f3(0, 0, 0), C.c_float(1.0), C.byref(ident), f3(0, 0, 0), f3(1, 0, 0), out) == 1
+    assert abs(out[0] - 1.0) < 1e-6 and abs(out[1] - 1.0) < 1e-6  # leaves the sphere at x = 1
+    assert lib.rayca_oracle_kat_sphere(f3(0, 0, 0), C.c_float(1.0), C.byref(ident), f3(2, 0, 0), f3(1, 0, 0), out) == 0
+    assert lib.rayca_oracle_kat_sphere(f3(4, 0, 0), C.c_float(1.0), C.byref(ident), f3(0, 0, 0), f3(0, 0, -1), out) == 0
+
+
+def test_sphere_min_max_centroid(oracle):
+    """rayca-geometry/src/sphere.rs:205-215 `min_max_and_centroid` (exact equality in the reference)."""
+    out = f9()
+    ident = trs()
+    oracle.lib().rayca_oracle_kat_sphere_bounds(f3(1, 2, 3), C.c_float(2.0), C.byref(ident), out)
+    assert out[:] == [-1.0, 0.0, 1.0, 3.0, 4.0, 5.0, 1.0, 2.0, 3.0]
+
+
+def test_sphere_normal(oracle):
+    """rayca-geometry/src/sphere.rs:217-223 `get_normal`."""
+    out = f3()
+    oracle.lib().rayca_oracle_kat_sphere_normal(f3(0, 0, 0), f3(0, 1, 0), out)
+    assert np.linalg.norm(np.array(out[:]) - np.array([0.0, 1.0, 0.0])) < 1e-6
+
+
+def test_triangle_centroid_min_max(oracle):
+    """rayca-geometry/src/triangle.rs:578-593 `centroid_and_min_max`: Triangle::default() = (-1,0,0), (1,0,0), (0,1,0);
+    centroid within 1e-3 of (a+b+c)*0.3333, min / max exact."""
+    out = f9()
+    ident = trs()
+    oracle.lib().rayca_oracle_kat_triangle_bounds(f9(-1, 0, 0, 1, 0, 0, 0, 1, 0), C.byref(ident), out)
+    assert out[0:3] == [-1.0, 0.0, 0.0] and out[3:6] == [1.0, 1.0, 0.0]
+    want = np.array([0.0, 1.0, 0.0], dtype=np.float32) * np.float32(0.3333)
+    assert np.linalg.norm(np.array(out[6:9], dtype=np.float32) - want) < 1e-3
+
+
+def _roundtrip(oracle, t, v):
+    fwd, back = f3(), f3()
+    oracle.lib().rayca_oracle_kat_trs_vec(C.byref(t), f3(*v), fwd)
+    oracle.lib().rayca_oracle_kat_trs_inverse_vec(C.byref(t), fwd, back)
+    return np.array(back[:], dtype=np.float32)
+
+
+def test_trs_inversion(oracle):
+    """rayca-math/src/trs.rs:505-553 `inverse_trs_{translation,scale,rotation}_only`, `inverse_trs_full`:
+    &inv * (&trs * v) is close to v (Vec3::close: every lane within EPS)."""
+    s2 = float(np.sqrt(np.float32(0.5)))
+    rot_z90 = (0.0, 0.0, s2, s2)  # Quat::axis_angle(Z, FRAC_PI_2)
+    cases = [(trs(t=(1, 2, 3)), (4, 5, 6)), (trs(s=(2, 3, 4)), (8, 9, 12)), (trs(q=rot_z90), (1, 0, 0)),
+             (trs(t=(1, 2, 3), q=rot_z90, s=(2, 2, 2)), (1, 1, 1))]
+    for t, v in cases:
+        got = _roundtrip(oracle, t, v)
+        assert np.all(np.abs(got - np.array(v, dtype=np.float32)) < EPS), (v, got)
+
+
+def test_byte_over_255_identity():
+    """shade.cuh::byte_to_unit: q = t * r, q' = fma(fma(-q, 255, t), r, q) with r = RN(1/255) equals the correctly
+    rounded t / 255 for every byte t (exact rational arithmetic; the CUDA path relies on it for bit parity of texels)."""
+    from fractions import Fraction
+
+    def rn(fr):
+        x = np.float32(float(fr))
+        best = None
+        for c in (np.nextafter(x, np.float32(-np.inf)), x, np.nextafter(x, np.float32(np.inf))):
+            d = abs(Fraction(float(c)) - fr)
+            even = (int(np.float32(c).view(np.uint32)) & 1) == 0
+            if best is None or d < best[0] or (d == best[0] and even):
+                best = (d, np.float32(c))
+        return best[1]
+
+    r = np.float32(float.fromhex("0x1.010102p-8"))
+    assert r == rn(Fraction(1, 255))
+    for t in range(256):
+        q = rn(Fraction(t) * Fraction(float(r)))
+        rem = rn(Fraction(t) - Fraction(float(q)) * 255)
+        q2 = rn(Fraction(float(rem)) * Fraction(float(r)) + Fraction(float(q)))
+        assert q2 == rn(Fraction(t, 255)) == np.float32(t) / np.float32(255.0), t
