@@ -92,3 +92,85 @@ def test_product_does_not_import_the_oracle():
                 text = open(os.path.join(root, f)).read()
                 for needle in ("import oracle", "from oracle", "librayca_oracle", "rayca_oracle_", "oracle_math"):
                     assert needle not in text, f"{f} references the oracle ({needle})"
+
+
+def test_header_compiles_as_c_and_layout_is_pinned(tmp_path):
+    """include/rayca_cuda.h compiles as plain C11 and every struct has the layout tests/abi_layout.c freezes with
+    _Static_asserts; the offsets / sizes the C compiler reports equal the ctypes mirror field by field (what the
+    #[repr(C)] structs of rayca-cuda/src/ffi.rs must reproduce too)."""
+    import subprocess
+
+    exe = tmp_path / "abi_layout"
+    cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc"
+    subprocess.check_call([cc, "-std=c11", "-Wall", "-Werror", "-pedantic", "-o", str(exe), os.path.join(ROOT, "tests", "abi_layout.c")])
+    lines = subprocess.check_output([str(exe)], text=True).split("\n")
+    seen = set()
+    for ln in lines:
+        if not ln:
+            continue
+        name, field, off, size = ln.split()
+        seen.add(name)
+        if name == "rayca_vertex":
+            assert int(size) == M.VERTEX_FLOATS * 4
+            continue
+        t = getattr(M, name)
+        if field == ".":
+            assert C.sizeof(t) == int(size), name
+        else:
+            d = getattr(t, field)
+            assert (d.offset, d.size) == (int(off), int(size)), f"{name}.{field}"
+    # every struct the header typedefs is covered (opaque handles excepted)
+    text = open(os.path.join(ROOT, "include", "rayca_cuda.h")).read()
+    declared = set(re.findall(r"typedef struct (rayca_[a-z_]+) \{", text))
+    assert declared == seen, declared ^ seen
+
+
+def test_glb_container_and_embedded_buffers(tmp_path):
+    """the harness loader reads binary glTF (.glb), buffers without a uri (the BIN chunk,
+    `Source::Bin` — `unimplemented!()` in rayca-model/src/loader/gltf.rs:239-241) and images stored in a bufferView;
+    the model equals the one loaded from the equivalent .gltf with base64 data URIs."""
+    import base64
+    import io
+    import json
+    import struct
+
+    from PIL import Image as PILImage
+
+    pos = np.array([[-1, 0, 0], [1, 0, 0], [0, 1, 0]], dtype=np.float32)
+    uv = np.array([[0, 0], [1, 0], [0.5, 1]], dtype=np.float32)
+    idx = np.array([0, 1, 2], dtype=np.uint16)
+    png = io.BytesIO()
+    PILImage.fromarray((np.arange(4 * 4 * 3) % 251).astype(np.uint8).reshape(4, 4, 3), "RGB").save(png, format="PNG")
+    png = png.getvalue()
+    parts = [pos.tobytes(), uv.tobytes(), idx.tobytes() + b"\0\0", png + b"\0" * ((4 - len(png) % 4) % 4)]
+    offs = np.cumsum([0] + [len(p) for p in parts])
+    blob = b"".join(parts)
+    doc = {"asset": {"version": "2.0"}, "scenes": [{"nodes": [0]}], "nodes": [{"mesh": 0, "translation": [0, 0.5, 0]}],
+           "meshes": [{"primitives": [{"attributes": {"POSITION": 0, "TEXCOORD_0": 1}, "indices": 2, "material": 0}]}],
+           "materials": [{"pbrMetallicRoughness": {"baseColorTexture": {"index": 0}, "metallicFactor": 0.0}}],
+           "textures": [{"source": 0}], "images": [{"bufferView": 3, "mimeType": "image/png"}],
+           "buffers": [{"byteLength": len(blob)}],
+           "bufferViews": [{"buffer": 0, "byteOffset": int(offs[0]), "byteLength": 36}, {"buffer": 0, "byteOffset": int(offs[1]), "byteLength": 24},
+                           {"buffer": 0, "byteOffset": int(offs[2]), "byteLength": 6}, {"buffer": 0, "byteOffset": int(offs[3]), "byteLength": len(png)}],
+           "accessors": [{"bufferView": 0, "componentType": 5126, "count": 3, "type": "VEC3"},
+                         {"bufferView": 1, "componentType": 5126, "count": 3, "type": "VEC2"},
+                         {"bufferView": 2, "componentType": 5123, "count": 3, "type": "SCALAR"}]}
+    js = json.dumps(doc).encode()
+    js += b" " * ((4 - len(js) % 4) % 4)
+    glb = b"glTF" + struct.pack("<II", 2, 12 + 8 + len(js) + 8 + len(blob)) + struct.pack("<II", len(js), 0x4E4F534A) + js + \
+        struct.pack("<II", len(blob), 0x004E4942) + blob
+    (tmp_path / "tri.glb").write_bytes(glb)
+    doc2 = json.loads(json.dumps(doc))
+    doc2["buffers"][0]["uri"] = "data:application/octet-stream;base64," + base64.b64encode(blob).decode()
+    doc2["images"][0] = {"uri": "data:image/png;base64," + base64.b64encode(png).decode()}
+    (tmp_path / "tri.gltf").write_text(json.dumps(doc2))
+    a, b = M.load_gltf_path(tmp_path / "tri.glb"), M.load_gltf_path(tmp_path / "tri.gltf")
+    for m in (a, b):
+        assert len(m.geometries) == 1 and len(m.images) == 1 and m.images[0].width == 4 and m.pbr_materials[0].albedo == 0
+    assert np.array_equal(a.geometries[0].vertices, b.geometries[0].vertices)
+    assert np.array_equal(a.geometries[0].indices, b.geometries[0].indices)
+    assert np.array_equal(a.images[0].data, b.images[0].data)
+    assert np.array_equal(a.geometries[0].vertices[:, :3], pos)
+    (tmp_path / "bad.glb").write_bytes(b"glTF" + struct.pack("<II", 1, 12) + b"\0" * 8)
+    with pytest.raises(ValueError):
+        M.load_gltf_path(tmp_path / "bad.glb")
