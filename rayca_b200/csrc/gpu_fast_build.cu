@@ -1099,6 +1099,27 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
 }
 
 
+// AoS sibling pairs {lo0.xyz ref0 | hi0.xyz - | lo1.xyz ref1 | hi1.xyz -} -> plane-major
+// {lo0.x lo1.x hi0.x hi1.x | lo0.y lo1.y hi0.y hi1.y | lo0.z lo1.z hi0.z hi1.z | ref0 ref1 w0 w1}, in place (trace.cuh,
+// RAYCA_SOA_PAIRS): one thread per pair reads its 64 bytes and writes them back.
+__global__ void transpose_pairs_kernel(float4* __restrict__ rec, size_t pairs) {
+    const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= pairs) return;
+    float4* q = rec + 4 * p;
+    const float4 a0 = q[0], a1 = q[1], b0 = q[2], b1 = q[3];
+    q[0] = make_float4(a0.x, b0.x, a1.x, b1.x);
+    q[1] = make_float4(a0.y, b0.y, a1.y, b1.y);
+    q[2] = make_float4(a0.z, b0.z, a1.z, b1.z);
+    q[3] = make_float4(a0.w, b0.w, a1.w, b1.w);
+}
+
+int transpose_pairs_device(void* d_nodes, size_t node_count, cudaStream_t st) {
+    const size_t pairs = node_count / 2;
+    if (pairs == 0) return RAYCA_OK;
+    transpose_pairs_kernel<<<(unsigned)((pairs + 255) / 256), 256, 0, st>>>(reinterpret_cast<float4*>(d_nodes), pairs);
+    return cudaGetLastError() == cudaSuccess ? RAYCA_OK : RAYCA_E_CUDA;
+}
+
 int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::string& err, float* device_ms) {
     const uint32_t N = (uint32_t)blas.tris.size();
     if (N == 0) { err = "no primitives"; return RAYCA_E_INVALID_ARG; }

@@ -24,6 +24,10 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
 // asks the caller to use the host builder (a level broader than the device work lists).
 int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t stream, std::string& err, float* device_ms);
 
+// In-place AoS -> plane-major transposition of the sibling-pair records (the layout the walk reads when the library is
+// built with RAYCA_SOA_PAIRS, see trace.cuh).  `node_count` 32-byte records, i.e. node_count / 2 pairs.
+int transpose_pairs_device(void* d_nodes, size_t node_count, cudaStream_t stream);
+
 // tunables shared with the host builder (fast_bvh.cpp)
 void fast_tree_tunables(int& bins, uint32_t& leaf_max, float& traversal_cost);
 

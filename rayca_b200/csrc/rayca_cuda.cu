@@ -66,6 +66,7 @@ struct rayca_scene {
     void* d_blas_prim_offset = nullptr;
     void* d_fast_nodes = nullptr;
     void* d_fast_tri = nullptr;
+    size_t fast_node_count = 0; // 32-byte records in d_fast_nodes
     GpuSceneView view{};
     uint32_t max_stack = 0;
 };
@@ -316,6 +317,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     if (host_fast_tree) {
         UP(d_fast_nodes, fast_nodes);
         UP(d_fast_tri, fast_tri);
+        s->fast_node_count = h.fast_nodes.size();
     } else {
         FastTreeDevice ft;
         rc = build_fast_tree_device(h, (const float4*)s->d_tri_pos, ctx->render_stream, ft, err);
@@ -325,6 +327,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         }
         s->d_fast_nodes = ft.nodes;
         s->d_fast_tri = ft.tri;
+        s->fast_node_count = (size_t)h.blas_prim_offset.back() * 2 + 2;
         h.fast_root = ft.root;
         h.fast_depth = ft.depth;
         h.max_stack = std::max(h.max_stack, ft.depth + 2);
@@ -337,6 +340,17 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         }
     }
 #undef UP
+#if RAYCA_SOA_PAIRS
+    if (s->fast_node_count * sizeof(GpuNode) >= (1ull << 32)) { // the walk addresses pair records with 32-bit byte offsets
+        rayca_cuda_scene_destroy(s);
+        return fail(RAYCA_E_UNSUPPORTED, "performance tree larger than 4 GiB");
+    }
+    if (transpose_pairs_device(s->d_fast_nodes, s->fast_node_count & ~size_t(1), ctx->render_stream) != RAYCA_OK ||
+        cudaStreamSynchronize(ctx->render_stream) != cudaSuccess) {
+        rayca_cuda_scene_destroy(s);
+        return fail(RAYCA_E_CUDA, "transposing the pair records");
+    }
+#endif
     GpuSceneView& v = s->view;
     v.nodes = (const float4*)s->d_nodes;
     v.tri_pos = (const float4*)s->d_tri_pos;

@@ -224,6 +224,17 @@ constexpr uint32_t kLeafFlag = 0x80000000u, kSphereFlag = 0x08000000u;
 #ifndef RAYCA_FOLD_TOL
 #define RAYCA_FOLD_TOL 0
 #endif
+// RAYCA_SOA_PAIRS: sibling pairs are stored plane-major — {lo0.x lo1.x hi0.x hi1.x | y | z | ref0 ref1 - -}, 64 bytes —
+// so the near / far planes of BOTH children are one 64-bit load each at a per-ray offset (0 or 8 bytes into the
+// axis' quad, chosen once from the sign of rd): the 12 LOP3 selects per visited pair (the hottest source line of the
+// round-1 kernel, 13 % of its samples) become address arithmetic.  The records are transposed on the device after the
+// build (gpu_fast_build.cu::transpose_pairs_device).
+#ifndef RAYCA_SOA_PAIRS
+#define RAYCA_SOA_PAIRS 0
+#endif
+#if RAYCA_SOA_PAIRS && !RAYCA_FOLD_TOL
+#error "RAYCA_SOA_PAIRS needs RAYCA_FOLD_TOL (the pair test reads the folded per-ray constants)"
+#endif
 #if RAYCA_FOLD_TOL
 // The relative widening of the interval is FOLDED into the per-ray constants: the near planes use rd (1 - tol') and
 // a_near (1 - tol'), the far planes rd (1 + tol') and a_far (1 + tol'), so a box costs 6 LOP3 + 6 FFMA + 2 FMNMX3 and
@@ -258,14 +269,45 @@ __device__ __forceinline__ FastRay make_fast_ray(const RayD& r) {
     asm("shr.s32 %0, %1, 31;" : "=r"(f.sx) : "r"(__float_as_int(r.rd.x)));
     asm("shr.s32 %0, %1, 31;" : "=r"(f.sy) : "r"(__float_as_int(r.rd.y)));
     asm("shr.s32 %0, %1, 31;" : "=r"(f.sz) : "r"(__float_as_int(r.rd.z)));
+#if RAYCA_SOA_PAIRS
+    f.sx = f.sx & 8u;          // near planes of x: lo at +0 (rd > 0) or hi at +8 (rd < 0); the far planes sit at offset ^ 8
+    f.sy = 16u + (f.sy & 8u);
+    f.sz = 32u + (f.sz & 8u);
+#endif
     return f;
 }
+#if RAYCA_SOA_PAIRS
+__device__ __forceinline__ float2 ldg_f2(const char* base, uint32_t off) {
+    return __ldg(reinterpret_cast<const float2*>(base + off));
+}
+// both children of the pair at byte offset `pair` of `nodes`: entry distances d0 / d1, "may intersect" h0 / h1, references
+__device__ __forceinline__ void slab_pair(const char* nodes, uint32_t pair, const FastRay& f, float& d0, float& d1, bool& h0, bool& h1,
+                                          uint32_t& c0, uint32_t& c1) {
+    const float2 nx = ldg_f2(nodes, pair + f.sx), fx = ldg_f2(nodes, pair + (f.sx ^ 8u));
+    const float2 ny = ldg_f2(nodes, pair + f.sy), fy = ldg_f2(nodes, pair + (f.sy ^ 8u));
+    const float2 nz = ldg_f2(nodes, pair + f.sz), fz = ldg_f2(nodes, pair + (f.sz ^ 8u));
+    const uint2 refs = __ldg(reinterpret_cast<const uint2*>(nodes + (pair + 48u)));
+    d0 = fmaxf(fmaxf(__fmaf_rn(nx.x, f.rnx, f.anx), __fmaf_rn(ny.x, f.rny, f.any)), __fmaf_rn(nz.x, f.rnz, f.anz));
+    d1 = fmaxf(fmaxf(__fmaf_rn(nx.y, f.rnx, f.anx), __fmaf_rn(ny.y, f.rny, f.any)), __fmaf_rn(nz.y, f.rnz, f.anz));
+    const float e0 = fminf(fminf(__fmaf_rn(fx.x, f.rfx, f.afx), __fmaf_rn(fy.x, f.rfy, f.afy)), __fmaf_rn(fz.x, f.rfz, f.afz));
+    const float e1 = fminf(fminf(__fmaf_rn(fx.y, f.rfx, f.afx), __fmaf_rn(fy.y, f.rfy, f.afy)), __fmaf_rn(fz.y, f.rfz, f.afz));
+    h0 = e0 >= d0 && e0 >= 0.0f;
+    h1 = e1 >= d1 && e1 >= 0.0f;
+    c0 = refs.x;
+    c1 = refs.y;
+}
+#endif
 // returns "may intersect"; entry <= the exact slab entry distance of the same box whenever that is positive
 __device__ __forceinline__ bool slab_fast(const float4 lo, const float4 hi, const FastRay& f, float& entry) {
-    const float tn = fmaxf(fmaxf(__fmaf_rn(pick(f.sx, hi.x, lo.x), f.rnx, f.anx), __fmaf_rn(pick(f.sy, hi.y, lo.y), f.rny, f.any)),
-                           __fmaf_rn(pick(f.sz, hi.z, lo.z), f.rnz, f.anz));
-    const float tf = fminf(fminf(__fmaf_rn(pick(f.sx, lo.x, hi.x), f.rfx, f.afx), __fmaf_rn(pick(f.sy, lo.y, hi.y), f.rfy, f.afy)),
-                           __fmaf_rn(pick(f.sz, lo.z, hi.z), f.rfz, f.afz));
+#if RAYCA_SOA_PAIRS
+    const uint32_t mx = 0u - ((f.sx >> 3) & 1u), my = 0u - ((f.sy >> 3) & 1u), mz = 0u - ((f.sz >> 3) & 1u); // root box only
+#else
+    const uint32_t mx = f.sx, my = f.sy, mz = f.sz;
+#endif
+    const float tn = fmaxf(fmaxf(__fmaf_rn(pick(mx, hi.x, lo.x), f.rnx, f.anx), __fmaf_rn(pick(my, hi.y, lo.y), f.rny, f.any)),
+                           __fmaf_rn(pick(mz, hi.z, lo.z), f.rnz, f.anz));
+    const float tf = fminf(fminf(__fmaf_rn(pick(mx, lo.x, hi.x), f.rfx, f.afx), __fmaf_rn(pick(my, lo.y, hi.y), f.rfy, f.afy)),
+                           __fmaf_rn(pick(mz, lo.z, hi.z), f.rfz, f.afz));
     entry = tn;
     return tf >= tn && tf >= 0.0f;
 }
@@ -425,6 +467,15 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
     for (;;) {
         // inner nodes: descend to the nearer accepted child, push the farther one
         while (!(cur & kLeafFlag)) {
+#if RAYCA_SOA_PAIRS
+            if (COUNT) wc->nodes += 2;
+            float d0, d1;
+            bool h0, h1;
+            uint32_t c0, c1;
+            slab_pair(reinterpret_cast<const char*>(fast_nodes), cur * 32u, fr, d0, d1, h0, h1, c0, c1);
+            h0 = h0 && !(d0 > best_t);
+            h1 = h1 && !(d1 > best_t);
+#else
             const float4* np = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(fast_nodes) + (unsigned long long)cur * 32ull);
             const float4 a0 = __ldg(np + 0), a1 = __ldg(np + 1), b0 = __ldg(np + 2), b1 = __ldg(np + 3);
             if (COUNT) wc->nodes += 2;
@@ -434,6 +485,7 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
             h0 = h0 && !(d0 > best_t);
             h1 = h1 && !(d1 > best_t);
             uint32_t c0 = __float_as_uint(a0.w), c1 = __float_as_uint(b0.w);
+#endif
             if (h0 && h1) {
                 if (d1 < d0) {
                     float td = d0; d0 = d1; d1 = td;
