@@ -414,6 +414,23 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
                       uint8_t* rgba8_out, const rayca_aux_out* aux /*nullable*/,
                       rayca_stats* stats /*nullable*/);
 
+/* Allocation-free render.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as rayca_cuda_render(ctx, scene, config, options, width, height, rgba8_out, NULL, stats) — the same
+ * kernel — but everything the launch needs beyond the scene lives in ONE file-scope `static __device__` array inside
+ * the library: the kernel's ray counters (256 bytes, cleared by every call) followed by the RGBA8 staging plane the
+ * kernel stores into before it is copied to `rgba8_out` (HOST memory, pageable or pinned).  The call performs no
+ * cudaMalloc / cudaFree / cudaHostAlloc and calls no allocating library routine; the array's device address is
+ * resolved once per device with cudaGetSymbolAddress, with that device current.
+ * Limits: width * height * 4 <= RAYCA_STATIC_FRAME_BYTES (8 MiB: up to 1920 x 1080), else RAYCA_E_INVALID_ARG; no aux
+ * planes; no sharding (options->shard_count <= 1).  Every GPU that loads the library holds the 8 MiB + 256 B array
+ * until the process exits.  ALL calls on one device share the array and it keeps the previous call's contents: calls
+ * that overlap on the GPU (two contexts or two host threads on the same device) race — serialise them. */
+#define RAYCA_STATIC_FRAME_BYTES (8u << 20)
+int rayca_cuda_render_static(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config,
+                             const rayca_options* options /*nullable*/, uint32_t width, uint32_t height,
+                             uint8_t* rgba8_out, rayca_stats* stats /*nullable*/);
+
 /* Same, but every output pointer is DEVICE memory on the context's device and the
  * work is enqueued on `cuda_stream` (a cudaStream_t; NULL = default stream)
  * without synchronising: the multi-GPU caller gathers tiles with NCCL afterwards. */

@@ -993,3 +993,87 @@ int rayca_cuda_scene_bvh_read(rayca_scene* s, float* nodes, uint32_t* blas_node_
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// rayca_cuda_render_static — the allocation-free render (include/rayca_cuda.h; no counterpart in the
+// reference).
+//
+// The launch's scratch — the kernel's ray counters, which must start at zero, and the RGBA8 plane the kernel stores
+// into before the frame is copied to the caller's host buffer — lives in ONE file-scope device array instead of
+// cudaMalloc'ed memory.  In host code `g_static_scratch` is only a host-side stand-in for the symbol, NOT a device
+// address: the address the kernel gets comes from cudaGetSymbolAddress, resolved once per device with that device
+// current (each device that loads the module has its own copy of the array).
+#include <mutex>
+
+namespace {
+constexpr size_t kStaticHeaderBytes = 256; // kCounterSlots x u64 ray counters, padded to the plane's alignment
+static_assert(kCounterSlots * sizeof(unsigned long long) <= kStaticHeaderBytes, "counters fit the header");
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticHeaderBytes + RAYCA_STATIC_FRAME_BYTES];
+
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_static_mutex;
+unsigned char* g_static_addr[kMaxStaticDevices] = {};
+
+// device address of g_static_scratch on `device` (which must be current)
+int static_scratch_address(int device, unsigned char** out) {
+    if (device < 0 || device >= kMaxStaticDevices) return fail(RAYCA_E_UNSUPPORTED, "device index beyond the static scratch table");
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_addr[device]) {
+        void* p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) return fail(RAYCA_E_CUDA, "cudaGetSymbolAddress returned a null address");
+        g_static_addr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_static_addr[device];
+    return RAYCA_OK;
+}
+
+// points ctx->d_counters at the static array for the duration of one call (enqueue_render and
+// rayca_cuda_last_counters read the pointer from the context), restoring it on every exit path
+struct CounterSwap {
+    rayca_ctx* ctx;
+    unsigned long long* saved;
+    CounterSwap(rayca_ctx* c, unsigned long long* p) : ctx(c), saved(c->d_counters) { c->d_counters = p; }
+    ~CounterSwap() { ctx->d_counters = saved; }
+};
+} // namespace
+
+extern "C" int rayca_cuda_render_static(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options,
+                                        uint32_t width, uint32_t height, uint8_t* rgba8_out, rayca_stats* stats) {
+    if (!ctx || !scene || !config || !rgba8_out || width == 0 || height == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
+    const unsigned long long bytes = (unsigned long long)width * height * 4ull;
+    if (bytes > RAYCA_STATIC_FRAME_BYTES)
+        return fail(RAYCA_E_INVALID_ARG, "rayca_cuda_render_static: a " + std::to_string(width) + " x " + std::to_string(height) +
+                                             " frame needs " + std::to_string(bytes) + " bytes, the static scratch holds " +
+                                             std::to_string((unsigned long long)RAYCA_STATIC_FRAME_BYTES) +
+                                             " (RAYCA_STATIC_FRAME_BYTES); use rayca_cuda_render");
+    if (options && options->shard_count > 1) return fail(RAYCA_E_INVALID_ARG, "rayca_cuda_render_static renders whole frames (shard_count <= 1)");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    unsigned char* base = nullptr;
+    int rc = static_scratch_address(ctx->device, &base);
+    if (rc != RAYCA_OK) return rc;
+    unsigned char* plane = base + kStaticHeaderBytes;
+    double t0 = now_ms();
+    rayca_stats local{};
+    {
+        CounterSwap swap(ctx, reinterpret_cast<unsigned long long*>(base));
+        // enqueue_render clears the counters on the stream (cudaMemsetAsync) before the launch: the array keeps the
+        // previous call's contents, and the counters are the part that must start at zero; every pixel of the
+        // plane inside width x height is overwritten by the kernel
+        rc = enqueue_render(ctx, scene, config, options, width, height, plane, nullptr, ctx->render_stream, nullptr, &local);
+        if (rc != RAYCA_OK) return rc;
+        CUDA_TRY(cudaMemcpyAsync(rgba8_out, plane, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->render_stream));
+        CUDA_TRY(cudaStreamSynchronize(ctx->render_stream));
+        if (stats) {
+            rc = rayca_cuda_last_counters(ctx, &local); // reads the counters through ctx->d_counters (still the static array)
+            if (rc != RAYCA_OK) return rc;
+        }
+    }
+    if (stats) {
+        local.kernel_launches = 1;
+        local.readback_ms = (now_ms() - t0) - local.trace_ms;
+        if (local.readback_ms < 0.0) local.readback_ms = 0.0;
+        *stats = local;
+    }
+    return RAYCA_OK;
+}

@@ -48,6 +48,7 @@ TRAVERSAL_ORDERED, TRAVERSAL_EXHAUSTIVE, TRAVERSAL_REFERENCE_ORDERED = 0, 1, 2
 FLAG_COUNT_WALK = 1
 FLAG_PERSISTENT = 2
 FLAG_DIRECT_ROWS = 4
+STATIC_FRAME_BYTES = 8 << 20  # RAYCA_STATIC_FRAME_BYTES: largest width * height * 4 rayca_cuda_render_static accepts
 
 _ERRORS = {-1: "RAYCA_E_INVALID_ARG", -2: "RAYCA_E_UNSUPPORTED", -3: "RAYCA_E_OOM", -4: "RAYCA_E_CUDA",
            -5: "RAYCA_E_NO_CAMERA"}
@@ -180,6 +181,8 @@ def load_library():
     lib.rayca_cuda_scene_destroy.restype = None
     lib.rayca_cuda_render.argtypes = [vp, vp, C.POINTER(M.rayca_config), C.POINTER(M.rayca_options), u32, u32, vp,
                                       C.POINTER(M.rayca_aux_out), C.POINTER(M.rayca_stats)]
+    lib.rayca_cuda_render_static.argtypes = [vp, vp, C.POINTER(M.rayca_config), C.POINTER(M.rayca_options), u32, u32, vp,
+                                             C.POINTER(M.rayca_stats)]
     lib.rayca_cuda_render_device.argtypes = [vp, vp, C.POINTER(M.rayca_config), C.POINTER(M.rayca_options), u32, u32,
                                              vp, C.POINTER(M.rayca_aux_out), vp, C.POINTER(M.rayca_stats)]
     lib.rayca_cuda_last_counters.argtypes = [vp, C.POINTER(M.rayca_stats)]
@@ -397,6 +400,20 @@ class DeviceScene:
                                                 C.byref(options) if options is not None else None, width, height,
                                                 rgba8.ctypes.data, C.byref(aux.c) if aux else None, C.byref(stats)))
         return rgba8, aux, stats
+
+    def render_static(self, config: Config, width: int, height: int, options: Optional[M.rayca_options] = None,
+                      out: Optional[np.ndarray] = None):
+        """rayca_cuda_render_static: the allocation-free render (scratch in a static device array of the library, frames
+        up to STATIC_FRAME_BYTES).  Returns (rgba8 HxWx4, stats).  Calls on one device must not overlap."""
+        if out is not None:
+            assert out.shape == (height, width, 4) and out.dtype == np.uint8 and out.flags["C_CONTIGUOUS"]
+        rgba8 = out if out is not None else np.zeros((height, width, 4), dtype=np.uint8)
+        stats = M.rayca_stats()
+        cfg = config.to_c()
+        _check(load_library().rayca_cuda_render_static(self.ctx._h, self._h, C.byref(cfg),
+                                                       C.byref(options) if options is not None else None, width, height,
+                                                       rgba8.ctypes.data, C.byref(stats)))
+        return rgba8, stats
 
     def render_device(self, config: Config, width: int, height: int, d_rgba8: int, stream: int = 0,
                       options: Optional[M.rayca_options] = None, d_aux: Optional[M.rayca_aux_out] = None):
