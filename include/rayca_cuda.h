@@ -35,7 +35,8 @@ enum {
     RAYCA_E_UNSUPPORTED = -2, /* combos that `todo!()`/panic in the reference (SURVEY A-20) */
     RAYCA_E_OOM = -3,
     RAYCA_E_CUDA = -4,
-    RAYCA_E_NO_CAMERA = -5 /* `assert!(!camera_draw_infos.is_empty())` rayca-soft/src/scene.rs:109 */
+    RAYCA_E_NO_CAMERA = -5, /* `assert!(!camera_draw_infos.is_empty())` rayca-soft/src/scene.rs:109 */
+    RAYCA_E_TIMEOUT = -6    /* rayca_cuda_frame_sync: a shared-frame flag wait gave up */
 };
 
 #define RAYCA_NONE (-1) /* Handle::NONE (rayca-util/src/pack.rs:59) */
@@ -362,7 +363,7 @@ int rayca_cuda_probe_read_bandwidth(rayca_ctx* ctx, size_t bytes, uint32_t reps,
  * rayca_cuda_render_to_frame then makes each rank's trace kernel store its tiles' pixels straight into their
  * final row-major place in the owner's frame, followed on the same stream by a one-thread kernel that
  * publishes `frame_id` in that rank's flag slot.  The owner enqueues rayca_cuda_frame_wait (a one-warp kernel
- * spinning on the flags, with a ~2 s time-out) and may then read the frame on the same stream: no collective,
+ * spinning on the flags, with a wall-clock time-out, see rayca_cuda_frame_sync) and may then read the frame on the same stream: no collective,
  * no local staging buffer, no pack / unpack kernel.
  * Back-pressure for a pipeline of frames: the owner calls rayca_cuda_frame_release(frame_id) once it has
  * consumed a frame (e.g. after its device-to-host copy, in stream order); a rank that is about to overwrite the
@@ -390,9 +391,29 @@ int rayca_cuda_frame_release(rayca_ctx* ctx, rayca_frame* frame, uint64_t frame_
 /* Any rank: in stream order, waits until the owner has released a frame id >= frame_id (0 returns at once). */
 int rayca_cuda_frame_acquire(rayca_ctx* ctx, rayca_frame* frame, uint64_t frame_id, void* cuda_stream);
 int rayca_cuda_frame_timed_out(rayca_frame* frame);
+/* The flag waits (frame_wait / frame_acquire) give up after a WALL-clock time-out (default 2000 ms; a rank can be that
+ * late for honest reasons: first-launch module load, a BVH rebuild): set it per frame object.  The enqueueing call has
+ * long returned by then, so the condition is reported by the synchronising call: rayca_cuda_frame_sync waits for
+ * `cuda_stream` and returns RAYCA_E_TIMEOUT if any wait of this frame object has given up since the last
+ * rayca_cuda_frame_clear_timeout.  After a time-out the frame's contents are UNDEFINED (a late rank may still be
+ * storing its tiles, or the owner may not have consumed the previous frame): do not present it. */
+int rayca_cuda_frame_set_timeout(rayca_frame* frame, double milliseconds);
+int rayca_cuda_frame_sync(rayca_ctx* ctx, rayca_frame* frame, void* cuda_stream);
+void rayca_cuda_frame_clear_timeout(rayca_frame* frame);
 
 /* Binds a context to one CUDA device (one process per GPU). */
 int rayca_cuda_init(int device, rayca_ctx** out);
+/* One context over several devices, driven by ONE host thread (SURVEY 8b "Threading"): what the reference's caller
+ * sees is a single `renderer.draw(&scene, &mut image)` that fans out over the rayon pool
+ * (rayca-soft/src/scene.rs:117-122); here the fan-out is over GPUs.  `devices` = device_count CUDA device indices
+ * (NULL / 0 = every visible device; an index may appear more than once, each entry is a shard of its own).
+ * rayca_cuda_scene_create builds the scene on devices[0] and copies the finished device arrays to the others;
+ * rayca_cuda_render interleaves the frame's 8-row tiles over the devices and every device's kernel stores its
+ * tiles at their final rows of the caller's buffer (pinned buffers: zero copy over each device's own PCIe link;
+ * pageable buffers: one strided copy per device).  Calls with aux planes or an explicit shard run on devices[0].
+ * The context's other entry points (render_device, render_to_frame, render_static, frames) address devices[0]. */
+int rayca_cuda_init_devices(const int* devices, int device_count, rayca_ctx** out);
+int rayca_cuda_device_count(rayca_ctx* ctx); /* shards of the context: 1 for rayca_cuda_init */
 void rayca_cuda_shutdown(rayca_ctx* ctx);
 
 /* Replaces scene.rs:90-99: SceneDrawInfo::new, BvhScene::from_scene, Tlas::build;

@@ -51,6 +51,10 @@ struct rayca_ctx {
     size_t scratch_bytes = 0;
     cudaStream_t render_stream = nullptr, copy_stream = nullptr;
     cudaEvent_t band_done[8] = {};
+    // multi-device context (rayca_cuda_init_devices): this context drives extra[0..] as well, each a complete
+    // single-device context of its own; scene_create replicates the scene on them and rayca_cuda_render shards the
+    // frame's row tiles over all of them from the ONE calling host thread
+    std::vector<rayca_ctx*> extra;
 };
 
 struct rayca_scene {
@@ -69,9 +73,21 @@ struct rayca_scene {
     size_t fast_node_count = 0; // 32-byte records in d_fast_nodes
     GpuSceneView view{};
     uint32_t max_stack = 0;
+    // multi-device contexts: device copies of the arrays above on ctx->extra[i] (replicas[i]->primary == this); a
+    // replica owns its device arrays only — flags, lights and materials the launch code consults stay with the primary
+    std::vector<rayca_scene*> replicas;
+    rayca_scene* primary = nullptr;
+    size_t nbytes[10] = {}; // byte sizes of d_nodes .. d_fast_tri in declaration order (what a replica copies)
 };
 
 namespace {
+const HostScene& host_of(const rayca_scene& s) { return s.primary ? s.primary->host : s.host; }
+} // namespace
+
+namespace {
+
+// index of one of rayca_scene's ten device-array members (d_nodes .. d_fast_tri are consecutive void* members)
+size_t slot_of(void* const* member, const rayca_scene* s) { return (size_t)(member - &s->d_nodes); }
 
 template <typename V>
 int upload(void** dst, const V& src) {
@@ -94,7 +110,7 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
         case RAYCA_INTEGRATOR_RAYTRACER:
         case RAYCA_INTEGRATOR_SCRATCHER:
             if (c.max_depth + 1 > (uint32_t)kMaxDepth) return fail(RAYCA_E_UNSUPPORTED, "max_depth > 16");
-            for (const GpuLight& l : sc.host.lights) // Light::get_direction is todo!() for quad lights (light/mod.rs:79-85)
+            for (const GpuLight& l : host_of(sc).lights) // Light::get_direction is todo!() for quad lights (light/mod.rs:79-85)
                 if (l.kind == RAYCA_LIGHT_QUAD) return fail(RAYCA_E_UNSUPPORTED, "quad lights under the raytracer / scratcher");
             break;
         case RAYCA_INTEGRATOR_PATHTRACER: {
@@ -106,14 +122,15 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
             bool nee = c.direct_sampler == RAYCA_SAMPLER_NEE || mis;
             bool bounces = c.russian_roulette || c.max_depth > (nee ? 1u : 0u);
             bool material_sampling = mis || (bounces && c.indirect_sampler == RAYCA_SAMPLER_BRDF);
-            if (mis && sc.host.lights.size() * (size_t)c.light_samples > kMaxMisSamples)
+            if (mis && host_of(sc).lights.size() * (size_t)c.light_samples > kMaxMisSamples)
                 return fail(RAYCA_E_UNSUPPORTED, "Mis keeps at most 16 light samples per hit");
             if (bounces && c.indirect_sampler != RAYCA_SAMPLER_COSINE && c.indirect_sampler != RAYCA_SAMPLER_HEMISPHERE &&
                 c.indirect_sampler != RAYCA_SAMPLER_BRDF)
                 return fail(RAYCA_E_UNSUPPORTED, "indirect sampler");
             if (material_sampling) { // Material::get_t is todo!() for PBR (material/mod.rs:163-169)
-                bool pbr = sc.host.materials.size() <= 1;
-                for (size_t k = 1; k < sc.host.materials.size(); ++k) pbr = pbr || sc.host.materials[k].kind == RAYCA_MATERIAL_PBR;
+                const HostScene& hs = host_of(sc);
+                bool pbr = hs.materials.size() <= 1;
+                for (size_t k = 1; k < hs.materials.size(); ++k) pbr = pbr || hs.materials[k].kind == RAYCA_MATERIAL_PBR;
                 if (pbr) return fail(RAYCA_E_UNSUPPORTED, "the Brdf / Mis samplers need Phong / GGX materials");
             }
             if (bounces && c.light_samples != 1) { // a tree of light_samples^depth paths per sample (pathtracer_branching)
@@ -121,7 +138,7 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
                 if (c.max_depth > (uint32_t)kMaxBranchDepth) return fail(RAYCA_E_UNSUPPORTED, "light_samples > 1 with max_depth > 8");
             }
             if (nee)
-                for (const GpuLight& l : sc.host.lights) // NEE: directional is todo!() (nee.rs:177)
+                for (const GpuLight& l : host_of(sc).lights) // NEE: directional is todo!() (nee.rs:177)
                     if (l.kind == RAYCA_LIGHT_DIRECTIONAL) return fail(RAYCA_E_UNSUPPORTED, "NEE with a directional light");
             break;
         }
@@ -199,18 +216,13 @@ const char* rayca_cuda_strerror(int code) {
         case RAYCA_E_OOM: return "out of memory";
         case RAYCA_E_CUDA: return "CUDA error";
         case RAYCA_E_NO_CAMERA: return "scene has no camera";
+        case RAYCA_E_TIMEOUT: return "timed out";
         default: return "unknown error";
     }
 }
 
-int rayca_cuda_init(int device, rayca_ctx** out) {
-    if (!out) return fail(RAYCA_E_INVALID_ARG, "null out");
-    int n = 0;
-    CUDA_TRY(cudaGetDeviceCount(&n));
-    if (device < 0 || device >= n) return fail(RAYCA_E_INVALID_ARG, "no such CUDA device");
-    CUDA_TRY(cudaSetDevice(device));
-    rayca_ctx* c = new (std::nothrow) rayca_ctx();
-    if (!c) return fail(RAYCA_E_OOM, "host allocation");
+namespace {
+int init_one(rayca_ctx* c, int device) { // every failure leaves `c` in a state rayca_cuda_shutdown can release
     c->device = device;
     CUDA_TRY(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
     CUDA_TRY(cudaMalloc((void**)&c->d_counters, kCounterSlots * sizeof(unsigned long long)));
@@ -220,12 +232,61 @@ int rayca_cuda_init(int device, rayca_ctx** out) {
     CUDA_TRY(cudaStreamCreateWithFlags(&c->render_stream, cudaStreamNonBlocking));
     CUDA_TRY(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     for (cudaEvent_t& e : c->band_done) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    return RAYCA_OK;
+}
+} // namespace
+
+int rayca_cuda_init(int device, rayca_ctx** out) {
+    if (!out) return fail(RAYCA_E_INVALID_ARG, "null out");
+    int n = 0;
+    CUDA_TRY(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail(RAYCA_E_INVALID_ARG, "no such CUDA device");
+    CUDA_TRY(cudaSetDevice(device));
+    rayca_ctx* c = new (std::nothrow) rayca_ctx();
+    if (!c) return fail(RAYCA_E_OOM, "host allocation");
+    int rc = init_one(c, device);
+    if (rc != RAYCA_OK) {
+        rayca_cuda_shutdown(c); // null-safe per member: releases whatever was created
+        return rc;
+    }
     *out = c;
     return RAYCA_OK;
 }
 
+int rayca_cuda_init_devices(const int* devices, int device_count, rayca_ctx** out) {
+    if (!out || device_count < 0 || (device_count > 0 && !devices)) return fail(RAYCA_E_INVALID_ARG, "null / negative argument");
+    int visible = 0;
+    CUDA_TRY(cudaGetDeviceCount(&visible));
+    std::vector<int> devs;
+    if (device_count == 0) {
+        for (int d = 0; d < visible; ++d) devs.push_back(d); // all visible devices
+    } else {
+        devs.assign(devices, devices + device_count);
+    }
+    if (devs.empty()) return fail(RAYCA_E_CUDA, "no CUDA device");
+    if (devs.size() > 32) return fail(RAYCA_E_INVALID_ARG, "at most 32 devices per context");
+    rayca_ctx* c = nullptr;
+    int rc = rayca_cuda_init(devs[0], &c);
+    if (rc != RAYCA_OK) return rc;
+    for (size_t k = 1; k < devs.size(); ++k) { // a device may be listed more than once: every entry is a shard of its own
+        rayca_ctx* e = nullptr;
+        rc = rayca_cuda_init(devs[k], &e);
+        if (rc != RAYCA_OK) {
+            rayca_cuda_shutdown(c);
+            return rc;
+        }
+        c->extra.push_back(e);
+    }
+    CUDA_TRY(cudaSetDevice(c->device));
+    *out = c;
+    return RAYCA_OK;
+}
+
+int rayca_cuda_device_count(rayca_ctx* ctx) { return ctx ? 1 + (int)ctx->extra.size() : 0; }
+
 void rayca_cuda_shutdown(rayca_ctx* c) {
     if (!c) return;
+    for (rayca_ctx* e : c->extra) rayca_cuda_shutdown(e);
     cudaSetDevice(c->device);
     cudaFree(c->d_counters);
     cudaFree(c->d_scratch);
@@ -240,6 +301,7 @@ void rayca_cuda_shutdown(rayca_ctx* c) {
 
 void rayca_cuda_scene_destroy(rayca_scene* s) {
     if (!s) return;
+    for (rayca_scene* r : s->replicas) rayca_cuda_scene_destroy(r);
     if (s->ctx) cudaSetDevice(s->ctx->device);
     cudaFree(s->d_nodes);
     cudaFree(s->d_tri_pos);
@@ -300,6 +362,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     HostScene& h = s->host;
 #define UP(dst, vec)                         \
     do {                                     \
+        s->nbytes[slot_of(&s->dst, s)] = std::max<size_t>(h.vec.size() * sizeof(h.vec[0]), 16); \
         int rc__ = upload(&s->dst, h.vec);   \
         if (rc__ != RAYCA_OK) {              \
             rayca_cuda_scene_destroy(s);     \
@@ -328,6 +391,8 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         s->d_fast_nodes = ft.nodes;
         s->d_fast_tri = ft.tri;
         s->fast_node_count = (size_t)h.blas_prim_offset.back() * 2 + 2;
+        s->nbytes[8] = s->fast_node_count * sizeof(GpuNode);
+        s->nbytes[9] = (size_t)h.blas_prim_offset.back() * 4 * sizeof(float4);
         h.fast_root = ft.root;
         h.fast_depth = ft.depth;
         h.max_stack = std::max(h.max_stack, ft.depth + 2);
@@ -382,6 +447,46 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     std::vector<float4>().swap(h.fast_tri);
     std::vector<GpuNode>().swap(h.fast_nodes);
     for (HostBlas& b : h.blas) PodVector<HostAttr>().swap(b.attrs);
+    // multi-device context: copy the finished device arrays to every other device (device-to-device, no rebuild)
+    for (rayca_ctx* e : ctx->extra) {
+        rayca_scene* r = new (std::nothrow) rayca_scene();
+        if (!r) {
+            rayca_cuda_scene_destroy(s);
+            return fail(RAYCA_E_OOM, "host allocation");
+        }
+        r->ctx = e;
+        r->primary = s;
+        s->replicas.push_back(r); // owned by s from here on: every failure below is released by scene_destroy(s)
+        void** src = &s->d_nodes;
+        void** dst = &r->d_nodes;
+        cudaError_t ce = cudaSetDevice(e->device);
+        for (int k = 0; k < 10 && ce == cudaSuccess; ++k) {
+            r->nbytes[k] = s->nbytes[k];
+            if (!src[k] || s->nbytes[k] == 0) continue;
+            ce = cudaMalloc(&dst[k], s->nbytes[k]);
+            if (ce == cudaSuccess) ce = cudaMemcpyPeerAsync(dst[k], e->device, src[k], ctx->device, s->nbytes[k], e->render_stream);
+        }
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->render_stream);
+        if (ce != cudaSuccess) {
+            cudaSetDevice(ctx->device);
+            rayca_cuda_scene_destroy(s);
+            return fail(ce == cudaErrorMemoryAllocation ? RAYCA_E_OOM : RAYCA_E_CUDA, std::string("replicating the scene: ") + cudaGetErrorString(ce));
+        }
+        r->fast_node_count = s->fast_node_count;
+        r->max_stack = s->max_stack;
+        r->view = s->view;
+        r->view.nodes = (const float4*)r->d_nodes;
+        r->view.tri_pos = (const float4*)r->d_tri_pos;
+        r->view.tri_attr = (const float4*)r->d_tri_attr;
+        r->view.materials = (const GpuMaterial*)r->d_materials;
+        r->view.images = (const GpuImage*)r->d_images;
+        r->view.texels = (const unsigned char*)r->d_texels;
+        r->view.lights = (const GpuLight*)r->d_lights;
+        r->view.blas_prim_offset = (const uint32_t*)r->d_blas_prim_offset;
+        r->view.fast_nodes = (const float4*)r->d_fast_nodes;
+        r->view.fast_tri = (const float4*)r->d_fast_tri;
+    }
+    if (!ctx->extra.empty()) CUDA_TRY(cudaSetDevice(ctx->device));
     double t2 = now_ms();
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
@@ -424,7 +529,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
                    const FrameTarget* target) {
     if (!ctx || !scene || !config || !d_rgba8 || width == 0 || height == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
     if (scene->ctx != ctx) return fail(RAYCA_E_INVALID_ARG, "scene belongs to another context (or is host-only)");
-    if (!scene->host.has_camera) return fail(RAYCA_E_NO_CAMERA, "no camera node in the scene");
+    if (!host_of(*scene).has_camera) return fail(RAYCA_E_NO_CAMERA, "no camera node in the scene");
     if ((uint64_t)width * height >= 0xFFFFFFFFull) return fail(RAYCA_E_UNSUPPORTED, "image too large");
     int rc = validate_config(*config, *scene);
     if (rc != RAYCA_OK) return rc;
@@ -480,7 +585,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     if (target || (options && (options->flags & RAYCA_FLAG_DIRECT_ROWS))) P.direct_rows = 1;
     const uint32_t mode = options ? options->traversal : (uint32_t)RAYCA_TRAVERSAL_ORDERED;
     if (mode > RAYCA_TRAVERSAL_REFERENCE_ORDERED) return fail(RAYCA_E_INVALID_ARG, "unknown traversal mode");
-    if (mode != RAYCA_TRAVERSAL_ORDERED && scene->host.has_spheres)
+    if (mode != RAYCA_TRAVERSAL_ORDERED && host_of(*scene).has_spheres)
         return fail(RAYCA_E_UNSUPPORTED, "the reference-tree walks (traversal 1 / 2) handle triangle scenes only");
     const bool count = options && (options->flags & RAYCA_FLAG_COUNT_WALK); // opt-in: walk counters cost registers
     const bool persistent = options && (options->flags & RAYCA_FLAG_PERSISTENT);
@@ -491,7 +596,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     P.groups_x = grid.x;
     P.tile_count = grid.x * grid.y;
     if (first) CUDA_TRY(cudaEventRecord(ctx->ev0, st));
-    LaunchSel sel{mode, count, persistent, false, scene->host.has_spheres, ctx->sm_count};
+    LaunchSel sel{mode, count, persistent, false, host_of(*scene).has_spheres, ctx->sm_count};
     uint32_t integrator = config->integrator;
     if (integrator == RAYCA_INTEGRATOR_PATHTRACER) { // an indirect ray needs depth < limit (pathtracer.rs:94)
         const bool mis = config->direct_sampler == RAYCA_SAMPLER_MIS;
@@ -501,7 +606,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
         bool general = mis || config->russian_roulette != 0 || (sel.bounce && config->indirect_sampler != RAYCA_SAMPLER_COSINE) ||
                        (sel.bounce && config->light_samples > 1);
         if (nee)
-            for (const GpuLight& l : scene->host.lights) general = general || l.kind == RAYCA_LIGHT_QUAD;
+            for (const GpuLight& l : host_of(*scene).lights) general = general || l.kind == RAYCA_LIGHT_QUAD;
         if (general) integrator = kInternalPathGeneral;
     }
     switch (integrator) {
@@ -601,6 +706,7 @@ struct rayca_frame {
     uint32_t width = 0, height = 0;
     bool imported = false;
     int* timed_out = nullptr; // pinned, device-visible
+    unsigned long long timeout_ns = 2000000000ull; // rayca_cuda_frame_set_timeout
 };
 
 namespace {
@@ -613,13 +719,21 @@ __global__ void frame_signal_kernel(volatile unsigned long long* slot, unsigned 
     __threadfence_system();
     *slot = value;
 }
-// one warp: lane r polls slot first+r; gives up after ~2 s so that a dead peer cannot hang the GPU
-__global__ void frame_wait_kernel(const volatile unsigned long long* flags, uint32_t ranks, unsigned long long frame_id, int* timed_out) {
+// one warp: lane r polls slot first+r; gives up after `timeout_ns` of WALL time (%globaltimer) so that a dead peer
+// cannot hang the GPU.  A time-out is sticky in `timed_out` until rayca_cuda_frame_clear_timeout; the frame's
+// contents are undefined from then on (a rank may still be storing into it).
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__global__ void frame_wait_kernel(const volatile unsigned long long* flags, uint32_t ranks, unsigned long long frame_id, int* timed_out,
+                                  unsigned long long timeout_ns) {
     const uint32_t r = threadIdx.x;
     if (r < ranks) {
-        const long long t0 = clock64();
+        const unsigned long long t0 = global_ns();
         while (flags[r] < frame_id) {
-            if (clock64() - t0 > 4000000000ll) {
+            if (global_ns() - t0 > timeout_ns) {
                 *timed_out = 1;
                 break;
             }
@@ -641,9 +755,13 @@ int rayca_cuda_frame_create(rayca_ctx* ctx, uint32_t width, uint32_t height, ray
     f->width = width;
     f->height = height;
     const size_t bytes = kFrameFlagBytes + (size_t)width * height * 4;
-    CUDA_TRY(cudaMalloc((void**)&f->base, bytes)); // a plain cudaMalloc block: IPC handles cover whole allocations
-    CUDA_TRY(cudaMemset(f->base, 0, bytes));
-    CUDA_TRY(cudaHostAlloc((void**)&f->timed_out, sizeof(int), cudaHostAllocMapped));
+    cudaError_t ce = cudaMalloc((void**)&f->base, bytes); // a plain cudaMalloc block: IPC handles cover whole allocations
+    if (ce == cudaSuccess) ce = cudaMemset(f->base, 0, bytes);
+    if (ce == cudaSuccess) ce = cudaHostAlloc((void**)&f->timed_out, sizeof(int), cudaHostAllocMapped);
+    if (ce != cudaSuccess) {
+        rayca_cuda_frame_destroy(f); // null-safe per member
+        return fail(ce == cudaErrorMemoryAllocation ? RAYCA_E_OOM : RAYCA_E_CUDA, std::string("frame_create: ") + cudaGetErrorString(ce));
+    }
     *f->timed_out = 0;
     *out = f;
     return RAYCA_OK;
@@ -669,7 +787,10 @@ int rayca_cuda_frame_import(rayca_ctx* ctx, const uint8_t handle[RAYCA_IPC_HANDL
     f->width = width;
     f->height = height;
     f->imported = true;
-    CUDA_TRY(cudaHostAlloc((void**)&f->timed_out, sizeof(int), cudaHostAllocMapped));
+    if (cudaError_t ce = cudaHostAlloc((void**)&f->timed_out, sizeof(int), cudaHostAllocMapped); ce != cudaSuccess) {
+        delete f;
+        return fail(RAYCA_E_CUDA, std::string("frame_import: ") + cudaGetErrorString(ce));
+    }
     *f->timed_out = 0;
     cudaIpcMemHandle_t h;
     std::memcpy(&h, handle, sizeof(h));
@@ -688,8 +809,11 @@ void* rayca_cuda_frame_pixels(rayca_frame* f) { return f ? f->base + kFrameFlagB
 void rayca_cuda_frame_destroy(rayca_frame* f) {
     if (!f) return;
     cudaSetDevice(f->ctx->device);
-    if (f->imported) cudaIpcCloseMemHandle(f->base);
-    else cudaFree(f->base);
+    if (f->imported) {
+        if (f->base) cudaIpcCloseMemHandle(f->base);
+    } else {
+        cudaFree(f->base);
+    }
     if (f->timed_out) cudaFreeHost(f->timed_out);
     delete f;
 }
@@ -723,7 +847,7 @@ int rayca_cuda_frame_acquire(rayca_ctx* ctx, rayca_frame* frame, uint64_t frame_
     int* d_flag = nullptr;
     CUDA_TRY(cudaHostGetDevicePointer((void**)&d_flag, frame->timed_out, 0));
     frame_wait_kernel<<<1, 32, 0, (cudaStream_t)cuda_stream>>>(
-        reinterpret_cast<const volatile unsigned long long*>(frame->base) + kConsumedSlot, 1, frame_id, d_flag);
+        reinterpret_cast<const volatile unsigned long long*>(frame->base) + kConsumedSlot, 1, frame_id, d_flag, frame->timeout_ns);
     CUDA_TRY(cudaGetLastError());
     return RAYCA_OK;
 }
@@ -734,16 +858,36 @@ int rayca_cuda_frame_wait(rayca_ctx* ctx, rayca_frame* frame, uint32_t rank_coun
     int* d_flag = nullptr;
     CUDA_TRY(cudaHostGetDevicePointer((void**)&d_flag, frame->timed_out, 0));
     frame_wait_kernel<<<1, 32, 0, (cudaStream_t)cuda_stream>>>(reinterpret_cast<const volatile unsigned long long*>(frame->base), rank_count,
-                                                              frame_id, d_flag);
+                                                              frame_id, d_flag, frame->timeout_ns);
     CUDA_TRY(cudaGetLastError());
     return RAYCA_OK;
 }
 
 int rayca_cuda_frame_timed_out(rayca_frame* f) { return (f && f->timed_out) ? *f->timed_out : 0; }
 
+int rayca_cuda_frame_set_timeout(rayca_frame* f, double milliseconds) {
+    if (!f || !(milliseconds > 0.0) || milliseconds > 3.6e6) return fail(RAYCA_E_INVALID_ARG, "time-out must be in (0, 1 h]");
+    f->timeout_ns = (unsigned long long)(milliseconds * 1.0e6);
+    return RAYCA_OK;
+}
+
+void rayca_cuda_frame_clear_timeout(rayca_frame* f) {
+    if (f && f->timed_out) *f->timed_out = 0;
+}
+
+int rayca_cuda_frame_sync(rayca_ctx* ctx, rayca_frame* frame, void* cuda_stream) {
+    if (!ctx || !frame) return fail(RAYCA_E_INVALID_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaStreamSynchronize((cudaStream_t)cuda_stream));
+    if (*frame->timed_out)
+        return fail(RAYCA_E_TIMEOUT, "shared frame: a flag wait gave up (a rank is late or dead); the frame's contents are undefined until the "
+                                     "ranks are back in step - rayca_cuda_frame_clear_timeout re-arms it");
+    return RAYCA_OK;
+}
+
 int rayca_cuda_host_alloc(size_t bytes, void** out) {
     if (!out || bytes == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
-    CUDA_TRY(cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+    CUDA_TRY(cudaHostAlloc(out, bytes, cudaHostAllocPortable | cudaHostAllocMapped)); // every device may store into it
     return RAYCA_OK;
 }
 
@@ -788,11 +932,112 @@ int rayca_cuda_last_counters(rayca_ctx* ctx, rayca_stats* stats) {
     return RAYCA_OK;
 }
 
+} // extern "C"
+
+namespace {
+// rayca_cuda_render on a multi-device context: ONE host thread, G = 1 + extra devices.  The frame's 8-row tiles are
+// interleaved over the devices (tile t -> device t mod G, like the one-process-per-GPU path: sky and geometry spread
+// evenly), every device's launch is enqueued on its own stream before any of them is waited for, and
+//   * a pinned / registered caller buffer is filled by the kernels' own stores (RAYCA_FLAG_DIRECT_ROWS): G PCIe links
+//     in parallel, no staging plane, no copy;
+//   * a pageable caller buffer gets each device's tiles from that device's staging plane with ONE strided copy
+//     (cudaMemcpy2DAsync: a "row" is a tile of 8 image rows, the destination pitch is G tiles).
+// This is the reference's fan-out (`par_iter_mut` over rows and pixels inside one `draw` call,
+// rayca-soft/src/scene.rs:117-122) with devices in place of rayon workers.
+int render_multi(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options, uint32_t width,
+                 uint32_t height, uint8_t* rgba8_out, rayca_stats* stats) {
+    const uint32_t G = 1u + (uint32_t)ctx->extra.size();
+    if (scene->replicas.size() + 1 != G) return fail(RAYCA_E_INVALID_ARG, "scene was not created on this multi-device context");
+    constexpr uint32_t kTile = 8;
+    const size_t tile_bytes = (size_t)kTile * width * 4;
+    const uint32_t tiles = (height + kTile - 1) / kTile, per = (tiles + G - 1) / G;
+    void* host_view = nullptr;
+    {
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, rgba8_out) == cudaSuccess && at.type == cudaMemoryTypeHost) host_view = at.devicePointer;
+        cudaGetLastError();
+        const char* e = std::getenv("RAYCA_ZERO_COPY");
+        if (e && std::atoi(e) == 0) host_view = nullptr; // A/B runs and tests: force the staged path
+    }
+    double t0 = now_ms();
+    int rc = RAYCA_OK;
+    for (uint32_t r = 0; r < G && rc == RAYCA_OK; ++r) {
+        rayca_ctx* c = r == 0 ? ctx : ctx->extra[r - 1];
+        rayca_scene* sc = r == 0 ? scene : scene->replicas[r - 1];
+        CUDA_TRY(cudaSetDevice(c->device));
+        rayca_options o{};
+        if (options) o = *options;
+        o.shard_index = r;
+        o.shard_count = G;
+        o.tile_rows = kTile;
+        void* target = host_view;
+        if (host_view) {
+            o.flags |= RAYCA_FLAG_DIRECT_ROWS;
+        } else {
+            const size_t need = (size_t)per * tile_bytes;
+            if (need > c->scratch_bytes) {
+                cudaFree(c->d_scratch);
+                c->d_scratch = nullptr;
+                c->scratch_bytes = 0;
+                CUDA_TRY(cudaMalloc(&c->d_scratch, need));
+                c->scratch_bytes = need;
+            }
+            target = c->d_scratch;
+        }
+        rc = enqueue_render(c, sc, config, &o, width, height, target, nullptr, c->render_stream, nullptr, nullptr);
+        if (rc != RAYCA_OK) break;
+        if (!host_view && r < tiles) {
+            const uint32_t mine = (tiles - r + G - 1) / G;           // tiles t = r, r + G, ... below `tiles`
+            const bool owns_tail = (height % kTile) != 0 && (tiles - 1) % G == r;
+            const uint32_t full = owns_tail ? mine - 1 : mine;
+            if (full)
+                CUDA_TRY(cudaMemcpy2DAsync(rgba8_out + (size_t)r * tile_bytes, (size_t)G * tile_bytes, c->d_scratch, tile_bytes, tile_bytes, full,
+                                           cudaMemcpyDeviceToHost, c->render_stream));
+            if (owns_tail)
+                CUDA_TRY(cudaMemcpyAsync(rgba8_out + (size_t)(tiles - 1) * tile_bytes, (unsigned char*)c->d_scratch + (size_t)(mine - 1) * tile_bytes,
+                                         (size_t)(height % kTile) * width * 4, cudaMemcpyDeviceToHost, c->render_stream));
+        }
+    }
+    // wait for every device even after a failure: nothing may still be writing into the caller's buffer on return
+    rayca_stats total{};
+    for (uint32_t r = 0; r < G; ++r) {
+        rayca_ctx* c = r == 0 ? ctx : ctx->extra[r - 1];
+        cudaSetDevice(c->device);
+        cudaError_t ce = cudaStreamSynchronize(c->render_stream);
+        if (ce != cudaSuccess && rc == RAYCA_OK) rc = fail(RAYCA_E_CUDA, std::string("multi-device render: ") + cudaGetErrorString(ce));
+        if (rc == RAYCA_OK && stats) {
+            rayca_stats one{};
+            int rc2 = rayca_cuda_last_counters(c, &one);
+            if (rc2 != RAYCA_OK) rc = rc2;
+            total.rays_primary += one.rays_primary;
+            total.rays_shadow += one.rays_shadow;
+            total.rays_secondary += one.rays_secondary;
+            total.node_bytes += one.node_bytes;
+            total.triangle_bytes += one.triangle_bytes;
+            total.trace_ms = std::max(total.trace_ms, one.trace_ms); // the devices run side by side
+            total.kernel_launches += 1;
+        }
+    }
+    cudaSetDevice(ctx->device);
+    if (rc != RAYCA_OK) return rc;
+    if (stats) {
+        total.readback_ms = std::max(0.0, (now_ms() - t0) - total.trace_ms);
+        *stats = total;
+    }
+    return RAYCA_OK;
+}
+} // namespace
+
+extern "C" {
+
 int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options, uint32_t width,
                       uint32_t height, uint8_t* rgba8_out, const rayca_aux_out* aux, rayca_stats* stats) {
     if (!ctx || !rgba8_out || width == 0 || height == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
     CUDA_TRY(cudaSetDevice(ctx->device));
     const bool sharded = options && options->shard_count > 1;
+    // multi-device context: the whole frame, sharded over the devices from this one call; parity planes (aux) and
+    // explicitly sharded calls stay on the context's first device
+    if (!ctx->extra.empty() && scene && !aux && !sharded && config) return render_multi(ctx, scene, config, options, width, height, rgba8_out, stats);
     if (sharded) { // one rank's tiles of a frame that several ranks fill: only straight into pinned memory, at the final rows
         cudaPointerAttributes at{};
         const bool pinned = cudaPointerGetAttributes(&at, rgba8_out) == cudaSuccess && at.type == cudaMemoryTypeHost;

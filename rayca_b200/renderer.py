@@ -51,7 +51,7 @@ FLAG_DIRECT_ROWS = 4
 STATIC_FRAME_BYTES = 8 << 20  # RAYCA_STATIC_FRAME_BYTES: largest width * height * 4 rayca_cuda_render_static accepts
 
 _ERRORS = {-1: "RAYCA_E_INVALID_ARG", -2: "RAYCA_E_UNSUPPORTED", -3: "RAYCA_E_OOM", -4: "RAYCA_E_CUDA",
-           -5: "RAYCA_E_NO_CAMERA"}
+           -5: "RAYCA_E_NO_CAMERA", -6: "RAYCA_E_TIMEOUT"}
 
 
 class RaycaError(RuntimeError):
@@ -172,7 +172,13 @@ def load_library():
     lib.rayca_cuda_frame_release.argtypes = [vp, vp, C.c_uint64, vp]
     lib.rayca_cuda_frame_acquire.argtypes = [vp, vp, C.c_uint64, vp]
     lib.rayca_cuda_frame_timed_out.argtypes = [vp]
+    lib.rayca_cuda_frame_set_timeout.argtypes = [vp, C.c_double]
+    lib.rayca_cuda_frame_sync.argtypes = [vp, vp, vp]
+    lib.rayca_cuda_frame_clear_timeout.argtypes = [vp]
+    lib.rayca_cuda_frame_clear_timeout.restype = None
     lib.rayca_cuda_init.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.rayca_cuda_init_devices.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
+    lib.rayca_cuda_device_count.argtypes = [vp]
     lib.rayca_cuda_shutdown.argtypes = [vp]
     lib.rayca_cuda_shutdown.restype = None
     lib.rayca_cuda_scene_create.argtypes = [vp, vp, u32, C.POINTER(vp), C.POINTER(M.rayca_stats)]
@@ -218,12 +224,20 @@ class AuxPlanes:
 
 
 class Context:
-    """rayca_ctx: one per process and GPU."""
+    """rayca_ctx.  `Context(device)`: one GPU (one process per GPU).  `Context(devices=[...])`: one context over several
+    GPUs driven by this thread (rayca_cuda_init_devices; `devices=[]` = every visible device): DeviceScene replicates the
+    scene and DeviceScene.render shards the frame over them."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device: int = 0, devices=None):
         self._h = C.c_void_p()
-        _check(load_library().rayca_cuda_init(device, C.byref(self._h)))
-        self.device = device
+        if devices is None:
+            _check(load_library().rayca_cuda_init(device, C.byref(self._h)))
+            self.device = device
+        else:
+            arr = (C.c_int * max(len(devices), 1))(*devices)
+            _check(load_library().rayca_cuda_init_devices(arr if devices else None, len(devices), C.byref(self._h)))
+            self.device = devices[0] if devices else 0
+        self.device_count = load_library().rayca_cuda_device_count(self._h)
 
     def probe_read_bandwidth(self, nbytes: int, reps: int) -> float:
         """GB/s of a streaming read over an nbytes buffer (L2-resident when small): bench.py's L2 roofline."""
@@ -337,6 +351,17 @@ class SharedFrame:
     def timed_out(self) -> bool:
         return bool(load_library().rayca_cuda_frame_timed_out(self._h))
 
+    def set_timeout(self, milliseconds: float) -> None:
+        """Wall-clock limit of the flag waits of this frame object (default 2000 ms)."""
+        _check(load_library().rayca_cuda_frame_set_timeout(self._h, milliseconds))
+
+    def sync(self, stream: int = 0) -> None:
+        """Waits for `stream`; raises RaycaError(RAYCA_E_TIMEOUT) if a flag wait gave up: the frame is then undefined."""
+        _check(load_library().rayca_cuda_frame_sync(self.ctx._h, self._h, stream))
+
+    def clear_timeout(self) -> None:
+        load_library().rayca_cuda_frame_clear_timeout(self._h)
+
     def close(self):
         if self._h:
             load_library().rayca_cuda_frame_destroy(self._h)
@@ -441,9 +466,10 @@ class DeviceScene:
 class CudaRenderer:
     """Drop-in for `SoftRenderer` (rayca-soft/src/scene.rs:11-14,57-61,88-154)."""
 
-    def __init__(self, config: Optional[Config] = None, device: int = 0):
+    def __init__(self, config: Optional[Config] = None, device: int = 0, devices=None):
+        """`devices`: list of CUDA devices one `draw` call fans out over ([] = all visible); default: `device` alone."""
         self.config = config if config is not None else Config()
-        self._ctx = Context(device)
+        self._ctx = Context(device, devices=devices)
 
     @staticmethod
     def new_with_config(config: Config) -> "CudaRenderer":

@@ -8,6 +8,7 @@ import pytest
 from rayca_b200 import model as M
 from rayca_b200 import renderer as R
 
+from conftest import load_desc
 from test_cuda_parity import check_against
 
 pytestmark = pytest.mark.gpu
@@ -171,3 +172,35 @@ def test_many_samples_per_pixel_on_a_ragged_image(ctx, oracle):
     tris = [[[-1, -1, 0], [1, -1, 0], [0, 1, 0]], [[-2, -1, -1], [2, -1, -1], [0, 2, -1]]]
     for spp, (w, h) in ((9, (21, 13)), (16, (10, 7)), (5, (19, 3))):
         compare(ctx, oracle, soup_scene(tris), w, h, cfg=R.Config(max_depth=1, samples_per_pixel=spp))
+
+
+def test_shared_frame_late_rank_is_reported_not_blended(ctx):
+    """a flag wait that gives up must surface as an error from a synchronising call, not as a silently torn
+    frame.  The owner waits for two ranks, only rank 0 ever stores: with a 50 ms limit rayca_cuda_frame_sync returns
+    RAYCA_E_TIMEOUT (sticky until cleared); once the missing rank has stored, the same wait succeeds."""
+    import time
+
+    sc = R.DeviceScene(ctx, load_desc("box"))
+    cfg = R.Config(max_depth=1)
+    frame = R.SharedFrame(ctx, 64, 64)
+    frame.set_timeout(50.0)
+    sc.render_to_frame(cfg, frame, 1, options=M.rayca_options(0, 0, 0, 2, 8, 0, 0))  # rank 0 of 2
+    t0 = time.perf_counter()
+    frame.wait(2, 1)
+    with pytest.raises(R.RaycaError) as e:
+        frame.sync()
+    waited = time.perf_counter() - t0
+    assert e.value.code == -6 and "undefined" in str(e.value)
+    assert 0.04 <= waited < 1.5, f"the wait gave up after {waited:.3f} s, limit 50 ms"
+    assert frame.timed_out()
+    with pytest.raises(R.RaycaError):  # sticky: still reported
+        frame.sync()
+    frame.clear_timeout()
+    sc.render_to_frame(cfg, frame, 1, options=M.rayca_options(0, 0, 1, 2, 8, 0, 0))  # the late rank arrives
+    frame.wait(2, 1)
+    frame.sync()
+    assert not frame.timed_out()
+    with pytest.raises(R.RaycaError):
+        frame.set_timeout(0.0)
+    frame.close()
+    sc.close()

@@ -174,3 +174,25 @@ def test_glb_container_and_embedded_buffers(tmp_path):
     (tmp_path / "bad.glb").write_bytes(b"glTF" + struct.pack("<II", 1, 12) + b"\0" * 8)
     with pytest.raises(ValueError):
         M.load_gltf_path(tmp_path / "bad.glb")
+
+
+def test_rust_ffi_mirror_lists_the_same_fields():
+    """rayca-cuda/src/ffi.rs (generated by tools/gen_ffi_rs.py; uncompiled here — no Rust toolchain) declares a
+    #[repr(C)] struct for every struct of the header with the same fields in the same order, and an extern "C"
+    declaration for every exported entry point."""
+    ffi = open(os.path.join(ROOT, "rayca-cuda", "src", "ffi.rs")).read()
+    text = open(os.path.join(ROOT, "include", "rayca_cuda.h")).read()
+    declared = set(re.findall(r"typedef struct (rayca_[a-z_]+) \{", text))
+    for name in sorted(declared):
+        rust = "".join(p.capitalize() for p in name.split("_"))  # rayca_pbr_material -> RaycaPbrMaterial
+        m = re.search(r"#\[repr\(C\)\]\s*#\[derive\([^)]*\)\]\s*pub struct " + rust + r" \{(.*?)\n\}", ffi, flags=re.S)
+        assert m, f"{rust} is missing from rayca-cuda/src/ffi.rs"
+        rust_fields = re.findall(r"pub ([a-z0-9_]+):", m.group(1))
+        if name == "rayca_vertex":
+            assert rust_fields == ["pos", "color", "normal", "tangent", "bitangent", "uv"]
+        else:
+            t = getattr(M, name)
+            assert rust_fields == [f for f, _ in t._fields_], name
+            assert f"size_of::<{rust}>() == {C.sizeof(t)}" in ffi, f"{rust}: size assertion"
+    rust_fns = set(re.findall(r"pub fn (rayca_cuda_[a-z_]+)\(", ffi))
+    assert rust_fns == set(declared_symbols()), rust_fns ^ set(declared_symbols())

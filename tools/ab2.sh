@@ -11,7 +11,7 @@ import sys, json
 for l in sys.stdin:
     l=l.strip()
     if l.startswith('{'):
-        d=json.loads(l); print('value', round(d['value'],1), 'kernel_ms', round(d['kernel_ms'],4), 'e2e', round(d['e2e']['value'],1), 'l2frac', round(d['roofline']['l2']['frac'],3), 'crc', d.get('frame_crc32'), 'clk', d['clocks'])
+        d=json.loads(l); print('value', round(d['value'],1), 'kernel_ms', round(d['kernel_ms'],4), 'e2e', round(d['e2e']['value'],1), 'l2frac', round(d['roofline']['frac'],3), 'crc', d.get('frame_crc32'), 'clk', d['clocks'])
     else: print(l)
 " >> $out
 done
