@@ -474,6 +474,13 @@ int rayca_cuda_scene_bvh_info(rayca_scene* scene, rayca_bvh_info* info);
 int rayca_cuda_scene_bvh_read(rayca_scene* scene, float* nodes, uint32_t* blas_node_offset,
                               uint32_t* blas_prim_offset, uint32_t* prim_src);
 
+/* `Image::dump_png` (rayca-model/src/image.rs:160-169): the RGBA8 frame (row-major, top-left origin) as an 8-bit RGBA,
+ * non-interlaced PNG — to a file, or into a caller buffer.  Host-only (no device needed).  encode_png: `*out_bytes`
+ * always receives the encoded size; with `out` NULL or `capacity` too small the call returns RAYCA_E_INVALID_ARG and
+ * the caller comes back with a buffer of that size.  Decoding the file yields the input bytes exactly. */
+int rayca_cuda_write_png(const char* path, const uint8_t* rgba8, uint32_t width, uint32_t height);
+int rayca_cuda_encode_png(const uint8_t* rgba8, uint32_t width, uint32_t height, uint8_t* out, size_t capacity, size_t* out_bytes);
+
 const char* rayca_cuda_strerror(int code);
 const char* rayca_cuda_last_error(void); /* thread-local detail string */
 uint32_t rayca_cuda_abi_version(void);

@@ -9,7 +9,7 @@ use std::env;
 use std::path::PathBuf;
 use std::process::Command;
 
-const SOURCES: [&str; 5] = ["rayca_cuda.cu", "host_scene.cpp", "bvh_build.cpp", "fast_bvh.cpp", "gpu_fast_build.cu"];
+const SOURCES: [&str; 6] = ["rayca_cuda.cu", "host_scene.cpp", "bvh_build.cpp", "fast_bvh.cpp", "gpu_fast_build.cu", "png_encode.cpp"];
 const HEADERS: [&str; 7] = ["rmath.h", "gpu_types.h", "host_scene.h", "gpu_fast_build.h", "trace.cuh", "shade.cuh", "render.cuh"];
 
 fn main() {
@@ -40,7 +40,7 @@ fn main() {
     println!("cargo:rerun-if-changed={}", src.join("../../include/rayca_cuda.h").display());
     println!("cargo:rerun-if-env-changed=NVCC");
     println!("cargo:rerun-if-env-changed=RAYCA_CUDA_SRC");
-    cmd.arg("-lgomp");
+    cmd.args(["-lgomp", "-lz"]);
     let status = cmd.status().unwrap_or_else(|e| panic!("cannot run {nvcc}: {e} (there is no CPU fallback: the crate needs the CUDA toolkit)"));
     if !status.success() {
         panic!("nvcc failed building librayca_cuda.so for sm_100a");

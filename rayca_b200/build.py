@@ -15,7 +15,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "librayca_cuda.so")
-SOURCES = ["rayca_cuda.cu", "host_scene.cpp", "bvh_build.cpp", "fast_bvh.cpp", "gpu_fast_build.cu"]
+SOURCES = ["rayca_cuda.cu", "host_scene.cpp", "bvh_build.cpp", "fast_bvh.cpp", "gpu_fast_build.cu", "png_encode.cpp"]
 HEADERS = ["rmath.h", "gpu_types.h", "host_scene.h", "gpu_fast_build.h", "trace.cuh", "shade.cuh", "render.cuh",
            os.path.join("..", "..", "include", "rayca_cuda.h")]
 
@@ -47,7 +47,7 @@ def build(force: bool = False, verbose: bool = False, out: str = OUT, defines=()
            "-Xptxas", "-v" if verbose else "-O3"]
     cmd += [f"-D{d}" for d in defines]
     cmd += [os.path.join(CSRC, f) for f in SOURCES]
-    cmd += ["-lgomp"]
+    cmd += ["-lgomp", "-lz"]  # zlib: deflate + crc32 of the PNG encoder (png_encode.cpp)
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         sys.stderr.write(res.stdout + res.stderr)

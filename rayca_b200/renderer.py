@@ -137,9 +137,19 @@ class Image:
                 self.buffer = np.zeros((self.height, self.width, 4), dtype=np.uint8)
 
     def dump_png(self, path) -> None:
-        from PIL import Image as PILImage
+        """Image::dump_png (image.rs:160-169), encoded by the library (rayca_cuda_write_png)."""
+        buf = np.ascontiguousarray(self.buffer)
+        _check(load_library().rayca_cuda_write_png(os.fspath(path).encode(), buf.ctypes.data, self.width, self.height))
 
-        PILImage.fromarray(self.buffer, "RGBA").save(path)
+    def encode_png(self) -> bytes:
+        """The frame as PNG bytes (rayca_cuda_encode_png)."""
+        lib = load_library()
+        buf = np.ascontiguousarray(self.buffer)
+        n = C.c_size_t()
+        lib.rayca_cuda_encode_png(buf.ctypes.data, self.width, self.height, None, 0, C.byref(n))
+        out = C.create_string_buffer(n.value)
+        _check(lib.rayca_cuda_encode_png(buf.ctypes.data, self.width, self.height, out, n.value, C.byref(n)))
+        return out.raw[:n.value]
 
 
 _lib = None
@@ -195,6 +205,8 @@ def load_library():
     lib.rayca_cuda_draw.argtypes = [vp, C.POINTER(M.rayca_config), u32, u32, vp]
     lib.rayca_cuda_scene_bvh_info.argtypes = [vp, C.POINTER(M.rayca_bvh_info)]
     lib.rayca_cuda_scene_bvh_read.argtypes = [vp, vp, vp, vp, vp]
+    lib.rayca_cuda_write_png.argtypes = [C.c_char_p, vp, u32, u32]
+    lib.rayca_cuda_encode_png.argtypes = [vp, u32, u32, vp, C.c_size_t, C.POINTER(C.c_size_t)]
     lib.rayca_cuda_strerror.restype = C.c_char_p
     lib.rayca_cuda_strerror.argtypes = [C.c_int]
     lib.rayca_cuda_last_error.restype = C.c_char_p
