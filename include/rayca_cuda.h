@@ -474,6 +474,22 @@ int rayca_cuda_scene_bvh_info(rayca_scene* scene, rayca_bvh_info* info);
 int rayca_cuda_scene_bvh_read(rayca_scene* scene, float* nodes, uint32_t* blas_node_offset,
                               uint32_t* blas_prim_offset, uint32_t* prim_src);
 
+/* Progressive accumulation across calls (the reference has no counterpart — its `draw` always traces
+ * all samples_per_pixel at once, rayca-soft/src/scene.rs:123-149).  An accumulator holds one running f32 sum per pixel.
+ * Each rayca_cuda_render_accumulate traces the NEXT `sample_count` samples of the config->samples_per_pixel the sequence
+ * is heading for (that total fixes the stratification grid, scene.rs:125-131, and must stay the same over the sequence),
+ * adds them to the sums in sample order and writes sum / (samples so far) -> gamma -> RGBA8 to `rgba8_out` (HOST,
+ * nullable).  Because the additions happen in the order of a single call, the frame written by the call that completes
+ * the sequence equals rayca_cuda_render with the same config byte for byte.  Whole frames only, one device. */
+typedef struct rayca_accum rayca_accum;
+int rayca_cuda_accum_create(rayca_ctx* ctx, uint32_t width, uint32_t height, rayca_accum** out);
+void rayca_cuda_accum_destroy(rayca_accum* accum);
+void rayca_cuda_accum_reset(rayca_accum* accum);       /* start a new sequence (new camera / scene / config) */
+uint32_t rayca_cuda_accum_samples(rayca_accum* accum); /* samples per pixel accumulated so far */
+int rayca_cuda_render_accumulate(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config,
+                                 const rayca_options* options /*nullable*/, rayca_accum* accum, uint32_t sample_count,
+                                 uint8_t* rgba8_out /*nullable*/, rayca_stats* stats /*nullable*/);
+
 /* `Image::dump_png` (rayca-model/src/image.rs:160-169): the RGBA8 frame (row-major, top-left origin) as an 8-bit RGBA,
  * non-interlaced PNG — to a file, or into a caller buffer.  Host-only (no device needed).  encode_png: `*out_bytes`
  * always receives the encoded size; with `out` NULL or `capacity` too small the call returns RAYCA_E_INVALID_ARG and

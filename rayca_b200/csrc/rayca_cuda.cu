@@ -508,9 +508,13 @@ struct Band {
     bool first, last;
 };
 struct FrameTarget {}; // shared-frame launch (rayca_cuda_render_to_frame): pixels at their image row
+struct AccumTarget {   // progressive accumulation (rayca_cuda_render_accumulate)
+    float4* plane;     // width x height running sums
+    uint32_t first, count; // samples [first, first + count) of config->samples_per_pixel
+};
 int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options, uint32_t width,
                    uint32_t height, void* d_rgba8, const rayca_aux_out* d_aux, cudaStream_t st, const Band* band, rayca_stats* stats,
-                   const FrameTarget* target = nullptr);
+                   const FrameTarget* target = nullptr, const AccumTarget* accum = nullptr);
 } // namespace
 
 extern "C" {
@@ -526,7 +530,7 @@ int rayca_cuda_render_device(rayca_ctx* ctx, rayca_scene* scene, const rayca_con
 namespace {
 int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options, uint32_t width,
                    uint32_t height, void* d_rgba8, const rayca_aux_out* d_aux, cudaStream_t st, const Band* band, rayca_stats* stats,
-                   const FrameTarget* target) {
+                   const FrameTarget* target, const AccumTarget* accum) {
     if (!ctx || !scene || !config || !d_rgba8 || width == 0 || height == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
     if (scene->ctx != ctx) return fail(RAYCA_E_INVALID_ARG, "scene belongs to another context (or is host-only)");
     if (!host_of(*scene).has_camera) return fail(RAYCA_E_NO_CAMERA, "no camera node in the scene");
@@ -572,6 +576,19 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     P.step = 1.0f / P.strate_count;
     P.strate_u = (uint32_t)P.strate_count;
     P.inv_gamma = 1.0f / config->gamma;
+    P.sample_first = 0;
+    P.sample_count = config->samples_per_pixel;
+    P.sample_div = (float)config->samples_per_pixel;
+    if (accum) {
+        if (P.shard_count > 1 || band) return fail(RAYCA_E_INVALID_ARG, "accumulation renders whole frames");
+        if (accum->count == 0 || (uint64_t)accum->first + accum->count > config->samples_per_pixel)
+            return fail(RAYCA_E_INVALID_ARG, "sample range beyond config->samples_per_pixel");
+        P.accum = accum->plane;
+        P.accum_load = accum->first > 0 ? 1u : 0u;
+        P.sample_first = accum->first;
+        P.sample_count = accum->count;
+        P.sample_div = (float)(accum->first + accum->count); // the mean of the samples so far; the last call divides by spp
+    }
     P.rgba8 = (unsigned char*)d_rgba8;
     if (d_aux) {
         P.hit_blas = d_aux->hit_blas;
@@ -631,7 +648,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     } else {
         own_rows = height;
     }
-    ctx->last_primary = own_rows * width * (uint64_t)config->samples_per_pixel;
+    ctx->last_primary = own_rows * width * (uint64_t)P.sample_count;
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
         stats->kernel_launches = 1;
@@ -1322,3 +1339,78 @@ extern "C" int rayca_cuda_render_static(rayca_ctx* ctx, rayca_scene* scene, cons
     }
     return RAYCA_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Progressive accumulation across calls.
+struct rayca_accum {
+    rayca_ctx* ctx = nullptr;
+    float4* plane = nullptr; // running per-pixel sums, in sample order
+    unsigned char* rgba8 = nullptr; // device staging plane for the pixels of the latest call
+    uint32_t width = 0, height = 0, done = 0;
+};
+
+extern "C" {
+
+int rayca_cuda_accum_create(rayca_ctx* ctx, uint32_t width, uint32_t height, rayca_accum** out) {
+    if (!ctx || !out || width == 0 || height == 0 || (uint64_t)width * height >= 0xFFFFFFFFull) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    rayca_accum* a = new (std::nothrow) rayca_accum();
+    if (!a) return fail(RAYCA_E_OOM, "host allocation");
+    a->ctx = ctx;
+    a->width = width;
+    a->height = height;
+    const size_t n = (size_t)width * height;
+    cudaError_t ce = cudaMalloc((void**)&a->plane, n * sizeof(float4));
+    if (ce == cudaSuccess) ce = cudaMalloc((void**)&a->rgba8, n * 4);
+    if (ce != cudaSuccess) {
+        rayca_cuda_accum_destroy(a);
+        return fail(ce == cudaErrorMemoryAllocation ? RAYCA_E_OOM : RAYCA_E_CUDA, std::string("accum_create: ") + cudaGetErrorString(ce));
+    }
+    *out = a;
+    return RAYCA_OK;
+}
+
+void rayca_cuda_accum_destroy(rayca_accum* a) {
+    if (!a) return;
+    if (a->ctx) cudaSetDevice(a->ctx->device);
+    cudaFree(a->plane);
+    cudaFree(a->rgba8);
+    delete a;
+}
+
+void rayca_cuda_accum_reset(rayca_accum* a) {
+    if (a) a->done = 0; // the next call starts every pixel from BLACK again and overwrites the plane
+}
+
+uint32_t rayca_cuda_accum_samples(rayca_accum* a) { return a ? a->done : 0; }
+
+int rayca_cuda_render_accumulate(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options,
+                                 rayca_accum* accum, uint32_t sample_count, uint8_t* rgba8_out, rayca_stats* stats) {
+    if (!ctx || !scene || !config || !accum || sample_count == 0) return fail(RAYCA_E_INVALID_ARG, "null / zero argument");
+    if (accum->ctx != ctx) return fail(RAYCA_E_INVALID_ARG, "accumulator belongs to another context");
+    if ((uint64_t)accum->done + sample_count > config->samples_per_pixel)
+        return fail(RAYCA_E_INVALID_ARG, "accumulating " + std::to_string(accum->done) + " + " + std::to_string(sample_count) +
+                                             " samples exceeds config->samples_per_pixel = " + std::to_string(config->samples_per_pixel));
+    if (options && options->shard_count > 1) return fail(RAYCA_E_INVALID_ARG, "accumulation renders whole frames (shard_count <= 1)");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    const AccumTarget t{accum->plane, accum->done, sample_count};
+    double t0 = now_ms();
+    rayca_stats local{};
+    int rc = enqueue_render(ctx, scene, config, options, accum->width, accum->height, accum->rgba8, nullptr, ctx->render_stream, nullptr, &local,
+                            nullptr, &t);
+    if (rc != RAYCA_OK) return rc;
+    if (rgba8_out)
+        CUDA_TRY(cudaMemcpyAsync(rgba8_out, accum->rgba8, (size_t)accum->width * accum->height * 4, cudaMemcpyDeviceToHost, ctx->render_stream));
+    CUDA_TRY(cudaStreamSynchronize(ctx->render_stream));
+    accum->done += sample_count;
+    if (stats) {
+        rc = rayca_cuda_last_counters(ctx, &local);
+        if (rc != RAYCA_OK) return rc;
+        local.kernel_launches = 1;
+        local.readback_ms = std::max(0.0, (now_ms() - t0) - local.trace_ms);
+        *stats = local;
+    }
+    return RAYCA_OK;
+}
+
+} // extern "C"

@@ -38,6 +38,13 @@ struct RenderParams {
     // shared frame (multi-GPU, rayca_cuda_render_to_frame): rgba8 points into the OWNER GPU's frame (peer memory
     // over NVLink) and pixels go to their final row-major position
     uint32_t direct_rows; // 1: write at the image row even when sharded
+    // Progressive accumulation (rayca_cuda_render_accumulate): this launch traces samples [sample_first, sample_first +
+    // sample_count) of the cfg.samples_per_pixel the sequence is heading for (which fixes the strata, scene.rs:125-131),
+    // starts every pixel's sum from `accum` (when accum_load) and leaves the new sum there; the pixel written is
+    // sum / sample_div.  A plain render has sample_first 0, sample_count = sample_div = samples_per_pixel, accum null.
+    float4* accum;
+    uint32_t sample_first, sample_count, accum_load;
+    float sample_div;
 };
 constexpr int kCounterSlots = 8;
 
@@ -900,7 +907,7 @@ __device__ __forceinline__ void trace_sample(const RenderParams& P, uint32_t x, 
 
 // `color /= spp; correct_gamma; *pixel = color.into()` (scene.rs:145-149) plus the optional parity planes.
 __device__ __forceinline__ void write_pixel(const RenderParams& P, uint32_t x, uint32_t y, uint32_t local_row, Col color, const HitD& primary) {
-    color = cdiv(color, (float)P.cfg.samples_per_pixel);
+    color = cdiv(color, P.sample_div);
     if (P.inv_gamma != 1.0f) { // powf(c, 1.0) == c in the reference's libm; skipping it keeps the bits
         color.r = gamma_pow(color.r, P.inv_gamma);
         color.g = gamma_pow(color.g, P.inv_gamma);
@@ -939,16 +946,20 @@ __device__ __forceinline__ void write_pixel(const RenderParams& P, uint32_t x, u
 //     reference's `color += sample` order (scene.rs:129-144), so the f32 sum has the same bits.
 template <int INTEGRATOR, int MODE, bool COUNT, bool BOUNCE>
 __device__ __forceinline__ void render_tile(const RenderParams& P, uint32_t x0, uint32_t row0, uint32_t lane, PixelCounters& pc) {
-    const uint32_t spp = P.cfg.samples_per_pixel;
+    const uint32_t spp = P.sample_count; // samples traced by THIS launch (all of cfg.samples_per_pixel unless accumulating)
     const uint32_t x = x0 + (lane & 7u), local_row = row0 + (lane >> 3);
     const uint32_t y = image_row(P, local_row);
     const bool mine = x < P.width && y < P.row_end;
     Col color{0.0f, 0.0f, 0.0f, 1.0f};
+    if (P.accum && P.accum_load && mine) { // the sum of the samples before sample_first, in sample order
+        const float4 a = P.accum[(size_t)y * P.width + x];
+        color = Col{a.x, a.y, a.z, a.w};
+    }
     HitD primary = no_hit();
     const bool want_aux = P.hit_prim || P.hit_blas || P.hit_src || P.depth || P.uv;
 #pragma unroll 1
     for (uint32_t k0 = 0; k0 < 32u * spp; k0 += 32u) {
-        const uint32_t k = k0 + lane, pl = k / spp, i = k - pl * spp;
+        const uint32_t k = k0 + lane, pl = k / spp, i = P.sample_first + (k - pl * spp);
         const uint32_t sx = x0 + (pl & 7u), srow = row0 + (pl >> 3), sy = image_row(P, srow);
         Col c{0.0f, 0.0f, 0.0f, 1.0f};
         HitD ph = no_hit();
@@ -964,7 +975,7 @@ __device__ __forceinline__ void render_tile(const RenderParams& P, uint32_t x0, 
             Col cs{__shfl_sync(0xFFFFFFFFu, c.r, src), __shfl_sync(0xFFFFFFFFu, c.g, src), __shfl_sync(0xFFFFFFFFu, c.b, src),
                    __shfl_sync(0xFFFFFFFFu, c.a, src)};
             if (ps == lane) color = cadd(color, cs);
-            if (want_aux && ks - ps * spp == spp - 1u) { // the parity planes describe sample spp-1
+            if (want_aux && ks - ps * spp == spp - 1u) { // the parity planes describe the last sample traced
                 const uint32_t hp = __shfl_sync(0xFFFFFFFFu, ph.prim, src);
                 const float ht = __shfl_sync(0xFFFFFFFFu, ph.t, src), hu = __shfl_sync(0xFFFFFFFFu, ph.u, src),
                             hv = __shfl_sync(0xFFFFFFFFu, ph.v, src);
@@ -977,6 +988,7 @@ __device__ __forceinline__ void render_tile(const RenderParams& P, uint32_t x0, 
             }
         }
     }
+    if (P.accum && mine) P.accum[(size_t)y * P.width + x] = make_float4(color.r, color.g, color.b, color.a);
     if (mine) write_pixel(P, x, y, local_row, color, primary);
 }
 

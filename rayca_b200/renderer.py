@@ -205,6 +205,15 @@ def load_library():
     lib.rayca_cuda_draw.argtypes = [vp, C.POINTER(M.rayca_config), u32, u32, vp]
     lib.rayca_cuda_scene_bvh_info.argtypes = [vp, C.POINTER(M.rayca_bvh_info)]
     lib.rayca_cuda_scene_bvh_read.argtypes = [vp, vp, vp, vp, vp]
+    lib.rayca_cuda_accum_create.argtypes = [vp, u32, u32, C.POINTER(vp)]
+    lib.rayca_cuda_accum_destroy.argtypes = [vp]
+    lib.rayca_cuda_accum_destroy.restype = None
+    lib.rayca_cuda_accum_reset.argtypes = [vp]
+    lib.rayca_cuda_accum_reset.restype = None
+    lib.rayca_cuda_accum_samples.argtypes = [vp]
+    lib.rayca_cuda_accum_samples.restype = u32
+    lib.rayca_cuda_render_accumulate.argtypes = [vp, vp, C.POINTER(M.rayca_config), C.POINTER(M.rayca_options), vp, u32, vp,
+                                                 C.POINTER(M.rayca_stats)]
     lib.rayca_cuda_write_png.argtypes = [C.c_char_p, vp, u32, u32]
     lib.rayca_cuda_encode_png.argtypes = [vp, u32, u32, vp, C.c_size_t, C.POINTER(C.c_size_t)]
     lib.rayca_cuda_strerror.restype = C.c_char_p
@@ -386,6 +395,33 @@ class SharedFrame:
             pass
 
 
+class Accumulator:
+    """rayca_accum: running per-pixel sums for progressive rendering (DeviceScene.render_accumulate)."""
+
+    def __init__(self, ctx: Context, width: int, height: int):
+        self.ctx, self.width, self.height = ctx, width, height
+        self._h = C.c_void_p()
+        _check(load_library().rayca_cuda_accum_create(ctx._h, width, height, C.byref(self._h)))
+
+    @property
+    def samples(self) -> int:
+        return load_library().rayca_cuda_accum_samples(self._h)
+
+    def reset(self) -> None:
+        load_library().rayca_cuda_accum_reset(self._h)
+
+    def close(self):
+        if self._h:
+            load_library().rayca_cuda_accum_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class DeviceScene:
     """rayca_scene: the flattened scene + BVH resident in HBM (or host-only when ctx is None)."""
 
@@ -450,6 +486,18 @@ class DeviceScene:
         _check(load_library().rayca_cuda_render_static(self.ctx._h, self._h, C.byref(cfg),
                                                        C.byref(options) if options is not None else None, width, height,
                                                        rgba8.ctypes.data, C.byref(stats)))
+        return rgba8, stats
+
+    def render_accumulate(self, config: Config, accum: Accumulator, sample_count: int,
+                          options: Optional[M.rayca_options] = None, out: Optional[np.ndarray] = None):
+        """rayca_cuda_render_accumulate: the next `sample_count` of config.samples_per_pixel samples; returns
+        (rgba8 of the mean so far, stats)."""
+        rgba8 = out if out is not None else np.zeros((accum.height, accum.width, 4), dtype=np.uint8)
+        stats = M.rayca_stats()
+        cfg = config.to_c()
+        _check(load_library().rayca_cuda_render_accumulate(self.ctx._h, self._h, C.byref(cfg),
+                                                           C.byref(options) if options is not None else None, accum._h,
+                                                           sample_count, rgba8.ctypes.data, C.byref(stats)))
         return rgba8, stats
 
     def render_device(self, config: Config, width: int, height: int, d_rgba8: int, stream: int = 0,

@@ -204,3 +204,34 @@ def test_shared_frame_late_rank_is_reported_not_blended(ctx):
         frame.set_timeout(0.0)
     frame.close()
     sc.close()
+
+
+@pytest.mark.parametrize("scene,cfg,w,h,chunks", [
+    ("suzanne", R.Config(max_depth=1, samples_per_pixel=16), 200, 120, [1, 3, 4, 8]),
+    ("cubes_over_plane", R.Config(max_depth=3, samples_per_pixel=9), 160, 96, [2, 2, 5]),  # bounces: keyed by sample index
+    ("box", R.Config(max_depth=1, samples_per_pixel=1), 64, 64, [1]),
+    ("glass", R.Config(integrator=R.IntegratorStrategy.Scratcher, max_depth=3, samples_per_pixel=4, gamma=2.2), 96, 96, [3, 1]),
+])
+def test_progressive_accumulation_equals_one_call(ctx, scene, cfg, w, h, chunks):
+    """samples accumulated over several calls, in sample order, give the bytes of ONE call with the
+    summed samples_per_pixel (same strata, same f32 additions); intermediate frames are the mean so far."""
+    dev = R.DeviceScene(ctx, load_desc(scene))
+    opts = M.rayca_options(0x5EED, 0, 0, 0, 0, 0, 0)
+    want, _, wst = dev.render(cfg, w, h, options=opts)
+    acc = R.Accumulator(ctx, w, h)
+    for rnd in range(2):  # a reset accumulator starts over
+        rays = 0
+        for n in chunks:
+            got, st = dev.render_accumulate(cfg, acc, n, options=opts)
+            rays += st.rays_primary
+        assert acc.samples == cfg.samples_per_pixel == sum(chunks)
+        assert np.array_equal(got, want), f"round {rnd}: {(got != want).sum()} bytes differ from the single call"
+        assert rays == wst.rays_primary
+        with pytest.raises(R.RaycaError):  # the sequence is complete
+            dev.render_accumulate(cfg, acc, 1, options=opts)
+        acc.reset()
+    if len(chunks) > 1:  # an intermediate frame is the mean of the samples so far: not black, not the final frame
+        mid, _ = dev.render_accumulate(cfg, acc, chunks[0], options=opts)
+        assert mid.any() and mid.shape == want.shape
+    acc.close()
+    dev.close()
