@@ -164,7 +164,7 @@ void launch_one(const RenderParams& P, dim3 groups, int sm_count, cudaStream_t s
         dim3 grid((unsigned)std::max<unsigned long long>(1, std::min(want, cap)));
         render_kernel<INTEGRATOR, MODE, COUNT, true, BOUNCE><<<grid, 128, 0, st>>>(P);
     } else {
-        render_kernel<INTEGRATOR, MODE, COUNT, false, BOUNCE><<<groups, 128, 0, st>>>(P);
+        render_kernel<INTEGRATOR, MODE, COUNT, false, BOUNCE><<<groups, kBlockThreads, 0, st>>>(P);
     }
 }
 
@@ -609,7 +609,8 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
 
     if (first) CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, kCounterSlots * sizeof(unsigned long long), st));
     else if (persistent) CUDA_TRY(cudaMemsetAsync(ctx->d_counters + 5, 0, sizeof(unsigned long long), st)); // next-group counter
-    dim3 grid((width + 15) / 16, (rows + 7) / 8);
+    dim3 grid((width + kGroupW - 1) / kGroupW, (rows + kGroupH - 1) / kGroupH);
+    if (persistent) grid = dim3((width + 15) / 16, (rows + 7) / 8); // the persistent form pulls 16x8 groups
     P.groups_x = grid.x;
     P.tile_count = grid.x * grid.y;
     if (first) CUDA_TRY(cudaEventRecord(ctx->ev0, st));

@@ -998,6 +998,16 @@ __device__ __forceinline__ void render_tile(const RenderParams& P, uint32_t x0, 
 #ifndef RAYCA_MIN_BLOCKS
 #define RAYCA_MIN_BLOCKS 8
 #endif
+// Static grid: warps per block along x and y (each warp an 8x4 pixel tile).  Default 2 x 2 = 128 threads = 16x8 pixels.
+// A/B knobs (tools/variants.py): 2 x 1 = 64 threads, 1 x 1 = one warp per block, 4 x 2 = 256 threads.
+#ifndef RAYCA_WARPS_X
+#define RAYCA_WARPS_X 2
+#endif
+#ifndef RAYCA_WARPS_Y
+#define RAYCA_WARPS_Y 2
+#endif
+constexpr uint32_t kWarpsX = RAYCA_WARPS_X, kWarpsY = RAYCA_WARPS_Y, kBlockThreads = 32u * kWarpsX * kWarpsY;
+constexpr uint32_t kGroupW = 8u * kWarpsX, kGroupH = 4u * kWarpsY; // pixels per block
 
 // Block = 128 threads = 4 warps; a warp owns an 8x4 pixel tile (coherent rays share node fetches
 // through L1), four consecutive tiles form a 16x8 pixel group.
@@ -1008,7 +1018,7 @@ __device__ __forceinline__ void render_tile(const RenderParams& P, uint32_t x0, 
 //     the 1080p frames (profiles/r01_ab_*): the block dispatcher already is a dynamic queue with 16k
 //     entries per frame, and the persistent form adds the fetch latency to every group.
 template <int INTEGRATOR, int MODE, bool COUNT, bool PERSISTENT, bool BOUNCE>
-__global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) render_kernel(const __grid_constant__ RenderParams P) {
+__global__ void __launch_bounds__(kBlockThreads, RAYCA_MIN_BLOCKS) render_kernel(const __grid_constant__ RenderParams P) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     PixelCounters pc;
     if (PERSISTENT) {
@@ -1026,7 +1036,7 @@ __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) render_kernel(const __g
             }
         }
     } else {
-        render_tile<INTEGRATOR, MODE, COUNT, BOUNCE>(P, blockIdx.x * 16u + (warp & 1u) * 8u, blockIdx.y * 8u + (warp >> 1) * 4u, lane, pc);
+        render_tile<INTEGRATOR, MODE, COUNT, BOUNCE>(P, blockIdx.x * kGroupW + (warp % kWarpsX) * 8u, blockIdx.y * kGroupH + (warp / kWarpsX) * 4u, lane, pc);
     }
     // warp-aggregated counters: one atomic per warp per counter
     uint32_t sh = __reduce_add_sync(0xFFFFFFFFu, pc.shadow);

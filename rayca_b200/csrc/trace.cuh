@@ -427,7 +427,7 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
     // 784 B of it, 119 MB per GPU — more than L2 keeps next to the scene — and the evictions showed up as 334 MB
     // of DRAM writes per 1080p frame (profiles/r01_ncu_render_kernel_v4.json).
     constexpr int kSm = RAYCA_SMEM_STACK;
-    __shared__ uint2 s_stack[kSm][128];
+    __shared__ uint2 s_stack[kSm][256];
     uint2 stack[kStackSize + 2 - kSm];
     const uint32_t tid = threadIdx.x;
     s_stack[0][tid] = make_uint2(kDone, 0xff800000u);
