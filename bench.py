@@ -35,7 +35,7 @@ sys.path.insert(0, ROOT)
 def metric_name(args):
     """BASELINE.json's metric on the workload actually run (the default is the 1080p Sponza-class frame)."""
     rays = "primary+shadow" if args.max_depth <= 1 else "primary+shadow+bounce"
-    scene = "Sponza-class scene" if args.workload == "atrium" else f"{args.workload} scene"
+    scene = {"atrium": "Sponza-class scene", "flighthelmet": "FlightHelmet textured PBR model"}.get(args.workload, f"{args.workload} scene")
     res = "1080p" if (args.width, args.height) == (1920, 1080) else f"{args.width}x{args.height}"
     return f"Mrays/s ({rays}, {res} {scene}" + (f", {args.spp} spp" if args.spp > 1 else "") + ")"
 
@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="atrium", choices=["atrium", "soup"])
+    ap.add_argument("--workload", default="atrium", choices=["atrium", "soup", "flighthelmet"])
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--spp", type=int, default=1)
@@ -62,12 +62,31 @@ def parse_args():
     return ap.parse_args()
 
 
+class _FixtureScene:
+    """A committed POD scene descriptor (tests/golden/*.scene.npz) standing in for a Scene object."""
+
+    def __init__(self, name):
+        from rayca_b200 import model as M
+
+        self.desc = M.SceneDesc.load(os.path.join(ROOT, "tests", "golden", f"{name}.scene.npz"))
+
+    def to_desc(self):
+        return self.desc
+
+
 def make_scene(args):
     from rayca_b200 import procedural as P
 
     if args.workload == "soup":
         n = args.triangles or 10_000_000
         return P.soup(n), f"procedural triangle soup, {n} triangles (BASELINE.md M4 generator)"
+    if args.workload == "flighthelmet":
+        # BASELINE config 2 asks for DamagedHelmet, which the reference checkout does not hold; its in-repo textured PBR
+        # model is FlightHelmet with the camera of the reference's `flight` test (rayca-soft/tests/gltf.rs:296-317)
+        return _FixtureScene("flighthelmet"), ("FlightHelmet.gltf (94,722 triangles, 6 PBR materials with albedo + normal + "
+                                               "metallic/roughness maps, textures point-subsampled to 256x256; tests/golden/"
+                                               "flighthelmet.scene.npz), camera of the reference's `flight` test — stand-in for "
+                                               "BASELINE config 2 (DamagedHelmet is not in the reference checkout)")
     n = args.triangles or 262_267
     return P.atrium(n), ("procedural Sponza-class atrium (sponza.bin absent from the reference checkout), "
                          "one BLAS, textured PBR, reference sponza-test camera/lights")
@@ -150,6 +169,15 @@ def sample_rows(args, rows_total):
     return [int(y) for y in ((np.arange(rows_total) + 0.5) / rows_total * args.height).astype(int) % args.height]
 
 
+RNG_SEED = 0x5EED  # key of the Philox counter RNG, the same on both sides
+
+
+def oracle_options():
+    from rayca_b200 import model as M
+
+    return M.rayca_options(RNG_SEED, 0, 0, 0, 0, 0, 0)
+
+
 def cpu_leg(osc, cfg, args, ys, flags, threads=0, keep=False):
     """Times the oracle's pixel loop on image rows `ys` (one call per row; the oracle hands out pixels, not rows, to
     its threads — rayca-soft/src/scene.rs:117-122 — so one row of 1920 pixels keeps every core busy).
@@ -158,7 +186,7 @@ def cpu_leg(osc, cfg, args, ys, flags, threads=0, keep=False):
 
     rays, ms, th, kept = 0, 0.0, 0, {}
     for y in ys:
-        rgba8, aux, st = osc.render(cfg.to_c(), args.width, args.height, flags=flags, threads=threads,
+        rgba8, aux, st = osc.render(cfg.to_c(), args.width, args.height, options=oracle_options(), flags=flags, threads=threads,
                                     rows=(int(y), int(y) + 1), want_aux=keep)
         rays += st.rays_primary + st.rays_shadow + st.rays_secondary
         ms += st.trace_ms
@@ -207,7 +235,7 @@ def cpu_legs(desc, cfg, args, rows, gpu=None):
     out["cpu_baseline"]["scaling_vs_1thread"] = faithful / max(out["cpu_1thread"]["value"], 1e-30)
     opt_frame = None
     try:
-        rgba8, aux, st = osc.render(cfg.to_c(), W, H, flags=O.OPTIMISED, threads=nthr, want_aux=gpu is not None)
+        rgba8, aux, st = osc.render(cfg.to_c(), W, H, options=oracle_options(), flags=O.OPTIMISED, threads=nthr, want_aux=gpu is not None)
         rays = st.rays_primary + st.rays_shadow + st.rays_secondary
         out["cpu_optimised"] = {"value": rays / (st.trace_ms * 1e-3) / 1e6, "unit": "Mrays/s", "cores": st.threads, "kind": "port",
                                 "tree_build_ms": st.opt_build_ms,
@@ -327,6 +355,8 @@ def ncu_profile_name(args, G):
         return "r02_ncu_none.json"
     if args.workload == "soup":
         return "r02_ncu_soup.json"
+    if args.workload == "flighthelmet":
+        return "r02_ncu_flighthelmet.json"
     return "r02_ncu_bounce.json" if args.max_depth > 1 else "r02_ncu_atrium.json"
 
 
@@ -608,7 +638,7 @@ def run_ours(args):
                     if peer else "render_device on every rank + NCCL all_gather + rank-0 copy of the frame to pinned host memory")
     e2e = {"value": rays_frame / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": param_bytes,
            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "what": e2e_what}
-    if G == 1:
+    if G == 1 and not isinstance(scene, _FixtureScene):
         img = R.Image(W, H)
         rnd = R.CudaRenderer.__new__(R.CudaRenderer)
         rnd.config, rnd._ctx = cfg, ctx
@@ -685,7 +715,12 @@ def run_ours(args):
                 "walk": {"node_records_per_ray": cst.node_bytes / 32 / max(rays_local_n, 1),
                          "triangle_bytes_per_ray": cst.triangle_bytes / max(rays_local_n, 1),
                          "algorithmic_bytes_per_ray": algo_bytes / max(rays_local_n, 1)}}
-        if not args.no_cpu_baseline and G == 1:
+        big = desc.triangle_count > 2_000_000 and not args.cpu_rows
+        if big:
+            line["cpu_baseline"] = {"unavailable": "the oracle's verbatim reference builder needs many minutes on this triangle count; "
+                                                   "pass --cpu-rows N to run the CPU legs anyway (parity of this workload's kernel path: "
+                                                   "tests/test_cuda_bench_frames.py::test_soup_16spp_rows_against_the_oracle)"}
+        if not args.no_cpu_baseline and G == 1 and not big:
             # the CUDA frame with its parity planes, through the reference-facing entry point, for the oracle comparison
             g8, gaux, _ = dev.render(cfg, W, H, options=opts, want_aux=True)
             line.update(cpu_legs(desc, cfg, args, args.cpu_rows or 8, gpu=(g8, gaux)))
