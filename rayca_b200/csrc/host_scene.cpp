@@ -638,7 +638,7 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
         return self;
     };
     out.root = emit_tnode(troot, 0);
-    out.max_stack = top_depth + max_blas_depth + 2;
+    out.max_stack = out.ref_stack = top_depth + max_blas_depth + 2;
     phase.lap("TLAS top pairs");
     if (fast_tree) {
         build_fast_tree(out);

@@ -86,7 +86,8 @@ struct HostScene {
     PodVector<float4> tri_attr;
     std::vector<uint32_t> blas_prim_offset, blas_node_offset;
     GpuNode root{};
-    uint32_t max_stack = 0;              // deepest push chain the ordered walk can need
+    uint32_t max_stack = 0;              // deepest push chain any walk of this scene can need (reference tree and performance tree)
+    uint32_t ref_stack = 0;              // ... a walk of the REFERENCE tree (traversal modes 1 / 2): TLAS depth + deepest BLAS + 2
     // performance layer
     std::vector<GpuNode> fast_nodes;
     std::vector<float4> fast_tri;

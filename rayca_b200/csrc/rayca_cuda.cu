@@ -112,6 +112,11 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
             if (c.max_depth + 1 > (uint32_t)kMaxDepth) return fail(RAYCA_E_UNSUPPORTED, "max_depth > 16");
             for (const GpuLight& l : host_of(sc).lights) // Light::get_direction is todo!() for quad lights (light/mod.rs:79-85)
                 if (l.kind == RAYCA_LIGHT_QUAD) return fail(RAYCA_E_UNSUPPORTED, "quad lights under the raytracer / scratcher");
+            // Hit::get_radiance -> get_pbr_material panics for Material::Ggx (the Raytracer's ggx::get_radiance reads PBR
+            // fields, rayca-soft/src/brdf/ggx.rs:11-52): refused like the reference's other panics
+            for (size_t k = 1; k < host_of(sc).materials.size(); ++k)
+                if (host_of(sc).materials[k].kind == RAYCA_MATERIAL_GGX)
+                    return fail(RAYCA_E_UNSUPPORTED, "GGX materials under the raytracer / scratcher (the reference panics)");
             break;
         case RAYCA_INTEGRATOR_PATHTRACER: {
             if (c.direct_sampler != RAYCA_SAMPLER_NEE && c.direct_sampler != RAYCA_SAMPLER_NONE && c.direct_sampler != RAYCA_SAMPLER_MIS)
@@ -354,10 +359,9 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         delete s;
         return fail(RAYCA_E_UNSUPPORTED, "more than 2^27 primitives");
     }
-    if (s->host.max_stack > (uint32_t)kStackSize) {
-        delete s;
-        return fail(RAYCA_E_UNSUPPORTED, "BVH deeper than the traversal stack");
-    }
+    // The reference allows BLAS depths up to 255 (u8 level, blas.rs:302-316); the product walk (traversal 0) never walks
+    // that tree — it only re-validates candidates against reference LEAF boxes — so a deep reference tree is not a
+    // reason to refuse the scene: the check moved to render time, for traversal modes 1 / 2 only.
     double t1 = now_ms();
     HostScene& h = s->host;
 #define UP(dst, vec)                         \
@@ -399,9 +403,18 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         if (std::getenv("RAYCA_TIMING"))
             std::fprintf(stderr, "[rayca] %-28s %8.2f ms (%u levels, %u warp subtrees, depth %u)\n", "performance tree (device)",
                          ft.build_ms, ft.levels, ft.small_subtrees, ft.depth);
-        if (h.max_stack > (uint32_t)kStackSize) {
+    }
+    // The walk's stack holds kStackSize entries and saturates beyond (trace.cuh): a performance tree deeper than that
+    // would drop subtrees silently, so such a scene is refused here, never mis-rendered.  With 16 SAH bins a level
+    // narrows the centroid range 16-fold and the binned builder cannot get near the limit on f32 input; the environment
+    // override exists so that tests can exercise the refusal (tests/test_cuda_edge_cases.py).
+    {
+        uint32_t limit = (uint32_t)kStackSize;
+        if (const char* e = std::getenv("RAYCA_MAX_TREE_DEPTH")) limit = std::min<uint32_t>(limit, (uint32_t)std::max(1, std::atoi(e)));
+        if (h.fast_depth + 2 > limit) {
             rayca_cuda_scene_destroy(s);
-            return fail(RAYCA_E_UNSUPPORTED, "BVH deeper than the traversal stack");
+            return fail(RAYCA_E_UNSUPPORTED, "performance tree deeper than the traversal stack (" + std::to_string(h.fast_depth) + " levels, limit " +
+                                                 std::to_string(limit - 2) + ")");
         }
     }
 #undef UP
@@ -602,6 +615,8 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     if (target || (options && (options->flags & RAYCA_FLAG_DIRECT_ROWS))) P.direct_rows = 1;
     const uint32_t mode = options ? options->traversal : (uint32_t)RAYCA_TRAVERSAL_ORDERED;
     if (mode > RAYCA_TRAVERSAL_REFERENCE_ORDERED) return fail(RAYCA_E_INVALID_ARG, "unknown traversal mode");
+    if (mode != RAYCA_TRAVERSAL_ORDERED && host_of(*scene).ref_stack > (uint32_t)kStackSize)
+        return fail(RAYCA_E_UNSUPPORTED, "reference tree deeper than the traversal stack: traversal modes 1 / 2 cannot walk it (mode 0 can)");
     if (mode != RAYCA_TRAVERSAL_ORDERED && host_of(*scene).has_spheres)
         return fail(RAYCA_E_UNSUPPORTED, "the reference-tree walks (traversal 1 / 2) handle triangle scenes only");
     const bool count = options && (options->flags & RAYCA_FLAG_COUNT_WALK); // opt-in: walk counters cost registers
