@@ -292,11 +292,15 @@ enum {
     RAYCA_FLAG_PERSISTENT = 2, /* persistent warps that pull 16x8 pixel groups from a global counter instead of
                                   one thread block per group.  NOT the default: measured 15-20 % slower than the
                                   static grid on B200 for the 1080p frames (render.cuh, profiles/r01_ab_registers_*) */
-    RAYCA_FLAG_DIRECT_ROWS = 4 /* sharded launches (shard_count > 1): the output pointer addresses the FULL width x height
+    RAYCA_FLAG_DIRECT_ROWS = 4, /* sharded launches (shard_count > 1): the output pointer addresses the FULL width x height
                                   frame and every owned pixel is stored at its final row-major position, instead of the
                                   shard's tiles packed one after the other — a frame all ranks can address (pinned host
                                   memory registered in every process, rayca_cuda_host_register) is then complete once
                                   every rank's launch is, with no gather and no device-to-host copy */
+    RAYCA_FLAG_SHARD_GROUPS = 8 /* with RAYCA_FLAG_DIRECT_ROWS (or a shared frame): the shard owns 16x8 pixel groups in a diagonal
+                                  checkerboard — group (gx, gy) belongs to shard (gx + gy) mod shard_count — instead of
+                                  row tiles.  Every shard then samples the whole image, which evens out the cost between
+                                  shards (8 shards of the 1080p atrium: slowest / mean 1.12 with row tiles) */
 };
 
 /* Optional per-pixel planes for parity checks; any pointer may be NULL.

@@ -560,6 +560,18 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     P.height = height;
     P.shard_count = (options && options->shard_count > 1) ? options->shard_count : 1;
     P.shard_index = options ? options->shard_index : 0;
+    // RAYCA_FLAG_SHARD_GROUPS: shard by 16x8 pixel groups in a diagonal checkerboard instead of row tiles (better balance
+    // between shards: every shard samples the whole image); pixels must then go to their final rows
+    const bool by_groups = P.shard_count > 1 && options && (options->flags & RAYCA_FLAG_SHARD_GROUPS);
+    if (by_groups) {
+        if (!(target || (options->flags & RAYCA_FLAG_DIRECT_ROWS)) || band || d_aux || accum || (options->flags & RAYCA_FLAG_PERSISTENT))
+            return fail(RAYCA_E_INVALID_ARG, "RAYCA_FLAG_SHARD_GROUPS needs RAYCA_FLAG_DIRECT_ROWS (or a shared frame), whole frames, no aux planes, the static grid");
+        if (P.shard_index >= P.shard_count) return fail(RAYCA_E_INVALID_ARG, "shard_index >= shard_count");
+        P.gshard_index = P.shard_index;
+        P.gshard_count = P.shard_count;
+        P.shard_index = 0;
+        P.shard_count = 1;
+    }
     P.tile_rows = (options && options->tile_rows) ? options->tile_rows : 8;
     if (P.tile_rows % 8 != 0) return fail(RAYCA_E_INVALID_ARG, "tile_rows must be a multiple of 8");
     if (P.shard_index >= P.shard_count) return fail(RAYCA_E_INVALID_ARG, "shard_index >= shard_count");
@@ -626,6 +638,10 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     else if (persistent) CUDA_TRY(cudaMemsetAsync(ctx->d_counters + 5, 0, sizeof(unsigned long long), st)); // next-group counter
     dim3 grid((width + kGroupW - 1) / kGroupW, (rows + kGroupH - 1) / kGroupH);
     if (persistent) grid = dim3((width + 15) / 16, (rows + 7) / 8); // the persistent form pulls 16x8 groups
+    if (by_groups) {
+        P.groups_x_full = grid.x;
+        grid.x = (grid.x + P.gshard_count - 1) / P.gshard_count;
+    }
     P.groups_x = grid.x;
     P.tile_count = grid.x * grid.y;
     if (first) CUDA_TRY(cudaEventRecord(ctx->ev0, st));
@@ -655,7 +671,15 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     if (last) CUDA_TRY(cudaEventRecord(ctx->ev1, st));
     // primary rays of this shard: pixels it owns x spp
     uint64_t own_rows = 0;
-    if (P.shard_count > 1) {
+    uint64_t own_pixels = 0;
+    if (by_groups) {
+        const uint32_t gy_n = (height + kGroupH - 1) / kGroupH;
+        for (uint32_t gy = 0; gy < gy_n; ++gy) {
+            const uint32_t h = std::min(height, (gy + 1) * kGroupH) - gy * kGroupH;
+            for (uint32_t gx = (P.gshard_index + P.gshard_count - gy % P.gshard_count) % P.gshard_count; gx < P.groups_x_full; gx += P.gshard_count)
+                own_pixels += (uint64_t)h * (std::min(width, (gx + 1) * kGroupW) - gx * kGroupW);
+        }
+    } else if (P.shard_count > 1) {
         uint32_t tiles = (height + P.tile_rows - 1) / P.tile_rows;
         for (uint32_t t = P.shard_index; t < tiles; t += P.shard_count) {
             uint32_t y0 = t * P.tile_rows, y1 = std::min(height, y0 + P.tile_rows);
@@ -664,7 +688,8 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     } else {
         own_rows = height;
     }
-    ctx->last_primary = own_rows * width * (uint64_t)P.sample_count;
+    if (!by_groups) own_pixels = own_rows * width;
+    ctx->last_primary = own_pixels * (uint64_t)P.sample_count;
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
         stats->kernel_launches = 1;
@@ -1005,7 +1030,7 @@ int render_multi(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config,
         o.tile_rows = kTile;
         void* target = host_view;
         if (host_view) {
-            o.flags |= RAYCA_FLAG_DIRECT_ROWS;
+            o.flags |= RAYCA_FLAG_DIRECT_ROWS | RAYCA_FLAG_SHARD_GROUPS;
         } else {
             const size_t need = (size_t)per * tile_bytes;
             if (need > c->scratch_bytes) {

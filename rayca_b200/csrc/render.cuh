@@ -45,6 +45,10 @@ struct RenderParams {
     float4* accum;
     uint32_t sample_first, sample_count, accum_load;
     float sample_div;
+    // RAYCA_FLAG_SHARD_GROUPS: the shard owns pixel GROUPS (one thread block each) in a diagonal checkerboard —
+    // group (gx, gy) belongs to shard (gx + gy) mod gshard_count — instead of whole row tiles; rows are then image rows
+    // (shard_count = 1 for the row arithmetic) and grid.x enumerates the shard's groups of a group row
+    uint32_t gshard_index, gshard_count, groups_x_full;
 };
 constexpr int kCounterSlots = 8;
 
@@ -1036,7 +1040,12 @@ __global__ void __launch_bounds__(kBlockThreads, RAYCA_MIN_BLOCKS) render_kernel
             }
         }
     } else {
-        render_tile<INTEGRATOR, MODE, COUNT, BOUNCE>(P, blockIdx.x * kGroupW + (warp % kWarpsX) * 8u, blockIdx.y * kGroupH + (warp / kWarpsX) * 4u, lane, pc);
+        uint32_t gx = blockIdx.x;
+        if (P.gshard_count > 1) { // this shard's blockIdx.x-th group of group row blockIdx.y
+            gx = (P.gshard_index + P.gshard_count - blockIdx.y % P.gshard_count) % P.gshard_count + blockIdx.x * P.gshard_count;
+            if (gx >= P.groups_x_full) return; // nothing was traced: the counters below would add zeros
+        }
+        render_tile<INTEGRATOR, MODE, COUNT, BOUNCE>(P, gx * kGroupW + (warp % kWarpsX) * 8u, blockIdx.y * kGroupH + (warp / kWarpsX) * 4u, lane, pc);
     }
     // warp-aggregated counters: one atomic per warp per counter
     uint32_t sh = __reduce_add_sync(0xFFFFFFFFu, pc.shadow);

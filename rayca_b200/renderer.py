@@ -48,6 +48,7 @@ TRAVERSAL_ORDERED, TRAVERSAL_EXHAUSTIVE, TRAVERSAL_REFERENCE_ORDERED = 0, 1, 2
 FLAG_COUNT_WALK = 1
 FLAG_PERSISTENT = 2
 FLAG_DIRECT_ROWS = 4
+FLAG_SHARD_GROUPS = 8  # with DIRECT_ROWS: shard by 16x8 pixel groups in a diagonal checkerboard instead of row tiles
 STATIC_FRAME_BYTES = 8 << 20  # RAYCA_STATIC_FRAME_BYTES: largest width * height * 4 rayca_cuda_render_static accepts
 
 _ERRORS = {-1: "RAYCA_E_INVALID_ARG", -2: "RAYCA_E_UNSUPPORTED", -3: "RAYCA_E_OOM", -4: "RAYCA_E_CUDA",

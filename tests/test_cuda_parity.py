@@ -319,6 +319,40 @@ def test_host_frame_of_three_shards_equals_single_launch(ctx, atrium):
         f.close()
 
 
+@pytest.mark.parametrize("G", [2, 3, 8])
+def test_group_checkerboard_shards_equal_single_launch(ctx, atrium, G):
+    """RAYCA_FLAG_SHARD_GROUPS: shard (gx + gy) mod G owns 16x8 pixel group (gx, gy); every pixel is stored exactly once,
+    into a host frame (DIRECT_ROWS) and into a shared device frame; the ray counts of the shards add up to the frame's."""
+    import torch
+
+    cfg = R.Config(max_depth=1)
+    w, h = 1283, 721  # ragged in x and y
+    full, _, fst = atrium.render(cfg, w, h)
+    flags = R.FLAG_DIRECT_ROWS | R.FLAG_SHARD_GROUPS
+    f = R.HostFrame(w, h)
+    try:
+        f.pixels[...] = 0
+        rays = [0, 0]
+        for g in range(G):
+            _, _, st = atrium.render(cfg, w, h, out=f.pixels, options=M.rayca_options(0, 0, g, G, 8, flags, 0))
+            rays[0] += st.rays_primary
+            rays[1] += st.rays_shadow
+        assert np.array_equal(f.pixels, full), f"{(f.pixels != full).sum()} bytes differ"
+        assert rays == [fst.rays_primary, fst.rays_shadow]
+    finally:
+        f.close()
+    frame = R.SharedFrame(ctx, w, h)
+    for g in range(G):
+        atrium.render_to_frame(cfg, frame, 1, options=M.rayca_options(0, 0, g, G, 8, R.FLAG_SHARD_GROUPS, 0))
+    torch.cuda.synchronize()
+    assert np.array_equal(torch.as_tensor(frame, device="cuda:0").cpu().numpy(), full)
+    frame.close()
+    with pytest.raises(R.RaycaError) as e:  # compact (tile-packed) output cannot be sharded by groups
+        buf = torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda:0")
+        atrium.render_device(cfg, w, h, buf.data_ptr(), options=M.rayca_options(0, 0, 0, G, 8, R.FLAG_SHARD_GROUPS, 0))
+    assert e.value.code == -1
+
+
 def test_shared_frame_wait_times_out_instead_of_hanging(ctx, atrium):
     """A rank that never publishes its flag must not hang the owner: the wait kernel gives up after ~2 s and
     frame_timed_out reports it."""

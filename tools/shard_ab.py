@@ -36,7 +36,8 @@ def main():
     stream = torch.cuda.current_stream().cuda_stream
 
     def time_shard(r, K):
-        opts = M.rayca_options(0x5EED, 0, r, K, a.tile, a.flags, 0)
+        fl = a.flags | (R.FLAG_DIRECT_ROWS if (a.flags & R.FLAG_SHARD_GROUPS) and K > 1 else 0)
+        opts = M.rayca_options(0x5EED, 0, r, K, a.tile, fl if K > 1 else (a.flags & ~R.FLAG_SHARD_GROUPS), 0)
         for _ in range(3):
             dev.render_device(cfg, W, H, buf.data_ptr(), stream=stream, options=opts)
         ms = []
