@@ -299,8 +299,10 @@ enum {
                                   every rank's launch is, with no gather and no device-to-host copy */
     RAYCA_FLAG_SHARD_GROUPS = 8 /* with RAYCA_FLAG_DIRECT_ROWS (or a shared frame): the shard owns 16x8 pixel groups in a diagonal
                                   checkerboard — group (gx, gy) belongs to shard (gx + gy) mod shard_count — instead of
-                                  row tiles.  Every shard then samples the whole image, which evens out the cost between
-                                  shards (8 shards of the 1080p atrium: slowest / mean 1.12 with row tiles) */
+                                  row tiles, so that every shard samples the whole image.  An option, not the default:
+                                  on the 1080p atrium split 8 ways it measured no better than row tiles (slowest / mean
+                                  1.09 against 1.12, mean 3 % worse: scattered groups lose cache locality), see
+                                  profiles/r02_shard_emulation.txt */
 };
 
 /* Optional per-pixel planes for parity checks; any pointer may be NULL.

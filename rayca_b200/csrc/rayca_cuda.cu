@@ -1030,7 +1030,7 @@ int render_multi(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config,
         o.tile_rows = kTile;
         void* target = host_view;
         if (host_view) {
-            o.flags |= RAYCA_FLAG_DIRECT_ROWS | RAYCA_FLAG_SHARD_GROUPS;
+            o.flags |= RAYCA_FLAG_DIRECT_ROWS; // row tiles: measured as fast as the group checkerboard and kinder to the caches
         } else {
             const size_t need = (size_t)per * tile_bytes;
             if (need > c->scratch_bytes) {
