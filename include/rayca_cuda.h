@@ -415,8 +415,8 @@ int rayca_cuda_init(int device, rayca_ctx** out);
  * (NULL / 0 = every visible device; an index may appear more than once, each entry is a shard of its own).
  * rayca_cuda_scene_create builds the scene on devices[0] and copies the finished device arrays to the others;
  * rayca_cuda_render interleaves the frame's 8-row tiles over the devices and every device's kernel stores its
- * tiles at their final rows of the caller's buffer (pinned buffers: zero copy over each device's own PCIe link;
- * pageable buffers: one strided copy per device).  Calls with aux planes or an explicit shard run on devices[0].
+ * tiles at their final rows (pinned caller buffers: zero copy over each device's own PCIe link; pageable buffers:
+ * through a pinned staging frame the context owns, copied out by the calling thread's OpenMP team).  Calls with aux planes or an explicit shard run on devices[0].
  * The context's other entry points (render_device, render_to_frame, render_static, frames) address devices[0]. */
 int rayca_cuda_init_devices(const int* devices, int device_count, rayca_ctx** out);
 int rayca_cuda_device_count(rayca_ctx* ctx); /* shards of the context: 1 for rayca_cuda_init */

@@ -55,6 +55,9 @@ struct rayca_ctx {
     // single-device context of its own; scene_create replicates the scene on them and rayca_cuda_render shards the
     // frame's row tiles over all of them from the ONE calling host thread
     std::vector<rayca_ctx*> extra;
+    // pinned (portable, mapped) staging frame of a multi-device context: pageable caller buffers are filled through it
+    unsigned char* h_stage = nullptr;
+    size_t h_stage_bytes = 0;
 };
 
 struct rayca_scene {
@@ -295,6 +298,7 @@ void rayca_cuda_shutdown(rayca_ctx* c) {
     cudaSetDevice(c->device);
     cudaFree(c->d_counters);
     cudaFree(c->d_scratch);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->render_stream) cudaStreamDestroy(c->render_stream);
@@ -998,8 +1002,8 @@ namespace {
 // evenly), every device's launch is enqueued on its own stream before any of them is waited for, and
 //   * a pinned / registered caller buffer is filled by the kernels' own stores (RAYCA_FLAG_DIRECT_ROWS): G PCIe links
 //     in parallel, no staging plane, no copy;
-//   * a pageable caller buffer gets each device's tiles from that device's staging plane with ONE strided copy
-//     (cudaMemcpy2DAsync: a "row" is a tile of 8 image rows, the destination pitch is G tiles).
+//   * a pageable caller buffer is filled through a pinned staging frame the context owns: the kernels store into that,
+//     the calling thread's OpenMP team copies it out.
 // This is the reference's fan-out (`par_iter_mut` over rows and pixels inside one `draw` call,
 // rayca-soft/src/scene.rs:117-122) with devices in place of rayon workers.
 int render_multi(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config, const rayca_options* options, uint32_t width,
@@ -1007,8 +1011,7 @@ int render_multi(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config,
     const uint32_t G = 1u + (uint32_t)ctx->extra.size();
     if (scene->replicas.size() + 1 != G) return fail(RAYCA_E_INVALID_ARG, "scene was not created on this multi-device context");
     constexpr uint32_t kTile = 8;
-    const size_t tile_bytes = (size_t)kTile * width * 4;
-    const uint32_t tiles = (height + kTile - 1) / kTile, per = (tiles + G - 1) / G;
+    const size_t frame_bytes = (size_t)width * height * 4;
     void* host_view = nullptr;
     {
         cudaPointerAttributes at{};
@@ -1016,6 +1019,22 @@ int render_multi(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config,
         cudaGetLastError();
         const char* e = std::getenv("RAYCA_ZERO_COPY");
         if (e && std::atoi(e) == 0) host_view = nullptr; // A/B runs and tests: force the staged path
+    }
+    // A pageable caller buffer (a Rust Vec<u8>, a numpy array) cannot be stored into by the devices, and strided
+    // device-to-pageable copies are slow (measured: 8 GPUs 2.7 Grays/s against 5.2 on ONE device).  So the devices
+    // store into a pinned staging frame the context owns (allocated once, reused across calls) and the calling
+    // thread's OpenMP team copies it to the caller's buffer.
+    const bool staged = host_view == nullptr;
+    if (staged) {
+        if (frame_bytes > ctx->h_stage_bytes) {
+            CUDA_TRY(cudaSetDevice(ctx->device));
+            if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+            ctx->h_stage = nullptr;
+            ctx->h_stage_bytes = 0;
+            CUDA_TRY(cudaHostAlloc((void**)&ctx->h_stage, frame_bytes, cudaHostAllocPortable | cudaHostAllocMapped));
+            ctx->h_stage_bytes = frame_bytes;
+        }
+        CUDA_TRY(cudaHostGetDevicePointer(&host_view, ctx->h_stage, 0));
     }
     double t0 = now_ms();
     int rc = RAYCA_OK;
@@ -1028,33 +1047,8 @@ int render_multi(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config,
         o.shard_index = r;
         o.shard_count = G;
         o.tile_rows = kTile;
-        void* target = host_view;
-        if (host_view) {
-            o.flags |= RAYCA_FLAG_DIRECT_ROWS; // row tiles: measured as fast as the group checkerboard and kinder to the caches
-        } else {
-            const size_t need = (size_t)per * tile_bytes;
-            if (need > c->scratch_bytes) {
-                cudaFree(c->d_scratch);
-                c->d_scratch = nullptr;
-                c->scratch_bytes = 0;
-                CUDA_TRY(cudaMalloc(&c->d_scratch, need));
-                c->scratch_bytes = need;
-            }
-            target = c->d_scratch;
-        }
-        rc = enqueue_render(c, sc, config, &o, width, height, target, nullptr, c->render_stream, nullptr, nullptr);
-        if (rc != RAYCA_OK) break;
-        if (!host_view && r < tiles) {
-            const uint32_t mine = (tiles - r + G - 1) / G;           // tiles t = r, r + G, ... below `tiles`
-            const bool owns_tail = (height % kTile) != 0 && (tiles - 1) % G == r;
-            const uint32_t full = owns_tail ? mine - 1 : mine;
-            if (full)
-                CUDA_TRY(cudaMemcpy2DAsync(rgba8_out + (size_t)r * tile_bytes, (size_t)G * tile_bytes, c->d_scratch, tile_bytes, tile_bytes, full,
-                                           cudaMemcpyDeviceToHost, c->render_stream));
-            if (owns_tail)
-                CUDA_TRY(cudaMemcpyAsync(rgba8_out + (size_t)(tiles - 1) * tile_bytes, (unsigned char*)c->d_scratch + (size_t)(mine - 1) * tile_bytes,
-                                         (size_t)(height % kTile) * width * 4, cudaMemcpyDeviceToHost, c->render_stream));
-        }
+        o.flags |= RAYCA_FLAG_DIRECT_ROWS; // row tiles: measured as fast as the group checkerboard and kinder to the caches
+        rc = enqueue_render(c, sc, config, &o, width, height, host_view, nullptr, c->render_stream, nullptr, nullptr);
     }
     // wait for every device even after a failure: nothing may still be writing into the caller's buffer on return
     rayca_stats total{};
@@ -1078,6 +1072,12 @@ int render_multi(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config,
     }
     cudaSetDevice(ctx->device);
     if (rc != RAYCA_OK) return rc;
+    if (staged) { // rows in parallel: one thread moves ~10 GB/s, the frame is 8 MB
+        const size_t row = (size_t)width * 4;
+        const unsigned char* src = ctx->h_stage;
+#pragma omp parallel for schedule(static)
+        for (int64_t y = 0; y < (int64_t)height; ++y) std::memcpy(rgba8_out + (size_t)y * row, src + (size_t)y * row, row);
+    }
     if (stats) {
         total.readback_ms = std::max(0.0, (now_ms() - t0) - total.trace_ms);
         *stats = total;
