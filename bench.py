@@ -209,6 +209,7 @@ def host_threads():
 
 
 def cpu_legs(desc, cfg, args, rows, gpu=None):
+    os.environ.setdefault("OMP_NUM_THREADS", str(host_threads()))
     """Every CPU figure of the bench line, all on the same fixed rows of the same frame:
       faithful   = the reference's algorithm (exhaustive unordered walk of the reference BVH, vertices re-transformed
                    per test) on all host threads — "rayca-soft on the host cores";
@@ -304,6 +305,8 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1; the oracle's scene build (and libgomp's pool) reads it when the library loads
+    os.environ["OMP_NUM_THREADS"] = str(host_threads())
     from oracle import binding as O
 
     scene, what = make_scene(args)
@@ -647,9 +650,17 @@ def run_ours(args):
             t1 = time.perf_counter()
             rnd.draw(scene, img)
             draws.append((time.perf_counter() - t1) * 1e3)
-        draw_e2e = {"ms": sorted(draws[1:])[1], "first_ms": draws[0],
-                    "what": "Draw::draw, median of 3 after one warm-up call: to_desc + flatten + reference BLAS and performance tree "
-                            "(both built on the GPU) + upload + render + read-back"}
+        lib_draws = []  # the library's share: what a Rust caller pays after its own FlatScene::from (rayca_cuda_draw-equivalent)
+        for _ in range(4):
+            t1 = time.perf_counter()
+            d2 = R.DeviceScene(ctx, desc, cfg.bvh)
+            d2.render(cfg, W, H, out=img.buffer)
+            d2.close()
+            lib_draws.append((time.perf_counter() - t1) * 1e3)
+        draw_e2e = {"ms": sorted(draws[1:])[1], "first_ms": draws[0], "library_ms": sorted(lib_draws[1:])[1],
+                    "what": "Draw::draw, median of 3 after one warm-up call: to_desc (Python harness) + flatten + reference BLAS and "
+                            "performance tree (both built on the GPU) + upload + render + read-back; library_ms = the same without "
+                            "to_desc: rayca_cuda_scene_create + rayca_cuda_render + rayca_cuda_scene_destroy through the C ABI"}
 
     if rank == 0:
         peaks = {}
