@@ -297,6 +297,9 @@ enum {
                                   shard's tiles packed one after the other — a frame all ranks can address (pinned host
                                   memory registered in every process, rayca_cuda_host_register) is then complete once
                                   every rank's launch is, with no gather and no device-to-host copy */
+    RAYCA_FLAG_NO_WAVEFRONT = 16, /* path tracing with bounces normally runs as wavefront stages with the live rays sorted
+                                     between depths (wavefront.cu); this flag keeps the one fused kernel (A/B runs, tests:
+                                     both produce the same bytes) */
     RAYCA_FLAG_SHARD_GROUPS = 8 /* with RAYCA_FLAG_DIRECT_ROWS (or a shared frame): the shard owns 16x8 pixel groups in a diagonal
                                   checkerboard — group (gx, gy) belongs to shard (gx + gy) mod shard_count — instead of
                                   row tiles, so that every shard samples the whole image.  An option, not the default:

@@ -15,8 +15,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "librayca_cuda.so")
-SOURCES = ["rayca_cuda.cu", "host_scene.cpp", "bvh_build.cpp", "fast_bvh.cpp", "gpu_fast_build.cu", "png_encode.cpp"]
-HEADERS = ["rmath.h", "gpu_types.h", "host_scene.h", "gpu_fast_build.h", "trace.cuh", "shade.cuh", "render.cuh",
+SOURCES = ["rayca_cuda.cu", "host_scene.cpp", "bvh_build.cpp", "fast_bvh.cpp", "gpu_fast_build.cu", "png_encode.cpp", "wavefront.cu"]
+HEADERS = ["rmath.h", "gpu_types.h", "host_scene.h", "gpu_fast_build.h", "trace.cuh", "shade.cuh", "render.cuh", "wavefront.h",
            os.path.join("..", "..", "include", "rayca_cuda.h")]
 
 
@@ -40,20 +40,37 @@ def build(force: bool = False, verbose: bool = False, out: str = OUT, defines=()
     if out == OUT and not force and not is_stale():
         return OUT
     host_cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
-    cmd = [nvcc_path(), "-shared", "-o", out, "-std=c++17", "-O3", "-lineinfo",
-           "-gencode", "arch=compute_100a,code=sm_100a", "--fmad=false",
-           "-ccbin", host_cxx, "-x", "cu",
-           "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math,-fopenmp,-O2",
-           "-Xptxas", "-v" if verbose else "-O3"]
-    cmd += [f"-D{d}" for d in defines]
-    cmd += [os.path.join(CSRC, f) for f in SOURCES]
-    cmd += ["-lgomp", "-lz"]  # zlib: deflate + crc32 of the PNG encoder (png_encode.cpp)
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        sys.stderr.write(res.stdout + res.stderr)
-        raise RuntimeError("nvcc failed")
+    common = [nvcc_path(), "-std=c++17", "-O3", "-lineinfo",
+              "-gencode", "arch=compute_100a,code=sm_100a", "--fmad=false",
+              "-ccbin", host_cxx, "-x", "cu",
+              "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math,-fopenmp,-O2",
+              "-Xptxas", "-v" if verbose else "-O3"]
+    common += [f"-D{d}" for d in defines]
+    # one nvcc per source, side by side (the two kernel translation units take over a minute each), then one link
+    import tempfile
+    from concurrent.futures import ThreadPoolExecutor
+
+    with tempfile.TemporaryDirectory(prefix="rayca_build_") as tmp:
+        def compile_one(src):
+            obj = os.path.join(tmp, os.path.splitext(src)[0] + ".o")
+            res = subprocess.run(common + ["-c", os.path.join(CSRC, src), "-o", obj], capture_output=True, text=True)
+            return src, obj, res
+
+        with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
+            results = list(ex.map(compile_one, SOURCES))
+        log = "".join(r.stdout + r.stderr for _, _, r in results)
+        if any(r.returncode != 0 for _, _, r in results):
+            sys.stderr.write(log)
+            raise RuntimeError("nvcc failed")
+        link = [nvcc_path(), "-shared", "-o", out, "-ccbin", host_cxx, "-gencode", "arch=compute_100a,code=sm_100a"]
+        link += [obj for _, obj, _ in results] + ["-lgomp", "-lz"]  # zlib: deflate + crc32 of the PNG encoder (png_encode.cpp)
+        res = subprocess.run(link, capture_output=True, text=True)
+        log += res.stdout + res.stderr
+        if res.returncode != 0:
+            sys.stderr.write(log)
+            raise RuntimeError("nvcc link failed")
     if verbose:
-        sys.stderr.write(res.stdout + res.stderr)
+        sys.stderr.write(log)
     return out
 
 

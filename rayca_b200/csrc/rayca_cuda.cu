@@ -13,6 +13,7 @@
 #include "gpu_fast_build.h"
 #include "host_scene.h"
 #include "render.cuh"
+#include "wavefront.h"
 
 using namespace rb;
 
@@ -58,6 +59,7 @@ struct rayca_ctx {
     // pinned (portable, mapped) staging frame of a multi-device context: pageable caller buffers are filled through it
     unsigned char* h_stage = nullptr;
     size_t h_stage_bytes = 0;
+    rb::WaveScratch wave; // device scratch of the wavefront path (wavefront.cu)
 };
 
 struct rayca_scene {
@@ -298,6 +300,7 @@ void rayca_cuda_shutdown(rayca_ctx* c) {
     cudaSetDevice(c->device);
     cudaFree(c->d_counters);
     cudaFree(c->d_scratch);
+    cudaFree(c->wave.base);
     if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -662,6 +665,14 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
             for (const GpuLight& l : host_of(*scene).lights) general = general || l.kind == RAYCA_LIGHT_QUAD;
         if (general) integrator = kInternalPathGeneral;
     }
+    uint32_t launches = 1;
+    const bool no_wave = options && (options->flags & RAYCA_FLAG_NO_WAVEFRONT);
+    if (!no_wave && !by_groups && wave_supported(P, mode, count, persistent, integrator == kInternalPathGeneral, sel.bounce)) {
+        // bounce rays: wavefront stages with the live rays sorted between depths (wavefront.cu)
+        std::string werr;
+        rc = wave_render(P, rows, sel.spheres, ctx->wave, st, &launches, werr);
+        if (rc != RAYCA_OK) return fail(rc, werr);
+    } else
     switch (integrator) {
         case kInternalPathGeneral: launch_integrator<(int)kInternalPathGeneral>(P, grid, sel, st); break;
         case RAYCA_INTEGRATOR_PATHTRACER: launch_integrator<RAYCA_INTEGRATOR_PATHTRACER>(P, grid, sel, st); break;
@@ -696,7 +707,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     ctx->last_primary = own_pixels * (uint64_t)P.sample_count;
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
-        stats->kernel_launches = 1;
+        stats->kernel_launches = launches;
         stats->rays_primary = ctx->last_primary;
     }
     return RAYCA_OK;

@@ -841,7 +841,7 @@ __device__ __forceinline__ unsigned char quantize(float c) {
 // One pixel: every sample's primary ray through the integrator, accumulation, gamma, RGBA8
 // (rayca-soft/src/scene.rs:123-149).
 // correct_gamma (color/mod.rs:175-180): one shared copy of powf
-__device__ __noinline__ float gamma_pow(float c, float inv_gamma) { return powf(c, inv_gamma); }
+static __device__ __noinline__ float gamma_pow(float c, float inv_gamma) { return powf(c, inv_gamma); }
 
 // image row of a launch-local row (row bands of the host path, interleaved tiles of a shard)
 __device__ __forceinline__ uint32_t image_row(const RenderParams& P, uint32_t local_row) {
@@ -863,11 +863,10 @@ __device__ __forceinline__ HitD no_hit() {
 }
 
 // One sample of one pixel: primary ray (scene.rs:129-141) through the integrator (scene.rs:80-86).
-template <int INTEGRATOR, int MODE, bool COUNT, bool BOUNCE>
-__device__ __forceinline__ void trace_sample(const RenderParams& P, uint32_t x, uint32_t y, uint32_t i, Col& c, HitD& ph, PixelCounters& pc) {
+// Primary ray of sample i of pixel (x, y) (scene.rs:129-141)
+__device__ __forceinline__ RayD primary_ray(const RenderParams& P, uint32_t x, uint32_t y, uint32_t i) {
     const GpuCamera& cam = P.scene.camera;
     const TrsF ctrs{V3{cam.t[0], cam.t[1], cam.t[2]}, Q4{cam.q[0], cam.q[1], cam.q[2], cam.q[3]}, V3{cam.s[0], cam.s[1], cam.s[2]}};
-    const uint32_t pixel = y * P.width + x;
     float ix = (float)(i % P.strate_u);
     float iy = (float)(i / P.strate_u);
     float xx = (2.0f * (((float)x + ix * P.step + P.offset) * P.inv_w) - 1.0f) * cam.angle * P.aspect;
@@ -876,7 +875,13 @@ __device__ __forceinline__ void trace_sample(const RenderParams& P, uint32_t x, 
     // &camera_trs.trs * Ray::new(origin, dir): scale, rotate, translate (trs.rs:275-284); no re-normalise
     V3 wd = rotate(dir * ctrs.s, ctrs.q);
     V3 wo = rotate(scale_point(V3{0.0f, 0.0f, 0.0f}, ctrs.s), ctrs.q) + ctrs.t;
-    RayD ray = make_ray(wo, wd);
+    return make_ray(wo, wd);
+}
+
+template <int INTEGRATOR, int MODE, bool COUNT, bool BOUNCE>
+__device__ __forceinline__ void trace_sample(const RenderParams& P, uint32_t x, uint32_t y, uint32_t i, Col& c, HitD& ph, PixelCounters& pc) {
+    const uint32_t pixel = y * P.width + x;
+    RayD ray = primary_ray(P, x, y, i);
     c = Col{0.0f, 0.0f, 0.0f, 1.0f};
     bool ok;
     ph = no_hit();
@@ -910,7 +915,8 @@ __device__ __forceinline__ void trace_sample(const RenderParams& P, uint32_t x, 
 }
 
 // `color /= spp; correct_gamma; *pixel = color.into()` (scene.rs:145-149) plus the optional parity planes.
-__device__ __forceinline__ void write_pixel(const RenderParams& P, uint32_t x, uint32_t y, uint32_t local_row, Col color, const HitD& primary) {
+// the colour half: `/ spp`, gamma, quantisation, RGBA8 (and the float plane)
+__device__ __forceinline__ void write_pixel_color(const RenderParams& P, uint32_t x, uint32_t y, uint32_t local_row, Col color) {
     color = cdiv(color, P.sample_div);
     if (P.inv_gamma != 1.0f) { // powf(c, 1.0) == c in the reference's libm; skipping it keeps the bits
         color.r = gamma_pow(color.r, P.inv_gamma);
@@ -920,6 +926,11 @@ __device__ __forceinline__ void write_pixel(const RenderParams& P, uint32_t x, u
     const size_t o = (size_t)((P.shard_count > 1 && !P.direct_rows) ? local_row : y) * P.width + x;
     uchar4 q = make_uchar4(quantize(color.r), quantize(color.g), quantize(color.b), quantize(color.a));
     reinterpret_cast<uchar4*>(P.rgba8)[o] = q;
+    if (P.rgba_f32) reinterpret_cast<float4*>(P.rgba_f32)[o] = make_float4(color.r, color.g, color.b, color.a);
+}
+// the parity planes of the primary hit
+__device__ __forceinline__ void write_pixel_aux(const RenderParams& P, uint32_t x, uint32_t y, uint32_t local_row, const HitD& primary) {
+    const size_t o = (size_t)((P.shard_count > 1 && !P.direct_rows) ? local_row : y) * P.width + x;
     const bool hit = primary.prim != 0xFFFFFFFFu;
     if (P.hit_prim || P.hit_blas || P.hit_src) {
         uint32_t blas = 0xFFFFFFFFu, local = 0xFFFFFFFFu, src = 0xFFFFFFFFu;
@@ -938,7 +949,10 @@ __device__ __forceinline__ void write_pixel(const RenderParams& P, uint32_t x, u
         P.uv[2 * o] = hit ? primary.u : 0.0f;
         P.uv[2 * o + 1] = hit ? primary.v : 0.0f;
     }
-    if (P.rgba_f32) reinterpret_cast<float4*>(P.rgba_f32)[o] = make_float4(color.r, color.g, color.b, color.a);
+}
+__device__ __forceinline__ void write_pixel(const RenderParams& P, uint32_t x, uint32_t y, uint32_t local_row, Col color, const HitD& primary) {
+    write_pixel_color(P, x, y, local_row, color);
+    write_pixel_aux(P, x, y, local_row, primary);
 }
 
 // One warp, one 8x4 pixel tile.

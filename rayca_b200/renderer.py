@@ -48,6 +48,7 @@ TRAVERSAL_ORDERED, TRAVERSAL_EXHAUSTIVE, TRAVERSAL_REFERENCE_ORDERED = 0, 1, 2
 FLAG_COUNT_WALK = 1
 FLAG_PERSISTENT = 2
 FLAG_DIRECT_ROWS = 4
+FLAG_NO_WAVEFRONT = 16  # keep the fused kernel for bounce frames (A/B, tests)
 FLAG_SHARD_GROUPS = 8  # with DIRECT_ROWS: shard by 16x8 pixel groups in a diagonal checkerboard instead of row tiles
 STATIC_FRAME_BYTES = 8 << 20  # RAYCA_STATIC_FRAME_BYTES: largest width * height * 4 rayca_cuda_render_static accepts
 

@@ -353,6 +353,48 @@ def test_group_checkerboard_shards_equal_single_launch(ctx, atrium, G):
     assert e.value.code == -1
 
 
+@pytest.mark.parametrize("scene,cfg,w,h", [
+    ("suzanne", R.Config(max_depth=2), 333, 217),
+    ("cubes_over_plane", R.Config(max_depth=3), 256, 144),
+    ("cubes_over_plane", R.Config(max_depth=5, direct_sampler=R.SamplerStrategy.NONE), 160, 90),  # no NEE: emissive-only paths
+    ("normalquad", R.Config(max_depth=4), 200, 120),
+    ("box", R.Config(max_depth=17), 96, 96),  # the deepest path the fused kernel keeps
+    ("scratcher_sphere", R.Config(max_depth=2), 128, 128),  # spheres: kernel instantiation MODE 3
+])
+def test_wavefront_stages_equal_the_fused_kernel(ctx, scene, cfg, w, h):
+    """bounce rays run as wavefront stages with the live rays radix-sorted between depths
+    (wavefront.cu).  The RNG is keyed by (pixel, sample, depth, dimension) and every value is computed by the same
+    device functions in the same order, so the frame, the parity planes and the ray counts equal the fused kernel's
+    (RAYCA_FLAG_NO_WAVEFRONT) bit for bit — through rayca_cuda_render (row bands), and sharded."""
+    import torch
+
+    sc = dev_scene(ctx, scene)
+    wave = M.rayca_options(0x5EED, 0, 0, 0, 0, 0, 0)
+    fused = M.rayca_options(0x5EED, 0, 0, 0, 0, R.FLAG_NO_WAVEFRONT, 0)
+    a8, a, ast = sc.render(cfg, w, h, options=wave, want_aux=True)
+    b8, b, bst = sc.render(cfg, w, h, options=fused, want_aux=True)
+    assert np.array_equal(a8, b8), f"{(a8 != b8).sum()} bytes differ"
+    assert np.array_equal(a.rgba_f32.view(np.uint32), b.rgba_f32.view(np.uint32))
+    assert np.array_equal(a.hit_src, b.hit_src) and np.array_equal(a.depth, b.depth) and np.array_equal(a.uv, b.uv)
+    assert (ast.rays_primary, ast.rays_shadow, ast.rays_secondary) == (bst.rays_primary, bst.rays_shadow, bst.rays_secondary)
+    assert ast.kernel_launches > bst.kernel_launches  # the stages really ran
+    # one launch over the whole frame on device memory, and three compact shards reassembled
+    buf = torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda:0")
+    sc.render_device(cfg, w, h, buf.data_ptr(), options=wave)
+    torch.cuda.synchronize()
+    assert np.array_equal(buf.cpu().numpy(), b8)
+    G, tile = 3, 8
+    tiles = (h + tile - 1) // tile
+    per = (tiles + G - 1) // G
+    out = np.zeros((per * G * tile, w, 4), dtype=np.uint8)
+    for g in range(G):
+        part = torch.zeros((per * tile, w, 4), dtype=torch.uint8, device="cuda:0")
+        sc.render_device(cfg, w, h, part.data_ptr(), options=M.rayca_options(0x5EED, 0, g, G, tile, 0, 0))
+        torch.cuda.synchronize()
+        out.reshape(per, G, tile, w, 4)[:, g] = part.cpu().numpy().reshape(per, tile, w, 4)
+    assert np.array_equal(out[:h], b8), "sharded wavefront frame differs"
+
+
 def test_shared_frame_wait_times_out_instead_of_hanging(ctx, atrium):
     """A rank that never publishes its flag must not hang the owner: the wait kernel gives up after ~2 s and
     frame_timed_out reports it."""
