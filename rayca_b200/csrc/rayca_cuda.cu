@@ -46,6 +46,7 @@ struct rayca_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     rayca_stats last{};
     uint64_t last_primary = 0;
+    uint32_t last_launches = 1; // kernels of the last frame (row bands and wavefront stages add up)
     // scratch for the host-buffer entry point: device planes, a side stream for the read-back, and
     // one event per row band (kernel done -> copy may start)
     void* d_scratch = nullptr;
@@ -710,6 +711,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
         stats->kernel_launches = launches;
         stats->rays_primary = ctx->last_primary;
     }
+    ctx->last_launches = first ? launches : ctx->last_launches + launches;
     return RAYCA_OK;
 }
 } // namespace
@@ -1001,7 +1003,7 @@ int rayca_cuda_last_counters(rayca_ctx* ctx, rayca_stats* stats) {
     stats->rays_secondary = c[1];
     stats->node_bytes = c[2] * 32ull;
     stats->triangle_bytes = c[3] * 48ull + c[4] * 16ull;
-    stats->kernel_launches = 1;
+    stats->kernel_launches = ctx->last_launches;
     return RAYCA_OK;
 }
 
@@ -1078,7 +1080,7 @@ int render_multi(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* config,
             total.node_bytes += one.node_bytes;
             total.triangle_bytes += one.triangle_bytes;
             total.trace_ms = std::max(total.trace_ms, one.trace_ms); // the devices run side by side
-            total.kernel_launches += 1;
+            total.kernel_launches += one.kernel_launches;
         }
     }
     cudaSetDevice(ctx->device);
@@ -1171,7 +1173,7 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
     }
     double t0 = now_ms();
     int rc = RAYCA_OK;
-    uint32_t launched = 0;
+    uint32_t launched = 0, kernels = 0; // launches of enqueue_render (bands); kernels they launched (wavefront stages count)
     uint32_t band_of[8] = {0};
     // Zero copy: when the caller's buffer is pinned host memory (rayca_cuda_host_alloc, or any cudaHostAlloc /
     // cudaHostRegister'ed range) the device can address it, so ONE launch stores the RGBA8 pixels straight into it
@@ -1190,6 +1192,7 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
         rc = enqueue_render(ctx, scene, config, options, width, height, host_view, aux ? &d : nullptr, ctx->render_stream, nullptr, &local);
         if (rc != RAYCA_OK) return rc;
         launched = 1;
+        kernels += local.kernel_launches;
         CUDA_TRY(cudaStreamSynchronize(ctx->render_stream));
     }
     for (uint32_t k = 0; k < nb; ++k) {
@@ -1199,6 +1202,7 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
         if (rc != RAYCA_OK) return rc;
         CUDA_TRY(cudaEventRecord(ctx->band_done[launched], ctx->render_stream));
         band_of[launched++] = k;
+        kernels += local.kernel_launches;
     }
     for (uint32_t j = 0; j < launched && !host_view; ++j) {
         const size_t y0 = edge[band_of[j]], y1 = edge[band_of[j] + 1];
@@ -1207,7 +1211,7 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
                                  ctx->copy_stream));
     }
     if (!host_view) CUDA_TRY(cudaStreamSynchronize(ctx->copy_stream));
-    local.kernel_launches = launched;
+    local.kernel_launches = kernels;
     if (aux) {
         if (aux->hit_blas) CUDA_TRY(cudaMemcpy(aux->hit_blas, d.hit_blas, n * 4, cudaMemcpyDeviceToHost));
         if (aux->hit_prim) CUDA_TRY(cudaMemcpy(aux->hit_prim, d.hit_prim, n * 4, cudaMemcpyDeviceToHost));
@@ -1374,7 +1378,11 @@ extern "C" int rayca_cuda_render_static(rayca_ctx* ctx, rayca_scene* scene, cons
         // enqueue_render clears the counters on the stream (cudaMemsetAsync) before the launch: the array keeps the
         // previous call's contents, and the counters are the part that must start at zero; every pixel of the
         // plane inside width x height is overwritten by the kernel
-        rc = enqueue_render(ctx, scene, config, options, width, height, plane, nullptr, ctx->render_stream, nullptr, &local);
+        // the fused kernel only: the wavefront path keeps its ray buffers in cudaMalloc'ed scratch
+        rayca_options fused{};
+        if (options) fused = *options;
+        fused.flags |= RAYCA_FLAG_NO_WAVEFRONT;
+        rc = enqueue_render(ctx, scene, config, &fused, width, height, plane, nullptr, ctx->render_stream, nullptr, &local);
         if (rc != RAYCA_OK) return rc;
         CUDA_TRY(cudaMemcpyAsync(rgba8_out, plane, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->render_stream));
         CUDA_TRY(cudaStreamSynchronize(ctx->render_stream));
