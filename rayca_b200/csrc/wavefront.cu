@@ -42,7 +42,8 @@ struct WaveView {
     uint32_t* idx_out; // sorted path indices
     uint32_t n;        // paths of this launch = rows x width
     uint32_t key_bits; // Morton bits per axis
-    uint32_t dead_key; // 1 << (3 * key_bits + 3): above every live key, so ended paths sort to the end
+    uint32_t dir_bits, key_mode; // see sort_key
+    uint32_t dead_key; // one bit above every live key, so that ended paths sort to the end
     float box_min[3], box_scale[3];
 };
 
@@ -54,16 +55,41 @@ __device__ __forceinline__ uint32_t spread3(uint32_t v) { // 10 bits -> every th
     return v;
 }
 
-// octant of the direction in the top bits, Morton code of the origin (key_bits per axis) below: rays that start in the
-// same cell and head into the same octant become neighbours
+__device__ __forceinline__ uint32_t spread2(uint32_t v) { // 16 bits -> every second bit
+    v = (v | (v << 8)) & 0x00FF00FFu;
+    v = (v | (v << 4)) & 0x0F0F0F0Fu;
+    v = (v | (v << 2)) & 0x33333333u;
+    v = (v | (v << 1)) & 0x55555555u;
+    return v;
+}
+
+// Sort key of a live ray.  key_mode 0: direction octant | Morton code of the origin (key_bits per axis).
+// key_mode 1: Morton code of the origin in a COARSE grid (key_bits per axis) | direction on the octahedral map
+// (dir_bits per axis, Morton order): rays that start in the same cell and point the same way — the ones that walk the
+// same nodes — become neighbours.  key_mode 2: the same fields, direction first.
 __device__ __forceinline__ uint32_t sort_key(const WaveView& w, V3 o, V3 d) {
     const float cells = (float)(1u << w.key_bits);
     const uint32_t qx = min((uint32_t)fmaxf((o.x - w.box_min[0]) * w.box_scale[0] * cells, 0.0f), (1u << w.key_bits) - 1u);
     const uint32_t qy = min((uint32_t)fmaxf((o.y - w.box_min[1]) * w.box_scale[1] * cells, 0.0f), (1u << w.key_bits) - 1u);
     const uint32_t qz = min((uint32_t)fmaxf((o.z - w.box_min[2]) * w.box_scale[2] * cells, 0.0f), (1u << w.key_bits) - 1u);
     const uint32_t morton = spread3(qx) | (spread3(qy) << 1) | (spread3(qz) << 2);
-    const uint32_t octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
-    return (octant << (3u * w.key_bits)) | morton;
+    if (w.key_mode == 0) {
+        const uint32_t octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+        return (octant << (3u * w.key_bits)) | morton;
+    }
+    // octahedral map of the direction: the unit octahedron unfolded onto [0,1]^2
+    const float inv = 1.0f / (fabsf(d.x) + fabsf(d.y) + fabsf(d.z) + 1e-30f);
+    float px = d.x * inv, py = d.y * inv;
+    if (d.z < 0.0f) {
+        const float tx = (1.0f - fabsf(py)) * (px >= 0.0f ? 1.0f : -1.0f), ty = (1.0f - fabsf(px)) * (py >= 0.0f ? 1.0f : -1.0f);
+        px = tx;
+        py = ty;
+    }
+    const float dc = (float)(1u << w.dir_bits);
+    const uint32_t du = min((uint32_t)fmaxf((px * 0.5f + 0.5f) * dc, 0.0f), (1u << w.dir_bits) - 1u);
+    const uint32_t dv = min((uint32_t)fmaxf((py * 0.5f + 0.5f) * dc, 0.0f), (1u << w.dir_bits) - 1u);
+    const uint32_t dir = spread2(du) | (spread2(dv) << 1);
+    return w.key_mode == 1 ? (morton << (2u * w.dir_bits)) | dir : (dir << (3u * w.key_bits)) | morton;
 }
 
 __device__ __forceinline__ Col ld_c(const float4* p) {
@@ -222,9 +248,14 @@ int wave_render(const RenderParams& P, uint32_t rows, bool spheres, WaveScratch&
     const uint32_t n = rows * P.width;
     const uint32_t max_depth = std::min<uint32_t>(P.cfg.max_depth, (uint32_t)kMaxDepth);
     const uint32_t levels = max_depth; // a level is stored at most once per depth
-    uint32_t key_bits = 7;             // Morton bits per axis: 3 x 7 + 3 octant bits = a 24-bit key, three radix passes
+    // key layout (see sort_key); the defaults are the best of the A/B in profiles/r02_wavefront_ab.txt
+    uint32_t key_mode = 1, key_bits = 4, dir_bits = 5;
+    if (const char* e = std::getenv("RAYCA_WAVE_KEY_MODE")) key_mode = (uint32_t)std::min(2, std::max(0, std::atoi(e)));
     if (const char* e = std::getenv("RAYCA_WAVE_KEY_BITS")) key_bits = (uint32_t)std::min(9, std::max(1, std::atoi(e)));
-    const int end_bit = (int)(3 * key_bits + 4); // live keys use 3 * key_bits + 3 bits, ended paths carry the bit above
+    if (const char* e = std::getenv("RAYCA_WAVE_DIR_BITS")) dir_bits = (uint32_t)std::min(8, std::max(1, std::atoi(e)));
+    if (key_mode != 0 && 3 * key_bits + 2 * dir_bits > 31) dir_bits = (31 - 3 * key_bits) / 2;
+    const uint32_t live_bits = key_mode == 0 ? 3 * key_bits + 3 : 3 * key_bits + 2 * dir_bits;
+    const int end_bit = (int)live_bits + 1; // ended paths carry the bit above the live keys
     size_t temp_bytes = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr,
                                     (int)n, 0, end_bit, st);
@@ -254,7 +285,9 @@ int wave_render(const RenderParams& P, uint32_t rows, bool spheres, WaveScratch&
     void* temp = p;
     w.n = n;
     w.key_bits = key_bits;
-    w.dead_key = 1u << (3 * key_bits + 3);
+    w.dir_bits = dir_bits;
+    w.key_mode = key_mode;
+    w.dead_key = 1u << live_bits;
     for (int a = 0; a < 3; ++a) {
         const float lo = P.scene.fast_root_min[a], hi = P.scene.fast_root_max[a];
         w.box_min[a] = lo;
