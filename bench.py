@@ -360,7 +360,7 @@ def ncu_profile_name(args, G):
         return "r02_ncu_soup.json"
     if args.workload == "flighthelmet":
         return "r02_ncu_flighthelmet.json"
-    return "r02_ncu_bounce.json" if args.max_depth > 1 else "r02_ncu_atrium.json"
+    return "r02_ncu_bounce_wavefront_stage1.json" if args.max_depth > 1 else "r02_ncu_atrium.json"
 
 
 def run_ours(args):
