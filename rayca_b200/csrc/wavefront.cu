@@ -226,6 +226,18 @@ __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_stage_kernel(const
     flush_counters(P, pc);
 }
 
+// The launch's pixels, device plane -> their place in the target (same index in both): one thread per pixel in
+// launch-local order, so a warp moves 128 contiguous bytes of an image row.  Used when the target is HOST memory: the
+// sorted stages would otherwise store 4 bytes at a time to scattered addresses over PCIe.
+__global__ void wave_copy_kernel(const __grid_constant__ RenderParams P, const uchar4* __restrict__ src, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t local_row = i / P.width, x = i - local_row * P.width, y = image_row(P, local_row);
+    if (y >= P.row_end) return;
+    const size_t o = (size_t)((P.shard_count > 1 && !P.direct_rows) ? local_row : y) * P.width + x;
+    reinterpret_cast<uchar4*>(P.rgba8)[o] = src[o];
+}
+
 } // namespace
 
 bool wave_supported(const RenderParams& P, uint32_t mode, bool count, bool persistent, bool general_integrator, bool bounce) {
@@ -244,8 +256,18 @@ T* carve(unsigned char*& p, size_t count) {
 }
 } // namespace
 
-int wave_render(const RenderParams& P, uint32_t rows, bool spheres, WaveScratch& ws, cudaStream_t st, uint32_t* launches, std::string& err) {
+int wave_render(const RenderParams& P_in, uint32_t rows, bool spheres, WaveScratch& ws, cudaStream_t st, uint32_t* launches, std::string& err) {
+    RenderParams P = P_in;
     const uint32_t n = rows * P.width;
+    // pixels bound for host memory (zero-copy frames, shared host frames of the multi-GPU paths) are staged on the device
+    bool stage_pixels = false;
+    {
+        cudaPointerAttributes at{};
+        stage_pixels = cudaPointerGetAttributes(&at, P.rgba8) == cudaSuccess && at.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+    }
+    // the plane is indexed like the target: whole-frame rows when pixels go to their image rows, launch rows otherwise
+    const size_t plane_pixels = (size_t)((P.shard_count > 1 && !P.direct_rows) ? rows : P.height) * P.width;
     const uint32_t max_depth = std::min<uint32_t>(P.cfg.max_depth, (uint32_t)kMaxDepth);
     const uint32_t levels = max_depth; // a level is stored at most once per depth
     // key layout (see sort_key); the defaults are the best of the A/B in profiles/r02_wavefront_ab.txt
@@ -260,7 +282,8 @@ int wave_render(const RenderParams& P, uint32_t rows, bool spheres, WaveScratch&
     cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr,
                                     (int)n, 0, end_bit, st);
     auto al = [](size_t b) { return (b + 255) & ~size_t(255); };
-    const size_t need = 2 * al((size_t)n * 16) + 2 * al((size_t)levels * n * 16) + 4 * al((size_t)n * 4) + al(temp_bytes) + 256;
+    const size_t need = 2 * al((size_t)n * 16) + 2 * al((size_t)levels * n * 16) + 4 * al((size_t)n * 4) + al(temp_bytes) +
+                        (stage_pixels ? al(plane_pixels * 4) : 0) + 256;
     if (need > ws.bytes) {
         cudaFree(ws.base);
         ws.base = nullptr;
@@ -282,7 +305,9 @@ int wave_render(const RenderParams& P, uint32_t rows, bool spheres, WaveScratch&
     w.keys_out = carve<uint32_t>(p, n);
     w.idx_in = carve<uint32_t>(p, n);
     w.idx_out = carve<uint32_t>(p, n);
+    uchar4* plane = stage_pixels ? carve<uchar4>(p, plane_pixels) : nullptr;
     void* temp = p;
+    if (stage_pixels) P.rgba8 = reinterpret_cast<unsigned char*>(plane);
     w.n = n;
     w.key_bits = key_bits;
     w.dir_bits = dir_bits;
@@ -308,6 +333,10 @@ int wave_render(const RenderParams& P, uint32_t rows, bool spheres, WaveScratch&
         }
         if (spheres) wave_stage_kernel<3><<<(n + 127) / 128, 128, 0, st>>>(P, w, depth);
         else wave_stage_kernel<0><<<(n + 127) / 128, 128, 0, st>>>(P, w, depth);
+        ++k;
+    }
+    if (stage_pixels) {
+        wave_copy_kernel<<<(n + 255) / 256, 256, 0, st>>>(P_in, plane, n);
         ++k;
     }
     if (launches) *launches = k;

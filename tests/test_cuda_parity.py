@@ -393,6 +393,19 @@ def test_wavefront_stages_equal_the_fused_kernel(ctx, scene, cfg, w, h):
         torch.cuda.synchronize()
         out.reshape(per, G, tile, w, 4)[:, g] = part.cpu().numpy().reshape(per, tile, w, 4)
     assert np.array_equal(out[:h], b8), "sharded wavefront frame differs"
+    # three shards stored at their final rows of a page-locked HOST frame (the multi-GPU default): the sorted stages'
+    # pixels are staged on the device and leave through one coalesced copy kernel; and the zero-copy single launch
+    f = R.HostFrame(w, h)
+    try:
+        for g in range(G):
+            sc.render(cfg, w, h, out=f.pixels, options=M.rayca_options(0x5EED, 0, g, G, tile, R.FLAG_DIRECT_ROWS, 0))
+        assert np.array_equal(f.pixels, b8), "host-frame wavefront shards differ"
+        f.pixels[...] = 0
+        sc.render_device(cfg, w, h, f.device_ptr, options=wave)
+        torch.cuda.synchronize()
+        assert np.array_equal(f.pixels, b8), "zero-copy wavefront frame differs"
+    finally:
+        f.close()
 
 
 def test_shared_frame_wait_times_out_instead_of_hanging(ctx, atrium):
