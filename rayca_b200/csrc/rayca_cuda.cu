@@ -668,7 +668,7 @@ int enqueue_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* confi
     }
     uint32_t launches = 1;
     const bool no_wave = options && (options->flags & RAYCA_FLAG_NO_WAVEFRONT);
-    if (!no_wave && !by_groups && wave_supported(P, mode, count, persistent, integrator == kInternalPathGeneral, sel.bounce)) {
+    if (!no_wave && !by_groups && wave_supported(P, rows, mode, count, persistent, integrator == kInternalPathGeneral, sel.bounce)) {
         // bounce rays: wavefront stages with the live rays sorted between depths (wavefront.cu)
         std::string werr;
         rc = wave_render(P, rows, sel.spheres, ctx->wave, st, &launches, werr);
@@ -1193,7 +1193,8 @@ int rayca_cuda_render(rayca_ctx* ctx, rayca_scene* scene, const rayca_config* co
     // frame goes to the device plane and leaves in one copy; unsharded frames only (a shard's tiles still go direct).
     const bool bouncing = config && config->integrator == RAYCA_INTEGRATOR_PATHTRACER && config->samples_per_pixel == 1 &&
                           config->max_depth > (config->direct_sampler == RAYCA_SAMPLER_NONE ? 0u : 1u) &&
-                          !(options && (options->flags & RAYCA_FLAG_NO_WAVEFRONT)) && !std::getenv("RAYCA_NO_WAVEFRONT");
+                          !(options && (options->flags & RAYCA_FLAG_NO_WAVEFRONT)) && !std::getenv("RAYCA_NO_WAVEFRONT") &&
+                          (size_t)width * height >= 600000; // wave_supported's size threshold
     if (host_view && bouncing && !sharded) {
         rc = enqueue_render(ctx, scene, config, options, width, height, base, aux ? &d : nullptr, ctx->render_stream, nullptr, &local);
         if (rc != RAYCA_OK) return rc;

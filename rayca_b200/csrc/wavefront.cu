@@ -240,8 +240,14 @@ __global__ void wave_copy_kernel(const __grid_constant__ RenderParams P, const u
 
 } // namespace
 
-bool wave_supported(const RenderParams& P, uint32_t mode, bool count, bool persistent, bool general_integrator, bool bounce) {
+bool wave_supported(const RenderParams& P, uint32_t rows, uint32_t mode, bool count, bool persistent, bool general_integrator, bool bounce) {
     if (std::getenv("RAYCA_NO_WAVEFRONT")) return false; // A/B runs
+    // Eight launches (fill, stage 0, four of the sort, stage 1, copy) each drain on their own: below about half a million
+    // paths the fused kernel's single launch is faster (1080p bounce frame over N GPUs, wavefront against fused:
+    // 2.07 M paths per GPU +20 %, 1.04 M +9 %, 0.52 M +0.6 %, 0.26 M -16 %; profiles/r02_wavefront_ab.txt)
+    size_t min_paths = 600000;
+    if (const char* e = std::getenv("RAYCA_WAVE_MIN_PATHS")) min_paths = (size_t)std::max(0, std::atoi(e));
+    if ((size_t)rows * P.width < min_paths) return false;
     return P.cfg.integrator == RAYCA_INTEGRATOR_PATHTRACER && !general_integrator && bounce && mode == RAYCA_TRAVERSAL_ORDERED && !count &&
            !persistent && P.cfg.samples_per_pixel == 1 && P.sample_count == 1 && P.sample_first == 0 && P.accum == nullptr &&
            P.cfg.light_samples == 1 && P.gshard_count <= 1;

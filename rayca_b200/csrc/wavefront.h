@@ -18,7 +18,8 @@ struct WaveScratch {
 
 // true when this launch can run as wavefront stages: Pathtracer with at least one bounce, cosine sampler, one light
 // sample, one sample per pixel, point lights, the product walk (traversal mode 0 / 3), the static grid
-bool wave_supported(const RenderParams& P, uint32_t mode, bool count, bool persistent, bool general_integrator, bool bounce);
+// ... and enough paths for the extra launches to pay (`rows` x width of this launch)
+bool wave_supported(const RenderParams& P, uint32_t rows, uint32_t mode, bool count, bool persistent, bool general_integrator, bool bounce);
 
 // Enqueues the whole frame on `st`: stage 0 (primary rays, depth 0 exactly as the fused kernel), then per bounce depth
 // a radix sort of the live rays by (direction octant, Morton code of the origin) and a stage that traces them in that

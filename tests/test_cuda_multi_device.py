@@ -46,7 +46,7 @@ def test_multi_device_render_equals_single_device(cuda_lib, single, devices, sce
     assert np.array_equal(got, want), f"pageable: {(got != want).sum()} bytes differ"
     assert (st.rays_primary, st.rays_shadow, st.rays_secondary) == (wst.rays_primary, wst.rays_shadow, wst.rays_secondary)
     if multi.device_count > 1:  # a 1-device context takes the ordinary path (row bands for pageable buffers)
-        assert st.kernel_launches >= multi.device_count  # more than one per device when bounces run as wavefront stages
+        assert st.kernel_launches >= multi.device_count  # more than one per device when a big bounce frame runs as wavefront stages
     # pinned caller buffer: every device's kernel stores its tiles straight into it
     img = R.Image(w, h, pinned=True)
     img.buffer[...] = 7

@@ -361,13 +361,14 @@ def test_group_checkerboard_shards_equal_single_launch(ctx, atrium, G):
     ("box", R.Config(max_depth=17), 96, 96),  # the deepest path the fused kernel keeps
     ("scratcher_sphere", R.Config(max_depth=2), 128, 128),  # spheres: kernel instantiation MODE 3
 ])
-def test_wavefront_stages_equal_the_fused_kernel(ctx, scene, cfg, w, h):
+def test_wavefront_stages_equal_the_fused_kernel(ctx, scene, cfg, w, h, monkeypatch):
     """bounce rays run as wavefront stages with the live rays radix-sorted between depths
     (wavefront.cu).  The RNG is keyed by (pixel, sample, depth, dimension) and every value is computed by the same
     device functions in the same order, so the frame, the parity planes and the ray counts equal the fused kernel's
     (RAYCA_FLAG_NO_WAVEFRONT) bit for bit — through rayca_cuda_render (row bands), and sharded."""
     import torch
 
+    monkeypatch.setenv("RAYCA_WAVE_MIN_PATHS", "0")  # small frames normally keep the fused kernel
     sc = dev_scene(ctx, scene)
     wave = M.rayca_options(0x5EED, 0, 0, 0, 0, 0, 0)
     fused = M.rayca_options(0x5EED, 0, 0, 0, 0, R.FLAG_NO_WAVEFRONT, 0)
