@@ -314,6 +314,7 @@ void rayca_cuda_shutdown(rayca_ctx* c) {
 
 void rayca_cuda_scene_destroy(rayca_scene* s) {
     if (!s) return;
+    const double td0 = now_ms();
     for (rayca_scene* r : s->replicas) rayca_cuda_scene_destroy(r);
     if (s->ctx) cudaSetDevice(s->ctx->device);
     cudaFree(s->d_nodes);
@@ -327,6 +328,7 @@ void rayca_cuda_scene_destroy(rayca_scene* s) {
     cudaFree(s->d_fast_nodes);
     cudaFree(s->d_fast_tri);
     delete s;
+    if (std::getenv("RAYCA_TIMING")) std::fprintf(stderr, "[rayca] %-28s %8.2f ms\n", "scene_destroy", now_ms() - td0);
 }
 
 int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32_t bvh, rayca_scene** out, rayca_stats* stats) {
@@ -381,6 +383,15 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
             return rc__;                     \
         }                                    \
     } while (0)
+    const bool timing = std::getenv("RAYCA_TIMING") != nullptr;
+    double tl = now_ms();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        const double t = now_ms();
+        std::fprintf(stderr, "[rayca] %-28s %8.2f ms\n", what, t - tl);
+        tl = t;
+    };
+    if (timing) std::fprintf(stderr, "[rayca] %-28s %8.2f ms\n", "build_host_scene (total)", t1 - t0);
     UP(d_nodes, nodes);
     UP(d_tri_pos, tri_pos);
     UP(d_tri_attr, tri_attr);
@@ -389,6 +400,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     UP(d_texels, texels);
     UP(d_lights, lights);
     UP(d_blas_prim_offset, blas_prim_offset);
+    lap("uploads (8 arrays)");
     if (host_fast_tree) {
         UP(d_fast_nodes, fast_nodes);
         UP(d_fast_tri, fast_tri);
@@ -412,6 +424,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
             std::fprintf(stderr, "[rayca] %-28s %8.2f ms (%u levels, %u warp subtrees, depth %u)\n", "performance tree (device)",
                          ft.build_ms, ft.levels, ft.small_subtrees, ft.depth);
     }
+    lap("performance tree (call)");
     // The walk's stack holds kStackSize entries and saturates beyond (trace.cuh): a performance tree deeper than that
     // would drop subtrees silently, so such a scene is refused here, never mis-rendered.  With 16 SAH bins a level
     // narrows the centroid range 16-fold and the binned builder cannot get near the limit on f32 input; the environment
@@ -468,6 +481,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     std::vector<float4>().swap(h.fast_tri);
     std::vector<GpuNode>().swap(h.fast_nodes);
     for (HostBlas& b : h.blas) PodVector<HostAttr>().swap(b.attrs);
+    lap("free host copies");
     // multi-device context: copy the finished device arrays to every other device (device-to-device, no rebuild)
     for (rayca_ctx* e : ctx->extra) {
         rayca_scene* r = new (std::nothrow) rayca_scene();
