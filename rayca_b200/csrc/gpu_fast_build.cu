@@ -879,15 +879,20 @@ __global__ void small_sizes(const WorkNode* __restrict__ small, uint32_t count, 
     if (i < count) sizes[i] = small[i].n - 1u; // pairs a subtree over n primitives can need
 }
 
-struct DeviceBuffers { // one cudaMalloc for all temporaries (35 separate allocations cost more than the build)
+// One allocation for all temporaries (35 separate allocations cost more than the build), taken from the device's
+// stream-ordered pool on the build's stream: `Draw::draw` rebuilds per call, and the pool (release threshold raised in
+// rayca_cuda_init) hands the same memory back without a cudaMalloc / cudaFree round trip (3 ms per draw before).
+struct DeviceBuffers {
     struct Want { void** p; size_t offset; };
     std::vector<Want> wants;
     size_t bytes = 0;
     void* base = nullptr;
+    cudaStream_t st;
     std::vector<void*> kept; // separately allocated outputs, freed unless released
-    ~DeviceBuffers() {
-        cudaFree(base);
-        for (void* p : kept) cudaFree(p);
+    explicit DeviceBuffers(cudaStream_t stream) : st(stream) {}
+    ~DeviceBuffers() { // the builders synchronise `st` before returning: nothing is in flight here
+        if (base) cudaFreeAsync(base, st);
+        for (void* p : kept) cudaFreeAsync(p, st);
     }
     template <class T> cudaError_t alloc(T** out, size_t count) { // temporaries: address assigned by commit()
         wants.push_back({(void**)out, bytes});
@@ -895,14 +900,14 @@ struct DeviceBuffers { // one cudaMalloc for all temporaries (35 separate alloca
         return cudaSuccess;
     }
     cudaError_t commit() {
-        cudaError_t e = cudaMalloc(&base, bytes);
+        cudaError_t e = cudaMallocAsync(&base, bytes, st);
         if (e != cudaSuccess) return e;
         for (const Want& w : wants) *w.p = (char*)base + w.offset;
         return cudaSuccess;
     }
     template <class T> cudaError_t alloc_output(T** out, size_t count) {
         void* p = nullptr;
-        cudaError_t e = cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T));
+        cudaError_t e = cudaMallocAsync(&p, std::max<size_t>(count, 1) * sizeof(T), st);
         if (e == cudaSuccess) kept.push_back(p);
         *out = (T*)p;
         return e;
@@ -923,6 +928,21 @@ inline uint32_t blocks_for(size_t n, uint32_t threads) { return (uint32_t)((n + 
         }                                                                            \
     } while (0)
 
+// Triangle-only scenes: primitive bounds from the world-space vertices already on the device (the same fminf / fmaxf
+// chain as the host's emit, host_scene.cpp: min and max are exact, so the bits are the host's) and the identity order —
+// instead of building both on the host and uploading 36 bytes per primitive.
+__global__ void prep_bounds_kernel(const float4* __restrict__ tri_pos, uint32_t n, float4* __restrict__ mn, float4* __restrict__ mx,
+                                   uint32_t* __restrict__ order) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = tri_pos[3 * (size_t)i], b = tri_pos[3 * (size_t)i + 1], c = tri_pos[3 * (size_t)i + 2];
+    mn[i] = make_float4(fminf(fminf(fminf(kF32Max, a.x), b.x), c.x), fminf(fminf(fminf(kF32Max, a.y), b.y), c.y),
+                        fminf(fminf(fminf(kF32Max, a.z), b.z), c.z), 0.0f);
+    mx[i] = make_float4(fmaxf(fmaxf(fmaxf(-kF32Max, a.x), b.x), c.x), fmaxf(fmaxf(fmaxf(-kF32Max, a.y), b.y), c.y),
+                        fmaxf(fmaxf(fmaxf(-kF32Max, a.z), b.z), c.z), 0.0f); // w: sphere id, none here
+    order[i] = i;
+}
+
 int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStream_t st, FastTreeDevice& out, std::string& err) {
     int bins_unused;
     uint32_t leaf_max;
@@ -933,7 +953,9 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
     if (N == 0) { err = "no primitives"; return RAYCA_E_INVALID_ARG; }
 
     // ---- host side: bounds in reference-global order, reference leaf of every primitive, sphere records
-    std::vector<float4> hmn(N), hmx(N);
+    bool any_sphere = false;
+    for (size_t bi = 0; bi < nb; ++bi) any_sphere = any_sphere || !hs.blas[bi].spheres.empty();
+    std::vector<float4> hmn(any_sphere ? N : 0), hmx(any_sphere ? N : 0); // sphere scenes: bounds from the host (a sphere's are not its record's)
     std::vector<uint32_t> ref_leaf(N, 0);
     std::vector<float4> sphere_records;
     std::vector<uint32_t> sphere_base(nb + 1, 0);
@@ -950,7 +972,7 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
             for (int64_t i = 0; i < (int64_t)n.count; ++i) ref_leaf[po + n.offset + (size_t)i] = leaf;
         }
 #pragma omp parallel for schedule(static) if (b.tris.size() > 8192)
-        for (int64_t k = 0; k < (int64_t)b.tris.size(); ++k) {
+        for (int64_t k = 0; k < (int64_t)(any_sphere ? b.tris.size() : 0); ++k) {
             const HostTri& t = b.tris[(size_t)k];
             const uint32_t id = po + (uint32_t)k;
             uint32_t sphere = 0;
@@ -976,7 +998,7 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
     }
 
     // ---- device buffers
-    DeviceBuffers buf;
+    DeviceBuffers buf(st);
     const uint32_t cap_big = N / (kSmall + 1) + 1;
     float4 *d_mn, *d_mx, *d_sphere, *d_tri;
     uint32_t *d_order[2], *d_node_of[2], *d_flags, *d_scan, *d_partial, *d_ref_leaf, *d_acc[2], *d_bins, *d_child_big, *d_child_small,
@@ -1017,19 +1039,23 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
     cudaEvent_t e0, e1;
     FB_TRY(cudaEventCreate(&e0));
     FB_TRY(cudaEventCreate(&e1));
-    FB_TRY(cudaMemcpyAsync(d_mn, hmn.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
-    FB_TRY(cudaMemcpyAsync(d_mx, hmx.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
+    if (any_sphere) {
+        FB_TRY(cudaMemcpyAsync(d_mn, hmn.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
+        FB_TRY(cudaMemcpyAsync(d_mx, hmx.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
+    }
     FB_TRY(cudaMemcpyAsync(d_ref_leaf, ref_leaf.data(), (size_t)N * 4, cudaMemcpyHostToDevice, st));
     if (!sphere_records.empty())
         FB_TRY(cudaMemcpyAsync(d_sphere, sphere_records.data(), sphere_records.size() * sizeof(float4), cudaMemcpyHostToDevice, st));
     FB_TRY(cudaEventRecord(e0, st));
     FB_TRY(cudaMemsetAsync(d_depth, 0, 4, st));
     FB_TRY(cudaMemsetAsync(d_records, 0, ((size_t)N * 2 + 2) * sizeof(GpuNode), st));
-    {   // order = identity
+    if (any_sphere) { // order = identity
         std::vector<uint32_t> iota(N);
         for (uint32_t i = 0; i < N; ++i) iota[i] = i;
         FB_TRY(cudaMemcpyAsync(d_order[0], iota.data(), (size_t)N * 4, cudaMemcpyHostToDevice, st));
         FB_TRY(cudaStreamSynchronize(st)); // iota goes out of scope
+    } else {
+        prep_bounds_kernel<<<(N + 255) / 256, 256, 0, st>>>(d_tri_pos, N, d_mn, d_mx, d_order[0]);
     }
     const uint32_t T = 256;
     uint32_t nbig = 0, nsmall = 0, pair_base = 0, levels = 0;
@@ -1131,7 +1157,7 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
         hmx[(size_t)i] = make_float4(t.bmax.x, t.bmax.y, t.bmax.z, 0.0f);
         hcen[(size_t)i] = make_float4(t.centroid.x, t.centroid.y, t.centroid.z, 0.0f);
     }
-    DeviceBuffers buf;
+    DeviceBuffers buf(st);
     const uint32_t cap = std::min<uint32_t>(N, 16384u); // nodes of one level; broader levels fall back to the host builder
     float4 *d_mn, *d_mx, *d_cen;
     uint32_t *d_order[2], *d_node_of[2], *d_flags, *d_scan, *d_partial, *d_hole, *d_tail, *d_acc[2], *d_bins, *d_split, *d_split_index,

@@ -234,7 +234,7 @@ struct PhaseTimer { // RAYCA_TIMING=1 prints the host phases of scene_create to 
 } // namespace
 
 int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::string& err, bool fast_tree,
-                     const BlasBuilder* blas_builder) {
+                     const BlasBuilder* blas_builder, bool gather_texels) {
     PhaseTimer phase;
     Flatten f(d, out);
     f.run();
@@ -246,9 +246,12 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
         const rayca_image& im = d.images[i];
         size_t bpp = im.color_type == RAYCA_COLOR_RGB8 ? 3 : (im.color_type == RAYCA_COLOR_RGBA8 ? 4 : 16);
         size_t bytes = (size_t)im.width * im.height * bpp;
-        size_t off = (out.texels.size() + 15) & ~size_t(15);
-        out.texels.resize(off + bytes);
-        if (bytes) std::memcpy(out.texels.data() + off, im.data, bytes);
+        size_t off = (out.texel_bytes + 15) & ~size_t(15);
+        out.texel_bytes = off + bytes;
+        if (gather_texels) { // the device path uploads every image straight from the caller's memory instead (rayca_cuda.cu)
+            out.texels.resize(off + bytes);
+            if (bytes) std::memcpy(out.texels.data() + off, im.data, bytes);
+        }
         out.images[i] = GpuImage{(unsigned long long)off, im.width, im.height, im.color_type, 0};
     }
 

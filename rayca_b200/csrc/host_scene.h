@@ -74,7 +74,8 @@ struct HostScene {
     std::vector<HostBlas> blas;          // in TLAS-reordered (blas_nodes) order after build
     std::vector<GpuMaterial> materials;  // [0] = Material::DEFAULT -> PbrMaterial::WHITE
     std::vector<GpuImage> images;
-    std::vector<unsigned char> texels;
+    std::vector<unsigned char> texels;   // gathered copy of all images (only when build_host_scene is asked to gather)
+    size_t texel_bytes = 0;              // size of the texel buffer; GpuImage::offset addresses it
     std::vector<GpuLight> lights;
     GpuCamera camera{};
     bool has_camera = false;
@@ -101,7 +102,7 @@ struct HostScene {
 // it built the BLAS and false to leave it to the host builder.
 using BlasBuilder = std::function<bool(HostBlas&, uint32_t max_depth)>;
 int build_host_scene(const rayca_scene_desc& desc, bool bvh, HostScene& out, std::string& err, bool fast_tree = true,
-                     const BlasBuilder* blas_builder = nullptr);
+                     const BlasBuilder* blas_builder = nullptr, bool gather_texels = true);
 
 // BLAS build: top-down SAH over 63 planes x 3 axes with the reference's tie-breaking
 // (bvh/blas.rs:64-127,245-316), evaluated through per-plane bins so that one pass over the

@@ -95,12 +95,15 @@ namespace {
 // index of one of rayca_scene's ten device-array members (d_nodes .. d_fast_tri are consecutive void* members)
 size_t slot_of(void* const* member, const rayca_scene* s) { return (size_t)(member - &s->d_nodes); }
 
+// Scene arrays come from the device's stream-ordered pool on the context's render stream (see init_one): a `draw` that
+// rebuilds per call gets last call's memory back without cudaMalloc / cudaFree round trips.  scene_create synchronises
+// the stream before it returns, so the arrays are safe to read from any stream afterwards.
 template <typename V>
-int upload(void** dst, const V& src) {
+int upload(void** dst, const V& src, cudaStream_t st) {
     using T = typename V::value_type;
     size_t bytes = std::max<size_t>(src.size() * sizeof(T), 16);
-    CUDA_TRY(cudaMalloc(dst, bytes));
-    if (!src.empty()) CUDA_TRY(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMallocAsync(dst, bytes, st));
+    if (!src.empty()) CUDA_TRY(cudaMemcpyAsync(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice, st));
     return RAYCA_OK;
 }
 
@@ -236,6 +239,14 @@ namespace {
 int init_one(rayca_ctx* c, int device) { // every failure leaves `c` in a state rayca_cuda_shutdown can release
     c->device = device;
     CUDA_TRY(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
+    {   // keep freed scene memory in the stream-ordered pool instead of returning it to the driver at every sync
+        cudaMemPool_t pool = nullptr;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess && pool) {
+            unsigned long long keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        cudaGetLastError();
+    }
     CUDA_TRY(cudaMalloc((void**)&c->d_counters, kCounterSlots * sizeof(unsigned long long)));
     CUDA_TRY(cudaMemset(c->d_counters, 0, kCounterSlots * sizeof(unsigned long long)));
     CUDA_TRY(cudaEventCreate(&c->ev0));
@@ -316,17 +327,15 @@ void rayca_cuda_scene_destroy(rayca_scene* s) {
     if (!s) return;
     const double td0 = now_ms();
     for (rayca_scene* r : s->replicas) rayca_cuda_scene_destroy(r);
-    if (s->ctx) cudaSetDevice(s->ctx->device);
-    cudaFree(s->d_nodes);
-    cudaFree(s->d_tri_pos);
-    cudaFree(s->d_tri_attr);
-    cudaFree(s->d_materials);
-    cudaFree(s->d_images);
-    cudaFree(s->d_texels);
-    cudaFree(s->d_lights);
-    cudaFree(s->d_blas_prim_offset);
-    cudaFree(s->d_fast_nodes);
-    cudaFree(s->d_fast_tri);
+    if (s->ctx) {
+        cudaSetDevice(s->ctx->device);
+        // like cudaFree's implicit synchronisation: no stream may still be reading the arrays; then the memory goes back
+        // to the pool in stream order (host-only scenes own no device memory)
+        cudaDeviceSynchronize();
+        void** arrays = &s->d_nodes;
+        for (int k = 0; k < 10; ++k)
+            if (arrays[k]) cudaFreeAsync(arrays[k], s->ctx->render_stream);
+    }
     delete s;
     if (std::getenv("RAYCA_TIMING")) std::fprintf(stderr, "[rayca] %-28s %8.2f ms\n", "scene_destroy", now_ms() - td0);
 }
@@ -356,7 +365,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         return brc == RAYCA_OK;
     };
     try {
-        rc = build_host_scene(*desc, bvh != 0, s->host, err, host_fast_tree, &device_blas);
+        rc = build_host_scene(*desc, bvh != 0, s->host, err, host_fast_tree, &device_blas, /*gather_texels=*/false);
     } catch (const std::bad_alloc&) {
         delete s;
         return fail(RAYCA_E_OOM, "host allocation while building the scene");
@@ -377,7 +386,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
 #define UP(dst, vec)                         \
     do {                                     \
         s->nbytes[slot_of(&s->dst, s)] = std::max<size_t>(h.vec.size() * sizeof(h.vec[0]), 16); \
-        int rc__ = upload(&s->dst, h.vec);   \
+        int rc__ = upload(&s->dst, h.vec, ctx->render_stream);   \
         if (rc__ != RAYCA_OK) {              \
             rayca_cuda_scene_destroy(s);     \
             return rc__;                     \
@@ -397,7 +406,21 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     UP(d_tri_attr, tri_attr);
     UP(d_materials, materials);
     UP(d_images, images);
-    UP(d_texels, texels);
+    {   // texels: every image goes straight from the caller's memory to its place in the device buffer (the gather into
+        // one host vector first cost 4 ms of the atrium's draw)
+        s->nbytes[slot_of(&s->d_texels, s)] = std::max<size_t>(h.texel_bytes, 16);
+        cudaError_t ce = cudaMallocAsync(&s->d_texels, std::max<size_t>(h.texel_bytes, 16), ctx->render_stream);
+        for (uint32_t i = 0; i < desc->image_count && ce == cudaSuccess; ++i) {
+            const rayca_image& im = desc->images[i];
+            const size_t bpp = im.color_type == RAYCA_COLOR_RGB8 ? 3 : (im.color_type == RAYCA_COLOR_RGBA8 ? 4 : 16);
+            const size_t bytes = (size_t)im.width * im.height * bpp;
+            if (bytes) ce = cudaMemcpyAsync((unsigned char*)s->d_texels + h.images[i].offset, im.data, bytes, cudaMemcpyHostToDevice, ctx->render_stream);
+        }
+        if (ce != cudaSuccess) {
+            rayca_cuda_scene_destroy(s);
+            return fail(ce == cudaErrorMemoryAllocation ? RAYCA_E_OOM : RAYCA_E_CUDA, std::string("texel upload: ") + cudaGetErrorString(ce));
+        }
+    }
     UP(d_lights, lights);
     UP(d_blas_prim_offset, blas_prim_offset);
     lap("uploads (8 arrays)");
@@ -498,7 +521,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         for (int k = 0; k < 10 && ce == cudaSuccess; ++k) {
             r->nbytes[k] = s->nbytes[k];
             if (!src[k] || s->nbytes[k] == 0) continue;
-            ce = cudaMalloc(&dst[k], s->nbytes[k]);
+            ce = cudaMallocAsync(&dst[k], s->nbytes[k], e->render_stream);
             if (ce == cudaSuccess) ce = cudaMemcpyPeerAsync(dst[k], e->device, src[k], ctx->device, s->nbytes[k], e->render_stream);
         }
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->render_stream);
@@ -522,6 +545,10 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         r->view.fast_tri = (const float4*)r->d_fast_tri;
     }
     if (!ctx->extra.empty()) CUDA_TRY(cudaSetDevice(ctx->device));
+    if (cudaError_t ce = cudaStreamSynchronize(ctx->render_stream); ce != cudaSuccess) { // the arrays may now be read from any stream
+        rayca_cuda_scene_destroy(s);
+        return fail(RAYCA_E_CUDA, std::string("scene_create: ") + cudaGetErrorString(ce));
+    }
     double t2 = now_ms();
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
