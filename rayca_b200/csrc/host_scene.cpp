@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <cstring>
 #include <functional>
+#include <mutex>
 
 namespace rb {
 namespace {
@@ -219,6 +220,51 @@ bool color_close_black(const float c[4]) { // Color::close (color/mod.rs:160-169
 }
 
 } // namespace
+
+// ---- block cache of the PodVector allocator (host_scene.h)
+namespace {
+struct PodBlock {
+    void* p;
+    size_t bytes;
+};
+std::mutex g_pod_mutex;
+std::vector<PodBlock> g_pod_blocks;
+size_t g_pod_bytes = 0;
+constexpr size_t kPodMaxBlocks = 16, kPodMaxBytes = size_t(1) << 30;
+// a block handed out by acquire may be LARGER than what its new owner asked for, and the owner gives it back with its own
+// (smaller) size: the real sizes of such blocks are remembered here, keyed by address
+std::vector<PodBlock> g_pod_true_size;
+} // namespace
+
+void* pod_block_acquire(size_t bytes) {
+    std::lock_guard<std::mutex> lock(g_pod_mutex);
+    size_t best = g_pod_blocks.size();
+    for (size_t i = 0; i < g_pod_blocks.size(); ++i) // the smallest block that fits without wasting more than a quarter
+        if (g_pod_blocks[i].bytes >= bytes && g_pod_blocks[i].bytes - bytes <= bytes / 4 &&
+            (best == g_pod_blocks.size() || g_pod_blocks[i].bytes < g_pod_blocks[best].bytes))
+            best = i;
+    if (best == g_pod_blocks.size()) return nullptr;
+    void* p = g_pod_blocks[best].p;
+    const size_t real = g_pod_blocks[best].bytes;
+    g_pod_bytes -= real;
+    g_pod_blocks.erase(g_pod_blocks.begin() + (long)best);
+    if (real != bytes) g_pod_true_size.push_back({p, real});
+    return p;
+}
+
+bool pod_block_release(void* p, size_t bytes) {
+    std::lock_guard<std::mutex> lock(g_pod_mutex);
+    for (size_t i = 0; i < g_pod_true_size.size(); ++i)
+        if (g_pod_true_size[i].p == p) {
+            bytes = g_pod_true_size[i].bytes;
+            g_pod_true_size.erase(g_pod_true_size.begin() + (long)i);
+            break;
+        }
+    if (g_pod_blocks.size() >= kPodMaxBlocks || g_pod_bytes + bytes > kPodMaxBytes) return false;
+    g_pod_blocks.push_back({p, bytes});
+    g_pod_bytes += bytes;
+    return true;
+}
 
 namespace {
 struct PhaseTimer { // RAYCA_TIMING=1 prints the host phases of scene_create to stderr

@@ -21,12 +21,30 @@ namespace rb {
 // std::vector whose resize() leaves trivially-constructible elements uninitialised: the big per-triangle arrays
 // (tens of MB) are written once by a parallel loop right after being sized, and value-initialising them first
 // costs a sequential pass of page faults (30 of the 42 ms "emit triangles" took for 262k triangles).
+// Big blocks (>= 1 MiB) that a PodVector gives back are kept — up to 16 blocks / 1 GiB — and handed to the next PodVector
+// that asks for that many bytes or a little more: `Draw::draw` rebuilds the scene on every call, and without this the
+// same 130 MB are mmap'ed, page-faulted in and munmap'ed per draw (measured: 2 ms to free + the faults inside emit / pack).
+void* pod_block_acquire(size_t bytes);            // host_scene.cpp; nullptr: nothing suitable cached
+bool pod_block_release(void* p, size_t bytes);    // true: kept (the caller must not free it)
+
 template <class T>
 struct DefaultInitAllocator : std::allocator<T> {
     template <class U> struct rebind { using other = DefaultInitAllocator<U>; };
     using std::allocator<T>::allocator;
     template <class U> void construct(U* p) noexcept(std::is_nothrow_default_constructible<U>::value) { ::new ((void*)p) U; }
     template <class U, class... A> void construct(U* p, A&&... a) { ::new ((void*)p) U(std::forward<A>(a)...); }
+    static constexpr size_t kCacheFrom = size_t(1) << 20;
+    T* allocate(size_t n) {
+        const size_t bytes = n * sizeof(T);
+        if (bytes >= kCacheFrom)
+            if (void* p = pod_block_acquire(bytes)) return static_cast<T*>(p);
+        return static_cast<T*>(::operator new(bytes));
+    }
+    void deallocate(T* p, size_t n) noexcept {
+        const size_t bytes = n * sizeof(T);
+        if (bytes >= kCacheFrom && pod_block_release(p, bytes)) return;
+        ::operator delete(p);
+    }
 };
 template <class T> using PodVector = std::vector<T, DefaultInitAllocator<T>>;
 
