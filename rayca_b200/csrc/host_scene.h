@@ -26,6 +26,7 @@ namespace rb {
 // same 130 MB are mmap'ed, page-faulted in and munmap'ed per draw (measured: 2 ms to free + the faults inside emit / pack).
 void* pod_block_acquire(size_t bytes);            // host_scene.cpp; nullptr: nothing suitable cached
 bool pod_block_release(void* p, size_t bytes);    // true: kept (the caller must not free it)
+void pod_cache_enable_pinning();                  // blocks entering the cache are page-locked from now on (a CUDA context exists)
 
 template <class T>
 struct DefaultInitAllocator : std::allocator<T> {

@@ -271,6 +271,7 @@ int rayca_cuda_init(int device, rayca_ctx** out) {
         rayca_cuda_shutdown(c); // null-safe per member: releases whatever was created
         return rc;
     }
+    pod_cache_enable_pinning();
     *out = c;
     return RAYCA_OK;
 }
@@ -497,7 +498,12 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     v.fast_root_max[0] = h.fast_root.max_x; v.fast_root_max[1] = h.fast_root.max_y; v.fast_root_max[2] = h.fast_root.max_z;
     v.fast_root_ref = h.fast_root.link0;
     s->max_stack = h.max_stack;
-    // host copies that are no longer needed
+    // host copies that are no longer needed — after the stream has drained: packed into page-locked blocks (host_scene.cpp)
+    // the uploads above are truly asynchronous and still read them
+    if (cudaError_t ce = cudaStreamSynchronize(ctx->render_stream); ce != cudaSuccess) {
+        rayca_cuda_scene_destroy(s);
+        return fail(RAYCA_E_CUDA, std::string("scene_create: ") + cudaGetErrorString(ce));
+    }
     std::vector<unsigned char>().swap(h.texels);
     PodVector<float4>().swap(h.tri_attr);
     PodVector<float4>().swap(h.tri_pos);
