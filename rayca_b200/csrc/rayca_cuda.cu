@@ -61,6 +61,9 @@ struct rayca_ctx {
     unsigned char* h_stage = nullptr;
     size_t h_stage_bytes = 0;
     rb::WaveScratch wave; // device scratch of the wavefront path (wavefront.cu)
+    // scenes created on this context and not destroyed yet: shutdown releases their device arrays and orphans them, so
+    // that a scene destroyed AFTER its context (garbage-collected bindings do that) never touches a dead stream
+    std::vector<rayca_scene*> scenes;
 };
 
 struct rayca_scene {
@@ -307,10 +310,17 @@ int rayca_cuda_init_devices(const int* devices, int device_count, rayca_ctx** ou
 
 int rayca_cuda_device_count(rayca_ctx* ctx) { return ctx ? 1 + (int)ctx->extra.size() : 0; }
 
+} // extern "C"
+namespace {
+void release_device_arrays(rayca_scene* s);
+}
+extern "C" {
+
 void rayca_cuda_shutdown(rayca_ctx* c) {
     if (!c) return;
     for (rayca_ctx* e : c->extra) rayca_cuda_shutdown(e);
     cudaSetDevice(c->device);
+    while (!c->scenes.empty()) release_device_arrays(c->scenes.back()); // orphaned: their later destroy frees host memory only
     cudaFree(c->d_counters);
     cudaFree(c->d_scratch);
     cudaFree(c->wave.base);
@@ -324,19 +334,32 @@ void rayca_cuda_shutdown(rayca_ctx* c) {
     delete c;
 }
 
+} // extern "C"
+namespace {
+// gives the scene's device arrays back to the pool and detaches the scene from its context
+void release_device_arrays(rayca_scene* s) {
+    if (!s->ctx) return;
+    cudaSetDevice(s->ctx->device);
+    // like cudaFree's implicit synchronisation: no stream may still be reading the arrays; then the memory goes back
+    // to the pool in stream order (host-only scenes own no device memory)
+    cudaDeviceSynchronize();
+    void** arrays = &s->d_nodes;
+    for (int k = 0; k < 10; ++k) {
+        if (arrays[k]) cudaFreeAsync(arrays[k], s->ctx->render_stream);
+        arrays[k] = nullptr;
+    }
+    auto& live = s->ctx->scenes;
+    live.erase(std::remove(live.begin(), live.end(), s), live.end());
+    s->ctx = nullptr;
+}
+} // namespace
+extern "C" {
+
 void rayca_cuda_scene_destroy(rayca_scene* s) {
     if (!s) return;
     const double td0 = now_ms();
     for (rayca_scene* r : s->replicas) rayca_cuda_scene_destroy(r);
-    if (s->ctx) {
-        cudaSetDevice(s->ctx->device);
-        // like cudaFree's implicit synchronisation: no stream may still be reading the arrays; then the memory goes back
-        // to the pool in stream order (host-only scenes own no device memory)
-        cudaDeviceSynchronize();
-        void** arrays = &s->d_nodes;
-        for (int k = 0; k < 10; ++k)
-            if (arrays[k]) cudaFreeAsync(arrays[k], s->ctx->render_stream);
-    }
+    release_device_arrays(s);
     delete s;
     if (std::getenv("RAYCA_TIMING")) std::fprintf(stderr, "[rayca] %-28s %8.2f ms\n", "scene_destroy", now_ms() - td0);
 }
@@ -347,6 +370,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     rayca_scene* s = new (std::nothrow) rayca_scene();
     if (!s) return fail(RAYCA_E_OOM, "host allocation");
     s->ctx = ctx;
+    ctx->scenes.push_back(s);
     double t0 = now_ms();
     std::string err;
     int rc;
@@ -368,15 +392,15 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     try {
         rc = build_host_scene(*desc, bvh != 0, s->host, err, host_fast_tree, &device_blas, /*gather_texels=*/false);
     } catch (const std::bad_alloc&) {
-        delete s;
+        rayca_cuda_scene_destroy(s);
         return fail(RAYCA_E_OOM, "host allocation while building the scene");
     }
     if (rc != RAYCA_OK) {
-        delete s;
+        rayca_cuda_scene_destroy(s);
         return fail(rc, err);
     }
     if (s->host.blas_prim_offset.back() >= (1u << 27)) {
-        delete s;
+        rayca_cuda_scene_destroy(s);
         return fail(RAYCA_E_UNSUPPORTED, "more than 2^27 primitives");
     }
     // The reference allows BLAS depths up to 255 (u8 level, blas.rs:302-316); the product walk (traversal 0) never walks
@@ -519,6 +543,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
             return fail(RAYCA_E_OOM, "host allocation");
         }
         r->ctx = e;
+        e->scenes.push_back(r);
         r->primary = s;
         s->replicas.push_back(r); // owned by s from here on: every failure below is released by scene_destroy(s)
         void** src = &s->d_nodes;

@@ -257,3 +257,23 @@ def test_ggx_material_under_the_raytracer_is_refused(ctx):
             sc.render(R.Config(integrator=integ, max_depth=1), 32, 32)
         assert e.value.code == -2
     sc.close()
+
+
+def test_scene_outliving_its_context_is_destroyed_safely(cuda_lib):
+    """Garbage-collected bindings may destroy a scene after its context: shutdown releases the scene's device arrays and
+    orphans it, the later destroy only frees host memory (a crash here once surfaced as a segfault at interpreter exit)."""
+    c = R.Context(0)
+    sc = R.DeviceScene(c, load_desc("box"))
+    sc.render(R.Config(max_depth=1), 32, 32)
+    multi = R.Context(devices=[0, 0])
+    ms = R.DeviceScene(multi, load_desc("box"))
+    c.close()
+    multi.close()
+    sc.close()
+    ms.close()
+    c2 = R.Context(0)  # the library is still usable
+    sc2 = R.DeviceScene(c2, load_desc("box"))
+    rgba8, _, _ = sc2.render(R.Config(max_depth=1), 32, 32)
+    assert rgba8.any()
+    sc2.close()
+    c2.close()
