@@ -170,12 +170,12 @@ int validate_config(const rayca_config& c, const rayca_scene& sc) {
 template <int INTEGRATOR, int MODE, bool COUNT, bool PERSISTENT, bool BOUNCE>
 void launch_one(const RenderParams& P, dim3 groups, int sm_count, cudaStream_t st) {
     if (PERSISTENT) {
-        static int blocks_per_sm = 0;
-        if (blocks_per_sm == 0) {
-            int n = 0;
-            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_kernel<INTEGRATOR, MODE, COUNT, true, BOUNCE>, 128, 0) != cudaSuccess || n < 1) n = 1;
-            blocks_per_sm = n;
-        }
+        // asked per launch: the answer depends on the current device, and a function-local static would be shared by every
+        // device and thread of the process; the occupancy query is microseconds and this path is not the default
+        int blocks_per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, render_kernel<INTEGRATOR, MODE, COUNT, true, BOUNCE>, 128, 0) != cudaSuccess ||
+            blocks_per_sm < 1)
+            blocks_per_sm = 1;
         unsigned long long want = ((unsigned long long)P.tile_count + 3) / 4; // 4 warps per block, one group each
         unsigned long long cap = (unsigned long long)sm_count * blocks_per_sm;
         dim3 grid((unsigned)std::max<unsigned long long>(1, std::min(want, cap)));
