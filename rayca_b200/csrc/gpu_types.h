@@ -99,7 +99,7 @@ struct GpuSceneView {
     float fast_root_min[3];
     uint32_t fast_root_ref;
     float fast_root_max[3];
-    uint32_t fast_pad;
+    uint32_t fast_record_count; // 32-byte records allocated behind fast_nodes (RAYCA_TREELET stages the first ones)
 };
 
 } // namespace rb

@@ -521,6 +521,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     v.fast_root_min[0] = h.fast_root.min_x; v.fast_root_min[1] = h.fast_root.min_y; v.fast_root_min[2] = h.fast_root.min_z;
     v.fast_root_max[0] = h.fast_root.max_x; v.fast_root_max[1] = h.fast_root.max_y; v.fast_root_max[2] = h.fast_root.max_z;
     v.fast_root_ref = h.fast_root.link0;
+    v.fast_record_count = (uint32_t)std::min<size_t>(s->fast_node_count, 0xFFFFFFFFu);
     s->max_stack = h.max_stack;
     // host copies that are no longer needed — after the stream has drained: packed into page-locked blocks (host_scene.cpp)
     // the uploads above are truly asynchronous and still read them

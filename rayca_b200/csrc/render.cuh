@@ -1038,6 +1038,7 @@ constexpr uint32_t kGroupW = 8u * kWarpsX, kGroupH = 4u * kWarpsY; // pixels per
 template <int INTEGRATOR, int MODE, bool COUNT, bool PERSISTENT, bool BOUNCE>
 __global__ void __launch_bounds__(kBlockThreads, RAYCA_MIN_BLOCKS) render_kernel(const __grid_constant__ RenderParams P) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (MODE == 0 || MODE == 3) stage_treelet(P.scene); // nothing unless RAYCA_TREELET
     PixelCounters pc;
     if (PERSISTENT) {
         // one atomic per warp per GROUP (4 tiles): same-address atomics retire at about one per L2 clock,

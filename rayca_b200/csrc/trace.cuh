@@ -26,6 +26,49 @@ constexpr int kStackSize = 96;
 #define RAYCA_SMEM_STACK 0
 #endif
 
+// RAYCA_TREELET = K > 0: the first K sibling pairs of the performance tree (64 B each; the device builder lays the
+// levels above the 32-primitive subtrees out breadth-first, so these are its top levels) are copied into shared
+// memory once per block with one bulk asynchronous copy (cp.async.bulk, 1-D TMA) and the walk reads them from there.
+// A/B only (tools/variants.py "tl*"), measured no better: profiles/r02_ab_walk_variants.txt.
+#ifndef RAYCA_TREELET
+#define RAYCA_TREELET 0
+#endif
+#if RAYCA_TREELET > 0
+__shared__ __align__(128) float4 g_treelet[RAYCA_TREELET * 4];
+__shared__ __align__(8) unsigned long long g_treelet_bar;
+__device__ __forceinline__ uint32_t treelet_records(const GpuSceneView& s) {
+    return min((uint32_t)RAYCA_TREELET * 2u, s.fast_record_count & ~1u);
+}
+// every thread of the block calls this once, before its first walk
+__device__ __forceinline__ void stage_treelet(const GpuSceneView& s) {
+    const uint32_t bytes = treelet_records(s) * 32u;
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&g_treelet_bar);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        if (bytes) {
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                             (uint32_t)__cvta_generic_to_shared(g_treelet)),
+                         "l"(s.fast_nodes), "r"(bytes), "r"(bar)
+                         : "memory");
+        } else {
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+        }
+    }
+    __syncthreads(); // the barrier is initialised for everyone
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done)
+                     : "r"(bar)
+                     : "memory");
+    }
+}
+#else
+__device__ __forceinline__ void stage_treelet(const GpuSceneView&) {}
+#endif
+
 struct RayD {
     V3 o, d, rd;
 };
@@ -400,6 +443,9 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
     const float4* __restrict__ fast_tri = s.fast_tri;
     const float4* __restrict__ ref_nodes = s.nodes;
     const FastRay fr = make_fast_ray(ray);
+#if RAYCA_TREELET > 0
+    const uint32_t treelet_top = treelet_records(s);
+#endif
 
     auto ref_leaf_accepts = [&](uint32_t leaf) -> bool {
         if (leaf == ok_leaf) return true;
@@ -476,8 +522,19 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
             h0 = h0 && !(d0 > best_t);
             h1 = h1 && !(d1 > best_t);
 #else
+#if RAYCA_TREELET > 0
+            float4 a0, a1, b0, b1;
+            if (cur < treelet_top) {
+                const float4* np = g_treelet + cur * 2u;
+                a0 = np[0]; a1 = np[1]; b0 = np[2]; b1 = np[3];
+            } else {
+                const float4* np = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(fast_nodes) + (unsigned long long)cur * 32ull);
+                a0 = __ldg(np + 0); a1 = __ldg(np + 1); b0 = __ldg(np + 2); b1 = __ldg(np + 3);
+            }
+#else
             const float4* np = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(fast_nodes) + (unsigned long long)cur * 32ull);
             const float4 a0 = __ldg(np + 0), a1 = __ldg(np + 1), b0 = __ldg(np + 2), b1 = __ldg(np + 3);
+#endif
             if (COUNT) wc->nodes += 2;
             float d0, d1;
             bool h0 = slab_fast(a0, a1, fr, d0);

@@ -173,6 +173,7 @@ __device__ __forceinline__ void flush_counters(const RenderParams& P, const Pixe
 template <int MODE>
 __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_stage0_kernel(const __grid_constant__ RenderParams P, const WaveView w) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    stage_treelet(P.scene); // nothing unless RAYCA_TREELET
     const uint32_t x = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u), local_row = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
     const uint32_t y = image_row(P, local_row);
     const bool mine = x < P.width && y < P.row_end;
@@ -207,6 +208,7 @@ __global__ void wave_fill_kernel(uint32_t* keys, uint32_t* idx, uint32_t n, uint
 template <int MODE>
 __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_stage_kernel(const __grid_constant__ RenderParams P, const WaveView w, uint32_t depth) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    stage_treelet(P.scene); // nothing unless RAYCA_TREELET
     PixelCounters pc;
     if (t < w.n && w.keys_out[t] != w.dead_key) {
         const uint32_t i = w.idx_out[t];
