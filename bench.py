@@ -360,7 +360,7 @@ def ncu_profile_name(args, G):
         return "r02_ncu_soup.json"
     if args.workload == "flighthelmet":
         return "r02_ncu_flighthelmet.json"
-    return "r02_ncu_bounce_wavefront_stage1.json" if args.max_depth > 1 else "r02_ncu_atrium.json"
+    return "r02_ncu_bounce_split_shade.json" if args.max_depth > 1 else "r02_ncu_atrium.json"
 
 
 def run_ours(args):
@@ -529,6 +529,7 @@ def run_ours(args):
     sampler.stop.set()
     sampler.join()
     total_ms = sum(a.elapsed_time(b) for a, b in ev)
+    launches_per_frame = max(int(dev.last_counters().kernel_launches), 1)  # of the last timed frame
     kernel_ms = sum(a.elapsed_time(b) for a, b in kev) / args.steps
     t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
     if G > 1:
@@ -707,7 +708,10 @@ def run_ours(args):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": bench_config(args, what, desc),
                 "rays_per_frame": rays_frame, "kernel_ms": kernel_ms, "build_s": build_s,
-                "clocks": clk, "gpu_launches": args.steps * ((3 if rank == 0 else 2) if peer else 1),  # peer: trace + flag signal (+ flag wait on rank 0)
+                "clocks": clk,
+                # this library's kernels per frame as the library counts them (1 for the fused kernel; fill + stages + copy
+                # for the wavefront path, cub's sort kernels not counted) x steps; peer: + flag signal (+ flag wait on rank 0)
+                "gpu_launches": args.steps * (launches_per_frame + ((2 if rank == 0 else 1) if peer else 0)),
                 "roofline": {"bound": "l2", "achieved": achieved, "peak": l2_peak, "unit": "GB/s", "frac": achieved / l2_peak,
                              "traffic": traffic, "peak_source": "measured in this run (rayca_cuda_probe_read_bandwidth: ld.global.cg "
                                                                 "over a 64 MiB L2-resident buffer, best of 5)",

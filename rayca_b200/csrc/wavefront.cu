@@ -45,6 +45,13 @@ struct WaveView {
     uint32_t dir_bits, key_mode; // see sort_key
     uint32_t dead_key; // one bit above every live key, so that ended paths sort to the end
     float box_min[3], box_scale[3];
+    // split stages (see wave_walk_kernel): the hit of the stage's ray, and the key layout of the sort by hit point
+    float4* hit_a;     // [n] {t, u, v, primitive}
+    float4* hit_b;     // [n] {p, sphere}
+    uint32_t hit_bits; // Morton bits per axis of the hit point
+    uint32_t miss_key; // rays that hit nothing: after every hit, before the ended paths
+    uint32_t* heads;   // [levels] next unfetched sorted path of wave_walk_fetch_kernel, one counter per depth
+    uint32_t fetch_min; // lanes that must still be busy for a warp to go on without fetching new rays
 };
 
 __device__ __forceinline__ uint32_t spread3(uint32_t v) { // 10 bits -> every third bit
@@ -63,16 +70,20 @@ __device__ __forceinline__ uint32_t spread2(uint32_t v) { // 16 bits -> every se
     return v;
 }
 
+__device__ __forceinline__ uint32_t morton_cell(const WaveView& w, V3 o, uint32_t bits) {
+    const float cells = (float)(1u << bits);
+    const uint32_t qx = min((uint32_t)fmaxf((o.x - w.box_min[0]) * w.box_scale[0] * cells, 0.0f), (1u << bits) - 1u);
+    const uint32_t qy = min((uint32_t)fmaxf((o.y - w.box_min[1]) * w.box_scale[1] * cells, 0.0f), (1u << bits) - 1u);
+    const uint32_t qz = min((uint32_t)fmaxf((o.z - w.box_min[2]) * w.box_scale[2] * cells, 0.0f), (1u << bits) - 1u);
+    return spread3(qx) | (spread3(qy) << 1) | (spread3(qz) << 2);
+}
+
 // Sort key of a live ray.  key_mode 0: direction octant | Morton code of the origin (key_bits per axis).
 // key_mode 1: Morton code of the origin in a COARSE grid (key_bits per axis) | direction on the octahedral map
 // (dir_bits per axis, Morton order): rays that start in the same cell and point the same way — the ones that walk the
 // same nodes — become neighbours.  key_mode 2: the same fields, direction first.
 __device__ __forceinline__ uint32_t sort_key(const WaveView& w, V3 o, V3 d) {
-    const float cells = (float)(1u << w.key_bits);
-    const uint32_t qx = min((uint32_t)fmaxf((o.x - w.box_min[0]) * w.box_scale[0] * cells, 0.0f), (1u << w.key_bits) - 1u);
-    const uint32_t qy = min((uint32_t)fmaxf((o.y - w.box_min[1]) * w.box_scale[1] * cells, 0.0f), (1u << w.key_bits) - 1u);
-    const uint32_t qz = min((uint32_t)fmaxf((o.z - w.box_min[2]) * w.box_scale[2] * cells, 0.0f), (1u << w.key_bits) - 1u);
-    const uint32_t morton = spread3(qx) | (spread3(qy) << 1) | (spread3(qz) << 2);
+    const uint32_t morton = morton_cell(w, o, w.key_bits);
     if (w.key_mode == 0) {
         const uint32_t octant = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
         return (octant << (3u * w.key_bits)) | morton;
@@ -98,12 +109,13 @@ __device__ __forceinline__ Col ld_c(const float4* p) {
 }
 __device__ __forceinline__ void st_c(float4* p, Col c) { *p = make_float4(c.r, c.g, c.b, c.a); }
 
-// One depth of Pathtracer::trace_impl for path `i` (pathtracer<MODE, false, true> in render.cuh, one loop iteration).
-// Returns true when the path goes on (its next ray, level and key are stored); otherwise `out` / `ok` hold the folded
-// radiance of the whole path (ok = false: `None`, the pixel is BLACK).
+// One depth of Pathtracer::trace_impl for path `i` (pathtracer<MODE, false, true> in render.cuh, one loop iteration),
+// from the point where the depth's ray has been traced (`hit`, `h`).  Returns true when the path goes on (its next ray,
+// level and key are stored); otherwise `out` / `ok` hold the folded radiance of the whole path (ok = false: `None`, the
+// pixel is BLACK).
 template <int MODE>
-__device__ __forceinline__ bool wave_step(const RenderParams& P, const WaveView& w, uint32_t i, RayD ray, uint32_t pixel, uint32_t depth,
-                                          HitD& primary, PixelCounters& pc, Col& out, bool& ok) {
+__device__ __forceinline__ bool wave_after_walk(const RenderParams& P, const WaveView& w, uint32_t i, const RayD& ray, uint32_t pixel, uint32_t depth,
+                                                const HitD& h, bool hit, PixelCounters& pc, Col& out, bool& ok) {
     const GpuSceneView& s = P.scene;
     const bool nee = P.cfg.direct_sampler == RAYCA_SAMPLER_NEE;
     const uint32_t max_depth = min(P.cfg.max_depth, (uint32_t)kMaxDepth);
@@ -112,9 +124,6 @@ __device__ __forceinline__ bool wave_step(const RenderParams& P, const WaveView&
     uint32_t levels = depth; // levels stored so far: every earlier depth stored one
     bool have_tail = false;
     Col tail{0.0f, 0.0f, 0.0f, 1.0f};
-    HitD h;
-    const bool hit = trace_ray<MODE, false, false>(s, ray, h, &pc.walk);
-    if (depth == 0) primary = h;
     if (hit) {
         Surf sf;
         load_surf<true, MODE == 3>(s, ray, h, sf);
@@ -160,6 +169,16 @@ __device__ __forceinline__ bool wave_step(const RenderParams& P, const WaveView&
     return false;
 }
 
+// the whole depth: trace the depth's ray, then the above
+template <int MODE>
+__device__ __forceinline__ bool wave_step(const RenderParams& P, const WaveView& w, uint32_t i, RayD ray, uint32_t pixel, uint32_t depth,
+                                          HitD& primary, PixelCounters& pc, Col& out, bool& ok) {
+    HitD h;
+    const bool hit = trace_ray<MODE, false, false>(P.scene, ray, h, &pc.walk);
+    if (depth == 0) primary = h;
+    return wave_after_walk<MODE>(P, w, i, ray, pixel, depth, h, hit, pc, out, ok);
+}
+
 __device__ __forceinline__ void flush_counters(const RenderParams& P, const PixelCounters& pc) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t sh = __reduce_add_sync(0xFFFFFFFFu, pc.shadow), se = __reduce_add_sync(0xFFFFFFFFu, pc.secondary);
@@ -196,8 +215,9 @@ __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_stage0_kernel(cons
 
 // pads the sort input beyond the launch's paths (rows x width need not fill the last sort tile) — and marks pixels outside
 // the image rows of a ragged last block
-__global__ void wave_fill_kernel(uint32_t* keys, uint32_t* idx, uint32_t n, uint32_t dead_key) {
+__global__ void wave_fill_kernel(uint32_t* keys, uint32_t* idx, uint32_t n, uint32_t dead_key, uint32_t* heads, uint32_t head_count) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < head_count) heads[i] = 0u;
     if (i < n) {
         keys[i] = dead_key;
         idx[i] = i;
@@ -220,6 +240,209 @@ __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_stage_kernel(const
         Col c{0.0f, 0.0f, 0.0f, 1.0f};
         bool ok = false;
         const bool alive = wave_step<MODE>(P, w, i, ray, y * P.width + x, depth, unused, pc, c, ok);
+        if (!alive) {
+            if (!ok) c = Col{0.0f, 0.0f, 0.0f, 1.0f};
+            write_pixel_color(P, x, y, local_row, cadd(Col{0.0f, 0.0f, 0.0f, 1.0f}, c));
+        }
+    }
+    flush_counters(P, pc);
+}
+
+// Split stage k >= 1, first half: one thread per path SORTED BY RAY, the depth's ray only.  The hit goes to memory with a
+// key made of the hit POINT: the second half (shading, shadow rays towards the point lights, the next bounce) then runs
+// on paths sorted by where they are now — their shadow rays leave from neighbouring points for the same lights, like
+// the shadow rays of a tile of primary hits — instead of inheriting the order of the rays that got them there.
+template <int MODE>
+__global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_walk_kernel(const __grid_constant__ RenderParams P, const WaveView w) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    stage_treelet(P.scene); // nothing unless RAYCA_TREELET
+    PixelCounters pc;
+    if (t < w.n && w.keys_out[t] != w.dead_key) {
+        const uint32_t i = w.idx_out[t];
+        const float4 o = w.ray_o[i], d = w.ray_d[i];
+        const RayD ray = make_ray(V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z});
+        HitD h;
+        const bool hit = trace_ray<MODE, false, false>(P.scene, ray, h, &pc.walk);
+        w.hit_a[i] = make_float4(h.t, h.u, h.v, __uint_as_float(hit ? h.prim : 0xFFFFFFFFu));
+        w.hit_b[i] = make_float4(h.p.x, h.p.y, h.p.z, __uint_as_float(h.sphere));
+        w.keys_in[i] = hit ? morton_cell(w, h.p, w.hit_bits) : w.miss_key;
+    }
+}
+
+// The same first half as a PERSISTENT kernel with dynamic ray fetch (Aila & Laine, "Understanding the efficiency of ray
+// traversal on GPUs", HPG 2009): a lane whose ray is finished does not wait for the longest ray of its warp — when
+// fewer than `fetch_min` lanes are still busy, the idle lanes take the next rays of the sorted queue (one atomic per
+// warp) and the warp goes on with 32 again.  Bounce rays of one warp differ in length by 2 x and more even when sorted
+// (14.8 of 32 lanes active per instruction in the one-ray-per-thread stage, profiles/r02_ncu_bounce_wavefront_stage1.json).
+// The walk is walk_fast_body's (trace.cuh), closest hit, triangles only, restated as a resumable loop: the same boxes
+// and triangles are tested with the same arithmetic and the same tie rule, so the hit is the same whatever the order.
+__global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_walk_fetch_kernel(const __grid_constant__ RenderParams P, const WaveView w, uint32_t* head) {
+    const GpuSceneView& s = P.scene;
+    const uint32_t lane = threadIdx.x & 31u;
+    constexpr uint32_t kFull = 0xFFFFFFFFu, kDone = 0xFFFFFFFFu;
+    const float4* __restrict__ fast_nodes = s.fast_nodes;
+    const float4* __restrict__ fast_tri = s.fast_tri;
+    const float4* __restrict__ ref_nodes = s.nodes;
+    uint2 stack[kStackSize + 2];
+    bool alive = false, exhausted = false;
+    uint32_t i = 0, cur = kDone, best = 0xFFFFFFFFu, ok_leaf = 0xFFFFFFFFu;
+    int sp = 1;
+    float best_t = 0.0f, bu = 0.0f, bv = 0.0f, bden = 1.0f;
+    RayD ray{};
+    FastRay fr{};
+    auto push = [&](uint32_t ref, float dist) {
+        stack[sp] = make_uint2(ref, __float_as_uint(dist));
+        sp = min(sp + 1, kStackSize + 1);
+    };
+    auto pop = [&]() -> uint32_t {
+        uint2 e;
+        do {
+            e = stack[--sp];
+        } while (__uint_as_float(e.y) > best_t);
+        return e.x;
+    };
+    auto ref_leaf_accepts = [&](uint32_t leaf) -> bool {
+        if (leaf == ok_leaf) return true;
+        const float4 lo = __ldg(&ref_nodes[2 * (size_t)leaf]);
+        const float4 hi = __ldg(&ref_nodes[2 * (size_t)leaf + 1]);
+        if (slab(lo, hi, ray) == kF32Max) return false;
+        ok_leaf = leaf;
+        return true;
+    };
+    for (;;) {
+        // ---- idle lanes fetch the next rays of the sorted queue
+        const uint32_t idle = __ballot_sync(kFull, !alive);
+        if (idle && !exhausted) {
+            const uint32_t leader = (uint32_t)__ffs((int)idle) - 1u;
+            uint32_t base = 0;
+            if (lane == leader) base = atomicAdd(head, (uint32_t)__popc(idle));
+            base = __shfl_sync(kFull, base, (int)leader);
+            bool dry = false;
+            if (!alive) {
+                const uint32_t t = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+                if (t < w.n && w.keys_out[t] != w.dead_key) {
+                    i = w.idx_out[t];
+                    const float4 o = w.ray_o[i], d = w.ray_d[i];
+                    ray = make_ray(V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z});
+                    fr = make_fast_ray(ray);
+                    best_t = __int_as_float(0x7f800000);
+                    best = 0xFFFFFFFFu;
+                    bu = bv = 0.0f;
+                    bden = 1.0f;
+                    ok_leaf = 0xFFFFFFFFu;
+                    bool go = !(ray.rd.x == 0.0f || ray.rd.y == 0.0f || ray.rd.z == 0.0f);
+                    if (go) {
+                        const float4 lo = make_float4(s.fast_root_min[0], s.fast_root_min[1], s.fast_root_min[2], 0.0f);
+                        const float4 hi = make_float4(s.fast_root_max[0], s.fast_root_max[1], s.fast_root_max[2], 0.0f);
+                        float e;
+                        go = slab_fast(lo, hi, fr, e);
+                    }
+                    stack[0] = make_uint2(kDone, 0xff800000u);
+                    sp = 1;
+                    cur = go ? s.fast_root_ref : kDone;
+                    alive = true;
+                } else {
+                    dry = true; // beyond the live paths (ended paths sort to the end)
+                }
+            }
+            exhausted = __any_sync(kFull, dry);
+        }
+        if (!__any_sync(kFull, alive)) break;
+        const uint32_t keep = exhausted ? 1u : w.fetch_min;
+        // ---- walk: one "descend to a leaf, test the leaf" round per iteration, for the lanes that hold a ray
+        do {
+            if (alive) {
+                while (!(cur & kLeafFlag)) {
+                    const float4* np = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(fast_nodes) + (unsigned long long)cur * 32ull);
+                    const float4 a0 = __ldg(np + 0), a1 = __ldg(np + 1), b0 = __ldg(np + 2), b1 = __ldg(np + 3);
+                    float d0, d1;
+                    bool h0 = slab_fast(a0, a1, fr, d0);
+                    bool h1 = slab_fast(b0, b1, fr, d1);
+                    h0 = h0 && !(d0 > best_t);
+                    h1 = h1 && !(d1 > best_t);
+                    uint32_t c0 = __float_as_uint(a0.w), c1 = __float_as_uint(b0.w);
+                    if (h0 && h1) {
+                        if (d1 < d0) {
+                            float td = d0; d0 = d1; d1 = td;
+                            uint32_t tc = c0; c0 = c1; c1 = tc;
+                        }
+                        cur = c0;
+                        push(c1, d1);
+                    } else if (h0) {
+                        cur = c0;
+                    } else if (h1) {
+                        cur = c1;
+                    } else {
+                        cur = pop();
+                    }
+                }
+                if (cur == kDone) { // the ray is finished: its hit goes out, the lane is free
+                    const bool hit = best != 0xFFFFFFFFu;
+                    const V3 p = ray.o + ray.d * best_t; // Hit::point, the `p` of the winning test (triangle.rs:121)
+                    w.hit_a[i] = make_float4(best_t, bu / bden, bv / bden, __uint_as_float(best));
+                    w.hit_b[i] = make_float4(p.x, p.y, p.z, __uint_as_float(0u));
+                    w.keys_in[i] = hit ? morton_cell(w, p, w.hit_bits) : w.miss_key;
+                    alive = false;
+                } else {
+                    const V3 o = ray.o, d = ray.d;
+                    const uint32_t first = cur & 0x07FFFFFFu, count = ((cur >> 28) & 7u) + 1u;
+                    for (uint32_t k = first; k < first + count; ++k) {
+                        const float4* q = fast_tri + 4 * (size_t)k;
+                        const float4 q0 = __ldg(q);
+                        const V3 n{q0.x, q0.y, q0.z};
+                        const float ndd = dot(d, n);
+                        if (ndd > 0.0f) continue;
+                        if (fabsf(ndd) < kF32Eps) continue;
+                        const float t = -(dot(n, o) + q0.w) / ndd;
+                        if (t < 0.0f) continue;
+                        if (t > best_t) continue;
+                        const float4 q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+                        const V3 v0{q1.x, q1.y, q1.z}, v1{q2.x, q2.y, q2.z}, v2{q3.x, q3.y, q3.z};
+                        const V3 p = o + d * t;
+                        V3 cc = cross(v1 - v0, p - v0);
+                        if (dot(n, cc) < 0.0f) continue;
+                        cc = cross(v2 - v1, p - v1);
+                        const float u = dot(n, cc);
+                        if (u < 0.0f) continue;
+                        cc = cross(v0 - v2, p - v2);
+                        const float v = dot(n, cc);
+                        if (v < 0.0f) continue;
+                        const uint32_t id = __float_as_uint(q1.w);
+                        if (t < best_t || (t == best_t && id < best && best != 0xFFFFFFFFu)) {
+                            if (ref_leaf_accepts(__float_as_uint(q2.w))) {
+                                best_t = t;
+                                best = id;
+                                bu = u;
+                                bv = v;
+                                bden = q3.w;
+                            }
+                        }
+                    }
+                    cur = pop();
+                }
+            }
+        } while ((uint32_t)__popc(__ballot_sync(kFull, alive)) >= keep);
+    }
+}
+
+// Split stage k >= 1, second half: one thread per path SORTED BY HIT POINT
+template <int MODE>
+__global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_shade_kernel(const __grid_constant__ RenderParams P, const WaveView w, uint32_t depth) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    stage_treelet(P.scene); // nothing unless RAYCA_TREELET
+    PixelCounters pc;
+    if (t < w.n && w.keys_out[t] != w.dead_key) {
+        const uint32_t i = w.idx_out[t];
+        const uint32_t local_row = i / P.width, x = i - local_row * P.width, y = image_row(P, local_row);
+        const float4 o = w.ray_o[i], d = w.ray_d[i], ha = w.hit_a[i], hb = w.hit_b[i];
+        const RayD ray = make_ray(V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z});
+        HitD h;
+        h.t = ha.x; h.u = ha.y; h.v = ha.z; h.prim = __float_as_uint(ha.w);
+        h.p = V3{hb.x, hb.y, hb.z};
+        h.sphere = __float_as_uint(hb.w);
+        Col c{0.0f, 0.0f, 0.0f, 1.0f};
+        bool ok = false;
+        const bool alive = wave_after_walk<MODE>(P, w, i, ray, y * P.width + x, depth, h, h.prim != 0xFFFFFFFFu, pc, c, ok);
         if (!alive) {
             if (!ok) c = Col{0.0f, 0.0f, 0.0f, 1.0f};
             write_pixel_color(P, x, y, local_row, cadd(Col{0.0f, 0.0f, 0.0f, 1.0f}, c));
@@ -284,14 +507,25 @@ int wave_render(const RenderParams& P_in, uint32_t rows, bool spheres, WaveScrat
     if (const char* e = std::getenv("RAYCA_WAVE_KEY_BITS")) key_bits = (uint32_t)std::min(9, std::max(1, std::atoi(e)));
     if (const char* e = std::getenv("RAYCA_WAVE_DIR_BITS")) dir_bits = (uint32_t)std::min(8, std::max(1, std::atoi(e)));
     if (key_mode != 0 && 3 * key_bits + 2 * dir_bits > 31) dir_bits = (31 - 3 * key_bits) / 2;
-    const uint32_t live_bits = key_mode == 0 ? 3 * key_bits + 3 : 3 * key_bits + 2 * dir_bits;
+    // split stages (wave_walk_kernel / wave_shade_kernel, a second sort by hit point in between): on unless RAYCA_WAVE_SPLIT=0
+    bool split = true;
+    uint32_t hit_bits = 7;
+    if (const char* e = std::getenv("RAYCA_WAVE_SPLIT")) split = std::atoi(e) != 0;
+    if (const char* e = std::getenv("RAYCA_WAVE_HIT_BITS")) hit_bits = (uint32_t)std::min(10, std::max(1, std::atoi(e)));
+    // the walk half as a persistent kernel with dynamic ray fetch (triangle-only scenes): on unless RAYCA_WAVE_FETCH=0
+    bool fetch = split && !spheres;
+    uint32_t fetch_min = 16;
+    if (const char* e = std::getenv("RAYCA_WAVE_FETCH")) fetch = fetch && std::atoi(e) != 0;
+    if (const char* e = std::getenv("RAYCA_WAVE_FETCH_MIN")) fetch_min = (uint32_t)std::min(32, std::max(1, std::atoi(e)));
+    uint32_t live_bits = key_mode == 0 ? 3 * key_bits + 3 : 3 * key_bits + 2 * dir_bits;
+    if (split) live_bits = std::max(live_bits, 3 * hit_bits + 1); // hit keys, then the miss key one bit above them
     const int end_bit = (int)live_bits + 1; // ended paths carry the bit above the live keys
     size_t temp_bytes = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr,
                                     (int)n, 0, end_bit, st);
     auto al = [](size_t b) { return (b + 255) & ~size_t(255); };
-    const size_t need = 2 * al((size_t)n * 16) + 2 * al((size_t)levels * n * 16) + 4 * al((size_t)n * 4) + al(temp_bytes) +
-                        (stage_pixels ? al(plane_pixels * 4) : 0) + 256;
+    const size_t need = (split ? 4 : 2) * al((size_t)n * 16) + 2 * al((size_t)levels * n * 16) + 4 * al((size_t)n * 4) + al(temp_bytes) +
+                        (stage_pixels ? al(plane_pixels * 4) : 0) + al((size_t)levels * 4) + 256;
     if (need > ws.bytes) {
         cudaFree(ws.base);
         ws.base = nullptr;
@@ -313,6 +547,14 @@ int wave_render(const RenderParams& P_in, uint32_t rows, bool spheres, WaveScrat
     w.keys_out = carve<uint32_t>(p, n);
     w.idx_in = carve<uint32_t>(p, n);
     w.idx_out = carve<uint32_t>(p, n);
+    if (split) {
+        w.hit_a = carve<float4>(p, n);
+        w.hit_b = carve<float4>(p, n);
+    }
+    w.heads = carve<uint32_t>(p, levels);
+    w.fetch_min = fetch_min;
+    w.hit_bits = hit_bits;
+    w.miss_key = 1u << (3 * hit_bits);
     uchar4* plane = stage_pixels ? carve<uchar4>(p, plane_pixels) : nullptr;
     void* temp = p;
     if (stage_pixels) P.rgba8 = reinterpret_cast<unsigned char*>(plane);
@@ -326,8 +568,16 @@ int wave_render(const RenderParams& P_in, uint32_t rows, bool spheres, WaveScrat
         w.box_min[a] = lo;
         w.box_scale[a] = hi > lo ? 1.0f / (hi - lo) : 0.0f;
     }
+    uint32_t fetch_blocks = 0;
+    if (fetch) { // as many blocks as the device keeps resident: every warp loops until the queue is dry
+        int dev = 0, sms = 0, per_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_walk_fetch_kernel, 128, 0);
+        fetch_blocks = (uint32_t)std::max(1, sms * std::max(1, per_sm));
+    }
     uint32_t k = 0;
-    wave_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(w.keys_in, w.idx_in, n, w.dead_key);
+    wave_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(w.keys_in, w.idx_in, n, w.dead_key, w.heads, levels);
     ++k;
     const dim3 grid((P.width + 15) / 16, (rows + 7) / 8);
     if (spheres) wave_stage0_kernel<3><<<grid, 128, 0, st>>>(P, w);
@@ -339,8 +589,28 @@ int wave_render(const RenderParams& P_in, uint32_t rows, bool spheres, WaveScrat
             err = std::string("wavefront sort: ") + cudaGetErrorString(e);
             return RAYCA_E_CUDA;
         }
-        if (spheres) wave_stage_kernel<3><<<(n + 127) / 128, 128, 0, st>>>(P, w, depth);
-        else wave_stage_kernel<0><<<(n + 127) / 128, 128, 0, st>>>(P, w, depth);
+        if (!split) {
+            if (spheres) wave_stage_kernel<3><<<(n + 127) / 128, 128, 0, st>>>(P, w, depth);
+            else wave_stage_kernel<0><<<(n + 127) / 128, 128, 0, st>>>(P, w, depth);
+            ++k;
+            continue;
+        }
+        if (fetch) {
+            const uint32_t blocks = std::min<uint32_t>((n + 127) / 128, fetch_blocks);
+            wave_walk_fetch_kernel<<<blocks, 128, 0, st>>>(P, w, w.heads + depth);
+        } else if (spheres) {
+            wave_walk_kernel<3><<<(n + 127) / 128, 128, 0, st>>>(P, w);
+        } else {
+            wave_walk_kernel<0><<<(n + 127) / 128, 128, 0, st>>>(P, w);
+        }
+        ++k;
+        e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, w.keys_in, w.keys_out, w.idx_in, w.idx_out, (int)n, 0, end_bit, st);
+        if (e != cudaSuccess) {
+            err = std::string("wavefront sort: ") + cudaGetErrorString(e);
+            return RAYCA_E_CUDA;
+        }
+        if (spheres) wave_shade_kernel<3><<<(n + 127) / 128, 128, 0, st>>>(P, w, depth);
+        else wave_shade_kernel<0><<<(n + 127) / 128, 128, 0, st>>>(P, w, depth);
         ++k;
     }
     if (stage_pixels) {
