@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--tile", type=int, default=8)
     ap.add_argument("--max-depth", type=int, default=1)
     ap.add_argument("--flags", type=int, default=0)
+    ap.add_argument("--no-flush", action="store_true", help="leave the L2 warm between timed launches")
     a = ap.parse_args()
     import torch
 
@@ -42,7 +43,8 @@ def main():
             dev.render_device(cfg, W, H, buf.data_ptr(), stream=stream, options=opts)
         ms = []
         for k in range(a.reps):
-            flush.fill_(k & 0xFF)
+            if not a.no_flush:
+                flush.fill_(k & 0xFF)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             dev.render_device(cfg, W, H, buf.data_ptr(), stream=stream, options=opts)
@@ -54,7 +56,7 @@ def main():
     whole = time_shard(0, 1)
     per = [time_shard(r, a.shards) for r in range(a.shards)]
     ideal = whole / a.shards
-    print(f"lib {os.environ.get('RAYCA_CUDA_LIB', 'product')} tile {a.tile} depth {a.max_depth}: whole frame {whole:.4f} ms, ideal per rank {ideal:.4f} ms; "
+    print(f"{'warm L2 ' if a.no_flush else ''}lib {os.environ.get('RAYCA_CUDA_LIB', 'product')} tile {a.tile} depth {a.max_depth}: whole frame {whole:.4f} ms, ideal per rank {ideal:.4f} ms; "
           f"shards of {a.shards}: min {min(per):.4f} mean {np.mean(per):.4f} max {max(per):.4f} ms -> efficiency {ideal / max(per):.3f} "
           f"(imbalance max/mean {max(per) / np.mean(per):.3f}, tail mean/ideal {np.mean(per) / ideal:.3f})")
 
