@@ -19,6 +19,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <chrono>
 #include <cstring>
 
 namespace rb {
@@ -943,7 +944,47 @@ __global__ void prep_bounds_kernel(const float4* __restrict__ tri_pos, uint32_t 
     order[i] = i;
 }
 
-int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStream_t st, FastTreeDevice& out, std::string& err) {
+// reference leaf of every primitive from the packed reference nodes already on the device (link0 = first primitive,
+// link1 = count for a leaf): one warp per node record of the BLAS range [0, blas_nodes) — the TLAS pairs behind it hold
+// COPIES of BLAS roots and are skipped
+__global__ void ref_leaf_kernel(const GpuNode* __restrict__ nodes, uint32_t blas_nodes, uint32_t* __restrict__ ref_leaf) {
+    const uint32_t k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (k >= blas_nodes) return;
+    const uint32_t first = nodes[k].link0, count = nodes[k].link1;
+    for (uint32_t i = lane; i < count; i += 32u) ref_leaf[first + i] = k;
+}
+
+// the reference leaf (index into HostScene::nodes) of every primitive, reference-global primitive order
+void reference_leaves(const HostScene& hs, PodVector<uint32_t>& ref_leaf) {
+    const size_t nb = hs.blas.size();
+    ref_leaf.resize(hs.blas_prim_offset[nb]); // every primitive lies in exactly one reference leaf: all entries are written
+    for (size_t bi = 0; bi < nb; ++bi) {
+        const HostBlas& b = hs.blas[bi];
+        const uint32_t po = hs.blas_prim_offset[bi];
+        // leaves own disjoint primitive ranges: the nodes are spread over the threads (a BLAS built without a tree is
+        // one leaf holding everything, hence the inner loop is the parallel one then)
+        if (b.nodes.size() < 64) {
+            for (size_t k = 0; k < b.nodes.size(); ++k) {
+                const HostNode& n = b.nodes[k];
+                if (k == 1 || n.count == 0) continue;
+                const uint32_t leaf = hs.blas_node_offset[bi] + (uint32_t)k;
+#pragma omp parallel for schedule(static) if (n.count > 8192)
+                for (int64_t i = 0; i < (int64_t)n.count; ++i) ref_leaf[po + n.offset + (size_t)i] = leaf;
+            }
+        } else {
+#pragma omp parallel for schedule(static, 4096)
+            for (int64_t k = 0; k < (int64_t)b.nodes.size(); ++k) {
+                const HostNode& n = b.nodes[(size_t)k];
+                if (k == 1 || n.count == 0) continue;
+                const uint32_t leaf = hs.blas_node_offset[bi] + (uint32_t)k;
+                for (uint32_t i = 0; i < n.count; ++i) ref_leaf[po + n.offset + (size_t)i] = leaf;
+            }
+        }
+    }
+}
+
+int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStream_t st, FastTreeDevice& out, std::string& err,
+                           const void* d_ref_nodes) {
     int bins_unused;
     uint32_t leaf_max;
     float trav_cost;
@@ -951,12 +992,25 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
     const size_t nb = hs.blas.size();
     const uint32_t N = hs.blas_prim_offset[nb];
     if (N == 0) { err = "no primitives"; return RAYCA_E_INVALID_ARG; }
+    const bool timing = std::getenv("RAYCA_TIMING") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double t_lap = now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        const double t = now();
+        std::fprintf(stderr, "[rayca]     %-26s %8.2f ms\n", what, t - t_lap);
+        t_lap = t;
+    };
 
     // ---- host side: bounds in reference-global order, reference leaf of every primitive, sphere records
     bool any_sphere = false;
     for (size_t bi = 0; bi < nb; ++bi) any_sphere = any_sphere || !hs.blas[bi].spheres.empty();
     std::vector<float4> hmn(any_sphere ? N : 0), hmx(any_sphere ? N : 0); // sphere scenes: bounds from the host (a sphere's are not its record's)
-    std::vector<uint32_t> ref_leaf(N, 0);
+    // triangle-only scenes with the reference nodes on the device: the table is made there (ref_leaf_kernel); sphere
+    // scenes need it on the host for their sphere records
+    const bool leaves_on_device = d_ref_nodes != nullptr && !any_sphere;
+    PodVector<uint32_t> ref_leaf;
+    if (!leaves_on_device) reference_leaves(hs, ref_leaf);
     std::vector<float4> sphere_records;
     std::vector<uint32_t> sphere_base(nb + 1, 0);
     for (size_t bi = 0; bi < nb; ++bi) sphere_base[bi + 1] = sphere_base[bi] + (uint32_t)hs.blas[bi].spheres.size();
@@ -964,14 +1018,7 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
     for (size_t bi = 0; bi < nb; ++bi) {
         const HostBlas& b = hs.blas[bi];
         const uint32_t po = hs.blas_prim_offset[bi];
-        for (size_t k = 0; k < b.nodes.size(); ++k) {
-            const HostNode& n = b.nodes[k];
-            if (k == 1 || n.count == 0) continue;
-            const uint32_t leaf = hs.blas_node_offset[bi] + (uint32_t)k;
-#pragma omp parallel for schedule(static) if (n.count > 8192)
-            for (int64_t i = 0; i < (int64_t)n.count; ++i) ref_leaf[po + n.offset + (size_t)i] = leaf;
-        }
-#pragma omp parallel for schedule(static) if (b.tris.size() > 8192)
+#pragma omp parallel for schedule(static) if (any_sphere && b.tris.size() > 8192)
         for (int64_t k = 0; k < (int64_t)(any_sphere ? b.tris.size() : 0); ++k) {
             const HostTri& t = b.tris[(size_t)k];
             const uint32_t id = po + (uint32_t)k;
@@ -990,13 +1037,14 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
             hmn[id] = make_float4(t.bmin.x, t.bmin.y, t.bmin.z, 0.0f);
             hmx[id] = make_float4(t.bmax.x, t.bmax.y, t.bmax.z, __builtin_bit_cast(float, sphere));
         }
-        for (size_t k = 0; k < b.tris.size(); ++k)
+        for (size_t k = 0; k < (b.spheres.empty() ? 0 : b.tris.size()); ++k) // (a serial scan of every primitive: sphere models only)
             if (b.tris[k].sphere) {
                 const uint32_t sphere = sphere_base[bi] + b.tris[k].sphere;
                 sphere_records[(size_t)(sphere - 1) * 4 + 3].w = __builtin_bit_cast(float, ref_leaf[po + k]);
             }
     }
 
+    lap("fast: host prep");
     // ---- device buffers
     DeviceBuffers buf(st);
     const uint32_t cap_big = N / (kSmall + 1) + 1;
@@ -1035,6 +1083,7 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
     FB_TRY(buf.alloc_output(&d_records, (size_t)N * 2 + 2));
     FB_TRY(buf.alloc(&d_root, 1));
     FB_TRY(buf.commit());
+    lap("fast: alloc");
 
     cudaEvent_t e0, e1;
     FB_TRY(cudaEventCreate(&e0));
@@ -1043,7 +1092,12 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
         FB_TRY(cudaMemcpyAsync(d_mn, hmn.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
         FB_TRY(cudaMemcpyAsync(d_mx, hmx.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
     }
-    FB_TRY(cudaMemcpyAsync(d_ref_leaf, ref_leaf.data(), (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    if (leaves_on_device) {
+        const uint32_t blas_nodes = hs.blas_node_offset[nb];
+        ref_leaf_kernel<<<blocks_for((size_t)blas_nodes * 32, 256), 256, 0, st>>>(static_cast<const GpuNode*>(d_ref_nodes), blas_nodes, d_ref_leaf);
+    } else {
+        FB_TRY(cudaMemcpyAsync(d_ref_leaf, ref_leaf.data(), (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    }
     if (!sphere_records.empty())
         FB_TRY(cudaMemcpyAsync(d_sphere, sphere_records.data(), sphere_records.size() * sizeof(float4), cudaMemcpyHostToDevice, st));
     FB_TRY(cudaEventRecord(e0, st));
@@ -1100,6 +1154,7 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
         ++levels;
         if (levels > 4096) { err = "device tree build: runaway depth"; return RAYCA_E_CUDA; }
     }
+    lap("fast: level loop");
     if (nsmall) {
         small_sizes<<<blocks_for(nsmall, T), T, 0, st>>>(d_small, nsmall, d_sizes);
         exclusive_scan(d_sizes, nsmall, d_pair_offset, d_partial, st);
@@ -1116,6 +1171,7 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     out.levels = levels;
+    lap("fast: subtrees + records");
     out.small_subtrees = nsmall;
     out.nodes = d_records;
     out.tri = d_tri;
@@ -1149,9 +1205,22 @@ int transpose_pairs_device(void* d_nodes, size_t node_count, cudaStream_t st) {
 int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::string& err, float* device_ms) {
     const uint32_t N = (uint32_t)blas.tris.size();
     if (N == 0) { err = "no primitives"; return RAYCA_E_INVALID_ARG; }
-    std::vector<float4> hmn(N), hmx(N), hcen(N);
+    const bool timing = std::getenv("RAYCA_TIMING") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double t_lap = now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        const double t = now();
+        std::fprintf(stderr, "[rayca]     %-26s %8.2f ms\n", what, t - t_lap);
+        t_lap = t;
+    };
+    // PodVector: recycled, page-locked blocks without value initialisation (host_scene.h) — three std::vectors of N
+    // float4 cost 1.4 ms of page faults and memset per build, and their uploads were pageable
+    PodVector<float4> hmn(N), hmx(N), hcen(N);
+    PodVector<uint32_t> order(N);
 #pragma omp parallel for schedule(static) if (N > 8192)
     for (int64_t i = 0; i < (int64_t)N; ++i) {
+        order[(size_t)i] = (uint32_t)i;
         const HostTri& t = blas.tris[(size_t)i];
         hmn[(size_t)i] = make_float4(t.bmin.x, t.bmin.y, t.bmin.z, 0.0f);
         hmx[(size_t)i] = make_float4(t.bmax.x, t.bmax.y, t.bmax.z, 0.0f);
@@ -1187,12 +1256,11 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
     FB_TRY(buf.alloc(&d_info, cap));
     FB_TRY(buf.alloc(&d_dec, cap));
     FB_TRY(buf.commit());
+    lap("blas: host prep + alloc");
 
     cudaEvent_t e0, e1;
     FB_TRY(cudaEventCreate(&e0));
     FB_TRY(cudaEventCreate(&e1));
-    std::vector<uint32_t> order(N);
-    for (uint32_t i = 0; i < N; ++i) order[i] = i;
     FB_TRY(cudaMemcpyAsync(d_mn, hmn.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
     FB_TRY(cudaMemcpyAsync(d_mx, hmx.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
     FB_TRY(cudaMemcpyAsync(d_cen, hcen.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
@@ -1245,6 +1313,7 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
         ++level;
     }
     FB_TRY(cudaEventRecord(e1, st));
+    lap("blas: uploads + level loop");
     std::vector<RefNode> tmp(next_id);
     FB_TRY(cudaMemcpyAsync(tmp.data(), d_nodes, (size_t)next_id * sizeof(RefNode), cudaMemcpyDeviceToHost, st));
     FB_TRY(cudaMemcpyAsync(order.data(), d_order[cur], (size_t)N * 4, cudaMemcpyDeviceToHost, st));
@@ -1255,6 +1324,7 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     if (device_ms) *device_ms = ms;
+    lap("blas: read back");
 
     // renumber in the reference's push order (blas.rs:296-311): a node's children are appended when the node is
     // processed, then the left subtree is processed completely before the right one
@@ -1293,10 +1363,12 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
         blas.nodes[t.out_index] = h;
     }
     blas.depth = deepest;
+    lap("blas: renumber nodes");
     PodVector<HostTri> sorted(N);
 #pragma omp parallel for schedule(static) if (N > 8192)
     for (int64_t i = 0; i < (int64_t)N; ++i) sorted[(size_t)i] = blas.tris[order[(size_t)i]];
     blas.tris.swap(sorted);
+    lap("blas: permute primitives");
     return RAYCA_OK;
 }
 

@@ -18,7 +18,11 @@ struct FastTreeDevice {
 
 // Inputs: the packed host scene WITHOUT its performance tree (HostScene::{blas, blas_prim_offset,
 // blas_node_offset} final) and the device copy of HostScene::tri_pos.  Returns RAYCA_OK or an error code.
-int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStream_t stream, FastTreeDevice& out, std::string& err);
+// `d_ref_nodes`: the device copy of HostScene::nodes when there is one — the reference leaf of every primitive is then
+// looked up on the device (triangle-only scenes); nullptr: on the host (reference_leaves).
+int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStream_t stream, FastTreeDevice& out, std::string& err,
+                           const void* d_ref_nodes = nullptr);
+void reference_leaves(const HostScene& hs, PodVector<uint32_t>& ref_leaf);
 
 // Reference BLAS (bvh_build.cpp's build_blas) on the device: same nodes, same primitive order.  RAYCA_E_UNSUPPORTED
 // asks the caller to use the host builder (a level broader than the device work lists).

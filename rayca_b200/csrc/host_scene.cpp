@@ -27,10 +27,7 @@ TrsF to_trs(const rayca_trs& t) {
     return r;
 }
 
-// ---- 3x3 helpers (rayca-math/src/mat3.rs), row-major m[i][j]
-struct M3 {
-    float m[3][3];
-};
+// ---- 3x3 helpers (rayca-math/src/mat3.rs), row-major m[i][j]; struct M3 lives in host_scene.h
 M3 m3_identity() { return M3{{{1, 0, 0}, {0, 1, 0}, {0, 0, 1}}}; }
 // mat3.rs:190-216
 M3 m3_from_quat(Q4 q) {
@@ -233,7 +230,7 @@ std::vector<PodBlock> g_pod_blocks; // cached (free) blocks
 std::vector<PodBlock> g_pod_lent;   // blocks handed out again: their real size and whether they are page-locked
 size_t g_pod_bytes = 0;
 bool g_pod_pin = false;
-constexpr size_t kPodMaxBlocks = 16, kPodMaxBytes = size_t(1) << 30;
+constexpr size_t kPodMaxBlocks = 32, kPodMaxBytes = size_t(1) << 30;
 } // namespace
 
 // Called once a CUDA context exists (rayca_cuda_init): from then on a block that enters the cache is page-locked
@@ -294,8 +291,82 @@ struct PhaseTimer { // RAYCA_TIMING=1 prints the host phases of scene_create to 
 };
 } // namespace
 
+namespace {
+// the mesh primitive that emitted triangle `src` of the BLAS (emit order), or nullptr for a sphere / quad-light triangle
+inline const HostMeshJob* job_of(const HostBlas& b, uint32_t src) {
+    size_t lo = 0, hi = b.jobs.size();
+    while (lo < hi) { // first job whose base exceeds src
+        const size_t mid = (lo + hi) / 2;
+        if (b.jobs[mid].base <= src) lo = mid + 1;
+        else hi = mid;
+    }
+    if (lo == 0) return nullptr;
+    const HostMeshJob& j = b.jobs[lo - 1];
+    return src < j.base + j.ntri ? &j : nullptr;
+}
+inline uint32_t material_of(const HostBlas& b, uint32_t src) {
+    if (const HostMeshJob* j = job_of(b, src)) return j->material;
+    return b.attrs[src].material;
+}
+} // namespace
+
+void pack_tri_attrs(const rayca_scene_desc& d, HostScene& out) {
+    for (size_t bi = 0; bi < out.blas.size(); ++bi) {
+        const HostBlas& b = out.blas[bi];
+        const uint32_t po = out.blas_prim_offset[bi];
+#pragma omp parallel for schedule(static) if (b.tris.size() > 8192)
+        for (int64_t k = 0; k < (int64_t)b.tris.size(); ++k) {
+            const HostTri& t = b.tris[(size_t)k];
+            float4* q = &out.tri_attr[((size_t)po + (size_t)k) * 12];
+            if (t.sphere) {
+                // sphere prim: attr record = {inverse Mat4 rows 0..2 | normal matrix rows (w: centre) | world t, q, s |
+                // material}; what primitive.rs:183-190 derives from the node TRS on every shaded hit
+                const HostSphere& sp = b.spheres[t.sphere - 1];
+                M4 inv = m4_from_inversed(sp.world);
+                M3 nm = normal_matrix_of(sp.world);
+                const float cc[3] = {sp.center.x, sp.center.y, sp.center.z};
+                for (int r = 0; r < 3; ++r) {
+                    q[r] = make_float4(inv.m[r][0], inv.m[r][1], inv.m[r][2], inv.m[r][3]);
+                    q[3 + r] = make_float4(nm.m[r][0], nm.m[r][1], nm.m[r][2], cc[r]);
+                }
+                q[6] = make_float4(sp.world.t.x, sp.world.t.y, sp.world.t.z, 0.0f);
+                q[7] = make_float4(sp.world.q.x, sp.world.q.y, sp.world.q.z, sp.world.q.w);
+                q[8] = make_float4(sp.world.s.x, sp.world.s.y, sp.world.s.z, 0.0f);
+                q[9] = make_float4(0.0f, 0.0f, 0.0f, __builtin_bit_cast(float, sp.material));
+                q[10] = q[11] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                continue;
+            }
+            if (const HostMeshJob* job = job_of(b, t.src)) {
+                // BvhTriangle attributes (bvh/triangle.rs:33-71, primitive.rs:239-268): vertex colour and uv verbatim,
+                // normal through the node's normal matrix, tangent and bitangent through its tangent matrix
+                const uint32_t local = t.src - (uint32_t)job->base;
+                for (int v = 0; v < 3; ++v) {
+                    const uint32_t vi = d.indices[job->first_index + (size_t)local * 3 + v]; // range-checked when emitted
+                    const rayca_vertex& vx = d.vertices[job->first_vertex + vi];
+                    const V3 n = m3_apply(job->normal_matrix, V3{vx.normal[0], vx.normal[1], vx.normal[2]});
+                    const V3 tg = m3_apply(job->tangent_matrix, V3{vx.tangent[0], vx.tangent[1], vx.tangent[2]});
+                    const V3 bt = m3_apply(job->tangent_matrix, V3{vx.bitangent[0], vx.bitangent[1], vx.bitangent[2]});
+                    q[v] = make_float4(vx.color[0], vx.color[1], vx.color[2], vx.color[3]);
+                    q[3 + v] = make_float4(n.x, n.y, n.z, vx.uv[0]);
+                    q[6 + v] = make_float4(tg.x, tg.y, tg.z, vx.uv[1]);
+                    q[9 + v] = make_float4(bt.x, bt.y, bt.z, v == 0 ? __builtin_bit_cast(float, job->material) : 0.0f);
+                }
+                continue;
+            }
+            const HostAttr& a = b.attrs[t.src]; // quad-light triangle
+            for (int v = 0; v < 3; ++v) {
+                q[v] = make_float4(a.color[v][0], a.color[v][1], a.color[v][2], a.color[v][3]);
+                q[3 + v] = make_float4(a.normal[v].x, a.normal[v].y, a.normal[v].z, a.uv[v][0]);
+                q[6 + v] = make_float4(a.tangent[v].x, a.tangent[v].y, a.tangent[v].z, a.uv[v][1]);
+                q[9 + v] = make_float4(a.bitangent[v].x, a.bitangent[v].y, a.bitangent[v].z,
+                                       v == 0 ? __builtin_bit_cast(float, a.material) : 0.0f);
+            }
+        }
+    }
+}
+
 int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::string& err, bool fast_tree,
-                     const BlasBuilder* blas_builder, bool gather_texels) {
+                     const BlasBuilder* blas_builder, bool gather_texels, bool defer_attrs) {
     PhaseTimer phase;
     Flatten f(d, out);
     f.run();
@@ -384,9 +455,7 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
         struct MeshJob {
             const MeshDraw* md;
             const rayca_geometry* g;
-            uint32_t material;
             size_t base;
-            M3 tangent_matrix, normal_matrix;
         };
         struct Chunk { uint32_t job, first, count; };
         std::vector<MeshJob> jobs;
@@ -423,13 +492,24 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
                 if (g.kind != RAYCA_GEOMETRY_TRIANGLE_MESH) { err = "unknown geometry kind"; return RAYCA_E_INVALID_ARG; }
                 const uint32_t ntri = g.index_count / 3;
                 const uint32_t job = (uint32_t)jobs.size();
-                jobs.push_back({&md, &g, material, total_prims, tangent_matrix, normal_matrix});
+                jobs.push_back({&md, &g, total_prims});
+                HostMeshJob rec;
+                rec.base = total_prims;
+                rec.ntri = ntri;
+                rec.first_index = g.first_index;
+                rec.first_vertex = g.first_vertex;
+                rec.material = material;
+                rec.tangent_matrix = tangent_matrix;
+                rec.normal_matrix = normal_matrix;
+                blas.jobs.push_back(rec);
                 for (uint32_t first = 0; first < ntri; first += 4096) chunks.push_back({job, first, std::min(4096u, ntri - first)});
                 total_prims += ntri;
             }
         }
+        blas.tris.reserve(total_prims + 2 * f.quad_draws[mi].size()); // the quad-light triangles are appended below
+        blas.attrs.reserve(total_prims + 2 * f.quad_draws[mi].size());
         blas.tris.resize(total_prims);
-        blas.attrs.resize(total_prims);
+        blas.attrs.resize(total_prims); // default-initialised (PodVector): mesh triangles never touch their slots
         for (const SphereSlot& ss : sphere_slots) {
             const HostSphere& sp = blas.spheres[ss.sphere - 1];
             HostTri ht{};
@@ -455,22 +535,14 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
             const MeshDraw& md = *job.md;
             for (uint32_t t = ch.first; t < ch.first + ch.count; ++t) {
                 HostTri& ht = blas.tris[job.base + t];
-                HostAttr& ha = blas.attrs[job.base + t];
                 V3 mv[3];
-                for (int k = 0; k < 3; ++k) {
+                for (int k = 0; k < 3; ++k) { // the shading attributes of the vertices are read by pack_tri_attrs
                     uint32_t vi = d.indices[g.first_index + (size_t)t * 3 + k];
                     if (vi >= g.vertex_count) { bad = 1; vi = 0; }
                     const rayca_vertex& v = d.vertices[g.first_vertex + vi];
                     mv[k] = V3{v.pos[0], v.pos[1], v.pos[2]};
-                    std::memcpy(ha.color[k], v.color, 16);
-                    ha.normal[k] = m3_apply(job.normal_matrix, V3{v.normal[0], v.normal[1], v.normal[2]});
-                    ha.tangent[k] = m3_apply(job.tangent_matrix, V3{v.tangent[0], v.tangent[1], v.tangent[2]});
-                    ha.bitangent[k] = m3_apply(job.tangent_matrix, V3{v.bitangent[0], v.bitangent[1], v.bitangent[2]});
-                    ha.uv[k][0] = v.uv[0];
-                    ha.uv[k][1] = v.uv[1];
                     ht.v[k] = trs_point(md.world, mv[k]); // Triangle::get_vertex (triangle.rs:67-69)
                 }
-                ha.material = job.material;
                 // Triangle::new centroid quirk (triangle.rs:59-62) then `trs * Vec3` (trs.rs:253-262)
                 V3 c = ((mv[0] + mv[1]) + mv[2]) * 0.3333f;
                 ht.centroid = trs_vec(md.world, c);
@@ -622,44 +694,21 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
 #pragma omp parallel for schedule(static) if (b.tris.size() > 8192)
         for (int64_t k = 0; k < (int64_t)b.tris.size(); ++k) {
             const HostTri& t = b.tris[(size_t)k];
-            const HostAttr& a = b.attrs[t.src];
             size_t gi = (size_t)po + (size_t)k;
             float4* p = &out.tri_pos[gi * 3];
             if (t.sphere) {
-                // sphere prim: attr record = {inverse Mat4 rows 0..2 | normal matrix rows (w: centre) | world t, q, s |
-                // material}; what primitive.rs:183-190 derives from the node TRS on every shaded hit
                 const HostSphere& sp = b.spheres[t.sphere - 1];
                 p[0] = make_float4(sp.center.x, sp.center.y, sp.center.z, __builtin_bit_cast(float, t.src));
-                p[1] = make_float4(sp.radius2, 0.0f, 0.0f, __builtin_bit_cast(float, a.material));
+                p[1] = make_float4(sp.radius2, 0.0f, 0.0f, __builtin_bit_cast(float, sp.material));
                 p[2] = make_float4(0.0f, 0.0f, 0.0f, __builtin_bit_cast(float, (uint32_t)bi));
-                float4* q = &out.tri_attr[gi * 12];
-                M4 inv = m4_from_inversed(sp.world);
-                M3 nm = normal_matrix_of(sp.world);
-                const float cc[3] = {sp.center.x, sp.center.y, sp.center.z};
-                for (int r = 0; r < 3; ++r) {
-                    q[r] = make_float4(inv.m[r][0], inv.m[r][1], inv.m[r][2], inv.m[r][3]);
-                    q[3 + r] = make_float4(nm.m[r][0], nm.m[r][1], nm.m[r][2], cc[r]);
-                }
-                q[6] = make_float4(sp.world.t.x, sp.world.t.y, sp.world.t.z, 0.0f);
-                q[7] = make_float4(sp.world.q.x, sp.world.q.y, sp.world.q.z, sp.world.q.w);
-                q[8] = make_float4(sp.world.s.x, sp.world.s.y, sp.world.s.z, 0.0f);
-                q[9] = make_float4(0.0f, 0.0f, 0.0f, __builtin_bit_cast(float, a.material));
-                q[10] = q[11] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                 continue;
             }
             p[0] = make_float4(t.v[0].x, t.v[0].y, t.v[0].z, __builtin_bit_cast(float, t.src));
-            p[1] = make_float4(t.v[1].x, t.v[1].y, t.v[1].z, __builtin_bit_cast(float, a.material));
+            p[1] = make_float4(t.v[1].x, t.v[1].y, t.v[1].z, __builtin_bit_cast(float, material_of(b, t.src)));
             p[2] = make_float4(t.v[2].x, t.v[2].y, t.v[2].z, __builtin_bit_cast(float, (uint32_t)bi));
-            float4* q = &out.tri_attr[gi * 12];
-            for (int v = 0; v < 3; ++v) {
-                q[v] = make_float4(a.color[v][0], a.color[v][1], a.color[v][2], a.color[v][3]);
-                q[3 + v] = make_float4(a.normal[v].x, a.normal[v].y, a.normal[v].z, a.uv[v][0]);
-                q[6 + v] = make_float4(a.tangent[v].x, a.tangent[v].y, a.tangent[v].z, a.uv[v][1]);
-                q[9 + v] = make_float4(a.bitangent[v].x, a.bitangent[v].y, a.bitangent[v].z,
-                                       v == 0 ? __builtin_bit_cast(float, a.material) : 0.0f);
-            }
         }
     }
+    if (!defer_attrs) pack_tri_attrs(d, out);
 
     phase.lap("pack nodes/triangles/attrs");
     // ---- TLAS top pairs: every record is a (box, links) copy of its child, so the walk needs

@@ -21,7 +21,7 @@ namespace rb {
 // std::vector whose resize() leaves trivially-constructible elements uninitialised: the big per-triangle arrays
 // (tens of MB) are written once by a parallel loop right after being sized, and value-initialising them first
 // costs a sequential pass of page faults (30 of the 42 ms "emit triangles" took for 262k triangles).
-// Big blocks (>= 1 MiB) that a PodVector gives back are kept — up to 16 blocks / 1 GiB — and handed to the next PodVector
+// Big blocks (>= 1 MiB) that a PodVector gives back are kept — up to 32 blocks / 1 GiB — and handed to the next PodVector
 // that asks for that many bytes or a little more: `Draw::draw` rebuilds the scene on every call, and without this the
 // same 130 MB are mmap'ed, page-faulted in and munmap'ed per draw (measured: 2 ms to free + the faults inside emit / pack).
 void* pod_block_acquire(size_t bytes);            // host_scene.cpp; nullptr: nothing suitable cached
@@ -80,9 +80,25 @@ struct HostNode {
     uint32_t offset, count; // count != 0: leaf over [offset, offset+count); else children offset, offset+1
 };
 
+struct M3 { // rayca-math/src/mat3.rs, row-major m[i][j]
+    float m[3][3];
+};
+
+// One triangle-mesh primitive of a BLAS: the triangles [base, base + ntri) of the emit order.  Their shading attributes
+// are not materialised per triangle: pack_tri_attrs computes them from the caller's vertices (which must still be
+// alive) straight into HostScene::tri_attr, in BLAS order.
+struct HostMeshJob {
+    size_t base = 0;
+    uint32_t ntri = 0;
+    uint32_t first_index = 0, first_vertex = 0;
+    uint32_t material = 0;
+    M3 tangent_matrix{}, normal_matrix{};
+};
+
 struct HostBlas {
     PodVector<HostTri> tris;     // reordered in place by the build
-    PodVector<HostAttr> attrs;   // indexed by HostTri::src
+    PodVector<HostAttr> attrs;   // indexed by HostTri::src; filled for spheres and quad-light triangles only
+    std::vector<HostMeshJob> jobs; // ascending base
     std::vector<HostSphere> spheres;
     std::vector<HostNode> nodes; // node 0 root, node 1 unused (blas.rs:250-256)
     uint32_t model = 0;
@@ -119,9 +135,13 @@ struct HostScene {
 // `fast_tree` = false leaves the performance tree to the device builder (gpu_fast_build.cu).
 // `blas_builder`, when given, replaces build_blas (the device builder of gpu_fast_build.cu): it returns true when
 // it built the BLAS and false to leave it to the host builder.
+// `defer_attrs`: HostScene::tri_attr is sized but not filled; the caller runs pack_tri_attrs itself (the device path
+// does, while the performance tree is being built on the GPU).
 using BlasBuilder = std::function<bool(HostBlas&, uint32_t max_depth)>;
 int build_host_scene(const rayca_scene_desc& desc, bool bvh, HostScene& out, std::string& err, bool fast_tree = true,
-                     const BlasBuilder* blas_builder = nullptr, bool gather_texels = true);
+                     const BlasBuilder* blas_builder = nullptr, bool gather_texels = true, bool defer_attrs = false);
+// Fills HostScene::tri_attr (12 float4 per primitive, BLAS order) from `desc`'s vertices and HostBlas::{tris, jobs, attrs}.
+void pack_tri_attrs(const rayca_scene_desc& desc, HostScene& scene);
 
 // BLAS build: top-down SAH over 63 planes x 3 axes with the reference's tie-breaking
 // (bvh/blas.rs:64-127,245-316), evaluated through per-plane bins so that one pass over the

@@ -389,8 +389,41 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         if (brc != RAYCA_OK) cudaGetLastError();
         return brc == RAYCA_OK;
     };
+    // Texels: the caller's images are pageable as a rule (decoded files), and a pageable cudaMemcpy blocks the calling
+    // thread at about 12 GB/s (1.3 of 15 ms of the atrium's draw).  They are gathered into one recycled page-locked block
+    // by all host threads instead and leave in ONE asynchronous copy on the copy stream, which runs under everything
+    // that follows.  (A helper thread doing the pageable copies was tried first: with the OpenMP workers spinning
+    // between the parallel loops of the build, every extra thread cost milliseconds of jitter on a 16-core host.)
+    // Offsets as build_host_scene lays the images out (checked below).
+    std::vector<size_t> texel_offset(desc->image_count, 0);
+    size_t texel_bytes = 0;
+    for (uint32_t i = 0; i < desc->image_count; ++i) {
+        const rayca_image& im = desc->images[i];
+        const size_t bpp = im.color_type == RAYCA_COLOR_RGB8 ? 3 : (im.color_type == RAYCA_COLOR_RGBA8 ? 4 : 16);
+        texel_offset[i] = (texel_bytes + 15) & ~size_t(15);
+        texel_bytes = texel_offset[i] + (size_t)im.width * im.height * bpp;
+    }
+    PodVector<unsigned char> texel_stage(texel_bytes);
+    {
+        struct Piece { const unsigned char* src; size_t dst, bytes; };
+        std::vector<Piece> pieces; // 1 MiB pieces so that one large image is spread over the threads too
+        for (uint32_t i = 0; i < desc->image_count; ++i) {
+            const rayca_image& im = desc->images[i];
+            const size_t bpp = im.color_type == RAYCA_COLOR_RGB8 ? 3 : (im.color_type == RAYCA_COLOR_RGBA8 ? 4 : 16);
+            const size_t bytes = (size_t)im.width * im.height * bpp;
+            for (size_t o = 0; o < bytes; o += size_t(1) << 20)
+                pieces.push_back({static_cast<const unsigned char*>(im.data) + o, texel_offset[i] + o, std::min(bytes - o, size_t(1) << 20)});
+        }
+#pragma omp parallel for schedule(dynamic, 1) if (texel_bytes > (size_t(1) << 20))
+        for (int64_t k = 0; k < (int64_t)pieces.size(); ++k) std::memcpy(texel_stage.data() + pieces[(size_t)k].dst, pieces[(size_t)k].src, pieces[(size_t)k].bytes);
+    }
+    s->nbytes[slot_of(&s->d_texels, s)] = std::max<size_t>(texel_bytes, 16);
+    if (int urc = upload(&s->d_texels, texel_stage, ctx->copy_stream); urc != RAYCA_OK) {
+        rayca_cuda_scene_destroy(s);
+        return urc;
+    }
     try {
-        rc = build_host_scene(*desc, bvh != 0, s->host, err, host_fast_tree, &device_blas, /*gather_texels=*/false);
+        rc = build_host_scene(*desc, bvh != 0, s->host, err, host_fast_tree, &device_blas, /*gather_texels=*/false, /*defer_attrs=*/true);
     } catch (const std::bad_alloc&) {
         rayca_cuda_scene_destroy(s);
         return fail(RAYCA_E_OOM, "host allocation while building the scene");
@@ -428,34 +461,33 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     if (timing) std::fprintf(stderr, "[rayca] %-28s %8.2f ms\n", "build_host_scene (total)", t1 - t0);
     UP(d_nodes, nodes);
     UP(d_tri_pos, tri_pos);
-    UP(d_tri_attr, tri_attr);
     UP(d_materials, materials);
     UP(d_images, images);
-    {   // texels: every image goes straight from the caller's memory to its place in the device buffer (the gather into
-        // one host vector first cost 4 ms of the atrium's draw)
-        s->nbytes[slot_of(&s->d_texels, s)] = std::max<size_t>(h.texel_bytes, 16);
-        cudaError_t ce = cudaMallocAsync(&s->d_texels, std::max<size_t>(h.texel_bytes, 16), ctx->render_stream);
-        for (uint32_t i = 0; i < desc->image_count && ce == cudaSuccess; ++i) {
-            const rayca_image& im = desc->images[i];
-            const size_t bpp = im.color_type == RAYCA_COLOR_RGB8 ? 3 : (im.color_type == RAYCA_COLOR_RGBA8 ? 4 : 16);
-            const size_t bytes = (size_t)im.width * im.height * bpp;
-            if (bytes) ce = cudaMemcpyAsync((unsigned char*)s->d_texels + h.images[i].offset, im.data, bytes, cudaMemcpyHostToDevice, ctx->render_stream);
-        }
-        if (ce != cudaSuccess) {
+    for (uint32_t i = 0; i < desc->image_count; ++i) // the helper thread's layout must be the one the image records carry
+        if (h.images[i].offset != texel_offset[i] || h.texel_bytes != texel_bytes) {
             rayca_cuda_scene_destroy(s);
-            return fail(ce == cudaErrorMemoryAllocation ? RAYCA_E_OOM : RAYCA_E_CUDA, std::string("texel upload: ") + cudaGetErrorString(ce));
+            return fail(RAYCA_E_CUDA, "texel layout mismatch");
         }
-    }
     UP(d_lights, lights);
     UP(d_blas_prim_offset, blas_prim_offset);
     lap("uploads (8 arrays)");
     if (host_fast_tree) {
+        pack_tri_attrs(*desc, h);
+        UP(d_tri_attr, tri_attr);
         UP(d_fast_nodes, fast_nodes);
         UP(d_fast_tri, fast_tri);
         s->fast_node_count = h.fast_nodes.size();
     } else {
+        // the shading attributes (the largest array) go out on the copy stream and travel while the tree is being built
+        pack_tri_attrs(*desc, h);
+        s->nbytes[slot_of(&s->d_tri_attr, s)] = std::max<size_t>(h.tri_attr.size() * sizeof(h.tri_attr[0]), 16);
+        if (int urc = upload(&s->d_tri_attr, h.tri_attr, ctx->copy_stream); urc != RAYCA_OK) {
+            rayca_cuda_scene_destroy(s);
+            return urc;
+        }
+        lap("pack + send attributes");
         FastTreeDevice ft;
-        rc = build_fast_tree_device(h, (const float4*)s->d_tri_pos, ctx->render_stream, ft, err);
+        rc = build_fast_tree_device(h, (const float4*)s->d_tri_pos, ctx->render_stream, ft, err, s->d_nodes);
         if (rc != RAYCA_OK) {
             rayca_cuda_scene_destroy(s);
             return fail(rc, err);
@@ -473,6 +505,7 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
                          ft.build_ms, ft.levels, ft.small_subtrees, ft.depth);
     }
     lap("performance tree (call)");
+
     // The walk's stack holds kStackSize entries and saturates beyond (trace.cuh): a performance tree deeper than that
     // would drop subtrees silently, so such a scene is refused here, never mis-rendered.  With 16 SAH bins a level
     // narrows the centroid range 16-fold and the binned builder cannot get near the limit on f32 input; the environment
@@ -528,6 +561,10 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     if (cudaError_t ce = cudaStreamSynchronize(ctx->render_stream); ce != cudaSuccess) {
         rayca_cuda_scene_destroy(s);
         return fail(RAYCA_E_CUDA, std::string("scene_create: ") + cudaGetErrorString(ce));
+    }
+    if (cudaError_t ce = cudaStreamSynchronize(ctx->copy_stream); ce != cudaSuccess) { // texels and shading attributes went this way
+        rayca_cuda_scene_destroy(s);
+        return fail(RAYCA_E_CUDA, std::string("scene_create (copy stream): ") + cudaGetErrorString(ce));
     }
     std::vector<unsigned char>().swap(h.texels);
     PodVector<float4>().swap(h.tri_attr);
