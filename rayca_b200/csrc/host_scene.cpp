@@ -15,6 +15,7 @@
 #include <cstring>
 #include <functional>
 #include <mutex>
+#include <unistd.h>
 
 namespace rb {
 namespace {
@@ -230,7 +231,19 @@ std::vector<PodBlock> g_pod_blocks; // cached (free) blocks
 std::vector<PodBlock> g_pod_lent;   // blocks handed out again: their real size and whether they are page-locked
 size_t g_pod_bytes = 0;
 bool g_pod_pin = false;
-constexpr size_t kPodMaxBlocks = 32, kPodMaxBytes = size_t(1) << 30;
+constexpr size_t kPodMaxBlocks = 32;
+// Cache size: a quarter of the physical memory, at most 6 GiB (a 10 M-triangle scene recycles ~3 GiB of host vectors per
+// draw; with the old 1 GiB cap they were mmap'ed, page-faulted and unmapped on every call: 0.6 s of a 1.3 s draw);
+// RAYCA_HOST_CACHE_MB overrides.
+size_t pod_max_bytes() {
+    static const size_t cap = [] {
+        if (const char* e = std::getenv("RAYCA_HOST_CACHE_MB")) return (size_t)std::max(0L, std::atol(e)) << 20;
+        const long pages = sysconf(_SC_PHYS_PAGES), page = sysconf(_SC_PAGE_SIZE);
+        const size_t phys = pages > 0 && page > 0 ? (size_t)pages * (size_t)page : (size_t(4) << 30);
+        return std::min(phys / 4, size_t(6) << 30);
+    }();
+    return cap;
+}
 } // namespace
 
 // Called once a CUDA context exists (rayca_cuda_init): from then on a block that enters the cache is page-locked
@@ -265,7 +278,7 @@ bool pod_block_release(void* p, size_t bytes) {
             g_pod_lent.erase(g_pod_lent.begin() + (long)i);
             break;
         }
-    if (g_pod_blocks.size() >= kPodMaxBlocks || g_pod_bytes + blk.bytes > kPodMaxBytes) {
+    if (g_pod_blocks.size() >= kPodMaxBlocks || g_pod_bytes + blk.bytes > pod_max_bytes()) {
         if (blk.pinned) cudaHostUnregister(blk.p); // the caller frees it
         return false;
     }
@@ -311,13 +324,21 @@ inline uint32_t material_of(const HostBlas& b, uint32_t src) {
 } // namespace
 
 void pack_tri_attrs(const rayca_scene_desc& d, HostScene& out) {
+    const size_t total = out.blas_prim_offset.back();
+    out.tri_attr.resize(total * 12);
+    pack_tri_attrs_range(d, out, 0, total, out.tri_attr.data());
+}
+
+void pack_tri_attrs_range(const rayca_scene_desc& d, const HostScene& out, size_t g0, size_t g1, float4* dst) {
     for (size_t bi = 0; bi < out.blas.size(); ++bi) {
         const HostBlas& b = out.blas[bi];
-        const uint32_t po = out.blas_prim_offset[bi];
-#pragma omp parallel for schedule(static) if (b.tris.size() > 8192)
-        for (int64_t k = 0; k < (int64_t)b.tris.size(); ++k) {
-            const HostTri& t = b.tris[(size_t)k];
-            float4* q = &out.tri_attr[((size_t)po + (size_t)k) * 12];
+        const size_t po = out.blas_prim_offset[bi];
+        const size_t lo = std::max(g0, po), hi = std::min(g1, po + b.tris.size());
+        if (lo >= hi) continue;
+#pragma omp parallel for schedule(static) if (hi - lo > 8192)
+        for (int64_t g = (int64_t)lo; g < (int64_t)hi; ++g) {
+            const HostTri& t = b.tris[(size_t)g - po];
+            float4* q = dst + ((size_t)g - g0) * 12;
             if (t.sphere) {
                 // sphere prim: attr record = {inverse Mat4 rows 0..2 | normal matrix rows (w: centre) | world t, q, s |
                 // material}; what primitive.rs:183-190 derives from the node TRS on every shaded hit
@@ -675,8 +696,7 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
     }
     if (total_tris >= 0xFFFFFFF0ull || total_nodes >= 0xFFFFFFF0ull) { err = "scene too large"; return RAYCA_E_UNSUPPORTED; }
     out.nodes.resize(total_nodes);
-    out.tri_pos.resize(total_tris * 3);
-    out.tri_attr.resize(total_tris * 12);
+    out.tri_pos.resize(total_tris * 3); // tri_attr: sized by pack_tri_attrs (the device path streams it in pieces instead)
     uint32_t max_blas_depth = 0;
     for (size_t bi = 0; bi < out.blas.size(); ++bi) {
         const HostBlas& b = out.blas[bi];

@@ -21,7 +21,7 @@ namespace rb {
 // std::vector whose resize() leaves trivially-constructible elements uninitialised: the big per-triangle arrays
 // (tens of MB) are written once by a parallel loop right after being sized, and value-initialising them first
 // costs a sequential pass of page faults (30 of the 42 ms "emit triangles" took for 262k triangles).
-// Big blocks (>= 1 MiB) that a PodVector gives back are kept — up to 32 blocks / 1 GiB — and handed to the next PodVector
+// Big blocks (>= 1 MiB) that a PodVector gives back are kept — up to 32 blocks / a quarter of the physical memory, at most 6 GiB — and handed to the next PodVector
 // that asks for that many bytes or a little more: `Draw::draw` rebuilds the scene on every call, and without this the
 // same 130 MB are mmap'ed, page-faulted in and munmap'ed per draw (measured: 2 ms to free + the faults inside emit / pack).
 void* pod_block_acquire(size_t bytes);            // host_scene.cpp; nullptr: nothing suitable cached
@@ -142,6 +142,9 @@ int build_host_scene(const rayca_scene_desc& desc, bool bvh, HostScene& out, std
                      const BlasBuilder* blas_builder = nullptr, bool gather_texels = true, bool defer_attrs = false);
 // Fills HostScene::tri_attr (12 float4 per primitive, BLAS order) from `desc`'s vertices and HostBlas::{tris, jobs, attrs}.
 void pack_tri_attrs(const rayca_scene_desc& desc, HostScene& scene);
+// ... the primitives [g0, g1) of the packed (reference-global) order into `dst` (12 float4 each): the device path packs
+// and uploads the array piece by piece through a small page-locked ring instead of materialising it on the host
+void pack_tri_attrs_range(const rayca_scene_desc& desc, const HostScene& scene, size_t g0, size_t g1, float4* dst);
 
 // BLAS build: top-down SAH over 63 planes x 3 axes with the reference's tie-breaking
 // (bvh/blas.rs:64-127,245-316), evaluated through per-plane bins so that one pass over the

@@ -471,6 +471,8 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     UP(d_lights, lights);
     UP(d_blas_prim_offset, blas_prim_offset);
     lap("uploads (8 arrays)");
+    constexpr int kRing = 3;
+    PodVector<float4> ring[kRing]; // page-locked staging of the shading attributes (below); read by copies until the final sync
     if (host_fast_tree) {
         pack_tri_attrs(*desc, h);
         UP(d_tri_attr, tri_attr);
@@ -478,12 +480,39 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         UP(d_fast_tri, fast_tri);
         s->fast_node_count = h.fast_nodes.size();
     } else {
-        // the shading attributes (the largest array) go out on the copy stream and travel while the tree is being built
-        pack_tri_attrs(*desc, h);
-        s->nbytes[slot_of(&s->d_tri_attr, s)] = std::max<size_t>(h.tri_attr.size() * sizeof(h.tri_attr[0]), 16);
-        if (int urc = upload(&s->d_tri_attr, h.tri_attr, ctx->copy_stream); urc != RAYCA_OK) {
-            rayca_cuda_scene_destroy(s);
-            return urc;
+        // The shading attributes (the largest array: 192 bytes per primitive) are never materialised on the host: they
+        // are packed piece by piece into a ring of three page-locked buffers and leave on the copy stream, the copies
+        // running under the packing of the next piece and under the tree build that follows.
+        {
+            const size_t total = h.blas_prim_offset.back();
+            const size_t attr_bytes = std::max<size_t>(total * 12 * sizeof(float4), 16);
+            s->nbytes[slot_of(&s->d_tri_attr, s)] = attr_bytes;
+            cudaError_t ce = cudaMallocAsync(&s->d_tri_attr, attr_bytes, ctx->copy_stream);
+            constexpr size_t kPiece = 65536; // primitives per piece: 12 MiB
+            cudaEvent_t sent[kRing] = {nullptr, nullptr, nullptr};
+            for (int k = 0; k < kRing && ce == cudaSuccess; ++k) {
+                ring[k].resize(std::min(total, kPiece) * 12);
+                ce = cudaEventCreateWithFlags(&sent[k], cudaEventDisableTiming);
+            }
+            size_t piece = 0;
+            for (size_t g0 = 0; g0 < total && ce == cudaSuccess; g0 += kPiece, ++piece) {
+                const size_t g1 = std::min(total, g0 + kPiece);
+                const int slot = (int)(piece % kRing);
+                if (piece >= (size_t)kRing) ce = cudaEventSynchronize(sent[slot]); // the copy that last read this buffer
+                if (ce != cudaSuccess) break;
+                pack_tri_attrs_range(*desc, h, g0, g1, ring[slot].data());
+                ce = cudaMemcpyAsync(static_cast<float4*>(s->d_tri_attr) + g0 * 12, ring[slot].data(), (g1 - g0) * 12 * sizeof(float4),
+                                     cudaMemcpyHostToDevice, ctx->copy_stream);
+                if (ce == cudaSuccess) ce = cudaEventRecord(sent[slot], ctx->copy_stream);
+            }
+            // (the ring lives until scene_create returns, after the copy stream has been drained)
+            for (int k = 0; k < kRing; ++k)
+                if (sent[k]) cudaEventDestroy(sent[k]);
+            if (ce != cudaSuccess) {
+                cudaStreamSynchronize(ctx->copy_stream);
+                rayca_cuda_scene_destroy(s);
+                return fail(ce == cudaErrorMemoryAllocation ? RAYCA_E_OOM : RAYCA_E_CUDA, std::string("attribute upload: ") + cudaGetErrorString(ce));
+            }
         }
         lap("pack + send attributes");
         FastTreeDevice ft;
