@@ -30,6 +30,9 @@ constexpr int kStackSize = 96;
 // levels above the 32-primitive subtrees out breadth-first, so these are its top levels) are copied into shared
 // memory once per block with one bulk asynchronous copy (cp.async.bulk, 1-D TMA) and the walk reads them from there.
 // A/B only (tools/variants.py "tl*"), measured no better: profiles/r02_ab_walk_variants.txt.
+#ifndef RAYCA_PREFETCH_FAR
+#define RAYCA_PREFETCH_FAR 0 // prefetch the pushed (far) child's record into L1 (tools/variants.py "pf"): measured in profiles/r02_ab_walk_variants.txt
+#endif
 #ifndef RAYCA_TREELET
 #define RAYCA_TREELET 0
 #endif
@@ -550,6 +553,14 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
                 }
                 cur = c0;
                 push(c1, d1);
+#if RAYCA_PREFETCH_FAR
+                // the far child will be popped later unless a closer hit culls it: ask for its line now (A/B only)
+                {
+                    const char* fa = (c1 & kLeafFlag) ? reinterpret_cast<const char*>(fast_tri) + (unsigned long long)(c1 & 0x07FFFFFFu) * 64ull
+                                                      : reinterpret_cast<const char*>(fast_nodes) + (unsigned long long)c1 * 32ull;
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(fa));
+                }
+#endif
             } else if (h0) {
                 cur = c0;
             } else if (h1) {
