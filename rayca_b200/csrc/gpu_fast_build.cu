@@ -281,52 +281,70 @@ __global__ void __launch_bounds__(kBinThreads) bin_prims(const float4* __restric
         else atomicAdd(g + i, local[i]);
     }
 }
-// 32 nodes x 3 axes per block: thread (node, axis) sweeps the 31 planes of its axis, thread (node, 0) decides
+// One block per node, one warp per axis, one bin per lane: the boxes and counts left and right of the 31 planes are
+// warp scans, lane k prices plane k (between bin k-1 and bin k), a butterfly keeps the cheapest (the lowest plane on
+// equal cost, like an ascending sweep with strict `<`); thread 0 decides.  (One thread per (node, axis) sweeping the
+// bins twice in global memory took 34 us per level whatever the node count.)
+__device__ __forceinline__ BoxF fast_box_union(const BoxF& a, const BoxF& b) {
+    BoxF r;
+    for (int k = 0; k < 3; ++k) { r.mn[k] = fminf(a.mn[k], b.mn[k]); r.mx[k] = fmaxf(a.mx[k], b.mx[k]); }
+    return r;
+}
+__device__ __forceinline__ BoxF fast_box_shfl(const BoxF& a, int d, bool up) {
+    BoxF r;
+    for (int k = 0; k < 3; ++k) {
+        r.mn[k] = up ? __shfl_up_sync(0xFFFFFFFFu, a.mn[k], d) : __shfl_down_sync(0xFFFFFFFFu, a.mn[k], d);
+        r.mx[k] = up ? __shfl_up_sync(0xFFFFFFFFu, a.mx[k], d) : __shfl_down_sync(0xFFFFFFFFu, a.mx[k], d);
+    }
+    return r;
+}
 __global__ void __launch_bounds__(96) decide_splits(const WorkNode* __restrict__ work, uint32_t nodes, const NodeInfo* __restrict__ info,
                                                     const uint32_t* __restrict__ bins, uint32_t pair_base, Decision* dec,
                                                     GpuNode* records, GpuNode* root_record, uint32_t* child_big, uint32_t* child_small) {
-    __shared__ float s_cost[96];
-    __shared__ uint32_t s_bin[96], s_nl[96];
-    const uint32_t local = threadIdx.x / 3, ax = threadIdx.x % 3;
-    const uint32_t s = blockIdx.x * 32 + local;
+    static_assert(kGpuBins == 32, "one bin per lane");
+    __shared__ float s_cost[3];
+    __shared__ uint32_t s_bin[3], s_nl[3];
+    const uint32_t s = blockIdx.x, ax = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    if (s >= nodes) return;
     float best_cost = kMaxF;
     uint32_t best_bin = 0, best_nl = 0;
-    if (s < nodes && (info[s].active >> ax & 1u)) {
-        const uint32_t* w = bins + ((size_t)s * 3 + ax) * kGpuBins * kBinWords;
-        float rarea[kGpuBins];
-        uint32_t rcnt[kGpuBins];
-        BoxF acc;
-        box_reset(acc);
-        uint32_t cnt = 0;
-        for (int k = kGpuBins - 1; k >= 1; --k) {
-            const uint32_t* b = w + k * kBinWords;
-            if (b[6]) {
-                const float lo[3] = {o2f(b[0]), o2f(b[1]), o2f(b[2])}, hi[3] = {o2f(b[3]), o2f(b[4]), o2f(b[5])};
-                box_grow(acc, lo, hi);
-            }
-            cnt += b[6];
-            rarea[k] = box_area(acc);
-            rcnt[k] = cnt;
+    if (info[s].active >> ax & 1u) { // the same for the whole warp
+        const uint32_t* b = bins + (((size_t)s * 3 + ax) * kGpuBins + lane) * kBinWords;
+        BoxF mine;
+        box_reset(mine); // an empty bin is the identity of the union
+        const uint32_t cmine = b[6];
+        if (cmine) {
+            const float lo[3] = {o2f(b[0]), o2f(b[1]), o2f(b[2])}, hi[3] = {o2f(b[3]), o2f(b[4]), o2f(b[5])};
+            box_grow(mine, lo, hi);
         }
-        box_reset(acc);
-        cnt = 0;
-        for (int k = 1; k < kGpuBins; ++k) { // plane between bin k-1 and bin k
-            const uint32_t* b = w + (k - 1) * kBinWords;
-            if (b[6]) {
-                const float lo[3] = {o2f(b[0]), o2f(b[1]), o2f(b[2])}, hi[3] = {o2f(b[3]), o2f(b[4]), o2f(b[5])};
-                box_grow(acc, lo, hi);
-            }
-            cnt += b[6];
-            if (cnt == 0 || rcnt[k] == 0) continue;
-            const float cost = box_area(acc) * (float)cnt + rarea[k] * (float)rcnt[k];
-            if (cost < best_cost) { best_cost = cost; best_bin = (uint32_t)k; best_nl = cnt; }
+        BoxF up = mine, down = mine; // inclusive prefix (bins <= lane) and suffix (bins >= lane)
+        uint32_t cup = cmine, cdown = cmine;
+        for (int d = 1; d < 32; d <<= 1) {
+            const BoxF ou = fast_box_shfl(up, d, true), od = fast_box_shfl(down, d, false);
+            const uint32_t cu = __shfl_up_sync(0xFFFFFFFFu, cup, d), cd = __shfl_down_sync(0xFFFFFFFFu, cdown, d);
+            if ((int)lane >= d) { up = fast_box_union(up, ou); cup += cu; }
+            if ((int)lane + d < 32) { down = fast_box_union(down, od); cdown += cd; }
+        }
+        const BoxF left = fast_box_shfl(up, 1, true); // bins < lane
+        const uint32_t cnt = __shfl_up_sync(0xFFFFFFFFu, cup, 1);
+        if (lane >= 1 && cnt != 0 && cdown != 0) { // plane `lane`: left = bins 0..lane-1, right = bins lane..31
+            const float cost = box_area(left) * (float)cnt + box_area(down) * (float)cdown;
+            if (cost < best_cost) { best_cost = cost; best_bin = lane; best_nl = cnt; }
+        }
+        for (int d = 16; d > 0; d >>= 1) {
+            const float oc = __shfl_xor_sync(0xFFFFFFFFu, best_cost, d);
+            const uint32_t ob = __shfl_xor_sync(0xFFFFFFFFu, best_bin, d), on = __shfl_xor_sync(0xFFFFFFFFu, best_nl, d);
+            if (oc < best_cost || (oc == best_cost && ob < best_bin)) { best_cost = oc; best_bin = ob; best_nl = on; }
         }
     }
-    s_cost[threadIdx.x] = best_cost;
-    s_bin[threadIdx.x] = best_bin;
-    s_nl[threadIdx.x] = best_nl;
+    if (lane == 0) {
+        s_cost[ax] = best_cost;
+        s_bin[ax] = best_bin;
+        s_nl[ax] = best_nl;
+    }
     __syncthreads();
-    if (ax != 0 || s >= nodes) return;
+    if (threadIdx.x != 0) return;
+    constexpr uint32_t local = 0;
     int axis = -1;
     float cost = kMaxF;
     for (int a = 0; a < 3; ++a)
@@ -719,52 +737,105 @@ __device__ __forceinline__ void ref_merge_bin(BoxF& acc, const uint32_t* b) {
     const float lo[3] = {o2f(b[0]), o2f(b[1]), o2f(b[2])}, hi[3] = {o2f(b[3]), o2f(b[4]), o2f(b[5])};
     box_grow(acc, lo, hi);
 }
-// find_best_split_plane + the no-split test (blas.rs:93-127,270-276): thread (node, axis) sweeps its 63 planes
+// find_best_split_plane + the no-split test (blas.rs:93-127,270-276).  One block per node, one WARP per axis: lane l
+// holds bins 2l+1 and 2l+2, prefix / suffix unions of boxes and counts are warp scans, every lane prices its two planes
+// and a butterfly picks the cheapest (lowest plane on equal cost: the reference keeps the first minimum of its
+// ascending sweep, strict `<`).  Unions of boxes and sums of counts are exact whatever the association, so the costs
+// are the bits the sequential sweep gets.  (The first version ran one THREAD per (node, axis) over two dependent
+// sweeps of 63 bins in global memory: 65 us per level whatever the node count, 1.2 of the 2.7 ms of a 262k-triangle
+// build.)
+__device__ __forceinline__ BoxF box_union(const BoxF& a, const BoxF& b) {
+    BoxF r;
+    for (int k = 0; k < 3; ++k) { r.mn[k] = fminf(a.mn[k], b.mn[k]); r.mx[k] = fmaxf(a.mx[k], b.mx[k]); }
+    return r;
+}
+__device__ __forceinline__ BoxF box_shfl_up(const BoxF& a, int d) {
+    BoxF r;
+    for (int k = 0; k < 3; ++k) { r.mn[k] = __shfl_up_sync(0xFFFFFFFFu, a.mn[k], d); r.mx[k] = __shfl_up_sync(0xFFFFFFFFu, a.mx[k], d); }
+    return r;
+}
+__device__ __forceinline__ BoxF box_shfl_down(const BoxF& a, int d) {
+    BoxF r;
+    for (int k = 0; k < 3; ++k) { r.mn[k] = __shfl_down_sync(0xFFFFFFFFu, a.mn[k], d); r.mx[k] = __shfl_down_sync(0xFFFFFFFFu, a.mx[k], d); }
+    return r;
+}
+__device__ __forceinline__ void ref_load_bin(const uint32_t* w, int k, BoxF& b, uint32_t& c) {
+    const uint32_t* p = w + k * kBinWords;
+    c = p[6];
+    box_reset(b); // an empty bin is the identity of the union (the sequential sweep skips it)
+    if (c) ref_merge_bin(b, p);
+}
+__device__ __forceinline__ float ref_candidate_cost(const BoxF& left, uint32_t nl, const BoxF& right, uint32_t nr) {
+    BoxF l, r;
+    ref_origin(l); // candidate boxes start at the origin (AABB::default(), blas.rs:66-67)
+    ref_origin(r);
+    l = box_union(l, left);
+    r = box_union(r, right);
+    float cost = (float)(int)nl * ref_area(l) + (float)(int)nr * ref_area(r); // evaluate_sah (blas.rs:83-88)
+    if (!(cost > 0.0f)) cost = kMaxF;
+    return cost;
+}
 __global__ void __launch_bounds__(96) ref_decide(const uint32_t* __restrict__ active_ids, uint32_t count, const RefNode* __restrict__ nodes,
                                                  const RefInfo* __restrict__ info, const uint32_t* __restrict__ bins, RefDecision* dec,
                                                  uint32_t* split_flags) {
-    __shared__ float s_cost[96];
-    __shared__ uint32_t s_plane[96], s_nl[96];
-    const uint32_t local = threadIdx.x / 3, ax = threadIdx.x % 3;
-    const uint32_t s = blockIdx.x * 32 + local;
+    __shared__ float s_cost[3];
+    __shared__ uint32_t s_plane[3], s_nl[3];
+    const uint32_t s = blockIdx.x, ax = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    if (s >= count) return;
     float best_cost = kMaxF;
     uint32_t best_plane = 0, best_nl = 0;
-    if (s < count && (info[s].active >> ax & 1u)) {
+    if (info[s].active >> ax & 1u) { // the same for the whole warp
         const uint32_t* w = bins + ((size_t)s * 3 + ax) * kRefBins * kBinWords;
-        float rarea[kRefPlanes];
-        uint32_t rcount[kRefPlanes];
-        BoxF acc;
-        ref_origin(acc);
-        uint32_t cnt = 0;
-        for (int i = kRefPlanes - 1; i >= 1; --i) { // right(i) = origin U bins k > i
-            const uint32_t* b = w + (i + 1) * kBinWords;
-            if (b[6]) ref_merge_bin(acc, b);
-            cnt += b[6];
-            rarea[i] = ref_area(acc);
-            rcount[i] = cnt;
+        BoxF b1, b2;
+        uint32_t c1, c2;
+        ref_load_bin(w, 2 * (int)lane + 1, b1, c1);
+        ref_load_bin(w, 2 * (int)lane + 2, b2, c2);
+        const BoxF both = box_union(b1, b2);
+        const uint32_t cboth = c1 + c2;
+        // bins of the lanes below (exclusive prefix) and above (exclusive suffix)
+        BoxF up = both, down = both;
+        uint32_t cup = cboth, cdown = cboth;
+        for (int d = 1; d < 32; d <<= 1) {
+            const BoxF ou = box_shfl_up(up, d), od = box_shfl_down(down, d);
+            const uint32_t cu = __shfl_up_sync(0xFFFFFFFFu, cup, d), cd = __shfl_down_sync(0xFFFFFFFFu, cdown, d);
+            if ((int)lane >= d) { up = box_union(up, ou); cup += cu; }
+            if ((int)lane + d < 32) { down = box_union(down, od); cdown += cd; }
         }
-        ref_origin(acc);
-        cnt = 0;
-        for (int i = 1; i < kRefPlanes; ++i) {
-            const uint32_t* b = w + i * kBinWords;
-            if (b[6]) ref_merge_bin(acc, b);
-            cnt += b[6];
-            float cost = (float)(int)cnt * ref_area(acc) + (float)(int)rcount[i] * rarea[i]; // evaluate_sah (blas.rs:83-88)
-            if (!(cost > 0.0f)) cost = kMaxF;
-            if (cost < best_cost) { best_cost = cost; best_plane = (uint32_t)i; best_nl = cnt; }
+        BoxF below = box_shfl_up(up, 1), above = box_shfl_down(down, 1);
+        uint32_t cbelow = __shfl_up_sync(0xFFFFFFFFu, cup, 1), cabove = __shfl_down_sync(0xFFFFFFFFu, cdown, 1);
+        if (lane == 0) { box_reset(below); cbelow = 0; }
+        if (lane == 31) { box_reset(above); cabove = 0; }
+        // plane i: left = bins 1..i, right = bins i+1..64
+        // i = 2l+1: left = below U b1, right = b2 U above;  i = 2l+2 (l < 31): left = below U both, right = above
+        {
+            const uint32_t nl = cbelow + c1;
+            const float cost = ref_candidate_cost(box_union(below, b1), nl, box_union(b2, above), c2 + cabove);
+            if (cost < best_cost) { best_cost = cost; best_plane = 2 * lane + 1; best_nl = nl; }
+        }
+        if (lane < 31) {
+            const uint32_t nl = cbelow + cboth;
+            const float cost = ref_candidate_cost(box_union(below, both), nl, above, cabove);
+            if (cost < best_cost) { best_cost = cost; best_plane = 2 * lane + 2; best_nl = nl; }
+        }
+        for (int d = 16; d > 0; d >>= 1) { // cheapest plane, the lowest one on equal cost
+            const float oc = __shfl_xor_sync(0xFFFFFFFFu, best_cost, d);
+            const uint32_t op = __shfl_xor_sync(0xFFFFFFFFu, best_plane, d), on = __shfl_xor_sync(0xFFFFFFFFu, best_nl, d);
+            if (oc < best_cost || (oc == best_cost && op < best_plane)) { best_cost = oc; best_plane = op; best_nl = on; }
         }
     }
-    s_cost[threadIdx.x] = best_cost;
-    s_plane[threadIdx.x] = best_plane;
-    s_nl[threadIdx.x] = best_nl;
+    if (lane == 0) {
+        s_cost[ax] = best_cost;
+        s_plane[ax] = best_plane;
+        s_nl[ax] = best_nl;
+    }
     __syncthreads();
-    if (ax != 0 || s >= count) return;
+    if (threadIdx.x != 0) return;
     float cost = kMaxF;
     int axis = 0;
     uint32_t plane = 0, nl = 0;
     bool any = false;
     for (int a = 0; a < 3; ++a)
-        if (s_cost[local * 3 + a] < cost) { cost = s_cost[local * 3 + a]; axis = a; plane = s_plane[local * 3 + a]; nl = s_nl[local * 3 + a]; any = true; }
+        if (s_cost[a] < cost) { cost = s_cost[a]; axis = a; plane = s_plane[a]; nl = s_nl[a]; any = true; }
     const RefNode& nd = nodes[active_ids[s]];
     const RefInfo& ri = info[s];
     BoxF nb;
@@ -1130,7 +1201,7 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
         prepare_nodes<<<blocks_for(nbig, T), T, 0, st>>>(d_acc[cur], nbig, d_info);
         init_bins<<<blocks_for((size_t)nbig * kNodeBinWords, T), T, 0, st>>>(d_bins, nbig);
         bin_prims<<<blocks_for(N, kBinThreads), kBinThreads, 0, st>>>(d_mn, d_mx, d_order[cur], d_node_of[cur], N, d_info, d_bins);
-        decide_splits<<<blocks_for(nbig, 32), 96, 0, st>>>(d_work[cur], nbig, d_info, d_bins, pair_base, d_dec, d_records, d_root,
+        decide_splits<<<nbig, 96, 0, st>>>(d_work[cur], nbig, d_info, d_bins, pair_base, d_dec, d_records, d_root,
                                                            d_child_big, d_child_small);
         exclusive_scan(d_child_big, nbig * 2, d_big_index, d_partial, st);
         exclusive_scan(d_child_small, nbig * 2, d_small_index, d_partial, st);
@@ -1288,7 +1359,7 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
         const int nxt = cur ^ 1;
         ref_init_bins<<<blocks_for((size_t)count * kRefNodeBinWords, T), T, 0, st>>>(d_bins, count);
         ref_bin_prims<<<blocks_for(N, kBinThreads), kBinThreads, 0, st>>>(d_mn, d_mx, d_cen, d_order[cur], d_node_of[cur], N, d_info, d_bins);
-        ref_decide<<<blocks_for(count, 32), 96, 0, st>>>(d_active[cur], count, d_nodes, d_info, d_bins, d_dec, d_split);
+        ref_decide<<<count, 96, 0, st>>>(d_active[cur], count, d_nodes, d_info, d_bins, d_dec, d_split);
         ref_flags<<<blocks_for(N, T), T, 0, st>>>(d_cen, d_order[cur], d_node_of[cur], N, d_dec, d_flags);
         exclusive_scan(d_flags, N, d_scan, d_partial, st);
         ref_counts<<<blocks_for(count, T), T, 0, st>>>(d_active[cur], count, d_nodes, d_scan, d_dec, d_split);
