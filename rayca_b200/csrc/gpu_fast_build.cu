@@ -123,7 +123,23 @@ __global__ void __launch_bounds__(kScanBlock) scan_final(const uint32_t* in, uin
     if (i < n) out[i] = partial[blockIdx.x] + ex;
     if (i == 0) out[n] = partial[gridDim.x];
 }
+// short inputs (the per-node arrays of a level): one block walks them in chunks of 1024 — one launch instead of three
+__global__ void __launch_bounds__(kScanBlock) scan_small(const uint32_t* in, uint32_t n, uint32_t* out) {
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < n; base += kScanBlock) {
+        const uint32_t i = base + threadIdx.x;
+        uint32_t total;
+        const uint32_t ex = block_exclusive(i < n ? in[i] : 0u, &total);
+        if (i < n) out[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) out[n] = carry;
+}
 void exclusive_scan(const uint32_t* in, uint32_t n, uint32_t* out, uint32_t* partial, cudaStream_t st) {
+    if (n <= 16u * kScanBlock) {
+        scan_small<<<1, kScanBlock, 0, st>>>(in, n, out);
+        return;
+    }
     const uint32_t blocks = (n + kScanBlock - 1) / kScanBlock;
     scan_partials<<<blocks, kScanBlock, 0, st>>>(in, n, partial);
     scan_partials_scan<<<1, kScanBlock, 0, st>>>(partial, blocks);
@@ -208,14 +224,31 @@ __global__ void accumulate_boxes(const float4* __restrict__ bmn, const float4* _
         lo[k] = run_min(lo[k], s, lane);
         hi[k] = run_max(hi[k], s, lane);
     }
-    if (s == kNone || !head) return;
-    uint32_t* a = acc + (size_t)s * kAcc;
+    // A block whose primitives all belong to ONE node (every block of the top levels) reduces in shared memory first:
+    // at level 0 the 12 words of the root took one atomic per warp each, 98k same-address atomics, 68 us.
+    __shared__ uint32_t s_acc[kAcc];
+    const uint32_t s0 = node_of[min(blockIdx.x * blockDim.x, n - 1u)];
+    const bool uniform = __syncthreads_and(s == s0 || p >= n) && s0 != kNone;
+    if (uniform) {
+        if (threadIdx.x < (uint32_t)kAcc) s_acc[threadIdx.x] = (threadIdx.x % 6u) < 3u ? kOrdMinInit : kOrdMaxInit;
+        __syncthreads();
+    }
+    if (s != kNone && head) {
+        uint32_t* a = uniform ? s_acc : acc + (size_t)s * kAcc;
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        atomicMin(a + k, lo[k]);
-        atomicMax(a + 3 + k, hi[k]);
-        atomicMin(a + 6 + k, lo[3 + k]);
-        atomicMax(a + 9 + k, hi[3 + k]);
+        for (int k = 0; k < 3; ++k) {
+            atomicMin(a + k, lo[k]);
+            atomicMax(a + 3 + k, hi[k]);
+            atomicMin(a + 6 + k, lo[3 + k]);
+            atomicMax(a + 9 + k, hi[3 + k]);
+        }
+    }
+    if (!uniform) return;
+    __syncthreads();
+    if (threadIdx.x < (uint32_t)kAcc) {
+        uint32_t* a = acc + (size_t)s0 * kAcc + threadIdx.x;
+        if ((threadIdx.x % 6u) < 3u) atomicMin(a, s_acc[threadIdx.x]);
+        else atomicMax(a, s_acc[threadIdx.x]);
     }
 }
 __global__ void prepare_nodes(const uint32_t* __restrict__ acc, uint32_t nodes, NodeInfo* info) {
