@@ -304,9 +304,8 @@ struct PhaseTimer { // RAYCA_TIMING=1 prints the host phases of scene_create to 
 };
 } // namespace
 
-namespace {
 // the mesh primitive that emitted triangle `src` of the BLAS (emit order), or nullptr for a sphere / quad-light triangle
-inline const HostMeshJob* job_of(const HostBlas& b, uint32_t src) {
+const HostMeshJob* mesh_job_of(const HostBlas& b, uint32_t src) {
     size_t lo = 0, hi = b.jobs.size();
     while (lo < hi) { // first job whose base exceeds src
         const size_t mid = (lo + hi) / 2;
@@ -317,8 +316,9 @@ inline const HostMeshJob* job_of(const HostBlas& b, uint32_t src) {
     const HostMeshJob& j = b.jobs[lo - 1];
     return src < j.base + j.ntri ? &j : nullptr;
 }
+namespace {
 inline uint32_t material_of(const HostBlas& b, uint32_t src) {
-    if (const HostMeshJob* j = job_of(b, src)) return j->material;
+    if (const HostMeshJob* j = mesh_job_of(b, src)) return j->material;
     return b.attrs[src].material;
 }
 } // namespace
@@ -357,7 +357,7 @@ void pack_tri_attrs_range(const rayca_scene_desc& d, const HostScene& out, size_
                 q[10] = q[11] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                 continue;
             }
-            if (const HostMeshJob* job = job_of(b, t.src)) {
+            if (const HostMeshJob* job = mesh_job_of(b, t.src)) {
                 // BvhTriangle attributes (bvh/triangle.rs:33-71, primitive.rs:239-268): vertex colour and uv verbatim,
                 // normal through the node's normal matrix, tangent and bitangent through its tangent matrix
                 const uint32_t local = t.src - (uint32_t)job->base;

@@ -141,6 +141,7 @@ using BlasBuilder = std::function<bool(HostBlas&, uint32_t max_depth)>;
 int build_host_scene(const rayca_scene_desc& desc, bool bvh, HostScene& out, std::string& err, bool fast_tree = true,
                      const BlasBuilder* blas_builder = nullptr, bool gather_texels = true, bool defer_attrs = false);
 // Fills HostScene::tri_attr (12 float4 per primitive, BLAS order) from `desc`'s vertices and HostBlas::{tris, jobs, attrs}.
+const HostMeshJob* mesh_job_of(const HostBlas& blas, uint32_t src); // the mesh primitive that emitted triangle `src`, or nullptr
 void pack_tri_attrs(const rayca_scene_desc& desc, HostScene& scene);
 // ... the primitives [g0, g1) of the packed (reference-global) order into `dst` (12 float4 each): the device path packs
 // and uploads the array piece by piece through a small page-locked ring instead of materialising it on the host

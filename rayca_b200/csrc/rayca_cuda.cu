@@ -355,6 +355,60 @@ void release_device_arrays(rayca_scene* s) {
 } // namespace
 extern "C" {
 
+// ---- shading attributes of mesh triangles computed on the device (scene_create) ------------------------------------
+// pack_tri_attrs (host_scene.cpp) restated per primitive: the caller's vertices and indices are uploaded as they are
+// (13 MB for the 262k-triangle atrium, against 50 MB of packed attributes) and one thread per primitive of the packed
+// order looks its mesh job up and writes its 12 quads.  Same operations in the same order as the host pack (the library
+// is compiled without FMA contraction on both sides), checked byte for byte under RAYCA_VERIFY_ATTRS=1
+// (tests/test_cuda_edge_cases.py).  Spheres and quad-light triangles are left to the host (a handful per scene).
+struct DevMeshJob {
+    uint32_t base, ntri, first_index, first_vertex, material, pad0, pad1, pad2;
+    float tm[9]; // tangent matrix, row-major
+    float nm[9]; // normal matrix
+    float pad3[2];
+};
+static_assert(sizeof(DevMeshJob) % 16 == 0, "job records are loaded as whole words");
+
+__device__ __forceinline__ void dev_m3_apply(const float* m, const float* v, float* out) { // m3_apply (host_scene.cpp)
+    for (int i = 0; i < 3; ++i) {
+        float acc = 0.0f;
+        for (int j = 0; j < 3; ++j) acc += m[i * 3 + j] * v[j];
+        out[i] = acc;
+    }
+}
+
+__global__ void mesh_attr_kernel(const float4* __restrict__ tri_pos, uint32_t total, const uint32_t* __restrict__ job_begin,
+                                 const DevMeshJob* __restrict__ jobs, const rayca_vertex* __restrict__ vertices,
+                                 const uint32_t* __restrict__ indices, float4* __restrict__ tri_attr) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= total) return;
+    const uint32_t src = __float_as_uint(tri_pos[3 * (size_t)g].w), bi = __float_as_uint(tri_pos[3 * (size_t)g + 2].w);
+    uint32_t lo = job_begin[bi], hi = job_begin[bi + 1];
+    const uint32_t first = lo;
+    while (lo < hi) { // first job whose base exceeds src
+        const uint32_t mid = (lo + hi) >> 1;
+        if (jobs[mid].base <= src) lo = mid + 1;
+        else hi = mid;
+    }
+    if (lo == first) return;
+    const DevMeshJob& job = jobs[lo - 1];
+    if (src >= job.base + job.ntri) return; // a sphere or a quad-light triangle: the host writes its record
+    const uint32_t local = src - job.base;
+    float4* q = tri_attr + (size_t)g * 12;
+    for (int v = 0; v < 3; ++v) {
+        const uint32_t vi = indices[job.first_index + (size_t)local * 3 + v];
+        const rayca_vertex& vx = vertices[job.first_vertex + vi];
+        float n[3], tg[3], bt[3];
+        dev_m3_apply(job.nm, vx.normal, n);
+        dev_m3_apply(job.tm, vx.tangent, tg);
+        dev_m3_apply(job.tm, vx.bitangent, bt);
+        q[v] = make_float4(vx.color[0], vx.color[1], vx.color[2], vx.color[3]);
+        q[3 + v] = make_float4(n[0], n[1], n[2], vx.uv[0]);
+        q[6 + v] = make_float4(tg[0], tg[1], tg[2], vx.uv[1]);
+        q[9 + v] = make_float4(bt[0], bt[1], bt[2], v == 0 ? __uint_as_float(job.material) : 0.0f);
+    }
+}
+
 void rayca_cuda_scene_destroy(rayca_scene* s) {
     if (!s) return;
     const double td0 = now_ms();
@@ -473,6 +527,10 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     lap("uploads (8 arrays)");
     constexpr int kRing = 3;
     PodVector<float4> ring[kRing]; // page-locked staging of the shading attributes (below); read by copies until the final sync
+    PodVector<unsigned char> raw_stage; // ... or of the caller's vertices and indices, when the device computes the attributes
+    std::vector<float4> other_attrs;    // ... and the records of the few primitives that are not mesh triangles
+    std::vector<DevMeshJob> dev_jobs;   // ... and the job tables of mesh_attr_kernel
+    std::vector<uint32_t> dev_job_begin;
     if (host_fast_tree) {
         pack_tri_attrs(*desc, h);
         UP(d_tri_attr, tri_attr);
@@ -483,7 +541,113 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         // The shading attributes (the largest array: 192 bytes per primitive) are never materialised on the host: they
         // are packed piece by piece into a ring of three page-locked buffers and leave on the copy stream, the copies
         // running under the packing of the next piece and under the tree build that follows.
-        {
+        // Scenes made of triangle meshes (all but a handful of primitives) do not even pack them on the host: the caller's
+        // vertices and indices go up as they are and mesh_attr_kernel writes the records (above).
+        size_t mesh_prims = 0;
+        for (const HostBlas& b : h.blas)
+            for (const HostMeshJob& j : b.jobs) mesh_prims += j.ntri;
+        const size_t total_prims = h.blas_prim_offset.back();
+        const bool device_attrs = mesh_prims > 0 && total_prims - mesh_prims <= 64 && !std::getenv("RAYCA_HOST_ATTRS") &&
+                                  desc->vertex_count * sizeof(rayca_vertex) + desc->index_count * 4 <= total_prims * 12 * sizeof(float4);
+        if (device_attrs) {
+            const size_t attr_bytes = std::max<size_t>(total_prims * 12 * sizeof(float4), 16);
+            s->nbytes[slot_of(&s->d_tri_attr, s)] = attr_bytes;
+            cudaError_t ce = cudaMallocAsync(&s->d_tri_attr, attr_bytes, ctx->render_stream);
+            // raw vertices | indices, gathered by all threads into one page-locked block (the caller's arrays are pageable)
+            const size_t vbytes = (size_t)desc->vertex_count * sizeof(rayca_vertex), voff = 0, ioff = (vbytes + 255) & ~size_t(255);
+            const size_t ibytes = (size_t)desc->index_count * 4;
+            raw_stage.resize(ioff + ibytes);
+            {
+                struct Piece { const unsigned char* src; size_t dst, bytes; };
+                std::vector<Piece> pieces;
+                for (size_t o = 0; o < vbytes; o += size_t(1) << 20)
+                    pieces.push_back({reinterpret_cast<const unsigned char*>(desc->vertices) + o, voff + o, std::min(vbytes - o, size_t(1) << 20)});
+                for (size_t o = 0; o < ibytes; o += size_t(1) << 20)
+                    pieces.push_back({reinterpret_cast<const unsigned char*>(desc->indices) + o, ioff + o, std::min(ibytes - o, size_t(1) << 20)});
+#pragma omp parallel for schedule(dynamic, 1) if (pieces.size() > 1)
+                for (int64_t k = 0; k < (int64_t)pieces.size(); ++k) std::memcpy(raw_stage.data() + pieces[(size_t)k].dst, pieces[(size_t)k].src, pieces[(size_t)k].bytes);
+            }
+            dev_jobs.clear();
+            std::vector<DevMeshJob>& jobs = dev_jobs;
+            std::vector<uint32_t>& job_begin = dev_job_begin;
+            job_begin.assign(h.blas.size() + 1, 0);
+            for (size_t bi = 0; bi < h.blas.size(); ++bi) {
+                for (const HostMeshJob& j : h.blas[bi].jobs) {
+                    DevMeshJob dj{};
+                    dj.base = (uint32_t)j.base;
+                    dj.ntri = j.ntri;
+                    dj.first_index = j.first_index;
+                    dj.first_vertex = j.first_vertex;
+                    dj.material = j.material;
+                    for (int r = 0; r < 3; ++r)
+                        for (int c = 0; c < 3; ++c) {
+                            dj.tm[r * 3 + c] = j.tangent_matrix.m[r][c];
+                            dj.nm[r * 3 + c] = j.normal_matrix.m[r][c];
+                        }
+                    jobs.push_back(dj);
+                }
+                job_begin[bi + 1] = (uint32_t)jobs.size();
+            }
+            void *d_raw = nullptr, *d_jobs = nullptr, *d_job_begin = nullptr;
+            if (ce == cudaSuccess) ce = cudaMallocAsync(&d_raw, std::max<size_t>(raw_stage.size(), 16), ctx->render_stream);
+            if (ce == cudaSuccess) ce = cudaMallocAsync(&d_jobs, jobs.size() * sizeof(DevMeshJob), ctx->render_stream);
+            if (ce == cudaSuccess) ce = cudaMallocAsync(&d_job_begin, job_begin.size() * 4, ctx->render_stream);
+            if (ce == cudaSuccess && !raw_stage.empty())
+                ce = cudaMemcpyAsync(d_raw, raw_stage.data(), raw_stage.size(), cudaMemcpyHostToDevice, ctx->render_stream);
+            if (ce == cudaSuccess) ce = cudaMemcpyAsync(d_jobs, jobs.data(), jobs.size() * sizeof(DevMeshJob), cudaMemcpyHostToDevice, ctx->render_stream);
+            if (ce == cudaSuccess) ce = cudaMemcpyAsync(d_job_begin, job_begin.data(), job_begin.size() * 4, cudaMemcpyHostToDevice, ctx->render_stream);
+            if (ce == cudaSuccess) {
+                mesh_attr_kernel<<<(unsigned)((total_prims + 255) / 256), 256, 0, ctx->render_stream>>>(
+                    (const float4*)s->d_tri_pos, (uint32_t)total_prims, (const uint32_t*)d_job_begin, (const DevMeshJob*)d_jobs,
+                    reinterpret_cast<const rayca_vertex*>(static_cast<unsigned char*>(d_raw) + voff),
+                    reinterpret_cast<const uint32_t*>(static_cast<unsigned char*>(d_raw) + ioff), (float4*)s->d_tri_attr);
+                ce = cudaGetLastError();
+            }
+            // the few primitives that are not mesh triangles: packed here, one small copy each, behind the kernel
+            if (ce == cudaSuccess && total_prims != mesh_prims) {
+                std::vector<size_t> where;
+                for (size_t bi = 0; bi < h.blas.size(); ++bi) {
+                    const HostBlas& b = h.blas[bi];
+#pragma omp parallel if (b.tris.size() > 8192)
+                    {
+                        std::vector<size_t> mine;
+#pragma omp for schedule(static) nowait
+                        for (int64_t k = 0; k < (int64_t)b.tris.size(); ++k) {
+                            const HostTri& t = b.tris[(size_t)k];
+                            if (t.sphere || !mesh_job_of(b, t.src)) mine.push_back(h.blas_prim_offset[bi] + (size_t)k);
+                        }
+#pragma omp critical
+                        where.insert(where.end(), mine.begin(), mine.end());
+                    }
+                }
+                other_attrs.resize(where.size() * 12);
+                for (size_t i = 0; i < where.size() && ce == cudaSuccess; ++i) {
+                    pack_tri_attrs_range(*desc, h, where[i], where[i] + 1, other_attrs.data() + i * 12);
+                    ce = cudaMemcpyAsync(static_cast<float4*>(s->d_tri_attr) + where[i] * 12, other_attrs.data() + i * 12, 12 * sizeof(float4),
+                                         cudaMemcpyHostToDevice, ctx->render_stream);
+                }
+            }
+            // (the staging block and the job tables live until scene_create returns, after the stream has been drained)
+            if (d_raw) cudaFreeAsync(d_raw, ctx->render_stream);
+            if (d_jobs) cudaFreeAsync(d_jobs, ctx->render_stream);
+            if (d_job_begin) cudaFreeAsync(d_job_begin, ctx->render_stream);
+            if (ce == cudaSuccess && std::getenv("RAYCA_VERIFY_ATTRS")) { // tests: the device records against the host pack, byte for byte
+                pack_tri_attrs(*desc, h);
+                std::vector<float4> got(total_prims * 12);
+                ce = cudaStreamSynchronize(ctx->render_stream);
+                if (ce == cudaSuccess) ce = cudaMemcpy(got.data(), s->d_tri_attr, got.size() * sizeof(float4), cudaMemcpyDeviceToHost);
+                if (ce == cudaSuccess && std::memcmp(got.data(), h.tri_attr.data(), got.size() * sizeof(float4)) != 0) {
+                    size_t bad = 0;
+                    while (std::memcmp(&got[bad * 12], &h.tri_attr[bad * 12], 12 * sizeof(float4)) == 0) ++bad;
+                    rayca_cuda_scene_destroy(s);
+                    return fail(RAYCA_E_CUDA, "device-computed attributes differ from the host pack at primitive " + std::to_string(bad));
+                }
+            }
+            if (ce != cudaSuccess) {
+                rayca_cuda_scene_destroy(s);
+                return fail(ce == cudaErrorMemoryAllocation ? RAYCA_E_OOM : RAYCA_E_CUDA, std::string("attribute kernel: ") + cudaGetErrorString(ce));
+            }
+        } else {
             const size_t total = h.blas_prim_offset.back();
             const size_t attr_bytes = std::max<size_t>(total * 12 * sizeof(float4), 16);
             s->nbytes[slot_of(&s->d_tri_attr, s)] = attr_bytes;

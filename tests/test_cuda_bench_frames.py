@@ -114,3 +114,20 @@ def test_soup_16spp_rows_against_the_oracle(ctx, oracle):
     assert gst.rays_primary == w * h * 16 and shadow > 0
     dev.close()
     osc.close()
+
+
+def test_atrium_bounce_frame_wavefront_equals_fused(atrium, monkeypatch):
+    """The 1080p bounce frame of the bench (BASELINE config 5) at full size: the wavefront stages — persistent ray-walk
+    kernel with dynamic fetch over two million sorted paths, shading re-sorted by hit point — against the fused kernel,
+    byte for byte and ray count for ray count; and the one-kernel-per-depth stage likewise."""
+    desc, dev, osc = atrium
+    cfg = R.Config(max_depth=2)
+    fused8, _, fst = dev.render(cfg, W, H, options=M.rayca_options(0x5EED, 0, 0, 0, 0, R.FLAG_NO_WAVEFRONT, 0))
+    wave8, _, wst = dev.render(cfg, W, H, options=M.rayca_options(0x5EED, 0, 0, 0, 0, 0, 0))
+    assert wst.kernel_launches > fst.kernel_launches, "the frame is large enough for the stages: they must have run"
+    assert np.array_equal(wave8, fused8), f"{(wave8 != fused8).sum()} bytes differ"
+    assert (wst.rays_primary, wst.rays_shadow, wst.rays_secondary) == (fst.rays_primary, fst.rays_shadow, fst.rays_secondary)
+    monkeypatch.setenv("RAYCA_WAVE_SPLIT", "0")
+    one8, _, ost = dev.render(cfg, W, H, options=M.rayca_options(0x5EED, 0, 0, 0, 0, 0, 0))
+    assert np.array_equal(one8, fused8)
+    assert (ost.rays_primary, ost.rays_shadow, ost.rays_secondary) == (fst.rays_primary, fst.rays_shadow, fst.rays_secondary)

@@ -591,3 +591,23 @@ def test_cornell_estimators_agree_in_the_mean(ctx):
     ref = means["nee"]
     for name, m in means.items():
         assert abs(m - ref) <= 0.03 * ref, means
+
+
+@pytest.mark.parametrize("scene", ["suzanne", "cubes_over_plane", "normalquad", "orientation", "cornell", "quadsphere", "dragon",
+                                   "flighthelmet", "atrium"])
+def test_device_computed_attributes_equal_the_host_pack(ctx, scene, monkeypatch):
+    """scene_create computes the shading attributes of mesh triangles on the device from the caller's vertices
+    (mesh_attr_kernel) instead of packing them on the host; under RAYCA_VERIFY_ATTRS it also runs the host pack and
+    refuses the scene unless the two arrays are equal byte for byte.  Scenes with scaled / rotated nodes, several BLAS,
+    vertex colours, tangents, quad-light triangles (cornell: written by the host, next to the kernel's) and spheres."""
+    monkeypatch.setenv("RAYCA_VERIFY_ATTRS", "1")
+    if scene == "atrium":
+        from rayca_b200 import procedural as P
+
+        desc = P.atrium(262_267).to_desc()
+    else:
+        desc = load_desc(scene)
+    sc = R.DeviceScene(ctx, desc)  # raises RaycaError on a mismatch
+    sc.close()
+    monkeypatch.setenv("RAYCA_HOST_ATTRS", "1")  # the host ring path still works
+    R.DeviceScene(ctx, desc).close()
