@@ -65,13 +65,17 @@ def build(force: bool = False, verbose: bool = False, out: str = OUT, defines=()
         def compile_one(src):
             with open(os.path.join(CSRC, src), "rb") as fh:
                 key = hashlib.sha1(" ".join(common).encode() + b"\0" + header_digest.digest() + fh.read()).hexdigest()
-            obj = os.path.join(cache, f"{os.path.splitext(src)[0]}-{key}.o")
+            obj = os.path.join(tmp if defines else cache, f"{os.path.splitext(src)[0]}-{key}.o")  # variants are not cached
             if os.path.exists(obj) and not verbose:
                 return src, obj, types.SimpleNamespace(returncode=0, stdout="", stderr="")
             part = os.path.join(tmp, os.path.splitext(src)[0] + ".o")
             res = subprocess.run(common + ["-c", os.path.join(CSRC, src), "-o", part], capture_output=True, text=True)
             if res.returncode == 0:
                 shutil.move(part, obj)
+                stem = os.path.splitext(src)[0] + "-"
+                for old in os.listdir(cache):  # one object per source and flag set would pile up 15 MB at a time
+                    if not defines and old.startswith(stem) and os.path.join(cache, old) != obj:
+                        os.remove(os.path.join(cache, old))
             return src, obj, res
 
         with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
