@@ -1306,8 +1306,13 @@ int transpose_pairs_device(void* d_nodes, size_t node_count, cudaStream_t st) {
     return cudaGetLastError() == cudaSuccess ? RAYCA_OK : RAYCA_E_CUDA;
 }
 
-int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::string& err, float* device_ms) {
-    const uint32_t N = (uint32_t)blas.tris.size();
+__global__ void iota_kernel(uint32_t* order, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) order[i] = i;
+}
+
+int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::string& err, float* device_ms, const DeviceBlasInput* dev) {
+    const uint32_t N = dev ? dev->n : (uint32_t)blas.tris.size();
     if (N == 0) { err = "no primitives"; return RAYCA_E_INVALID_ARG; }
     const bool timing = std::getenv("RAYCA_TIMING") != nullptr;
     auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
@@ -1320,10 +1325,10 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
     };
     // PodVector: recycled, page-locked blocks without value initialisation (host_scene.h) — three std::vectors of N
     // float4 cost 1.4 ms of page faults and memset per build, and their uploads were pageable
-    PodVector<float4> hmn(N), hmx(N), hcen(N);
+    PodVector<float4> hmn(dev ? 0 : N), hmx(dev ? 0 : N), hcen(dev ? 0 : N);
     PodVector<uint32_t> order(N);
 #pragma omp parallel for schedule(static) if (N > 8192)
-    for (int64_t i = 0; i < (int64_t)N; ++i) {
+    for (int64_t i = 0; i < (int64_t)(dev ? 0 : N); ++i) {
         order[(size_t)i] = (uint32_t)i;
         const HostTri& t = blas.tris[(size_t)i];
         hmn[(size_t)i] = make_float4(t.bmin.x, t.bmin.y, t.bmin.z, 0.0f);
@@ -1339,9 +1344,11 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
     RefInfo* d_info;
     RefDecision* d_dec;
     const size_t node_cap = (size_t)N * 2 + 2;
-    FB_TRY(buf.alloc(&d_mn, N));
-    FB_TRY(buf.alloc(&d_mx, N));
-    FB_TRY(buf.alloc(&d_cen, N));
+    if (!dev) {
+        FB_TRY(buf.alloc(&d_mn, N));
+        FB_TRY(buf.alloc(&d_mx, N));
+        FB_TRY(buf.alloc(&d_cen, N));
+    }
     for (int k = 0; k < 2; ++k) {
         FB_TRY(buf.alloc(&d_order[k], N));
         FB_TRY(buf.alloc(&d_node_of[k], N));
@@ -1365,10 +1372,17 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
     cudaEvent_t e0, e1;
     FB_TRY(cudaEventCreate(&e0));
     FB_TRY(cudaEventCreate(&e1));
-    FB_TRY(cudaMemcpyAsync(d_mn, hmn.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
-    FB_TRY(cudaMemcpyAsync(d_mx, hmx.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
-    FB_TRY(cudaMemcpyAsync(d_cen, hcen.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
-    FB_TRY(cudaMemcpyAsync(d_order[0], order.data(), (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    if (dev) {
+        d_mn = const_cast<float4*>(dev->mn);
+        d_mx = const_cast<float4*>(dev->mx);
+        d_cen = const_cast<float4*>(dev->cen);
+        iota_kernel<<<blocks_for(N, 256), 256, 0, st>>>(d_order[0], N);
+    } else {
+        FB_TRY(cudaMemcpyAsync(d_mn, hmn.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
+        FB_TRY(cudaMemcpyAsync(d_mx, hmx.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
+        FB_TRY(cudaMemcpyAsync(d_cen, hcen.data(), (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, st));
+        FB_TRY(cudaMemcpyAsync(d_order[0], order.data(), (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    }
     FB_TRY(cudaEventRecord(e0, st));
     RefNode init[2];
     std::memset(init, 0, sizeof(init));
@@ -1421,6 +1435,7 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
     std::vector<RefNode> tmp(next_id);
     FB_TRY(cudaMemcpyAsync(tmp.data(), d_nodes, (size_t)next_id * sizeof(RefNode), cudaMemcpyDeviceToHost, st));
     FB_TRY(cudaMemcpyAsync(order.data(), d_order[cur], (size_t)N * 4, cudaMemcpyDeviceToHost, st));
+    if (dev) FB_TRY(cudaMemcpyAsync(dev->order_out, d_order[cur], (size_t)N * 4, cudaMemcpyDeviceToDevice, st));
     FB_TRY(cudaStreamSynchronize(st));
     FB_TRY(cudaGetLastError());
     float ms = 0.0f;
@@ -1468,12 +1483,106 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
     }
     blas.depth = deepest;
     lap("blas: renumber nodes");
+    if (dev) { // the primitives live on the device: the host keeps the order only (rayca_cuda_scene_bvh_read)
+        blas.order.swap(order);
+        blas.device_prims = N;
+        return RAYCA_OK;
+    }
     PodVector<HostTri> sorted(N);
 #pragma omp parallel for schedule(static) if (N > 8192)
     for (int64_t i = 0; i < (int64_t)N; ++i) sorted[(size_t)i] = blas.tris[order[(size_t)i]];
     blas.tris.swap(sorted);
     lap("blas: permute primitives");
     return RAYCA_OK;
+}
+
+// ---- mesh triangles emitted on the device ---------------------------------------------------------------------------
+__device__ __forceinline__ const DeviceMeshJob& job_of_emit(const DeviceMeshJob* jobs, uint32_t job_count, uint32_t t) {
+    uint32_t lo = 0, hi = job_count;
+    while (lo < hi) { // first job whose base exceeds t (t lies in a job: the jobs tile [0, n))
+        const uint32_t mid = (lo + hi) >> 1;
+        if (jobs[mid].base <= t) lo = mid + 1;
+        else hi = mid;
+    }
+    return jobs[lo - 1];
+}
+
+__global__ void emit_mesh_kernel(const DeviceMeshJob* __restrict__ jobs, uint32_t job_count, uint32_t n, const rayca_vertex* __restrict__ vertices,
+                                 const uint32_t* __restrict__ indices, float4* __restrict__ pos, float4* __restrict__ mn, float4* __restrict__ mx,
+                                 float4* __restrict__ cen, uint32_t* bad) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const DeviceMeshJob& job = job_of_emit(jobs, job_count, t);
+    const uint32_t local = t - job.base;
+    const TrsF world{V3{job.t[0], job.t[1], job.t[2]}, Q4{job.q[0], job.q[1], job.q[2], job.q[3]}, V3{job.s[0], job.s[1], job.s[2]}};
+    V3 mv[3], wv[3];
+    for (int k = 0; k < 3; ++k) {
+        uint32_t vi = indices[job.first_index + (size_t)local * 3 + k];
+        if (vi >= job.vertex_count) { *bad = 1u; vi = 0; }
+        const rayca_vertex& v = vertices[job.first_vertex + vi];
+        mv[k] = V3{v.pos[0], v.pos[1], v.pos[2]};
+        wv[k] = trs_point(world, mv[k]); // Triangle::get_vertex (triangle.rs:67-69)
+        pos[3 * (size_t)t + k] = make_float4(wv[k].x, wv[k].y, wv[k].z, 0.0f);
+    }
+    // Triangle::new centroid quirk (triangle.rs:59-62) then `trs * Vec3` (trs.rs:253-262)
+    const V3 c = trs_vec(world, ((mv[0] + mv[1]) + mv[2]) * 0.3333f);
+    cen[t] = make_float4(c.x, c.y, c.z, 0.0f);
+    mn[t] = make_float4(fminf(fminf(fminf(kF32Max, wv[0].x), wv[1].x), wv[2].x), fminf(fminf(fminf(kF32Max, wv[0].y), wv[1].y), wv[2].y),
+                        fminf(fminf(fminf(kF32Max, wv[0].z), wv[1].z), wv[2].z), 0.0f);
+    mx[t] = make_float4(fmaxf(fmaxf(fmaxf(-kF32Max, wv[0].x), wv[1].x), wv[2].x), fmaxf(fmaxf(fmaxf(-kF32Max, wv[0].y), wv[1].y), wv[2].y),
+                        fmaxf(fmaxf(fmaxf(-kF32Max, wv[0].z), wv[1].z), wv[2].z), 0.0f);
+}
+
+__global__ void gather_tri_pos_kernel(const float4* __restrict__ pos, const uint32_t* __restrict__ order, const DeviceMeshJob* __restrict__ jobs,
+                                      uint32_t job_count, uint32_t n, uint32_t blas_index, float4* __restrict__ tri_pos) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const uint32_t src = order[k];
+    const DeviceMeshJob& job = job_of_emit(jobs, job_count, src);
+    const float4 a = pos[3 * (size_t)src], b = pos[3 * (size_t)src + 1], c = pos[3 * (size_t)src + 2];
+    tri_pos[3 * (size_t)k] = make_float4(a.x, a.y, a.z, __uint_as_float(src));
+    tri_pos[3 * (size_t)k + 1] = make_float4(b.x, b.y, b.z, __uint_as_float(job.material));
+    tri_pos[3 * (size_t)k + 2] = make_float4(c.x, c.y, c.z, __uint_as_float(blas_index));
+}
+
+void free_device_blas_mesh(DeviceBlasMesh& m, cudaStream_t st) {
+    void* ptrs[] = {m.pos, m.mn, m.mx, m.cen, m.order, m.jobs, m.bad};
+    for (void* p : ptrs)
+        if (p) cudaFreeAsync(p, st);
+    m = DeviceBlasMesh{};
+}
+
+int emit_mesh_device(const std::vector<DeviceMeshJob>& jobs, uint32_t n, const void* d_vertices, const void* d_indices, cudaStream_t st,
+                     DeviceBlasMesh& out, std::string& err) {
+    out = DeviceBlasMesh{};
+    out.n = n;
+    out.job_count = (uint32_t)jobs.size();
+    cudaError_t ce = cudaMallocAsync((void**)&out.pos, (size_t)n * 3 * sizeof(float4), st);
+    if (ce == cudaSuccess) ce = cudaMallocAsync((void**)&out.mn, (size_t)n * sizeof(float4), st);
+    if (ce == cudaSuccess) ce = cudaMallocAsync((void**)&out.mx, (size_t)n * sizeof(float4), st);
+    if (ce == cudaSuccess) ce = cudaMallocAsync((void**)&out.cen, (size_t)n * sizeof(float4), st);
+    if (ce == cudaSuccess) ce = cudaMallocAsync((void**)&out.order, (size_t)n * 4, st);
+    if (ce == cudaSuccess) ce = cudaMallocAsync((void**)&out.jobs, jobs.size() * sizeof(DeviceMeshJob), st);
+    if (ce == cudaSuccess) ce = cudaMallocAsync((void**)&out.bad, 4, st);
+    if (ce == cudaSuccess) ce = cudaMemsetAsync(out.bad, 0, 4, st);
+    // `jobs` is a pageable vector of the caller: this copy is staged before the call returns
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(out.jobs, jobs.data(), jobs.size() * sizeof(DeviceMeshJob), cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess) {
+        emit_mesh_kernel<<<blocks_for(n, 256), 256, 0, st>>>(out.jobs, out.job_count, n, static_cast<const rayca_vertex*>(d_vertices),
+                                                            static_cast<const uint32_t*>(d_indices), out.pos, out.mn, out.mx, out.cen, out.bad);
+        ce = cudaGetLastError();
+    }
+    if (ce != cudaSuccess) {
+        err = std::string("device emit: ") + cudaGetErrorString(ce);
+        free_device_blas_mesh(out, st);
+        return ce == cudaErrorMemoryAllocation ? RAYCA_E_OOM : RAYCA_E_CUDA;
+    }
+    return RAYCA_OK;
+}
+
+int gather_tri_pos_device(const DeviceBlasMesh& m, uint32_t blas_index, float4* d_tri_pos, cudaStream_t st) {
+    gather_tri_pos_kernel<<<blocks_for(m.n, 256), 256, 0, st>>>(m.pos, m.order, m.jobs, m.job_count, m.n, blas_index, d_tri_pos);
+    return cudaGetLastError() == cudaSuccess ? RAYCA_OK : RAYCA_E_CUDA;
 }
 
 } // namespace rb

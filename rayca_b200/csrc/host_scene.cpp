@@ -387,7 +387,7 @@ void pack_tri_attrs_range(const rayca_scene_desc& d, const HostScene& out, size_
 }
 
 int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::string& err, bool fast_tree,
-                     const BlasBuilder* blas_builder, bool gather_texels, bool defer_attrs) {
+                     const BlasBuilder* blas_builder, bool gather_texels, bool defer_attrs, const MeshBlasBuilder* mesh_builder) {
     PhaseTimer phase;
     Flatten f(d, out);
     f.run();
@@ -483,6 +483,7 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
         std::vector<Chunk> chunks;
         struct SphereSlot { size_t slot; uint32_t sphere; uint32_t material; float radius; };
         std::vector<SphereSlot> sphere_slots;
+        std::vector<HostMeshEmit> emits;
         size_t total_prims = 0;
         for (const MeshDraw& md : f.mesh_draws[mi]) {
             const rayca_node& n = d.nodes[m.node_offset + md.node_local];
@@ -523,8 +524,19 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
                 rec.tangent_matrix = tangent_matrix;
                 rec.normal_matrix = normal_matrix;
                 blas.jobs.push_back(rec);
+                if (mesh_builder) emits.push_back({rec, md.world, g.vertex_count});
                 for (uint32_t first = 0; first < ntri; first += 4096) chunks.push_back({job, first, std::min(4096u, ntri - first)});
                 total_prims += ntri;
+            }
+        }
+        const uint32_t max_depth = bvh ? 255u : 0u; // scene.rs:95-99: !config.bvh => max_depth(0)
+        if (mesh_builder && sphere_slots.empty() && f.quad_draws[mi].empty() && total_prims >= 16384 && total_prims < 0xFFFFFFF0ull) {
+            const int r = (*mesh_builder)(blas, emits, max_depth, err);
+            if (r < 0) return r;
+            if (r == 1) {
+                phase.lap("emit + reference BLAS (device)");
+                out.blas.push_back(std::move(blas));
+                continue;
             }
         }
         blas.tris.reserve(total_prims + 2 * f.quad_draws[mi].size()); // the quad-light triangles are appended below
@@ -613,7 +625,6 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
             }
         }
         phase.lap("emit triangles");
-        const uint32_t max_depth = bvh ? 255u : 0u; // scene.rs:95-99: !config.bvh => max_depth(0)
         if (blas_builder && (*blas_builder)(blas, max_depth)) {
             phase.lap("reference BLAS build (device)");
         } else {
@@ -690,7 +701,7 @@ int build_host_scene(const rayca_scene_desc& d, bool bvh, HostScene& out, std::s
     out.blas_prim_offset.assign(1, 0);
     for (const HostBlas& b : out.blas) {
         total_nodes += b.nodes.size();
-        total_tris += b.tris.size();
+        total_tris += b.prim_count();
         out.blas_node_offset.push_back((uint32_t)total_nodes);
         out.blas_prim_offset.push_back((uint32_t)total_tris);
     }

@@ -99,6 +99,11 @@ struct HostBlas {
     PodVector<HostTri> tris;     // reordered in place by the build
     PodVector<HostAttr> attrs;   // indexed by HostTri::src; filled for spheres and quad-light triangles only
     std::vector<HostMeshJob> jobs; // ascending base
+    // primitives emitted and kept on the DEVICE (scene_create's mesh-only fast path): `tris` stays empty, the build
+    // leaves the count and its primitive order (BLAS position -> emit index) here
+    size_t device_prims = 0;
+    PodVector<uint32_t> order;
+    size_t prim_count() const { return tris.empty() ? device_prims : tris.size(); }
     std::vector<HostSphere> spheres;
     std::vector<HostNode> nodes; // node 0 root, node 1 unused (blas.rs:250-256)
     uint32_t model = 0;
@@ -138,8 +143,19 @@ struct HostScene {
 // `defer_attrs`: HostScene::tri_attr is sized but not filled; the caller runs pack_tri_attrs itself (the device path
 // does, while the performance tree is being built on the GPU).
 using BlasBuilder = std::function<bool(HostBlas&, uint32_t max_depth)>;
+// `mesh_builder`, when given, is offered every model that consists of triangle meshes only (no spheres, no quad lights)
+// BEFORE its triangles are emitted on the host: the mesh primitives with the world TRS of their nodes.  It returns 1 when it
+// has emitted the triangles and built the BLAS itself (HostBlas::{nodes, depth, device_prims, order} set, `tris` empty),
+// 0 to leave the model to the host emit, or a negative RAYCA_E_* code (detail in `err`).
+struct HostMeshEmit {
+    HostMeshJob job;
+    TrsF world;
+    uint32_t vertex_count; // of the geometry: indices are checked against it
+};
+using MeshBlasBuilder = std::function<int(HostBlas&, const std::vector<HostMeshEmit>&, uint32_t max_depth, std::string& err)>;
 int build_host_scene(const rayca_scene_desc& desc, bool bvh, HostScene& out, std::string& err, bool fast_tree = true,
-                     const BlasBuilder* blas_builder = nullptr, bool gather_texels = true, bool defer_attrs = false);
+                     const BlasBuilder* blas_builder = nullptr, bool gather_texels = true, bool defer_attrs = false,
+                     const MeshBlasBuilder* mesh_builder = nullptr);
 // Fills HostScene::tri_attr (12 float4 per primitive, BLAS order) from `desc`'s vertices and HostBlas::{tris, jobs, attrs}.
 const HostMeshJob* mesh_job_of(const HostBlas& blas, uint32_t src); // the mesh primitive that emitted triangle `src`, or nullptr
 void pack_tri_attrs(const rayca_scene_desc& desc, HostScene& scene);

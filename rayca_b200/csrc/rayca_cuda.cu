@@ -443,6 +443,101 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         if (brc != RAYCA_OK) cudaGetLastError();
         return brc == RAYCA_OK;
     };
+    // Models made of triangle meshes only are emitted ON THE DEVICE from the caller's vertices and indices, uploaded as
+    // they are: emit_mesh_device restates the host emit loop per triangle (same expressions, no FMA on either side),
+    // build_blas_device reads the bounds where they are, and the packed positions are a gather by the build's order —
+    // the host never holds those triangles (emit 1.4 ms + permutation and packing 0.7 ms of the atrium's draw).  Off for
+    // scenes with spheres (their performance tree takes bounds from the host) and under the host-builder / verification
+    // switches, which need the host triangles.
+    bool any_sphere_geometry = false;
+    for (uint32_t i = 0; i < desc->geometry_count; ++i) any_sphere_geometry = any_sphere_geometry || desc->geometries[i].kind == RAYCA_GEOMETRY_SPHERE;
+    const bool device_emit = bvh && !host_fast_tree && !host_ref_tree && !any_sphere_geometry && desc->vertex_count > 0 && desc->index_count > 0 &&
+                             !std::getenv("RAYCA_HOST_EMIT") && !std::getenv("RAYCA_HOST_ATTRS") && !std::getenv("RAYCA_VERIFY_ATTRS");
+    PodVector<unsigned char> raw_stage; // the caller's vertices | indices, page-locked; read by a copy until the final sync
+    void* d_raw = nullptr;              // ... on the device (freed in stream order at the end of scene_create)
+    const size_t raw_vbytes = (size_t)desc->vertex_count * sizeof(rayca_vertex), raw_ioff = (raw_vbytes + 255) & ~size_t(255);
+    const size_t raw_ibytes = (size_t)desc->index_count * 4;
+    auto upload_raw = [&]() -> cudaError_t { // gathered by all threads into one page-locked block, one asynchronous copy
+        if (d_raw) return cudaSuccess;
+        raw_stage.resize(raw_ioff + raw_ibytes);
+        struct Piece { const unsigned char* src; size_t dst, bytes; };
+        std::vector<Piece> pieces;
+        for (size_t o = 0; o < raw_vbytes; o += size_t(1) << 20)
+            pieces.push_back({reinterpret_cast<const unsigned char*>(desc->vertices) + o, o, std::min(raw_vbytes - o, size_t(1) << 20)});
+        for (size_t o = 0; o < raw_ibytes; o += size_t(1) << 20)
+            pieces.push_back({reinterpret_cast<const unsigned char*>(desc->indices) + o, raw_ioff + o, std::min(raw_ibytes - o, size_t(1) << 20)});
+#pragma omp parallel for schedule(dynamic, 1) if (pieces.size() > 1)
+        for (int64_t k = 0; k < (int64_t)pieces.size(); ++k) std::memcpy(raw_stage.data() + pieces[(size_t)k].dst, pieces[(size_t)k].src, pieces[(size_t)k].bytes);
+        cudaError_t ce = cudaMallocAsync(&d_raw, std::max<size_t>(raw_stage.size(), 16), ctx->render_stream);
+        if (ce == cudaSuccess && !raw_stage.empty())
+            ce = cudaMemcpyAsync(d_raw, raw_stage.data(), raw_stage.size(), cudaMemcpyHostToDevice, ctx->render_stream);
+        return ce;
+    };
+    std::vector<std::pair<uint32_t, DeviceBlasMesh>> device_meshes; // (model, its triangles on the device)
+    struct FreeMeshes { // every exit path gives the per-model device arrays back (stream-ordered)
+        std::vector<std::pair<uint32_t, DeviceBlasMesh>>& v;
+        void*& raw;
+        cudaStream_t st;
+        ~FreeMeshes() {
+            for (auto& m : v) free_device_blas_mesh(m.second, st);
+            if (raw) cudaFreeAsync(raw, st);
+            raw = nullptr;
+        }
+    } free_meshes{device_meshes, d_raw, ctx->render_stream};
+    const MeshBlasBuilder device_mesh_blas = [&](HostBlas& blas, const std::vector<HostMeshEmit>& emits, uint32_t max_depth, std::string& mesh_err) -> int {
+        size_t n = 0;
+        std::vector<DeviceMeshJob> jobs;
+        for (const HostMeshEmit& e : emits) {
+            DeviceMeshJob j{};
+            j.base = (uint32_t)e.job.base;
+            j.ntri = e.job.ntri;
+            j.first_index = e.job.first_index;
+            j.first_vertex = e.job.first_vertex;
+            j.vertex_count = e.vertex_count;
+            j.material = e.job.material;
+            j.t[0] = e.world.t.x; j.t[1] = e.world.t.y; j.t[2] = e.world.t.z;
+            j.q[0] = e.world.q.x; j.q[1] = e.world.q.y; j.q[2] = e.world.q.z; j.q[3] = e.world.q.w;
+            j.s[0] = e.world.s.x; j.s[1] = e.world.s.y; j.s[2] = e.world.s.z;
+            if (e.job.base != n) return 0; // the jobs must tile [0, n) in order (they do: emit order)
+            n += e.job.ntri;
+            jobs.push_back(j);
+        }
+        if (jobs.empty() || upload_raw() != cudaSuccess) {
+            cudaGetLastError();
+            return 0;
+        }
+        DeviceBlasMesh mesh;
+        if (emit_mesh_device(jobs, (uint32_t)n, d_raw, static_cast<unsigned char*>(d_raw) + raw_ioff, ctx->render_stream, mesh, mesh_err) != RAYCA_OK) {
+            cudaGetLastError();
+            return 0;
+        }
+        DeviceBlasInput in;
+        in.n = mesh.n;
+        in.mn = mesh.mn;
+        in.mx = mesh.mx;
+        in.cen = mesh.cen;
+        in.order_out = mesh.order;
+        float ms = 0.0f;
+        std::string build_err;
+        const int brc = build_blas_device(blas, max_depth, ctx->render_stream, build_err, &ms, &in); // synchronises the stream
+        uint32_t bad = 0;
+        if (brc == RAYCA_OK && cudaMemcpy(&bad, mesh.bad, 4, cudaMemcpyDeviceToHost) != cudaSuccess) bad = 0;
+        if (brc != RAYCA_OK || bad) {
+            cudaGetLastError();
+            free_device_blas_mesh(mesh, ctx->render_stream);
+            blas.nodes.clear();
+            blas.order.clear();
+            blas.device_prims = 0;
+            if (bad) {
+                mesh_err = "vertex index out of range";
+                return RAYCA_E_INVALID_ARG;
+            }
+            return 0; // e.g. a level broader than the device work lists: the host emits and builds
+        }
+        if (std::getenv("RAYCA_TIMING")) std::fprintf(stderr, "[rayca] %-28s %8.2f ms\n", "  BLAS kernels", ms);
+        device_meshes.emplace_back(blas.model, mesh);
+        return 1;
+    };
     // Texels: the caller's images are pageable as a rule (decoded files), and a pageable cudaMemcpy blocks the calling
     // thread at about 12 GB/s (1.3 of 15 ms of the atrium's draw).  They are gathered into one recycled page-locked block
     // by all host threads instead and leave in ONE asynchronous copy on the copy stream, which runs under everything
@@ -477,7 +572,8 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         return urc;
     }
     try {
-        rc = build_host_scene(*desc, bvh != 0, s->host, err, host_fast_tree, &device_blas, /*gather_texels=*/false, /*defer_attrs=*/true);
+        rc = build_host_scene(*desc, bvh != 0, s->host, err, host_fast_tree, &device_blas, /*gather_texels=*/false, /*defer_attrs=*/true,
+                              device_emit ? &device_mesh_blas : nullptr);
     } catch (const std::bad_alloc&) {
         rayca_cuda_scene_destroy(s);
         return fail(RAYCA_E_OOM, "host allocation while building the scene");
@@ -514,7 +610,32 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     };
     if (timing) std::fprintf(stderr, "[rayca] %-28s %8.2f ms\n", "build_host_scene (total)", t1 - t0);
     UP(d_nodes, nodes);
-    UP(d_tri_pos, tri_pos);
+    {   // packed positions: models emitted on the device are gathered there by their build's order, the others come from the host
+        bool all_device = !device_meshes.empty();
+        for (const HostBlas& b : h.blas) all_device = all_device && b.tris.empty() && b.device_prims > 0;
+        if (all_device) {
+            s->nbytes[slot_of(&s->d_tri_pos, s)] = std::max<size_t>(h.tri_pos.size() * sizeof(h.tri_pos[0]), 16);
+            if (cudaError_t ce = cudaMallocAsync(&s->d_tri_pos, s->nbytes[slot_of(&s->d_tri_pos, s)], ctx->render_stream); ce != cudaSuccess) {
+                s->d_tri_pos = nullptr;
+                rayca_cuda_scene_destroy(s);
+                return fail(ce == cudaErrorMemoryAllocation ? RAYCA_E_OOM : RAYCA_E_CUDA, std::string("triangle positions: ") + cudaGetErrorString(ce));
+            }
+        } else {
+            UP(d_tri_pos, tri_pos);
+        }
+        for (size_t bi = 0; bi < h.blas.size(); ++bi) {
+            if (!h.blas[bi].tris.empty() || h.blas[bi].device_prims == 0) continue;
+            for (auto& m : device_meshes)
+                if (m.first == h.blas[bi].model && m.second.n == h.blas[bi].device_prims) {
+                    if (gather_tri_pos_device(m.second, (uint32_t)bi, static_cast<float4*>(s->d_tri_pos) + (size_t)h.blas_prim_offset[bi] * 3,
+                                              ctx->render_stream) != RAYCA_OK) {
+                        rayca_cuda_scene_destroy(s);
+                        return fail(RAYCA_E_CUDA, "gathering the triangle positions");
+                    }
+                    break;
+                }
+        }
+    }
     UP(d_materials, materials);
     UP(d_images, images);
     for (uint32_t i = 0; i < desc->image_count; ++i) // the helper thread's layout must be the one the image records carry
@@ -527,7 +648,6 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
     lap("uploads (8 arrays)");
     constexpr int kRing = 3;
     PodVector<float4> ring[kRing]; // page-locked staging of the shading attributes (below); read by copies until the final sync
-    PodVector<unsigned char> raw_stage; // ... or of the caller's vertices and indices, when the device computes the attributes
     std::vector<float4> other_attrs;    // ... and the records of the few primitives that are not mesh triangles
     std::vector<DevMeshJob> dev_jobs;   // ... and the job tables of mesh_attr_kernel
     std::vector<uint32_t> dev_job_begin;
@@ -547,26 +667,16 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
         for (const HostBlas& b : h.blas)
             for (const HostMeshJob& j : b.jobs) mesh_prims += j.ntri;
         const size_t total_prims = h.blas_prim_offset.back();
-        const bool device_attrs = mesh_prims > 0 && total_prims - mesh_prims <= 64 && !std::getenv("RAYCA_HOST_ATTRS") &&
-                                  desc->vertex_count * sizeof(rayca_vertex) + desc->index_count * 4 <= total_prims * 12 * sizeof(float4);
+        const bool device_attrs = !device_meshes.empty() || // (those models have no host triangles to pack from)
+                                  (mesh_prims > 0 && total_prims - mesh_prims <= 64 && !std::getenv("RAYCA_HOST_ATTRS") &&
+                                   desc->vertex_count * sizeof(rayca_vertex) + desc->index_count * 4 <= total_prims * 12 * sizeof(float4));
         if (device_attrs) {
             const size_t attr_bytes = std::max<size_t>(total_prims * 12 * sizeof(float4), 16);
             s->nbytes[slot_of(&s->d_tri_attr, s)] = attr_bytes;
             cudaError_t ce = cudaMallocAsync(&s->d_tri_attr, attr_bytes, ctx->render_stream);
-            // raw vertices | indices, gathered by all threads into one page-locked block (the caller's arrays are pageable)
-            const size_t vbytes = (size_t)desc->vertex_count * sizeof(rayca_vertex), voff = 0, ioff = (vbytes + 255) & ~size_t(255);
-            const size_t ibytes = (size_t)desc->index_count * 4;
-            raw_stage.resize(ioff + ibytes);
-            {
-                struct Piece { const unsigned char* src; size_t dst, bytes; };
-                std::vector<Piece> pieces;
-                for (size_t o = 0; o < vbytes; o += size_t(1) << 20)
-                    pieces.push_back({reinterpret_cast<const unsigned char*>(desc->vertices) + o, voff + o, std::min(vbytes - o, size_t(1) << 20)});
-                for (size_t o = 0; o < ibytes; o += size_t(1) << 20)
-                    pieces.push_back({reinterpret_cast<const unsigned char*>(desc->indices) + o, ioff + o, std::min(ibytes - o, size_t(1) << 20)});
-#pragma omp parallel for schedule(dynamic, 1) if (pieces.size() > 1)
-                for (int64_t k = 0; k < (int64_t)pieces.size(); ++k) std::memcpy(raw_stage.data() + pieces[(size_t)k].dst, pieces[(size_t)k].src, pieces[(size_t)k].bytes);
-            }
+            // the caller's vertices | indices: already on the device when a model was emitted there
+            const size_t voff = 0, ioff = raw_ioff;
+            if (ce == cudaSuccess) ce = upload_raw();
             dev_jobs.clear();
             std::vector<DevMeshJob>& jobs = dev_jobs;
             std::vector<uint32_t>& job_begin = dev_job_begin;
@@ -588,12 +698,9 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
                 }
                 job_begin[bi + 1] = (uint32_t)jobs.size();
             }
-            void *d_raw = nullptr, *d_jobs = nullptr, *d_job_begin = nullptr;
-            if (ce == cudaSuccess) ce = cudaMallocAsync(&d_raw, std::max<size_t>(raw_stage.size(), 16), ctx->render_stream);
+            void *d_jobs = nullptr, *d_job_begin = nullptr;
             if (ce == cudaSuccess) ce = cudaMallocAsync(&d_jobs, jobs.size() * sizeof(DevMeshJob), ctx->render_stream);
             if (ce == cudaSuccess) ce = cudaMallocAsync(&d_job_begin, job_begin.size() * 4, ctx->render_stream);
-            if (ce == cudaSuccess && !raw_stage.empty())
-                ce = cudaMemcpyAsync(d_raw, raw_stage.data(), raw_stage.size(), cudaMemcpyHostToDevice, ctx->render_stream);
             if (ce == cudaSuccess) ce = cudaMemcpyAsync(d_jobs, jobs.data(), jobs.size() * sizeof(DevMeshJob), cudaMemcpyHostToDevice, ctx->render_stream);
             if (ce == cudaSuccess) ce = cudaMemcpyAsync(d_job_begin, job_begin.data(), job_begin.size() * 4, cudaMemcpyHostToDevice, ctx->render_stream);
             if (ce == cudaSuccess) {
@@ -628,7 +735,6 @@ int rayca_cuda_scene_create(rayca_ctx* ctx, const rayca_scene_desc* desc, uint32
                 }
             }
             // (the staging block and the job tables live until scene_create returns, after the stream has been drained)
-            if (d_raw) cudaFreeAsync(d_raw, ctx->render_stream);
             if (d_jobs) cudaFreeAsync(d_jobs, ctx->render_stream);
             if (d_job_begin) cudaFreeAsync(d_job_begin, ctx->render_stream);
             if (ce == cudaSuccess && std::getenv("RAYCA_VERIFY_ATTRS")) { // tests: the device records against the host pack, byte for byte
@@ -1622,6 +1728,8 @@ int rayca_cuda_scene_bvh_read(rayca_scene* s, float* nodes, uint32_t* blas_node_
         if (prim_src) {
             uint32_t* o = prim_src + h.blas_prim_offset[bi];
             for (const HostTri& t : b.tris) *o++ = t.src;
+            if (b.tris.empty()) // a model emitted on the device: the build left its primitive order on the host
+                for (uint32_t src : b.order) *o++ = src;
         }
     }
     return RAYCA_OK;
