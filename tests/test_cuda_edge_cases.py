@@ -277,3 +277,27 @@ def test_scene_outliving_its_context_is_destroyed_safely(cuda_lib):
     assert rgba8.any()
     sc2.close()
     c2.close()
+
+
+def test_out_of_range_vertex_index_is_refused_on_both_emit_paths(ctx, monkeypatch):
+    """An index beyond its geometry's vertices: the host emit loop refuses the scene with RAYCA_E_INVALID_ARG; so must the
+    device emit (models of >= 16384 mesh triangles are emitted by a kernel, which raises a flag the host reads back)."""
+    import ctypes as C
+
+    from rayca_b200 import procedural as P
+
+    desc = P.soup(20_000).to_desc()
+    idx = np.ctypeslib.as_array((C.c_uint32 * int(desc.desc.index_count)).from_address(int(desc.desc.indices)))
+    good = int(idx[12345])
+    idx[12345] = 0x7FFFFFFF
+    try:
+        for host in (False, True):
+            if host:
+                monkeypatch.setenv("RAYCA_HOST_EMIT", "1")
+            with pytest.raises(R.RaycaError) as e:
+                R.DeviceScene(ctx, desc)
+            assert e.value.code == -1 and "vertex index out of range" in str(e.value)
+    finally:
+        idx[12345] = good
+    monkeypatch.delenv("RAYCA_HOST_EMIT", raising=False)
+    R.DeviceScene(ctx, desc).close()  # the repaired scene builds
