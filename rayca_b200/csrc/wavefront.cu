@@ -276,6 +276,11 @@ __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_walk_kernel(const 
 // (14.8 of 32 lanes active per instruction in the one-ray-per-thread stage, profiles/r02_ncu_bounce_wavefront_stage1.json).
 // The walk is walk_fast_body's (trace.cuh), closest hit, triangles only, restated as a resumable loop: the same boxes
 // and triangles are tested with the same arithmetic and the same tie rule, so the hit is the same whatever the order.
+// SPECULATE: a lane that reaches a leaf while others are still descending puts the leaf aside and goes on with its
+// next stack entry (Aila & Laine's "speculative traversal"); the node loop then ends at the lane's SECOND leaf and both
+// are tested — the trip counts of the node loop vary less across the warp.  Entries visited before the postponed leaf
+// could shorten the ray are extra work, never a different hit (culling only ever drops what cannot win).
+template <bool SPECULATE>
 __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_walk_fetch_kernel(const __grid_constant__ RenderParams P, const WaveView w, uint32_t* head) {
     const GpuSceneView& s = P.scene;
     const uint32_t lane = threadIdx.x & 31u;
@@ -308,6 +313,42 @@ __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_walk_fetch_kernel(
         if (slab(lo, hi, ray) == kF32Max) return false;
         ok_leaf = leaf;
         return true;
+    };
+    auto test_leaf = [&](uint32_t ref) { // Triangle::intersects on the leaf's 64-byte records, as in walk_fast_body
+        const V3 o = ray.o, d = ray.d;
+        const uint32_t first = ref & 0x07FFFFFFu, count = ((ref >> 28) & 7u) + 1u;
+        for (uint32_t k = first; k < first + count; ++k) {
+            const float4* q = fast_tri + 4 * (size_t)k;
+            const float4 q0 = __ldg(q);
+            const V3 n{q0.x, q0.y, q0.z};
+            const float ndd = dot(d, n);
+            if (ndd > 0.0f) continue;
+            if (fabsf(ndd) < kF32Eps) continue;
+            const float t = -(dot(n, o) + q0.w) / ndd;
+            if (t < 0.0f) continue;
+            if (t > best_t) continue;
+            const float4 q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+            const V3 v0{q1.x, q1.y, q1.z}, v1{q2.x, q2.y, q2.z}, v2{q3.x, q3.y, q3.z};
+            const V3 p = o + d * t;
+            V3 cc = cross(v1 - v0, p - v0);
+            if (dot(n, cc) < 0.0f) continue;
+            cc = cross(v2 - v1, p - v1);
+            const float u = dot(n, cc);
+            if (u < 0.0f) continue;
+            cc = cross(v0 - v2, p - v2);
+            const float v = dot(n, cc);
+            if (v < 0.0f) continue;
+            const uint32_t id = __float_as_uint(q1.w);
+            if (t < best_t || (t == best_t && id < best && best != 0xFFFFFFFFu)) {
+                if (ref_leaf_accepts(__float_as_uint(q2.w))) {
+                    best_t = t;
+                    best = id;
+                    bu = u;
+                    bv = v;
+                    bden = q3.w;
+                }
+            }
+        }
     };
     for (;;) {
         // ---- idle lanes fetch the next rays of the sorted queue
@@ -352,6 +393,11 @@ __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_walk_fetch_kernel(
         // ---- walk: one "descend to a leaf, test the leaf" round per iteration, for the lanes that hold a ray
         do {
             if (alive) {
+                uint32_t aside = kDone; // SPECULATE: the leaf put aside in this round (kDone: none)
+                if (SPECULATE && (cur & kLeafFlag) && cur != kDone) { // the last pop was a leaf already
+                    aside = cur;
+                    cur = pop();
+                }
                 while (!(cur & kLeafFlag)) {
                     const float4* np = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(fast_nodes) + (unsigned long long)cur * 32ull);
                     const float4 a0 = __ldg(np + 0), a1 = __ldg(np + 1), b0 = __ldg(np + 2), b1 = __ldg(np + 3);
@@ -375,7 +421,12 @@ __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_walk_fetch_kernel(
                     } else {
                         cur = pop();
                     }
+                    if (SPECULATE && (cur & kLeafFlag) && cur != kDone && aside == kDone) {
+                        aside = cur;
+                        cur = pop();
+                    }
                 }
+                if (SPECULATE && aside != kDone) test_leaf(aside);
                 if (cur == kDone) { // the ray is finished: its hit goes out, the lane is free
                     const bool hit = best != 0xFFFFFFFFu;
                     const V3 p = ray.o + ray.d * best_t; // Hit::point, the `p` of the winning test (triangle.rs:121)
@@ -384,40 +435,7 @@ __global__ void __launch_bounds__(128, RAYCA_MIN_BLOCKS) wave_walk_fetch_kernel(
                     w.keys_in[i] = hit ? morton_cell(w, p, w.hit_bits) : w.miss_key;
                     alive = false;
                 } else {
-                    const V3 o = ray.o, d = ray.d;
-                    const uint32_t first = cur & 0x07FFFFFFu, count = ((cur >> 28) & 7u) + 1u;
-                    for (uint32_t k = first; k < first + count; ++k) {
-                        const float4* q = fast_tri + 4 * (size_t)k;
-                        const float4 q0 = __ldg(q);
-                        const V3 n{q0.x, q0.y, q0.z};
-                        const float ndd = dot(d, n);
-                        if (ndd > 0.0f) continue;
-                        if (fabsf(ndd) < kF32Eps) continue;
-                        const float t = -(dot(n, o) + q0.w) / ndd;
-                        if (t < 0.0f) continue;
-                        if (t > best_t) continue;
-                        const float4 q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
-                        const V3 v0{q1.x, q1.y, q1.z}, v1{q2.x, q2.y, q2.z}, v2{q3.x, q3.y, q3.z};
-                        const V3 p = o + d * t;
-                        V3 cc = cross(v1 - v0, p - v0);
-                        if (dot(n, cc) < 0.0f) continue;
-                        cc = cross(v2 - v1, p - v1);
-                        const float u = dot(n, cc);
-                        if (u < 0.0f) continue;
-                        cc = cross(v0 - v2, p - v2);
-                        const float v = dot(n, cc);
-                        if (v < 0.0f) continue;
-                        const uint32_t id = __float_as_uint(q1.w);
-                        if (t < best_t || (t == best_t && id < best && best != 0xFFFFFFFFu)) {
-                            if (ref_leaf_accepts(__float_as_uint(q2.w))) {
-                                best_t = t;
-                                best = id;
-                                bu = u;
-                                bv = v;
-                                bden = q3.w;
-                            }
-                        }
-                    }
+                    test_leaf(cur);
                     cur = pop();
                 }
             }
@@ -517,6 +535,8 @@ int wave_render(const RenderParams& P_in, uint32_t rows, bool spheres, WaveScrat
     uint32_t fetch_min = 16;
     if (const char* e = std::getenv("RAYCA_WAVE_FETCH")) fetch = fetch && std::atoi(e) != 0;
     if (const char* e = std::getenv("RAYCA_WAVE_FETCH_MIN")) fetch_min = (uint32_t)std::min(32, std::max(1, std::atoi(e)));
+    bool speculate = false; // RAYCA_WAVE_SPEC=1: speculative traversal in the walk half (A/B in profiles/r02_wavefront_ab.txt)
+    if (const char* e = std::getenv("RAYCA_WAVE_SPEC")) speculate = std::atoi(e) != 0;
     uint32_t live_bits = key_mode == 0 ? 3 * key_bits + 3 : 3 * key_bits + 2 * dir_bits;
     if (split) live_bits = std::max(live_bits, 3 * hit_bits + 1); // hit keys, then the miss key one bit above them
     const int end_bit = (int)live_bits + 1; // ended paths carry the bit above the live keys
@@ -573,7 +593,8 @@ int wave_render(const RenderParams& P_in, uint32_t rows, bool spheres, WaveScrat
         int dev = 0, sms = 0, per_sm = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_walk_fetch_kernel, 128, 0);
+        if (speculate) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_walk_fetch_kernel<true>, 128, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_walk_fetch_kernel<false>, 128, 0);
         fetch_blocks = (uint32_t)std::max(1, sms * std::max(1, per_sm));
     }
     uint32_t k = 0;
@@ -597,7 +618,8 @@ int wave_render(const RenderParams& P_in, uint32_t rows, bool spheres, WaveScrat
         }
         if (fetch) {
             const uint32_t blocks = std::min<uint32_t>((n + 127) / 128, fetch_blocks);
-            wave_walk_fetch_kernel<<<blocks, 128, 0, st>>>(P, w, w.heads + depth);
+            if (speculate) wave_walk_fetch_kernel<true><<<blocks, 128, 0, st>>>(P, w, w.heads + depth);
+            else wave_walk_fetch_kernel<false><<<blocks, 128, 0, st>>>(P, w, w.heads + depth);
         } else if (spheres) {
             wave_walk_kernel<3><<<(n + 127) / 128, 128, 0, st>>>(P, w);
         } else {

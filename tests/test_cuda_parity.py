@@ -362,8 +362,9 @@ def test_group_checkerboard_shards_equal_single_launch(ctx, atrium, G):
     ("scratcher_sphere", R.Config(max_depth=2), 128, 128),  # spheres: kernel instantiation MODE 3
 ])
 # the stage of a depth: "fetch" (default) = persistent ray walk with dynamic fetch, then shading re-sorted by hit point;
+# "spec" = the same with speculative traversal (a leaf is put aside while the lane goes on descending);
 # "split" = the same two halves, one ray per thread; "stage" = one kernel per depth
-@pytest.mark.parametrize("stage", ["fetch", "split", "stage"])
+@pytest.mark.parametrize("stage", ["fetch", "spec", "split", "stage"])
 def test_wavefront_stages_equal_the_fused_kernel(ctx, scene, cfg, w, h, stage, monkeypatch):
     """bounce rays run as wavefront stages with the live rays radix-sorted between depths
     (wavefront.cu).  The RNG is keyed by (pixel, sample, depth, dimension) and every value is computed by the same
@@ -373,7 +374,8 @@ def test_wavefront_stages_equal_the_fused_kernel(ctx, scene, cfg, w, h, stage, m
 
     monkeypatch.setenv("RAYCA_WAVE_MIN_PATHS", "0")  # small frames normally keep the fused kernel
     monkeypatch.setenv("RAYCA_WAVE_SPLIT", "0" if stage == "stage" else "1")
-    monkeypatch.setenv("RAYCA_WAVE_FETCH", "1" if stage == "fetch" else "0")
+    monkeypatch.setenv("RAYCA_WAVE_FETCH", "1" if stage in ("fetch", "spec") else "0")
+    monkeypatch.setenv("RAYCA_WAVE_SPEC", "1" if stage == "spec" else "0")  # speculative traversal in the walk half
     sc = dev_scene(ctx, scene)
     wave = M.rayca_options(0x5EED, 0, 0, 0, 0, 0, 0)
     fused = M.rayca_options(0x5EED, 0, 0, 0, 0, R.FLAG_NO_WAVEFRONT, 0)
