@@ -181,6 +181,10 @@ void launch_one(const RenderParams& P, dim3 groups, int sm_count, cudaStream_t s
         dim3 grid((unsigned)std::max<unsigned long long>(1, std::min(want, cap)));
         render_kernel<INTEGRATOR, MODE, COUNT, true, BOUNCE><<<grid, 128, 0, st>>>(P);
     } else {
+        // A/B: RAYCA_L1_CARVEOUT=<percent of the L1 / shared-memory array asked for shared memory> (the kernels use none: 0 asks
+        // for the largest L1); unset: the driver's default.  profiles/r02_ab_walk_variants.txt.
+        if (const char* e = std::getenv("RAYCA_L1_CARVEOUT"))
+            cudaFuncSetAttribute(render_kernel<INTEGRATOR, MODE, COUNT, false, BOUNCE>, cudaFuncAttributePreferredSharedMemoryCarveout, std::atoi(e));
         render_kernel<INTEGRATOR, MODE, COUNT, false, BOUNCE><<<groups, kBlockThreads, 0, st>>>(P);
     }
 }
