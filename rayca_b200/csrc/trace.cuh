@@ -30,6 +30,9 @@ constexpr int kStackSize = 96;
 // levels above the 32-primitive subtrees out breadth-first, so these are its top levels) are copied into shared
 // memory once per block with one bulk asynchronous copy (cp.async.bulk, 1-D TMA) and the walk reads them from there.
 // A/B only (tools/variants.py "tl*"), measured no better: profiles/r02_ab_walk_variants.txt.
+#ifndef RAYCA_ANY_NODIST
+#define RAYCA_ANY_NODIST 1 // any-hit walks keep 4-byte stack entries (below); 0 restores 8-byte entries everywhere for A/B runs
+#endif
 #ifndef RAYCA_PREFETCH_FAR
 #define RAYCA_PREFETCH_FAR 0 // prefetch the pushed (far) child's record into L1 (tools/variants.py "pf"): measured in profiles/r02_ab_walk_variants.txt
 #endif
@@ -501,6 +504,24 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
     stack[0] = make_uint2(kDone, 0xff800000u);
     int sp = 1;
     uint32_t cur = go ? s.fast_root_ref : kDone;
+#if RAYCA_ANY_NODIST
+    // An any-hit query never shortens its ray, so an entry that was pushed is never culled later: its distance word is
+    // neither stored nor read — the two words of an entry live in different 128-byte lines of local memory, so the stack
+    // of a shadow ray takes half the L1 lines (+0.2 % on the atrium frame, +0.8 % on the bounce frame: profiles/r02_ab_walk_variants.txt).
+    auto push = [&](uint32_t ref, float dist) {
+        if (ANY) stack[sp].x = ref;
+        else stack[sp] = make_uint2(ref, __float_as_uint(dist));
+        sp = min(sp + 1, kStackSize + 1);
+    };
+    auto pop = [&]() -> uint32_t {
+        if (ANY) return stack[--sp].x;
+        uint2 e;
+        do {
+            e = stack[--sp];
+        } while (__uint_as_float(e.y) > best_t);
+        return e.x;
+    };
+#else
     auto push = [&](uint32_t ref, float dist) {
         stack[sp] = make_uint2(ref, __float_as_uint(dist)); // unguarded store, saturating count
         sp = min(sp + 1, kStackSize + 1);
@@ -512,6 +533,7 @@ __device__ __forceinline__ bool walk_fast_body(const GpuSceneView& s, const RayD
         } while (__uint_as_float(e.y) > best_t);
         return e.x;
     };
+#endif
 #endif
     for (;;) {
         // inner nodes: descend to the nearer accepted child, push the farther one
