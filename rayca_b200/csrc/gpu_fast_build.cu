@@ -173,12 +173,6 @@ __global__ void init_acc(uint32_t* acc, uint32_t nodes) {
     const uint32_t k = i % kAcc;
     acc[i] = (k % 6) < 3 ? kOrdMinInit : kOrdMaxInit;
 }
-__global__ void init_bins(uint32_t* bins, uint32_t nodes) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (size_t)nodes * kNodeBinWords) return;
-    const uint32_t k = (uint32_t)(i % kBinWords);
-    bins[i] = k < 3 ? kOrdMinInit : (k < 6 ? kOrdMaxInit : 0u);
-}
 // Box and centroid box of every big node: positions of a node are contiguous, so a warp first reduces each run of
 // equal slots with shuffles and only the first lane of a run touches memory (same-address atomics from different
 // warps serialise at ~15 ns each: 2 ms per level for the top levels without this).
@@ -251,9 +245,15 @@ __global__ void accumulate_boxes(const float4* __restrict__ bmn, const float4* _
         else atomicMax(a, s_acc[threadIdx.x]);
     }
 }
-__global__ void prepare_nodes(const uint32_t* __restrict__ acc, uint32_t nodes, NodeInfo* info) {
-    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+// one block per node: the node's bins are initialised here as well (was a launch of its own)
+__global__ void prepare_nodes(const uint32_t* __restrict__ acc, uint32_t nodes, NodeInfo* info, uint32_t* bins) {
+    const uint32_t s = blockIdx.x;
     if (s >= nodes) return;
+    for (uint32_t i = threadIdx.x; i < (uint32_t)kNodeBinWords; i += blockDim.x) {
+        const uint32_t k = i % kBinWords;
+        bins[(size_t)s * kNodeBinWords + i] = k < 3 ? kOrdMinInit : (k < 6 ? kOrdMaxInit : 0u);
+    }
+    if (threadIdx.x != 0) return;
     const uint32_t* a = acc + (size_t)s * kAcc;
     NodeInfo ni;
     ni.active = 0;
@@ -421,7 +421,7 @@ __global__ void __launch_bounds__(96) decide_splits(const WorkNode* __restrict__
 }
 // one thread per child: append it to the next level's big list or to the list of small subtrees
 __global__ void make_children(const WorkNode* __restrict__ work, uint32_t nodes, Decision* dec, const uint32_t* __restrict__ big_index,
-                              const uint32_t* __restrict__ small_index, WorkNode* next, WorkNode* small, uint32_t small_base) {
+                              const uint32_t* __restrict__ small_index, WorkNode* next, WorkNode* small, uint32_t small_base, uint32_t* next_acc) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nodes * 2) return;
     const uint32_t s = i >> 1, c = i & 1u;
@@ -436,6 +436,7 @@ __global__ void make_children(const WorkNode* __restrict__ work, uint32_t nodes,
         const uint32_t slot = big_index[i];
         next[slot] = child;
         d.child_slot[c] = slot;
+        for (uint32_t k = 0; k < (uint32_t)kAcc; ++k) next_acc[(size_t)slot * kAcc + k] = (k % 6u) < 3u ? kOrdMinInit : kOrdMaxInit; // was init_acc
     } else {
         small[small_base + small_index[i]] = child;
     }
@@ -690,10 +691,17 @@ __device__ __forceinline__ int ref_bin_of(float c, float lo, float scale) {
     }
     return a;
 }
+// one block per node; `bins` (when given) are initialised here as well (was a launch of its own)
 __global__ void ref_prepare(const uint32_t* __restrict__ acc, const uint32_t* __restrict__ active_ids, uint32_t count, RefNode* nodes,
-                            RefInfo* info) {
-    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+                            RefInfo* info, uint32_t* bins) {
+    const uint32_t s = blockIdx.x;
     if (s >= count) return;
+    if (bins)
+        for (uint32_t i = threadIdx.x; i < (uint32_t)kRefNodeBinWords; i += blockDim.x) {
+            const uint32_t k = i % kBinWords;
+            bins[(size_t)s * kRefNodeBinWords + i] = k < 3 ? kOrdMinInit : (k < 6 ? kOrdMaxInit : 0u);
+        }
+    if (threadIdx.x != 0) return;
     const uint32_t* a = acc + (size_t)s * kAcc;
     RefNode& nd = nodes[active_ids[s]];
     RefInfo ri;
@@ -710,12 +718,6 @@ __global__ void ref_prepare(const uint32_t* __restrict__ acc, const uint32_t* __
         }
     }
     info[s] = ri;
-}
-__global__ void ref_init_bins(uint32_t* bins, uint32_t nodes) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (size_t)nodes * kRefNodeBinWords) return;
-    const uint32_t k = (uint32_t)(i % kBinWords);
-    bins[i] = k < 3 ? kOrdMinInit : (k < 6 ? kOrdMaxInit : 0u);
 }
 __global__ void __launch_bounds__(kBinThreads) ref_bin_prims(const float4* __restrict__ bmn, const float4* __restrict__ bmx,
                                                            const float4* __restrict__ cen, const uint32_t* __restrict__ order,
@@ -912,7 +914,7 @@ __global__ void ref_counts(const uint32_t* __restrict__ active_ids, uint32_t cou
     split_flags[s] = d.split;
 }
 __global__ void ref_children(const uint32_t* __restrict__ active_ids, uint32_t count, RefNode* nodes, RefDecision* dec,
-                             const uint32_t* __restrict__ split_index, uint32_t next_id, uint32_t level, uint32_t* next_active) {
+                             const uint32_t* __restrict__ split_index, uint32_t next_id, uint32_t level, uint32_t* next_active, uint32_t* next_acc) {
     const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= count) return;
     RefDecision& d = dec[s];
@@ -931,6 +933,7 @@ __global__ void ref_children(const uint32_t* __restrict__ active_ids, uint32_t c
         nodes[left + c] = ch;
         next_active[2 * k + c] = left + c;
         d.child_slot[c] = 2 * k + c;
+        for (uint32_t j = 0; j < (uint32_t)kAcc; ++j) next_acc[(size_t)(2 * k + c) * kAcc + j] = (j % 6u) < 3u ? kOrdMinInit : kOrdMaxInit; // was init_acc
     }
 }
 // the permutation of the swap loop, part 1: where the holes and the tail lefts are
@@ -1231,8 +1234,7 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
     }
     while (nbig > 0) {
         const int nxt = cur ^ 1;
-        prepare_nodes<<<blocks_for(nbig, T), T, 0, st>>>(d_acc[cur], nbig, d_info);
-        init_bins<<<blocks_for((size_t)nbig * kNodeBinWords, T), T, 0, st>>>(d_bins, nbig);
+        prepare_nodes<<<nbig, 224, 0, st>>>(d_acc[cur], nbig, d_info, d_bins);
         bin_prims<<<blocks_for(N, kBinThreads), kBinThreads, 0, st>>>(d_mn, d_mx, d_order[cur], d_node_of[cur], N, d_info, d_bins);
         decide_splits<<<nbig, 96, 0, st>>>(d_work[cur], nbig, d_info, d_bins, pair_base, d_dec, d_records, d_root,
                                                            d_child_big, d_child_small);
@@ -1244,8 +1246,7 @@ int build_fast_tree_device(const HostScene& hs, const float4* d_tri_pos, cudaStr
         FB_TRY(cudaStreamSynchronize(st));
         if (counts[0] > cap_big || (size_t)nsmall + counts[1] > N) { err = "device tree build: work list overflow"; return RAYCA_E_CUDA; }
         make_children<<<blocks_for((size_t)nbig * 2, T), T, 0, st>>>(d_work[cur], nbig, d_dec, d_big_index, d_small_index, d_work[nxt],
-                                                                  d_small, nsmall);
-        if (counts[0]) init_acc<<<blocks_for((size_t)counts[0] * kAcc, T), T, 0, st>>>(d_acc[nxt], counts[0]);
+                                                                  d_small, nsmall, d_acc[nxt]);
         left_flags<<<blocks_for(N, T), T, 0, st>>>(d_mn, d_mx, d_order[cur], d_node_of[cur], N, d_work[cur], d_dec, d_flags);
         exclusive_scan(d_flags, N, d_scan, d_partial, st);
         scatter_prims<<<blocks_for(N, T), T, 0, st>>>(d_order[cur], d_node_of[cur], N, d_work[cur], d_dec, d_flags, d_scan, d_order[nxt],
@@ -1401,10 +1402,9 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
     uint32_t count = 1, next_id = 2, level = 0;
     int cur = 0;
     for (;;) {
-        ref_prepare<<<blocks_for(count, T), T, 0, st>>>(d_acc[cur], d_active[cur], count, d_nodes, d_info);
+        ref_prepare<<<count, 256, 0, st>>>(d_acc[cur], d_active[cur], count, d_nodes, d_info, level >= max_depth ? nullptr : d_bins);
         if (level >= max_depth) break;
         const int nxt = cur ^ 1;
-        ref_init_bins<<<blocks_for((size_t)count * kRefNodeBinWords, T), T, 0, st>>>(d_bins, count);
         ref_bin_prims<<<blocks_for(N, kBinThreads), kBinThreads, 0, st>>>(d_mn, d_mx, d_cen, d_order[cur], d_node_of[cur], N, d_info, d_bins);
         ref_decide<<<count, 96, 0, st>>>(d_active[cur], count, d_nodes, d_info, d_bins, d_dec, d_split);
         ref_flags<<<blocks_for(N, T), T, 0, st>>>(d_cen, d_order[cur], d_node_of[cur], N, d_dec, d_flags);
@@ -1418,13 +1418,12 @@ int build_blas_device(HostBlas& blas, uint32_t max_depth, cudaStream_t st, std::
             err = "device BLAS build: level too broad";
             return RAYCA_E_UNSUPPORTED;
         }
-        ref_children<<<blocks_for(count, T), T, 0, st>>>(d_active[cur], count, d_nodes, d_dec, d_split_index, next_id, level, d_active[nxt]);
+        ref_children<<<blocks_for(count, T), T, 0, st>>>(d_active[cur], count, d_nodes, d_dec, d_split_index, next_id, level, d_active[nxt], d_acc[nxt]);
         ref_tables<<<blocks_for(N, T), T, 0, st>>>(d_node_of[cur], N, d_active[cur], d_nodes, d_dec, d_flags, d_scan, d_hole, d_tail);
         ref_scatter<<<blocks_for(N, T), T, 0, st>>>(d_order[cur], d_node_of[cur], N, d_active[cur], d_nodes, d_dec, d_flags, d_scan, d_hole,
                                                     d_tail, d_order[nxt], d_node_of[nxt]);
         cur = nxt; // the partition may have reordered ranges even when nothing split
         if (splits == 0) break;
-        init_acc<<<blocks_for((size_t)splits * 2 * kAcc, T), T, 0, st>>>(d_acc[cur], splits * 2);
         accumulate_boxes<<<blocks_for(N, T), T, 0, st>>>(d_mn, d_mx, d_order[cur], d_node_of[cur], N, d_acc[cur]);
         next_id += 2 * splits;
         count = 2 * splits;
